@@ -1,0 +1,551 @@
+"""Host-side schedule of the K3M pretraining step: forward, hand-written backward, in terms of
+the kernel contracts of `include/k3m.h` (op table `k3m_b200.ops.CudaOps`).
+
+What the schedule follows in the reference (all in `vilbert_k3m/vilbert_k3m.py`):
+`bert_tri` `:2507-2671` -> `BertEncoder.forward` `:1686-1750` (three pairwise passes) ->
+`get_sequence_pooled_output_final` `:2376-2411` -> `structure_aggregator` `:2413-2505` ->
+`BertPreTrainingHeads.forward` `:1875-1909` -> loss block `:2739-2846`.
+
+B200-first differences from the reference's eager graph (results are the same):
+  * The three passes run in lock-step.  The four text-side streams (title@t<->v, title@t<->pv,
+    PV@pv<->v, PV@t<->pv) all apply the same `encoder.layer[i]` weights at the same point of
+    their pass, so they are stacked along M into one [4*B*L, H] GEMM per projection; the two
+    image streams are stacked the same way for `encoder.v_layer[i]`.
+  * q/k/v (and the three fusion gates) are single fused GEMMs over adjacent arena weights.
+  * bias, GELU, dropout, residual add live in GEMM epilogues; dropout masks are regenerated
+    from a counter-based RNG in backward, never stored.
+  * There is no autograd graph: every block has an explicit backward that writes weight
+    gradients straight into one flat fp32 arena (the all-reduce / AdamW buffer).
+  * Static shapes, no host synchronisation inside -> the whole step is CUDA-graph capturable.
+"""
+import torch
+
+from .struct_plan import build_struct_plan
+
+ACT_NONE, ACT_GELU, ACT_DGELU, ACT_SIGMOID, ACT_TANH, ACT_DTANH = 0, 1, 2, 3, 4, 5
+
+
+class _Seg(object):
+    """A run of `B` sequences of length `L` starting at row `r0` of a stacked activation."""
+    __slots__ = ("r0", "B", "L", "mask")
+
+    def __init__(self, r0, B, L, mask):
+        self.r0, self.B, self.L, self.mask = r0, B, L, mask
+
+    @property
+    def r1(self):
+        return self.r0 + self.B * self.L
+
+
+def _merge_segs(segs):
+    """Adjacent segments with equal L become one attention launch (masks concatenated)."""
+    out = []
+    for s in segs:
+        if out and out[-1].L == s.L and out[-1].r1 == s.r0:
+            p = out[-1]
+            out[-1] = _Seg(p.r0, p.B + s.B, p.L, torch.cat([p.mask, s.mask], 0))
+        else:
+            out.append(s)
+    return out
+
+
+class Engine(object):
+    def __init__(self, cfg, layout, ops, weights, grads, rng, act_dtype):
+        """weights: flat arena in `act_dtype` (bf16 shadow of the fp32 masters);
+        grads: flat fp32 arena of the same layout; rng: int64 [2] device tensor (seed, step)."""
+        self.cfg, self.layout, self.ops = cfg, layout, ops
+        self.w, self.g, self.rng, self.adt = weights, grads, rng, act_dtype
+        self.training = False
+        self.tape = []
+        self._site = 0
+        self._wv, self._gv = {}, {}
+
+    # ---- views / small helpers -------------------------------------------------------------
+    def W(self, name):
+        v = self._wv.get(name)
+        if v is None:
+            v = self._wv[name] = self.layout.view(self.w, name)
+        return v
+
+    def G(self, name):
+        v = self._gv.get(name)
+        if v is None:
+            v = self._gv[name] = self.layout.view(self.g, name)
+        return v
+
+    def site(self, p):
+        """A dropout application: (p, unique site id) in training mode, else None."""
+        self._site += 1
+        if self.training and p > 0.0:
+            return (float(p), self._site)
+        return None
+
+    def empty(self, rows, cols, dtype=None):
+        return torch.empty(rows, cols, dtype=dtype or self.adt, device=self.w.device)
+
+    def zeros(self, rows, cols, dtype=None):
+        return torch.zeros(rows, cols, dtype=dtype or self.adt, device=self.w.device)
+
+    def wgrad(self, dy, x, wname):
+        """G[w] += dy^T x    (dy [M,out], x [M,in] -> [out,in])."""
+        self.ops.gemm(dy, x, "tn", out=self.G(wname), accumulate=True)
+
+    def dgrad(self, dy, wname, **kw):
+        """dy [M,out] @ W[out,in] -> [M,in]."""
+        return self.ops.gemm(dy, self.W(wname), "nn", rng=self.rng, **kw)
+
+    # ---- blocks ------------------------------------------------------------------------------
+    def attn_out_fwd(self, ctx, x, p_dense, p_ln, p_drop):
+        """LN(dropout(ctx W^T + b) + x)  — BertSelfOutput `:485-489` and the BertBiOutput halves
+        `:986-996`."""
+        ops = self.ops
+        s = self.site(p_drop)
+        z = ops.gemm(ctx, self.W(p_dense + ".weight"), "nt", bias=self.W(p_dense + ".bias"),
+                     drop=s, rng=self.rng, addend=x)
+        a, mean, rstd = ops.ln_fwd(z, self.W(p_ln + ".weight"), self.W(p_ln + ".bias"))
+        return a, (ctx, z, mean, rstd, s, p_dense, p_ln)
+
+    def attn_out_bwd(self, da, saved):
+        """-> (dx residual grad, dctx)."""
+        ctx, z, mean, rstd, s, p_dense, p_ln = saved
+        dz, dzm = self.ops.ln_bwd(da, z, self.W(p_ln + ".weight"), mean, rstd,
+                                  self.G(p_ln + ".weight"), self.G(p_ln + ".bias"),
+                                  drop_in=s, rng=self.rng, dbias=self.G(p_dense + ".bias"))
+        self.wgrad(dzm, ctx, p_dense + ".weight")
+        dctx = self.dgrad(dzm, p_dense + ".weight")
+        return dz, dctx
+
+    def ffn_fwd(self, a, p_int, p_out, p_drop, out=None):
+        """LN(dropout(gelu(a W1^T + b1) W2^T + b2) + a) — BertIntermediate `:515-518` +
+        BertOutput `:528-532` (and the image twins)."""
+        ops = self.ops
+        M = a.shape[0]
+        w1 = self.W(p_int + ".dense.weight")
+        pre = self.empty(M, w1.shape[0])
+        h = ops.gemm(a, w1, "nt", bias=self.W(p_int + ".dense.bias"), act=ACT_GELU, aux_out=pre)
+        s = self.site(p_drop)
+        z = ops.gemm(h, self.W(p_out + ".dense.weight"), "nt", bias=self.W(p_out + ".dense.bias"),
+                     drop=s, rng=self.rng, addend=a)
+        y, mean, rstd = ops.ln_fwd(z, self.W(p_out + ".LayerNorm.weight"),
+                                   self.W(p_out + ".LayerNorm.bias"), out=out)
+        return y, (a, pre, h, z, mean, rstd, s, p_int, p_out)
+
+    def ffn_bwd(self, dy, saved):
+        a, pre, h, z, mean, rstd, s, p_int, p_out = saved
+        ops = self.ops
+        dz, dzm = ops.ln_bwd(dy, z, self.W(p_out + ".LayerNorm.weight"), mean, rstd,
+                             self.G(p_out + ".LayerNorm.weight"), self.G(p_out + ".LayerNorm.bias"),
+                             drop_in=s, rng=self.rng, dbias=self.G(p_out + ".dense.bias"))
+        self.wgrad(dzm, h, p_out + ".dense.weight")
+        dpre = self.dgrad(dzm, p_out + ".dense.weight", act=ACT_DGELU, aux_in=pre)
+        ops.colsum(dpre, self.G(p_int + ".dense.bias"))
+        self.wgrad(dpre, a, p_int + ".dense.weight")
+        return self.dgrad(dpre, p_int + ".dense.weight", addend=dz)
+
+    def layer_fwd(self, p, x, segs, image, out=None):
+        """BertLayer `:535-548` / BertImageLayer `:696-709` on a stacked activation."""
+        c, ops = self.cfg, self.ops
+        H = x.shape[1]
+        heads = c.v_num_attention_heads if image else c.num_attention_heads
+        p_att = c.v_attention_probs_dropout_prob if image else c.attention_probs_dropout_prob
+        p_hid = c.v_hidden_dropout_prob if image else c.hidden_dropout_prob
+        d = H // heads
+        qkv = ops.gemm(x, self.W(p + ".attention.self.qkv.weight"), "nt",
+                       bias=self.W(p + ".attention.self.qkv.bias"))
+        ctx = self.empty(x.shape[0], H)
+        att = []
+        for sg in segs:
+            s = self.site(p_att)
+            v = qkv[sg.r0:sg.r1]
+            _, lse = ops.attn_fwd(v, 0, v, H, 2 * H, sg.mask, sg.B, heads, sg.L, sg.L, d,
+                                  drop=s, rng=self.rng, out=ctx[sg.r0:sg.r1])
+            att.append((sg, s, lse))
+        a, sv_o = self.attn_out_fwd(ctx, x, p + ".attention.output.dense",
+                                    p + ".attention.output.LayerNorm", p_hid)
+        y, sv_f = self.ffn_fwd(a, p + ".intermediate", p + ".output", p_hid, out=out)
+        saved = (p, x, qkv, att, heads, d, sv_o, sv_f)
+        return y, saved
+
+    def layer_bwd(self, dy, saved):
+        p, x, qkv, att, heads, d, sv_o, sv_f = saved
+        ops = self.ops
+        H = x.shape[1]
+        da = self.ffn_bwd(dy, sv_f)
+        dz1, dctx = self.attn_out_bwd(da, sv_o)
+        ctx = sv_o[0]
+        dqkv = self.empty(x.shape[0], 3 * H)
+        for sg, s, lse in att:
+            v = qkv[sg.r0:sg.r1]
+            dv = dqkv[sg.r0:sg.r1]
+            ops.attn_bwd(dctx[sg.r0:sg.r1], ctx[sg.r0:sg.r1], v, 0, v, H, 2 * H, sg.mask, lse,
+                         dv, dv, sg.B, heads, sg.L, sg.L, d, drop=s, rng=self.rng)
+        ops.colsum(dqkv, self.G(p + ".attention.self.qkv.bias"))
+        self.wgrad(dqkv, x, p + ".attention.self.qkv.weight")
+        return self.dgrad(dqkv, p + ".attention.self.qkv.weight", addend=dz1)
+
+    def connection_fwd(self, p, x1, sg1, x2, sg2, two_text, out1, out2):
+        """BertConnectionLayer `:1030-1071` / `_two_text` `:1074-1111`.  Stream 1 = image (PV in
+        the two-text pass), stream 2 = text.  ctx1 (text-length) = queries of 2 over K/V of 1,
+        masked by mask1 (`:786-800`); ctx2 = queries of 1 over K/V of 2.  The image stream gets
+        ctx2 through dense1, the text stream ctx1 through dense2 (`:1061-1063`)."""
+        c, ops = self.cfg, self.ops
+        heads = c.bi_num_attention_heads
+        Hb = c.hidden_size if two_text else c.bi_hidden_size
+        d = Hb // heads
+        B, L1, L2 = sg1.B, sg1.L, sg2.L
+        b = p + ".biattention."
+        qkv1 = ops.gemm(x1, self.W(b + "qkv1.weight"), "nt", bias=self.W(b + "qkv1.bias"))
+        qkv2 = ops.gemm(x2, self.W(b + "qkv2.weight"), "nt", bias=self.W(b + "qkv2.bias"))
+        s1 = self.site(c.v_attention_probs_dropout_prob)
+        ctx1, lse1 = ops.attn_fwd(qkv2, 0, qkv1, Hb, 2 * Hb, sg1.mask, B, heads, L2, L1, d,
+                                  drop=s1, rng=self.rng)
+        s2 = self.site(c.attention_probs_dropout_prob)
+        ctx2, lse2 = ops.attn_fwd(qkv1, 0, qkv2, Hb, 2 * Hb, sg2.mask, B, heads, L1, L2, d,
+                                  drop=s2, rng=self.rng)
+        o = p + ".biOutput."
+        a1, sv_o1 = self.attn_out_fwd(ctx2, x1, o + "dense1", o + "LayerNorm1", c.v_hidden_dropout_prob)
+        a2, sv_o2 = self.attn_out_fwd(ctx1, x2, o + "dense2", o + "LayerNorm2", c.hidden_dropout_prob)
+        p1 = c.hidden_dropout_prob if two_text else c.v_hidden_dropout_prob
+        y1, sv_f1 = self.ffn_fwd(a1, p + ".v_intermediate", p + ".v_output", p1, out=out1)
+        y2, sv_f2 = self.ffn_fwd(a2, p + ".t_intermediate", p + ".t_output", c.hidden_dropout_prob,
+                                 out=out2)
+        saved = (p, x1, sg1, x2, sg2, Hb, heads, d, qkv1, qkv2, (s1, lse1), (s2, lse2),
+                 sv_o1, sv_o2, sv_f1, sv_f2)
+        return y1, y2, saved
+
+    def connection_bwd(self, dy1, dy2, saved, dx1_out, dx2_out):
+        (p, x1, sg1, x2, sg2, Hb, heads, d, qkv1, qkv2, (s1, lse1), (s2, lse2),
+         sv_o1, sv_o2, sv_f1, sv_f2) = saved
+        ops = self.ops
+        B, L1, L2 = sg1.B, sg1.L, sg2.L
+        da1 = self.ffn_bwd(dy1, sv_f1)
+        da2 = self.ffn_bwd(dy2, sv_f2)
+        dz1, dctx2 = self.attn_out_bwd(da1, sv_o1)      # residual grads of x1 / x2
+        dz2, dctx1 = self.attn_out_bwd(da2, sv_o2)
+        ctx2, ctx1 = sv_o1[0], sv_o2[0]
+        dqkv1 = self.empty(x1.shape[0], 3 * Hb)
+        dqkv2 = self.empty(x2.shape[0], 3 * Hb)
+        ops.attn_bwd(dctx1, ctx1, qkv2, 0, qkv1, Hb, 2 * Hb, sg1.mask, lse1, dqkv2, dqkv1,
+                     B, heads, L2, L1, d, drop=s1, rng=self.rng)
+        ops.attn_bwd(dctx2, ctx2, qkv1, 0, qkv2, Hb, 2 * Hb, sg2.mask, lse2, dqkv1, dqkv2,
+                     B, heads, L1, L2, d, drop=s2, rng=self.rng)
+        b = p + ".biattention."
+        ops.colsum(dqkv1, self.G(b + "qkv1.bias"))
+        ops.colsum(dqkv2, self.G(b + "qkv2.bias"))
+        self.wgrad(dqkv1, x1, b + "qkv1.weight")
+        self.wgrad(dqkv2, x2, b + "qkv2.weight")
+        self.dgrad(dqkv1, b + "qkv1.weight", addend=dz1, out=dx1_out)
+        self.dgrad(dqkv2, b + "qkv2.weight", addend=dz2, out=dx2_out)
+
+    # ---- embeddings ------------------------------------------------------------------------
+    def text_embed_fwd(self, ids, type_ids, L):
+        """BertEmbeddings `:361-382` (position ids are always arange(L), `:364`)."""
+        ops = self.ops
+        e = "embeddings."
+        x = ops.embed_fwd(ids, type_ids, self.W(e + "word_embeddings.weight"),
+                          self.W(e + "position_embeddings.weight"),
+                          self.W(e + "token_type_embeddings.weight"), L)
+        s = self.site(self.cfg.hidden_dropout_prob)
+        y, mean, rstd = ops.ln_fwd(x, self.W(e + "LayerNorm.weight"), self.W(e + "LayerNorm.bias"),
+                                   drop=s, rng=self.rng)
+        return y, (ids, type_ids, L, x, mean, rstd, s)
+
+    def text_embed_bwd(self, dy, saved):
+        ids, type_ids, L, x, mean, rstd, s = saved
+        e = "embeddings."
+        dx, _ = self.ops.ln_bwd(dy, x, self.W(e + "LayerNorm.weight"), mean, rstd,
+                                self.G(e + "LayerNorm.weight"), self.G(e + "LayerNorm.bias"),
+                                drop_out=s, rng=self.rng)
+        self.ops.embed_bwd(dx, ids, type_ids, L, self.G(e + "word_embeddings.weight"),
+                           self.G(e + "position_embeddings.weight"),
+                           self.G(e + "token_type_embeddings.weight"))
+
+    def image_embed_fwd(self, feat, loc):
+        """BertImageEmbeddings `:2153-2161`: the 5-d box projection is the GEMM's addend."""
+        ops = self.ops
+        e = "v_embeddings."
+        fa = ops.cast(feat, self.adt)
+        le = ops.loc_embed_fwd(loc, self.W(e + "image_location_embeddings.weight"),
+                               self.W(e + "image_location_embeddings.bias"))
+        z = ops.gemm(fa, self.W(e + "image_embeddings.weight"), "nt",
+                     bias=self.W(e + "image_embeddings.bias"), addend=le)
+        s = self.site(self.cfg.hidden_dropout_prob)
+        y, mean, rstd = ops.ln_fwd(z, self.W(e + "LayerNorm.weight"), self.W(e + "LayerNorm.bias"),
+                                   drop=s, rng=self.rng)
+        return y, (fa, loc, z, mean, rstd, s)
+
+    def image_embed_bwd(self, dy, saved):
+        fa, loc, z, mean, rstd, s = saved
+        e = "v_embeddings."
+        _, dz = self.ops.ln_bwd(dy, z, self.W(e + "LayerNorm.weight"), mean, rstd,
+                                self.G(e + "LayerNorm.weight"), self.G(e + "LayerNorm.bias"),
+                                drop_out=s, rng=self.rng, dbias=self.G(e + "image_embeddings.bias"),
+                                want_masked=True)
+        self.wgrad(dz, fa, e + "image_embeddings.weight")
+        self.ops.loc_embed_bwd(dz, loc, self.G(e + "image_location_embeddings.weight"),
+                               self.G(e + "image_location_embeddings.bias"))
+
+    # ---- fusion ----------------------------------------------------------------------------
+    def fuse_fwd(self, mod, indiv, c1, c2, noise, out):
+        """`get_sequence_pooled_output_final` `:2376-2411`; mode 1 = `pre_sampling_sequence`
+        `:2331-2374` (hard Gumbel pick per token and channel, straight-through backward)."""
+        ops, mode = self.ops, self.cfg.if_pre_sampling
+        if mode == 0:
+            ops.lincomb3(indiv, c1, c2, 1.0 / 3, 1.0 / 3, 1.0 / 3, out=out)
+            return (mode,)
+        if mode == 2:
+            raise NotImplementedError("if_pre_sampling=2 (soft fusion) is not on the K3M hot path")
+        if mode != 1:
+            ops.lincomb3(c1, c2, None, 0.5, 0.5, 0.0, out=out)
+            return (mode,)
+        cat = ops.relu_cat3(indiv, c1, c2)
+        gates = ops.gemm(cat, self.W("score_%s.weight" % mod), "nt",
+                         bias=self.W("score_%s.bias" % mod), out_dtype=torch.float32)
+        self._site += 1
+        site = self._site
+        ops.fuse_select_fwd(cat, gates, noise=noise, site=site, rng=self.rng, out=out)
+        return (mode, mod, cat, gates, noise, site)
+
+    def fuse_bwd(self, dout, saved, d_indiv, d_c1, d_c2):
+        """Accumulates into d_indiv / d_c1 / d_c2 (all pre-initialised)."""
+        ops, mode = self.ops, saved[0]
+        if mode == 0:
+            for t in (d_indiv, d_c1, d_c2):
+                ops.axpy(dout, t, 1.0 / 3)
+            return
+        if mode != 1:
+            ops.axpy(dout, d_c1, 0.5)
+            ops.axpy(dout, d_c2, 0.5)
+            return
+        _, mod, cat, gates, noise, site = saved
+        dgates, dcat = ops.fuse_select_bwd(dout, cat, gates, noise=noise, site=site, rng=self.rng)
+        ops.colsum(dgates, self.G("score_%s.bias" % mod))
+        self.wgrad(dgates, cat, "score_%s.weight" % mod)
+        self.dgrad(dgates, "score_%s.weight" % mod, addend=dcat, out=dcat)
+        ops.relu_bwd_split3(dcat, cat, d_indiv, d_c1, d_c2)
+
+    # ---- heads -----------------------------------------------------------------------------
+    def head_fwd(self, p, x, p_dec_w, p_dec_b, logits_dtype, n_cols):
+        """transform (dense -> GELU -> LN, `:1795-1799` / `:1814-1818`) + decoder."""
+        ops = self.ops
+        M, H = x.shape
+        pre = self.empty(M, H)
+        h = ops.gemm(x, self.W(p + ".transform.dense.weight"), "nt",
+                     bias=self.W(p + ".transform.dense.bias"), act=ACT_GELU, aux_out=pre)
+        hn, mean, rstd = ops.ln_fwd(h, self.W(p + ".transform.LayerNorm.weight"),
+                                    self.W(p + ".transform.LayerNorm.bias"))
+        ld = (n_cols + 7) // 8 * 8
+        logits = self.zeros(M, ld, logits_dtype) if ld != n_cols else self.empty(M, ld, logits_dtype)
+        ops.gemm(hn, self.W(p_dec_w), "nt", bias=self.W(p_dec_b), out=logits[:, :n_cols])
+        return logits, (p, x, pre, h, hn, mean, rstd, p_dec_w, p_dec_b, n_cols)
+
+    def head_bwd(self, dlogits, saved, dx):
+        """dlogits [M, ld] in act dtype (columns >= n_cols are zero); dx += grad of x."""
+        p, x, pre, h, hn, mean, rstd, p_dec_w, p_dec_b, n_cols = saved
+        ops = self.ops
+        dl = dlogits[:, :n_cols]
+        ops.colsum(dl, self.G(p_dec_b))
+        self.wgrad(dl, hn, p_dec_w)
+        dhn = self.dgrad(dl, p_dec_w)
+        dh, _ = ops.ln_bwd(dhn, h, self.W(p + ".transform.LayerNorm.weight"), mean, rstd,
+                           self.G(p + ".transform.LayerNorm.weight"),
+                           self.G(p + ".transform.LayerNorm.bias"))
+        dpre = ops.act_bwd(dh, pre, ACT_DGELU)
+        ops.colsum(dpre, self.G(p + ".transform.dense.bias"))
+        self.wgrad(dpre, x, p + ".transform.dense.weight")
+        self.dgrad(dpre, p + ".transform.dense.weight", addend=dx, out=dx)
+
+    # ---- structure aggregator + LPM ----------------------------------------------------------
+    def struct_fwd(self, c_init, seq_pv, plan):
+        """`structure_aggregator` `:2413-2505` as batched kernels over the host-built plan."""
+        ops, f32 = self.ops, torch.float32
+        B, H = c_init.shape
+        X, PV = ops.pair_gather_fwd(c_init, seq_pv, plan["pair_item"], plan["pair_rows"])
+        t = ops.gemm(X, self.W("struc_w1.weight"), "nt", bias=self.W("struc_w1.bias"), out_dtype=f32)
+        s, att = ops.struct_attn_fwd(t, self.W("struc_w2.weight"), self.W("struc_w2.bias"), plan["seg"])
+        s_a = ops.cast(s, self.adt)
+        c_final = ops.gemm(s_a, self.W("struc_w3.weight"), "nt", bias=self.W("struc_w3.bias"),
+                           addend=c_init, out_dtype=f32)
+        dc_final = self.zeros(B, H, f32)
+        dPV = self.zeros(PV.shape[0], 2 * H, f32)
+        loss = ops.lpm_fwd_bwd(c_final, PV, plan["terms"], float(self.cfg.margin), dc_final, dPV)
+        return c_final, loss, (plan, X, t, att, s_a, dc_final, dPV)
+
+    def struct_bwd(self, saved, w_lpm, dc_init, dseq_pv):
+        """dc_init [B,H] fp32 += ; dseq_pv [B*L,H] += ."""
+        plan, X, t, att, s_a, dc_final, dPV = saved
+        ops, f32 = self.ops, torch.float32
+        if w_lpm != 1.0:
+            ops.scale_(dc_final, w_lpm)
+            ops.scale_(dPV, w_lpm)
+        ops.axpy(dc_final, dc_init, 1.0)
+        ops.colsum(dc_final, self.G("struc_w3.bias"))
+        dcf = ops.cast(dc_final, self.adt)
+        self.wgrad(dcf, s_a, "struc_w3.weight")
+        ds = self.dgrad(dcf, "struc_w3.weight", out_dtype=f32)
+        dt = self.zeros(t.shape[0], t.shape[1], f32)
+        ops.struct_attn_bwd(ds, t, att, self.W("struc_w2.weight"), plan["seg"], dt,
+                            self.G("struc_w2.weight"), self.G("struc_w2.bias"))
+        ops.colsum(dt, self.G("struc_w1.bias"))
+        dta = ops.cast(dt, self.adt)
+        self.wgrad(dta, X, "struc_w1.weight")
+        dX = self.dgrad(dta, "struc_w1.weight", out_dtype=f32)
+        ops.pair_gather_bwd(dX, dPV, plan["pair_item"], plan["pair_rows"], dc_init, dseq_pv)
+
+    # ---- the step --------------------------------------------------------------------------
+    def forward(self, batch, plan, noise=None, loss_weights=(1.0, 1.0, 1.0, 1.0)):
+        """batch: dict of device tensors named as the reference's forward() arguments
+        (`vilbert_k3m.py:2673-2696`); plan: device tensors from `build_struct_plan`;
+        noise: optional dict mod -> [B*L, 3, H] fp32 Gumbel noise (parity mode);
+        loss_weights: (mlm_t, mrm, mlm_pv, lpm) weights of the summed loss (`pretrain.py:1055`).
+        Returns dict(loss_t, loss_v, loss_pv, loss_itm, loss_lpm (each fp32 [1]), c_initial,
+        c_final)."""
+        c, ops, f32 = self.cfg, self.ops, torch.float32
+        self.tape, self._site = [], 0
+        noise = noise or {}
+        ids_t, ids_pv = batch["input_ids"], batch["input_ids_pv"]
+        B, Lt = ids_t.shape
+        Lpv = ids_pv.shape[1]
+        Lv1 = batch["image_feat"].shape[1]
+        H, Hv = c.hidden_size, c.v_hidden_size
+        Mt, Mp, Mv = B * Lt, B * Lpv, B * Lv1
+        mask_t = ops.mask_additive(batch["attention_mask"])          # `:2561`
+        mask_pv = ops.mask_additive(batch["attention_mask_pv"])      # `:2570`
+        mask_v = ops.mask_additive(batch["image_attention_mask"])    # `:2580`
+        e_t, sv_et = self.text_embed_fwd(ids_t.reshape(-1), batch["token_type_ids"].reshape(-1), Lt)
+        e_pv, sv_epv = self.text_embed_fwd(ids_pv.reshape(-1), batch["token_type_ids_pv"].reshape(-1), Lpv)
+        e_v, sv_ev = self.image_embed_fwd(batch["image_feat"].reshape(Mv, -1),
+                                          batch["image_loc"].reshape(Mv, -1))
+        # stacked streams: text [T1 | T3 | P2 | P3], image [V1 | V2]
+        T1, T3 = slice(0, Mt), slice(Mt, 2 * Mt)
+        P2, P3 = slice(2 * Mt, 2 * Mt + Mp), slice(2 * Mt + Mp, 2 * Mt + 2 * Mp)
+        V1, V2 = slice(0, Mv), slice(Mv, 2 * Mv)
+        X = self.empty(2 * Mt + 2 * Mp, H)
+        Y = self.empty(2 * Mv, Hv)
+        for sl in (T1, T3):
+            X[sl].copy_(e_t)
+        for sl in (P2, P3):
+            X[sl].copy_(e_pv)
+        for sl in (V1, V2):
+            Y[sl].copy_(e_v)
+        sgT, sgP, sgV = _Seg(0, B, Lt, mask_t), _Seg(0, B, Lpv, mask_pv), _Seg(0, B, Lv1, mask_v)
+        segs_x = _merge_segs([_Seg(0, B, Lt, mask_t), _Seg(Mt, B, Lt, mask_t),
+                              _Seg(2 * Mt, B, Lpv, mask_pv), _Seg(2 * Mt + Mp, B, Lpv, mask_pv)])
+        segs_y = _merge_segs([_Seg(0, B, Lv1, mask_v), _Seg(Mv, B, Lv1, mask_v)])
+        stages = []
+        s1 = s2 = 0
+        for count, (e1, e2) in enumerate(zip(c.v_biattention_id, c.t_biattention_id)):
+            for i in range(s2, e2):
+                X, sv = self.layer_fwd("encoder.layer.%d" % i, X, segs_x, False)
+                stages.append(("t", sv))
+            for i in range(s1, e1):
+                Y, sv = self.layer_fwd("encoder.v_layer.%d" % i, Y, segs_y, True)
+                stages.append(("v", sv))
+            Xn, Yn = torch.empty_like(X), torch.empty_like(Y)
+            _, _, sa = self.connection_fwd("encoder.c_layer.%d" % count, Y[V1], sgV, X[T1], sgT,
+                                           False, Yn[V1], Xn[T1])
+            _, _, sb = self.connection_fwd("encoder.c_layer_pv_v.%d" % count, Y[V2], sgV, X[P2], sgP,
+                                           False, Yn[V2], Xn[P2])
+            _, _, sc = self.connection_fwd("encoder.c_layer_pv_t.%d" % count, X[P3], sgP, X[T3], sgT,
+                                           True, Xn[P3], Xn[T3])
+            stages.append(("c", sa, sb, sc))
+            X, Y = Xn, Yn
+            s1, s2 = e1, e2
+        for i in range(s1, c.v_num_hidden_layers):
+            Y, sv = self.layer_fwd("encoder.v_layer.%d" % i, Y, segs_y, True)
+            stages.append(("v", sv))
+        for i in range(s2, c.num_hidden_layers):
+            X, sv = self.layer_fwd("encoder.layer.%d" % i, X, segs_x, False)
+            stages.append(("t", sv))
+        # fusion: title / PV sequences land in one stacked buffer S for the shared MLM head
+        S = self.empty(Mt + Mp, H)
+        seqV = self.empty(Mv, Hv)
+        sv_fv = self.fuse_fwd("v", e_v, Y[V1], Y[V2], noise.get("v"), seqV)
+        sv_ft = self.fuse_fwd("t", e_t, X[T1], X[T3], noise.get("t"), S[:Mt])
+        sv_fp = self.fuse_fwd("pv", e_pv, X[P2], X[P3], noise.get("pv"), S[Mt:])
+        pool_t = ops.mean_pool_fwd(S[:Mt], B, Lt, f32)
+        pool_pv = ops.mean_pool_fwd(S[Mt:], B, Lpv, f32)
+        pool_vr = ops.mean_pool_fwd(seqV, B, Lv1, self.adt)
+        pool_v = ops.gemm(pool_vr, self.W("map_bi_to_individual.weight"), "nt",
+                          bias=self.W("map_bi_to_individual.bias"), out_dtype=f32)
+        c_init = ops.lincomb3(pool_v, pool_t, pool_pv, 1.0 / 3, 1.0 / 3, 1.0 / 3, out_dtype=f32)
+        c_final, loss_lpm, sv_s = self.struct_fwd(c_init, S[Mt:], plan)
+        loss_itm = ops.itm_loss(pool_t, pool_pv, pool_v, self.W("cls.seq_relationship.weight"),
+                                self.W("cls.seq_relationship.bias"), batch["next_sentence_label"],
+                                batch["next_sentence_label_pv_v"], batch["next_sentence_label_pv_t"],
+                                drop=self.site(0.1), rng=self.rng)
+        w_t, w_v, w_pv, w_lpm = [float(x) for x in loss_weights]
+        V, Tv = c.vocab_size, c.v_target_size
+        logits, sv_h = self.head_fwd("cls.predictions", S, "embeddings.word_embeddings.weight",
+                                     "cls.predictions.bias", self.adt, V)
+        lab_t, lab_pv = batch["masked_lm_labels"].reshape(-1), batch["masked_lm_labels_pv"].reshape(-1)
+        loss_t = ops.xent_fwd_bwd(logits[:Mt], lab_t, ops.count_valid(lab_t, -1), V,
+                                  dlogits=logits[:Mt], grad_scale=w_t)
+        loss_pv = ops.xent_fwd_bwd(logits[Mt:], lab_pv, ops.count_valid(lab_pv, -1), V,
+                                   dlogits=logits[Mt:], grad_scale=w_pv)
+        logits_v, sv_hv = self.head_fwd("cls.imagePredictions", seqV,
+                                        "cls.imagePredictions.decoder.weight",
+                                        "cls.imagePredictions.decoder.bias", f32, Tv)
+        dlv = self.zeros(Mv, logits_v.shape[1])
+        il = batch["image_label"].reshape(-1)
+        loss_v = ops.kl_fwd_bwd(logits_v, batch["image_target"].reshape(-1, Tv), il,
+                                ops.count_eq(il, 1), Tv, Lv1, dlogits=dlv, grad_scale=w_v)
+        self.saved = dict(dims=(B, Lt, Lpv, Lv1, Mt, Mp, Mv), stages=stages, emb=(sv_et, sv_epv, sv_ev),
+                          fuse=(sv_fv, sv_ft, sv_fp), struct=sv_s, w_lpm=w_lpm, pool_vr=pool_vr,
+                          head=(logits, sv_h), head_v=(dlv, sv_hv))
+        return dict(loss_t=loss_t, loss_v=loss_v, loss_pv=loss_pv, loss_itm=loss_itm,
+                    loss_lpm=loss_lpm, c_initial=c_init, c_final=c_final)
+
+    def backward(self):
+        """Gradient of w_t*loss_t + w_v*loss_v + w_pv*loss_pv + w_lpm*loss_lpm, accumulated into
+        the fp32 gradient arena (which the caller zeroes once per optimizer step)."""
+        c, ops, f32 = self.cfg, self.ops, torch.float32
+        sv = self.saved
+        B, Lt, Lpv, Lv1, Mt, Mp, Mv = sv["dims"]
+        H, Hv = c.hidden_size, c.v_hidden_size
+        T1, T3 = slice(0, Mt), slice(Mt, 2 * Mt)
+        P2, P3 = slice(2 * Mt, 2 * Mt + Mp), slice(2 * Mt + Mp, 2 * Mt + 2 * Mp)
+        V1, V2 = slice(0, Mv), slice(Mv, 2 * Mv)
+        dS = self.zeros(Mt + Mp, H)
+        dseqV = self.zeros(Mv, Hv)
+        self.head_bwd(sv["head"][0], sv["head"][1], dS)
+        self.head_bwd(sv["head_v"][0], sv["head_v"][1], dseqV)
+        dc_init = self.zeros(B, H, f32)
+        self.struct_bwd(sv["struct"], sv["w_lpm"], dc_init, dS[Mt:])
+        ops.scale_(dc_init, 1.0 / 3)                       # c_initial = (v + t + pv) / 3
+        ops.mean_pool_bwd(dc_init, dS[:Mt], B, Lt)
+        ops.mean_pool_bwd(dc_init, dS[Mt:], B, Lpv)
+        ops.colsum(dc_init, self.G("map_bi_to_individual.bias"))
+        dpa = ops.cast(dc_init, self.adt)
+        self.wgrad(dpa, sv["pool_vr"], "map_bi_to_individual.weight")
+        dpr = self.dgrad(dpa, "map_bi_to_individual.weight", out_dtype=f32)
+        ops.mean_pool_bwd(dpr, dseqV, B, Lv1)
+        dX = self.zeros(2 * Mt + 2 * Mp, H)
+        dY = self.zeros(2 * Mv, Hv)
+        d_et, d_epv, d_ev = self.zeros(Mt, H), self.zeros(Mp, H), self.zeros(Mv, Hv)
+        sv_fv, sv_ft, sv_fp = sv["fuse"]
+        self.fuse_bwd(dseqV, sv_fv, d_ev, dY[V1], dY[V2])
+        self.fuse_bwd(dS[:Mt], sv_ft, d_et, dX[T1], dX[T3])
+        self.fuse_bwd(dS[Mt:], sv_fp, d_epv, dX[P2], dX[P3])
+        for st in reversed(sv["stages"]):
+            if st[0] == "t":
+                dX = self.layer_bwd(dX, st[1])
+            elif st[0] == "v":
+                dY = self.layer_bwd(dY, st[1])
+            else:
+                dXn, dYn = torch.empty_like(dX), torch.empty_like(dY)
+                self.connection_bwd(dY[V1], dX[T1], st[1], dYn[V1], dXn[T1])
+                self.connection_bwd(dY[V2], dX[P2], st[2], dYn[V2], dXn[P2])
+                self.connection_bwd(dX[P3], dX[T3], st[3], dXn[P3], dXn[T3])
+                dX, dY = dXn, dYn
+        for sl in (T1, T3):
+            ops.axpy(dX[sl], d_et, 1.0)
+        for sl in (P2, P3):
+            ops.axpy(dX[sl], d_epv, 1.0)
+        for sl in (V1, V2):
+            ops.axpy(dY[sl], d_ev, 1.0)
+        sv_et, sv_epv, sv_ev = sv["emb"]
+        self.text_embed_bwd(d_et, sv_et)
+        self.text_embed_bwd(d_epv, sv_epv)
+        self.image_embed_bwd(d_ev, sv_ev)
+        self.saved = None

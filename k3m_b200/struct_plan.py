@@ -1,0 +1,73 @@
+"""Host-side index plan for the structure aggregator and the link-prediction (LPM) loss.
+
+The reference walks `index_p` / `index_v` in Python, one (item, PV) pair at a time, syncing the
+device for every `index_p[i, j, 0] == 0` test (`vilbert_k3m/vilbert_k3m.py:2437-2446`), and
+draws LPM negatives with `random.sample` (`:2480`, `:2492`).  Both depend only on the integer
+index tensors, which arrive from the host loader — so the whole plan is built on the host,
+once per batch, *before* any kernel runs, and the device side becomes four batched kernels.
+
+The `random.sample` call sequence (order, population, k) is reproduced exactly, so seeding
+Python's `random` the same way yields the same negatives as the reference.
+"""
+import random
+
+import numpy as np
+
+
+def build_struct_plan(index_p, index_v, L_pv, num_negative_pv, rng=random):
+    """index_p / index_v: integer arrays [B, max_num_pv, 2] (numpy or nested lists).
+
+    Returns a dict of int32 numpy arrays:
+      pair_item [P]      item of each valid (item, PV) pair, in reference loop order
+      pair_rows [P, 4]   rows of the stacked PV sequence [B*L_pv, H]: (p0, p1, v0, v1)
+      seg       [B, 2]   (start, end) pair range whose `t` rows item i attends over
+      terms     [T, 4]   LPM terms (item, pair, negative item, negative value pair)
+    """
+    ip = np.asarray(index_p).astype(np.int64)
+    iv = np.asarray(index_v).astype(np.int64)
+    B, J = ip.shape[0], ip.shape[1]
+    pair_item, pair_rows, seg, first = [], [], [], []
+    last = None
+    for i in range(B):
+        start = len(pair_item)
+        for j in range(J):
+            if ip[i, j, 0] == 0:          # loop stops at the first [0, *] row (`:2441`)
+                break
+            base = i * L_pv
+            pair_item.append(i)
+            pair_rows.append((base + ip[i, j, 0], base + ip[i, j, 1],
+                              base + iv[i, j, 0], base + iv[i, j, 1]))
+        end = len(pair_item)
+        first.append(start)
+        if end > start:
+            last = (start, end)
+        elif last is None:
+            # reference: NameError -> bare except -> t = c_initial[i] (`:2452-2456`); only for
+            # leading items without PVs.  Not representable as a pair range.
+            raise ValueError("item %d has no property/value pair and no earlier item has one; "
+                             "the reference's fallback for this case is not supported" % i)
+        # an item without PVs silently reuses the previous item's `t` (stale variable)
+        seg.append(last)
+    counts = [0] * B
+    for i in pair_item:
+        counts[i] += 1
+    terms = []
+    n_ent = num_negative_pv // 2
+    n_val = num_negative_pv - n_ent
+    for i in range(B):
+        for j in range(counts[i]):
+            pj = first[i] + j
+            cand = [k for k in range(B) if k != i]
+            if cand:
+                for k in rng.sample(cand, min(len(cand), n_ent)):
+                    terms.append((i, pj, k, pj))
+            cand = [k for k in range(counts[i]) if k != j]
+            if cand:
+                for k in rng.sample(cand, min(len(cand), n_val)):
+                    terms.append((i, pj, i, first[i] + k))
+    return dict(
+        pair_item=np.asarray(pair_item, dtype=np.int32).reshape(-1),
+        pair_rows=np.asarray(pair_rows, dtype=np.int32).reshape(-1, 4),
+        seg=np.asarray(seg, dtype=np.int32).reshape(-1, 2),
+        terms=np.asarray(terms, dtype=np.int32).reshape(-1, 4),
+    )

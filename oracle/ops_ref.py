@@ -314,6 +314,21 @@ class RefOps(object):
         """y += alpha * x."""
         y.add_((alpha * x.float()).to(y.dtype))
 
+    def cast(self, x, dtype):
+        return x.to(dtype)
+
+    def scale_(self, x, alpha):
+        x.mul_(alpha)
+
+    def act_bwd(self, dy, pre, act):
+        """dy * act'(pre) (ACT_DGELU)."""
+        assert act == ACT_DGELU
+        return (dy.float() * _dgelu(pre.float())).to(self.adt)
+
+    def mask_additive(self, mask):
+        """(1 - mask) * -10000 as fp32 [B, L] (`vilbert_k3m.py:2561`)."""
+        return (1.0 - mask.float()) * -10000.0
+
     # ---- pooling ---------------------------------------------------------------------------
     def mean_pool_fwd(self, seq, B, L, out_dtype=torch.float32):
         """[B*L, H] -> [B, H]: mean over tokens 1..L-1 (padding included, `:2405-2409`)."""
@@ -410,7 +425,7 @@ class RefOps(object):
     def count_eq(self, labels, value):
         return (labels.reshape(-1) == value).sum().float().reshape(1)
 
-    def xent_fwd_bwd(self, logits, labels, count, n_cols, dlogits=None):
+    def xent_fwd_bwd(self, logits, labels, count, n_cols, dlogits=None, grad_scale=1.0):
         """Mean cross-entropy with ignore_index=-1 over rows of logits[:, :n_cols];
         dlogits = (softmax - onehot) / count on labelled rows, 0 elsewhere.  -> loss [1]."""
         lab = labels.reshape(-1)
@@ -423,12 +438,13 @@ class RefOps(object):
         if dlogits is not None:
             g = torch.softmax(lg, 1)
             g.scatter_add_(1, safe[:, None], -torch.ones_like(g[:, :1]))
-            g = g * (valid[:, None] / count)
-            dlogits.zero_()
+            g = g * (valid[:, None] * (grad_scale / count))
+            if dlogits.shape[1] > n_cols:
+                dlogits[:, n_cols:] = 0
             dlogits[:, :n_cols] = g.to(dlogits.dtype)
         return loss.reshape(1)
 
-    def kl_fwd_bwd(self, logits, target, image_label, count, n_cols, Lv1, dlogits=None):
+    def kl_fwd_bwd(self, logits, target, image_label, count, n_cols, Lv1, dlogits=None, grad_scale=1.0):
         """MRM (`:2754-2760`): logits [B*Lv1, ld] fp32 (row 0 of each item = global region, no
         target); target [B*(Lv1-1), n_cols]; loss = sum_{label==1} sum_c xlogy(t,t) - t*logp
         / count."""
@@ -440,16 +456,18 @@ class RefOps(object):
         kl = torch.xlogy(tg, tg) - tg * logp
         loss = (kl * w).sum() / count
         if dlogits is not None:
-            g = (torch.softmax(lg, 2) * tg.sum(2, keepdim=True) - tg) * w / count
+            g = (torch.softmax(lg, 2) * tg.sum(2, keepdim=True) - tg) * w * (grad_scale / count)
             dlogits.zero_()
             dlogits.reshape(B, Lv1, -1)[:, 1:, :n_cols] = g.to(dlogits.dtype)
         return loss.reshape(1)
 
-    def itm_loss(self, pool_t, pool_pv, pool_v, w, b, labels, drop=None, rng=None):
-        """ITM head value (`:1881-1887`, `:2828-2832`): CE(Linear(dropout(sum of pooled)))."""
+    def itm_loss(self, pool_t, pool_pv, pool_v, w, b, l1, l2, l3, drop=None, rng=None):
+        """ITM head value (`:1881-1887`, `:2828-2832`): CE(Linear(dropout(sum of pooled))) with
+        label 1 - ((l1 + l2 + l3) == 0)."""
         x = _apply_drop(pool_t.float() + pool_pv.float() + pool_v.float(), drop, rng)
         lg = x @ w.float().t() + b.float()
-        return torch.nn.functional.cross_entropy(lg, labels.long(), ignore_index=-1).reshape(1)
+        labels = 1 - ((l1 + l2 + l3) == 0).long()
+        return torch.nn.functional.cross_entropy(lg, labels, ignore_index=-1).reshape(1)
 
     # ---- optimizer -------------------------------------------------------------------------
     def adamw(self, p32, g32, m, v, p_act, hyper, grad_scale=1.0, zero_grad=True):
