@@ -1,0 +1,141 @@
+/* libk3m_sm100a.so — C ABI of the B200-native K3M pretraining-step kernels.
+ *
+ * The reference (sunzeyeah/K3M) has no native code on this path: its "interface" is the Python
+ * class API of vilbert_k3m/vilbert_k3m.py, and every arithmetic op is an ATen library call.  Each
+ * entry point below therefore names the reference Python lines it replaces.  Conventions:
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer owned by the caller;
+ *   - "act" tensors are bf16 (row-major, explicit row stride `ld*` in elements); statistics,
+ *     losses and gradients of parameters are fp32;
+ *   - asynchronous on `stream` (a cudaStream_t), no allocation, no host synchronisation,
+ *     CUDA-graph capturable; re-entrant across streams;
+ *   - return 0 on success, <0 on error (K3M_ERR_*); k3m_last_error_string() describes the last
+ *     error of the calling thread.  No exceptions cross the ABI.
+ *   - dropout: `rng` -> two device uint64 {seed, step}; `site` numbers the dropout application
+ *     inside the step; p == 0 or rng == NULL disables it.  Masks are regenerated in backward
+ *     from the same (seed, step, site, element index) — Philox4x32-10, 16 bits per element.
+ */
+#ifndef K3M_H_
+#define K3M_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define K3M_OK 0
+#define K3M_ERR_ARG -1
+#define K3M_ERR_CUDA -2
+#define K3M_ERR_UNSUPPORTED -3
+
+/* epilogue activations of k3m_gemm_bf16 */
+#define K3M_ACT_NONE 0
+#define K3M_ACT_GELU 1    /* aux_out (optional) receives the pre-activation; out = gelu(v)   */
+#define K3M_ACT_DGELU 2   /* out = v * gelu'(aux_in)                                         */
+#define K3M_ACT_SIGMOID 3
+#define K3M_ACT_TANH 4
+#define K3M_ACT_DTANH 5   /* out = v * (1 - aux_in^2)                                        */
+
+/* GEMM operand layouts */
+#define K3M_GEMM_NT 0 /* A[M,K] , B[N,K]  : Y = X W^T    (nn.Linear forward)                   */
+#define K3M_GEMM_NN 1 /* A[M,K] , B[K,N]  : dX = dY W    (input gradient)                      */
+#define K3M_GEMM_TN 2 /* A[K,M] , B[K,N]  : dW = dY^T X  (weight gradient)                     */
+
+int k3m_get_version(void);
+const char* k3m_last_error_string(void);
+
+/* tcgen05/TMEM/TMA GEMM with fused epilogue.  Replaces every nn.Linear on the path
+ * (vilbert_k3m.py:440-446, 485-489, 515-518, 528-532, 764-783, 986-996, 1795-1799, 1836-1839,
+ * 1921-1924, 2153-2161, 2347-2360) together with the elementwise ops the reference runs after
+ * it (gelu :125, nn.Dropout, residual add) and their autograd backward.
+ *   v = acc (+ bias[n]); activation; dropout(p); v += addend[m,n];
+ *   out = accumulate ? out + v (fp32 atomics, split-K) : v.                                     */
+int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int layout, int M, int N, int K,
+                  void* out, int ldc, int out_f32, int accumulate, const void* bias, int act,
+                  const void* aux_in, int ld_aux_in, void* aux_out, int ld_aux_out,
+                  const void* addend, int ld_add, int addend_f32, const void* rng,
+                  unsigned int drop_site, float drop_p, void* stream);
+
+/* BertLayerNorm (vilbert_k3m.py:319-332): TF style, biased variance, eps inside the sqrt.      */
+int k3m_ln_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
+               int M, int H, float eps, const void* rng, unsigned int site, float drop_p, void* stream);
+/* backward of LN (+ the dropouts around it); dgamma/dbeta/dbias are accumulated (+=).           */
+int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+               void* dx, void* dxm, float* dgamma, float* dbeta, float* dbias, int M, int H,
+               const void* rng, unsigned int site_out, float p_out, unsigned int site_in, float p_in,
+               void* stream);
+int k3m_colsum(const void* x, int ld, int x_f32, float* out, int M, int N, void* stream);
+int k3m_cast(const void* x, int x_f32, void* y, int y_f32, long long n, void* stream);
+int k3m_lincomb3(const void* a, int lda, const void* b, int ldb, const void* c, int ldc, float wa,
+                 float wb, float wc, int in_f32, void* out, int ldo, int out_f32, int rows, int cols,
+                 void* stream);
+int k3m_axpy(const void* x, int ldx, int x_f32, void* y, int ldy, int y_f32, float alpha, int rows,
+             int cols, void* stream);
+int k3m_scale(float* x, float alpha, long long n, void* stream);
+int k3m_dgelu_mul(const void* dy, const void* pre, void* dx, long long n, void* stream);
+/* (1 - mask) * -10000 (vilbert_k3m.py:2561, 2570, 2580)                                          */
+int k3m_mask_additive(const long long* mask, float* out, int n, void* stream);
+
+/* BertSelfAttention.forward (vilbert_k3m.py:449-464) and both directions of
+ * BertBiAttention.forward (:786-824): softmax(q k^T / sqrt(d) + mask) -> dropout -> @ v.         */
+int k3m_attn_fwd(const void* q, int ldq, int q_off, const void* kv, int ldkv, int k_off, int v_off,
+                 const float* mask, int B, int H, int Lq, int Lk, int d, void* ctx, int ldo, float* lse,
+                 const void* rng, unsigned int site, float drop_p, void* stream);
+int k3m_attn_bwd(const void* dctx, int ldo, const void* q, int ldq, int q_off, const void* kv, int ldkv,
+                 int k_off, int v_off, const float* mask, const float* lse, void* dq, int lddq, void* dkv,
+                 int lddkv, int B, int H, int Lq, int Lk, int d, const void* rng, unsigned int site,
+                 float drop_p, void* stream);
+
+/* BertEmbeddings.forward gathers (vilbert_k3m.py:361-376); backward skips padding_idx 0 (:343).   */
+int k3m_embed_fwd(const long long* ids, const long long* type_ids, const void* word, const void* pos,
+                  const void* typ, void* out, int M, int L, int H, void* stream);
+int k3m_embed_bwd(const void* dx, const long long* ids, const long long* type_ids, float* dword,
+                  float* dpos, float* dtyp, int M, int L, int H, void* stream);
+/* image_location_embeddings, a K=5 projection (vilbert_k3m.py:2155)                              */
+int k3m_loc_embed_fwd(const float* loc, const void* w, const void* b, void* out, int M, int N, void* stream);
+int k3m_loc_embed_bwd(const void* dy, const float* loc, float* dw, float* db, int M, int N, void* stream);
+
+/* pre_sampling_sequence (vilbert_k3m.py:2331-2374): relu + concat, hard Gumbel pick, backward.    */
+int k3m_relu_cat3(const void* a, int lda, const void* b, int ldb, const void* c, int ldc, void* out,
+                  int M, int H, void* stream);
+int k3m_fuse_select_fwd(const void* cat, const float* gates, const float* noise, const void* rng,
+                        unsigned int site, void* out, int ldo, int M, int H, void* stream);
+int k3m_fuse_select_bwd(const void* dout, int ldd, const void* cat, const float* gates, const float* noise,
+                        const void* rng, unsigned int site, void* dgates, void* dcat, int M, int H,
+                        void* stream);
+int k3m_relu_bwd_split3(const void* dcat, const void* cat, void* da, int lda, void* db, int ldb, void* dc,
+                        int ldc, int M, int H, void* stream);
+/* token-mean pooling over positions 1.. (vilbert_k3m.py:2405-2409)                               */
+int k3m_mean_pool_fwd(const void* seq, int ld, void* out, int out_f32, int B, int L, int H, void* stream);
+int k3m_mean_pool_bwd(const float* dpool, void* dseq, int ld, int B, int L, int H, void* stream);
+
+/* structure_aggregator (vilbert_k3m.py:2413-2467) and the LPM loss (:2469-2502) over the host plan */
+int k3m_pair_gather_fwd(const float* c_init, const void* seq, int lds, const int* pair_item,
+                        const int* pair_rows, void* X, float* PV, int P, int H, void* stream);
+int k3m_pair_gather_bwd(const float* dX, const float* dPV, const int* pair_item, const int* pair_rows,
+                        float* dc_init, float* dseq32, int P, int H, void* stream);
+int k3m_struct_attn_fwd(const float* t, const void* w2, const void* b2, const int* seg, float* s_out,
+                        float* att, int B, int maxn, int H, void* stream);
+int k3m_struct_attn_bwd(const float* ds, const float* t, const float* att, const void* w2, const int* seg,
+                        float* dt, float* dw2, float* db2, int B, int maxn, int H, void* stream);
+int k3m_lpm_fwd_bwd(const float* c_final, const float* PV, const int* terms, int T, int H, float margin,
+                    float* loss, float* dc_final, float* dPV, void* stream);
+
+/* loss block (vilbert_k3m.py:2739-2832)                                                          */
+int k3m_count_labels(const long long* labels, int n, long long value, int equal, float* out, void* stream);
+int k3m_xent_fwd_bwd(void* logits, int ld, const long long* labels, const float* count, int M, int V,
+                     float grad_scale, float* loss, int write_grad, void* stream);
+int k3m_kl_fwd_bwd(const float* logits, int ld, const float* target, const long long* image_label,
+                   const float* count, int B, int Lv1, int T, float grad_scale, float* loss, void* dlogits,
+                   void* stream);
+int k3m_itm_loss(const float* pool_t, const float* pool_pv, const float* pool_v, const void* w, const void* b,
+                 const long long* l1, const long long* l2, const long long* l3, int B, int H, const void* rng,
+                 unsigned int site, float drop_p, float* loss, void* stream);
+
+/* torch.optim.AdamW step (pretrain.py:919-924) over a flat range; hyper = device fp32[8]
+ * {lr, beta1, beta2, eps, weight_decay, step, grad_scale, -}.                                     */
+int k3m_adamw(float* p32, float* g32, float* m, float* v, void* p16, const float* hyper, long long n,
+              int zero_grad, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* K3M_H_ */

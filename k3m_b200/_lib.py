@@ -1,0 +1,36 @@
+"""ctypes binding of libk3m_sm100a.so (the C ABI declared in include/k3m.h).
+
+There is no CPU or library fallback: if the shared library is missing or a symbol fails to
+resolve, importing the op table raises."""
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libk3m_sm100a.so")
+
+_lib = None
+
+
+class K3MError(RuntimeError):
+    pass
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise K3MError(
+            "k3m_b200: %s is missing — build it with `python -m k3m_b200.build` "
+            "(nvcc, sm_100a). There is no fallback path." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.k3m_last_error_string.restype = ctypes.c_char_p
+    lib.k3m_get_version.restype = ctypes.c_int
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().k3m_last_error_string().decode("utf-8", "replace")
+        raise K3MError("%s failed (%d): %s" % (what, rc, msg))

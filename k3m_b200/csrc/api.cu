@@ -1,0 +1,27 @@
+// Error plumbing shared by every entry point of libk3m_sm100a.so (see include/k3m.h).
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void k3m_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int k3m_check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    k3m_set_error("%s: %s", what, cudaGetErrorString(e));
+    return K3M_ERR_CUDA;
+  }
+  return K3M_OK;
+}
+
+extern "C" const char* k3m_last_error_string(void) { return g_err; }
+extern "C" int k3m_get_version(void) { return 1; }

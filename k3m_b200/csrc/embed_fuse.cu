@@ -1,0 +1,277 @@
+// Embedding gathers, the 5-d box projection, modal fusion (hard Gumbel selection) and pooling.
+// All HBM-bound or tiny; index gathers are exact integer arithmetic.
+#include "common.cuh"
+
+namespace {
+
+// out[r] = word[ids[r]] + pos[r % L] + typ[type_ids[r]]     (BertEmbeddings, vilbert_k3m.py:361-376)
+__global__ void __launch_bounds__(128) embed_fwd_kernel(const long long* __restrict__ ids, const long long* __restrict__ tids,
+                                                        const bf16* __restrict__ word, const bf16* __restrict__ pos,
+                                                        const bf16* __restrict__ typ, bf16* __restrict__ out, int M, int L, int H) {
+  const int row = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const bf16* w = word + (size_t)ids[row] * H;
+  const bf16* p = pos + (size_t)(row % L) * H;
+  const bf16* t = typ + (size_t)tids[row] * H;
+  for (int c = lane * 8; c < H; c += 256) {
+    float a[8], b[8], e[8];
+    ld8(w + c, a); ld8(p + c, b); ld8(t + c, e);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] += b[j] + e[j];
+    st8(out + (size_t)row * H + c, a);
+  }
+}
+
+// scatter-add of dx rows into the fp32 embedding gradients; word row 0 (padding_idx) is skipped
+__global__ void __launch_bounds__(128) embed_bwd_kernel(const bf16* __restrict__ dx, const long long* __restrict__ ids,
+                                                        const long long* __restrict__ tids, float* __restrict__ dword,
+                                                        float* __restrict__ dpos, float* __restrict__ dtyp, int M, int L, int H) {
+  const int row = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const long long id = ids[row];
+  float* w = dword + (size_t)id * H;
+  float* p = dpos + (size_t)(row % L) * H;
+  float* t = dtyp + (size_t)tids[row] * H;
+  for (int c = lane; c < H; c += 32) {
+    const float g = __bfloat162float(dx[(size_t)row * H + c]);
+    if (id != 0) atomicAdd(w + c, g);
+    atomicAdd(p + c, g);
+    atomicAdd(t + c, g);
+  }
+}
+
+// out[m, n] = sum_k loc[m, k] w[n, k] + b[n],  k < 5
+__global__ void loc_fwd_kernel(const float* __restrict__ loc, const bf16* __restrict__ w, const bf16* __restrict__ b,
+                               bf16* __restrict__ out, int M, int N) {
+  const size_t n = (size_t)M * N;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int m = (int)(i / N), c = (int)(i % N);
+    float acc = ld_f(b + c);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) acc = fmaf(loc[(size_t)m * 5 + k], ld_f(w + (size_t)c * 5 + k), acc);
+    out[i] = __float2bfloat16(acc);
+  }
+}
+
+// dw[n, k] += sum_m dy[m, n] loc[m, k] ; db[n] += sum_m dy[m, n]       one thread per column n
+__global__ void __launch_bounds__(128) loc_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ loc,
+                                                      float* __restrict__ dw, float* __restrict__ db, int M, int N, int rows_per) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= N) return;
+  const int r0 = blockIdx.y * rows_per;
+  int r1 = r0 + rows_per;
+  if (r1 > M) r1 = M;
+  float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int m = r0; m < r1; ++m) {
+    const float g = __bfloat162float(dy[(size_t)m * N + c]);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) acc[k] = fmaf(g, loc[(size_t)m * 5 + k], acc[k]);
+    acc[5] += g;
+  }
+#pragma unroll
+  for (int k = 0; k < 5; ++k) atomicAdd(dw + (size_t)c * 5 + k, acc[k]);
+  atomicAdd(db + c, acc[5]);
+}
+
+// cat[m] = [relu(a[m]) | relu(b[m]) | relu(c[m])]
+__global__ void relu_cat3_kernel(const bf16* a, int lda, const bf16* b, int ldb, const bf16* c, int ldc, bf16* out, int M, int H) {
+  const int hv = H / 8;
+  const size_t n = (size_t)M * 3 * hv;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int m = (int)(i / (3 * hv)), r = (int)(i % (3 * hv)), k = r / hv, col = (r % hv) * 8;
+    const bf16* src = k == 0 ? a + (size_t)m * lda : (k == 1 ? b + (size_t)m * ldb : c + (size_t)m * ldc);
+    float v[8];
+    ld8(src + col, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+    st8(out + (size_t)m * 3 * H + k * H + col, v);
+  }
+}
+
+// Gumbel(0,1) draw for element lin of a noise site: 4 draws per Philox call
+__device__ __forceinline__ float gumbel_at(const unsigned long long* rng, unsigned int site, unsigned long long lin) {
+  uint32_t w[4];
+  rng_words(rng, site, lin >> 2, w);
+  const float u = ((float)(w[lin & 3] >> 8) + 0.5f) * (1.0f / 16777216.0f);
+  return -logf(-logf(u));
+}
+
+// y_k = softmax_k(sigmoid(gate_k) + g_k), hard pick = first arg-max  (pre_sampling_sequence,
+// vilbert_k3m.py:2331-2374; F.gumbel_softmax(hard=True, tau=1))
+__device__ __forceinline__ void ysoft3(const float* gates, const float* noise, const unsigned long long* rng,
+                                       unsigned int site, int m, int h, int H, float ak[3], float y[3], int* pick) {
+  float z[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    ak[k] = sigmoid_f(gates[(size_t)m * 3 * H + k * H + h]);
+    const size_t lin = ((size_t)m * 3 + k) * H + h;
+    const float g = noise ? noise[lin] : gumbel_at(rng, site, lin);
+    z[k] = ak[k] + g;
+  }
+  const float mx = fmaxf(z[0], fmaxf(z[1], z[2]));
+  float e[3], s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { e[k] = __expf(z[k] - mx); s += e[k]; }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) y[k] = e[k] / s;
+  int p = 0;
+  if (y[1] > y[p]) p = 1;
+  if (y[2] > y[p]) p = 2;
+  *pick = p;
+}
+
+__global__ void fuse_fwd_kernel(const bf16* __restrict__ cat, const float* __restrict__ gates, const float* __restrict__ noise,
+                                const unsigned long long* rng, unsigned int site, bf16* __restrict__ out, int ldo, int M, int H) {
+  const size_t n = (size_t)M * H;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int m = (int)(i / H), h = (int)(i % H);
+    float ak[3], y[3];
+    int pick;
+    ysoft3(gates, noise, rng, site, m, h, H, ak, y, &pick);
+    out[(size_t)m * ldo + h] = cat[(size_t)m * 3 * H + pick * H + h];
+  }
+}
+
+// straight-through backward: dgates[m,k,h] and dcat_direct[m,k,h] = dout * onehot
+__global__ void fuse_bwd_kernel(const bf16* __restrict__ dout, int ldd, const bf16* __restrict__ cat,
+                                const float* __restrict__ gates, const float* __restrict__ noise,
+                                const unsigned long long* rng, unsigned int site, bf16* __restrict__ dgates,
+                                bf16* __restrict__ dcat, int M, int H) {
+  const size_t n = (size_t)M * H;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int m = (int)(i / H), h = (int)(i % H);
+    float ak[3], y[3];
+    int pick;
+    ysoft3(gates, noise, rng, site, m, h, H, ak, y, &pick);
+    const float go = __bfloat162float(dout[(size_t)m * ldd + h]);
+    float dy[3], dot = 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      dy[k] = go * __bfloat162float(cat[(size_t)m * 3 * H + k * H + h]);
+      dot += y[k] * dy[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const size_t o = (size_t)m * 3 * H + k * H + h;
+      dgates[o] = __float2bfloat16(y[k] * (dy[k] - dot) * ak[k] * (1.0f - ak[k]));
+      dcat[o] = __float2bfloat16(k == pick ? go : 0.f);
+    }
+  }
+}
+
+// d{a,b,c}[m,h] += dcat[m, k*H + h] * (cat[m, k*H + h] > 0)
+__global__ void relu_split3_kernel(const bf16* __restrict__ dcat, const bf16* __restrict__ cat, bf16* da, int lda, bf16* db,
+                                   int ldb, bf16* dc, int ldc, int M, int H) {
+  const size_t n = (size_t)M * 3 * H;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int m = (int)(i / (3 * H)), r = (int)(i % (3 * H)), k = r / H, h = r % H;
+    if (__bfloat162float(cat[i]) > 0.f) {
+      bf16* dst = k == 0 ? da + (size_t)m * lda + h : (k == 1 ? db + (size_t)m * ldb + h : dc + (size_t)m * ldc + h);
+      *dst = __float2bfloat16(__bfloat162float(*dst) + __bfloat162float(dcat[i]));
+    }
+  }
+}
+
+// pooled[b, h] = mean_{i=1..L-1} seq[b*L + i, h]       (vilbert_k3m.py:2405-2409)
+template <typename TO>
+__global__ void pool_fwd_kernel(const bf16* __restrict__ seq, int ld, TO* __restrict__ out, int B, int L, int H) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * H) return;
+  const int b = i / H, h = i % H;
+  float acc = 0.f;
+  for (int t = 1; t < L; ++t) acc += __bfloat162float(seq[(size_t)(b * L + t) * ld + h]);
+  st_f(out + i, acc / (float)(L - 1));
+}
+
+// dseq[b*L + i, h] += dpool[b, h] / (L-1), i >= 1
+__global__ void pool_bwd_kernel(const float* __restrict__ dpool, bf16* __restrict__ dseq, int ld, int B, int L, int H) {
+  const size_t n = (size_t)B * L * H;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int h = (int)(i % H);
+    const int r = (int)(i / H), b = r / L, t = r % L;
+    if (t == 0) continue;
+    bf16* p = dseq + (size_t)r * ld + h;
+    *p = __float2bfloat16(__bfloat162float(*p) + dpool[(size_t)b * H + h] / (float)(L - 1));
+  }
+}
+
+inline int grid_for(size_t n, int block) {
+  size_t g = (n + block - 1) / block;
+  if (g > 148 * 16) g = 148 * 16;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+}  // namespace
+
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" int k3m_embed_fwd(const long long* ids, const long long* type_ids, const void* word, const void* pos,
+                             const void* typ, void* out, int M, int L, int H, void* stream) {
+  K3M_REQUIRE(M > 0 && H % 8 == 0, "embed_fwd: H must be a multiple of 8");
+  embed_fwd_kernel<<<(M + 3) / 4, 128, 0, ST(stream)>>>(ids, type_ids, (const bf16*)word, (const bf16*)pos,
+                                                        (const bf16*)typ, (bf16*)out, M, L, H);
+  return k3m_check_launch("k3m_embed_fwd");
+}
+
+extern "C" int k3m_embed_bwd(const void* dx, const long long* ids, const long long* type_ids, float* dword, float* dpos,
+                             float* dtyp, int M, int L, int H, void* stream) {
+  embed_bwd_kernel<<<(M + 3) / 4, 128, 0, ST(stream)>>>((const bf16*)dx, ids, type_ids, dword, dpos, dtyp, M, L, H);
+  return k3m_check_launch("k3m_embed_bwd");
+}
+
+extern "C" int k3m_loc_embed_fwd(const float* loc, const void* w, const void* b, void* out, int M, int N, void* stream) {
+  loc_fwd_kernel<<<grid_for((size_t)M * N, 256), 256, 0, ST(stream)>>>(loc, (const bf16*)w, (const bf16*)b, (bf16*)out, M, N);
+  return k3m_check_launch("k3m_loc_embed_fwd");
+}
+
+extern "C" int k3m_loc_embed_bwd(const void* dy, const float* loc, float* dw, float* db, int M, int N, void* stream) {
+  int gy = (M + 127) / 128;
+  if (gy > 64) gy = 64;
+  loc_bwd_kernel<<<dim3((N + 127) / 128, gy), 128, 0, ST(stream)>>>((const bf16*)dy, loc, dw, db, M, N, (M + gy - 1) / gy);
+  return k3m_check_launch("k3m_loc_embed_bwd");
+}
+
+extern "C" int k3m_relu_cat3(const void* a, int lda, const void* b, int ldb, const void* c, int ldc, void* out, int M,
+                             int H, void* stream) {
+  K3M_REQUIRE(H % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "relu_cat3: widths must be multiples of 8");
+  relu_cat3_kernel<<<grid_for((size_t)M * 3 * H / 8, 256), 256, 0, ST(stream)>>>((const bf16*)a, lda, (const bf16*)b, ldb,
+                                                                                 (const bf16*)c, ldc, (bf16*)out, M, H);
+  return k3m_check_launch("k3m_relu_cat3");
+}
+
+extern "C" int k3m_fuse_select_fwd(const void* cat, const float* gates, const float* noise, const void* rng,
+                                   unsigned int site, void* out, int ldo, int M, int H, void* stream) {
+  K3M_REQUIRE(noise || rng, "fuse_select: need either a noise tensor or the RNG state");
+  fuse_fwd_kernel<<<grid_for((size_t)M * H, 256), 256, 0, ST(stream)>>>((const bf16*)cat, gates, noise,
+                                                                        (const unsigned long long*)rng, site, (bf16*)out, ldo, M, H);
+  return k3m_check_launch("k3m_fuse_select_fwd");
+}
+
+extern "C" int k3m_fuse_select_bwd(const void* dout, int ldd, const void* cat, const float* gates, const float* noise,
+                                   const void* rng, unsigned int site, void* dgates, void* dcat, int M, int H, void* stream) {
+  K3M_REQUIRE(noise || rng, "fuse_select: need either a noise tensor or the RNG state");
+  fuse_bwd_kernel<<<grid_for((size_t)M * H, 256), 256, 0, ST(stream)>>>(
+      (const bf16*)dout, ldd, (const bf16*)cat, gates, noise, (const unsigned long long*)rng, site, (bf16*)dgates, (bf16*)dcat, M, H);
+  return k3m_check_launch("k3m_fuse_select_bwd");
+}
+
+extern "C" int k3m_relu_bwd_split3(const void* dcat, const void* cat, void* da, int lda, void* db, int ldb, void* dc,
+                                   int ldc, int M, int H, void* stream) {
+  relu_split3_kernel<<<grid_for((size_t)M * 3 * H, 256), 256, 0, ST(stream)>>>((const bf16*)dcat, (const bf16*)cat, (bf16*)da,
+                                                                               lda, (bf16*)db, ldb, (bf16*)dc, ldc, M, H);
+  return k3m_check_launch("k3m_relu_bwd_split3");
+}
+
+extern "C" int k3m_mean_pool_fwd(const void* seq, int ld, void* out, int out_f32, int B, int L, int H, void* stream) {
+  K3M_REQUIRE(L >= 2, "mean_pool: need at least two tokens");
+  const int g = (B * H + 255) / 256;
+  if (out_f32) pool_fwd_kernel<float><<<g, 256, 0, ST(stream)>>>((const bf16*)seq, ld, (float*)out, B, L, H);
+  else pool_fwd_kernel<bf16><<<g, 256, 0, ST(stream)>>>((const bf16*)seq, ld, (bf16*)out, B, L, H);
+  return k3m_check_launch("k3m_mean_pool_fwd");
+}
+
+extern "C" int k3m_mean_pool_bwd(const float* dpool, void* dseq, int ld, int B, int L, int H, void* stream) {
+  pool_bwd_kernel<<<grid_for((size_t)B * L * H, 256), 256, 0, ST(stream)>>>(dpool, (bf16*)dseq, ld, B, L, H);
+  return k3m_check_launch("k3m_mean_pool_bwd");
+}

@@ -1,0 +1,426 @@
+// bf16 GEMM for sm_100a: TMA -> shared memory (128B swizzle) -> tcgen05.mma (accumulators in
+// TMEM) -> tcgen05.ld -> fused epilogue (bias, GELU / GELU', sigmoid, tanh, dropout, residual
+// addend, fp32 accumulate for weight gradients with split-K).
+//
+// One CTA computes one 128 x BN output tile (optionally one K-split of it):
+//   warp 0      TMA producer (one elected lane)
+//   warp 1      TMEM allocator + MMA issuer (one elected lane)
+//   warps 2..5  epilogue: warp w reads TMEM lanes 32*(w%4) .. +31 (one output row per thread)
+// Operand layouts ("major" = which dimension is contiguous in global memory):
+//   nt  A[M,K]  K-major   B[N,K]  K-major      forward  Y = X W^T
+//   nn  A[M,K]  K-major   B[K,N]  MN-major     dgrad    dX = dY W
+//   tn  A[K,M]  MN-major  B[K,N]  MN-major     wgrad    dW = dY^T X
+// MN-major tiles are loaded as 64(k) x 64(mn) TMA boxes; the UMMA descriptor then uses
+// LBO = 8 KB (next 64-wide mn chunk) and SBO = 1 KB (next 8 k-rows).
+#include <cuda.h>
+#include <stdarg.h>
+#include <stdio.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle row
+
+struct GemmParams {
+  int M, N, K;
+  int kb_per_split;  // k-blocks handled by one CTA along grid.z
+  void* out;
+  int ldc, out_f32, accumulate;
+  const bf16* bias;
+  int act;
+  const bf16* aux_in;
+  int ld_aux_in;
+  bf16* aux_out;
+  int ld_aux_out;
+  const void* addend;
+  int ld_add, addend_f32;
+  DropSpec drop;
+  int drop_ld;
+  int vec_ok;  // all epilogue pointers 16 B aligned with ld % 8 == 0
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t addr, uint32_t r[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, "
+      "%15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(addr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// shared-memory matrix descriptor (SWIZZLE_128B, descriptor version 1)
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+template <int BN, int STAGES, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(192, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, GemmParams p) {
+  constexpr int A_BYTES = BM * BK * 2;
+  constexpr int B_BYTES = BN * BK * 2;
+  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
+  const int total_kb = (p.K + BK - 1) / BK;
+  const int kb0 = blockIdx.z * p.kb_per_split;
+  int nkb = total_kb - kb0;
+  if (nkb > p.kb_per_split) nkb = p.kb_per_split;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
+        const int k0 = (kb0 + i) * BK;
+        uint8_t* a = sA + s * A_BYTES;
+        uint8_t* b = sB + s * B_BYTES;
+        if (A_MN) {
+#pragma unroll
+          for (int c = 0; c < BM / 64; ++c) tma_load_2d(a + c * 8192, &map_a, &full[s], m0 + c * 64, k0);
+        } else {
+          tma_load_2d(a, &map_a, &full[s], k0, m0);
+        }
+        if (B_MN) {
+#pragma unroll
+          for (int c = 0; c < BN / 64; ++c) tma_load_2d(b + c * 8192, &map_b, &full[s], n0 + c * 64, k0);
+        } else {
+          tma_load_2d(b, &map_b, &full[s], k0, n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) |
+                                 ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&full[s], ph);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t a = smem_u32(sA + s * A_BYTES), b = smem_u32(sB + s * B_BYTES);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          const uint64_t da = A_MN ? make_desc(a + k * 2048, 8192, 1024) : make_desc(a + k * 32, 0, 1024);
+          const uint64_t db = B_MN ? make_desc(b + k * 2048, 8192, 1024) : make_desc(b + k * 32, 0, 1024);
+          umma_bf16(tmem_base, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    // ---- epilogue -------------------------------------------------------------------------------
+    const int q = warp & 3;
+    const int row = m0 + q * 32 + lane;
+    const bool row_ok = row < p.M;
+    if (nkb > 0) {
+      mbar_wait(tmem_full, 0);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    const bool has_drop = p.drop.thresh != 0;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      uint32_t r[32];
+      if (nkb > 0) {
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), r);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0;
+      }
+      if (!row_ok) continue;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const int col = n0 + c * 32 + g * 8;
+        if (col >= p.N) break;
+        const int nv = (p.N - col) < 8 ? (p.N - col) : 8;
+        const bool vec = p.vec_ok && nv == 8;
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+        if (p.bias) {
+          float t[8];
+          if (vec) ld8(p.bias + col, t);
+          else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(p.bias + col + j) : 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] += t[j];
+        }
+        if (p.act == ACT_GELU) {
+          if (p.aux_out) {
+            bf16* ao = p.aux_out + (size_t)row * p.ld_aux_out + col;
+            if (vec) st8(ao, v);
+            else for (int j = 0; j < nv; ++j) st_f(ao + j, v[j]);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
+        } else if (p.act == ACT_DGELU || p.act == ACT_DTANH) {
+          const bf16* ai = p.aux_in + (size_t)row * p.ld_aux_in + col;
+          float t[8];
+          if (vec) ld8(ai, t);
+          else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ai + j) : 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] *= (p.act == ACT_DGELU) ? dgelu_f(t[j]) : (1.0f - t[j] * t[j]);
+        } else if (p.act == ACT_SIGMOID) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = sigmoid_f(v[j]);
+        } else if (p.act == ACT_TANH) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = tanhf(v[j]);
+        }
+        if (has_drop) {
+          uint32_t w[4];
+          const unsigned long long lin = (unsigned long long)row * (unsigned long long)p.drop_ld + (unsigned long long)col;
+          rng_words(p.drop.rng, p.drop.site, lin >> 3, w);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] *= drop_mult(p.drop, w, j);
+        }
+        if (p.addend) {
+          float t[8];
+          if (p.addend_f32) {
+            const float* ad = reinterpret_cast<const float*>(p.addend) + (size_t)row * p.ld_add + col;
+            if (vec) ld8(ad, t);
+            else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ad[j] : 0.f;
+          } else {
+            const bf16* ad = reinterpret_cast<const bf16*>(p.addend) + (size_t)row * p.ld_add + col;
+            if (vec) ld8(ad, t);
+            else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ad + j) : 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] += t[j];
+        }
+        if (p.out_f32) {
+          float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col;
+          if (p.accumulate) {
+            for (int j = 0; j < nv; ++j) atomicAdd(o + j, v[j]);
+          } else if (vec) {
+            st8(o, v);
+          } else {
+            for (int j = 0; j < nv; ++j) o[j] = v[j];
+          }
+        } else {
+          bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)row * p.ldc + col;
+          if (vec) st8(o, v);
+          else for (int j = 0; j < nv; ++j) st_f(o + j, v[j]);
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
+  }
+}
+
+
+// ---- host side ------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(f);
+  });
+  return fn;
+}
+
+typedef std::tuple<const void*, int, int, int, int, int> MapKey;
+std::map<MapKey, CUtensorMap> g_maps;
+std::mutex g_maps_mu;
+
+// 2-D bf16 tensor [outer, inner] with row stride ld (elements), box [box_outer, box_inner], SW128
+bool get_map(const void* ptr, int inner, int outer, int ld, int box_inner, int box_outer, CUtensorMap* out) {
+  MapKey key(ptr, inner, outer, ld, box_inner, box_outer);
+  {
+    std::lock_guard<std::mutex> lk(g_maps_mu);
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) {
+      *out = it->second;
+      return true;
+    }
+  }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    k3m_set_error("cuTensorMapEncodeTiled entry point not available");
+    return false;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    k3m_set_error("cuTensorMapEncodeTiled failed (%d) ptr=%p inner=%d outer=%d ld=%d box=%dx%d", (int)r, ptr, inner,
+                  outer, ld, box_inner, box_outer);
+    return false;
+  }
+  std::lock_guard<std::mutex> lk(g_maps_mu);
+  if (g_maps.size() > 65536) g_maps.clear();
+  g_maps[key] = m;
+  *out = m;
+  return true;
+}
+
+template <int BN, int STAGES, bool A_MN, bool B_MN>
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int splits, cudaStream_t st) {
+  constexpr int SMEM = STAGES * (BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 16 + 1024;
+  static bool configured = false;
+  auto kern = gemm_kernel<BN, STAGES, A_MN, B_MN>;
+  if (!configured) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess) {
+      k3m_set_error("gemm: cannot set dynamic shared memory to %d", SMEM);
+      return K3M_ERR_CUDA;
+    }
+    configured = true;
+  }
+  dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM, splits);
+  kern<<<grid, 192, SMEM, st>>>(ma, mb, p);
+  return k3m_check_launch("k3m_gemm_bf16");
+}
+
+template <bool A_MN, bool B_MN>
+int dispatch(int bn, const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int splits, cudaStream_t st) {
+  if (bn == 64) return launch<64, 4, A_MN, B_MN>(ma, mb, p, splits, st);
+  return launch<128, 3, A_MN, B_MN>(ma, mb, p, splits, st);
+}
+
+}  // namespace
+
+extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int layout, int M, int N, int K,
+                             void* out, int ldc, int out_f32, int accumulate, const void* bias, int act,
+                             const void* aux_in, int ld_aux_in, void* aux_out, int ld_aux_out, const void* addend,
+                             int ld_add, int addend_f32, const void* rng, unsigned int drop_site, float drop_p,
+                             void* stream) {
+  K3M_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem M=%d N=%d K=%d", M, N, K);
+  K3M_REQUIRE(layout >= 0 && layout <= 2, "gemm: layout must be 0 (nt), 1 (nn) or 2 (tn)");
+  K3M_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm: operand row strides must be multiples of 8 elements (lda=%d ldb=%d)", lda, ldb);
+  K3M_REQUIRE(((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0, "gemm: operands must be 16-byte aligned");
+  K3M_REQUIRE(!accumulate || out_f32, "gemm: accumulate needs an fp32 output");
+  K3M_REQUIRE(!(act == ACT_DGELU || act == ACT_DTANH) || aux_in, "gemm: activation-derivative epilogue needs aux_in");
+  const bool a_mn = layout == 2, b_mn = layout != 0;
+  const int bn = (N <= 64) ? 64 : 128;
+  CUtensorMap ma, mb;
+  // A: K-major -> tensor [M, K]; MN-major -> tensor [K, M]
+  if (!(a_mn ? get_map(a, M, K, lda, 64, 64, &ma) : get_map(a, K, M, lda, 64, BM, &ma))) return K3M_ERR_CUDA;
+  if (!(b_mn ? get_map(b, N, K, ldb, 64, 64, &mb) : get_map(b, K, N, ldb, 64, bn, &mb))) return K3M_ERR_CUDA;
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  const int total_kb = (K + BK - 1) / BK;
+  int splits = 1;
+  if (accumulate) {
+    const int tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+    while (tiles * splits < 148 && total_kb / (splits * 2) >= 4) splits *= 2;
+  }
+  p.kb_per_split = (total_kb + splits - 1) / splits;
+  splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.out = out; p.ldc = ldc; p.out_f32 = out_f32; p.accumulate = accumulate;
+  p.bias = reinterpret_cast<const bf16*>(bias);
+  p.act = act;
+  p.aux_in = reinterpret_cast<const bf16*>(aux_in); p.ld_aux_in = ld_aux_in;
+  p.aux_out = reinterpret_cast<bf16*>(aux_out); p.ld_aux_out = ld_aux_out;
+  p.addend = addend; p.ld_add = ld_add; p.addend_f32 = addend_f32;
+  p.drop.rng = reinterpret_cast<const unsigned long long*>(rng);
+  p.drop.site = drop_site;
+  p.drop.thresh = (rng && drop_p > 0.f) ? (unsigned int)(drop_p * 65536.0f + 0.5f) : 0u;
+  p.drop.scale = 1.0f / (1.0f - drop_p);
+  p.drop_ld = (N + 7) / 8 * 8;
+  auto al = [](const void* q, int ld, int esz) { return q == nullptr || ((((uintptr_t)q) & 15) == 0 && (ld * esz) % 16 == 0); };
+  p.vec_ok = al(out, ldc, out_f32 ? 4 : 2) && al(bias, 8, 2) && al(aux_in, ld_aux_in, 2) && al(aux_out, ld_aux_out, 2) &&
+             al(addend, ld_add, addend_f32 ? 4 : 2) && (!out_f32 || (ldc % 8 == 0 && (((uintptr_t)out) & 31) == 0));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (layout == 0) return dispatch<false, false>(bn, ma, mb, p, splits, st);
+  if (layout == 1) return dispatch<false, true>(bn, ma, mb, p, splits, st);
+  return dispatch<true, true>(bn, ma, mb, p, splits, st);
+}

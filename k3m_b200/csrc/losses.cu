@@ -1,0 +1,402 @@
+// Loss kernels (masked-LM cross entropy, masked-region KL, ITM value), the batched structure
+// aggregator + link-prediction loss, and multi-tensor AdamW.
+#include "common.cuh"
+
+namespace {
+
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+// ---- label counts ---------------------------------------------------------------------------
+__global__ void count_kernel(const long long* __restrict__ lab, int n, long long value, int equal, float* __restrict__ out) {
+  __shared__ float red[32];
+  float c = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) c += ((lab[i] == value) == (equal != 0)) ? 1.f : 0.f;
+  c = block_sum(c, red);
+  if (threadIdx.x == 0) out[0] = c;
+}
+
+// ---- masked-LM cross entropy (CrossEntropyLoss(ignore_index=-1), vilbert_k3m.py:2817-2826) -----------
+// One CTA per row.  loss += (lse - logit[label]) / count ; dlogits = (softmax - onehot) * gscale / count
+// written in place over the logits (rows without a label become zero).
+__global__ void __launch_bounds__(256) xent_kernel(bf16* __restrict__ logits, int ld, const long long* __restrict__ labels,
+                                                   const float* __restrict__ count, int V, float gscale,
+                                                   float* __restrict__ loss, int write_grad) {
+  __shared__ float red[32];
+  const int row = blockIdx.x;
+  bf16* lr = logits + (size_t)row * ld;
+  const long long lab = labels[row];
+  if (lab < 0) {
+    if (write_grad)
+      for (int c = threadIdx.x; c < ld; c += blockDim.x) lr[c] = __float2bfloat16(0.f);
+    return;
+  }
+  float mx = -3.0e38f;
+  for (int c = threadIdx.x; c < V; c += blockDim.x) mx = fmaxf(mx, __bfloat162float(lr[c]));
+  mx = block_max(mx, red);
+  float s = 0.f;
+  for (int c = threadIdx.x; c < V; c += blockDim.x) s += __expf(__bfloat162float(lr[c]) - mx);
+  s = block_sum(s, red);
+  const float lse = mx + __logf(s);
+  const float inv_cnt = 1.0f / count[0];
+  if (threadIdx.x == 0) atomicAdd(loss, (lse - __bfloat162float(lr[lab])) * inv_cnt);
+  if (write_grad) {
+    const float g = gscale * inv_cnt;
+    __syncthreads();
+    for (int c = threadIdx.x; c < ld; c += blockDim.x) {
+      float v = 0.f;
+      if (c < V) v = (__expf(__bfloat162float(lr[c]) - lse) - (c == lab ? 1.f : 0.f)) * g;
+      lr[c] = __float2bfloat16(v);
+    }
+  }
+}
+
+// ---- masked-region KL (KLDivLoss(none)(log_softmax, target) * (label==1) / count, :2754-2760) ------
+// One CTA per (item, region) row of the fp32 logits [B*Lv1, ld]; row 0 of every item is the global
+// region (no target).  dlogits (bf16, same ld) = (softmax * sum(t) - t) * gscale / count.
+__global__ void __launch_bounds__(256) kl_kernel(const float* __restrict__ logits, int ld, const float* __restrict__ target,
+                                                 const long long* __restrict__ label, const float* __restrict__ count, int T,
+                                                 int Lv1, float gscale, float* __restrict__ loss, bf16* __restrict__ dlogits) {
+  __shared__ float red[32];
+  const int row = blockIdx.x;
+  const int b = row / Lv1, i = row % Lv1;
+  bf16* dr = dlogits ? dlogits + (size_t)row * ld : nullptr;
+  const bool active = i > 0 && label[(size_t)b * (Lv1 - 1) + (i - 1)] == 1;
+  if (!active) {
+    if (dr)
+      for (int c = threadIdx.x; c < ld; c += blockDim.x) dr[c] = __float2bfloat16(0.f);
+    return;
+  }
+  const float* lr = logits + (size_t)row * ld;
+  const float* tr = target + ((size_t)b * (Lv1 - 1) + (i - 1)) * T;
+  float mx = -3.0e38f;
+  for (int c = threadIdx.x; c < T; c += blockDim.x) mx = fmaxf(mx, lr[c]);
+  mx = block_max(mx, red);
+  float s = 0.f, ts = 0.f;
+  for (int c = threadIdx.x; c < T; c += blockDim.x) {
+    s += __expf(lr[c] - mx);
+    ts += tr[c];
+  }
+  s = block_sum(s, red);
+  ts = block_sum(ts, red);
+  const float lse = mx + __logf(s);
+  float kl = 0.f;
+  for (int c = threadIdx.x; c < T; c += blockDim.x) {
+    const float t = tr[c];
+    if (t > 0.f) kl += t * (__logf(t) - (lr[c] - lse));
+  }
+  kl = block_sum(kl, red);
+  const float inv_cnt = 1.0f / count[0];
+  if (threadIdx.x == 0) atomicAdd(loss, kl * inv_cnt);
+  if (dr) {
+    const float g = gscale * inv_cnt;
+    for (int c = threadIdx.x; c < ld; c += blockDim.x) {
+      float v = 0.f;
+      if (c < T) v = (__expf(lr[c] - lse) * ts - tr[c]) * g;
+      dr[c] = __float2bfloat16(v);
+    }
+  }
+}
+
+// ---- ITM value: CE(Linear_{H->2}(dropout(pool_t + pool_pv + pool_v)), 1 - ((l1+l2+l3)==0)) -----------
+__global__ void __launch_bounds__(128) itm_kernel(const float* pt, const float* ppv, const float* pv, const bf16* w,
+                                                  const bf16* bias, const long long* l1, const long long* l2,
+                                                  const long long* l3, int B, int H, DropSpec drop, float* loss) {
+  __shared__ float red[32];
+  const int b = blockIdx.x;
+  float a0 = 0.f, a1 = 0.f;
+  for (int c = threadIdx.x; c < H; c += blockDim.x) {
+    float x = pt[(size_t)b * H + c] + ppv[(size_t)b * H + c] + pv[(size_t)b * H + c];
+    if (drop.thresh) x *= drop_mult_at(drop, (unsigned long long)b * ((H + 7) / 8 * 8) + c);
+    a0 = fmaf(x, ld_f(w + c), a0);
+    a1 = fmaf(x, ld_f(w + H + c), a1);
+  }
+  a0 = block_sum(a0, red) + ld_f(bias);
+  a1 = block_sum(a1, red) + ld_f(bias + 1);
+  if (threadIdx.x == 0) {
+    const int lab = ((l1[b] + l2[b] + l3[b]) == 0) ? 0 : 1;
+    const float mx = fmaxf(a0, a1);
+    const float lse = mx + __logf(__expf(a0 - mx) + __expf(a1 - mx));
+    atomicAdd(loss, (lse - (lab ? a1 : a0)) / (float)B);
+  }
+}
+
+// ---- structure aggregator (structure_aggregator, vilbert_k3m.py:2437-2467) ---------------------------
+// X[p] = [c_init[item] | mean(seq[r0], seq[r1]) | mean(seq[r2], seq[r3])]  (bf16 for the W1 GEMM);
+// PV[p] = the two means in fp32 for the LPM norms.
+__global__ void pair_gather_fwd_kernel(const float* __restrict__ c_init, const bf16* __restrict__ seq, int lds,
+                                       const int* __restrict__ item, const int* __restrict__ rows, bf16* __restrict__ X,
+                                       float* __restrict__ PV, int P, int H) {
+  const size_t n = (size_t)P * H;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int p = (int)(i / H), h = (int)(i % H);
+    const int* r = rows + (size_t)p * 4;
+    const float pm = 0.5f * (__bfloat162float(seq[(size_t)r[0] * lds + h]) + __bfloat162float(seq[(size_t)r[1] * lds + h]));
+    const float vm = 0.5f * (__bfloat162float(seq[(size_t)r[2] * lds + h]) + __bfloat162float(seq[(size_t)r[3] * lds + h]));
+    bf16* x = X + (size_t)p * 3 * H;
+    x[h] = __float2bfloat16(c_init[(size_t)item[p] * H + h]);
+    x[H + h] = __float2bfloat16(pm);
+    x[2 * H + h] = __float2bfloat16(vm);
+    PV[(size_t)p * 2 * H + h] = pm;
+    PV[(size_t)p * 2 * H + H + h] = vm;
+  }
+}
+
+// one CTA per pair (pairs of one item may share sequence rows -> read-modify-write must not race
+// across CTAs: sequence rows get fp32 atomics on a scratch [rows, H] buffer that the caller adds).
+__global__ void pair_gather_bwd_kernel(const float* __restrict__ dX, const float* __restrict__ dPV, const int* __restrict__ item,
+                                       const int* __restrict__ rows, float* __restrict__ dc_init, float* __restrict__ dseq32,
+                                       int P, int H) {
+  const size_t n = (size_t)P * H;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int p = (int)(i / H), h = (int)(i % H);
+    const int* r = rows + (size_t)p * 4;
+    const float* dx = dX + (size_t)p * 3 * H;
+    atomicAdd(dc_init + (size_t)item[p] * H + h, dx[h]);
+    const float gp = 0.5f * (dx[H + h] + dPV[(size_t)p * 2 * H + h]);
+    const float gv = 0.5f * (dx[2 * H + h] + dPV[(size_t)p * 2 * H + H + h]);
+    atomicAdd(dseq32 + (size_t)r[0] * H + h, gp);
+    atomicAdd(dseq32 + (size_t)r[1] * H + h, gp);
+    atomicAdd(dseq32 + (size_t)r[2] * H + h, gv);
+    atomicAdd(dseq32 + (size_t)r[3] * H + h, gv);
+  }
+}
+
+// one CTA per item: scores b_j = w2 . leaky_relu(t_j) + b2 over the item's pair range, softmax,
+// s = sum_j att_j t_j.  att is stored [B, maxn].
+__global__ void __launch_bounds__(256) struct_attn_fwd_kernel(const float* __restrict__ t, const bf16* __restrict__ w2,
+                                                              const bf16* __restrict__ b2, const int* __restrict__ seg,
+                                                              float* __restrict__ s_out, float* __restrict__ att, int maxn, int H) {
+  extern __shared__ float sc[];  // [maxn]
+  __shared__ float red[32];
+  const int i = blockIdx.x, s0 = seg[2 * i], n = seg[2 * i + 1] - s0;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int j = warp; j < n; j += nw) {
+    const float* tr = t + (size_t)(s0 + j) * H;
+    float a = 0.f;
+    for (int c = lane; c < H; c += 32) {
+      const float v = tr[c];
+      a = fmaf(v > 0.f ? v : 0.01f * v, ld_f(w2 + c), a);
+    }
+    a = warp_sum(a);
+    if (lane == 0) sc[j] = a + ld_f(b2);
+  }
+  __syncthreads();
+  float mx = -3.0e38f;
+  for (int j = threadIdx.x; j < n; j += blockDim.x) mx = fmaxf(mx, sc[j]);
+  mx = block_max(mx, red);
+  float sum = 0.f;
+  for (int j = threadIdx.x; j < n; j += blockDim.x) sum += __expf(sc[j] - mx);
+  sum = block_sum(sum, red);
+  __syncthreads();
+  for (int j = threadIdx.x; j < n; j += blockDim.x) {
+    const float a = __expf(sc[j] - mx) / sum;
+    sc[j] = a;
+    att[(size_t)i * maxn + j] = a;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < H; c += blockDim.x) {
+    float acc = 0.f;
+    for (int j = 0; j < n; ++j) acc = fmaf(sc[j], t[(size_t)(s0 + j) * H + c], acc);
+    s_out[(size_t)i * H + c] = acc;
+  }
+}
+
+__global__ void __launch_bounds__(256) struct_attn_bwd_kernel(const float* __restrict__ ds, const float* __restrict__ t,
+                                                              const float* __restrict__ att, const bf16* __restrict__ w2,
+                                                              const int* __restrict__ seg, float* __restrict__ dt,
+                                                              float* __restrict__ dw2, float* __restrict__ db2, int maxn, int H) {
+  extern __shared__ float sm[];  // da[maxn], dsc[maxn]
+  __shared__ float red[32];
+  float* da = sm;
+  float* dsc = sm + maxn;
+  const int i = blockIdx.x, s0 = seg[2 * i], n = seg[2 * i + 1] - s0;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const float* dsr = ds + (size_t)i * H;
+  for (int j = warp; j < n; j += nw) {
+    const float* tr = t + (size_t)(s0 + j) * H;
+    float a = 0.f;
+    for (int c = lane; c < H; c += 32) a = fmaf(tr[c], dsr[c], a);
+    a = warp_sum(a);
+    if (lane == 0) da[j] = a;
+  }
+  __syncthreads();
+  float dot = 0.f;
+  for (int j = threadIdx.x; j < n; j += blockDim.x) dot += att[(size_t)i * maxn + j] * da[j];
+  dot = block_sum(dot, red);
+  float bsum = 0.f;
+  for (int j = threadIdx.x; j < n; j += blockDim.x) {
+    const float a = att[(size_t)i * maxn + j];
+    dsc[j] = a * (da[j] - dot);
+    bsum += dsc[j];
+  }
+  bsum = block_sum(bsum, red);
+  if (threadIdx.x == 0) atomicAdd(db2, bsum);
+  __syncthreads();
+  for (int c = threadIdx.x; c < H; c += blockDim.x) {
+    const float wc = ld_f(w2 + c), g = dsr[c];
+    float dwc = 0.f;
+    for (int j = 0; j < n; ++j) {
+      const float tv = t[(size_t)(s0 + j) * H + c];
+      const float a = att[(size_t)i * maxn + j];
+      atomicAdd(dt + (size_t)(s0 + j) * H + c, a * g + dsc[j] * wc * (tv > 0.f ? 1.f : 0.01f));
+      dwc = fmaf(dsc[j], tv > 0.f ? tv : 0.01f * tv, dwc);
+    }
+    atomicAdd(dw2 + c, dwc);
+  }
+}
+
+// ---- link-prediction loss (vilbert_k3m.py:2469-2502) --------------------------------------------------
+// one CTA per term (i, j, ni, nv): pos = |c[i] + p[j] - v[j]|, neg = |c[ni] + p[j] - v[nv]|,
+// loss += max(0, neg - pos + margin) / T, and the gradient goes straight to dc_final / dPV.
+__global__ void __launch_bounds__(128) lpm_kernel(const float* __restrict__ c_final, const float* __restrict__ PV,
+                                                  const int* __restrict__ terms, int T, int H, float margin,
+                                                  float* __restrict__ loss, float* __restrict__ dc, float* __restrict__ dPV) {
+  __shared__ float red[32];
+  const int tix = blockIdx.x;
+  const int i = terms[4 * tix], j = terms[4 * tix + 1], ni = terms[4 * tix + 2], nv = terms[4 * tix + 3];
+  const float* ci = c_final + (size_t)i * H;
+  const float* cn = c_final + (size_t)ni * H;
+  const float* pj = PV + (size_t)j * 2 * H;
+  const float* vj = pj + H;
+  const float* vn = PV + (size_t)nv * 2 * H + H;
+  float sp = 0.f, sn = 0.f;
+  for (int c = threadIdx.x; c < H; c += blockDim.x) {
+    const float up = ci[c] + pj[c] - vj[c], un = cn[c] + pj[c] - vn[c];
+    sp = fmaf(up, up, sp);
+    sn = fmaf(un, un, sn);
+  }
+  sp = block_sum(sp, red);
+  sn = block_sum(sn, red);
+  const float npos = sqrtf(sp), nneg = sqrtf(sn);
+  const float hinge = nneg - npos + margin;
+  if (hinge <= 0.f) return;
+  const float invT = 1.0f / (float)T;
+  if (threadIdx.x == 0) atomicAdd(loss, hinge * invT);
+  const float gp = -invT / fmaxf(npos, 1e-30f), gn = invT / fmaxf(nneg, 1e-30f);
+  for (int c = threadIdx.x; c < H; c += blockDim.x) {
+    const float up = (ci[c] + pj[c] - vj[c]) * gp, un = (cn[c] + pj[c] - vn[c]) * gn;
+    atomicAdd(dc + (size_t)i * H + c, up);
+    atomicAdd(dc + (size_t)ni * H + c, un);
+    atomicAdd(dPV + (size_t)j * 2 * H + c, up + un);
+    atomicAdd(dPV + (size_t)j * 2 * H + H + c, -up);
+    atomicAdd(dPV + (size_t)nv * 2 * H + H + c, -un);
+  }
+}
+
+// ---- multi-tensor AdamW over a flat arena range (torch.optim.AdamW semantics, pretrain.py:919-924) ----
+// hyper (device fp32[8]) = lr, beta1, beta2, eps, weight_decay, step, grad_scale, unused.  Reading the
+// hyper-parameters from device memory keeps the kernel node valid across CUDA-graph replays.
+__global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
+                                                    float* __restrict__ v, bf16* __restrict__ p16,
+                                                    const float* __restrict__ hyper, size_t n4, int zero_grad) {
+  const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], step = hyper[5], gs = hyper[6];
+  const float bc1 = 1.0f - powf(b1, step), bc2 = 1.0f - powf(b2, step);
+  const float step_size = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2), decay = 1.0f - lr * wd;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 pp = reinterpret_cast<float4*>(p)[i], gg = reinterpret_cast<float4*>(g)[i];
+    float4 mm = reinterpret_cast<float4*>(m)[i], vv = reinterpret_cast<float4*>(v)[i];
+    float* pa = &pp.x; float* ga = &gg.x; float* ma = &mm.x; float* va = &vv.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float gr = ga[k] * gs;
+      pa[k] *= decay;
+      ma[k] = b1 * ma[k] + (1.0f - b1) * gr;
+      va[k] = b2 * va[k] + (1.0f - b2) * gr * gr;
+      pa[k] -= step_size * ma[k] / (sqrtf(va[k]) * inv_sqrt_bc2 + eps);
+    }
+    reinterpret_cast<float4*>(p)[i] = pp;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+    if (zero_grad) reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(pp.x, pp.y), hi = __floats2bfloat162_rn(pp.z, pp.w);
+    uint2 u;
+    u.x = *reinterpret_cast<uint32_t*>(&lo);
+    u.y = *reinterpret_cast<uint32_t*>(&hi);
+    reinterpret_cast<uint2*>(p16)[i] = u;
+  }
+}
+
+}  // namespace
+
+extern "C" int k3m_count_labels(const long long* labels, int n, long long value, int equal, float* out, void* stream) {
+  count_kernel<<<1, 1024, 0, ST(stream)>>>(labels, n, value, equal, out);
+  return k3m_check_launch("k3m_count_labels");
+}
+
+extern "C" int k3m_xent_fwd_bwd(void* logits, int ld, const long long* labels, const float* count, int M, int V,
+                                float grad_scale, float* loss, int write_grad, void* stream) {
+  K3M_REQUIRE(M > 0 && V > 0 && ld >= V, "xent: bad shape");
+  xent_kernel<<<M, 256, 0, ST(stream)>>>((bf16*)logits, ld, labels, count, V, grad_scale, loss, write_grad);
+  return k3m_check_launch("k3m_xent_fwd_bwd");
+}
+
+extern "C" int k3m_kl_fwd_bwd(const float* logits, int ld, const float* target, const long long* image_label,
+                              const float* count, int B, int Lv1, int T, float grad_scale, float* loss, void* dlogits,
+                              void* stream) {
+  K3M_REQUIRE(B > 0 && Lv1 >= 2 && ld >= T, "kl: bad shape");
+  kl_kernel<<<B * Lv1, 256, 0, ST(stream)>>>(logits, ld, target, image_label, count, T, Lv1, grad_scale, loss, (bf16*)dlogits);
+  return k3m_check_launch("k3m_kl_fwd_bwd");
+}
+
+extern "C" int k3m_itm_loss(const float* pool_t, const float* pool_pv, const float* pool_v, const void* w, const void* b,
+                            const long long* l1, const long long* l2, const long long* l3, int B, int H, const void* rng,
+                            unsigned int site, float drop_p, float* loss, void* stream) {
+  DropSpec d;
+  d.rng = (const unsigned long long*)rng;
+  d.site = site;
+  d.thresh = (rng && drop_p > 0.f) ? (unsigned int)(drop_p * 65536.0f + 0.5f) : 0u;
+  d.scale = 1.0f / (1.0f - drop_p);
+  itm_kernel<<<B, 128, 0, ST(stream)>>>(pool_t, pool_pv, pool_v, (const bf16*)w, (const bf16*)b, l1, l2, l3, B, H, d, loss);
+  return k3m_check_launch("k3m_itm_loss");
+}
+
+extern "C" int k3m_pair_gather_fwd(const float* c_init, const void* seq, int lds, const int* pair_item, const int* pair_rows,
+                                   void* X, float* PV, int P, int H, void* stream) {
+  K3M_REQUIRE(P > 0, "pair_gather: no pairs");
+  size_t n = (size_t)P * H;
+  int g = (int)((n + 255) / 256);
+  if (g > 148 * 8) g = 148 * 8;
+  pair_gather_fwd_kernel<<<g, 256, 0, ST(stream)>>>(c_init, (const bf16*)seq, lds, pair_item, pair_rows, (bf16*)X, PV, P, H);
+  return k3m_check_launch("k3m_pair_gather_fwd");
+}
+
+extern "C" int k3m_pair_gather_bwd(const float* dX, const float* dPV, const int* pair_item, const int* pair_rows,
+                                   float* dc_init, float* dseq32, int P, int H, void* stream) {
+  size_t n = (size_t)P * H;
+  int g = (int)((n + 255) / 256);
+  if (g > 148 * 8) g = 148 * 8;
+  pair_gather_bwd_kernel<<<g, 256, 0, ST(stream)>>>(dX, dPV, pair_item, pair_rows, dc_init, dseq32, P, H);
+  return k3m_check_launch("k3m_pair_gather_bwd");
+}
+
+extern "C" int k3m_struct_attn_fwd(const float* t, const void* w2, const void* b2, const int* seg, float* s_out, float* att,
+                                   int B, int maxn, int H, void* stream) {
+  K3M_REQUIRE(maxn > 0 && maxn <= 8192, "struct_attn: bad maxn");
+  struct_attn_fwd_kernel<<<B, 256, maxn * sizeof(float), ST(stream)>>>(t, (const bf16*)w2, (const bf16*)b2, seg, s_out, att, maxn, H);
+  return k3m_check_launch("k3m_struct_attn_fwd");
+}
+
+extern "C" int k3m_struct_attn_bwd(const float* ds, const float* t, const float* att, const void* w2, const int* seg,
+                                   float* dt, float* dw2, float* db2, int B, int maxn, int H, void* stream) {
+  struct_attn_bwd_kernel<<<B, 256, 2 * maxn * sizeof(float), ST(stream)>>>(ds, t, att, (const bf16*)w2, seg, dt, dw2, db2, maxn, H);
+  return k3m_check_launch("k3m_struct_attn_bwd");
+}
+
+extern "C" int k3m_lpm_fwd_bwd(const float* c_final, const float* PV, const int* terms, int T, int H, float margin,
+                               float* loss, float* dc_final, float* dPV, void* stream) {
+  if (T <= 0) return K3M_OK;
+  lpm_kernel<<<T, 128, 0, ST(stream)>>>(c_final, PV, terms, T, H, margin, loss, dc_final, dPV);
+  return k3m_check_launch("k3m_lpm_fwd_bwd");
+}
+
+extern "C" int k3m_adamw(float* p32, float* g32, float* m, float* v, void* p16, const float* hyper, long long n,
+                         int zero_grad, void* stream) {
+  K3M_REQUIRE(n % 4 == 0, "adamw: range length must be a multiple of 4");
+  K3M_REQUIRE((((uintptr_t)p32 | (uintptr_t)g32 | (uintptr_t)m | (uintptr_t)v) & 15) == 0 && (((uintptr_t)p16) & 7) == 0,
+              "adamw: misaligned range");
+  const size_t n4 = (size_t)n / 4;
+  size_t g = (n4 + 255) / 256;
+  if (g > 148 * 16) g = 148 * 16;
+  adamw_kernel<<<(int)g, 256, 0, ST(stream)>>>(p32, g32, m, v, (bf16*)p16, hyper, n4, zero_grad);
+  return k3m_check_launch("k3m_adamw");
+}

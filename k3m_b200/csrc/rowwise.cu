@@ -1,0 +1,382 @@
+// HBM-bound row-wise kernels: LayerNorm forward / backward (+ dropout, + bias-gradient column
+// sums), column sums, casts and small elementwise helpers.  One warp owns one row; every global
+// access is a 16-byte vector; statistics and reductions are fp32.
+#include "common.cuh"
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------
+// LayerNorm forward: y = (x - mean) * rstd * gamma + beta   [TF style: eps inside the sqrt,
+// biased variance — vilbert_k3m.py:328-332], optional dropout on y (embeddings).
+// NV = 8-element vectors per lane (H <= 256 * NV).
+template <int NV>
+__global__ void __launch_bounds__(128) ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ gamma,
+                                                     const bf16* __restrict__ beta, bf16* __restrict__ y,
+                                                     float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                                     int M, int H, float eps, DropSpec drop) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (row >= M) return;
+  const bf16* xr = x + (size_t)row * H;
+  float v[NV][8];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (lane + 32 * i) * 8;
+    if (c < H) {
+      ld8(xr + c, v[i]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += v[i][j];
+    }
+  }
+  const float mean = warp_sum(s) / (float)H;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (lane + 32 * i) * 8;
+    if (c < H) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = v[i][j] - mean;
+        q += d * d;
+      }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / (float)H + eps);
+  if (lane == 0) {
+    mean_out[row] = mean;
+    rstd_out[row] = rstd;
+  }
+  bf16* yr = y + (size_t)row * H;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (lane + 32 * i) * 8;
+    if (c < H) {
+      float g[8], b[8], o[8];
+      ld8(gamma + c, g);
+      ld8(beta + c, b);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * g[j] + b[j];
+      if (drop.thresh) {
+        uint32_t w[4];
+        rng_words(drop.rng, drop.site, ((unsigned long long)row * H + c) >> 3, w);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] *= drop_mult(drop, w, j);
+      }
+      st8(yr + c, o);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// LayerNorm backward.  dy is optionally masked first by the post-LN dropout (drop_out).
+// dx -> bf16; if drop_in is set a second output dxm = dx * mask_in * scale is written (gradient of
+// the GEMM output that was dropped out before the residual add).  Column sums: dgamma += dy*xhat,
+// dbeta += dy, dbias += dxm  (fp32 atomics, one set per CTA after a grid-stride loop over rows).
+template <int NV>
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+                                                     const bf16* __restrict__ gamma, const float* __restrict__ mean_in,
+                                                     const float* __restrict__ rstd_in, bf16* __restrict__ dx,
+                                                     bf16* __restrict__ dxm, float* __restrict__ dgamma,
+                                                     float* __restrict__ dbeta, float* __restrict__ dbias, int M, int H,
+                                                     DropSpec drop_out, DropSpec drop_in) {
+  extern __shared__ float sred[];  // [8 warps][3][H]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float ag[NV][8], ab[NV][8], ac[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ag[i][j] = ab[i][j] = ac[i][j] = 0.f;
+  float gm[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (lane + 32 * i) * 8;
+    if (c < H) ld8(gamma + c, gm[i]);
+  }
+  for (int row = blockIdx.x * 8 + warp; row < M; row += gridDim.x * 8) {
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float g[NV][8], xh[NV][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (lane + 32 * i) * 8;
+      if (c < H) {
+        float d[8], xv[8];
+        ld8(dy + (size_t)row * H + c, d);
+        ld8(x + (size_t)row * H + c, xv);
+        if (drop_out.thresh) {
+          uint32_t w[4];
+          rng_words(drop_out.rng, drop_out.site, ((unsigned long long)row * H + c) >> 3, w);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) d[j] *= drop_mult(drop_out, w, j);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] = (xv[j] - mean) * rstd;
+          ag[i][j] += d[j] * xh[i][j];
+          ab[i][j] += d[j];
+          g[i][j] = d[j] * gm[i][j];
+          s1 += g[i][j];
+          s2 += g[i][j] * xh[i][j];
+        }
+      }
+    }
+    s1 = warp_sum(s1) / (float)H;
+    s2 = warp_sum(s2) / (float)H;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (lane + 32 * i) * 8;
+      if (c < H) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (g[i][j] - s1 - xh[i][j] * s2) * rstd;
+        st8(dx + (size_t)row * H + c, o);
+        if (drop_in.thresh) {
+          uint32_t w[4];
+          rng_words(drop_in.rng, drop_in.site, ((unsigned long long)row * H + c) >> 3, w);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] *= drop_mult(drop_in, w, j);
+          st8(dxm + (size_t)row * H + c, o);
+        }
+        if (dbias) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) ac[i][j] += o[j];
+        }
+      }
+    }
+  }
+  // cross-warp reduction of the three column-sum sets, then one atomic per column per CTA
+  float* s0 = sred + (size_t)warp * 3 * H;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (lane + 32 * i) * 8;
+    if (c < H) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s0[c + j] = ag[i][j];
+        s0[H + c + j] = ab[i][j];
+        s0[2 * H + c + j] = ac[i][j];
+      }
+    }
+  }
+  __syncthreads();
+  const int nsets = dbias ? 3 : 2;
+  for (int idx = threadIdx.x; idx < nsets * H; idx += blockDim.x) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += sred[(size_t)w * 3 * H + idx];
+    float* dst = idx < H ? dgamma + idx : (idx < 2 * H ? dbeta + (idx - H) : dbias + (idx - 2 * H));
+    atomicAdd(dst, t);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// out[n] += sum_m x[m, n]   (x bf16 or fp32, row stride ld)
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, int ld, float* __restrict__ out, int M, int N,
+                                                     int rows_per_cta) {
+  __shared__ float sred[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + lane;
+  const int r0 = blockIdx.y * rows_per_cta;
+  int r1 = r0 + rows_per_cta;
+  if (r1 > M) r1 = M;
+  float acc = 0.f;
+  if (col < N)
+    for (int r = r0 + warp; r < r1; r += 8) acc += ld_f(x + (size_t)r * ld + col);
+  sred[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && col < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += sred[w][lane];
+    atomicAdd(out + col, t);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+template <typename TI, typename TO>
+__global__ void cast_kernel(const TI* __restrict__ x, TO* __restrict__ y, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    st_f(y + i, ld_f(x + i));
+}
+
+// out = wa*a + wb*b + wc*c   (c optional)
+template <typename TI, typename TO>
+__global__ void lincomb3_kernel(const TI* a, const TI* b, const TI* c, float wa, float wb, float wc, TO* out, int rows,
+                                int cols, int lda, int ldb, int ldc, int ldo) {
+  const size_t n = (size_t)rows * cols;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols), k = (int)(i % cols);
+    float v = wa * ld_f(a + (size_t)r * lda + k) + wb * ld_f(b + (size_t)r * ldb + k);
+    if (c) v += wc * ld_f(c + (size_t)r * ldc + k);
+    st_f(out + (size_t)r * ldo + k, v);
+  }
+}
+
+// y += alpha * x
+template <typename TX, typename TY>
+__global__ void axpy_kernel(const TX* x, TY* y, float alpha, int rows, int cols, int ldx, int ldy) {
+  const size_t n = (size_t)rows * cols;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols), k = (int)(i % cols);
+    TY* p = y + (size_t)r * ldy + k;
+    st_f(p, ld_f(p) + alpha * ld_f(x + (size_t)r * ldx + k));
+  }
+}
+
+__global__ void scale_kernel(float* x, float alpha, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) x[i] *= alpha;
+}
+
+// dx = dy * gelu'(pre)
+__global__ void dgelu_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ pre, bf16* __restrict__ dx, size_t n8) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    float a[8], b[8];
+    ld8(dy + i * 8, a);
+    ld8(pre + i * 8, b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] *= dgelu_f(b[j]);
+    st8(dx + i * 8, a);
+  }
+}
+
+// (1 - mask) * -10000   (vilbert_k3m.py:2561)
+__global__ void mask_additive_kernel(const long long* __restrict__ mask, float* __restrict__ out, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (1.0f - (float)mask[i]) * -10000.0f;
+}
+
+inline int grid_for(size_t n, int block) {
+  size_t g = (n + block - 1) / block;
+  if (g > 148 * 16) g = 148 * 16;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+inline DropSpec make_drop(const void* rng, unsigned int site, float p) {
+  DropSpec d;
+  d.rng = reinterpret_cast<const unsigned long long*>(rng);
+  d.site = site;
+  d.thresh = (rng && p > 0.f) ? (unsigned int)(p * 65536.0f + 0.5f) : 0u;
+  d.scale = 1.0f / (1.0f - p);
+  return d;
+}
+
+}  // namespace
+
+extern "C" int k3m_ln_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd, int M,
+                          int H, float eps, const void* rng, unsigned int site, float drop_p, void* stream) {
+  K3M_REQUIRE(M > 0 && H > 0 && H % 8 == 0 && H <= 4096, "ln_fwd: need H %% 8 == 0 and H <= 4096 (H=%d)", H);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  DropSpec d = make_drop(rng, site, drop_p);
+  const int grid = (M + 3) / 4;
+  const int nv = (H + 255) / 256;
+#define LN_FWD(NV)                                                                                             \
+  ln_fwd_kernel<NV><<<grid, 128, 0, st>>>((const bf16*)x, (const bf16*)gamma, (const bf16*)beta, (bf16*)y, mean, \
+                                          rstd, M, H, eps, d)
+  if (nv <= 1) LN_FWD(1);
+  else if (nv <= 2) LN_FWD(2);
+  else if (nv <= 4) LN_FWD(4);
+  else if (nv <= 8) LN_FWD(8);
+  else LN_FWD(16);
+#undef LN_FWD
+  return k3m_check_launch("k3m_ln_fwd");
+}
+
+extern "C" int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                          void* dx, void* dxm, float* dgamma, float* dbeta, float* dbias, int M, int H, const void* rng,
+                          unsigned int site_out, float p_out, unsigned int site_in, float p_in, void* stream) {
+  K3M_REQUIRE(M > 0 && H > 0 && H % 8 == 0 && H <= 1024, "ln_bwd: need H %% 8 == 0 and H <= 1024 (H=%d)", H);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  DropSpec dout = make_drop(rng, site_out, p_out), din = make_drop(rng, site_in, p_in);
+  K3M_REQUIRE(!din.thresh || dxm, "ln_bwd: drop_in needs the dxm output");
+  int grid = (M + 7) / 8;
+  if (grid > 148 * 2) grid = 148 * 2;
+  const size_t smem = (size_t)8 * 3 * H * sizeof(float);
+  const int nv = (H + 255) / 256;
+#define LN_BWD(NV)                                                                                                   \
+  do {                                                                                                               \
+    static bool cfg = false;                                                                                         \
+    if (!cfg) {                                                                                                      \
+      cudaFuncSetAttribute(ln_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 3 * 1024 * 4);        \
+      cfg = true;                                                                                                    \
+    }                                                                                                                \
+    ln_bwd_kernel<NV><<<grid, 256, smem, st>>>((const bf16*)dy, (const bf16*)x, (const bf16*)gamma, mean, rstd,       \
+                                               (bf16*)dx, (bf16*)dxm, dgamma, dbeta, dbias, M, H, dout, din);         \
+  } while (0)
+  if (nv <= 1) LN_BWD(1);
+  else if (nv <= 2) LN_BWD(2);
+  else LN_BWD(4);
+#undef LN_BWD
+  return k3m_check_launch("k3m_ln_bwd");
+}
+
+extern "C" int k3m_colsum(const void* x, int ld, int x_f32, float* out, int M, int N, void* stream) {
+  K3M_REQUIRE(M > 0 && N > 0, "colsum: empty");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int gy = (M + 255) / 256;
+  if (gy > 64) gy = 64;
+  const int rows_per = (M + gy - 1) / gy;
+  dim3 grid((N + 31) / 32, gy);
+  if (x_f32) colsum_kernel<float><<<grid, 256, 0, st>>>((const float*)x, ld, out, M, N, rows_per);
+  else colsum_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)x, ld, out, M, N, rows_per);
+  return k3m_check_launch("k3m_colsum");
+}
+
+extern "C" int k3m_cast(const void* x, int x_f32, void* y, int y_f32, long long n, void* stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int g = grid_for((size_t)n, 256);
+  if (x_f32 && !y_f32) cast_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)x, (bf16*)y, (size_t)n);
+  else if (!x_f32 && y_f32) cast_kernel<bf16, float><<<g, 256, 0, st>>>((const bf16*)x, (float*)y, (size_t)n);
+  else if (x_f32) cast_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, (float*)y, (size_t)n);
+  else cast_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)x, (bf16*)y, (size_t)n);
+  return k3m_check_launch("k3m_cast");
+}
+
+extern "C" int k3m_lincomb3(const void* a, int lda, const void* b, int ldb, const void* c, int ldc, float wa, float wb,
+                            float wc, int in_f32, void* out, int ldo, int out_f32, int rows, int cols, void* stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int g = grid_for((size_t)rows * cols, 256);
+  if (in_f32 && out_f32)
+    lincomb3_kernel<float, float><<<g, 256, 0, st>>>((const float*)a, (const float*)b, (const float*)c, wa, wb, wc,
+                                                     (float*)out, rows, cols, lda, ldb, ldc, ldo);
+  else if (!in_f32 && !out_f32)
+    lincomb3_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)a, (const bf16*)b, (const bf16*)c, wa, wb, wc,
+                                                   (bf16*)out, rows, cols, lda, ldb, ldc, ldo);
+  else if (in_f32)
+    lincomb3_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)a, (const float*)b, (const float*)c, wa, wb, wc,
+                                                    (bf16*)out, rows, cols, lda, ldb, ldc, ldo);
+  else
+    lincomb3_kernel<bf16, float><<<g, 256, 0, st>>>((const bf16*)a, (const bf16*)b, (const bf16*)c, wa, wb, wc,
+                                                    (float*)out, rows, cols, lda, ldb, ldc, ldo);
+  return k3m_check_launch("k3m_lincomb3");
+}
+
+extern "C" int k3m_axpy(const void* x, int ldx, int x_f32, void* y, int ldy, int y_f32, float alpha, int rows, int cols,
+                        void* stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int g = grid_for((size_t)rows * cols, 256);
+  if (x_f32 && y_f32) axpy_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, (float*)y, alpha, rows, cols, ldx, ldy);
+  else if (!x_f32 && !y_f32) axpy_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)x, (bf16*)y, alpha, rows, cols, ldx, ldy);
+  else if (x_f32) axpy_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)x, (bf16*)y, alpha, rows, cols, ldx, ldy);
+  else axpy_kernel<bf16, float><<<g, 256, 0, st>>>((const bf16*)x, (float*)y, alpha, rows, cols, ldx, ldy);
+  return k3m_check_launch("k3m_axpy");
+}
+
+extern "C" int k3m_scale(float* x, float alpha, long long n, void* stream) {
+  scale_kernel<<<grid_for((size_t)n, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(x, alpha, (size_t)n);
+  return k3m_check_launch("k3m_scale");
+}
+
+extern "C" int k3m_dgelu_mul(const void* dy, const void* pre, void* dx, long long n, void* stream) {
+  K3M_REQUIRE(n % 8 == 0, "dgelu_mul: n must be a multiple of 8");
+  dgelu_kernel<<<grid_for((size_t)n / 8, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      (const bf16*)dy, (const bf16*)pre, (bf16*)dx, (size_t)n / 8);
+  return k3m_check_launch("k3m_dgelu_mul");
+}
+
+extern "C" int k3m_mask_additive(const long long* mask, float* out, int n, void* stream) {
+  mask_additive_kernel<<<(n + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(mask, out, n);
+  return k3m_check_launch("k3m_mask_additive");
+}

@@ -1,0 +1,329 @@
+"""Op table over the C ABI: every method takes torch CUDA tensors, passes raw device pointers,
+strides and the current CUDA stream to libk3m_sm100a.so, and returns torch tensors that own the
+outputs.  torch is used for memory and streams only — no torch arithmetic runs here."""
+import ctypes
+
+import torch
+
+from . import _lib
+
+ACT_NONE, ACT_GELU, ACT_DGELU, ACT_SIGMOID, ACT_TANH, ACT_DTANH = 0, 1, 2, 3, 4, 5
+_LAYOUT = {"nt": 0, "nn": 1, "tn": 2}
+_c = ctypes
+_vp, _i, _f, _u, _ll = _c.c_void_p, _c.c_int, _c.c_float, _c.c_uint, _c.c_longlong
+
+
+def _p(t):
+    return _vp(t.data_ptr()) if t is not None else _vp(0)
+
+
+def _ld(t):
+    if t is None:
+        return 0
+    assert t.dim() == 2 and t.stride(1) == 1, "row-major 2-D tensor expected"
+    return t.stride(0)
+
+
+def _isf32(t):
+    if t.dtype == torch.float32:
+        return 1
+    assert t.dtype == torch.bfloat16, t.dtype
+    return 0
+
+
+class CudaOps(object):
+    def __init__(self, device=None):
+        if not torch.cuda.is_available():
+            raise _lib.K3MError("k3m_b200 needs a CUDA device (sm_100a); there is no CPU path")
+        self.lib = _lib.load()
+        self.adt = torch.bfloat16
+        self.device = torch.device(device if device is not None else "cuda")
+        self.launches = 0
+
+    def _st(self):
+        return _vp(torch.cuda.current_stream().cuda_stream)
+
+    def _call(self, name, *args):
+        self.launches += 1
+        _lib.check(getattr(self.lib, name)(*args), name)
+
+    def _drop(self, drop, rng):
+        if drop is None:
+            return _vp(0), _u(0), _f(0.0)
+        return _p(rng), _u(drop[1]), _f(drop[0])
+
+    # ---- GEMM ------------------------------------------------------------------------------
+    def gemm(self, a, b, layout, out=None, out_dtype=None, bias=None, act=ACT_NONE, aux_in=None,
+             aux_out=None, addend=None, drop=None, rng=None, accumulate=False):
+        assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+        if layout == "nt":
+            M, K = a.shape
+            N = b.shape[0]
+            assert b.shape[1] == K
+        elif layout == "nn":
+            M, K = a.shape
+            N = b.shape[1]
+            assert b.shape[0] == K
+        else:
+            K, M = a.shape
+            N = b.shape[1]
+            assert b.shape[0] == K
+        if out is None:
+            out = torch.empty(M, N, dtype=out_dtype or self.adt, device=a.device)
+            accumulate = False
+        assert tuple(out.shape) == (M, N)
+        r, s, p = self._drop(drop, rng)
+        self._call("k3m_gemm_bf16", _p(a), _i(_ld(a)), _p(b), _i(_ld(b)), _i(_LAYOUT[layout]),
+                   _i(M), _i(N), _i(K), _p(out), _i(_ld(out)), _i(_isf32(out)), _i(1 if accumulate else 0),
+                   _p(bias), _i(act), _p(aux_in), _i(_ld(aux_in)), _p(aux_out), _i(_ld(aux_out)),
+                   _p(addend), _i(_ld(addend)), _i(_isf32(addend) if addend is not None else 0),
+                   r, s, p, self._st())
+        return out
+
+    def colsum(self, x, out):
+        self._call("k3m_colsum", _p(x), _i(_ld(x)), _i(_isf32(x)), _p(out), _i(x.shape[0]), _i(x.shape[1]),
+                   self._st())
+
+    # ---- LayerNorm -------------------------------------------------------------------------
+    def ln_fwd(self, x, gamma, beta, out=None, drop=None, rng=None, eps=1e-12):
+        M, H = x.shape
+        assert x.is_contiguous()
+        if out is None:
+            out = torch.empty(M, H, dtype=self.adt, device=x.device)
+        assert out.is_contiguous()
+        mean = torch.empty(M, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(M, dtype=torch.float32, device=x.device)
+        r, s, p = self._drop(drop, rng)
+        self._call("k3m_ln_fwd", _p(x), _p(gamma), _p(beta), _p(out), _p(mean), _p(rstd), _i(M), _i(H),
+                   _f(eps), r, s, p, self._st())
+        return out, mean, rstd
+
+    def ln_bwd(self, dy, x, gamma, mean, rstd, dgamma, dbeta, drop_out=None, drop_in=None, rng=None,
+               dbias=None, want_masked=False):
+        M, H = x.shape
+        assert dy.is_contiguous() and x.is_contiguous()
+        dx = torch.empty(M, H, dtype=self.adt, device=x.device)
+        dxm = torch.empty(M, H, dtype=self.adt, device=x.device) if drop_in is not None else None
+        po = drop_out if drop_out is not None else (0.0, 0)
+        pi = drop_in if drop_in is not None else (0.0, 0)
+        self._call("k3m_ln_bwd", _p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dx), _p(dxm), _p(dgamma),
+                   _p(dbeta), _p(dbias), _i(M), _i(H), _p(rng), _u(po[1]), _f(po[0]), _u(pi[1]), _f(pi[0]),
+                   self._st())
+        return dx, (dxm if dxm is not None else dx)
+
+    # ---- attention -------------------------------------------------------------------------
+    def attn_fwd(self, qbuf, q_off, kvbuf, k_off, v_off, mask_add, B, H, Lq, Lk, d, drop=None, rng=None,
+                 out=None):
+        if out is None:
+            out = torch.empty(B * Lq, H * d, dtype=self.adt, device=qbuf.device)
+        lse = torch.empty(B * H * Lq, dtype=torch.float32, device=qbuf.device)
+        r, s, p = self._drop(drop, rng)
+        self._call("k3m_attn_fwd", _p(qbuf), _i(_ld(qbuf)), _i(q_off), _p(kvbuf), _i(_ld(kvbuf)), _i(k_off),
+                   _i(v_off), _p(mask_add), _i(B), _i(H), _i(Lq), _i(Lk), _i(d), _p(out), _i(_ld(out)),
+                   _p(lse), r, s, p, self._st())
+        return out, lse
+
+    def attn_bwd(self, dctx, ctx, qbuf, q_off, kvbuf, k_off, v_off, mask_add, lse, dqbuf, dkvbuf, B, H, Lq,
+                 Lk, d, drop=None, rng=None):
+        r, s, p = self._drop(drop, rng)
+        self._call("k3m_attn_bwd", _p(dctx), _i(_ld(dctx)), _p(qbuf), _i(_ld(qbuf)), _i(q_off), _p(kvbuf),
+                   _i(_ld(kvbuf)), _i(k_off), _i(v_off), _p(mask_add), _p(lse), _p(dqbuf), _i(_ld(dqbuf)),
+                   _p(dkvbuf), _i(_ld(dkvbuf)), _i(B), _i(H), _i(Lq), _i(Lk), _i(d), r, s, p, self._st())
+
+    # ---- embeddings ------------------------------------------------------------------------
+    def embed_fwd(self, ids, type_ids, word, pos, typ, L, out=None):
+        M, H = ids.numel(), word.shape[1]
+        if out is None:
+            out = torch.empty(M, H, dtype=self.adt, device=word.device)
+        self._call("k3m_embed_fwd", _p(ids), _p(type_ids), _p(word), _p(pos), _p(typ), _p(out), _i(M), _i(L),
+                   _i(H), self._st())
+        return out
+
+    def embed_bwd(self, dx, ids, type_ids, L, dword, dpos, dtyp):
+        M, H = dx.shape
+        self._call("k3m_embed_bwd", _p(dx), _p(ids), _p(type_ids), _p(dword), _p(dpos), _p(dtyp), _i(M), _i(L),
+                   _i(H), self._st())
+
+    def loc_embed_fwd(self, loc, w, b, out=None):
+        M, N = loc.shape[0], w.shape[0]
+        assert loc.dtype == torch.float32 and loc.shape[1] == 5 and loc.is_contiguous()
+        if out is None:
+            out = torch.empty(M, N, dtype=self.adt, device=loc.device)
+        self._call("k3m_loc_embed_fwd", _p(loc), _p(w), _p(b), _p(out), _i(M), _i(N), self._st())
+        return out
+
+    def loc_embed_bwd(self, dy, loc, dw, db):
+        M, N = dy.shape
+        assert dy.is_contiguous()
+        self._call("k3m_loc_embed_bwd", _p(dy), _p(loc), _p(dw), _p(db), _i(M), _i(N), self._st())
+
+    # ---- fusion ----------------------------------------------------------------------------
+    def relu_cat3(self, a, b, c, out=None):
+        M, H = a.shape
+        if out is None:
+            out = torch.empty(M, 3 * H, dtype=self.adt, device=a.device)
+        self._call("k3m_relu_cat3", _p(a), _i(_ld(a)), _p(b), _i(_ld(b)), _p(c), _i(_ld(c)), _p(out), _i(M),
+                   _i(H), self._st())
+        return out
+
+    def fuse_select_fwd(self, cat, gates, noise=None, site=0, rng=None, out=None):
+        M, H = cat.shape[0], cat.shape[1] // 3
+        assert gates.dtype == torch.float32 and gates.is_contiguous() and cat.is_contiguous()
+        if out is None:
+            out = torch.empty(M, H, dtype=self.adt, device=cat.device)
+        self._call("k3m_fuse_select_fwd", _p(cat), _p(gates), _p(noise), _p(rng), _u(site), _p(out),
+                   _i(_ld(out)), _i(M), _i(H), self._st())
+        return out
+
+    def fuse_select_bwd(self, dout, cat, gates, noise=None, site=0, rng=None):
+        M, H = cat.shape[0], cat.shape[1] // 3
+        dg = torch.empty(M, 3 * H, dtype=self.adt, device=cat.device)
+        dc = torch.empty(M, 3 * H, dtype=self.adt, device=cat.device)
+        self._call("k3m_fuse_select_bwd", _p(dout), _i(_ld(dout)), _p(cat), _p(gates), _p(noise), _p(rng),
+                   _u(site), _p(dg), _p(dc), _i(M), _i(H), self._st())
+        return dg, dc
+
+    def relu_bwd_split3(self, dcat, cat, da, db, dc):
+        M, H = da.shape
+        self._call("k3m_relu_bwd_split3", _p(dcat), _p(cat), _p(da), _i(_ld(da)), _p(db), _i(_ld(db)), _p(dc),
+                   _i(_ld(dc)), _i(M), _i(H), self._st())
+
+    def lincomb3(self, a, b, c, wa, wb, wc, out=None, out_dtype=None):
+        rows, cols = a.shape
+        if out is None:
+            out = torch.empty(rows, cols, dtype=out_dtype or a.dtype, device=a.device)
+        self._call("k3m_lincomb3", _p(a), _i(_ld(a)), _p(b), _i(_ld(b)), _p(c), _i(_ld(c)), _f(wa), _f(wb),
+                   _f(wc), _i(_isf32(a)), _p(out), _i(_ld(out)), _i(_isf32(out)), _i(rows), _i(cols), self._st())
+        return out
+
+    def axpy(self, x, y, alpha=1.0):
+        rows, cols = x.shape
+        self._call("k3m_axpy", _p(x), _i(_ld(x)), _i(_isf32(x)), _p(y), _i(_ld(y)), _i(_isf32(y)), _f(alpha),
+                   _i(rows), _i(cols), self._st())
+
+    def cast(self, x, dtype):
+        assert x.is_contiguous()
+        y = torch.empty(x.shape, dtype=dtype, device=x.device)
+        self._call("k3m_cast", _p(x), _i(_isf32(x)), _p(y), _i(_isf32(y)), _ll(x.numel()), self._st())
+        return y
+
+    def scale_(self, x, alpha):
+        assert x.dtype == torch.float32 and x.is_contiguous()
+        self._call("k3m_scale", _p(x), _f(alpha), _ll(x.numel()), self._st())
+
+    def act_bwd(self, dy, pre, act):
+        assert act == ACT_DGELU and dy.is_contiguous() and pre.is_contiguous()
+        dx = torch.empty_like(dy)
+        self._call("k3m_dgelu_mul", _p(dy), _p(pre), _p(dx), _ll(dy.numel()), self._st())
+        return dx
+
+    def mask_additive(self, mask):
+        assert mask.dtype == torch.int64 and mask.is_contiguous()
+        out = torch.empty(mask.shape, dtype=torch.float32, device=mask.device)
+        self._call("k3m_mask_additive", _p(mask), _p(out), _i(mask.numel()), self._st())
+        return out
+
+    # ---- pooling ---------------------------------------------------------------------------
+    def mean_pool_fwd(self, seq, B, L, out_dtype=torch.float32):
+        H = seq.shape[1]
+        out = torch.empty(B, H, dtype=out_dtype, device=seq.device)
+        self._call("k3m_mean_pool_fwd", _p(seq), _i(_ld(seq)), _p(out), _i(_isf32(out)), _i(B), _i(L), _i(H),
+                   self._st())
+        return out
+
+    def mean_pool_bwd(self, dpool, dseq, B, L):
+        assert dpool.dtype == torch.float32 and dpool.is_contiguous()
+        self._call("k3m_mean_pool_bwd", _p(dpool), _p(dseq), _i(_ld(dseq)), _i(B), _i(L), _i(dseq.shape[1]),
+                   self._st())
+
+    # ---- structure aggregator + LPM ----------------------------------------------------------
+    def pair_gather_fwd(self, c_init, seq, pair_item, pair_rows):
+        P, H = pair_item.numel(), c_init.shape[1]
+        X = torch.empty(P, 3 * H, dtype=self.adt, device=seq.device)
+        PV = torch.empty(P, 2 * H, dtype=torch.float32, device=seq.device)
+        self._call("k3m_pair_gather_fwd", _p(c_init), _p(seq), _i(_ld(seq)), _p(pair_item), _p(pair_rows), _p(X),
+                   _p(PV), _i(P), _i(H), self._st())
+        return X, PV
+
+    def pair_gather_bwd(self, dx, dpv, pair_item, pair_rows, dc_init, dseq):
+        P, H = pair_item.numel(), dc_init.shape[1]
+        scratch = torch.zeros(dseq.shape[0], H, dtype=torch.float32, device=dseq.device)
+        self._call("k3m_pair_gather_bwd", _p(dx), _p(dpv), _p(pair_item), _p(pair_rows), _p(dc_init), _p(scratch),
+                   _i(P), _i(H), self._st())
+        self.axpy(scratch, dseq, 1.0)
+
+    def struct_attn_fwd(self, t, w2, b2, seg):
+        B, H = seg.shape[0], t.shape[1]
+        maxn = self._maxn(seg)
+        s = torch.empty(B, H, dtype=torch.float32, device=t.device)
+        att = torch.zeros(B, maxn, dtype=torch.float32, device=t.device)
+        self._call("k3m_struct_attn_fwd", _p(t), _p(w2), _p(b2), _p(seg), _p(s), _p(att), _i(B), _i(maxn), _i(H),
+                   self._st())
+        return s, att
+
+    def _maxn(self, seg):
+        n = getattr(seg, "_k3m_maxn", None)
+        if n is None:
+            raise _lib.K3MError("struct plan tensors must come from CudaOps.plan_to_device")
+        return n
+
+    def plan_to_device(self, plan, device):
+        """numpy plan (struct_plan.build_struct_plan) -> device int32 tensors; the longest pair range
+        is recorded on the host so no device->host sync is needed later."""
+        out = {}
+        for k, v in plan.items():
+            out[k] = torch.from_numpy(v).to(device, non_blocking=True)
+        seg = plan["seg"]
+        out["seg"]._k3m_maxn = int((seg[:, 1] - seg[:, 0]).max())
+        return out
+
+    def struct_attn_bwd(self, ds, t, att, w2, seg, dt, dw2, db2):
+        B, H = seg.shape[0], t.shape[1]
+        self._call("k3m_struct_attn_bwd", _p(ds), _p(t), _p(att), _p(w2), _p(seg), _p(dt), _p(dw2), _p(db2),
+                   _i(B), _i(att.shape[1]), _i(H), self._st())
+
+    def lpm_fwd_bwd(self, c_final, pv, terms, margin, dc_final, dpv):
+        loss = torch.zeros(1, dtype=torch.float32, device=c_final.device)
+        self._call("k3m_lpm_fwd_bwd", _p(c_final), _p(pv), _p(terms), _i(terms.shape[0]), _i(c_final.shape[1]),
+                   _f(margin), _p(loss), _p(dc_final), _p(dpv), self._st())
+        return loss
+
+    # ---- losses ----------------------------------------------------------------------------
+    def count_valid(self, labels, ignore):
+        out = torch.empty(1, dtype=torch.float32, device=labels.device)
+        self._call("k3m_count_labels", _p(labels), _i(labels.numel()), _ll(ignore), _i(0), _p(out), self._st())
+        return out
+
+    def count_eq(self, labels, value):
+        out = torch.empty(1, dtype=torch.float32, device=labels.device)
+        self._call("k3m_count_labels", _p(labels), _i(labels.numel()), _ll(value), _i(1), _p(out), self._st())
+        return out
+
+    def xent_fwd_bwd(self, logits, labels, count, n_cols, dlogits=None, grad_scale=1.0):
+        assert dlogits is None or dlogits.data_ptr() == logits.data_ptr(), "gradient is written in place"
+        loss = torch.zeros(1, dtype=torch.float32, device=logits.device)
+        self._call("k3m_xent_fwd_bwd", _p(logits), _i(_ld(logits)), _p(labels), _p(count), _i(logits.shape[0]),
+                   _i(n_cols), _f(grad_scale), _p(loss), _i(1 if dlogits is not None else 0), self._st())
+        return loss
+
+    def kl_fwd_bwd(self, logits, target, image_label, count, n_cols, Lv1, dlogits=None, grad_scale=1.0):
+        assert logits.dtype == torch.float32 and target.dtype == torch.float32 and target.is_contiguous()
+        assert dlogits is None or _ld(dlogits) == _ld(logits)
+        loss = torch.zeros(1, dtype=torch.float32, device=logits.device)
+        self._call("k3m_kl_fwd_bwd", _p(logits), _i(_ld(logits)), _p(target), _p(image_label), _p(count),
+                   _i(logits.shape[0] // Lv1), _i(Lv1), _i(n_cols), _f(grad_scale), _p(loss), _p(dlogits),
+                   self._st())
+        return loss
+
+    def itm_loss(self, pool_t, pool_pv, pool_v, w, b, l1, l2, l3, drop=None, rng=None):
+        B, H = pool_t.shape
+        loss = torch.zeros(1, dtype=torch.float32, device=pool_t.device)
+        r, s, p = self._drop(drop, rng)
+        self._call("k3m_itm_loss", _p(pool_t), _p(pool_pv), _p(pool_v), _p(w), _p(b), _p(l1), _p(l2), _p(l3),
+                   _i(B), _i(H), r, s, p, _p(loss), self._st())
+        return loss
+
+    # ---- optimizer -------------------------------------------------------------------------
+    def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True):
+        self._call("k3m_adamw", _p(p32), _p(g32), _p(m), _p(v), _p(p_act), _p(hyper), _ll(p32.numel()),
+                   _i(1 if zero_grad else 0), self._st())

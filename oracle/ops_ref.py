@@ -470,10 +470,13 @@ class RefOps(object):
         return torch.nn.functional.cross_entropy(lg, labels, ignore_index=-1).reshape(1)
 
     # ---- optimizer -------------------------------------------------------------------------
-    def adamw(self, p32, g32, m, v, p_act, hyper, grad_scale=1.0, zero_grad=True):
-        """torch.optim.AdamW step on a flat range.  hyper fp32 [6] = (lr, beta1, beta2, eps, wd,
-        step).  Writes the act-dtype shadow copy and (optionally) zeroes the gradient."""
-        lr, b1, b2, eps, wd, step = [float(x) for x in hyper[:6]]
+    def plan_to_device(self, plan, device):
+        return {k: torch.from_numpy(v).to(device) for k, v in plan.items()}
+
+    def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True):
+        """torch.optim.AdamW step on a flat range.  hyper fp32 [8] = (lr, beta1, beta2, eps, wd,
+        step, grad_scale, -).  Writes the act-dtype shadow copy and (optionally) zeroes the grad."""
+        lr, b1, b2, eps, wd, step, grad_scale = [float(x) for x in hyper[:7]]
         g = g32 * grad_scale
         p32.mul_(1.0 - lr * wd)
         m.mul_(b1).add_(g, alpha=1.0 - b1)

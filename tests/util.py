@@ -1,0 +1,105 @@
+"""Shared helpers for the parity tests."""
+import os
+import random
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+from k3m_b200.config import BertConfig  # noqa: E402
+from k3m_b200.engine import Engine  # noqa: E402
+from k3m_b200.layout import ArenaLayout, param_spec  # noqa: E402
+from k3m_b200.struct_plan import build_struct_plan  # noqa: E402
+from k3m_b200.synth import synth_batch, synth_state_dict  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def load_golden(name):
+    return torch.load(os.path.join(GOLDEN, name + ".pt"), weights_only=False)
+
+
+def sample_index(numel, k=16):
+    g = torch.Generator().manual_seed(numel)
+    return torch.randint(0, numel, (k,), generator=g)
+
+
+def make_noise(cfg, B, Lt, Lv1, Lpv, seed):
+    g = torch.Generator().manual_seed(seed)
+    out = {}
+    for m, (L, H) in (("v", (Lv1, cfg.bi_hidden_size)), ("t", (Lt, cfg.hidden_size)), ("pv", (Lpv, cfg.hidden_size))):
+        out[m] = -torch.empty(B, L, 3, H).exponential_(generator=g).log()
+    return out
+
+
+def case_setup(fx):
+    """fixture -> (cfg, state_dict, batch, noise or None)"""
+    cfg = BertConfig.from_dict(fx["config"])
+    for k, v in fx["overrides"].items():
+        setattr(cfg, k, v)
+    B, Lt, Lv, Lpv, mpv = fx["dims"]
+    sd = synth_state_dict(param_spec(cfg), seed=fx["seeds"]["weights"])
+    batch = synth_batch(cfg, B, Lt, Lv, Lpv, max_num_pv=mpv, seed=fx["seeds"]["batch"])
+    noise = make_noise(cfg, B, Lt, Lv + 1, Lpv, fx["seeds"]["noise"]) if cfg.if_pre_sampling == 1 else None
+    return cfg, sd, batch, noise
+
+
+def run_engine(cfg, sd, batch, noise, ops, device, adt, py_seed, training=False):
+    """One forward+backward of the engine; returns (outputs dict, layout, fp32 grad arena)."""
+    L = ArenaLayout(cfg)
+    w32 = torch.zeros(L.total)
+    for n, (off, num, _) in L.offsets.items():
+        w32[off:off + num] = sd[n].reshape(-1)
+    w = w32.to(device=device, dtype=adt)
+    g = torch.zeros(L.total, dtype=torch.float32, device=device)
+    rng = torch.tensor([1234, 0], dtype=torch.int64, device=device)
+    eng = Engine(cfg, L, ops, w, g, rng, adt)
+    eng.training = training
+    random.seed(py_seed)
+    plan = build_struct_plan(batch["index_p"].numpy(), batch["index_v"].numpy(), batch["input_ids_pv"].shape[1],
+                             cfg.num_negative_pv)
+    plan = ops.plan_to_device(plan, device)
+    b = {k: v.to(device) for k, v in batch.items()}
+    en = None
+    if noise is not None:
+        en = {m: x.reshape(-1, 3, x.shape[-1]).contiguous().to(device) for m, x in noise.items()}
+    out = eng.forward(b, plan, en)
+    eng.backward()
+    return out, L, g
+
+
+def compare_with_golden(fx, out, L, g, loss_rtol, grad_tol, key_bias_atol=None):
+    """losses: relative; gradients: |norm - ref| / ref and sampled elements vs the tensor's max-abs."""
+    errs = []
+    for k, ref in fx["losses"].items():
+        got = float(out[k].reshape(-1)[0])
+        if abs(got - ref) > loss_rtol * max(abs(ref), 1e-6):
+            errs.append("%s: got %.6f want %.6f" % (k, got, ref))
+    for k in ("c_initial", "c_final"):
+        ref = fx[k]
+        got = out[k].float().cpu()
+        e = float((got - ref).abs().max()) / (float(ref.abs().max()) + 1e-12)
+        if e > max(grad_tol, 10 * loss_rtol):
+            errs.append("%s: rel err %.3e" % (k, e))
+    gc = g.cpu()
+    worst = 0.0
+    for n, (off, num, shape) in L.offsets.items():
+        ref = fx["grads"][n]
+        got = gc[off:off + num]
+        if ref is None:
+            if float(got.abs().max()) != 0.0:
+                errs.append("%s: reference has no gradient, got max %.3e" % (n, float(got.abs().max())))
+            continue
+        scale = ref["maxabs"]
+        if scale < 1e-7:      # key biases / struc_w2.bias: mathematically zero gradients
+            if float(got.abs().max()) > (key_bias_atol or 1e-5):
+                errs.append("%s: expected ~0 gradient, got %.3e" % (n, float(got.abs().max())))
+            continue
+        e1 = abs(float(got.norm()) - ref["norm"]) / ref["norm"]
+        e2 = float((got[sample_index(num)] - ref["sample"]).abs().max()) / scale
+        worst = max(worst, e1, e2)
+        if e1 > grad_tol or e2 > grad_tol:
+            errs.append("%s: norm err %.3e sample err %.3e" % (n, e1, e2))
+    return errs, worst

@@ -1,0 +1,104 @@
+"""Generates tests/golden/*.pt by running the UNMODIFIED reference model
+(/root/reference/vilbert_k3m/vilbert_k3m.py, imported through oracle/ref_harness.py) in fp32 on
+CPU, deterministic mode (eval -> dropout off, Gumbel noise injected by patching
+torch.nn.functional.gumbel_softmax in THIS process, random.seed before the forward for the LPM
+negatives).  Only works in the build container; the fixtures are committed.
+
+Each fixture holds: config dict + driver overrides, the seeds that regenerate weights
+(`synth_state_dict`) and inputs (`synth_batch`), the Gumbel noise, the five losses, c_initial /
+c_final, and for every parameter the gradient's L2 norm, max-abs and 16 sampled elements.
+"""
+import os
+import random
+import sys
+
+import torch
+import torch.nn.functional as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from k3m_b200.config import BertConfig, K3M_BASE_6LAYER_6CONNECT, K3M_TINY  # noqa: E402
+from k3m_b200.layout import param_spec  # noqa: E402
+from k3m_b200.synth import FORWARD_ORDER, synth_batch, synth_state_dict  # noqa: E402
+from oracle import ref_harness  # noqa: E402
+
+CASES = {
+    # name: (config, overrides, B, Lt, Lv, Lpv, max_num_pv, weight seed, batch seed, noise seed, py seed)
+    "tiny_hard": (K3M_TINY, dict(if_pre_sampling=1, margin=10.0, num_negative_pv=4), 4, 12, 9, 20, 4, 1, 7, 5, 3),
+    "tiny_mean": (K3M_TINY, dict(if_pre_sampling=0, margin=1.0, num_negative_pv=4), 3, 16, 8, 24, 5, 2, 8, 0, 4),
+    "tiny_inter": (K3M_TINY, dict(if_pre_sampling=3, margin=10.0, num_negative_pv=2), 5, 8, 12, 16, 3, 3, 9, 0, 5),
+    "base_hard": (K3M_BASE_6LAYER_6CONNECT, dict(if_pre_sampling=1, margin=10.0, num_negative_pv=4),
+                  4, 36, 36, 36, 8, 1, 7, 5, 3),
+}
+
+
+def sample_index(numel, k=16):
+    g = torch.Generator().manual_seed(numel)
+    return torch.randint(0, numel, (k,), generator=g)
+
+
+def make_noise(cfg, B, Lt, Lv1, Lpv, seed):
+    g = torch.Generator().manual_seed(seed)
+    out = {}
+    for m, (L, H) in (("v", (Lv1, cfg.bi_hidden_size)), ("t", (Lt, cfg.hidden_size)), ("pv", (Lpv, cfg.hidden_size))):
+        out[m] = -torch.empty(B, L, 3, H).exponential_(generator=g).log()
+    return out
+
+
+def run_case(name):
+    d, ov, B, Lt, Lv, Lpv, mpv, wseed, bseed, nseed, pyseed = CASES[name]
+    ref, rcfg, model = ref_harness.make_reference_model(d, ov)
+    cfg = BertConfig.from_dict(d)
+    for k, v in ov.items():
+        setattr(cfg, k, v)
+    sd = synth_state_dict(param_spec(cfg), seed=wseed)
+    full = dict(sd)
+    full["cls.predictions.decoder.weight"] = sd["embeddings.word_embeddings.weight"]
+    model.load_state_dict(full)
+    model.tie_weights()
+    model.eval()
+    batch = synth_batch(cfg, B, Lt, Lv, Lpv, max_num_pv=mpv, seed=bseed)
+    noise = make_noise(cfg, B, Lt, Lv + 1, Lpv, nseed) if cfg.if_pre_sampling == 1 else None
+    orig = F.gumbel_softmax
+    if noise is not None:
+        order = iter(["v", "t", "pv"])   # call order in get_sequence_pooled_output_final (:2387-2392)
+
+        def patched(logits, tau=1, hard=False, eps=1e-10, dim=-1):
+            y = ((logits + noise[next(order)]) / tau).softmax(dim)
+            idx = y.max(dim, keepdim=True)[1]
+            yh = torch.zeros_like(logits).scatter_(dim, idx, 1.0)
+            return yh - y.detach() + y
+        F.gumbel_softmax = patched
+    random.seed(pyseed)
+    out = model(*[batch[k] for k in FORWARD_ORDER], input_ids_pv=batch["input_ids_pv"],
+                token_type_ids_pv=batch["token_type_ids_pv"], attention_mask_pv=batch["attention_mask_pv"],
+                masked_lm_labels_pv=batch["masked_lm_labels_pv"],
+                next_sentence_label_pv_v=batch["next_sentence_label_pv_v"],
+                next_sentence_label_pv_t=batch["next_sentence_label_pv_t"],
+                index_p=batch["index_p"], index_v=batch["index_v"], device="cpu")
+    F.gumbel_softmax = orig
+    (out[0] + out[1] + out[3] + out[9]).backward()      # pretrain.py:1055
+    grads = {}
+    for n, p in model.named_parameters():
+        if p.grad is None:
+            grads[n] = None
+            continue
+        g = p.grad.reshape(-1)
+        grads[n] = dict(norm=float(g.norm()), maxabs=float(g.abs().max()), sample=g[sample_index(g.numel())].clone())
+    fx = dict(case=name, config=d, overrides=ov, dims=(B, Lt, Lv, Lpv, mpv),
+              seeds=dict(weights=wseed, batch=bseed, noise=nseed, python=pyseed),
+              noise=noise,
+              losses=dict(loss_t=float(out[0]), loss_v=float(out[1]), loss_pv=float(out[3]),
+                          loss_itm=float(out[6]), loss_lpm=float(out[9])),
+              c_initial=out[7].detach().clone(), c_final=out[8].detach().clone(), grads=grads)
+    if noise is not None:
+        fx["noise"] = None   # regenerated from the seed by make_noise (keeps the fixture small)
+    path = os.path.join(ROOT, "tests", "golden", name + ".pt")
+    torch.save(fx, path)
+    print(name, fx["losses"], os.path.getsize(path))
+
+
+if __name__ == "__main__":
+    for n in (sys.argv[1:] or CASES):
+        run_case(n)
