@@ -53,9 +53,13 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// Bounded: a protocol bug must surface as a trapped launch (error code at the next API call), never
+// as a kernel that spins until the box's watchdog fires.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t done;
+  uint32_t spins = 0;
   do {
+    if (++spins > (1u << 26)) __trap();
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"

@@ -1,0 +1,500 @@
+"""GPU: every entry point of libk3m_sm100a.so (through k3m_b200.ops.CudaOps -> the C ABI) against
+the PyTorch restatement of its contract (oracle/ops_ref.py) on the same seeded inputs.
+
+Tolerances: integer / index work (gathers, masks, counts, dropout keep-masks) is bit-exact;
+bf16 outputs are compared to the fp32 result rounded to bf16 with a few ulp of slack; fp32
+outputs (statistics, losses, parameter gradients) to 1e-4 relative unless stated."""
+import math
+
+import pytest
+import torch
+
+from oracle.ops_ref import RefOps, dropout_keep
+
+pytestmark = pytest.mark.gpu
+BF, F32 = torch.bfloat16, torch.float32
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from k3m_b200.ops import CudaOps
+    return CudaOps(DEV)
+
+
+@pytest.fixture(scope="module")
+def ref():
+    return RefOps(F32)
+
+
+def rnd(*shape, seed=0, scale=1.0, dtype=BF):
+    g = torch.Generator().manual_seed(seed + 7919 * len(shape) + sum(shape))
+    return (torch.randn(*shape, generator=g) * scale).to(dtype).to(DEV)
+
+
+def close(got, want, rtol, atol, what=""):
+    got, want = got.float(), want.float()
+    err = (got - want).abs()
+    tol = atol + rtol * want.abs()
+    bad = err > tol
+    assert not bool(bad.any()), "%s: %d/%d bad, max err %.4e (want max %.4e)" % (
+        what, int(bad.sum()), bad.numel(), float(err.max()), float(want.abs().max()))
+
+
+def close_bf16(got, want, what="", ulps=2.0, atol=1e-6):
+    close(got, want, ulps * 2.0 ** -8, atol, what)
+
+
+RNG = None
+
+
+def rng_state():
+    return torch.tensor([0x1234ABCD5678, 3], dtype=torch.int64, device=DEV)
+
+
+# ---- GEMM ----------------------------------------------------------------------------------------
+GEMM_SHAPES = [(128, 128, 64), (256, 768, 768), (2304, 768, 3072), (300, 200, 136), (37, 1601, 1024),
+               (2368, 1024, 2048), (64, 2, 768), (1, 768, 768), (130, 64, 8), (4608, 2304, 768)]
+
+
+@pytest.mark.parametrize("layout", ["nt", "nn", "tn"])
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_plain(ops, ref, layout, M, N, K):
+    if layout != "nt" and (N % 8 or M % 8):
+        Np, Mp = (N + 7) // 8 * 8, (M + 7) // 8 * 8
+    else:
+        Np, Mp = N, M
+    s = 1.0 / math.sqrt(K)
+    if layout == "nt":
+        a, b = rnd(M, K), rnd(N, K, seed=1, scale=s)
+    elif layout == "nn":
+        a, b = rnd(M, K), rnd(K, Np, seed=1, scale=s)[:, :N]
+    else:
+        a, b = rnd(K, Mp)[:, :M], rnd(K, Np, seed=1, scale=s)[:, :N]
+    got = ops.gemm(a, b, layout, out_dtype=F32)
+    want = ref.gemm(a, b, layout, out_dtype=F32)
+    close(got, want, 1e-4, 2e-4 * math.sqrt(K) * s * 4, "gemm %s" % layout)
+    got16 = ops.gemm(a, b, layout)
+    close_bf16(got16, want, "gemm bf16 %s" % layout, atol=1e-3)
+
+
+@pytest.mark.parametrize("act", [0, 1, 3, 4])
+def test_gemm_epilogue_bias_act_addend(ops, ref, act):
+    M, N, K = 300, 776, 264
+    a, w = rnd(M, K), rnd(N, K, seed=1, scale=0.06)
+    bias, add = rnd(N, seed=2), rnd(M, N, seed=3)
+    aux_g = torch.zeros(M, N, dtype=BF, device=DEV)
+    aux_r = torch.zeros(M, N, dtype=F32, device=DEV)
+    got = ops.gemm(a, w, "nt", bias=bias, act=act, aux_out=aux_g if act == 1 else None, addend=add)
+    want = ref.gemm(a, w, "nt", bias=bias, act=act, aux_out=aux_r if act == 1 else None, addend=add)
+    close_bf16(got, want, "epilogue act=%d" % act, atol=2e-3)
+    if act == 1:
+        close_bf16(aux_g, aux_r, "aux_out", atol=2e-3)
+
+
+@pytest.mark.parametrize("act", [2, 5])
+def test_gemm_epilogue_derivative(ops, ref, act):
+    M, N, K = 260, 384, 200
+    a, w = rnd(M, K), rnd(K, N, seed=1, scale=0.07)
+    aux = rnd(M, N, seed=4, scale=0.8 if act == 5 else 1.5)
+    add = rnd(M, N, seed=5, dtype=F32)
+    got = ops.gemm(a, w, "nn", act=act, aux_in=aux, addend=add, out_dtype=F32)
+    want = ref.gemm(a, w, "nn", act=act, aux_in=aux, addend=add, out_dtype=F32)
+    close(got, want, 1e-4, 1e-4, "derivative epilogue")
+
+
+def test_gemm_dropout_mask_bit_exact(ops, ref):
+    M, N, K = 200, 328, 128
+    a, w = rnd(M, K), rnd(N, K, seed=1, scale=0.1)
+    r = rng_state()
+    got = ops.gemm(a, w, "nt", drop=(0.1, 17), rng=r, out_dtype=F32)
+    plain = ops.gemm(a, w, "nt", out_dtype=F32)
+    keep = dropout_keep(r, 17, M, N, 0.1)
+    nz = plain != 0
+    assert torch.equal((got != 0) & nz, keep & nz)          # the keep mask itself: bit-exact
+    close(got, torch.where(keep, plain / 0.9, torch.zeros_like(plain)), 1e-5, 1e-6, "dropout scale")
+    frac = float(keep.float().mean())
+    assert 0.88 < frac < 0.92
+
+
+def test_gemm_accumulate_split_k(ops, ref):
+    # weight-gradient shape: small M,N, long K -> split-K with fp32 atomics onto a non-zero output
+    K, M, N = 4608, 768, 776
+    a, b = rnd(K, M, scale=0.05), rnd(K, N, seed=1, scale=0.05)[:, :770]
+    base = rnd(M, 770, seed=2, dtype=F32)
+    got, want = base.clone(), base.clone()
+    ops.gemm(a, b, "tn", out=got, accumulate=True)
+    ref.gemm(a, b, "tn", out=want, accumulate=True)
+    close(got, want, 1e-4, 1e-4, "split-K accumulate")
+
+
+def test_gemm_strided_views(ops, ref):
+    # operands / outputs that are column slices of wider buffers (qkv, logits[:, :V])
+    M, K, N = 192, 256, 200
+    A = rnd(M, 3 * K)
+    a = A[:, K:2 * K]
+    w = rnd(N, K, seed=1, scale=0.06)
+    out_g = torch.full((M, 208), 7.0, dtype=BF, device=DEV)
+    out_r = torch.full((M, 208), 7.0, dtype=F32, device=DEV)
+    ops.gemm(a, w, "nt", out=out_g[:, :N])
+    ref.gemm(a, w, "nt", out=out_r[:, :N])
+    close_bf16(out_g, out_r, "strided", atol=1e-3)
+    assert bool((out_g[:, N:] == 7.0).all())
+
+
+def test_gemm_rejects_bad_arguments(ops):
+    from k3m_b200._lib import K3MError
+    a, w = rnd(64, 68), rnd(64, 68, seed=1)
+    with pytest.raises(K3MError):
+        ops.gemm(a[:, :60][:, 1:], w[:, 1:60], "nt")       # misaligned base pointer
+    with pytest.raises(K3MError):
+        ops.gemm(rnd(64, 64), rnd(64, 64), "nt", out=torch.zeros(64, 64, dtype=BF, device=DEV), accumulate=True)
+
+
+# ---- LayerNorm -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,H", [(2304, 768), (2368, 1024), (37, 64), (1, 768)])
+@pytest.mark.parametrize("drop", [None, (0.1, 5)])
+def test_ln_fwd(ops, ref, M, H, drop):
+    x, g, b = rnd(M, H, scale=2.0), rnd(H, seed=1), rnd(H, seed=2)
+    r = rng_state()
+    y, mean, rstd = ops.ln_fwd(x, g, b, drop=drop, rng=r)
+    yr, mr, rr = ref.ln_fwd(x, g, b, drop=drop, rng=r)
+    close(mean, mr, 1e-5, 1e-5, "mean")
+    close(rstd, rr, 1e-4, 1e-6, "rstd")
+    close_bf16(y, yr, "ln y", atol=1e-3)
+    if drop is not None:
+        assert torch.equal(y == 0, (yr == 0) | (y == 0) & (yr.abs() < 1e-3))
+
+
+@pytest.mark.parametrize("M,H", [(2304, 768), (2368, 1024), (37, 64)])
+@pytest.mark.parametrize("mode", ["plain", "drop_in", "drop_out"])
+def test_ln_bwd(ops, ref, M, H, mode):
+    x, g, dy = rnd(M, H, scale=2.0), rnd(H, seed=1), rnd(M, H, seed=3)
+    r = rng_state()
+    _, mean, rstd = ref.ln_fwd(x, g, g)
+    kw = dict(drop_in=(0.1, 9)) if mode == "drop_in" else dict(drop_out=(0.1, 9), want_masked=True) if mode == "drop_out" else {}
+    res = []
+    for o in (ops, ref):
+        dg = torch.zeros(H, dtype=F32, device=DEV) + 1.0
+        db = torch.zeros(H, dtype=F32, device=DEV) - 2.0
+        dbias = torch.zeros(H, dtype=F32, device=DEV) + 0.5
+        dx, dxm = o.ln_bwd(dy, x, g, mean, rstd, dg, db, rng=r, dbias=dbias, **kw)
+        res.append((dx, dxm, dg, db, dbias))
+    (dx, dxm, dg, db, dbias), (dxr, dxmr, dgr, dbr, dbiasr) = res
+    close_bf16(dx, dxr, "dx", atol=2e-3, ulps=3)
+    close_bf16(dxm, dxmr, "dxm", atol=2e-3, ulps=3)
+    s = math.sqrt(M)
+    close(dg, dgr, 2e-3, 2e-3 * s, "dgamma")
+    close(db, dbr, 2e-3, 2e-3 * s, "dbeta")
+    close(dbias, dbiasr, 2e-2, 2e-2 * s, "dbias")   # sums of bf16-rounded dx in the ref vs fp32 in the kernel
+
+
+def test_colsum_cast_axpy_lincomb_scale_mask(ops, ref):
+    x = rnd(2304, 776)[:, :770]
+    o1, o2 = torch.ones(770, dtype=F32, device=DEV), torch.ones(770, dtype=F32, device=DEV)
+    ops.colsum(x, o1)
+    ref.colsum(x, o2)
+    close(o1, o2, 1e-4, 1e-3, "colsum bf16")
+    xf = rnd(100, 2304, dtype=F32)
+    o1, o2 = torch.zeros(2304, dtype=F32, device=DEV), torch.zeros(2304, dtype=F32, device=DEV)
+    ops.colsum(xf, o1)
+    ref.colsum(xf, o2)
+    close(o1, o2, 1e-5, 1e-4, "colsum f32")
+    assert torch.equal(ops.cast(xf, BF), xf.to(BF))
+    assert torch.equal(ops.cast(xf.to(BF), F32), xf.to(BF).float())
+    a, b, c = rnd(64, 768), rnd(64, 768, seed=1), rnd(64, 768, seed=2)
+    close(ops.lincomb3(a, b, c, 1 / 3, 1 / 3, 1 / 3, out_dtype=F32), ref.lincomb3(a, b, c, 1 / 3, 1 / 3, 1 / 3, out_dtype=F32),
+          1e-6, 1e-6, "lincomb3")
+    close_bf16(ops.lincomb3(a, b, None, 0.5, 0.5, 0.0), ref.lincomb3(a, b, None, 0.5, 0.5, 0.0), "lincomb2")
+    y1 = rnd(64, 1536, seed=5)
+    y2 = y1.clone().float()
+    ops.axpy(a, y1[:, 768:], 0.25)
+    ref.axpy(a, y2[:, 768:], 0.25)
+    close_bf16(y1, y2, "axpy")
+    z = rnd(1000, dtype=F32)
+    z2 = z.clone()
+    ops.scale_(z, 1 / 3)
+    assert torch.allclose(z, z2 / 3, rtol=1e-6)
+    pre, dyy = rnd(128, 768, scale=1.5), rnd(128, 768, seed=1)
+    close_bf16(ops.act_bwd(dyy, pre, 2), ref.act_bwd(dyy, pre, 2), "dgelu", atol=1e-3)
+    mask = (torch.rand(64, 36) > 0.3).long().to(DEV)
+    assert torch.equal(ops.mask_additive(mask), ref.mask_additive(mask))
+
+
+# ---- attention -------------------------------------------------------------------------------------
+ATTN = [  # B, heads, Lq, Lk, d
+    (8, 12, 36, 36, 64), (8, 8, 37, 37, 128), (8, 8, 36, 37, 128), (8, 8, 37, 36, 128), (4, 8, 36, 36, 96),
+    (2, 12, 128, 128, 64), (2, 8, 101, 128, 128), (2, 8, 128, 101, 128), (3, 2, 5, 7, 16)]
+
+
+def _attn_inputs(B, H, Lq, Lk, d):
+    qbuf = rnd(B * Lq, 3 * H * d, scale=1.0)
+    kvbuf = rnd(B * Lk, 3 * H * d, seed=1, scale=1.0)
+    lens = torch.randint(max(1, Lk // 2), Lk + 1, (B,), generator=torch.Generator().manual_seed(B * Lk))
+    mask = (torch.arange(Lk)[None, :] < lens[:, None]).long().to(DEV)
+    return qbuf, kvbuf, (1.0 - mask.float()) * -10000.0
+
+
+@pytest.mark.parametrize("B,H,Lq,Lk,d", ATTN)
+@pytest.mark.parametrize("drop", [None, (0.1, 21)])
+def test_attn_fwd(ops, ref, B, H, Lq, Lk, d, drop):
+    qbuf, kvbuf, mask = _attn_inputs(B, H, Lq, Lk, d)
+    r = rng_state()
+    ctx, lse = ops.attn_fwd(qbuf, 0, kvbuf, H * d, 2 * H * d, mask, B, H, Lq, Lk, d, drop=drop, rng=r)
+    ctxr, lser = ref.attn_fwd(qbuf, 0, kvbuf, H * d, 2 * H * d, mask, B, H, Lq, Lk, d, drop=drop, rng=r)
+    close(lse, lser, 1e-5, 1e-4, "lse")
+    close_bf16(ctx, ctxr, "ctx", atol=2e-3)
+
+
+@pytest.mark.parametrize("B,H,Lq,Lk,d", ATTN)
+@pytest.mark.parametrize("drop", [None, (0.1, 21)])
+def test_attn_bwd(ops, ref, B, H, Lq, Lk, d, drop):
+    qbuf, kvbuf, mask = _attn_inputs(B, H, Lq, Lk, d)
+    r = rng_state()
+    dctx = rnd(B * Lq, H * d, seed=4)
+    ctxr, lser = ref.attn_fwd(qbuf, 0, kvbuf, H * d, 2 * H * d, mask, B, H, Lq, Lk, d, drop=drop, rng=r)
+    ctx = ctxr.to(BF)
+    W = 3 * H * d
+    dq_g, dkv_g = torch.zeros(B * Lq, W, dtype=BF, device=DEV), torch.zeros(B * Lk, W, dtype=BF, device=DEV)
+    dq_r, dkv_r = torch.zeros(B * Lq, W, dtype=F32, device=DEV), torch.zeros(B * Lk, W, dtype=F32, device=DEV)
+    ops.attn_bwd(dctx, ctx, qbuf, 0, kvbuf, H * d, 2 * H * d, mask, lser, dq_g, dkv_g, B, H, Lq, Lk, d, drop=drop, rng=r)
+    ref.attn_bwd(dctx, ctx, qbuf, 0, kvbuf, H * d, 2 * H * d, mask, lser, dq_r, dkv_r, B, H, Lq, Lk, d, drop=drop, rng=r)
+    sc = float(dq_r.abs().max())
+    close_bf16(dq_g, dq_r, "dq", atol=4e-3 * sc, ulps=3)
+    close_bf16(dkv_g, dkv_r, "dkv", atol=4e-3 * float(dkv_r.abs().max()), ulps=3)
+
+
+# ---- embeddings ------------------------------------------------------------------------------------
+def test_embed_fwd_bwd_bit_exact_gather(ops, ref):
+    V, L, H, B = 21128, 36, 768, 16
+    g = torch.Generator().manual_seed(5)
+    ids = torch.randint(0, V, (B * L,), generator=g)
+    ids[::7] = 0                       # padding rows
+    ids[1::9] = ids[1]                 # collisions in the scatter-add
+    ids, typ_ids = ids.to(DEV), torch.randint(0, 2, (B * L,), generator=g).to(DEV)
+    word, pos, typ = rnd(V, H, scale=0.02), rnd(512, H, seed=1, scale=0.02), rnd(2, H, seed=2, scale=0.02)
+    out = ops.embed_fwd(ids, typ_ids, word, pos, typ, L)
+    want = ref.embed_fwd(ids, typ_ids, word, pos, typ, L)
+    assert torch.equal(out, want.to(BF))          # fp32 sum of three bf16 rows, one rounding
+    dx = rnd(B * L, H, seed=3)
+    res = []
+    for o in (ops, ref):
+        dw, dp, dt = (torch.zeros(V, H, dtype=F32, device=DEV), torch.zeros(512, H, dtype=F32, device=DEV),
+                      torch.zeros(2, H, dtype=F32, device=DEV))
+        o.embed_bwd(dx, ids, typ_ids, L, dw, dp, dt)
+        res.append((dw, dp, dt))
+    assert float(res[0][0][0].abs().max()) == 0.0   # padding_idx row gets nothing from this path
+    for a, b, n in zip(res[0], res[1], ("dword", "dpos", "dtype")):
+        close(a, b, 1e-5, 1e-4, n)
+    assert torch.equal(res[0][0] != 0, res[1][0] != 0)
+
+
+def test_loc_embed(ops, ref):
+    M, N = 2368, 1024
+    loc = torch.rand(M, 5, generator=torch.Generator().manual_seed(1)).to(DEV)
+    w, b = rnd(N, 5), rnd(N, seed=1)
+    close_bf16(ops.loc_embed_fwd(loc, w, b), ref.loc_embed_fwd(loc, w, b), "loc fwd", atol=1e-3)
+    dy = rnd(M, N, seed=2)
+    res = []
+    for o in (ops, ref):
+        dw, db = torch.zeros(N, 5, dtype=F32, device=DEV), torch.zeros(N, dtype=F32, device=DEV)
+        o.loc_embed_bwd(dy, loc, dw, db)
+        res.append((dw, db))
+    close(res[0][0], res[1][0], 1e-4, 1e-3, "loc dw")
+    close(res[0][1], res[1][1], 1e-4, 1e-3, "loc db")
+
+
+# ---- fusion (hard Gumbel pick) ----------------------------------------------------------------------
+@pytest.mark.parametrize("use_noise", [True, False])
+def test_fuse_select(ops, ref, use_noise):
+    M, H = 333, 768
+    a, b, c = rnd(M, H), rnd(M, H, seed=1), rnd(M, H, seed=2)
+    cat = ops.relu_cat3(a, b, c)
+    assert torch.equal(cat, ref.relu_cat3(a, b, c).to(BF))
+    gates = rnd(M, 3 * H, seed=3, dtype=F32)
+    r = rng_state()
+    noise = None
+    if use_noise:
+        noise = -torch.empty(M, 3, H).exponential_(generator=torch.Generator().manual_seed(3)).log().to(DEV)
+    out = ops.fuse_select_fwd(cat, gates, noise=noise, site=4, rng=r)
+    want = ref.fuse_select_fwd(cat, gates, noise=noise, site=4, rng=r)
+    mism = (out.float() != want.to(BF).float())
+    # the pick is an argmax over fp32 values computed with slightly different exp/log: allow a
+    # vanishing fraction of near-ties with injected noise, a small one with on-device noise
+    assert float(mism.float().mean()) <= (1e-5 if use_noise else 2e-3), float(mism.float().mean())
+    dout = rnd(M, H, seed=5)
+    dg, dc = ops.fuse_select_bwd(dout, cat, gates, noise=noise, site=4, rng=r)
+    dgr, dcr = ref.fuse_select_bwd(dout, cat, gates, noise=noise, site=4, rng=r)
+    ok = ~mism
+    ok3 = torch.cat([ok, ok, ok], 1)
+    close_bf16(torch.where(ok3, dc.float(), 0 * dcr), torch.where(ok3, dcr, 0 * dcr), "dcat")
+    if use_noise:
+        close_bf16(dg, dgr, "dgates", atol=2e-3 * float(dgr.abs().max()), ulps=3)
+    d1 = [torch.zeros(M, H, dtype=BF, device=DEV) + 1 for _ in range(3)]
+    d2 = [torch.zeros(M, H, dtype=F32, device=DEV) + 1 for _ in range(3)]
+    ops.relu_bwd_split3(dcr.to(BF), cat, *d1)
+    ref.relu_bwd_split3(dcr.to(BF), cat, *d2)
+    for x, y in zip(d1, d2):
+        close_bf16(x, y, "relu split")
+
+
+def test_gumbel_noise_distribution(ops, ref):
+    """on-device noise path: selection frequencies with zero gates must be ~1/3 each"""
+    M, H = 512, 768
+    cat = torch.cat([torch.full((M, H), v, dtype=BF, device=DEV) for v in (1.0, 2.0, 3.0)], 1)
+    gates = torch.zeros(M, 3 * H, dtype=F32, device=DEV)
+    out = ops.fuse_select_fwd(cat, gates, site=9, rng=rng_state())
+    for v in (1.0, 2.0, 3.0):
+        assert abs(float((out == v).float().mean()) - 1 / 3) < 0.01
+
+
+def test_mean_pool(ops, ref):
+    B, L, H = 64, 37, 1024
+    seq = rnd(B * L, 2 * H)[:, H:]
+    close(ops.mean_pool_fwd(seq, B, L, F32), ref.mean_pool_fwd(seq, B, L, F32), 1e-5, 1e-5, "pool f32")
+    close_bf16(ops.mean_pool_fwd(seq, B, L, BF), ref.mean_pool_fwd(seq, B, L, F32), "pool bf16")
+    dp = rnd(B, H, seed=1, dtype=F32)
+    d1 = rnd(B * L, H, seed=2)
+    d2 = d1.clone().float()
+    ops.mean_pool_bwd(dp, d1, B, L)
+    ref.mean_pool_bwd(dp, d2, B, L)
+    close_bf16(d1, d2, "pool bwd")
+
+
+# ---- structure aggregator + LPM ------------------------------------------------------------------
+def _plan(B, L, mpv, seed):
+    import random
+    import numpy as np
+    from k3m_b200.struct_plan import build_struct_plan
+    rs = np.random.RandomState(seed)
+    ip = np.zeros((B, mpv, 2), dtype=np.int64)
+    iv = np.zeros((B, mpv, 2), dtype=np.int64)
+    for i in range(B):
+        n = rs.randint(1, mpv + 1)
+        for j in range(n):
+            p = np.sort(rs.choice(np.arange(1, L), 4, replace=False))
+            ip[i, j] = p[:2]
+            iv[i, j] = p[2:]
+    random.seed(seed)
+    return build_struct_plan(ip, iv, L, 4)
+
+
+def test_struct_aggregator_kernels(ops, ref):
+    B, L, H = 16, 36, 768
+    plan_np = _plan(B, L, 6, 3)
+    plan = ops.plan_to_device(plan_np, DEV)
+    c_init, seq = rnd(B, H, dtype=F32), rnd(B * L, H, seed=1)
+    X, PV = ops.pair_gather_fwd(c_init, seq, plan["pair_item"], plan["pair_rows"])
+    Xr, PVr = ref.pair_gather_fwd(c_init, seq, plan["pair_item"], plan["pair_rows"])
+    assert torch.equal(PV, PVr)                     # 2-row means of bf16 rows: exact in fp32
+    assert torch.equal(X, Xr.to(BF))
+    P = X.shape[0]
+    t = rnd(P, H, seed=2, dtype=F32)
+    w2, b2 = rnd(1, H, seed=3, scale=0.05), rnd(1, seed=4)
+    s, att = ops.struct_attn_fwd(t, w2, b2, plan["seg"])
+    sr, attr = ref.struct_attn_fwd(t, w2, b2, plan["seg"])
+    close(att, attr, 1e-4, 1e-6, "att")
+    close(s, sr, 1e-4, 1e-5, "s")
+    ds = rnd(B, H, seed=5, dtype=F32)
+    res = []
+    for o, a in ((ops, att), (ref, attr)):
+        dt = torch.zeros(P, H, dtype=F32, device=DEV)
+        dw2, db2 = torch.zeros(1, H, dtype=F32, device=DEV), torch.zeros(1, dtype=F32, device=DEV)
+        o.struct_attn_bwd(ds, t, a, w2, plan["seg"], dt, dw2, db2)
+        res.append((dt, dw2, db2))
+    for a, b, n in zip(res[0], res[1], ("dt", "dw2", "db2")):
+        close(a, b, 1e-3, 1e-4 * float(b.abs().max()) + 1e-5, n)
+    c_final = rnd(B, H, seed=6, dtype=F32)
+    res = []
+    for o in (ops, ref):
+        dc, dpv = torch.zeros(B, H, dtype=F32, device=DEV), torch.zeros(P, 2 * H, dtype=F32, device=DEV)
+        loss = o.lpm_fwd_bwd(c_final, PV, plan["terms"], 60.0, dc, dpv)
+        res.append((loss, dc, dpv))
+    assert float(res[1][0]) > 0
+    for a, b, n in zip(res[0], res[1], ("lpm loss", "dc_final", "dPV")):
+        close(a, b, 1e-4, 1e-6, n)
+    res = []
+    dX, dPV = rnd(P, 3 * H, seed=7, dtype=F32), rnd(P, 2 * H, seed=8, dtype=F32)
+    for o, dt_ in ((ops, BF), (ref, F32)):
+        dci = torch.zeros(B, H, dtype=F32, device=DEV)
+        dseq = torch.zeros(B * L, H, dtype=dt_, device=DEV)
+        o.pair_gather_bwd(dX, dPV, plan["pair_item"], plan["pair_rows"], dci, dseq)
+        res.append((dci, dseq))
+    close(res[0][0], res[1][0], 1e-5, 1e-5, "dc_init")
+    close_bf16(res[0][1], res[1][1], "dseq", atol=1e-3)
+
+
+# ---- losses ----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,V", [(512, 21128), (40, 1000), (3, 21128)])
+def test_xent(ops, ref, M, V):
+    ld = (V + 7) // 8 * 8
+    logits = rnd(M, ld, scale=2.0)
+    g = torch.Generator().manual_seed(M)
+    labels = torch.randint(0, V, (M,), generator=g)
+    labels[torch.rand(M, generator=g) > 0.2] = -1
+    labels[0] = V - 1
+    labels = labels.to(DEV)
+    cnt = ops.count_valid(labels, -1)
+    assert float(cnt) == float((labels != -1).sum())
+    assert float(ops.count_eq(labels, -1)) == float((labels == -1).sum())
+    dl_r = torch.zeros(M, ld, dtype=F32, device=DEV)
+    want = ref.xent_fwd_bwd(logits, labels, cnt, V, dlogits=dl_r, grad_scale=0.7)
+    lg = logits.clone()
+    got = ops.xent_fwd_bwd(lg, labels, cnt, V, dlogits=lg, grad_scale=0.7)
+    close(got, want, 1e-5, 1e-6, "xent loss")
+    close_bf16(lg, dl_r, "dlogits", atol=1e-6)
+    assert bool((lg[labels == -1] == 0).all())
+    lg2 = logits.clone()
+    got2 = ops.xent_fwd_bwd(lg2, labels, cnt, V)          # value only: logits untouched
+    assert torch.equal(lg2, logits) and float(got2) == float(got)
+
+
+def test_kl(ops, ref):
+    B, Lv1, T = 16, 37, 1601
+    ld = (T + 7) // 8 * 8
+    logits = rnd(B * Lv1, ld, dtype=F32, scale=2.0)
+    target = torch.softmax(rnd(B * (Lv1 - 1), T, dtype=F32, seed=1) * 3, 1)
+    target[5] = 0.0                                        # xlogy(0, 0) = 0
+    il = (torch.rand(B * (Lv1 - 1), generator=torch.Generator().manual_seed(2)) < 0.15).long() * 2 - 1
+    il = il.to(DEV)
+    il[5] = 1
+    cnt = ops.count_eq(il, 1)
+    dl_g = torch.full((B * Lv1, ld), 3.0, dtype=BF, device=DEV)
+    dl_r = torch.zeros(B * Lv1, ld, dtype=F32, device=DEV)
+    got = ops.kl_fwd_bwd(logits, target, il, cnt, T, Lv1, dlogits=dl_g, grad_scale=1.3)
+    want = ref.kl_fwd_bwd(logits, target, il, cnt, T, Lv1, dlogits=dl_r, grad_scale=1.3)
+    close(got, want, 1e-5, 1e-6, "kl loss")
+    close_bf16(dl_g, dl_r, "kl dlogits", atol=1e-7)
+
+
+def test_itm(ops, ref):
+    B, H = 64, 768
+    pt, pp, pv = rnd(B, H, dtype=F32), rnd(B, H, seed=1, dtype=F32), rnd(B, H, seed=2, dtype=F32)
+    w, b = rnd(2, H, seed=3, scale=0.05), rnd(2, seed=4)
+    z = torch.zeros(B, dtype=torch.int64, device=DEV)
+    l1 = z.clone()
+    l1[::3] = 1
+    r = rng_state()
+    for drop in (None, (0.1, 77)):
+        close(ops.itm_loss(pt, pp, pv, w, b, l1, z, z, drop=drop, rng=r),
+              ref.itm_loss(pt, pp, pv, w, b, l1, z, z, drop=drop, rng=r), 1e-5, 1e-6, "itm")
+
+
+# ---- optimizer -------------------------------------------------------------------------------------
+def test_adamw_matches_torch_optim(ops, ref):
+    n = 1 << 20
+    p0 = rnd(n, dtype=F32, scale=0.02)
+    p = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.AdamW([p], lr=1e-4, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01)
+    p32, m, v = p0.clone(), torch.zeros_like(p0), torch.zeros_like(p0)
+    p16 = torch.zeros(n, dtype=BF, device=DEV)
+    for step in (1, 2, 3):
+        g = rnd(n, dtype=F32, seed=step, scale=1e-3)
+        p.grad = g.clone()
+        opt.step()
+        g32 = g.clone() * 4.0                              # grad_scale 0.25 undoes it (1/world)
+        hyper = torch.tensor([1e-4, 0.9, 0.98, 1e-8, 0.01, float(step), 0.25, 0.0], dtype=F32, device=DEV)
+        ops.adamw(p32, g32, m, v, p16, hyper, zero_grad=True)
+        assert float(g32.abs().max()) == 0.0
+        close(p32, p.data, 1e-6, 1e-8, "adamw step %d" % step)
+        assert torch.equal(p16, p32.to(BF))
