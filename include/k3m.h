@@ -116,8 +116,10 @@ int k3m_struct_attn_fwd(const float* t, const void* w2, const void* b2, const in
                         float* att, int B, int maxn, int H, void* stream);
 int k3m_struct_attn_bwd(const float* ds, const float* t, const float* att, const void* w2, const int* seg,
                         float* dt, float* dw2, float* db2, int B, int maxn, int H, void* stream);
-int k3m_lpm_fwd_bwd(const float* c_final, const float* PV, const int* terms, int T, int H, float margin,
-                    float* loss, float* dc_final, float* dPV, void* stream);
+/* `terms` holds T rows; if n_valid (device int, may be NULL) is given only the first *n_valid count
+ * (fixed-capacity term lists for CUDA-graph replay).                                              */
+int k3m_lpm_fwd_bwd(const float* c_final, const float* PV, const int* terms, int T, const int* n_valid,
+                    int H, float margin, float* loss, float* dc_final, float* dPV, void* stream);
 
 /* loss block (vilbert_k3m.py:2739-2832)                                                          */
 int k3m_count_labels(const long long* labels, int n, long long value, int equal, float* out, void* stream);

@@ -249,10 +249,14 @@ __global__ void __launch_bounds__(256) struct_attn_bwd_kernel(const float* __res
 // one CTA per term (i, j, ni, nv): pos = |c[i] + p[j] - v[j]|, neg = |c[ni] + p[j] - v[nv]|,
 // loss += max(0, neg - pos + margin) / T, and the gradient goes straight to dc_final / dPV.
 __global__ void __launch_bounds__(128) lpm_kernel(const float* __restrict__ c_final, const float* __restrict__ PV,
-                                                  const int* __restrict__ terms, int T, int H, float margin,
+                                                  const int* __restrict__ terms, int T_cap,
+                                                  const int* __restrict__ n_valid, int H, float margin,
                                                   float* __restrict__ loss, float* __restrict__ dc, float* __restrict__ dPV) {
   __shared__ float red[32];
   const int tix = blockIdx.x;
+  // the term list may be padded to a fixed capacity (CUDA-graph replay); the real count lives on the device
+  const int T = n_valid ? *n_valid : T_cap;
+  if (tix >= T) return;
   const int i = terms[4 * tix], j = terms[4 * tix + 1], ni = terms[4 * tix + 2], nv = terms[4 * tix + 3];
   const float* ci = c_final + (size_t)i * H;
   const float* cn = c_final + (size_t)ni * H;
@@ -382,10 +386,10 @@ extern "C" int k3m_struct_attn_bwd(const float* ds, const float* t, const float*
   return k3m_check_launch("k3m_struct_attn_bwd");
 }
 
-extern "C" int k3m_lpm_fwd_bwd(const float* c_final, const float* PV, const int* terms, int T, int H, float margin,
-                               float* loss, float* dc_final, float* dPV, void* stream) {
+extern "C" int k3m_lpm_fwd_bwd(const float* c_final, const float* PV, const int* terms, int T, const int* n_valid,
+                               int H, float margin, float* loss, float* dc_final, float* dPV, void* stream) {
   if (T <= 0) return K3M_OK;
-  lpm_kernel<<<T, 128, 0, ST(stream)>>>(c_final, PV, terms, T, H, margin, loss, dc_final, dPV);
+  lpm_kernel<<<T, 128, 0, ST(stream)>>>(c_final, PV, terms, T, n_valid, H, margin, loss, dc_final, dPV);
   return k3m_check_launch("k3m_lpm_fwd_bwd");
 }
 

@@ -59,6 +59,7 @@ class Engine(object):
         self.tape = []
         self._site = 0
         self._wv, self._gv = {}, {}
+        self.on_ready = None     # callback(prefixes | None): weight gradients of these blocks are final
 
     # ---- views / small helpers -------------------------------------------------------------
     def W(self, name):
@@ -368,7 +369,8 @@ class Engine(object):
                            addend=c_init, out_dtype=f32)
         dc_final = self.zeros(B, H, f32)
         dPV = self.zeros(PV.shape[0], 2 * H, f32)
-        loss = ops.lpm_fwd_bwd(c_final, PV, plan["terms"], float(self.cfg.margin), dc_final, dPV)
+        loss = ops.lpm_fwd_bwd(c_final, PV, plan["terms"], float(self.cfg.margin), dc_final, dPV,
+                               n_valid=plan.get("n_terms"))
         return c_final, loss, (plan, X, t, att, s_a, dc_final, dPV)
 
     def struct_bwd(self, saved, w_lpm, dc_init, dseq_pv):
@@ -527,17 +529,22 @@ class Engine(object):
         self.fuse_bwd(dseqV, sv_fv, d_ev, dY[V1], dY[V2])
         self.fuse_bwd(dS[:Mt], sv_ft, d_et, dX[T1], dX[T3])
         self.fuse_bwd(dS[Mt:], sv_fp, d_epv, dX[P2], dX[P3])
+        ready = self.on_ready or (lambda prefixes: None)
+        ready(None)
         for st in reversed(sv["stages"]):
             if st[0] == "t":
                 dX = self.layer_bwd(dX, st[1])
+                ready([st[1][0]])
             elif st[0] == "v":
                 dY = self.layer_bwd(dY, st[1])
+                ready([st[1][0]])
             else:
                 dXn, dYn = torch.empty_like(dX), torch.empty_like(dY)
                 self.connection_bwd(dY[V1], dX[T1], st[1], dYn[V1], dXn[T1])
                 self.connection_bwd(dY[V2], dX[P2], st[2], dYn[V2], dXn[P2])
                 self.connection_bwd(dX[P3], dX[T3], st[3], dXn[P3], dXn[T3])
                 dX, dY = dXn, dYn
+                ready([st[1][0], st[2][0], st[3][0]])
         for sl in (T1, T3):
             ops.axpy(dX[sl], d_et, 1.0)
         for sl in (P2, P3):

@@ -120,9 +120,79 @@ def _round_up(x, m):
     return (x + m - 1) // m * m
 
 
+def no_grad_names(cfg, names):
+    """Parameters that never receive a gradient in the K3M pretraining step:
+    `q_dense1/2` are never called (`vilbert_k3m.py:976,983`), the pooler outputs are discarded by
+    `forward` (`:2620-2631`), `map_individual_to_bi` and `soft_*` are only used by
+    `if_pre_sampling == 2`, the `score_*` gates only by `if_pre_sampling == 1`, and the ITM loss is
+    never added to the training loss (`pretrain.py:1055`) so `cls.seq_relationship` is value-only.
+    torch.optim.AdamW skips such parameters entirely (no decay, no state)."""
+    out = set()
+    for n in names:
+        if (".q_dense" in n or n.startswith("t_pooler.") or n.startswith("v_pooler.")
+                or n.startswith("map_individual_to_bi.") or n.startswith("soft_")
+                or n.startswith("cls.seq_relationship.")):
+            out.add(n)
+        elif n.startswith("score_") and getattr(cfg, "if_pre_sampling", 1) != 1:
+            out.add(n)
+    return out
+
+
+def exec_order(cfg, names):
+    """Parameter names sorted by the point of the forward schedule that first uses them
+    (`BertEncoder.forward` `vilbert_k3m.py:1686-1750`: text layers up to the next connection,
+    image layers up to it, the three connection layers, ...; then fusion, aggregator, heads).
+    Backward finishes weight gradients in the reverse of this order, so contiguous arena ranges
+    taken from the END become ready first: gradient buckets are plain slices."""
+    stage = {}
+
+    def put(prefix, k):
+        stage[prefix] = k
+
+    k = 0
+    put("embeddings.", k)
+    put("v_embeddings.", k)
+    k += 1
+    s1 = s2 = 0
+    for count, (e1, e2) in enumerate(zip(cfg.v_biattention_id, cfg.t_biattention_id)):
+        for i in range(s2, e2):
+            put("encoder.layer.%d." % i, k)
+            k += 1
+        for i in range(s1, e1):
+            put("encoder.v_layer.%d." % i, k)
+            k += 1
+        for c in ("c_layer", "c_layer_pv_v", "c_layer_pv_t"):
+            put("encoder.%s.%d." % (c, count), k)
+            k += 1
+        s1, s2 = e1, e2
+    for i in range(s1, cfg.v_num_hidden_layers):
+        put("encoder.v_layer.%d." % i, k)
+        k += 1
+    for i in range(s2, cfg.num_hidden_layers):
+        put("encoder.layer.%d." % i, k)
+        k += 1
+    prefixes = sorted(stage.keys(), key=len, reverse=True)
+
+    def key(item):
+        idx, n = item
+        for p in prefixes:
+            if n.startswith(p):
+                return (stage[p], idx)
+        return (k + 1, idx)           # fusion gates, aggregator, heads, poolers: after the encoder
+
+    return [n for _, n in sorted(enumerate(names), key=key)]
+
+
 class ArenaLayout(object):
     """name -> (offset, numel, shape) in one flat buffer; every tensor starts 64-element aligned
     (128 B in bf16, 256 B in fp32) so TMA descriptors can point straight into the arena.
+
+    The arena has three contiguous regions, in this order:
+      [0, decay_end)            trained, weight decay 0.01   (`pretrain.py:835-851` substring rule)
+      [decay_end, trained_end)  trained, no weight decay     (biases, `LayerNorm.{weight,bias}`)
+      [trained_end, total)      parameters that never get a gradient (`no_grad_names`)
+    so AdamW is two launches over plain ranges and the gradient all-reduce covers exactly
+    [0, trained_end) in contiguous buckets.
 
     Fused groups are emitted back to back *without* padding in between (their row sizes are
     multiples of 64 elements for every supported config), so that e.g.
@@ -135,35 +205,37 @@ class ArenaLayout(object):
         self.spec = param_spec(cfg)
         self.offsets = OrderedDict()
         self.fused = OrderedDict()      # fused name -> (offset, shape)
-        self.decay_ranges = []          # (start, end) element ranges with weight decay
-        off = 0
-        placed = set()
         names = list(self.spec.keys())
+        frozen = no_grad_names(cfg, names)
+        self.frozen = frozen
+        state = {"off": 0}
+        placed = set()
 
         def place(name):
-            nonlocal off
             shape = self.spec[name]
             n = 1
             for d in shape:
                 n *= d
-            self.offsets[name] = (off, n, shape)
-            off += n
+            self.offsets[name] = (state["off"], n, shape)
+            state["off"] += n
             placed.add(name)
 
         def place_group(fused_name, members):
-            nonlocal off
-            off = _round_up(off, self.ALIGN)
-            start = off
+            state["off"] = _round_up(state["off"], self.ALIGN)
+            start = state["off"]
             for m in members:
                 place(m)
             shapes = [self.spec[m] for m in members]
             rows = sum(sh[0] for sh in shapes)
             self.fused[fused_name] = (start, (rows,) + tuple(shapes[0][1:]))
 
-        for name in names:
-            if name in placed:
-                continue
-            base = None
+        def region_of(name):
+            if name in frozen:
+                return 2
+            return 1 if is_no_decay(name) else 0
+
+        def group_of(name):
+            """-> (fused name, members) if `name` opens a fused group, else None."""
             for q, grp, tag in (
                 (".attention.self.query", ("query", "key", "value"), "qkv"),
                 (".biattention.query1", ("query1", "key1", "value1"), "qkv1"),
@@ -171,21 +243,30 @@ class ArenaLayout(object):
             ):
                 for kind in (".weight", ".bias"):
                     if name.endswith(q + kind):
-                        base = name[: -len(q + kind)]
-                        prefix = base + q[: q.rfind(".") + 1]
-                        members = [prefix + g + kind for g in grp]
-                        place_group(prefix + tag + kind, members)
-            if base is not None:
-                continue
+                        prefix = name[: -len(q + kind)] + q[: q.rfind(".") + 1]
+                        return prefix + tag + kind, [prefix + g + kind for g in grp]
             if name.startswith("score_self_"):
-                m = name[len("score_self_"):]           # e.g. "v.weight"
-                mod, kind = m.split(".")
-                members = ["score_%s_%s.%s" % (g, mod, kind) for g in ("self", "cross1", "cross2")]
-                place_group("score_%s.%s" % (mod, kind), members)
-                continue
-            off = _round_up(off, self.ALIGN)
-            place(name)
-        self.total = _round_up(off, self.ALIGN)
+                mod, kind = name[len("score_self_"):].split(".")
+                return ("score_%s.%s" % (mod, kind),
+                        ["score_%s_%s.%s" % (g, mod, kind) for g in ("self", "cross1", "cross2")])
+            return None
+
+        bounds = []
+        ordered = exec_order(cfg, names)
+        for region in (0, 1, 2):
+            for name in ordered:
+                if name in placed or region_of(name) != region:
+                    continue
+                grp = group_of(name)
+                if grp is not None:
+                    assert all(region_of(m) == region for m in grp[1])
+                    place_group(grp[0], grp[1])
+                    continue
+                state["off"] = _round_up(state["off"], self.ALIGN)
+                place(name)
+            state["off"] = _round_up(state["off"], 1024)
+            bounds.append(state["off"])
+        self.decay_end, self.trained_end, self.total = bounds
         assert placed == set(names)
 
     def view(self, flat, name):
@@ -197,3 +278,22 @@ class ArenaLayout(object):
         for d in shape:
             n *= d
         return flat[off:off + n].view(*shape)
+
+    def segments(self, group_fn=None):
+        """Merged (start, end, key) runs over the trained region; key = group_fn(name) (default:
+        the weight-decay flag).  Alignment gaps are absorbed into the preceding run (they hold
+        zeros with zero gradients, so any update leaves them at zero... except weight decay of 0)."""
+        group_fn = group_fn or (lambda n: not is_no_decay(n))
+        items = sorted(((off, num, n) for n, (off, num, _) in self.offsets.items() if n not in self.frozen))
+        runs = []
+        for off, num, n in items:
+            k = group_fn(n)
+            if runs and runs[-1][2] == k:
+                runs[-1][1] = off + num
+            else:
+                if runs:
+                    runs[-1][1] = off
+                runs.append([off, off + num, k])
+        if runs:
+            runs[-1][1] = self.trained_end
+        return [tuple(r) for r in runs]

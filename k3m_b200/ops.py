@@ -282,9 +282,10 @@ class CudaOps(object):
         self._call("k3m_struct_attn_bwd", _p(ds), _p(t), _p(att), _p(w2), _p(seg), _p(dt), _p(dw2), _p(db2),
                    _i(B), _i(att.shape[1]), _i(H), self._st())
 
-    def lpm_fwd_bwd(self, c_final, pv, terms, margin, dc_final, dpv):
+    def lpm_fwd_bwd(self, c_final, pv, terms, margin, dc_final, dpv, n_valid=None):
         loss = torch.zeros(1, dtype=torch.float32, device=c_final.device)
-        self._call("k3m_lpm_fwd_bwd", _p(c_final), _p(pv), _p(terms), _i(terms.shape[0]), _i(c_final.shape[1]),
+        self._call("k3m_lpm_fwd_bwd", _p(c_final), _p(pv), _p(terms), _i(terms.shape[0]), _p(n_valid),
+                   _i(c_final.shape[1]),
                    _f(margin), _p(loss), _p(dc_final), _p(dpv), self._st())
         return loss
 

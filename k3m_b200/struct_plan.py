@@ -71,3 +71,27 @@ def build_struct_plan(index_p, index_v, L_pv, num_negative_pv, rng=random):
         seg=np.asarray(seg, dtype=np.int32).reshape(-1, 2),
         terms=np.asarray(terms, dtype=np.int32).reshape(-1, 4),
     )
+
+
+def plan_capacity(B, max_num_pv, num_negative_pv):
+    """(pairs, terms, maxn) upper bounds for a batch of B items with at most `max_num_pv` pairs."""
+    P = B * max_num_pv
+    return P, max(1, P * max(1, num_negative_pv)), max_num_pv
+
+
+def pad_struct_plan(plan, B, max_num_pv, num_negative_pv):
+    """Fixed-shape version of a plan, for CUDA-graph replay: pairs are padded with (item 0, row 0)
+    entries that no `seg` range and no term refers to (their `t` rows get a zero gradient, so they
+    contribute nothing to any weight gradient), terms are padded with zeros and the real count is
+    returned as `n_terms` (int32 [1])."""
+    P_cap, T_cap, _ = plan_capacity(B, max_num_pv, num_negative_pv)
+    P, T = plan["pair_item"].shape[0], plan["terms"].shape[0]
+    if P > P_cap or T > T_cap:
+        raise ValueError("struct plan exceeds its capacity (P=%d/%d, T=%d/%d)" % (P, P_cap, T, T_cap))
+    out = dict(pair_item=np.zeros(P_cap, dtype=np.int32), pair_rows=np.zeros((P_cap, 4), dtype=np.int32),
+               seg=plan["seg"].copy(), terms=np.zeros((T_cap, 4), dtype=np.int32),
+               n_terms=np.asarray([T], dtype=np.int32))
+    out["pair_item"][:P] = plan["pair_item"]
+    out["pair_rows"][:P] = plan["pair_rows"]
+    out["terms"][:T] = plan["terms"]
+    return out

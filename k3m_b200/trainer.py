@@ -1,0 +1,314 @@
+"""The K3M pretraining step as one object: forward + backward + gradient all-reduce + AdamW.
+
+This is the part of the reference's driver loop between `optimizer.zero_grad()` and
+`scheduler.step()` (`pretrain.py:986-1110`): `model(...)` -> `loss = out[0] + out[1]*w + out[3] +
+out[9]` (`:1021,1055`) -> `loss.backward()` (DDP all-reduce inside, `:166`) -> `optimizer.step()`
+(`torch.optim.AdamW`, `:919-924`) -> `scheduler.step()` (`WarmupLinearSchedule`, `:927-931`).
+
+Memory (all on one B200, replicated per rank; 461.7 M parameters -> 8.3 GB):
+  p32 / m / v   fp32 master weights and AdamW moments        [total]
+  w16           bf16 shadow of p32 (what the kernels read)   [total]
+  g32           fp32 gradient arena (wgrad GEMMs accumulate straight into it)
+arranged by `ArenaLayout`: [decay | no-decay | never-trained], each in forward execution order, so
+AdamW is two launches and gradient buckets are contiguous slices that become final from the end of
+the arena backwards while backward is still running.
+
+Static shapes + no host synchronisation inside -> the whole step is one CUDA graph.  Per step the
+host only (1) builds the structure-aggregator index plan from `index_p/index_v` (host integers
+that the loader produced on the host anyway), (2) copies the batch host->device into the graph's
+static input buffers, (3) writes the learning rate, (4) replays the graph.
+"""
+import math
+
+import numpy as np
+import torch
+
+from . import optim
+from .engine import Engine
+from .layout import ArenaLayout
+from .ops import CudaOps
+from .struct_plan import build_struct_plan, pad_struct_plan, plan_capacity
+
+LOSS_NAMES = ("loss_t", "loss_v", "loss_pv", "loss_itm", "loss_lpm")
+
+
+def input_spec(cfg, B, Lt, Lv1, Lpv, max_num_pv):
+    """name -> (shape, dtype) of the tensors the reference's loader yields
+    (`concept_cap_dataset_struc.py:372-413`) and `forward` takes (`vilbert_k3m.py:2673-2696`)."""
+    i64, f32 = torch.int64, torch.float32
+    return dict(
+        input_ids=((B, Lt), i64), token_type_ids=((B, Lt), i64), attention_mask=((B, Lt), i64),
+        masked_lm_labels=((B, Lt), i64),
+        input_ids_pv=((B, Lpv), i64), token_type_ids_pv=((B, Lpv), i64), attention_mask_pv=((B, Lpv), i64),
+        masked_lm_labels_pv=((B, Lpv), i64),
+        image_feat=((B, Lv1, cfg.v_feature_size), f32), image_loc=((B, Lv1, 5), f32),
+        image_attention_mask=((B, Lv1), i64), image_label=((B, Lv1 - 1), i64),
+        image_target=((B, Lv1 - 1, cfg.v_target_size), f32),
+        next_sentence_label=((B,), i64), next_sentence_label_pv_v=((B,), i64),
+        next_sentence_label_pv_t=((B,), i64),
+    )
+
+
+class PretrainStep(object):
+    def __init__(self, cfg, batch_size, len_t=36, len_v=36, len_pv=36, max_num_pv=8, device="cuda",
+                 state_dict=None, init_seed=0, lr=1e-4, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01,
+                 warmup_steps=0, total_steps=0, loss_img_weight=1.0, training=True, rng_seed=1234,
+                 use_graph=True, process_group=None, bucket_mb=64, overlap=True, ops=None):
+        """`ops`: kernel table; default (and the only product path) is `CudaOps`, which raises without
+        a CUDA device.  Tests inject the fp32 PyTorch restatement to check this host logic on CPU."""
+        self.cfg, self.device = cfg, torch.device(device)
+        self.B, self.Lt, self.Lv1, self.Lpv, self.max_num_pv = batch_size, len_t, len_v + 1, len_pv, max_num_pv
+        self.ops = ops if ops is not None else CudaOps(self.device)
+        self._cuda = self.device.type == "cuda"
+        adt = getattr(self.ops, "adt", torch.bfloat16)
+        self.layout = L = ArenaLayout(cfg)
+        dev, f32 = self.device, torch.float32
+        self.p32 = torch.zeros(L.total, dtype=f32, device=dev)
+        self.m = torch.zeros(L.total, dtype=f32, device=dev)
+        self.v = torch.zeros(L.total, dtype=f32, device=dev)
+        self.g32 = torch.zeros(L.total, dtype=f32, device=dev)
+        self.w16 = torch.zeros(L.total, dtype=adt, device=dev)
+        self.rng = torch.tensor([rng_seed, 0], dtype=torch.int64, device=dev)
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.warmup_steps, self.total_steps = warmup_steps, total_steps
+        self.loss_weights = (1.0, float(loss_img_weight), 1.0, 1.0)     # `pretrain.py:1055`
+        self.global_step = 0
+        self.group = process_group
+        self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
+        self.overlap = overlap
+        self.engine = Engine(cfg, L, self.ops, self.w16, self.g32, self.rng, adt)
+        self.engine.training = training
+        if state_dict is not None:
+            self.load_state_dict(state_dict)
+        else:
+            self.init_weights(init_seed)
+        # static graph inputs
+        self.spec = input_spec(cfg, self.B, self.Lt, self.Lv1, self.Lpv, max_num_pv)
+        self.inputs = {k: torch.zeros(s, dtype=d, device=dev) for k, (s, d) in self.spec.items()}
+        P_cap, T_cap, maxn = plan_capacity(self.B, max_num_pv, cfg.num_negative_pv)
+        i32 = torch.int32
+        self.plan = dict(pair_item=torch.zeros(P_cap, dtype=i32, device=dev),
+                         pair_rows=torch.zeros(P_cap, 4, dtype=i32, device=dev),
+                         seg=torch.zeros(self.B, 2, dtype=i32, device=dev),
+                         terms=torch.zeros(T_cap, 4, dtype=i32, device=dev),
+                         n_terms=torch.zeros(1, dtype=i32, device=dev))
+        self.plan["seg"]._k3m_maxn = maxn
+        pin = (lambda t: t.pin_memory()) if self._cuda else (lambda t: t)
+        self._plan_host = [{k: pin(torch.zeros(v.shape, dtype=i32)) for k, v in self.plan.items()}
+                           for _ in range(2)]
+        # AdamW hyper-parameters live on the device (graph nodes stay valid); ring of pinned copies
+        self.hyper = torch.zeros(2, 8, dtype=f32, device=dev)
+        self._hyper_host = [pin(torch.zeros(2, 8, dtype=f32)) for _ in range(2)]
+        self._slot_events = [None, None]
+        self.losses = torch.zeros(8, dtype=f32, device=dev)
+        self.losses_host = pin(torch.zeros(8, dtype=f32))
+        self.h2d_bytes = sum(int(np.prod(s)) * (8 if d == torch.int64 else 4) for s, d in self.spec.values())
+        self.h2d_bytes += sum(v.numel() * 4 for v in self.plan.values()) + self.hyper.numel() * 4
+        self.d2h_bytes = self.losses.numel() * 4
+        self._buckets = self._make_buckets(bucket_mb)
+        self._comm_stream = torch.cuda.Stream(device=dev) if (self.world > 1 and self._cuda) else None
+        self.use_graph = use_graph and self._cuda
+        self.graph = None
+        self.launches_per_step = 0
+
+    # ---- parameters ------------------------------------------------------------------------
+    def init_weights(self, seed):
+        """`init_weights` (`vilbert_k3m.py:1940-1951`): N(0, initializer_range) for Linear and
+        Embedding weights, zero biases, LayerNorm = (1, 0); `struc_w1/2/3` are created after
+        `self.apply(self.init_weights)` (`:2257-2259`) and keep nn.Linear's default
+        U(-1/sqrt(in), 1/sqrt(in)) init for weight and bias."""
+        L = self.layout
+        g = torch.Generator(device=self.device).manual_seed(seed)
+        for n, (off, num, shape) in L.offsets.items():
+            t = self.p32[off:off + num]
+            if n.startswith("struc_w"):
+                bound = 1.0 / math.sqrt(L.spec[n.rsplit(".", 1)[0] + ".weight"][1])
+                t.uniform_(-bound, bound, generator=g)
+            elif "LayerNorm" in n:
+                t.fill_(1.0 if n.endswith("weight") else 0.0)
+            elif len(shape) == 1:
+                t.zero_()
+            else:
+                t.normal_(0.0, self.cfg.initializer_range, generator=g)
+        self.w16.copy_(self.p32)
+
+    def load_state_dict(self, sd):
+        """Reference-layout state_dict (999 keys; the tied `cls.predictions.decoder.weight` alias
+        and a leading `module.` are accepted, `pretrain.py:745-762`)."""
+        L = self.layout
+        missing = []
+        for n, (off, num, shape) in L.offsets.items():
+            t = sd.get(n, sd.get("module." + n))
+            if t is None:
+                missing.append(n)
+                continue
+            if tuple(t.shape) != tuple(shape):
+                raise ValueError("%s: shape %s, expected %s" % (n, tuple(t.shape), tuple(shape)))
+            self.p32[off:off + num].copy_(t.reshape(-1).to(torch.float32))
+        if missing:
+            raise KeyError("state_dict is missing %d parameters, e.g. %s" % (len(missing), missing[:3]))
+        self.w16.copy_(self.p32)
+
+    def state_dict(self):
+        from .layout import TIED_ALIAS
+        out = {}
+        for n in self.layout.spec:
+            off, num, shape = self.layout.offsets[n]
+            out[n] = self.p32[off:off + num].view(*shape)
+        out[TIED_ALIAS[0]] = out[TIED_ALIAS[1]]
+        return out
+
+    def grad(self, name):
+        off, num, shape = self.layout.offsets[name]
+        return self.g32[off:off + num].view(*shape)
+
+    # ---- gradient buckets (data parallel) ----------------------------------------------------
+    def _make_buckets(self, bucket_mb):
+        """Contiguous fp32 slices of the trained region, listed in the order they become final in
+        backward: the decay region from its END towards the start in `bucket_mb` pieces, then the
+        (small) no-decay region as one last bucket."""
+        L = self.layout
+        step = max(1, int(bucket_mb * (1 << 20) // 4))
+        out, hi = [], L.decay_end
+        while hi > 0:
+            lo = max(0, hi - step)
+            out.append((lo, hi))
+            hi = lo
+        out.append((L.decay_end, L.trained_end))
+        # stage prefix -> lowest decay-region offset of its parameters
+        self._stage_lo = {}
+        for n, (off, num, _) in L.offsets.items():
+            if off >= L.decay_end:
+                continue
+            parts = n.split(".")
+            key = ".".join(parts[:3]) if parts[0] == "encoder" else "<tail>"
+            if parts[0] in ("embeddings", "v_embeddings"):
+                key = "<embed>"
+            self._stage_lo[key] = min(self._stage_lo.get(key, L.decay_end), off)
+        return out
+
+    def _reduce_range(self, lo, hi):
+        t = self.g32[lo:hi]
+        if self._comm_stream is None:
+            torch.distributed.all_reduce(t, group=self.group)
+            return
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        with torch.cuda.stream(self._comm_stream):
+            self._comm_stream.wait_event(ev)
+            torch.distributed.all_reduce(t, group=self.group)
+
+    def _on_ready(self, prefixes):
+        """Engine callback: backward has finished every weight gradient of `prefixes` (None = the
+        heads, fusion gates and aggregator).  Launch every bucket that is now final."""
+        if self.world == 1 or not self.overlap:
+            return
+        keys = ["<tail>"] if prefixes is None else prefixes
+        for k in keys:
+            self._ready_lo = min(self._ready_lo, self._stage_lo.get(k, self._ready_lo))
+        while self._next_bucket < len(self._buckets) - 1 and self._buckets[self._next_bucket][0] >= self._ready_lo:
+            self._reduce_range(*self._buckets[self._next_bucket])
+            self._next_bucket += 1
+
+    def _finish_reduce(self):
+        if self.world == 1:
+            return
+        while self._next_bucket < len(self._buckets):
+            self._reduce_range(*self._buckets[self._next_bucket])
+            self._next_bucket += 1
+        if self._comm_stream is not None:
+            torch.cuda.current_stream().wait_stream(self._comm_stream)
+
+    # ---- the device side of one step ---------------------------------------------------------
+    def _device_step(self):
+        L, ops = self.layout, self.ops
+        self._ready_lo, self._next_bucket = L.decay_end, 0
+        out = self.engine.forward(self.inputs, self.plan, None, self.loss_weights)
+        self.engine.on_ready = self._on_ready
+        self.engine.backward()
+        self._finish_reduce()
+        # gradients are summed over ranks; hyper[:, 6] = 1/world turns that into DDP's mean
+        for gi, (lo, hi) in enumerate(((0, L.decay_end), (L.decay_end, L.trained_end))):
+            ops.adamw(self.p32[lo:hi], self.g32[lo:hi], self.m[lo:hi], self.v[lo:hi], self.w16[lo:hi],
+                      self.hyper[gi], zero_grad=True)
+        self.rng[1:].add_(1)
+        w = self.loss_weights
+        torch.stack([out[k].reshape(()) for k in LOSS_NAMES], out=self.losses[:5])
+        self.losses[5] = (out["loss_t"] * w[0] + out["loss_v"] * w[1] + out["loss_pv"] * w[2]
+                          + out["loss_lpm"] * w[3]).reshape(())
+        self.c_initial, self.c_final = out["c_initial"], out["c_final"]
+
+    def _capture(self):
+        # warm-up on a side stream (lazy module loading, cudaFuncSetAttribute, NCCL setup), then capture
+        s = torch.cuda.Stream(device=self.device)
+        s.wait_stream(torch.cuda.current_stream())
+        snap = (self.p32.clone(), self.m.clone(), self.v.clone(), self.w16.clone(), self.rng.clone())
+        with torch.cuda.stream(s):
+            self._device_step()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        for dst, src in zip((self.p32, self.m, self.v, self.w16, self.rng), snap):
+            dst.copy_(src)
+        self.g32.zero_()
+        del snap
+        self.graph = torch.cuda.CUDAGraph()
+        n0 = self.ops.launches
+        with torch.cuda.graph(self.graph, stream=s):
+            self._device_step()
+        self.launches_per_step = self.ops.launches - n0
+
+    # ---- host side -----------------------------------------------------------------------------
+    def _write_hyper(self, slot):
+        step = self.global_step + 1
+        f = 1.0
+        if self.total_steps > 0:
+            f = optim.warmup_linear_factor(self.global_step, self.warmup_steps, self.total_steps)
+        h = self._hyper_host[slot]
+        for gi, wd in enumerate((self.weight_decay, 0.0)):
+            h[gi] = torch.tensor([self.lr * f, self.betas[0], self.betas[1], self.eps, wd, float(step),
+                                  1.0 / self.world, 0.0])
+        self.hyper.copy_(h, non_blocking=True)
+
+    def step(self, batch):
+        """batch: dict of HOST tensors named as the reference's forward() arguments (pinned memory
+        makes the copies asynchronous).  Returns the device tensor `self.losses`
+        [loss_t, loss_v, loss_pv, loss_itm, loss_lpm, weighted training loss, -, -]; call
+        `read_losses()` for the host copy (one device->host sync, like the reference's per-step
+        `.cpu()` at `pretrain.py:1071-1075`)."""
+        slot = self.global_step & 1
+        if self._slot_events[slot] is not None:
+            self._slot_events[slot].synchronize()           # pinned staging of step-2 has been consumed
+        plan = build_struct_plan(batch["index_p"].numpy(), batch["index_v"].numpy(), self.Lpv,
+                                 self.cfg.num_negative_pv)
+        plan = pad_struct_plan(plan, self.B, self.max_num_pv, self.cfg.num_negative_pv)
+        ph = self._plan_host[slot]
+        for k, v in plan.items():
+            ph[k].copy_(torch.from_numpy(v).reshape(ph[k].shape))
+            self.plan[k].copy_(ph[k], non_blocking=True)
+        for k, dst in self.inputs.items():
+            src = batch[k]
+            if tuple(src.shape) != tuple(dst.shape) or src.dtype != dst.dtype:
+                raise ValueError("%s: got %s %s, this step was built for %s %s" % (
+                    k, tuple(src.shape), src.dtype, tuple(dst.shape), dst.dtype))
+            dst.copy_(src, non_blocking=True)
+        self._write_hyper(slot)
+        if self._cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+            self._slot_events[slot] = ev
+        if self.use_graph:
+            if self.graph is None:
+                self._capture()
+            self.graph.replay()
+        else:
+            n0 = getattr(self.ops, "launches", 0)
+            self._device_step()
+            self.launches_per_step = getattr(self.ops, "launches", 0) - n0
+        self.global_step += 1
+        return self.losses
+
+    def read_losses(self):
+        self.losses_host.copy_(self.losses, non_blocking=True)
+        if self._cuda:
+            torch.cuda.current_stream().synchronize()
+        return {k: float(self.losses_host[i]) for i, k in enumerate(LOSS_NAMES + ("loss",))}

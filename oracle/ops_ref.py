@@ -391,13 +391,15 @@ class RefOps(object):
             dw2.add_((dsc[:, None] * torch.nn.functional.leaky_relu(tt)).sum(0).reshape(dw2.shape))
             db2.add_(dsc.sum().reshape(db2.shape))
 
-    def lpm_fwd_bwd(self, c_final, pv, terms, margin, dc_final, dpv):
+    def lpm_fwd_bwd(self, c_final, pv, terms, margin, dc_final, dpv, n_valid=None):
         """terms [T,4] int32 = (item i, pair j, negative item, negative value-pair).
         pos = |c[i] + p[j] - v[j]|, neg = |c[ni] + p[j] - v[nv]|;
         loss = mean(max(0, neg - pos + margin)) (MarginRankingLoss(pos, neg, +1), `:2502`).
         Gradients of the loss are accumulated into dc_final [B,H] / dpv [P,2H] (fp32)."""
         H = c_final.shape[1]
         tm = terms.long()
+        if n_valid is not None:
+            tm = tm[:int(n_valid)]
         i, j, ni, nv = tm[:, 0], tm[:, 1], tm[:, 2], tm[:, 3]
         p, v = pv[:, :H], pv[:, H:]
         up = c_final[i] + p[j] - v[j]
