@@ -1,0 +1,295 @@
+#!/usr/bin/env python
+"""Benchmark of the K3M pretraining step (fwd + bwd + gradient all-reduce + AdamW).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One rank per GPU (torchrun sets RANK / LOCAL_RANK / WORLD_SIZE for N > 1).  Workload = BASELINE.json
+configs[1]: `bert_base_6layer_6conect`, batch 64 per GPU, 36-token titles, 36 regions (+1 global)
+x 2048-d, 36 PV tokens, all losses, dropout on, bf16 — weak scaling (global batch 64 * N; at N = 8
+this is configs[2]'s global batch 512).  Synthetic data, random-init weights.
+
+Prints ONE JSON line (rank 0).  `value` = samples/s with the batch already resident in HBM (graph
+replay only); `e2e` = samples/s through the public call `PretrainStep.step(host_batch)` +
+`read_losses()` with pinned host inputs (H2D of ~35 MB per step and D2H of the losses inside the
+timed region).  `--impl reference` times the CPU restatement of the reference step (oracle port,
+fp32, torch.optim.AdamW) on the host cores on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "pretrain samples/sec (fwd+bwd+opt)"
+UNIT = "samples/s"
+DIMS = dict(len_t=36, len_v=36, len_pv=36, max_num_pv=8)
+PER_GPU_BATCH = 64
+# algorithmic FLOPs of the reference graph as written, fwd+bwd, 36/37/36 (FlopCounterMode probe)
+FLOPS_PER_SAMPLE = 159.6e9
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm_gbs=d["hbm_gbs"], tflops=d["bf16_tflops"], tflops_sustained=d["bf16_tflops_sustained"],
+                    source="measured")
+    return dict(hbm_gbs=6650.0, tflops=1590.0, tflops_sustained=1400.0, source="fallback")
+
+
+def workload_config(n_gpus):
+    return {"workload": "K3M pretrain step, bert_base_6layer_6conect, batch %d/GPU, 36 title / 36+1 regions x 2048 / "
+                        "36 PV tokens, MLM-t + MRM-KL + MLM-pv + LPM (+ITM value), dropout on" % PER_GPU_BATCH,
+            "global_batch": PER_GPU_BATCH * n_gpus, "per_gpu_batch": PER_GPU_BATCH,
+            "parallelism": "dp%d" % n_gpus,
+            "l2": "no explicit flush: one step streams > 20 GB (weights, moments, gradients) through a 126 MB L2"}
+
+
+def make_cfg():
+    from k3m_b200.config import BertConfig, K3M_BASE_6LAYER_6CONNECT
+    cfg = BertConfig.from_dict(K3M_BASE_6LAYER_6CONNECT)
+    cfg.if_pre_sampling, cfg.margin, cfg.num_negative_pv = 1, 10.0, 4
+    return cfg
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ---- CPU arm: the oracle port of the reference step on the host cores ---------------------------------
+def cpu_reference_step_rate(steps, warmup, batch=8, threads=None):
+    """samples/s of the CPU restatement of the reference step (oracle/k3m_oracle.py: fp32 forward
+    through autograd, backward, torch.optim.AdamW with the reference's two groups), dropout off
+    (the restatement is deterministic; dropout is < 1 % of the reference's CPU time).  One step =
+    BASELINE configs[0]: batch 8 of the same 36/37/36 workload."""
+    import random
+    import torch
+    from k3m_b200.layout import is_no_decay, param_spec
+    from k3m_b200.synth import synth_batch, synth_state_dict
+    from oracle.k3m_oracle import Oracle, total_loss
+    threads = threads or os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    cfg = make_cfg()
+    sd = synth_state_dict(param_spec(cfg), seed=0)
+    params = {k: torch.nn.Parameter(v) for k, v in sd.items()}
+    groups = [dict(params=[p for n, p in params.items() if not is_no_decay(n)], weight_decay=0.01),
+              dict(params=[p for n, p in params.items() if is_no_decay(n)], weight_decay=0.0)]
+    opt = torch.optim.AdamW(groups, lr=1e-4, betas=(0.9, 0.98), eps=1e-8)
+    orc = Oracle(cfg, params)
+    batches = [synth_batch(cfg, batch, DIMS["len_t"], DIMS["len_v"], DIMS["len_pv"], DIMS["max_num_pv"], seed=100 + i)
+               for i in range(2)]
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        opt.zero_grad(set_to_none=True)
+        random.seed(it)
+        out = orc.forward(batches[it % 2], None)
+        total_loss(out).backward()
+        opt.step()
+        if it >= warmup:
+            times.append(time.perf_counter() - t0)
+    sec = sum(times) / len(times)
+    return batch / sec, sec, threads, batch
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    steps = max(1, min(args.steps, 3))
+    warm = 1
+    v, sec, threads, batch = cpu_reference_step_rate(steps, warm)
+    sample = "%d step(s) of batch %d (BASELINE configs[0]) after %d warm-up, fp32, %d threads" % (steps, batch, warm, threads)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warm, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.gpus),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ---- GPU arm ------------------------------------------------------------------------------------------
+def kernel_breakdown(step, batch):
+    """One eager (non-graph) step with every launch bracketed by CUDA events on the launching stream:
+    -> {entry point: (launches, total ms, total FLOPs)}.  Parameters/optimizer state are restored."""
+    import torch
+    snap = (step.p32.clone(), step.m.clone(), step.v.clone(), step.w16.clone(), step.rng.clone())
+    use_graph, step.use_graph = step.use_graph, False
+    step.ops.timing = []
+    step.step(batch)
+    torch.cuda.synchronize()
+    rows, step.ops.timing = step.ops.timing, None
+    step.use_graph = use_graph
+    step.global_step -= 1
+    for dst, src in zip((step.p32, step.m, step.v, step.w16, step.rng), snap):
+        dst.copy_(src)
+    out = {}
+    for name, work, e0, e1 in rows:
+        n, ms, fl = out.get(name, (0, 0.0, 0.0))
+        out[name] = (n + 1, ms + e0.elapsed_time(e1), fl + work)
+    return out
+
+
+def run_gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    from k3m_b200.synth import synth_batch
+    from k3m_b200.trainer import PretrainStep
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("bench.py --gpus %d must be launched with torchrun --nproc-per-node %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    group = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        group = dist.group.WORLD
+    cfg = make_cfg()
+    B = PER_GPU_BATCH
+    step = PretrainStep(cfg, B, device=dev, init_seed=0, lr=1e-4, warmup_steps=100, total_steps=100000,
+                        training=True, rng_seed=1234, use_graph=True, process_group=group, **DIMS)
+    host = []
+    for i in range(4):
+        b = synth_batch(cfg, B, DIMS["len_t"], DIMS["len_v"], DIMS["len_pv"], DIMS["max_num_pv"],
+                        seed=1234 + 97 * rank + i)
+        host.append({k: v.pin_memory() for k, v in b.items()})
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    # warm-up through the public call (captures the graph on the first step)
+    for i in range(max(3, args.warmup)):
+        step.step(host[i % 4])
+    loss0 = step.read_losses()
+    # ---- (1) device-resident: graph replays only ----
+    barrier()
+    clocks = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step.graph.replay()
+    e1.record()
+    barrier()
+    ms_dev = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    # ---- (2) end to end: host batch -> H2D -> step -> D2H losses, every step ----
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        step.step(host[i % 4])
+        last = step.read_losses()
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    clk = clocks.stop() if clocks is not None else None
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+    peaks = load_peaks()
+    kb = kernel_breakdown(step, host[0])
+    tot_ms = sum(v[1] for v in kb.values())
+    g_n, g_ms, g_fl = kb.get("k3m_gemm_bf16", (0, 1e-9, 0.0))
+    gemm_tflops = g_fl / (g_ms * 1e-3) / 1e12
+    samples = B * world
+    step_tflops = FLOPS_PER_SAMPLE * B / (ms_dev * 1e-3) / 1e12        # per GPU
+    line = {
+        "metric": METRIC, "value": samples / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(world),
+        "clocks": clk,
+        "e2e": {"value": samples / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": step.h2d_bytes, "d2h_bytes_per_step": step.d2h_bytes},
+        "gpu_launches": step.launches_per_step * args.steps * 2,
+        "launches_per_step": step.launches_per_step,
+        "roofline": {"bound": "tensor", "kernel": "gemm_kernel (k3m_gemm_bf16: tcgen05/TMEM/TMA)",
+                     "achieved": gemm_tflops, "peak": peaks["tflops"], "unit": "TFLOP/s",
+                     "frac": gemm_tflops / peaks["tflops"], "traffic": None, "peak_source": peaks["source"],
+                     "launches_per_step": g_n, "ms_per_step_in_kernel": g_ms,
+                     "share_of_step_kernel_time": g_ms / tot_ms,
+                     "flops_per_step_in_kernel": g_fl,
+                     "how": "every launch of one eager step bracketed by CUDA events on the launching stream"},
+        "step_roofline": {"bound": "tensor", "flops_per_sample": FLOPS_PER_SAMPLE, "achieved": step_tflops,
+                          "peak": peaks["tflops_sustained"], "unit": "TFLOP/s per GPU",
+                          "frac": step_tflops / peaks["tflops_sustained"], "frac_of_burst": step_tflops / peaks["tflops"]},
+        "kernel_ms": {k: {"launches": v[0], "ms": round(v[1], 4)} for k, v in sorted(kb.items(), key=lambda kv: -kv[1][1])},
+        "losses_first": loss0, "losses_last": last,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        v, sec, threads, batch = cpu_reference_step_rate(2, 1)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": "2 steps of batch %d (BASELINE configs[0]) after 1 warm-up: oracle port "
+                                          "(fp32 autograd restatement + torch.optim.AdamW), %.1f s/step" % (batch, sec)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="k3m_b200", choices=["k3m_b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -39,13 +39,25 @@ class CudaOps(object):
         self.adt = torch.bfloat16
         self.device = torch.device(device if device is not None else "cuda")
         self.launches = 0
+        # profiling aid (bench.py): when a list, every launch is bracketed by CUDA events on the
+        # launching stream and (entry point, work, event pair) is appended; never on in the product path
+        self.timing = None
+        self._work = 0.0
 
     def _st(self):
         return _vp(torch.cuda.current_stream().cuda_stream)
 
     def _call(self, name, *args):
         self.launches += 1
+        if self.timing is None:
+            _lib.check(getattr(self.lib, name)(*args), name)
+            return
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
         _lib.check(getattr(self.lib, name)(*args), name)
+        e1.record()
+        self.timing.append((name, self._work, e0, e1))
+        self._work = 0.0
 
     def _drop(self, drop, rng):
         if drop is None:
@@ -73,6 +85,7 @@ class CudaOps(object):
             accumulate = False
         assert tuple(out.shape) == (M, N)
         r, s, p = self._drop(drop, rng)
+        self._work = 2.0 * M * N * K
         self._call("k3m_gemm_bf16", _p(a), _i(_ld(a)), _p(b), _i(_ld(b)), _i(_LAYOUT[layout]),
                    _i(M), _i(N), _i(K), _p(out), _i(_ld(out)), _i(_isf32(out)), _i(1 if accumulate else 0),
                    _p(bias), _i(act), _p(aux_in), _i(_ld(aux_in)), _p(aux_out), _i(_ld(aux_out)),
