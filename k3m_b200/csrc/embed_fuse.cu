@@ -92,7 +92,9 @@ __global__ void relu_cat3_kernel(const bf16* a, int lda, const bf16* b, int ldb,
 __device__ __forceinline__ float gumbel_at(const unsigned long long* rng, unsigned int site, unsigned long long lin) {
   uint32_t w[4];
   rng_words(rng, site, lin >> 2, w);
-  const float u = ((float)(w[lin & 3] >> 8) + 0.5f) * (1.0f / 16777216.0f);
+  // 23 random bits + 1/2 is exact in fp32, so u stays inside [2^-24, 1 - 2^-24] and the noise is
+  // finite (with 24 bits, 16777215.5 rounds to 2^24 -> u = 1 -> g = +inf -> NaN in the backward softmax)
+  const float u = ((float)(w[lin & 3] >> 9) + 0.5f) * (1.0f / 8388608.0f);
   return -logf(-logf(u));
 }
 

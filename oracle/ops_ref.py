@@ -62,13 +62,14 @@ def dropout_keep(rng, site, rows, cols, p, ld=None):
 
 
 def gumbel_noise(rng, site, n):
-    """n fp32 Gumbel(0,1) draws g = -log(-log(u)), 4 per Philox call, u = (r>>8 + 0.5) / 2^24."""
+    """n fp32 Gumbel(0,1) draws g = -log(-log(u)), 4 per Philox call, u = (r>>9 + 0.5) / 2^23
+    (exact in fp32, never 0 or 1 -> finite noise)."""
     dev = rng.device
     lin = torch.arange(n, device=dev, dtype=torch.int64)
     w = _rng_words(rng, site, lin >> 2)
     e = lin & 3
     word = torch.where(e == 0, w[0], torch.where(e == 1, w[1], torch.where(e == 2, w[2], w[3])))
-    u = ((word >> 8).to(torch.float32) + 0.5) * (1.0 / 16777216.0)
+    u = ((word >> 9).to(torch.float32) + 0.5) * (1.0 / 8388608.0)
     return -torch.log(-torch.log(u))
 
 
