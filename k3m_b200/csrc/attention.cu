@@ -21,6 +21,8 @@ struct AttnArgs {
   DropSpec drop;
 };
 
+#include "attn_mma.cuh"
+
 __device__ __forceinline__ void load_tile(bf16* dst, int dstride, const bf16* src, int ld, int rows, int d) {
   // rows x d bf16, global row stride ld, 16 B vector loads (d % 8 == 0), smem row stride dstride
   const int vec_per_row = d >> 3;
@@ -216,6 +218,58 @@ int fill_args(AttnArgs* a, const void* q, int ldq, int q_off, const void* kv, in
   return K3M_OK;
 }
 
+// ---- tensor-core path dispatch (d in {16, 64, 96, 128}; up to 128 x 128 tokens per head) ----------------
+template <int D, int NKT>
+int launch_fwd_mma(const AttnArgs& a, bf16* ctx, int ldo, float* lse, cudaStream_t st) {
+  const int nw = (a.Lq + 15) / 16;
+  const size_t smem = (size_t)(nw * 16 + 2 * NKT * 8) * (D + 8) * 2;
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(attn_fwd_mma<D, NKT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 16 * 3 * (D + 8) * 2);
+    configured = true;
+  }
+  attn_fwd_mma<D, NKT><<<dim3(a.H, a.B), nw * 32, smem, st>>>(a, ctx, ldo, lse);
+  return k3m_check_launch("k3m_attn_fwd");
+}
+
+template <int D, int NKT>
+int launch_bwd_mma(const AttnArgs& a, const bf16* dctx, int ldo, const float* lse, bf16* dq, int lddq, bf16* dkv,
+                   int lddkv, cudaStream_t st) {
+  const int nw = (a.Lq + 15) / 16;
+  const size_t smem = (size_t)2 * (nw * 16 + NKT * 8) * (D + 8) * 2 + (size_t)2 * nw * 16 * (NKT * 8 + 8) * 2;
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(attn_bwd_mma<D, NKT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         2 * (128 + NKT * 8) * (D + 8) * 2 + 2 * 128 * (NKT * 8 + 8) * 2);
+    configured = true;
+  }
+  attn_bwd_mma<D, NKT><<<dim3(a.H, a.B), nw * 32, smem, st>>>(a, dctx, ldo, lse, dq, lddq, dkv, lddkv);
+  return k3m_check_launch("k3m_attn_bwd");
+}
+
+bool mma_ok(const AttnArgs& a) {
+  return (a.d == 16 || a.d == 64 || a.d == 96 || a.d == 128) && a.Lq <= 128 && a.Lk <= 128;
+}
+
+#define K3M_ATTN_DISPATCH(FN, ...)                                       \
+  do {                                                                   \
+    const bool small = a.Lk <= 48;                                       \
+    switch (a.d) {                                                       \
+      case 16: return small ? FN<16, 6>(__VA_ARGS__) : FN<16, 16>(__VA_ARGS__);    \
+      case 64: return small ? FN<64, 6>(__VA_ARGS__) : FN<64, 16>(__VA_ARGS__);    \
+      case 96: return small ? FN<96, 6>(__VA_ARGS__) : FN<96, 16>(__VA_ARGS__);    \
+      default: return small ? FN<128, 6>(__VA_ARGS__) : FN<128, 16>(__VA_ARGS__);  \
+    }                                                                    \
+  } while (0)
+
+int fwd_mma(const AttnArgs& a, bf16* ctx, int ldo, float* lse, cudaStream_t st) {
+  K3M_ATTN_DISPATCH(launch_fwd_mma, a, ctx, ldo, lse, st);
+}
+int bwd_mma(const AttnArgs& a, const bf16* dctx, int ldo, const float* lse, bf16* dq, int lddq, bf16* dkv, int lddkv,
+            cudaStream_t st) {
+  K3M_ATTN_DISPATCH(launch_bwd_mma, a, dctx, ldo, lse, dq, lddq, dkv, lddkv, st);
+}
+
 }  // namespace
 
 extern "C" int k3m_attn_fwd(const void* q, int ldq, int q_off, const void* kv, int ldkv, int k_off, int v_off,
@@ -224,6 +278,7 @@ extern "C" int k3m_attn_fwd(const void* q, int ldq, int q_off, const void* kv, i
   AttnArgs a;
   int rc = fill_args(&a, q, ldq, q_off, kv, ldkv, k_off, v_off, mask, B, H, Lq, Lk, d, rng, site, drop_p);
   if (rc) return rc;
+  if (mma_ok(a)) return fwd_mma(a, (bf16*)ctx, ldo, lse, reinterpret_cast<cudaStream_t>(stream));
   K3M_REQUIRE(Lk <= 32 * MAX_NJ, "attn_fwd: at most %d keys (Lk=%d)", 32 * MAX_NJ, Lk);
   const int lkp = (Lk + 7) & ~7;
   const size_t smem = (size_t)2 * Lk * (d + 2) * 2 + 4 + (size_t)4 * d * 4 + (size_t)4 * lkp * 4;
@@ -244,6 +299,9 @@ extern "C" int k3m_attn_bwd(const void* dctx, int ldo, const void* q, int ldq, i
   AttnArgs a;
   int rc = fill_args(&a, q, ldq, q_off, kv, ldkv, k_off, v_off, mask, B, H, Lq, Lk, d, rng, site, drop_p);
   if (rc) return rc;
+  K3M_REQUIRE(lddq % 8 == 0 && lddkv % 8 == 0 && ldo % 8 == 0, "attn_bwd: strides must be multiples of 8");
+  if (mma_ok(a))
+    return bwd_mma(a, (const bf16*)dctx, ldo, lse, (bf16*)dq, lddq, (bf16*)dkv, lddkv, reinterpret_cast<cudaStream_t>(stream));
   K3M_REQUIRE(Lk <= 128 && Lq <= 128, "attn_bwd: at most 128 x 128 tokens per head (Lq=%d Lk=%d)", Lq, Lk);
   K3M_REQUIRE(lddq % 8 == 0 && lddkv % 8 == 0 && ldo % 8 == 0, "attn_bwd: strides must be multiples of 8");
   const int lkp = (Lk + 7) & ~7;

@@ -1,0 +1,301 @@
+// Tensor-core attention for the short K3M sequences: one CTA per (batch, head), one warp per 16 query
+// rows, whole K / V of the head in shared memory, S = Q K^T and O = P V as warp-level bf16 MMAs
+// (m16n8k16, fp32 accumulate) with the softmax done on the accumulator registers (quad shuffles).
+// Tiles are far below the 128-row tcgen05 atom (L = 36..128, d = 64..128), so the 5th-gen tensor
+// core path would spend its time on TMEM allocation and barriers; mma.sync keeps a (b, h) problem
+// inside one small CTA and lets ~8 of them share an SM.
+//
+// Included by attention.cu inside its anonymous namespace (uses AttnArgs / DropSpec).
+#pragma once
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void ldsm_x4(uint32_t r[4], const void* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_addr(p)));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t r[4], const void* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_addr(p)));
+}
+__device__ __forceinline__ void mma16816(float c[4], const uint32_t a[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// rows x D bf16 tile -> shared memory with row stride DS; rows >= valid are zero-filled
+template <int D, int DS>
+__device__ __forceinline__ void load_tile_z(bf16* dst, const bf16* src, int ld, int valid, int rows) {
+  constexpr int VPR = D / 8;
+  for (int idx = threadIdx.x; idx < rows * VPR; idx += blockDim.x) {
+    const int r = idx / VPR, c = (idx % VPR) * 8;
+    uint4 u = make_uint4(0u, 0u, 0u, 0u);
+    if (r < valid) u = *reinterpret_cast<const uint4*>(src + (size_t)r * ld + c);
+    *reinterpret_cast<uint4*>(dst + (size_t)r * DS + c) = u;
+  }
+}
+
+// acc[t] (16 x 8 per key tile t) += A(16 x D rows i0.. of As) * B^T, B = rows of Bs (keys), both [.][DS]
+template <int D, int DS, int NKT>
+__device__ __forceinline__ void qk_mma(float (*acc)[4], const bf16* As, int i0, const bf16* Bs, int lane) {
+#pragma unroll
+  for (int kk = 0; kk < D / 16; ++kk) {
+    uint32_t af[4];
+    ldsm_x4(af, As + (size_t)(i0 + (lane & 15)) * DS + kk * 16 + (lane >> 4) * 8);
+#pragma unroll
+    for (int t = 0; t < NKT; t += 2) {
+      uint32_t bfr[4];
+      ldsm_x4(bfr, Bs + (size_t)(t * 8 + (lane & 7) + (lane >> 4) * 8) * DS + kk * 16 + ((lane >> 3) & 1) * 8);
+      mma16816(acc[t], af, bfr[0], bfr[1]);
+      mma16816(acc[t + 1], af, bfr[2], bfr[3]);
+    }
+  }
+}
+
+// dropout multipliers of one accumulator tile: row `prow`, key tile t, this thread's 2 columns (2q, 2q+1)
+__device__ __forceinline__ void drop_pair(const DropSpec& dr, unsigned long long prow, int lkp, int t, int q,
+                                          float& m0, float& m1) {
+  uint32_t w[4];
+  rng_words(dr.rng, dr.site, (prow * (unsigned long long)lkp >> 3) + (unsigned long long)t, w);
+  const uint32_t x = w[q];
+  m0 = (x & 0xFFFFu) >= dr.thresh ? dr.scale : 0.f;
+  m1 = (x >> 16) >= dr.thresh ? dr.scale : 0.f;
+}
+
+template <int D, int NKT>
+__global__ void __launch_bounds__(256) attn_fwd_mma(AttnArgs a, bf16* __restrict__ ctx, int ldo, float* __restrict__ lse_out) {
+  constexpr int DS = D + 8, LKP = NKT * 8;
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int Lq = a.Lq, Lk = a.Lk;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int LQP = nw * 16;
+  bf16* Qs = reinterpret_cast<bf16*>(smem);
+  bf16* Ks = Qs + (size_t)LQP * DS;
+  bf16* Vs = Ks + (size_t)LKP * DS;
+  load_tile_z<D, DS>(Qs, a.q + (size_t)b * Lq * a.ldq + a.q_off + h * D, a.ldq, Lq, LQP);
+  load_tile_z<D, DS>(Ks, a.kv + (size_t)b * Lk * a.ldkv + a.k_off + h * D, a.ldkv, Lk, LKP);
+  load_tile_z<D, DS>(Vs, a.kv + (size_t)b * Lk * a.ldkv + a.v_off + h * D, a.ldkv, Lk, LKP);
+  __syncthreads();
+  const int g = lane >> 2, q = lane & 3, i0 = warp * 16;
+  float s[NKT][4];
+#pragma unroll
+  for (int t = 0; t < NKT; ++t) s[t][0] = s[t][1] = s[t][2] = s[t][3] = 0.f;
+  qk_mma<D, DS, NKT>(s, Qs, i0, Ks, lane);
+  const float* mrow = a.mask + (size_t)b * Lk;
+  float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+  for (int t = 0; t < NKT; ++t) {
+    const int j = t * 8 + 2 * q;
+    const float ma = j < Lk ? mrow[j] : -INFINITY, mb = j + 1 < Lk ? mrow[j + 1] : -INFINITY;
+    s[t][0] = fmaf(s[t][0], a.scale, ma); s[t][1] = fmaf(s[t][1], a.scale, mb);
+    s[t][2] = fmaf(s[t][2], a.scale, ma); s[t][3] = fmaf(s[t][3], a.scale, mb);
+    mx0 = fmaxf(mx0, fmaxf(s[t][0], s[t][1]));
+    mx1 = fmaxf(mx1, fmaxf(s[t][2], s[t][3]));
+  }
+  mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+  mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+  float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+  for (int t = 0; t < NKT; ++t) {
+    s[t][0] = __expf(s[t][0] - mx0); s[t][1] = __expf(s[t][1] - mx0);
+    s[t][2] = __expf(s[t][2] - mx1); s[t][3] = __expf(s[t][3] - mx1);
+    sum0 += s[t][0] + s[t][1];
+    sum1 += s[t][2] + s[t][3];
+  }
+  sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+  sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+  const int r0 = i0 + g, r1 = i0 + g + 8;
+  const unsigned long long prow0 = (unsigned long long)(b * a.H + h) * Lq + r0, prow1 = prow0 + 8;
+  if (q == 0) {
+    if (r0 < Lq) lse_out[prow0] = mx0 + __logf(sum0);
+    if (r1 < Lq) lse_out[prow1] = mx1 + __logf(sum1);
+  }
+  const float inv0 = 1.0f / sum0, inv1 = 1.0f / sum1;
+  const int lkp = (Lk + 7) & ~7;
+#pragma unroll
+  for (int t = 0; t < NKT; ++t) {
+    float m00 = 1.f, m01 = 1.f, m10 = 1.f, m11 = 1.f;
+    if (a.drop.thresh && t * 8 < Lk) {
+      if (r0 < Lq) drop_pair(a.drop, prow0, lkp, t, q, m00, m01);
+      if (r1 < Lq) drop_pair(a.drop, prow1, lkp, t, q, m10, m11);
+    }
+    s[t][0] *= inv0 * m00; s[t][1] *= inv0 * m01;
+    s[t][2] *= inv1 * m10; s[t][3] *= inv1 * m11;
+  }
+  // O = P V : P from the accumulator registers (bf16), V^T fragments by transposing ldmatrix
+  float o[D / 8][4];
+#pragma unroll
+  for (int c = 0; c < D / 8; ++c) o[c][0] = o[c][1] = o[c][2] = o[c][3] = 0.f;
+#pragma unroll
+  for (int kt = 0; kt < NKT / 2; ++kt) {
+    uint32_t pf[4];
+    pf[0] = pack_bf16(s[2 * kt][0], s[2 * kt][1]);
+    pf[1] = pack_bf16(s[2 * kt][2], s[2 * kt][3]);
+    pf[2] = pack_bf16(s[2 * kt + 1][0], s[2 * kt + 1][1]);
+    pf[3] = pack_bf16(s[2 * kt + 1][2], s[2 * kt + 1][3]);
+#pragma unroll
+    for (int c = 0; c < D / 8; c += 2) {
+      uint32_t vf[4];
+      ldsm_x4_t(vf, Vs + (size_t)(kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * DS + c * 8 + (lane >> 4) * 8);
+      mma16816(o[c], pf, vf[0], vf[1]);
+      mma16816(o[c + 1], pf, vf[2], vf[3]);
+    }
+  }
+  bf16* o0 = ctx + (size_t)(b * Lq + r0) * ldo + h * D + 2 * q;
+  bf16* o1 = ctx + (size_t)(b * Lq + r1) * ldo + h * D + 2 * q;
+#pragma unroll
+  for (int c = 0; c < D / 8; ++c) {
+    if (r0 < Lq) *reinterpret_cast<uint32_t*>(o0 + c * 8) = pack_bf16(o[c][0], o[c][1]);
+    if (r1 < Lq) *reinterpret_cast<uint32_t*>(o1 + c * 8) = pack_bf16(o[c][2], o[c][3]);
+  }
+}
+
+// Backward.  P is recomputed from Q, K and the saved log-sum-exp.
+//   dp_ij = m_ij (dO_i . V_j) ; D_i = sum_j p_ij dp_ij ; dS_ij = p_ij (dp_ij - D_i)
+//   dQ = scale * dS K ;  dK = scale * dS^T Q ;  dV = (P m)^T dO
+// Phase 1: one warp per 16 query rows (S, dP, dS, dQ; P m and dS go to shared memory as bf16).
+// Phase 2: one warp per 16 key rows (dV, dK) with the transposed operands read by ldmatrix.trans.
+template <int D, int NKT>
+__global__ void __launch_bounds__(256) attn_bwd_mma(AttnArgs a, const bf16* __restrict__ dctx, int ldo,
+                                                    const float* __restrict__ lse, bf16* __restrict__ dq, int lddq,
+                                                    bf16* __restrict__ dkv, int lddkv) {
+  constexpr int DS = D + 8, LKP = NKT * 8, PS = LKP + 8;
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int Lq = a.Lq, Lk = a.Lk;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int LQP = nw * 16;
+  bf16* Qs = reinterpret_cast<bf16*>(smem);
+  bf16* dOs = Qs + (size_t)LQP * DS;
+  bf16* Ks = dOs + (size_t)LQP * DS;
+  bf16* Vs = Ks + (size_t)LKP * DS;
+  bf16* Ps = Vs + (size_t)LKP * DS;      // [LQP][PS]  dropped probabilities
+  bf16* Ss = Ps + (size_t)LQP * PS;      // [LQP][PS]  dS
+  load_tile_z<D, DS>(Qs, a.q + (size_t)b * Lq * a.ldq + a.q_off + h * D, a.ldq, Lq, LQP);
+  load_tile_z<D, DS>(dOs, dctx + (size_t)b * Lq * ldo + h * D, ldo, Lq, LQP);
+  load_tile_z<D, DS>(Ks, a.kv + (size_t)b * Lk * a.ldkv + a.k_off + h * D, a.ldkv, Lk, LKP);
+  load_tile_z<D, DS>(Vs, a.kv + (size_t)b * Lk * a.ldkv + a.v_off + h * D, a.ldkv, Lk, LKP);
+  __syncthreads();
+  const int g = lane >> 2, q = lane & 3, i0 = warp * 16;
+  const int lkp = (Lk + 7) & ~7;
+  {
+    float s[NKT][4], dp[NKT][4];
+#pragma unroll
+    for (int t = 0; t < NKT; ++t) {
+      s[t][0] = s[t][1] = s[t][2] = s[t][3] = 0.f;
+      dp[t][0] = dp[t][1] = dp[t][2] = dp[t][3] = 0.f;
+    }
+    qk_mma<D, DS, NKT>(s, Qs, i0, Ks, lane);
+    qk_mma<D, DS, NKT>(dp, dOs, i0, Vs, lane);
+    const int r0 = i0 + g, r1 = i0 + g + 8;
+    const unsigned long long prow0 = (unsigned long long)(b * a.H + h) * Lq + r0, prow1 = prow0 + 8;
+    const float l0 = r0 < Lq ? lse[prow0] : 0.f, l1 = r1 < Lq ? lse[prow1] : 0.f;
+    const float* mrow = a.mask + (size_t)b * Lk;
+    float D0 = 0.f, D1 = 0.f;
+    uint32_t pm[NKT][2];     // dropped P, packed, kept for the smem store
+#pragma unroll
+    for (int t = 0; t < NKT; ++t) {
+      const int j = t * 8 + 2 * q;
+      const bool v0 = j < Lk, v1 = j + 1 < Lk;
+      const float ma = v0 ? mrow[j] : 0.f, mb = v1 ? mrow[j + 1] : 0.f;
+      float p00 = (v0 && r0 < Lq) ? __expf(fmaf(s[t][0], a.scale, ma) - l0) : 0.f;
+      float p01 = (v1 && r0 < Lq) ? __expf(fmaf(s[t][1], a.scale, mb) - l0) : 0.f;
+      float p10 = (v0 && r1 < Lq) ? __expf(fmaf(s[t][2], a.scale, ma) - l1) : 0.f;
+      float p11 = (v1 && r1 < Lq) ? __expf(fmaf(s[t][3], a.scale, mb) - l1) : 0.f;
+      float m00 = 1.f, m01 = 1.f, m10 = 1.f, m11 = 1.f;
+      if (a.drop.thresh && t * 8 < Lk) {
+        if (r0 < Lq) drop_pair(a.drop, prow0, lkp, t, q, m00, m01);
+        if (r1 < Lq) drop_pair(a.drop, prow1, lkp, t, q, m10, m11);
+      }
+      dp[t][0] *= m00; dp[t][1] *= m01; dp[t][2] *= m10; dp[t][3] *= m11;
+      D0 += p00 * dp[t][0] + p01 * dp[t][1];
+      D1 += p10 * dp[t][2] + p11 * dp[t][3];
+      pm[t][0] = pack_bf16(p00 * m00, p01 * m01);
+      pm[t][1] = pack_bf16(p10 * m10, p11 * m11);
+      s[t][0] = p00; s[t][1] = p01; s[t][2] = p10; s[t][3] = p11;
+    }
+    D0 += __shfl_xor_sync(0xffffffffu, D0, 1); D0 += __shfl_xor_sync(0xffffffffu, D0, 2);
+    D1 += __shfl_xor_sync(0xffffffffu, D1, 1); D1 += __shfl_xor_sync(0xffffffffu, D1, 2);
+    uint32_t dsf[NKT][2];
+#pragma unroll
+    for (int t = 0; t < NKT; ++t) {
+      dsf[t][0] = pack_bf16(s[t][0] * (dp[t][0] - D0), s[t][1] * (dp[t][1] - D0));
+      dsf[t][1] = pack_bf16(s[t][2] * (dp[t][2] - D1), s[t][3] * (dp[t][3] - D1));
+      const int j = t * 8 + 2 * q;
+      *reinterpret_cast<uint32_t*>(Ps + (size_t)r0 * PS + j) = pm[t][0];
+      *reinterpret_cast<uint32_t*>(Ps + (size_t)r1 * PS + j) = pm[t][1];
+      *reinterpret_cast<uint32_t*>(Ss + (size_t)r0 * PS + j) = dsf[t][0];
+      *reinterpret_cast<uint32_t*>(Ss + (size_t)r1 * PS + j) = dsf[t][1];
+    }
+    // dQ = scale * dS K   (A = dS from registers, B[k = key][n = channel] by transposing ldmatrix on K)
+    float o[D / 8][4];
+#pragma unroll
+    for (int c = 0; c < D / 8; ++c) o[c][0] = o[c][1] = o[c][2] = o[c][3] = 0.f;
+#pragma unroll
+    for (int kt = 0; kt < NKT / 2; ++kt) {
+      uint32_t af[4] = {dsf[2 * kt][0], dsf[2 * kt][1], dsf[2 * kt + 1][0], dsf[2 * kt + 1][1]};
+#pragma unroll
+      for (int c = 0; c < D / 8; c += 2) {
+        uint32_t kf[4];
+        ldsm_x4_t(kf, Ks + (size_t)(kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * DS + c * 8 + (lane >> 4) * 8);
+        mma16816(o[c], af, kf[0], kf[1]);
+        mma16816(o[c + 1], af, kf[2], kf[3]);
+      }
+    }
+    bf16* q0 = dq + (size_t)(b * Lq + r0) * lddq + a.q_off + h * D + 2 * q;
+    bf16* q1 = dq + (size_t)(b * Lq + r1) * lddq + a.q_off + h * D + 2 * q;
+#pragma unroll
+    for (int c = 0; c < D / 8; ++c) {
+      if (r0 < Lq) *reinterpret_cast<uint32_t*>(q0 + c * 8) = pack_bf16(o[c][0] * a.scale, o[c][1] * a.scale);
+      if (r1 < Lq) *reinterpret_cast<uint32_t*>(q1 + c * 8) = pack_bf16(o[c][2] * a.scale, o[c][3] * a.scale);
+    }
+  }
+  __syncthreads();
+  // phase 2: key tiles
+  for (int jt = warp; jt < NKT / 2; jt += nw) {
+    const int j0 = jt * 16;
+    float dv[D / 8][4], dk[D / 8][4];
+#pragma unroll
+    for (int c = 0; c < D / 8; ++c) {
+      dv[c][0] = dv[c][1] = dv[c][2] = dv[c][3] = 0.f;
+      dk[c][0] = dk[c][1] = dk[c][2] = dk[c][3] = 0.f;
+    }
+    for (int it = 0; it < LQP / 16; ++it) {
+      uint32_t pa[4], sa[4];
+      const size_t off = (size_t)(it * 16 + (lane & 7) + (lane >> 4) * 8) * PS + j0 + ((lane >> 3) & 1) * 8;
+      ldsm_x4_t(pa, Ps + off);
+      ldsm_x4_t(sa, Ss + off);
+#pragma unroll
+      for (int c = 0; c < D / 8; c += 2) {
+        uint32_t of[4], qf[4];
+        const size_t boff = (size_t)(it * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * DS + c * 8 + (lane >> 4) * 8;
+        ldsm_x4_t(of, dOs + boff);
+        ldsm_x4_t(qf, Qs + boff);
+        mma16816(dv[c], pa, of[0], of[1]);
+        mma16816(dv[c + 1], pa, of[2], of[3]);
+        mma16816(dk[c], sa, qf[0], qf[1]);
+        mma16816(dk[c + 1], sa, qf[2], qf[3]);
+      }
+    }
+    const int r0 = j0 + g, r1 = j0 + g + 8;
+    bf16* k0 = dkv + (size_t)(b * Lk + r0) * lddkv + h * D + 2 * q;
+    bf16* k1 = dkv + (size_t)(b * Lk + r1) * lddkv + h * D + 2 * q;
+#pragma unroll
+    for (int c = 0; c < D / 8; ++c) {
+      if (r0 < Lk) {
+        *reinterpret_cast<uint32_t*>(k0 + a.k_off + c * 8) = pack_bf16(dk[c][0] * a.scale, dk[c][1] * a.scale);
+        *reinterpret_cast<uint32_t*>(k0 + a.v_off + c * 8) = pack_bf16(dv[c][0], dv[c][1]);
+      }
+      if (r1 < Lk) {
+        *reinterpret_cast<uint32_t*>(k1 + a.k_off + c * 8) = pack_bf16(dk[c][2] * a.scale, dk[c][3] * a.scale);
+        *reinterpret_cast<uint32_t*>(k1 + a.v_off + c * 8) = pack_bf16(dv[c][2], dv[c][3]);
+      }
+    }
+  }
+}

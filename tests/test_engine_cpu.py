@@ -8,7 +8,7 @@ from oracle.ops_ref import RefOps
 from tests.util import case_setup, compare_with_golden, load_golden, run_engine
 
 
-@pytest.mark.parametrize("name", ["tiny_hard", "tiny_mean", "tiny_inter", "base_hard"])
+@pytest.mark.parametrize("name", ["tiny_hard", "tiny_mean", "tiny_inter", "base_hard", "base_mean"])
 def test_schedule_matches_reference_fp32(name):
     fx = load_golden(name)
     cfg, sd, batch, noise = case_setup(fx)

@@ -243,7 +243,8 @@ def test_attn_fwd(ops, ref, B, H, Lq, Lk, d, drop):
     ctx, lse = ops.attn_fwd(qbuf, 0, kvbuf, H * d, 2 * H * d, mask, B, H, Lq, Lk, d, drop=drop, rng=r)
     ctxr, lser = ref.attn_fwd(qbuf, 0, kvbuf, H * d, 2 * H * d, mask, B, H, Lq, Lk, d, drop=drop, rng=r)
     close(lse, lser, 1e-5, 1e-4, "lse")
-    close_bf16(ctx, ctxr, "ctx", atol=2e-3)
+    # P is rounded to bf16 before the P V tensor-core product (2^-9 relative per term, like flash-attention)
+    close_bf16(ctx, ctxr, "ctx", atol=8e-3)
 
 
 @pytest.mark.parametrize("B,H,Lq,Lk,d", ATTN)

@@ -21,7 +21,7 @@ def _run_oracle(fx):
     return out, sdo
 
 
-@pytest.mark.parametrize("name", CASES + ["base_hard"])
+@pytest.mark.parametrize("name", CASES + ["base_hard", "base_mean"])
 def test_oracle_matches_golden(name):
     fx = load_golden(name)
     out, sdo = _run_oracle(fx)
@@ -41,8 +41,9 @@ def test_oracle_matches_golden(name):
         tol = 1e-5 * ref["maxabs"] + 1e-7
         assert float((g[sample_index(g.numel())] - ref["sample"]).abs().max()) <= tol, n
         assert abs(float(g.norm()) - ref["norm"]) <= 1e-4 * ref["norm"] + 1e-7, n
-    if name == "base_hard":
-        assert n_none == 86 and len(fx["grads"]) == 998
+    if name in ("base_hard", "base_mean"):
+        # 86 never-trained tensors; the 18 score_* gate tensors join them unless if_pre_sampling == 1
+        assert n_none == (86 if name == "base_hard" else 104) and len(fx["grads"]) == 998
 
 
 @pytest.mark.skipif(not ref_harness.available(), reason="reference tree not mounted")

@@ -28,12 +28,14 @@ CASES = {
     "tiny_hard": (K3M_TINY, dict(if_pre_sampling=1, margin=10.0, num_negative_pv=4), 4, 12, 9, 20, 4, 1, 7, 5, 3),
     "tiny_mean": (K3M_TINY, dict(if_pre_sampling=0, margin=1.0, num_negative_pv=4), 3, 16, 8, 24, 5, 2, 8, 0, 4),
     "tiny_inter": (K3M_TINY, dict(if_pre_sampling=3, margin=10.0, num_negative_pv=2), 5, 8, 12, 16, 3, 3, 9, 0, 5),
+    "base_mean": (K3M_BASE_6LAYER_6CONNECT, dict(if_pre_sampling=0, margin=10.0, num_negative_pv=4),
+                  4, 36, 36, 36, 8, 1, 7, 0, 3),
     "base_hard": (K3M_BASE_6LAYER_6CONNECT, dict(if_pre_sampling=1, margin=10.0, num_negative_pv=4),
                   4, 36, 36, 36, 8, 1, 7, 5, 3),
 }
 
 
-def sample_index(numel, k=16):
+def sample_index(numel, k=256):
     g = torch.Generator().manual_seed(numel)
     return torch.randint(0, numel, (k,), generator=g)
 
