@@ -15,6 +15,7 @@
 #include <cuda.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <map>
 #include <mutex>
@@ -29,7 +30,8 @@ constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle row
 
 struct GemmParams {
   int M, N, K;
-  int kb_per_split;  // k-blocks handled by one CTA along grid.z
+  int kb_per_split;  // k-blocks of one K-split
+  int tiles_m, tiles_n, splits;
   void* out;
   int ldc, out_f32, accumulate;
   const bf16* bias;
@@ -110,34 +112,118 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
   return d;
 }
 
+// fused epilogue of one 32-column chunk of one output row (accumulators in r[], fp32 bit patterns)
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t r[32], int row, int col0, bool has_drop) {
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    const int col = col0 + g * 8;
+    if (col >= p.N) break;
+    const int nv = (p.N - col) < 8 ? (p.N - col) : 8;
+    const bool vec = p.vec_ok && nv == 8;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+    if (p.bias) {
+      float t[8];
+      if (vec) ld8(p.bias + col, t);
+      else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(p.bias + col + j) : 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += t[j];
+    }
+    if (p.act == ACT_GELU) {
+      if (p.aux_out) {
+        bf16* ao = p.aux_out + (size_t)row * p.ld_aux_out + col;
+        if (vec) st8(ao, v);
+        else for (int j = 0; j < nv; ++j) st_f(ao + j, v[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
+    } else if (p.act == ACT_DGELU || p.act == ACT_DTANH) {
+      const bf16* ai = p.aux_in + (size_t)row * p.ld_aux_in + col;
+      float t[8];
+      if (vec) ld8(ai, t);
+      else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ai + j) : 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] *= (p.act == ACT_DGELU) ? dgelu_f(t[j]) : (1.0f - t[j] * t[j]);
+    } else if (p.act == ACT_SIGMOID) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = sigmoid_f(v[j]);
+    } else if (p.act == ACT_TANH) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = tanhf(v[j]);
+    }
+    if (has_drop) {
+      uint32_t w[4];
+      const unsigned long long lin = (unsigned long long)row * (unsigned long long)p.drop_ld + (unsigned long long)col;
+      rng_words(p.drop.rng, p.drop.site, lin >> 3, w);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] *= drop_mult(p.drop, w, j);
+    }
+    if (p.addend) {
+      float t[8];
+      if (p.addend_f32) {
+        const float* ad = reinterpret_cast<const float*>(p.addend) + (size_t)row * p.ld_add + col;
+        if (vec) ld8(ad, t);
+        else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ad[j] : 0.f;
+      } else {
+        const bf16* ad = reinterpret_cast<const bf16*>(p.addend) + (size_t)row * p.ld_add + col;
+        if (vec) ld8(ad, t);
+        else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ad + j) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += t[j];
+    }
+    if (p.out_f32) {
+      float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col;
+      if (p.accumulate) {
+        for (int j = 0; j < nv; ++j) atomicAdd(o + j, v[j]);
+      } else if (vec) {
+        st8(o, v);
+      } else {
+        for (int j = 0; j < nv; ++j) o[j] = v[j];
+      }
+    } else {
+      bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)row * p.ldc + col;
+      if (vec) st8(o, v);
+      else for (int j = 0; j < nv; ++j) st_f(o + j, v[j]);
+    }
+  }
+}
+
+// Persistent, warp-specialised: every CTA walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...
+// (tile = (split, m, n), n fastest so neighbouring CTAs share the A panel in L2).  The smem ring
+// (TMA -> MMA) runs across tile boundaries and the accumulator is double-buffered in TMEM, so the
+// epilogue of tile i overlaps the main loop of tile i + 1.
 template <int BN, int STAGES, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(192, (BN <= 128 ? 2 : 1))
 gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, GemmParams p) {
   constexpr int A_BYTES = BM * BK * 2;
   constexpr int B_BYTES = BN * BK * 2;
-  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+  constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * A_BYTES;
   uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
   uint64_t* empty = full + STAGES;
-  uint64_t* tmem_full = empty + STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tmem_full = empty + STAGES;   // [2]
+  uint64_t* tmem_empty = tmem_full + 2;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
   const int total_kb = (p.K + BK - 1) / BK;
-  const int kb0 = blockIdx.z * p.kb_per_split;
-  int nkb = total_kb - kb0;
-  if (nkb > p.kb_per_split) nkb = p.kb_per_split;
+  const int tiles_mn = p.tiles_m * p.tiles_n;
+  const int total_tiles = tiles_mn * p.splits;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    mbar_init(tmem_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 4);      // one arrive per epilogue warp
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -152,25 +238,35 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
 
   if (warp == 0) {
     if (lane == 0) {
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % STAGES;
-        const uint32_t ph = (i / STAGES) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
-        mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
-        const int k0 = (kb0 + i) * BK;
-        uint8_t* a = sA + s * A_BYTES;
-        uint8_t* b = sB + s * B_BYTES;
-        if (A_MN) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int split = tile / tiles_mn, mn = tile % tiles_mn;
+        const int m0 = (mn / p.tiles_n) * BM, n0 = (mn % p.tiles_n) * BN;
+        const int kb0 = split * p.kb_per_split;
+        int nkb = total_kb - kb0;
+        if (nkb > p.kb_per_split) nkb = p.kb_per_split;
+        for (int i = 0; i < nkb; ++i, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
+          const int k0 = (kb0 + i) * BK;
+          uint8_t* a = sA + s * A_BYTES;
+          uint8_t* b = sB + s * B_BYTES;
+          if (A_MN) {
 #pragma unroll
-          for (int c = 0; c < BM / 64; ++c) tma_load_2d(a + c * 8192, &map_a, &full[s], m0 + c * 64, k0);
-        } else {
-          tma_load_2d(a, &map_a, &full[s], k0, m0);
-        }
-        if (B_MN) {
+            for (int c = 0; c < BM / 64; ++c) tma_load_2d(a + c * 8192, &map_a, &full[s], m0 + c * 64, k0);
+          } else {
+            tma_load_2d(a, &map_a, &full[s], k0, m0);
+          }
+          if (B_MN) {
 #pragma unroll
-          for (int c = 0; c < BN / 64; ++c) tma_load_2d(b + c * 8192, &map_b, &full[s], n0 + c * 64, k0);
-        } else {
-          tma_load_2d(b, &map_b, &full[s], k0, n0);
+            for (int c = 0; c < BN / 64; ++c) tma_load_2d(b + c * 8192, &map_b, &full[s], n0 + c * 64, k0);
+          } else {
+            tma_load_2d(b, &map_b, &full[s], k0, n0);
+          }
         }
       }
     }
@@ -178,116 +274,56 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     if (lane == 0) {
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) |
                                  ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % STAGES;
-        const uint32_t ph = (i / STAGES) & 1;
-        mbar_wait(&full[s], ph);
+      uint32_t it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+        const int split = tile / tiles_mn;
+        const int kb0 = split * p.kb_per_split;
+        int nkb = total_kb - kb0;
+        if (nkb > p.kb_per_split) nkb = p.kb_per_split;
+        const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
+        mbar_wait(&tmem_empty[as], aph ^ 1);          // epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t a = smem_u32(sA + s * A_BYTES), b = smem_u32(sB + s * B_BYTES);
+        const uint32_t tacc = tmem_base + as * BN;
+        for (int i = 0; i < nkb; ++i, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait(&full[s], ph);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a = smem_u32(sA + s * A_BYTES), b = smem_u32(sB + s * B_BYTES);
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          const uint64_t da = A_MN ? make_desc(a + k * 2048, 8192, 1024) : make_desc(a + k * 32, 0, 1024);
-          const uint64_t db = B_MN ? make_desc(b + k * 2048, 8192, 1024) : make_desc(b + k * 32, 0, 1024);
-          umma_bf16(tmem_base, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = A_MN ? make_desc(a + k * 2048, 8192, 1024) : make_desc(a + k * 32, 0, 1024);
+            const uint64_t db = B_MN ? make_desc(b + k * 2048, 8192, 1024) : make_desc(b + k * 32, 0, 1024);
+            umma_bf16(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty[s]);
         }
-        umma_commit(&empty[s]);
+        umma_commit(&tmem_full[as]);
       }
-      umma_commit(tmem_full);
     }
   } else {
-    // ---- epilogue -------------------------------------------------------------------------------
+    // ---- epilogue warps 2..5: TMEM lanes 32*(warp%4) .. +31, one output row per thread ----
     const int q = warp & 3;
-    const int row = m0 + q * 32 + lane;
-    const bool row_ok = row < p.M;
-    if (nkb > 0) {
-      mbar_wait(tmem_full, 0);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    }
     const bool has_drop = p.drop.thresh != 0;
+    uint32_t lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int mn = tile % tiles_mn;
+      const int m0 = (mn / p.tiles_n) * BM, n0 = (mn % p.tiles_n) * BN;
+      const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < p.M;
+      mbar_wait(&tmem_full[as], aph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-      uint32_t r[32];
-      if (nkb > 0) {
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), r);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) r[j] = 0;
+      for (int c = 0; c < BN / 32; ++c) {
+        if (n0 + c * 32 >= p.N) break;
+        uint32_t r[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)(c * 32), r);
+        if (row_ok) epilogue_chunk(p, r, row, n0 + c * 32, has_drop);
       }
-      if (!row_ok) continue;
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const int col = n0 + c * 32 + g * 8;
-        if (col >= p.N) break;
-        const int nv = (p.N - col) < 8 ? (p.N - col) : 8;
-        const bool vec = p.vec_ok && nv == 8;
-        float v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
-        if (p.bias) {
-          float t[8];
-          if (vec) ld8(p.bias + col, t);
-          else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(p.bias + col + j) : 0.f;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] += t[j];
-        }
-        if (p.act == ACT_GELU) {
-          if (p.aux_out) {
-            bf16* ao = p.aux_out + (size_t)row * p.ld_aux_out + col;
-            if (vec) st8(ao, v);
-            else for (int j = 0; j < nv; ++j) st_f(ao + j, v[j]);
-          }
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
-        } else if (p.act == ACT_DGELU || p.act == ACT_DTANH) {
-          const bf16* ai = p.aux_in + (size_t)row * p.ld_aux_in + col;
-          float t[8];
-          if (vec) ld8(ai, t);
-          else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ai + j) : 0.f;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] *= (p.act == ACT_DGELU) ? dgelu_f(t[j]) : (1.0f - t[j] * t[j]);
-        } else if (p.act == ACT_SIGMOID) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = sigmoid_f(v[j]);
-        } else if (p.act == ACT_TANH) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = tanhf(v[j]);
-        }
-        if (has_drop) {
-          uint32_t w[4];
-          const unsigned long long lin = (unsigned long long)row * (unsigned long long)p.drop_ld + (unsigned long long)col;
-          rng_words(p.drop.rng, p.drop.site, lin >> 3, w);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] *= drop_mult(p.drop, w, j);
-        }
-        if (p.addend) {
-          float t[8];
-          if (p.addend_f32) {
-            const float* ad = reinterpret_cast<const float*>(p.addend) + (size_t)row * p.ld_add + col;
-            if (vec) ld8(ad, t);
-            else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ad[j] : 0.f;
-          } else {
-            const bf16* ad = reinterpret_cast<const bf16*>(p.addend) + (size_t)row * p.ld_add + col;
-            if (vec) ld8(ad, t);
-            else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ad + j) : 0.f;
-          }
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] += t[j];
-        }
-        if (p.out_f32) {
-          float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col;
-          if (p.accumulate) {
-            for (int j = 0; j < nv; ++j) atomicAdd(o + j, v[j]);
-          } else if (vec) {
-            st8(o, v);
-          } else {
-            for (int j = 0; j < nv; ++j) o[j] = v[j];
-          }
-        } else {
-          bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)row * p.ldc + col;
-          if (vec) st8(o, v);
-          else for (int j = 0; j < nv; ++j) st_f(o + j, v[j]);
-        }
-      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[as])) : "memory");
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -357,9 +393,19 @@ bool get_map(const void* ptr, int inner, int outer, int ld, int box_inner, int b
   return true;
 }
 
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  }
+  return n;
+}
+
 template <int BN, int STAGES, bool A_MN, bool B_MN>
-int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int splits, cudaStream_t st) {
-  constexpr int SMEM = STAGES * (BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 1) * 8 + 16 + 1024;
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams p, cudaStream_t st) {
+  constexpr int SMEM = STAGES * (BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 4) * 8 + 16 + 1024;
   static bool configured = false;
   auto kern = gemm_kernel<BN, STAGES, A_MN, B_MN>;
   if (!configured) {
@@ -369,15 +415,31 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, in
     }
     configured = true;
   }
-  dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM, splits);
+  p.tiles_m = (p.M + BM - 1) / BM;
+  p.tiles_n = (p.N + BN - 1) / BN;
+  const int total = p.tiles_m * p.tiles_n * p.splits;
+  const int resident = num_sms() * (BN <= 128 ? 2 : 1);
+  const int grid = total < resident ? total : resident;
   kern<<<grid, 192, SMEM, st>>>(ma, mb, p);
   return k3m_check_launch("k3m_gemm_bf16");
 }
 
 template <bool A_MN, bool B_MN>
-int dispatch(int bn, const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int splits, cudaStream_t st) {
-  if (bn == 64) return launch<64, 4, A_MN, B_MN>(ma, mb, p, splits, st);
-  return launch<128, 3, A_MN, B_MN>(ma, mb, p, splits, st);
+int dispatch(int bn, const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st) {
+  if (bn == 64) return launch<64, 4, A_MN, B_MN>(ma, mb, p, st);
+  if (bn == 256) return launch<256, 4, A_MN, B_MN>(ma, mb, p, st);
+  return launch<128, 3, A_MN, B_MN>(ma, mb, p, st);
+}
+
+// tile width.  Measured on B200 (tools/bench_gemm.py): two co-resident 128 x 128 CTAs per SM beat one
+// 128 x 256 CTA whenever the main loop is short (K <= 3072: the epilogue of a 256-wide tile is twice as
+// long and only one CTA's epilogue warps work on it); long-K problems (weight gradients, vocab dgrad)
+// prefer the wider tile, which reads A once per 256 output columns.
+int pick_bn(int M, int N, int K, int force) {
+  if (N <= 64) return 64;
+  if (force == 64 || force == 128 || force == 256) return force;
+  (void)M;
+  return (K >= 4096 && N >= 256) ? 256 : 128;
 }
 
 }  // namespace
@@ -394,7 +456,8 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   K3M_REQUIRE(!accumulate || out_f32, "gemm: accumulate needs an fp32 output");
   K3M_REQUIRE(!(act == ACT_DGELU || act == ACT_DTANH) || aux_in, "gemm: activation-derivative epilogue needs aux_in");
   const bool a_mn = layout == 2, b_mn = layout != 0;
-  const int bn = (N <= 64) ? 64 : 128;
+  static const int force_bn = getenv("K3M_GEMM_BN") ? atoi(getenv("K3M_GEMM_BN")) : 0;
+  const int bn = pick_bn(M, N, K, force_bn);
   CUtensorMap ma, mb;
   // A: K-major -> tensor [M, K]; MN-major -> tensor [K, M]
   if (!(a_mn ? get_map(a, M, K, lda, 64, 64, &ma) : get_map(a, K, M, lda, 64, BM, &ma))) return K3M_ERR_CUDA;
@@ -405,10 +468,12 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   int splits = 1;
   if (accumulate) {
     const int tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
-    while (tiles * splits < 148 && total_kb / (splits * 2) >= 4) splits *= 2;
+    const int resident = num_sms() * (bn <= 128 ? 2 : 1);
+    while (tiles * splits * 2 <= resident && total_kb / (splits * 2) >= 4) splits *= 2;
   }
   p.kb_per_split = (total_kb + splits - 1) / splits;
   splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.splits = splits;
   p.out = out; p.ldc = ldc; p.out_f32 = out_f32; p.accumulate = accumulate;
   p.bias = reinterpret_cast<const bf16*>(bias);
   p.act = act;
@@ -424,7 +489,7 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   p.vec_ok = al(out, ldc, out_f32 ? 4 : 2) && al(bias, 8, 2) && al(aux_in, ld_aux_in, 2) && al(aux_out, ld_aux_out, 2) &&
              al(addend, ld_add, addend_f32 ? 4 : 2) && (!out_f32 || (ldc % 8 == 0 && (((uintptr_t)out) & 31) == 0));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (layout == 0) return dispatch<false, false>(bn, ma, mb, p, splits, st);
-  if (layout == 1) return dispatch<false, true>(bn, ma, mb, p, splits, st);
-  return dispatch<true, true>(bn, ma, mb, p, splits, st);
+  if (layout == 0) return dispatch<false, false>(bn, ma, mb, p, st);
+  if (layout == 1) return dispatch<false, true>(bn, ma, mb, p, st);
+  return dispatch<true, true>(bn, ma, mb, p, st);
 }
