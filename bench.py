@@ -240,6 +240,13 @@ def run_gpu_arm(args):
     peaks = load_peaks()
     kb = kernel_breakdown(step, host[0])
     tot_ms = sum(v[1] for v in kb.values())
+    shapes = {k: v for k, v in kb.items() if k.startswith("k3m_gemm_bf16 ")}
+    merged = {}
+    for k, v in kb.items():
+        n = k.split(" ")[0]
+        a = merged.get(n, (0, 0.0, 0.0))
+        merged[n] = (a[0] + v[0], a[1] + v[1], a[2] + v[2])
+    kb = merged
     g_n, g_ms, g_fl = kb.get("k3m_gemm_bf16", (0, 1e-9, 0.0))
     gemm_tflops = g_fl / (g_ms * 1e-3) / 1e12
     samples = B * world
@@ -264,6 +271,8 @@ def run_gpu_arm(args):
                           "peak": peaks["tflops_sustained"], "unit": "TFLOP/s per GPU",
                           "frac": step_tflops / peaks["tflops_sustained"], "frac_of_burst": step_tflops / peaks["tflops"]},
         "kernel_ms": {k: {"launches": v[0], "ms": round(v[1], 4)} for k, v in sorted(kb.items(), key=lambda kv: -kv[1][1])},
+        "gemm_shapes": {k[len("k3m_gemm_bf16 "):]: {"launches": v[0], "ms": round(v[1], 4), "tflops": round(v[2] / max(v[1], 1e-9) / 1e9, 1)}
+                        for k, v in sorted(shapes.items(), key=lambda kv: -kv[1][1])},
         "losses_first": loss0, "losses_last": last,
     }
     if world == 1 and not args.no_cpu_baseline:

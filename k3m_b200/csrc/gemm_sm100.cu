@@ -45,6 +45,7 @@ struct GemmParams {
   DropSpec drop;
   int drop_ld;
   int vec_ok;  // all epilogue pointers 16 B aligned with ld % 8 == 0
+  int tma_out; // out (and aux_out) leave through TMA bulk stores
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -112,99 +113,131 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
   return d;
 }
 
-// fused epilogue of one 32-column chunk of one output row (accumulators in r[], fp32 bit patterns)
-__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t r[32], int row, int col0, bool has_drop) {
+// ---- epilogue pieces -------------------------------------------------------------------------------
+// values of one 8-column group of one output row: v = final value, pre = GELU pre-activation (aux_out)
+__device__ __forceinline__ void compute_group(const GemmParams& p, const uint32_t* acc, int row, int col, int nv,
+                                              bool vec, bool has_drop, float v[8], float pre[8]) {
 #pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    const int col = col0 + g * 8;
-    if (col >= p.N) break;
-    const int nv = (p.N - col) < 8 ? (p.N - col) : 8;
-    const bool vec = p.vec_ok && nv == 8;
-    float v[8];
+  for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(acc[j]);
+  if (p.bias) {
+    float t[8];
+    if (vec) ld8(p.bias + col, t);
+    else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(p.bias + col + j) : 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
-    if (p.bias) {
-      float t[8];
-      if (vec) ld8(p.bias + col, t);
-      else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(p.bias + col + j) : 0.f;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] += t[j];
-    }
-    if (p.act == ACT_GELU) {
-      if (p.aux_out) {
-        bf16* ao = p.aux_out + (size_t)row * p.ld_aux_out + col;
-        if (vec) st8(ao, v);
-        else for (int j = 0; j < nv; ++j) st_f(ao + j, v[j]);
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
-    } else if (p.act == ACT_DGELU || p.act == ACT_DTANH) {
-      const bf16* ai = p.aux_in + (size_t)row * p.ld_aux_in + col;
-      float t[8];
-      if (vec) ld8(ai, t);
-      else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ai + j) : 0.f;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] *= (p.act == ACT_DGELU) ? dgelu_f(t[j]) : (1.0f - t[j] * t[j]);
-    } else if (p.act == ACT_SIGMOID) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = sigmoid_f(v[j]);
-    } else if (p.act == ACT_TANH) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = tanhf(v[j]);
-    }
-    if (has_drop) {
-      uint32_t w[4];
-      const unsigned long long lin = (unsigned long long)row * (unsigned long long)p.drop_ld + (unsigned long long)col;
-      rng_words(p.drop.rng, p.drop.site, lin >> 3, w);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] *= drop_mult(p.drop, w, j);
-    }
-    if (p.addend) {
-      float t[8];
-      if (p.addend_f32) {
-        const float* ad = reinterpret_cast<const float*>(p.addend) + (size_t)row * p.ld_add + col;
-        if (vec) ld8(ad, t);
-        else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ad[j] : 0.f;
-      } else {
-        const bf16* ad = reinterpret_cast<const bf16*>(p.addend) + (size_t)row * p.ld_add + col;
-        if (vec) ld8(ad, t);
-        else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ad + j) : 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] += t[j];
-    }
-    if (p.out_f32) {
-      float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col;
-      if (p.accumulate) {
-        for (int j = 0; j < nv; ++j) atomicAdd(o + j, v[j]);
-      } else if (vec) {
-        st8(o, v);
-      } else {
-        for (int j = 0; j < nv; ++j) o[j] = v[j];
-      }
-    } else {
-      bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)row * p.ldc + col;
-      if (vec) st8(o, v);
-      else for (int j = 0; j < nv; ++j) st_f(o + j, v[j]);
-    }
+    for (int j = 0; j < 8; ++j) v[j] += t[j];
   }
+  if (p.act == ACT_GELU) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { pre[j] = v[j]; v[j] = gelu_f(v[j]); }
+  } else if (p.act == ACT_DGELU || p.act == ACT_DTANH) {
+    const bf16* ai = p.aux_in + (size_t)row * p.ld_aux_in + col;
+    float t[8];
+    if (vec) ld8(ai, t);
+    else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ai + j) : 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] *= (p.act == ACT_DGELU) ? dgelu_f(t[j]) : (1.0f - t[j] * t[j]);
+  } else if (p.act == ACT_SIGMOID) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = sigmoid_f(v[j]);
+  } else if (p.act == ACT_TANH) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = tanhf(v[j]);
+  }
+  if (has_drop) {
+    uint32_t w[4];
+    const unsigned long long lin = (unsigned long long)row * (unsigned long long)p.drop_ld + (unsigned long long)col;
+    rng_words(p.drop.rng, p.drop.site, lin >> 3, w);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] *= drop_mult(p.drop, w, j);
+  }
+  if (p.addend) {
+    float t[8];
+    if (p.addend_f32) {
+      const float* ad = reinterpret_cast<const float*>(p.addend) + (size_t)row * p.ld_add + col;
+      if (vec) ld8(ad, t);
+      else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ad[j] : 0.f;
+    } else {
+      const bf16* ad = reinterpret_cast<const bf16*>(p.addend) + (size_t)row * p.ld_add + col;
+      if (vec) ld8(ad, t);
+      else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ad + j) : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] += t[j];
+  }
+}
+
+// direct (row-per-thread) stores: fallback when the output cannot be described by a TMA tensor map
+__device__ __forceinline__ void store_group_direct(const GemmParams& p, int row, int col, int nv, bool vec,
+                                                   const float v[8], const float pre[8]) {
+  if (p.act == ACT_GELU && p.aux_out) {
+    bf16* ao = p.aux_out + (size_t)row * p.ld_aux_out + col;
+    if (vec) st8(ao, pre);
+    else for (int j = 0; j < nv; ++j) st_f(ao + j, pre[j]);
+  }
+  if (p.out_f32) {
+    float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col;
+    if (p.accumulate) {
+      for (int j = 0; j < nv; ++j) atomicAdd(o + j, v[j]);
+    } else if (vec) {
+      st8(o, v);
+    } else {
+      for (int j = 0; j < nv; ++j) o[j] = v[j];
+    }
+  } else {
+    bf16* o = reinterpret_cast<bf16*>(p.out) + (size_t)row * p.ldc + col;
+    if (vec) st8(o, v);
+    else for (int j = 0; j < nv; ++j) st_f(o + j, v[j]);
+  }
+}
+
+// staging buffer of one epilogue warp: 32 rows x 128 B, SWIZZLE_128B (16-byte chunk c of row r lives at
+// chunk c ^ (r & 7)); written row-per-thread without bank conflicts, read by the TMA store engine
+// `off` = byte offset inside the (1024-byte aligned) staging buffer in the un-swizzled row-major box
+// layout; SWIZZLE_128B XORs the 16-byte chunk index (address bits 4..6) with address bits 7..9
+// (SWIZZLE_64B, used for 64-byte rows: chunk bits 4..5 ^= address bits 7..8)
+__device__ __forceinline__ uint32_t swz(uint32_t off, uint32_t mask) { return off ^ (((off >> 7) & mask) << 4); }
+__device__ __forceinline__ void stage_bf16(uint8_t* buf, uint32_t off, uint32_t mask, const float v[8]) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+  *reinterpret_cast<uint4*>(buf + swz(off, mask)) = u;
+}
+__device__ __forceinline__ void stage_f32(uint8_t* buf, uint32_t off, uint32_t mask, const float v[8]) {
+  *reinterpret_cast<float4*>(buf + swz(off, mask)) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(buf + swz(off + 16, mask)) = make_float4(v[4], v[5], v[6], v[7]);
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(smem_u32(src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const void* src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(smem_u32(src)), "r"(c0), "r"(c1) : "memory");
 }
 
 // Persistent, warp-specialised: every CTA walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...
 // (tile = (split, m, n), n fastest so neighbouring CTAs share the A panel in L2).  The smem ring
 // (TMA -> MMA) runs across tile boundaries and the accumulator is double-buffered in TMEM, so the
 // epilogue of tile i overlaps the main loop of tile i + 1.
-template <int BN, int STAGES, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(192, (BN <= 128 ? 2 : 1))
-gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, GemmParams p) {
+template <int BN, int STAGES, int EW, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(64 + 128 * EW, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+            const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_aux, GemmParams p) {
+  // warps: 0 = TMA producer, 1 = MMA issuer, 2 .. 2+4*EW-1 = epilogue.  Epilogue warp e handles the
+  // TMEM lane quarter (warp % 4) and the column group e / 4 (CW = BN / EW columns) of every tile.
   constexpr int A_BYTES = BM * BK * 2;
   constexpr int B_BYTES = BN * BK * 2;
+  constexpr int CW = BN / EW;
+  static_assert(CW == 32 || CW == 64, "an epilogue warp owns 32 or 64 output columns");
+  constexpr int NBUF = EW <= 2 ? 2 : 1;        // staging buffers (4 KB each) per epilogue warp
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * A_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
+  uint8_t* sStage = sB + STAGES * B_BYTES;                                   // [4*EW warps][NBUF][4096], 1024-aligned
+  uint64_t* full = reinterpret_cast<uint64_t*>(sStage + 4 * EW * NBUF * 4096);
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;   // [2]
@@ -222,7 +255,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 4);      // one arrive per epilogue warp
+      mbar_init(&tmem_empty[s], 4 * EW); // one arrive per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -302,29 +335,100 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       }
     }
   } else {
-    // ---- epilogue warps 2..5: TMEM lanes 32*(warp%4) .. +31, one output row per thread ----
-    const int q = warp & 3;
+    // ---- epilogue warps: one output row per thread, CW columns per warp ----
+    // Outputs leave through a per-warp swizzled staging buffer and TMA (bulk store, or bulk reduce-add
+    // for split-K / accumulated weight gradients): full-line coalesced writes whatever the row stride.
+    const int e = warp - 2, q = warp & 3, cg = e >> 2;
     const bool has_drop = p.drop.thresh != 0;
+    const bool want_aux = p.act == ACT_GELU && p.aux_out != nullptr;
+    uint8_t* my_stage = sStage + e * NBUF * 4096;
+    const int esz = p.out_f32 ? 4 : 2;
+    const int chunk_cols = (CW * esz > 128) ? 128 / esz : CW;      // columns per staged box (<= 128 B per row)
+    const uint32_t row_bytes = (uint32_t)(chunk_cols * esz);
+    const uint32_t smask = row_bytes == 64 ? 3u : 7u, amask = CW * 2 == 64 ? 3u : 7u;   // 64 B rows use SWIZZLE_64B
+    uint32_t nstore = 0;
+    if (lane == 0 && p.tma_out) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
+      if (want_aux) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_aux) : "memory");
+    }
     uint32_t lt = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const int mn = tile % tiles_mn;
-      const int m0 = (mn / p.tiles_n) * BM, n0 = (mn % p.tiles_n) * BN;
+      const int m0 = (mn / p.tiles_n) * BM, n0 = (mn % p.tiles_n) * BN + cg * CW;
       const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
       const int row = m0 + q * 32 + lane;
       const bool row_ok = row < p.M;
       mbar_wait(&tmem_full[as], aph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cg * CW;
+      if (n0 < p.N) {
+        uint8_t* buf = nullptr;
+        uint8_t* abuf = nullptr;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        if (n0 + c * 32 >= p.N) break;
-        uint32_t r[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + (uint32_t)(c * 32), r);
-        if (row_ok) epilogue_chunk(p, r, row, n0 + c * 32, has_drop);
+        for (int cc = 0; cc < CW; cc += 32) {
+          if (!p.tma_out && n0 + cc >= p.N) break;
+          const int lc = cc % chunk_cols;            // column of this 32-wide slab inside the staged box
+          if (p.tma_out && lc == 0) {
+            buf = my_stage + (nstore % NBUF) * 4096;
+            abuf = my_stage + ((nstore + 1) % NBUF) * 4096;
+            // the bulk store that last read the buffer(s) must have finished reading
+            if (lane == 0) {
+              if (want_aux || NBUF == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+              else asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            }
+            __syncwarp();
+          }
+          uint32_t r[32];
+          tmem_ld32(tbase + (uint32_t)cc, r);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const int col = n0 + cc + g * 8;
+            const int nv = (p.N - col) < 8 ? (p.N - col) : 8;
+            const bool ok = row_ok && nv > 0;
+            const bool vec = p.vec_ok && nv == 8;
+            float v[8], pre[8];
+            if (ok) {
+              compute_group(p, r + g * 8, row, col, nv, vec, has_drop, v, pre);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = pre[j] = 0.f;
+            }
+            if (p.tma_out) {
+              const uint32_t off = (uint32_t)lane * row_bytes + (uint32_t)((lc + g * 8) * esz);
+              if (p.out_f32) stage_f32(buf, off, smask, v);
+              else stage_bf16(buf, off, smask, v);
+              if (want_aux) {
+                if (NBUF > 1) {
+                  stage_bf16(abuf, (uint32_t)lane * (uint32_t)(CW * 2) + (uint32_t)((cc + g * 8) * 2), amask, pre);
+                } else if (ok) {   // one staging buffer per warp: the pre-activation is stored row-per-thread
+                  bf16* ao = p.aux_out + (size_t)row * p.ld_aux_out + col;
+                  if (vec) st8(ao, pre);
+                  else for (int j = 0; j < nv; ++j) st_f(ao + j, pre[j]);
+                }
+              }
+            } else if (ok) {
+              store_group_direct(p, row, col, nv, vec, v, pre);
+            }
+          }
+          if (p.tma_out && (lc + 32 == chunk_cols)) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+              const int c0 = n0 + cc + 32 - chunk_cols;
+              if (p.accumulate) tma_reduce_add_2d(&map_c, buf, c0, m0 + q * 32);
+              else tma_store_2d(&map_c, buf, c0, m0 + q * 32);
+              if (want_aux && NBUF > 1) tma_store_2d(&map_aux, abuf, n0, m0 + q * 32);
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            nstore += (want_aux && NBUF > 1) ? 2 : 1;
+          }
+        }
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[as])) : "memory");
     }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // all bulk stores complete
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -353,13 +457,14 @@ EncodeTiledFn get_encode() {
   return fn;
 }
 
-typedef std::tuple<const void*, int, int, int, int, int> MapKey;
+typedef std::tuple<const void*, int, int, int, int, int, int> MapKey;
 std::map<MapKey, CUtensorMap> g_maps;
 std::mutex g_maps_mu;
 
 // 2-D bf16 tensor [outer, inner] with row stride ld (elements), box [box_outer, box_inner], SW128
-bool get_map(const void* ptr, int inner, int outer, int ld, int box_inner, int box_outer, CUtensorMap* out) {
-  MapKey key(ptr, inner, outer, ld, box_inner, box_outer);
+bool get_map(const void* ptr, int inner, int outer, int ld, int box_inner, int box_outer, CUtensorMap* out,
+             int esize = 2) {
+  MapKey key(ptr, inner, outer, ld, box_inner, box_outer, esize);
   {
     std::lock_guard<std::mutex> lk(g_maps_mu);
     auto it = g_maps.find(key);
@@ -374,12 +479,13 @@ bool get_map(const void* ptr, int inner, int outer, int ld, int box_inner, int b
     return false;
   }
   cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * (cuuint64_t)esize};
   cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUtensorMap m;
-  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  CUresult r = enc(&m, esize == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   box_inner * esize == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     k3m_set_error("cuTensorMapEncodeTiled failed (%d) ptr=%p inner=%d outer=%d ld=%d box=%dx%d", (int)r, ptr, inner,
@@ -403,11 +509,15 @@ int num_sms() {
   return n;
 }
 
-template <int BN, int STAGES, bool A_MN, bool B_MN>
-int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams p, cudaStream_t st) {
-  constexpr int SMEM = STAGES * (BM * BK * 2 + BN * BK * 2) + (2 * STAGES + 4) * 8 + 16 + 1024;
+template <int BN, int STAGES, int EW, bool A_MN, bool B_MN>
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx, GemmParams p,
+           cudaStream_t st) {
+  // operand ring + epilogue staging (4*EW warps x NBUF x 4 KB) + barriers + 1 KB alignment slack
+  constexpr int NBUF = EW <= 2 ? 2 : 1;
+  constexpr int SMEM = STAGES * (BM * BK * 2 + BN * BK * 2) + 4 * EW * NBUF * 4096 + (2 * STAGES + 4) * 8 + 16 + 1024;
+  static_assert(SMEM <= 227 * 1024, "shared memory budget");
   static bool configured = false;
-  auto kern = gemm_kernel<BN, STAGES, A_MN, B_MN>;
+  auto kern = gemm_kernel<BN, STAGES, EW, A_MN, B_MN>;
   if (!configured) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess) {
       k3m_set_error("gemm: cannot set dynamic shared memory to %d", SMEM);
@@ -418,28 +528,29 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams p, cudaStrea
   p.tiles_m = (p.M + BM - 1) / BM;
   p.tiles_n = (p.N + BN - 1) / BN;
   const int total = p.tiles_m * p.tiles_n * p.splits;
-  const int resident = num_sms() * (BN <= 128 ? 2 : 1);
-  const int grid = total < resident ? total : resident;
-  kern<<<grid, 192, SMEM, st>>>(ma, mb, p);
+  const int grid = total < num_sms() ? total : num_sms();
+  kern<<<grid, 64 + 128 * EW, SMEM, st>>>(ma, mb, mc, mx, p);
   return k3m_check_launch("k3m_gemm_bf16");
 }
 
+// (tile width, epilogue column groups) variants: 256/4 (16 epilogue warps), 128/4, 128/2, 64/1
 template <bool A_MN, bool B_MN>
-int dispatch(int bn, const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st) {
-  if (bn == 64) return launch<64, 4, A_MN, B_MN>(ma, mb, p, st);
-  if (bn == 256) return launch<256, 4, A_MN, B_MN>(ma, mb, p, st);
-  return launch<128, 3, A_MN, B_MN>(ma, mb, p, st);
+int dispatch(int bn, int ew, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx,
+             const GemmParams& p, cudaStream_t st) {
+  if (bn == 64) return launch<64, 6, 1, A_MN, B_MN>(ma, mb, mc, mx, p, st);
+  if (bn == 256) return launch<256, 3, 4, A_MN, B_MN>(ma, mb, mc, mx, p, st);
+  if (ew == 4) return launch<128, 5, 4, A_MN, B_MN>(ma, mb, mc, mx, p, st);
+  return launch<128, 5, 2, A_MN, B_MN>(ma, mb, mc, mx, p, st);
 }
 
-// tile width.  Measured on B200 (tools/bench_gemm.py): two co-resident 128 x 128 CTAs per SM beat one
-// 128 x 256 CTA whenever the main loop is short (K <= 3072: the epilogue of a 256-wide tile is twice as
-// long and only one CTA's epilogue warps work on it); long-K problems (weight gradients, vocab dgrad)
-// prefer the wider tile, which reads A once per 256 output columns.
+// tile width: 128 x 256 (85 flop per operand byte from L2) once it still gives every SM a tile, else
+// 128 x 128; operand traffic from L2, not the tensor pipe, bounds these K <= 3072 problems
 int pick_bn(int M, int N, int K, int force) {
   if (N <= 64) return 64;
   if (force == 64 || force == 128 || force == 256) return force;
-  (void)M;
-  return (K >= 4096 && N >= 256) ? 256 : 128;
+  if (K >= 4096 && N >= 256) return 256;
+  const long tiles256 = (long)((M + BM - 1) / BM) * ((N + 255) / 256);
+  return (N >= 256 && tiles256 >= (long)num_sms() * 3 / 4) ? 256 : 128;
 }
 
 }  // namespace
@@ -468,7 +579,7 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   int splits = 1;
   if (accumulate) {
     const int tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
-    const int resident = num_sms() * (bn <= 128 ? 2 : 1);
+    const int resident = num_sms();
     while (tiles * splits * 2 <= resident && total_kb / (splits * 2) >= 4) splits *= 2;
   }
   p.kb_per_split = (total_kb + splits - 1) / splits;
@@ -489,7 +600,24 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   p.vec_ok = al(out, ldc, out_f32 ? 4 : 2) && al(bias, 8, 2) && al(aux_in, ld_aux_in, 2) && al(aux_out, ld_aux_out, 2) &&
              al(addend, ld_add, addend_f32 ? 4 : 2) && (!out_f32 || (ldc % 8 == 0 && (((uintptr_t)out) & 31) == 0));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (layout == 0) return dispatch<false, false>(bn, ma, mb, p, st);
-  if (layout == 1) return dispatch<false, true>(bn, ma, mb, p, st);
-  return dispatch<true, true>(bn, ma, mb, p, st);
+  // TMA-store epilogue when the outputs can be described by tensor maps (16-byte aligned base and row pitch)
+  CUtensorMap mc = ma, mx = ma;
+  const int esz = out_f32 ? 4 : 2;
+  auto tma_able = [](const void* q, long pitch_bytes) { return q != nullptr && (((uintptr_t)q) & 15) == 0 && pitch_bytes % 16 == 0; };
+  static const int no_tma_store = getenv("K3M_GEMM_NO_TMA_STORE") ? atoi(getenv("K3M_GEMM_NO_TMA_STORE")) : 0;
+  const bool want_aux = act == ACT_GELU && aux_out != nullptr;
+  p.tma_out = !no_tma_store && tma_able(out, (long)ldc * esz) && (!want_aux || (!out_f32 && tma_able(aux_out, (long)ld_aux_out * 2)));
+  // epilogue warps: 16 (4 column groups) when the epilogue does real work per element, else 8
+  static const int force_ew = getenv("K3M_GEMM_EW") ? atoi(getenv("K3M_GEMM_EW")) : 0;
+  const bool heavy = act != ACT_NONE || p.drop.thresh != 0 || addend != nullptr;
+  const int ew = bn == 256 ? 4 : bn == 64 ? 1 : (force_ew ? force_ew : (heavy ? 4 : 2));
+  const int cw = bn / ew;
+  if (p.tma_out) {
+    const int box = (cw * esz > 128) ? 128 / esz : cw;
+    if (!get_map(out, N, M, ldc, box, 32, &mc, esz)) return K3M_ERR_CUDA;
+    if (want_aux && ew <= 2 && !get_map(aux_out, N, M, ld_aux_out, cw, 32, &mx, 2)) return K3M_ERR_CUDA;
+  }
+  if (layout == 0) return dispatch<false, false>(bn, ew, ma, mb, mc, mx, p, st);
+  if (layout == 1) return dispatch<false, true>(bn, ew, ma, mb, mc, mx, p, st);
+  return dispatch<true, true>(bn, ew, ma, mb, mc, mx, p, st);
 }

@@ -43,6 +43,7 @@ class CudaOps(object):
         # launching stream and (entry point, work, event pair) is appended; never on in the product path
         self.timing = None
         self._work = 0.0
+        self._tag = ""
 
     def _st(self):
         return _vp(torch.cuda.current_stream().cuda_stream)
@@ -56,8 +57,9 @@ class CudaOps(object):
         e0.record()
         _lib.check(getattr(self.lib, name)(*args), name)
         e1.record()
-        self.timing.append((name, self._work, e0, e1))
+        self.timing.append((name + self._tag, self._work, e0, e1))
         self._work = 0.0
+        self._tag = ""
 
     def _drop(self, drop, rng):
         if drop is None:
@@ -86,6 +88,10 @@ class CudaOps(object):
         assert tuple(out.shape) == (M, N)
         r, s, p = self._drop(drop, rng)
         self._work = 2.0 * M * N * K
+        if self.timing is not None:
+            self._tag = " %s %dx%dx%d%s%s%s%s%s" % (layout, M, N, K, " bias" if bias is not None else "", " act%d" % act if act else "",
+                                                   " drop" if drop is not None else "", " add" if addend is not None else "",
+                                                   " acc" if accumulate else (" f32" if out.dtype == torch.float32 else ""))
         self._call("k3m_gemm_bf16", _p(a), _i(_ld(a)), _p(b), _i(_ld(b)), _i(_LAYOUT[layout]),
                    _i(M), _i(N), _i(K), _p(out), _i(_ld(out)), _i(_isf32(out)), _i(1 if accumulate else 0),
                    _p(bias), _i(act), _p(aux_in), _i(_ld(aux_in)), _p(aux_out), _i(_ld(aux_out)),
