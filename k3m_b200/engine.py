@@ -434,31 +434,53 @@ class Engine(object):
         segs_x = _merge_segs([_Seg(0, B, Lt, mask_t), _Seg(Mt, B, Lt, mask_t),
                               _Seg(2 * Mt, B, Lpv, mask_pv), _Seg(2 * Mt + Mp, B, Lpv, mask_pv)])
         segs_y = _merge_segs([_Seg(0, B, Lv1, mask_v), _Seg(Mv, B, Lv1, mask_v)])
+        # stages: ("tv", [text layer saves], [image layer saves]) | ("c", save_tv, save_pvv, save_tpv).
+        # The text and image stacks between two connection stages are independent, and so are the three
+        # connection layers of a stage: they are handed to ops.parallel (concurrent streams).
         stages = []
         s1 = s2 = 0
+        box = {"X": X, "Y": Y}
+
+        def run_layers(t_range, v_range):
+            tsv, vsv = [], []
+
+            def text():
+                for i in t_range:
+                    box["X"], sv = self.layer_fwd("encoder.layer.%d" % i, box["X"], segs_x, False)
+                    tsv.append(sv)
+
+            def image():
+                for i in v_range:
+                    box["Y"], sv = self.layer_fwd("encoder.v_layer.%d" % i, box["Y"], segs_y, True)
+                    vsv.append(sv)
+
+            ops.parallel([text if len(t_range) else None, image if len(v_range) else None])
+            stages.append(("tv", tsv, vsv))
+
         for count, (e1, e2) in enumerate(zip(c.v_biattention_id, c.t_biattention_id)):
-            for i in range(s2, e2):
-                X, sv = self.layer_fwd("encoder.layer.%d" % i, X, segs_x, False)
-                stages.append(("t", sv))
-            for i in range(s1, e1):
-                Y, sv = self.layer_fwd("encoder.v_layer.%d" % i, Y, segs_y, True)
-                stages.append(("v", sv))
+            run_layers(range(s2, e2), range(s1, e1))
+            X, Y = box["X"], box["Y"]
             Xn, Yn = torch.empty_like(X), torch.empty_like(Y)
-            _, _, sa = self.connection_fwd("encoder.c_layer.%d" % count, Y[V1], sgV, X[T1], sgT,
-                                           False, Yn[V1], Xn[T1])
-            _, _, sb = self.connection_fwd("encoder.c_layer_pv_v.%d" % count, Y[V2], sgV, X[P2], sgP,
-                                           False, Yn[V2], Xn[P2])
-            _, _, sc = self.connection_fwd("encoder.c_layer_pv_t.%d" % count, X[P3], sgP, X[T3], sgT,
-                                           True, Xn[P3], Xn[T3])
-            stages.append(("c", sa, sb, sc))
-            X, Y = Xn, Yn
+            sv_c = [None, None, None]
+
+            def conn_a():
+                sv_c[0] = self.connection_fwd("encoder.c_layer.%d" % count, Y[V1], sgV, X[T1], sgT,
+                                              False, Yn[V1], Xn[T1])[2]
+
+            def conn_b():
+                sv_c[1] = self.connection_fwd("encoder.c_layer_pv_v.%d" % count, Y[V2], sgV, X[P2], sgP,
+                                              False, Yn[V2], Xn[P2])[2]
+
+            def conn_c():
+                sv_c[2] = self.connection_fwd("encoder.c_layer_pv_t.%d" % count, X[P3], sgP, X[T3], sgT,
+                                              True, Xn[P3], Xn[T3])[2]
+
+            ops.parallel([conn_a, conn_b, conn_c])
+            stages.append(("c", sv_c[0], sv_c[1], sv_c[2]))
+            box["X"], box["Y"] = Xn, Yn
             s1, s2 = e1, e2
-        for i in range(s1, c.v_num_hidden_layers):
-            Y, sv = self.layer_fwd("encoder.v_layer.%d" % i, Y, segs_y, True)
-            stages.append(("v", sv))
-        for i in range(s2, c.num_hidden_layers):
-            X, sv = self.layer_fwd("encoder.layer.%d" % i, X, segs_x, False)
-            stages.append(("t", sv))
+        run_layers(range(s2, c.num_hidden_layers), range(s1, c.v_num_hidden_layers))
+        X, Y = box["X"], box["Y"]
         # fusion: title / PV sequences land in one stacked buffer S for the shared MLM head
         S = self.empty(Mt + Mp, H)
         seqV = self.empty(Mv, Hv)
@@ -531,20 +553,29 @@ class Engine(object):
         self.fuse_bwd(dS[Mt:], sv_fp, d_epv, dX[P2], dX[P3])
         ready = self.on_ready or (lambda prefixes: None)
         ready(None)
+        box = {"dX": dX, "dY": dY}
         for st in reversed(sv["stages"]):
-            if st[0] == "t":
-                dX = self.layer_bwd(dX, st[1])
-                ready([st[1][0]])
-            elif st[0] == "v":
-                dY = self.layer_bwd(dY, st[1])
-                ready([st[1][0]])
+            if st[0] == "tv":
+                def text(tsv=st[1]):
+                    for s_ in reversed(tsv):
+                        box["dX"] = self.layer_bwd(box["dX"], s_)
+
+                def image(vsv=st[2]):
+                    for s_ in reversed(vsv):
+                        box["dY"] = self.layer_bwd(box["dY"], s_)
+
+                ops.parallel([text if st[1] else None, image if st[2] else None])
+                ready([s_[0] for s_ in st[1]] + [s_[0] for s_ in st[2]])
             else:
+                dX, dY = box["dX"], box["dY"]
                 dXn, dYn = torch.empty_like(dX), torch.empty_like(dY)
-                self.connection_bwd(dY[V1], dX[T1], st[1], dYn[V1], dXn[T1])
-                self.connection_bwd(dY[V2], dX[P2], st[2], dYn[V2], dXn[P2])
-                self.connection_bwd(dX[P3], dX[T3], st[3], dXn[P3], dXn[T3])
-                dX, dY = dXn, dYn
+                ops.parallel([
+                    lambda: self.connection_bwd(dY[V1], dX[T1], st[1], dYn[V1], dXn[T1]),
+                    lambda: self.connection_bwd(dY[V2], dX[P2], st[2], dYn[V2], dXn[P2]),
+                    lambda: self.connection_bwd(dX[P3], dX[T3], st[3], dXn[P3], dXn[T3])])
+                box["dX"], box["dY"] = dXn, dYn
                 ready([st[1][0], st[2][0], st[3][0]])
+        dX, dY = box["dX"], box["dY"]
         for sl in (T1, T3):
             ops.axpy(dX[sl], d_et, 1.0)
         for sl in (P2, P3):

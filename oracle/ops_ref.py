@@ -95,6 +95,12 @@ class RefOps(object):
     def __init__(self, act_dtype=torch.float32):
         self.adt = act_dtype
 
+    def parallel(self, fns):
+        """independent closures (concurrent streams in the CUDA op table): sequential here"""
+        for f in fns:
+            if f is not None:
+                f()
+
     # ---- GEMM ------------------------------------------------------------------------------
     def gemm(self, a, b, layout, out=None, out_dtype=None, bias=None, act=ACT_NONE, aux_in=None,
              aux_out=None, addend=None, drop=None, rng=None, accumulate=False):
