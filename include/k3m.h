@@ -12,7 +12,7 @@
  *     error of the calling thread.  No exceptions cross the ABI.
  *   - dropout: `rng` -> two device uint64 {seed, step}; `site` numbers the dropout application
  *     inside the step; p == 0 or rng == NULL disables it.  Masks are regenerated in backward
- *     from the same (seed, step, site, element index) — Philox4x32-10, 16 bits per element.
+ *     from the same (seed, step, site, element index) — Philox4x32-7, 16 bits per element.
  */
 #ifndef K3M_H_
 #define K3M_H_
@@ -70,6 +70,9 @@ int k3m_lincomb3(const void* a, int lda, const void* b, int ldb, const void* c, 
 int k3m_axpy(const void* x, int ldx, int x_f32, void* y, int ldy, int y_f32, float alpha, int rows,
              int cols, void* stream);
 int k3m_scale(float* x, float alpha, long long n, void* stream);
+/* x[rows, cols] (row stride ld) *= *alpha, alpha a DEVICE fp32 scalar: how the upstream gradient of a
+ * loss (autograd's grad_output of `loss.backward()`, pretrain.py:1062) reaches the stored d(loss)/d(logits) */
+int k3m_scale_dev(void* x, int ld, int x_f32, const float* alpha, int rows, int cols, void* stream);
 int k3m_dgelu_mul(const void* dy, const void* pre, void* dx, long long n, void* stream);
 /* (1 - mask) * -10000 (vilbert_k3m.py:2561, 2570, 2580)                                          */
 int k3m_mask_additive(const long long* mask, float* out, int n, void* stream);

@@ -46,6 +46,8 @@ struct GemmParams {
   int drop_ld;
   int vec_ok;  // all epilogue pointers 16 B aligned with ld % 8 == 0
   int tma_out; // out (and aux_out) leave through TMA bulk stores
+  int two_pass;
+  int tin;     // epilogue operand that ARRIVES through TMA into the staging buffer: 0 none, 1 aux_in, 2 addend
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -116,7 +118,8 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
 // ---- epilogue pieces -------------------------------------------------------------------------------
 // values of one 8-column group of one output row: v = final value, pre = GELU pre-activation (aux_out)
 __device__ __forceinline__ void compute_group(const GemmParams& p, const uint32_t* acc, int row, int col, int nv,
-                                              bool vec, bool has_drop, float v[8], float pre[8]) {
+                                              bool vec, bool has_drop, float v[8], float pre[8],
+                                              const float* staged, int tin) {
 #pragma unroll
   for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(acc[j]);
   if (p.bias) {
@@ -130,10 +133,15 @@ __device__ __forceinline__ void compute_group(const GemmParams& p, const uint32_
 #pragma unroll
     for (int j = 0; j < 8; ++j) { pre[j] = v[j]; v[j] = gelu_f(v[j]); }
   } else if (p.act == ACT_DGELU || p.act == ACT_DTANH) {
-    const bf16* ai = p.aux_in + (size_t)row * p.ld_aux_in + col;
     float t[8];
-    if (vec) ld8(ai, t);
-    else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ai + j) : 0.f;
+    if (tin == 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t[j] = staged[j];
+    } else {
+      const bf16* ai = p.aux_in + (size_t)row * p.ld_aux_in + col;
+      if (vec) ld8(ai, t);
+      else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ai + j) : 0.f;
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) v[j] *= (p.act == ACT_DGELU) ? dgelu_f(t[j]) : (1.0f - t[j] * t[j]);
   } else if (p.act == ACT_SIGMOID) {
@@ -152,7 +160,10 @@ __device__ __forceinline__ void compute_group(const GemmParams& p, const uint32_
   }
   if (p.addend) {
     float t[8];
-    if (p.addend_f32) {
+    if (tin == 2) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t[j] = staged[j];
+    } else if (p.addend_f32) {
       const float* ad = reinterpret_cast<const float*>(p.addend) + (size_t)row * p.ld_add + col;
       if (vec) ld8(ad, t);
       else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ad[j] : 0.f;
@@ -223,7 +234,8 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const 
 template <int BN, int STAGES, int EW, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(64 + 128 * EW, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-            const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_aux, GemmParams p) {
+            const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_aux,
+            const __grid_constant__ CUtensorMap map_in, GemmParams p) {
   // warps: 0 = TMA producer, 1 = MMA issuer, 2 .. 2+4*EW-1 = epilogue.  Epilogue warp e handles the
   // TMEM lane quarter (warp % 4) and the column group e / 4 (CW = BN / EW columns) of every tile.
   constexpr int A_BYTES = BM * BK * 2;
@@ -241,7 +253,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;   // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* in_bars = tmem_empty + 2;     // [4 * EW] one per epilogue warp: TMA-fed epilogue operand landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(in_bars + 4 * EW);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_kb = (p.K + BK - 1) / BK;
@@ -257,6 +270,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       mbar_init(&tmem_full[s], 1);
       mbar_init(&tmem_empty[s], 4 * EW); // one arrive per epilogue warp
     }
+    for (int s = 0; s < 4 * EW; ++s) mbar_init(&in_bars[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -338,6 +352,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     // ---- epilogue warps: one output row per thread, CW columns per warp ----
     // Outputs leave through a per-warp swizzled staging buffer and TMA (bulk store, or bulk reduce-add
     // for split-K / accumulated weight gradients): full-line coalesced writes whatever the row stride.
+    // A bf16 epilogue operand (GELU' pre-activation or the residual addend) ARRIVES the same way: its
+    // 32 x CW box is bulk-loaded into the staging buffer while the main loop of the tile is still
+    // running, read row-per-thread from shared memory and overwritten in place by the result
+    // (row-per-thread global loads cost 32 L1 wavefronts per instruction and made these epilogues
+    // longer than the K = 768 main loop).
     const int e = warp - 2, q = warp & 3, cg = e >> 2;
     const bool has_drop = p.drop.thresh != 0;
     const bool want_aux = p.act == ACT_GELU && p.aux_out != nullptr;
@@ -346,11 +365,34 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     const int chunk_cols = (CW * esz > 128) ? 128 / esz : CW;      // columns per staged box (<= 128 B per row)
     const uint32_t row_bytes = (uint32_t)(chunk_cols * esz);
     const uint32_t smask = row_bytes == 64 ? 3u : 7u, amask = CW * 2 == 64 ? 3u : 7u;   // 64 B rows use SWIZZLE_64B
+    // one staging buffer and two outputs (GELU forward keeps the pre-activation): two passes over the
+    // accumulator, each staged and bulk-stored through the same buffer (host guarantees bf16 out)
+    // (measured: recomputing the activation in the second pass costs more than the row-per-thread
+    // store of the pre-activation it replaces; enabled by GemmParams::two_pass for experiments only)
+    const bool two_pass = p.two_pass && p.tma_out && want_aux && NBUF == 1;
+    const int tin = p.tin;                                          // host: only with tma_out, bf16 out, !want_aux
+    uint64_t* in_bar = in_bars + e;
+    uint32_t in_phase = 0;
     uint32_t nstore = 0;
     if (lane == 0 && p.tma_out) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
       if (want_aux) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_aux) : "memory");
+      if (tin) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_in) : "memory");
     }
+    // bulk-load the operand box of `tile` into the buffer its result will be staged in
+    auto prefetch_in = [&](int tile) {
+      const int mn = tile % tiles_mn;
+      const int m0 = (mn / p.tiles_n) * BM, n0 = (mn % p.tiles_n) * BN + cg * CW;
+      if (n0 >= p.N) return;
+      if (lane == 0) {
+        // the bulk store that last read this buffer must have finished reading it
+        if (NBUF == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        else asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        mbar_expect_tx(in_bar, 32 * CW * 2);
+        tma_load_2d(my_stage + (nstore % NBUF) * 4096, &map_in, in_bar, n0, m0 + q * 32);
+      }
+    };
+    if (tin && (int)blockIdx.x < total_tiles) prefetch_in(blockIdx.x);
     uint32_t lt = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const int mn = tile % tiles_mn;
@@ -362,73 +404,97 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cg * CW;
       if (n0 < p.N) {
+        if (tin) {
+          mbar_wait(in_bar, in_phase);
+          in_phase ^= 1;
+        }
         uint8_t* buf = nullptr;
         uint8_t* abuf = nullptr;
+        for (int pass = 0; pass < (two_pass ? 2 : 1); ++pass) {
 #pragma unroll 1
-        for (int cc = 0; cc < CW; cc += 32) {
-          if (!p.tma_out && n0 + cc >= p.N) break;
-          const int lc = cc % chunk_cols;            // column of this 32-wide slab inside the staged box
-          if (p.tma_out && lc == 0) {
-            buf = my_stage + (nstore % NBUF) * 4096;
-            abuf = my_stage + ((nstore + 1) % NBUF) * 4096;
-            // the bulk store that last read the buffer(s) must have finished reading
-            if (lane == 0) {
-              if (want_aux || NBUF == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-              else asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          for (int cc = 0; cc < CW; cc += 32) {
+            if (!p.tma_out && n0 + cc >= p.N) break;
+            const int lc = cc % chunk_cols;            // column of this 32-wide slab inside the staged box
+            if (p.tma_out && lc == 0) {
+              buf = my_stage + (nstore % NBUF) * 4096;
+              abuf = my_stage + ((nstore + 1) % NBUF) * 4096;
+              // the bulk store that last read the buffer(s) must have finished reading (with a TMA-fed
+              // operand the prefetch already waited for that before it overwrote the buffer)
+              if (lane == 0 && !tin) {
+                if (want_aux || NBUF == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                else asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+              }
+              __syncwarp();
             }
-            __syncwarp();
-          }
-          uint32_t r[32];
-          tmem_ld32(tbase + (uint32_t)cc, r);
+            uint32_t r[32];
+            tmem_ld32(tbase + (uint32_t)cc, r);
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const int col = n0 + cc + g * 8;
-            const int nv = (p.N - col) < 8 ? (p.N - col) : 8;
-            const bool ok = row_ok && nv > 0;
-            const bool vec = p.vec_ok && nv == 8;
-            float v[8], pre[8];
-            if (ok) {
-              compute_group(p, r + g * 8, row, col, nv, vec, has_drop, v, pre);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = pre[j] = 0.f;
-            }
-            if (p.tma_out) {
+            for (int g = 0; g < 4; ++g) {
+              const int col = n0 + cc + g * 8;
+              const int nv = (p.N - col) < 8 ? (p.N - col) : 8;
+              const bool ok = row_ok && nv > 0;
+              const bool vec = p.vec_ok && nv == 8;
               const uint32_t off = (uint32_t)lane * row_bytes + (uint32_t)((lc + g * 8) * esz);
-              if (p.out_f32) stage_f32(buf, off, smask, v);
-              else stage_bf16(buf, off, smask, v);
-              if (want_aux) {
-                if (NBUF > 1) {
-                  stage_bf16(abuf, (uint32_t)lane * (uint32_t)(CW * 2) + (uint32_t)((cc + g * 8) * 2), amask, pre);
-                } else if (ok) {   // one staging buffer per warp: the pre-activation is stored row-per-thread
-                  bf16* ao = p.aux_out + (size_t)row * p.ld_aux_out + col;
-                  if (vec) st8(ao, pre);
-                  else for (int j = 0; j < nv; ++j) st_f(ao + j, pre[j]);
+              float v[8], pre[8], staged[8];
+              if (tin) {
+                const uint4 u = *reinterpret_cast<const uint4*>(buf + swz(off, smask));
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float2 f = __bfloat1622float2(h[i]);
+                  staged[2 * i] = f.x; staged[2 * i + 1] = f.y;
                 }
               }
-            } else if (ok) {
-              store_group_direct(p, row, col, nv, vec, v, pre);
+              if (ok) {
+                compute_group(p, r + g * 8, row, col, nv, vec, has_drop, v, pre, staged, tin);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = pre[j] = 0.f;
+              }
+              if (p.tma_out) {
+                if (two_pass) {
+                  stage_bf16(buf, off, smask, pass == 0 ? pre : v);
+                } else {
+                  if (p.out_f32) stage_f32(buf, off, smask, v);
+                  else stage_bf16(buf, off, smask, v);
+                  if (want_aux) {
+                    if (NBUF > 1) {
+                      stage_bf16(abuf, (uint32_t)lane * (uint32_t)(CW * 2) + (uint32_t)((cc + g * 8) * 2), amask, pre);
+                    } else if (ok) {   // fp32 out + pre-activation with one buffer: row-per-thread store
+                      bf16* ao = p.aux_out + (size_t)row * p.ld_aux_out + col;
+                      if (vec) st8(ao, pre);
+                      else for (int j = 0; j < nv; ++j) st_f(ao + j, pre[j]);
+                    }
+                  }
+                }
+              } else if (ok) {
+                store_group_direct(p, row, col, nv, vec, v, pre);
+              }
             }
-          }
-          if (p.tma_out && (lc + 32 == chunk_cols)) {
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) {
-              const int c0 = n0 + cc + 32 - chunk_cols;
-              if (p.accumulate) tma_reduce_add_2d(&map_c, buf, c0, m0 + q * 32);
-              else tma_store_2d(&map_c, buf, c0, m0 + q * 32);
-              if (want_aux && NBUF > 1) tma_store_2d(&map_aux, abuf, n0, m0 + q * 32);
-              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            if (p.tma_out && (lc + 32 == chunk_cols)) {
+              asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+              __syncwarp();
+              if (lane == 0) {
+                const int c0 = n0 + cc + 32 - chunk_cols;
+                if (two_pass && pass == 0) tma_store_2d(&map_aux, buf, c0, m0 + q * 32);
+                else if (p.accumulate) tma_reduce_add_2d(&map_c, buf, c0, m0 + q * 32);
+                else tma_store_2d(&map_c, buf, c0, m0 + q * 32);
+                if (want_aux && NBUF > 1) tma_store_2d(&map_aux, abuf, n0, m0 + q * 32);
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+              }
+              nstore += (want_aux && NBUF > 1) ? 2 : 1;
             }
-            nstore += (want_aux && NBUF > 1) ? 2 : 1;
           }
         }
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[as])) : "memory");
+      if (tin && tile + (int)gridDim.x < total_tiles) prefetch_in(tile + gridDim.x);
     }
-    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // all bulk stores complete
+    // the staging buffers must outlive the bulk stores' READS only; global visibility of the writes is
+    // given by grid completion
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -510,11 +576,11 @@ int num_sms() {
 }
 
 template <int BN, int STAGES, int EW, bool A_MN, bool B_MN>
-int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx, GemmParams p,
-           cudaStream_t st) {
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx,
+           const CUtensorMap& mi, GemmParams p, cudaStream_t st) {
   // operand ring + epilogue staging (4*EW warps x NBUF x 4 KB) + barriers + 1 KB alignment slack
   constexpr int NBUF = EW <= 2 ? 2 : 1;
-  constexpr int SMEM = STAGES * (BM * BK * 2 + BN * BK * 2) + 4 * EW * NBUF * 4096 + (2 * STAGES + 4) * 8 + 16 + 1024;
+  constexpr int SMEM = STAGES * (BM * BK * 2 + BN * BK * 2) + 4 * EW * NBUF * 4096 + (2 * STAGES + 4 + 4 * EW) * 8 + 16 + 1024;
   static_assert(SMEM <= 227 * 1024, "shared memory budget");
   static bool configured = false;
   auto kern = gemm_kernel<BN, STAGES, EW, A_MN, B_MN>;
@@ -529,18 +595,18 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
   p.tiles_n = (p.N + BN - 1) / BN;
   const int total = p.tiles_m * p.tiles_n * p.splits;
   const int grid = total < num_sms() ? total : num_sms();
-  kern<<<grid, 64 + 128 * EW, SMEM, st>>>(ma, mb, mc, mx, p);
+  kern<<<grid, 64 + 128 * EW, SMEM, st>>>(ma, mb, mc, mx, mi, p);
   return k3m_check_launch("k3m_gemm_bf16");
 }
 
 // (tile width, epilogue column groups) variants: 256/4 (16 epilogue warps), 128/4, 128/2, 64/1
 template <bool A_MN, bool B_MN>
 int dispatch(int bn, int ew, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx,
-             const GemmParams& p, cudaStream_t st) {
-  if (bn == 64) return launch<64, 6, 1, A_MN, B_MN>(ma, mb, mc, mx, p, st);
-  if (bn == 256) return launch<256, 3, 4, A_MN, B_MN>(ma, mb, mc, mx, p, st);
-  if (ew == 4) return launch<128, 5, 4, A_MN, B_MN>(ma, mb, mc, mx, p, st);
-  return launch<128, 5, 2, A_MN, B_MN>(ma, mb, mc, mx, p, st);
+             const CUtensorMap& mi, const GemmParams& p, cudaStream_t st) {
+  if (bn == 64) return launch<64, 6, 1, A_MN, B_MN>(ma, mb, mc, mx, mi, p, st);
+  if (bn == 256) return launch<256, 3, 4, A_MN, B_MN>(ma, mb, mc, mx, mi, p, st);
+  if (ew == 4) return launch<128, 5, 4, A_MN, B_MN>(ma, mb, mc, mx, mi, p, st);
+  return launch<128, 5, 2, A_MN, B_MN>(ma, mb, mc, mx, mi, p, st);
 }
 
 // tile width: 128 x 256 (85 flop per operand byte from L2) once it still gives every SM a tile, else
@@ -612,12 +678,28 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   const bool heavy = act != ACT_NONE || p.drop.thresh != 0 || addend != nullptr;
   const int ew = bn == 256 ? 4 : bn == 64 ? 1 : (force_ew ? force_ew : (heavy ? 4 : 2));
   const int cw = bn / ew;
+  CUtensorMap mi = ma;
+  p.tin = 0;
+  static const int two_pass = getenv("K3M_GEMM_TWO_PASS") ? atoi(getenv("K3M_GEMM_TWO_PASS")) : 0;
+  p.two_pass = two_pass;
   if (p.tma_out) {
     const int box = (cw * esz > 128) ? 128 / esz : cw;
     if (!get_map(out, N, M, ldc, box, 32, &mc, esz)) return K3M_ERR_CUDA;
-    if (want_aux && ew <= 2 && !get_map(aux_out, N, M, ld_aux_out, cw, 32, &mx, 2)) return K3M_ERR_CUDA;
+    if (want_aux && !get_map(aux_out, N, M, ld_aux_out, cw, 32, &mx, 2)) return K3M_ERR_CUDA;
+    // one bf16 epilogue operand can arrive through TMA into the staging buffer (same box as the output)
+    static const int no_tma_in = getenv("K3M_GEMM_NO_TMA_IN") ? atoi(getenv("K3M_GEMM_NO_TMA_IN")) : 0;
+    if (!no_tma_in && !out_f32 && !want_aux) {
+      const void* src = nullptr;
+      int ld_src = 0;
+      if ((act == ACT_DGELU || act == ACT_DTANH) && tma_able(aux_in, (long)ld_aux_in * 2)) {
+        p.tin = 1; src = aux_in; ld_src = ld_aux_in;
+      } else if (addend != nullptr && !addend_f32 && tma_able(addend, (long)ld_add * 2)) {
+        p.tin = 2; src = addend; ld_src = ld_add;
+      }
+      if (p.tin && !get_map(src, N, M, ld_src, cw, 32, &mi, 2)) return K3M_ERR_CUDA;
+    }
   }
-  if (layout == 0) return dispatch<false, false>(bn, ew, ma, mb, mc, mx, p, st);
-  if (layout == 1) return dispatch<false, true>(bn, ew, ma, mb, mc, mx, p, st);
-  return dispatch<true, true>(bn, ew, ma, mb, mc, mx, p, st);
+  if (layout == 0) return dispatch<false, false>(bn, ew, ma, mb, mc, mx, mi, p, st);
+  if (layout == 1) return dispatch<false, true>(bn, ew, ma, mb, mc, mx, mi, p, st);
+  return dispatch<true, true>(bn, ew, ma, mb, mc, mx, mi, p, st);
 }

@@ -229,6 +229,17 @@ __global__ void scale_kernel(float* x, float alpha, size_t n) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) x[i] *= alpha;
 }
 
+// x[r, :] *= *alpha (device scalar): upstream loss gradients reach the Python class API as device tensors
+template <typename T>
+__global__ void scale_dev_kernel(T* x, const float* __restrict__ alpha, int rows, int cols, int ld) {
+  const float a = *alpha;
+  const size_t n = (size_t)rows * cols;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    T* p = x + (i / cols) * (size_t)ld + (i % cols);
+    st_f(p, ld_f(p) * a);
+  }
+}
+
 // dx = dy * gelu'(pre)
 __global__ void dgelu_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ pre, bf16* __restrict__ dx, size_t n8) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
@@ -367,6 +378,16 @@ extern "C" int k3m_axpy(const void* x, int ldx, int x_f32, void* y, int ldy, int
 extern "C" int k3m_scale(float* x, float alpha, long long n, void* stream) {
   scale_kernel<<<grid_for((size_t)n, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(x, alpha, (size_t)n);
   return k3m_check_launch("k3m_scale");
+}
+
+extern "C" int k3m_scale_dev(void* x, int ld, int x_f32, const float* alpha, int rows, int cols, void* stream) {
+  K3M_REQUIRE(alpha != nullptr && rows >= 0 && cols >= 0 && ld >= cols, "scale_dev: bad arguments");
+  if (rows == 0 || cols == 0) return K3M_OK;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int g = grid_for((size_t)rows * cols, 256);
+  if (x_f32) scale_dev_kernel<float><<<g, 256, 0, st>>>((float*)x, alpha, rows, cols, ld);
+  else scale_dev_kernel<bf16><<<g, 256, 0, st>>>((bf16*)x, alpha, rows, cols, ld);
+  return k3m_check_launch("k3m_scale_dev");
 }
 
 extern "C" int k3m_dgelu_mul(const void* dy, const void* pre, void* dx, long long n, void* stream) {

@@ -89,7 +89,27 @@ class Engine(object):
 
     def wgrad(self, dy, x, wname):
         """G[w] += dy^T x    (dy [M,out], x [M,in] -> [out,in])."""
-        self.ops.gemm(dy, x, "tn", out=self.G(wname), accumulate=True)
+        g = self.G(wname)
+        self._aux(lambda: self.ops.gemm(dy, x, "tn", out=g, accumulate=True), (dy, x))
+
+    def bgrad(self, dy, bname):
+        """G[b] += column sums of dy."""
+        g = self.G(bname)
+        self._aux(lambda: self.ops.colsum(dy, g), (dy,))
+
+    def _aux(self, fn, keep):
+        """Weight / bias gradients feed only the optimizer: they leave the dgrad chain (the critical
+        path of backward) for an auxiliary stream when the op table has one."""
+        aux = getattr(self.ops, "aux", None)
+        if aux is None:
+            fn()
+        else:
+            aux(fn, keep)
+
+    def _join_aux(self):
+        j = getattr(self.ops, "join_aux", None)
+        if j is not None:
+            j()
 
     def dgrad(self, dy, wname, **kw):
         """dy [M,out] @ W[out,in] -> [M,in]."""
@@ -139,7 +159,7 @@ class Engine(object):
                              drop_in=s, rng=self.rng, dbias=self.G(p_out + ".dense.bias"))
         self.wgrad(dzm, h, p_out + ".dense.weight")
         dpre = self.dgrad(dzm, p_out + ".dense.weight", act=ACT_DGELU, aux_in=pre)
-        ops.colsum(dpre, self.G(p_int + ".dense.bias"))
+        self.bgrad(dpre, p_int + ".dense.bias")
         self.wgrad(dpre, a, p_int + ".dense.weight")
         return self.dgrad(dpre, p_int + ".dense.weight", addend=dz)
 
@@ -180,7 +200,7 @@ class Engine(object):
             dv = dqkv[sg.r0:sg.r1]
             ops.attn_bwd(dctx[sg.r0:sg.r1], ctx[sg.r0:sg.r1], v, 0, v, H, 2 * H, sg.mask, lse,
                          dv, dv, sg.B, heads, sg.L, sg.L, d, drop=s, rng=self.rng)
-        ops.colsum(dqkv, self.G(p + ".attention.self.qkv.bias"))
+        self.bgrad(dqkv, p + ".attention.self.qkv.bias")
         self.wgrad(dqkv, x, p + ".attention.self.qkv.weight")
         return self.dgrad(dqkv, p + ".attention.self.qkv.weight", addend=dz1)
 
@@ -231,8 +251,8 @@ class Engine(object):
         ops.attn_bwd(dctx2, ctx2, qkv1, 0, qkv2, Hb, 2 * Hb, sg2.mask, lse2, dqkv1, dqkv2,
                      B, heads, L1, L2, d, drop=s2, rng=self.rng)
         b = p + ".biattention."
-        ops.colsum(dqkv1, self.G(b + "qkv1.bias"))
-        ops.colsum(dqkv2, self.G(b + "qkv2.bias"))
+        self.bgrad(dqkv1, b + "qkv1.bias")
+        self.bgrad(dqkv2, b + "qkv2.bias")
         self.wgrad(dqkv1, x1, b + "qkv1.weight")
         self.wgrad(dqkv2, x2, b + "qkv2.weight")
         self.dgrad(dqkv1, b + "qkv1.weight", addend=dz1, out=dx1_out)
@@ -320,7 +340,7 @@ class Engine(object):
             return
         _, mod, cat, gates, noise, site = saved
         dgates, dcat = ops.fuse_select_bwd(dout, cat, gates, noise=noise, site=site, rng=self.rng)
-        ops.colsum(dgates, self.G("score_%s.bias" % mod))
+        self.bgrad(dgates, "score_%s.bias" % mod)
         self.wgrad(dgates, cat, "score_%s.weight" % mod)
         self.dgrad(dgates, "score_%s.weight" % mod, addend=dcat, out=dcat)
         ops.relu_bwd_split3(dcat, cat, d_indiv, d_c1, d_c2)
@@ -345,14 +365,14 @@ class Engine(object):
         p, x, pre, h, hn, mean, rstd, p_dec_w, p_dec_b, n_cols = saved
         ops = self.ops
         dl = dlogits[:, :n_cols]
-        ops.colsum(dl, self.G(p_dec_b))
+        self.bgrad(dl, p_dec_b)
         self.wgrad(dl, hn, p_dec_w)
         dhn = self.dgrad(dl, p_dec_w)
         dh, _ = ops.ln_bwd(dhn, h, self.W(p + ".transform.LayerNorm.weight"), mean, rstd,
                            self.G(p + ".transform.LayerNorm.weight"),
                            self.G(p + ".transform.LayerNorm.bias"))
         dpre = ops.act_bwd(dh, pre, ACT_DGELU)
-        ops.colsum(dpre, self.G(p + ".transform.dense.bias"))
+        self.bgrad(dpre, p + ".transform.dense.bias")
         self.wgrad(dpre, x, p + ".transform.dense.weight")
         self.dgrad(dpre, p + ".transform.dense.weight", addend=dx, out=dx)
 
@@ -381,14 +401,14 @@ class Engine(object):
             ops.scale_(dc_final, w_lpm)
             ops.scale_(dPV, w_lpm)
         ops.axpy(dc_final, dc_init, 1.0)
-        ops.colsum(dc_final, self.G("struc_w3.bias"))
+        self.bgrad(dc_final, "struc_w3.bias")
         dcf = ops.cast(dc_final, self.adt)
         self.wgrad(dcf, s_a, "struc_w3.weight")
         ds = self.dgrad(dcf, "struc_w3.weight", out_dtype=f32)
         dt = self.zeros(t.shape[0], t.shape[1], f32)
         ops.struct_attn_bwd(ds, t, att, self.W("struc_w2.weight"), plan["seg"], dt,
                             self.G("struc_w2.weight"), self.G("struc_w2.bias"))
-        ops.colsum(dt, self.G("struc_w1.bias"))
+        self.bgrad(dt, "struc_w1.bias")
         dta = ops.cast(dt, self.adt)
         self.wgrad(dta, X, "struc_w1.weight")
         dX = self.dgrad(dta, "struc_w1.weight", out_dtype=f32)
@@ -520,12 +540,23 @@ class Engine(object):
         return dict(loss_t=loss_t, loss_v=loss_v, loss_pv=loss_pv, loss_itm=loss_itm,
                     loss_lpm=loss_lpm, c_initial=c_init, c_final=c_final)
 
-    def backward(self):
+    def backward(self, grad_scales=None):
         """Gradient of w_t*loss_t + w_v*loss_v + w_pv*loss_pv + w_lpm*loss_lpm, accumulated into
-        the fp32 gradient arena (which the caller zeroes once per optimizer step)."""
+        the fp32 gradient arena (which the caller zeroes once per optimizer step).
+        `grad_scales`: optional (g_t, g_v, g_pv, g_lpm) fp32 DEVICE scalars (autograd's upstream
+        gradients of the four losses, `k3m_b200.vilbert_k3m`); each multiplies the stored
+        d(loss)/d(logits) of its loss before anything is propagated."""
         c, ops, f32 = self.cfg, self.ops, torch.float32
         sv = self.saved
         B, Lt, Lpv, Lv1, Mt, Mp, Mv = sv["dims"]
+        if grad_scales is not None:
+            g_t, g_v, g_pv, g_lpm = grad_scales
+            dlog = sv["head"][0]
+            ops.scale_dev_(dlog[:Mt], g_t)
+            ops.scale_dev_(dlog[Mt:], g_pv)
+            ops.scale_dev_(sv["head_v"][0], g_v)
+            ops.scale_dev_(sv["struct"][5], g_lpm)      # dc_final
+            ops.scale_dev_(sv["struct"][6], g_lpm)      # dPV
         H, Hv = c.hidden_size, c.v_hidden_size
         T1, T3 = slice(0, Mt), slice(Mt, 2 * Mt)
         P2, P3 = slice(2 * Mt, 2 * Mt + Mp), slice(2 * Mt + Mp, 2 * Mt + 2 * Mp)
@@ -539,7 +570,7 @@ class Engine(object):
         ops.scale_(dc_init, 1.0 / 3)                       # c_initial = (v + t + pv) / 3
         ops.mean_pool_bwd(dc_init, dS[:Mt], B, Lt)
         ops.mean_pool_bwd(dc_init, dS[Mt:], B, Lpv)
-        ops.colsum(dc_init, self.G("map_bi_to_individual.bias"))
+        self.bgrad(dc_init, "map_bi_to_individual.bias")
         dpa = ops.cast(dc_init, self.adt)
         self.wgrad(dpa, sv["pool_vr"], "map_bi_to_individual.weight")
         dpr = self.dgrad(dpa, "map_bi_to_individual.weight", out_dtype=f32)
@@ -551,7 +582,12 @@ class Engine(object):
         self.fuse_bwd(dseqV, sv_fv, d_ev, dY[V1], dY[V2])
         self.fuse_bwd(dS[:Mt], sv_ft, d_et, dX[T1], dX[T3])
         self.fuse_bwd(dS[Mt:], sv_fp, d_epv, dX[P2], dX[P3])
-        ready = self.on_ready or (lambda prefixes: None)
+        on_ready = self.on_ready or (lambda prefixes: None)
+
+        def ready(prefixes):
+            self._join_aux()
+            on_ready(prefixes)
+
         ready(None)
         box = {"dX": dX, "dY": dY}
         for st in reversed(sv["stages"]):
@@ -586,4 +622,5 @@ class Engine(object):
         self.text_embed_bwd(d_et, sv_et)
         self.text_embed_bwd(d_epv, sv_epv)
         self.image_embed_bwd(d_ev, sv_ev)
+        self._join_aux()
         self.saved = None

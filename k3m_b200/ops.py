@@ -45,6 +45,11 @@ class CudaOps(object):
         self._work = 0.0
         self._tag = ""
         self._side = []
+        # auxiliary stream per launching stream for off-critical-path work (weight gradients):
+        # stream handle -> [aux stream, tensors kept alive until the join, pending flag]
+        self._aux = {}
+        import os
+        self.use_aux = os.environ.get("K3M_WGRAD_STREAM", "1") != "0"
 
     def parallel(self, fns):
         """Run independent closures on concurrent CUDA streams (fork after the current stream, join back
@@ -71,11 +76,45 @@ class CudaOps(object):
             st.wait_event(fork)
             with torch.cuda.stream(st):
                 f()
+                self.join_aux()
                 ev = torch.cuda.Event()
                 ev.record(st)
             joins.append(ev)
         for ev in joins:
             main.wait_event(ev)
+
+    def aux(self, fn, keep=()):
+        """Run `fn` (kernels whose results nothing on the critical path reads: weight and bias gradients)
+        on the auxiliary stream of the current stream, ordered after everything queued on it so far.
+        `keep`: tensors `fn` reads; they stay referenced until `join_aux`, because the caching allocator
+        would otherwise hand their memory to the next allocation on the launching stream while the
+        auxiliary stream has not consumed them yet."""
+        if self.timing is not None or not self.use_aux:
+            fn()
+            return
+        cur = torch.cuda.current_stream()
+        rec = self._aux.get(cur.cuda_stream)
+        if rec is None:
+            rec = self._aux[cur.cuda_stream] = [torch.cuda.Stream(device=self.device), [], False]
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        rec[0].wait_event(ev)
+        with torch.cuda.stream(rec[0]):
+            fn()
+        rec[1].extend(keep)
+        rec[2] = True
+
+    def join_aux(self):
+        """The current stream waits for its auxiliary stream (no-op if nothing is pending)."""
+        cur = torch.cuda.current_stream()
+        rec = self._aux.get(cur.cuda_stream)
+        if rec is None or not rec[2]:
+            return
+        ev = torch.cuda.Event()
+        ev.record(rec[0])
+        cur.wait_event(ev)
+        del rec[1][:]
+        rec[2] = False
 
     def _st(self):
         return _vp(torch.cuda.current_stream().cuda_stream)
@@ -252,15 +291,23 @@ class CudaOps(object):
         self._call("k3m_axpy", _p(x), _i(_ld(x)), _i(_isf32(x)), _p(y), _i(_ld(y)), _i(_isf32(y)), _f(alpha),
                    _i(rows), _i(cols), self._st())
 
-    def cast(self, x, dtype):
+    def cast(self, x, dtype, out=None):
         assert x.is_contiguous()
-        y = torch.empty(x.shape, dtype=dtype, device=x.device)
+        y = out if out is not None else torch.empty(x.shape, dtype=dtype, device=x.device)
+        assert y.is_contiguous() and y.dtype == dtype and y.numel() == x.numel()
         self._call("k3m_cast", _p(x), _i(_isf32(x)), _p(y), _i(_isf32(y)), _ll(x.numel()), self._st())
         return y
 
     def scale_(self, x, alpha):
         assert x.dtype == torch.float32 and x.is_contiguous()
         self._call("k3m_scale", _p(x), _f(alpha), _ll(x.numel()), self._st())
+
+    def scale_dev_(self, x, alpha):
+        """x *= alpha[0] with alpha an fp32 device tensor."""
+        assert alpha.dtype == torch.float32 and alpha.numel() == 1
+        x2 = x if x.dim() == 2 else x.reshape(1, -1)
+        self._call("k3m_scale_dev", _p(x2), _i(_ld(x2)), _i(_isf32(x2)), _p(alpha), _i(x2.shape[0]), _i(x2.shape[1]),
+                   self._st())
 
     def act_bwd(self, dy, pre, act):
         assert act == ACT_DGELU and dy.is_contiguous() and pre.is_contiguous()

@@ -106,7 +106,11 @@ class PretrainStep(object):
         self.h2d_bytes += sum(v.numel() * 4 for v in self.plan.values()) + self.hyper.numel() * 4
         self.d2h_bytes = self.losses.numel() * 4
         self._buckets = self._make_buckets(bucket_mb)
-        self._comm_stream = torch.cuda.Stream(device=dev) if (self.world > 1 and self._cuda) else None
+        # side stream of the optimizer pipeline: all-reduce of a gradient bucket (world > 1) followed by
+        # AdamW on the same range, while backward is still producing the earlier layers' gradients
+        import os
+        self.overlap_opt = overlap and os.environ.get("K3M_OPT_OVERLAP", "1") != "0"
+        self._comm_stream = torch.cuda.Stream(device=dev) if (self._cuda and (self.world > 1 or self.overlap_opt)) else None
         self.use_graph = use_graph and self._cuda
         self.graph = None
         self.launches_per_step = 0
@@ -187,34 +191,46 @@ class PretrainStep(object):
             self._stage_lo[key] = min(self._stage_lo.get(key, L.decay_end), off)
         return out
 
-    def _reduce_range(self, lo, hi):
+    def _bucket_step(self, bi):
+        """All-reduce (world > 1) then AdamW of bucket `bi`, on the side stream when there is one.  A
+        bucket's parameters are no longer read by backward once its gradients are final (`_on_ready`), so
+        updating them under the rest of backward is safe; AdamW is HBM-bound and the GEMMs it runs
+        beside are not."""
+        lo, hi = self._buckets[bi]
+        gi = 1 if bi == len(self._buckets) - 1 else 0       # the last bucket is the no-decay region
         t = self.g32[lo:hi]
+
+        def work():
+            if self.world > 1:
+                torch.distributed.all_reduce(t, group=self.group)
+            # gradients are summed over ranks; hyper[:, 6] = 1/world turns that into DDP's mean
+            self.ops.adamw(self.p32[lo:hi], t, self.m[lo:hi], self.v[lo:hi], self.w16[lo:hi], self.hyper[gi],
+                           zero_grad=True)
+
         if self._comm_stream is None:
-            torch.distributed.all_reduce(t, group=self.group)
+            work()
             return
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream())
         with torch.cuda.stream(self._comm_stream):
             self._comm_stream.wait_event(ev)
-            torch.distributed.all_reduce(t, group=self.group)
+            work()
 
     def _on_ready(self, prefixes):
         """Engine callback: backward has finished every weight gradient of `prefixes` (None = the
         heads, fusion gates and aggregator).  Launch every bucket that is now final."""
-        if self.world == 1 or not self.overlap:
+        if not self.overlap or (self.world == 1 and not self.overlap_opt):
             return
         keys = ["<tail>"] if prefixes is None else prefixes
         for k in keys:
             self._ready_lo = min(self._ready_lo, self._stage_lo.get(k, self._ready_lo))
         while self._next_bucket < len(self._buckets) - 1 and self._buckets[self._next_bucket][0] >= self._ready_lo:
-            self._reduce_range(*self._buckets[self._next_bucket])
+            self._bucket_step(self._next_bucket)
             self._next_bucket += 1
 
-    def _finish_reduce(self):
-        if self.world == 1:
-            return
+    def _finish_buckets(self):
         while self._next_bucket < len(self._buckets):
-            self._reduce_range(*self._buckets[self._next_bucket])
+            self._bucket_step(self._next_bucket)
             self._next_bucket += 1
         if self._comm_stream is not None:
             torch.cuda.current_stream().wait_stream(self._comm_stream)
@@ -226,11 +242,7 @@ class PretrainStep(object):
         out = self.engine.forward(self.inputs, self.plan, None, self.loss_weights)
         self.engine.on_ready = self._on_ready
         self.engine.backward()
-        self._finish_reduce()
-        # gradients are summed over ranks; hyper[:, 6] = 1/world turns that into DDP's mean
-        for gi, (lo, hi) in enumerate(((0, L.decay_end), (L.decay_end, L.trained_end))):
-            ops.adamw(self.p32[lo:hi], self.g32[lo:hi], self.m[lo:hi], self.v[lo:hi], self.w16[lo:hi],
-                      self.hyper[gi], zero_grad=True)
+        self._finish_buckets()
         self.rng[1:].add_(1)
         w = self.loss_weights
         torch.stack([out[k].reshape(()) for k in LOSS_NAMES], out=self.losses[:5])

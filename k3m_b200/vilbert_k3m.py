@@ -1,0 +1,387 @@
+"""Drop-in model classes: the reference's Python class API over the sm_100a kernels.
+
+`BertForMultiModalPreTraining_tri_stru(config)` mirrors the reference class of the same name
+(`vilbert_k3m/vilbert_k3m.py:2190-2860`): same constructor, same `forward(...)` signature and
+10-tuple return (`:2673-2696`, `:2834-2846`), same `named_parameters()` names and order (998) and
+`state_dict()` keys (999, tied decoder alias), `from_pretrained` (`utils.py:884-1078`), so it drops
+into `pretrain.py:990-1024` / `train_concap_struc.py:503`:
+
+    out = model(input_ids, image_feat, image_loc, segment_ids, input_mask, image_mask, lm_label_ids,
+                image_label, image_target, is_next, False, input_ids_pv, ...)
+    loss = out[0] + out[1] * w + out[3] + out[9]; loss.backward(); optimizer.step()
+
+How it differs inside (results are the reference's):
+  * every parameter is an fp32 `nn.Parameter` that is a VIEW into one flat arena (`ArenaLayout`);
+    `torch.optim.AdamW` / `clip_grad_norm_` / checkpoints see ordinary parameters;
+  * forward casts the arena to a bf16 shadow and runs `Engine.forward` (hand-written kernels through
+    the C ABI); the four training losses come back attached to ONE autograd node whose backward runs
+    `Engine.backward` and points every trained parameter's `.grad` at its slice of the fp32
+    gradient arena (`.grad` of the 86 never-trained tensors stays None, like in the reference);
+  * data parallel: autograd hooks of `DistributedDataParallel` never fire (there is no per-parameter
+    autograd graph) — call `model.set_process_group(pg)` instead and backward all-reduces the
+    gradient arena itself (mean over ranks, DDP semantics).
+There is no CPU path: without the CUDA library `forward` raises (`k3m_b200._lib`).  Tests inject
+the fp32 restatement of the kernels through `ops=` to check THIS host logic on CPU.
+
+The graph-captured production step (`k3m_b200.trainer.PretrainStep`: static buffers, fused AdamW,
+overlapped all-reduce) is what `bench.py` measures; this class is the compatibility surface.
+"""
+import logging
+import os
+import sys
+
+import torch
+from torch import nn
+
+from .config import BertConfig  # noqa: F401  (re-exported under the reference's module path)
+from .engine import Engine
+from .layout import ArenaLayout, TIED_ALIAS
+from .struct_plan import build_struct_plan
+
+logger = logging.getLogger(__name__)
+
+WEIGHTS_NAME = "pytorch_model.bin"      # `utils.py:44`
+
+
+class _Node(nn.Module):
+    """Anonymous container: gives parameters the reference's dotted names."""
+
+    def forward(self, *a, **k):
+        raise RuntimeError("k3m_b200 modules are parameter containers; call the model's forward()")
+
+
+class _StepFunction(torch.autograd.Function):
+    """One autograd node for the whole step.  Inputs: a dummy leaf (so that autograd records the
+    node) and the owning module; outputs: the four training losses (differentiable) and the
+    value-only results."""
+
+    @staticmethod
+    def forward(ctx, anchor, owner, batch, plan):
+        out = owner._engine.forward(batch, plan, None, (1.0, 1.0, 1.0, 1.0))
+        ctx.owner = owner
+        ctx.token = owner._fwd_token
+        res = (out["loss_t"], out["loss_v"], out["loss_pv"], out["loss_lpm"], out["loss_itm"],
+               out["c_initial"], out["c_final"])
+        ctx.mark_non_differentiable(res[4], res[5], res[6])
+        return res
+
+    @staticmethod
+    def backward(ctx, g_t, g_v, g_pv, g_lpm, *unused):
+        owner = ctx.owner
+        if ctx.token != owner._fwd_token:
+            raise RuntimeError("backward() of a K3M step whose activations were released by a later forward(); "
+                               "call backward before the next forward (the reference's drivers do)")
+        owner._run_backward((g_t, g_v, g_pv, g_lpm))
+        return None, None, None, None
+
+
+class K3MPreTrainedModel(nn.Module):
+    """Parameter arena + the reference's `PreTrainedModel` entry points used by the drivers."""
+
+    config_class = BertConfig
+    base_model_prefix = "bert"
+
+    def __init__(self, config, ops=None):
+        super(K3MPreTrainedModel, self).__init__()
+        if not isinstance(config, BertConfig):
+            raise ValueError(
+                "Parameter config in `{}(config)` should be an instance of class `BertConfig`. "
+                "To create a model from a Google pretrained model use "
+                "`model = {}.from_pretrained(PRETRAINED_MODEL_NAME)`".format(
+                    self.__class__.__name__, self.__class__.__name__))
+        self.config = config
+        self._ops = ops
+        self._layout = ArenaLayout(config)
+        self._arena = torch.zeros(self._layout.total, dtype=torch.float32)
+        self._engine = None
+        self._w16 = self._g32 = self._rng = None
+        self._anchor = torch.zeros(1, requires_grad=True)
+        self._fwd_token = 0
+        self._group = None
+        self._params = {}
+        self._build_parameters()
+        self.init_weights()
+
+    # ---- parameters ------------------------------------------------------------------------
+    def _build_parameters(self):
+        L = self._layout
+        for name in L.spec:
+            off, num, shape = L.offsets[name]
+            p = nn.Parameter(self._arena[off:off + num].view(*shape))
+            self._params[name] = p
+            self._node_for(name).register_parameter(name.rsplit(".", 1)[1], p)
+        # the tied decoder (`tie_weights`, `vilbert_k3m.py:2266-2272`): same Parameter object under a
+        # second name -> named_parameters() lists it once, state_dict() twice (999 keys)
+        self._node_for(TIED_ALIAS[0]).register_parameter(TIED_ALIAS[0].rsplit(".", 1)[1],
+                                                         self._params[TIED_ALIAS[1]])
+
+    def _node_for(self, dotted):
+        node = self
+        for part in dotted.split(".")[:-1]:
+            nxt = node._modules.get(part)
+            if nxt is None:
+                nxt = _Node()
+                node.add_module(part, nxt)
+            node = nxt
+        return node
+
+    def _rebind(self):
+        """Point every Parameter at the (new) arena; drops device-side state."""
+        L = self._layout
+        with torch.no_grad():
+            for name, p in self._params.items():
+                off, num, shape = L.offsets[name]
+                p.data = self._arena[off:off + num].view(*shape)
+                p.grad = None
+        self._engine = None
+        self._w16 = self._g32 = self._rng = None
+        self._anchor = torch.zeros(1, requires_grad=True, device=self._arena.device)
+
+    def _apply(self, fn, recurse=True):
+        """`.cuda()` / `.to(device)` / `.float()`: move the ARENA, then re-view the parameters (the
+        default per-parameter move would scatter them).  Master weights stay fp32 — `.half()` /
+        `.bfloat16()` are accepted and ignored: the kernels compute in bf16 from a shadow copy anyway."""
+        new = fn(self._arena)
+        if new.dtype != torch.float32:
+            new = new.to(torch.float32)
+        if new is not self._arena:
+            self._arena = new.contiguous()
+            self._rebind()
+        return self
+
+    def init_weights(self, seed=None):
+        """`init_weights` (`vilbert_k3m.py:1940-1951`) applied by `self.apply` BEFORE `struc_w1/2/3`
+        exist (`:2252-2259`): N(0, initializer_range) Linear / Embedding weights, zero biases,
+        LayerNorm (1, 0); the aggregator keeps nn.Linear's default U(-1/sqrt(in), 1/sqrt(in))."""
+        import math
+        g = None
+        if seed is not None:
+            g = torch.Generator(device=self._arena.device).manual_seed(seed)
+        with torch.no_grad():
+            for n, p in self._params.items():
+                if n.startswith("struc_w"):
+                    fan_in = self._layout.spec[n.rsplit(".", 1)[0] + ".weight"][1]
+                    bound = 1.0 / math.sqrt(fan_in)
+                    p.uniform_(-bound, bound, generator=g)
+                elif "LayerNorm" in n:
+                    p.fill_(1.0 if n.endswith("weight") else 0.0)
+                elif p.dim() == 1:
+                    p.zero_()
+                else:
+                    p.normal_(0.0, self.config.initializer_range, generator=g)
+
+    def tie_weights(self):
+        """Already tied by construction (one Parameter, two names)."""
+
+    def set_process_group(self, group, world_size=None):
+        """Data parallel without DDP: backward all-reduces the fp32 gradient arena over `group` and
+        divides by its size (what DDP's hooks do per bucket, `pretrain.py:166`)."""
+        self._group = group
+        self._world = world_size if world_size is not None else torch.distributed.get_world_size(group)
+
+    # ---- checkpoints -----------------------------------------------------------------------
+    @classmethod
+    def from_pretrained(cls, pretrained_model_name_or_path, *model_args, **kwargs):
+        """`PreTrainedModel.from_pretrained` (`utils.py:884-1078`) for local files: a directory holding
+        `pytorch_model.bin` or a path to a `.bin`; keys may carry `module.` (saved from DDP,
+        `pretrain.py:1238-1251`) or `bert.` prefixes.  Returns the model in eval mode, or None (after
+        logging) when the file does not exist — the reference's convention (`utils.py:977`)."""
+        config = kwargs.pop("config", None)
+        state_dict = kwargs.pop("state_dict", None)
+        kwargs.pop("cache_dir", None)
+        kwargs.pop("from_tf", None)
+        kwargs.pop("default_gpu", None)
+        output_loading_info = kwargs.pop("output_loading_info", False)
+        if config is None:
+            cfg_path = os.path.join(pretrained_model_name_or_path, "config.json")
+            config = BertConfig.from_json_file(cfg_path)
+        model = cls(config, *model_args, **kwargs)
+        if state_dict is None:
+            path = pretrained_model_name_or_path
+            if os.path.isdir(path):
+                path = os.path.join(path, WEIGHTS_NAME)
+            if not os.path.isfile(path):
+                logger.error("Model name '%s' was not found: no file %s", pretrained_model_name_or_path, path)
+                return None
+            state_dict = torch.load(path, map_location="cpu")
+        clean = {}
+        for k, v in state_dict.items():
+            for pre in ("module.", "bert."):
+                if k.startswith(pre):
+                    k = k[len(pre):]
+            clean[k] = v
+        res = model.load_state_dict(clean, strict=False)
+        if res.missing_keys:
+            logger.info("Weights of %s not initialized from pretrained model: %s", cls.__name__, res.missing_keys)
+        if res.unexpected_keys:
+            logger.info("Weights from pretrained model not used in %s: %s", cls.__name__, res.unexpected_keys)
+        model.eval()
+        if output_loading_info:
+            return model, {"missing_keys": res.missing_keys, "unexpected_keys": res.unexpected_keys,
+                           "error_msgs": []}
+        return model
+
+    def save_pretrained(self, save_directory):
+        """`utils.py:847-882`: config.json + pytorch_model.bin."""
+        assert os.path.isdir(save_directory), "Saving path should be a directory where the model and configuration can be saved"
+        with open(os.path.join(save_directory, "config.json"), "w", encoding="utf-8") as f:
+            f.write(self.config.to_json_string())
+        torch.save({k: v.detach().cpu().clone() for k, v in self.state_dict().items()},
+                   os.path.join(save_directory, WEIGHTS_NAME))
+
+    # ---- device state ----------------------------------------------------------------------
+    def _ensure_engine(self):
+        if self._engine is not None:
+            return
+        dev = self._arena.device
+        if self._ops is None:
+            if dev.type != "cuda":
+                from . import _lib
+                raise _lib.K3MError("k3m_b200 runs on a CUDA device (sm_100a) only: move the model with "
+                                    ".cuda() first; there is no CPU path")
+            from .ops import CudaOps
+            self._ops = CudaOps(dev)
+        adt = getattr(self._ops, "adt", torch.bfloat16)
+        L = self._layout
+        self._w16 = torch.zeros(L.total, dtype=adt, device=dev)
+        self._g32 = torch.zeros(L.total, dtype=torch.float32, device=dev)
+        self._rng = torch.tensor([getattr(self.config, "rng_seed", 1234), 0], dtype=torch.int64, device=dev)
+        self._engine = Engine(self.config, L, self._ops, self._w16, self._g32, self._rng, adt)
+
+    def _run_backward(self, grads):
+        L, ops = self._layout, self._ops
+        dev = self._arena.device
+        first = self._params[next(n for n in L.spec if n not in L.frozen)]
+        if first.grad is None:
+            self._g32.zero_()          # fresh accumulation (optimizer.zero_grad(set_to_none=True))
+        scales = []
+        for g in grads:
+            if g is None:
+                g = torch.zeros(1, dtype=torch.float32, device=dev)
+            scales.append(g.reshape(1).to(torch.float32).contiguous())
+        self._engine.backward(tuple(scales))
+        if self._group is not None and self._world > 1:
+            torch.distributed.all_reduce(self._g32[:L.trained_end], group=self._group)
+            ops.scale_(self._g32[:L.trained_end], 1.0 / self._world)
+        for n, p in self._params.items():
+            if n in L.frozen:
+                continue
+            if p.grad is None:
+                off, num, shape = L.offsets[n]
+                p.grad = self._g32[off:off + num].view(*shape)
+
+
+def _as_dev(t, device, dtype=None):
+    if t is None:
+        return None
+    t = t.to(device=device, non_blocking=True)
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    return t.contiguous()
+
+
+class BertForMultiModalPreTraining_tri_stru(K3MPreTrainedModel):
+    """`vilbert_k3m/vilbert_k3m.py:2190-2860`: title / image / PV tri-stream ViLBERT with the
+    structure aggregator and the MLM + MRM-KL + MLM-pv + LPM (+ ITM value) pretraining losses."""
+
+    def __init__(self, config, ops=None):
+        if getattr(config, "visual_target", 0) != 0:
+            raise NotImplementedError("visual_target 1 (MSE) / 2 (NCE) are not on the K3M path "
+                                      "(the reference's NCE branch reads an undefined attribute, vilbert_k3m.py:2764)")
+        super(BertForMultiModalPreTraining_tri_stru, self).__init__(config, ops)
+
+    def forward(
+            self,
+            input_ids,
+            image_feat,
+            image_loc,
+            token_type_ids=None,
+            attention_mask=None,
+            image_attention_mask=None,
+            masked_lm_labels=None,
+            image_label=None,
+            image_target=None,
+            next_sentence_label=None,
+            output_all_attention_masks=False,
+            input_ids_pv=None,
+            token_type_ids_pv=None,
+            attention_mask_pv=None,
+            masked_lm_labels_pv=None,
+            next_sentence_label_pv_v=None,
+            next_sentence_label_pv_t=None,
+            index_p=None,
+            index_v=None,
+            device=None,
+    ):
+        """Returns the reference's 10-tuple (`:2834-2846`):
+        (mlm_t[1], mrm[1], 0, mlm_pv[1], 0, 0, itm[1], c_initial[B,768], c_final[B,768], lpm[1]).
+        The label-free branch of the reference (`:2853-2859`) reads undefined names and cannot run
+        there either; here it raises."""
+        if masked_lm_labels is None or next_sentence_label is None or image_target is None:
+            raise NotImplementedError("the K3M pretraining forward needs the labels "
+                                      "(the reference's label-free branch is not runnable, vilbert_k3m.py:2853-2859)")
+        if input_ids_pv is None or index_p is None or index_v is None:
+            raise ValueError("input_ids_pv / index_p / index_v are required (tri-stream model)")
+        self._ensure_engine()
+        dev = self._arena.device
+        i64, f32 = torch.int64, torch.float32
+        ones = lambda ref: torch.ones_like(ref)          # noqa: E731  (`bert_tri` defaults, `:2546-2556`)
+        zeros = lambda ref: torch.zeros_like(ref)        # noqa: E731
+        B = input_ids.shape[0]
+        batch = dict(
+            input_ids=_as_dev(input_ids, dev, i64),
+            token_type_ids=_as_dev(token_type_ids if token_type_ids is not None else zeros(input_ids), dev, i64),
+            attention_mask=_as_dev(attention_mask if attention_mask is not None else ones(input_ids), dev, i64),
+            masked_lm_labels=_as_dev(masked_lm_labels, dev, i64),
+            input_ids_pv=_as_dev(input_ids_pv, dev, i64),
+            token_type_ids_pv=_as_dev(token_type_ids_pv if token_type_ids_pv is not None else zeros(input_ids_pv), dev, i64),
+            attention_mask_pv=_as_dev(attention_mask_pv if attention_mask_pv is not None else ones(input_ids_pv), dev, i64),
+            masked_lm_labels_pv=_as_dev(masked_lm_labels_pv, dev, i64),
+            image_feat=_as_dev(image_feat, dev, f32),
+            image_loc=_as_dev(image_loc, dev, f32),
+            image_attention_mask=_as_dev(image_attention_mask if image_attention_mask is not None
+                                         else torch.ones(image_feat.shape[:2], dtype=i64), dev, i64),
+            image_label=_as_dev(image_label, dev, i64),
+            image_target=_as_dev(image_target, dev, f32),
+            next_sentence_label=_as_dev(next_sentence_label.reshape(B), dev, i64),
+            next_sentence_label_pv_v=_as_dev((next_sentence_label_pv_v if next_sentence_label_pv_v is not None
+                                              else zeros(next_sentence_label)).reshape(B), dev, i64),
+            next_sentence_label_pv_t=_as_dev((next_sentence_label_pv_t if next_sentence_label_pv_t is not None
+                                              else zeros(next_sentence_label)).reshape(B), dev, i64),
+        )
+        # the aggregator's pair lists and LPM negatives are drawn on the host with the reference's own
+        # `random.sample` call sequence (`:2437-2502`) — one device->host copy of two small index
+        # tensors replaces the reference's one sync per (item, PV) pair
+        plan = build_struct_plan(index_p.detach().cpu().numpy(), index_v.detach().cpu().numpy(),
+                                 batch["input_ids_pv"].shape[1], self.config.num_negative_pv)
+        plan = self._ops.plan_to_device(plan, dev)
+        ops = self._ops
+        ops.cast(self._arena, self._w16.dtype, out=self._w16)      # bf16 shadow of the (possibly just updated) masters
+        eng = self._engine
+        eng.training = self.training
+        self._fwd_token += 1
+        if torch.is_grad_enabled():
+            lt, lv, lpv, llpm, litm, c_init, c_fin = _StepFunction.apply(self._anchor, self, batch, plan)
+        else:
+            out = eng.forward(batch, plan, None, (1.0, 1.0, 1.0, 1.0))
+            eng.saved = None
+            lt, lv, lpv, llpm, litm = (out[k] for k in ("loss_t", "loss_v", "loss_pv", "loss_lpm", "loss_itm"))
+            c_init, c_fin = out["c_initial"], out["c_final"]
+        self._rng[1:].add_(1)
+        return (lt.reshape(1), lv.reshape(1), 0, lpv.reshape(1), 0, 0, litm.reshape(1), c_init, c_fin,
+                llpm.reshape(1))
+
+
+def install_as_reference():
+    """Make `from vilbert_k3m.vilbert_k3m import BertConfig, BertForMultiModalPreTraining_tri_stru`
+    (`pretrain.py:25`, `train_concap_struc.py:26`) resolve to this package."""
+    import types
+    pkg = sys.modules.get("vilbert_k3m")
+    if pkg is None:
+        pkg = types.ModuleType("vilbert_k3m")
+        pkg.__path__ = []
+        sys.modules["vilbert_k3m"] = pkg
+    mod = sys.modules[__name__]
+    sys.modules["vilbert_k3m.vilbert_k3m"] = mod
+    pkg.vilbert_k3m = mod
+    return mod

@@ -27,9 +27,12 @@ def _mulhilo(m, c):
     return u >> 16, lo
 
 
+PHILOX_ROUNDS = 7
+
+
 def philox4x32(c0, c1, c2, c3, k0, k1):
-    """Philox4x32-10 on int64 tensors holding 32-bit values (same rounds as the CUDA kernels)."""
-    for _ in range(10):
+    """Philox4x32-7 on int64 tensors holding 32-bit values (same rounds as the CUDA kernels)."""
+    for _ in range(PHILOX_ROUNDS):
         hi0, lo0 = _mulhilo(_M0, c0)
         hi1, lo1 = _mulhilo(_M1, c2)
         c0, c1, c2, c3 = (hi1 ^ c1 ^ k0) & _MASK32, lo1, (hi0 ^ c3 ^ k1) & _MASK32, lo0
@@ -321,8 +324,14 @@ class RefOps(object):
         """y += alpha * x."""
         y.add_((alpha * x.float()).to(y.dtype))
 
-    def cast(self, x, dtype):
+    def cast(self, x, dtype, out=None):
+        if out is not None:
+            out.copy_(x)
+            return out
         return x.to(dtype)
+
+    def scale_dev_(self, x, alpha):
+        x.mul_(alpha.to(x.dtype))
 
     def scale_(self, x, alpha):
         x.mul_(alpha)
