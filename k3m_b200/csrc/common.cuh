@@ -81,15 +81,25 @@ __device__ __forceinline__ float drop_mult_at(const DropSpec& d, unsigned long l
 // divergent polynomial branches.  The epilogues that use it are instruction-issue bound (K = 768
 // leaves ~6000 clocks of main loop per 128x256 tile), so this is what the tile time is made of.
 // `e` returns exp(-x^2 / 2) for the derivative.
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
 __device__ __forceinline__ float gauss_cdf(float x, float& e) {
   const float z = fabsf(x) * 0.70710678118654752f;
-  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
-  e = __expf(-0.5f * x * x);
-  float p = fmaf(1.061405429f, t, -1.453152027f);
-  p = fmaf(p, t, 1.421413741f);
-  p = fmaf(p, t, -0.284496736f);
-  p = fmaf(p, t, 0.254829592f);
-  const float h = 0.5f * p * t * e;   // 0.5 * erfc(|x| / sqrt 2)
+  const float t = rcp_approx(fmaf(0.3275911f, z, 1.0f));        // MUFU.RCP, no IEEE fix-up path
+  e = ex2_approx(x * x * -0.72134752044448170f);                 // exp(-x^2 / 2) = 2^(-x^2 log2(e) / 2)
+  float p = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);  // coefficients carry the 0.5 of erfc / 2
+  p = fmaf(p, t, 0.5f * 1.421413741f);
+  p = fmaf(p, t, 0.5f * -0.284496736f);
+  p = fmaf(p, t, 0.5f * 0.254829592f);
+  const float h = p * t * e;          // 0.5 * erfc(|x| / sqrt 2)
   return x >= 0.0f ? 1.0f - h : h;
 }
 __device__ __forceinline__ float gelu_f(float x) {

@@ -46,7 +46,7 @@ struct GemmParams {
   int drop_ld;
   int vec_ok;  // all epilogue pointers 16 B aligned with ld % 8 == 0
   int tma_out; // out (and aux_out) leave through TMA bulk stores
-  int two_pass;
+  int fast;    // specialised epilogue (F_* below), 0 = generic
   int tin;     // epilogue operand that ARRIVES through TMA into the staging buffer: 0 none, 1 aux_in, 2 addend
 };
 
@@ -227,6 +227,143 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const 
                ::"l"(map), "r"(smem_u32(src)), "r"(c0), "r"(c1) : "memory");
 }
 
+// ---- specialised epilogues ----------------------------------------------------------------------
+// The generic epilogue above decides everything per 8-column group at run time (activation, vector
+// or scalar access, edge handling): ~35 issued instructions per output element, a third of them
+// branches and predicate shuffling — longer than the K = 768 main loop of the tile it overlaps with.
+// The four shapes of epilogue the K3M step spends its time in are compiled separately, branch-free:
+//   F_PLAIN  out = acc (+ bias) (dropout)                        projections, plain dgrads
+//   F_ADD    out = acc (+ bias) (dropout) + addend (via TMA)     attention-out / FFN-down, dgrad + residual
+//   F_GELU   aux = acc + bias, out = gelu(aux)                   FFN-up
+//   F_DGELU  out = acc * gelu'(aux_in) (aux_in via TMA)          FFN-down dgrad
+// Preconditions (host): bf16 output through TMA, no accumulation, N % 8 == 0, 16-byte aligned bias.
+enum { F_NONE = 0, F_PLAIN = 1, F_ADD = 2, F_GELU = 3, F_DGELU = 4 };
+
+__device__ __forceinline__ uint4 pack_bf16x8(const float v[8]) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+  return u;
+}
+__device__ __forceinline__ void unpack_bf16x8(const uint4& u, float v[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __bfloat1622float2(h[i]);
+    v[2 * i] = f.x; v[2 * i + 1] = f.y;
+  }
+}
+
+// acc (+ bias) of one 8-column group
+__device__ __forceinline__ void acc_bias(const GemmParams& p, const uint32_t* r, int col, float v[8]) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[j]);
+  if (p.bias != nullptr && col < p.N) {
+    float t[8];
+    ld8(p.bias + col, t);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] += t[j];
+  }
+}
+
+// one 32-row x CW-column piece of an output tile, by one epilogue warp (row = lane)
+template <int CW, int NBUF, int MODE>
+__device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap* mc, const CUtensorMap* mx,
+                                          uint8_t* my_stage, uint32_t& nstore, uint32_t tbase, int row0, int n0,
+                                          int lane) {
+  constexpr uint32_t RB = CW * 2;                 // bytes per staged row
+  constexpr uint32_t SM = RB == 64 ? 3u : 7u;     // 64-byte rows are SWIZZLE_64B boxes
+  uint8_t* buf = my_stage + (nstore % NBUF) * 4096;
+  uint8_t* abuf = my_stage + ((nstore + 1) % NBUF) * 4096;
+  if (MODE == F_PLAIN || MODE == F_GELU) {        // (TMA-fed modes: the operand prefetch waited already)
+    if (lane == 0) {
+      if (MODE == F_GELU || NBUF == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      else asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+    }
+    __syncwarp();
+  }
+  if (MODE == F_GELU && NBUF == 1) {
+    // one staging buffer, two outputs: two passes over the accumulator (TMEM reads are cheap) — the
+    // pre-activation leaves first, then the activation through the same buffer
+#pragma unroll
+    for (int pass = 0; pass < 2; ++pass) {
+#pragma unroll
+      for (int cc = 0; cc < CW; cc += 32) {
+        uint32_t r[32];
+        tmem_ld32(tbase + (uint32_t)cc, r);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float v[8];
+          acc_bias(p, r + g * 8, n0 + cc + g * 8, v);
+          if (pass == 1) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
+          }
+          *reinterpret_cast<uint4*>(buf + swz((uint32_t)lane * RB + (uint32_t)((cc + g * 8) * 2), SM)) = pack_bf16x8(v);
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_2d(pass == 0 ? mx : mc, buf, n0, row0);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        if (pass == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      }
+      __syncwarp();
+    }
+    nstore += 1;
+    return;
+  }
+  const bool has_drop = p.drop.thresh != 0;
+  const int row = row0 + lane;
+#pragma unroll
+  for (int cc = 0; cc < CW; cc += 32) {
+    uint32_t r[32];
+    tmem_ld32(tbase + (uint32_t)cc, r);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const int col = n0 + cc + g * 8;
+      const uint32_t off = swz((uint32_t)lane * RB + (uint32_t)((cc + g * 8) * 2), SM);
+      float v[8];
+      acc_bias(p, r + g * 8, col, v);
+      if (MODE == F_GELU) {
+        *reinterpret_cast<uint4*>(abuf + off) = pack_bf16x8(v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
+      }
+      if (MODE == F_DGELU) {
+        float t[8];
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(buf + off), t);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] *= dgelu_f(t[j]);
+      }
+      if (MODE != F_GELU && MODE != F_DGELU && has_drop) {
+        uint32_t w[4];
+        const unsigned long long lin = (unsigned long long)row * (unsigned long long)p.drop_ld + (unsigned long long)col;
+        rng_words(p.drop.rng, p.drop.site, lin >> 3, w);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] *= drop_mult(p.drop, w, j);
+      }
+      if (MODE == F_ADD) {
+        float t[8];
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(buf + off), t);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] += t[j];
+      }
+      *reinterpret_cast<uint4*>(buf + off) = pack_bf16x8(v);
+    }
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_2d(mc, buf, n0, row0);
+    if (MODE == F_GELU) tma_store_2d(mx, abuf, n0, row0);
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  }
+  nstore += MODE == F_GELU ? 2 : 1;
+}
+
 // Persistent, warp-specialised: every CTA walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...
 // (tile = (split, m, n), n fastest so neighbouring CTAs share the A panel in L2).  The smem ring
 // (TMA -> MMA) runs across tile boundaries and the accumulator is double-buffered in TMEM, so the
@@ -365,11 +502,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     const int chunk_cols = (CW * esz > 128) ? 128 / esz : CW;      // columns per staged box (<= 128 B per row)
     const uint32_t row_bytes = (uint32_t)(chunk_cols * esz);
     const uint32_t smask = row_bytes == 64 ? 3u : 7u, amask = CW * 2 == 64 ? 3u : 7u;   // 64 B rows use SWIZZLE_64B
-    // one staging buffer and two outputs (GELU forward keeps the pre-activation): two passes over the
-    // accumulator, each staged and bulk-stored through the same buffer (host guarantees bf16 out)
-    // (measured: recomputing the activation in the second pass costs more than the row-per-thread
-    // store of the pre-activation it replaces; enabled by GemmParams::two_pass for experiments only)
-    const bool two_pass = p.two_pass && p.tma_out && want_aux && NBUF == 1;
     const int tin = p.tin;                                          // host: only with tma_out, bf16 out, !want_aux
     uint64_t* in_bar = in_bars + e;
     uint32_t in_phase = 0;
@@ -410,7 +542,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         }
         uint8_t* buf = nullptr;
         uint8_t* abuf = nullptr;
-        for (int pass = 0; pass < (two_pass ? 2 : 1); ++pass) {
+        if (p.fast) {
+          const int row0 = m0 + q * 32;
+          switch (p.fast) {
+            case F_PLAIN: fast_tile<CW, NBUF, F_PLAIN>(p, &map_c, &map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
+            case F_ADD: fast_tile<CW, NBUF, F_ADD>(p, &map_c, &map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
+            case F_GELU: fast_tile<CW, NBUF, F_GELU>(p, &map_c, &map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
+            default: fast_tile<CW, NBUF, F_DGELU>(p, &map_c, &map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
+          }
+        } else {
 #pragma unroll 1
           for (int cc = 0; cc < CW; cc += 32) {
             if (!p.tma_out && n0 + cc >= p.N) break;
@@ -452,9 +592,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
                 for (int j = 0; j < 8; ++j) v[j] = pre[j] = 0.f;
               }
               if (p.tma_out) {
-                if (two_pass) {
-                  stage_bf16(buf, off, smask, pass == 0 ? pre : v);
-                } else {
+                {
                   if (p.out_f32) stage_f32(buf, off, smask, v);
                   else stage_bf16(buf, off, smask, v);
                   if (want_aux) {
@@ -476,8 +614,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
               __syncwarp();
               if (lane == 0) {
                 const int c0 = n0 + cc + 32 - chunk_cols;
-                if (two_pass && pass == 0) tma_store_2d(&map_aux, buf, c0, m0 + q * 32);
-                else if (p.accumulate) tma_reduce_add_2d(&map_c, buf, c0, m0 + q * 32);
+                if (p.accumulate) tma_reduce_add_2d(&map_c, buf, c0, m0 + q * 32);
                 else tma_store_2d(&map_c, buf, c0, m0 + q * 32);
                 if (want_aux && NBUF > 1) tma_store_2d(&map_aux, abuf, n0, m0 + q * 32);
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -680,8 +817,6 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   const int cw = bn / ew;
   CUtensorMap mi = ma;
   p.tin = 0;
-  static const int two_pass = getenv("K3M_GEMM_TWO_PASS") ? atoi(getenv("K3M_GEMM_TWO_PASS")) : 0;
-  p.two_pass = two_pass;
   if (p.tma_out) {
     const int box = (cw * esz > 128) ? 128 / esz : cw;
     if (!get_map(out, N, M, ldc, box, 32, &mc, esz)) return K3M_ERR_CUDA;
@@ -697,6 +832,19 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
         p.tin = 2; src = addend; ld_src = ld_add;
       }
       if (p.tin && !get_map(src, N, M, ld_src, cw, 32, &mi, 2)) return K3M_ERR_CUDA;
+    }
+  }
+  p.fast = F_NONE;
+  static const int no_fast = getenv("K3M_GEMM_NO_FAST") ? atoi(getenv("K3M_GEMM_NO_FAST")) : 0;
+  if (!no_fast && p.tma_out && !out_f32 && !accumulate && p.vec_ok && N % 8 == 0) {
+    const bool has_drop = p.drop.thresh != 0;
+    if (act == ACT_NONE && aux_out == nullptr) {
+      if (addend == nullptr) p.fast = F_PLAIN;
+      else if (p.tin == 2) p.fast = F_ADD;
+    } else if (act == ACT_GELU && want_aux && addend == nullptr && !has_drop) {
+      p.fast = F_GELU;
+    } else if (act == ACT_DGELU && p.tin == 1 && addend == nullptr && bias == nullptr && !has_drop) {
+      p.fast = F_DGELU;
     }
   }
   if (layout == 0) return dispatch<false, false>(bn, ew, ma, mb, mc, mx, mi, p, st);
