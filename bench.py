@@ -154,11 +154,15 @@ def kernel_breakdown(step, batch):
     import torch
     snap = (step.p32.clone(), step.m.clone(), step.v.clone(), step.w16.clone(), step.rng.clone())
     use_graph, step.use_graph = step.use_graph, False
+    # rank 0 profiles alone: no collective may be issued here (the other ranks are already at the final
+    # barrier), so the step runs as a single-rank step
+    world, step.world = step.world, 1
     step.ops.timing = []
     step.step(batch)
     torch.cuda.synchronize()
     rows, step.ops.timing = step.ops.timing, None
     step.use_graph = use_graph
+    step.world = world
     step.global_step -= 1
     for dst, src in zip((step.p32, step.m, step.v, step.w16, step.rng), snap):
         dst.copy_(src)
@@ -208,10 +212,17 @@ def run_gpu_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t)
 
+    def note(msg):
+        if os.environ.get("K3M_BENCH_VERBOSE"):
+            sys.stderr.write("[bench rank %d] %s\n" % (rank, msg))
+            sys.stderr.flush()
+
     # warm-up through the public call (captures the graph on the first step)
     for i in range(max(3, args.warmup)):
         step.step(host[i % 4])
+        note("warm-up step %d queued" % i)
     loss0 = step.read_losses()
+    note("warm-up done %s" % loss0)
     # ---- (1) device-resident: graph replays only ----
     barrier()
     clocks = ClockSampler(local) if rank == 0 else None
@@ -222,6 +233,7 @@ def run_gpu_arm(args):
     e1.record()
     barrier()
     ms_dev = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    note("device-resident loop done: %.3f ms/step" % ms_dev)
     # ---- (2) end to end: host batch -> H2D -> step -> D2H losses, every step ----
     barrier()
     e0.record()
@@ -231,6 +243,7 @@ def run_gpu_arm(args):
     e1.record()
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    note("end-to-end loop done: %.3f ms/step" % ms_e2e)
     clk = clocks.stop() if clocks is not None else None
     if rank != 0:
         if world > 1:

@@ -92,6 +92,46 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
       "}" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
 }
+// ---- CTA-pair (cta_group::2) variants: two CTAs of one cluster (one TPC) work on a 256-row tile; each
+// loads its own 128 rows of A and HALF of the B tile, the leader (rank 0) issues one MMA for both.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// destination in the executing CTA, completion bytes signalled on `bar_cluster` (a shared::cluster address,
+// the leader's barrier)
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint32_t bar_cluster, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1) : "memory");
+}
+// arrives on the barrier at the same shared-memory offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster) : "memory");
+}
+
 __device__ __forceinline__ void tmem_ld32(uint32_t addr, uint32_t r[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, "
@@ -368,15 +408,18 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
 // (tile = (split, m, n), n fastest so neighbouring CTAs share the A panel in L2).  The smem ring
 // (TMA -> MMA) runs across tile boundaries and the accumulator is double-buffered in TMEM, so the
 // epilogue of tile i overlaps the main loop of tile i + 1.
-template <int BN, int STAGES, int EW, bool A_MN, bool B_MN>
+template <int BN, int STAGES, int EW, bool A_MN, bool B_MN, int CTAS>
 __global__ void __launch_bounds__(64 + 128 * EW, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
             const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_aux,
             const __grid_constant__ CUtensorMap map_in, GemmParams p) {
   // warps: 0 = TMA producer, 1 = MMA issuer, 2 .. 2+4*EW-1 = epilogue.  Epilogue warp e handles the
   // TMEM lane quarter (warp % 4) and the column group e / 4 (CW = BN / EW columns) of every tile.
+  // CTAS == 2: CTA pair, 256 x BN tile per pair, this CTA holds rows rank*128.. of A / D and columns
+  // rank*BN/2.. of B (see the cta_group::2 helpers above)
+  constexpr int BNL = BN / CTAS;              // B columns this CTA loads
   constexpr int A_BYTES = BM * BK * 2;
-  constexpr int B_BYTES = BN * BK * 2;
+  constexpr int B_BYTES = BNL * BK * 2;
   constexpr int CW = BN / EW;
   static_assert(CW == 32 || CW == 64, "an epilogue warp owns 32 or 64 output columns");
   constexpr int NBUF = EW <= 2 ? 2 : 1;        // staging buffers (4 KB each) per epilogue warp
@@ -397,6 +440,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   const int total_kb = (p.K + BK - 1) / BK;
   const int tiles_mn = p.tiles_m * p.tiles_n;
   const int total_tiles = tiles_mn * p.splits;
+  const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0;
+  const int tile0 = blockIdx.x / CTAS, tstride = gridDim.x / CTAS;     // tiles are walked per CTA pair
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -405,18 +451,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 4 * EW); // one arrive per epilogue warp
+      mbar_init(&tmem_empty[s], 4 * EW * CTAS); // one arrive per epilogue warp (of both CTAs of a pair)
     }
     for (int s = 0; s < 4 * EW; ++s) mbar_init(&in_bars[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"(TMEM_COLS));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    if (CTAS == 2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"(TMEM_COLS));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"(TMEM_COLS));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
+  if (CTAS == 2) cluster_sync_all();     // the peer's barriers must be initialised before anything signals them
+  else __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
 
@@ -425,9 +478,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
       uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const uint32_t full0 = CTAS == 2 ? mapa_u32(smem_u32(&full[0]), 0) : 0u;   // the leader's full barriers
+      for (int tile = tile0; tile < total_tiles; tile += tstride) {
         const int split = tile / tiles_mn, mn = tile % tiles_mn;
-        const int m0 = (mn / p.tiles_n) * BM, n0 = (mn % p.tiles_n) * BN;
+        const int m0 = (mn / p.tiles_n) * (BM * CTAS) + (int)rank * BM, n0 = (mn % p.tiles_n) * BN + (int)rank * BNL;
         const int kb0 = split * p.kb_per_split;
         int nkb = total_kb - kb0;
         if (nkb > p.kb_per_split) nkb = p.kb_per_split;
@@ -435,37 +489,54 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(&empty[s], ph ^ 1);
-          mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
+          if (leader) mbar_expect_tx(&full[s], CTAS * (A_BYTES + B_BYTES));
           const int k0 = (kb0 + i) * BK;
           uint8_t* a = sA + s * A_BYTES;
           uint8_t* b = sB + s * B_BYTES;
-          if (A_MN) {
+          if (CTAS == 2) {
+            const uint32_t bar = full0 + (uint32_t)s * 8u;
+            if (A_MN) {
 #pragma unroll
-            for (int c = 0; c < BM / 64; ++c) tma_load_2d(a + c * 8192, &map_a, &full[s], m0 + c * 64, k0);
-          } else {
-            tma_load_2d(a, &map_a, &full[s], k0, m0);
-          }
-          if (B_MN) {
+              for (int c = 0; c < BM / 64; ++c) tma_load_2d_pair(a + c * 8192, &map_a, bar, m0 + c * 64, k0);
+            } else {
+              tma_load_2d_pair(a, &map_a, bar, k0, m0);
+            }
+            if (B_MN) {
 #pragma unroll
-            for (int c = 0; c < BN / 64; ++c) tma_load_2d(b + c * 8192, &map_b, &full[s], n0 + c * 64, k0);
+              for (int c = 0; c < BNL / 64; ++c) tma_load_2d_pair(b + c * 8192, &map_b, bar, n0 + c * 64, k0);
+            } else {
+              tma_load_2d_pair(b, &map_b, bar, k0, n0);
+            }
           } else {
-            tma_load_2d(b, &map_b, &full[s], k0, n0);
+            if (A_MN) {
+#pragma unroll
+              for (int c = 0; c < BM / 64; ++c) tma_load_2d(a + c * 8192, &map_a, &full[s], m0 + c * 64, k0);
+            } else {
+              tma_load_2d(a, &map_a, &full[s], k0, m0);
+            }
+            if (B_MN) {
+#pragma unroll
+              for (int c = 0; c < BN / 64; ++c) tma_load_2d(b + c * 8192, &map_b, &full[s], n0 + c * 64, k0);
+            } else {
+              tma_load_2d(b, &map_b, &full[s], k0, n0);
+            }
           }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (lane == 0 && leader) {
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) |
-                                 ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+                                 ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) |
+                                 ((uint32_t)((BM * CTAS) >> 4) << 24);
       uint32_t it = 0, lt = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      for (int tile = tile0; tile < total_tiles; tile += tstride, ++lt) {
         const int split = tile / tiles_mn;
         const int kb0 = split * p.kb_per_split;
         int nkb = total_kb - kb0;
         if (nkb > p.kb_per_split) nkb = p.kb_per_split;
         const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
-        mbar_wait(&tmem_empty[as], aph ^ 1);          // epilogue has drained this accumulator
+        mbar_wait(&tmem_empty[as], aph ^ 1);          // epilogue (of both CTAs) has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t tacc = tmem_base + as * BN;
         for (int i = 0; i < nkb; ++i, ++it) {
@@ -478,11 +549,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t da = A_MN ? make_desc(a + k * 2048, 8192, 1024) : make_desc(a + k * 32, 0, 1024);
             const uint64_t db = B_MN ? make_desc(b + k * 2048, 8192, 1024) : make_desc(b + k * 32, 0, 1024);
-            umma_bf16(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            if (CTAS == 2) umma_bf16_pair(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            else umma_bf16(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty[s]);
+          if (CTAS == 2) umma_commit_pair(&empty[s]);
+          else umma_commit(&empty[s]);
         }
-        umma_commit(&tmem_full[as]);
+        if (CTAS == 2) umma_commit_pair(&tmem_full[as]);
+        else umma_commit(&tmem_full[as]);
       }
     }
   } else {
@@ -514,7 +588,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     // bulk-load the operand box of `tile` into the buffer its result will be staged in
     auto prefetch_in = [&](int tile) {
       const int mn = tile % tiles_mn;
-      const int m0 = (mn / p.tiles_n) * BM, n0 = (mn % p.tiles_n) * BN + cg * CW;
+      const int m0 = (mn / p.tiles_n) * (BM * CTAS) + (int)rank * BM, n0 = (mn % p.tiles_n) * BN + cg * CW;
       if (n0 >= p.N) return;
       if (lane == 0) {
         // the bulk store that last read this buffer must have finished reading it
@@ -524,11 +598,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         tma_load_2d(my_stage + (nstore % NBUF) * 4096, &map_in, in_bar, n0, m0 + q * 32);
       }
     };
-    if (tin && (int)blockIdx.x < total_tiles) prefetch_in(blockIdx.x);
+    if (tin && tile0 < total_tiles) prefetch_in(tile0);
+    const uint32_t tmem_empty0 = CTAS == 2 ? mapa_u32(smem_u32(&tmem_empty[0]), 0) : 0u;   // the leader's
     uint32_t lt = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+    for (int tile = tile0; tile < total_tiles; tile += tstride, ++lt) {
       const int mn = tile % tiles_mn;
-      const int m0 = (mn / p.tiles_n) * BM, n0 = (mn % p.tiles_n) * BN + cg * CW;
+      const int m0 = (mn / p.tiles_n) * (BM * CTAS) + (int)rank * BM, n0 = (mn % p.tiles_n) * BN + cg * CW;
       const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
       const int row = m0 + q * 32 + lane;
       const bool row_ok = row < p.M;
@@ -626,18 +701,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
-      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[as])) : "memory");
-      if (tin && tile + (int)gridDim.x < total_tiles) prefetch_in(tile + gridDim.x);
+      if (lane == 0) {
+        if (CTAS == 2) mbar_arrive_cluster(tmem_empty0 + as * 8u);
+        else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[as])) : "memory");
+      }
+      if (tin && tile + tstride < total_tiles) prefetch_in(tile + tstride);
     }
     // the staging buffers must outlive the bulk stores' READS only; global visibility of the writes is
     // given by grid completion
     if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
+  if (CTAS == 2) cluster_sync_all();     // the leader's MMAs read the peer's shared memory and write its TMEM
+  else __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
+    if (CTAS == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
   }
 }
 
@@ -712,15 +792,16 @@ int num_sms() {
   return n;
 }
 
-template <int BN, int STAGES, int EW, bool A_MN, bool B_MN>
+template <int BN, int STAGES, int EW, bool A_MN, bool B_MN, int CTAS>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx,
            const CUtensorMap& mi, GemmParams p, cudaStream_t st) {
   // operand ring + epilogue staging (4*EW warps x NBUF x 4 KB) + barriers + 1 KB alignment slack
   constexpr int NBUF = EW <= 2 ? 2 : 1;
-  constexpr int SMEM = STAGES * (BM * BK * 2 + BN * BK * 2) + 4 * EW * NBUF * 4096 + (2 * STAGES + 4 + 4 * EW) * 8 + 16 + 1024;
+  constexpr int SMEM = STAGES * (BM * BK * 2 + (BN / CTAS) * BK * 2) + 4 * EW * NBUF * 4096 +
+                       (2 * STAGES + 4 + 4 * EW) * 8 + 16 + 1024;
   static_assert(SMEM <= 227 * 1024, "shared memory budget");
   static bool configured = false;
-  auto kern = gemm_kernel<BN, STAGES, EW, A_MN, B_MN>;
+  auto kern = gemm_kernel<BN, STAGES, EW, A_MN, B_MN, CTAS>;
   if (!configured) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess) {
       k3m_set_error("gemm: cannot set dynamic shared memory to %d", SMEM);
@@ -728,22 +809,44 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
     }
     configured = true;
   }
-  p.tiles_m = (p.M + BM - 1) / BM;
+  p.tiles_m = (p.M + BM * CTAS - 1) / (BM * CTAS);
   p.tiles_n = (p.N + BN - 1) / BN;
   const int total = p.tiles_m * p.tiles_n * p.splits;
-  const int grid = total < num_sms() ? total : num_sms();
-  kern<<<grid, 64 + 128 * EW, SMEM, st>>>(ma, mb, mc, mx, mi, p);
+  const int slots = num_sms() / CTAS;                 // CTAs (or CTA pairs) resident at once
+  const int grid = (total < slots ? total : slots) * CTAS;
+  if (CTAS == 1) {
+    kern<<<grid, 64 + 128 * EW, SMEM, st>>>(ma, mb, mc, mx, mi, p);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(64 + 128 * EW);
+    cfg.dynamicSmemBytes = SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CTAS;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, mx, mi, p) != cudaSuccess) {
+      k3m_set_error("gemm: cluster launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+      return K3M_ERR_CUDA;
+    }
+  }
   return k3m_check_launch("k3m_gemm_bf16");
 }
 
-// (tile width, epilogue column groups) variants: 256/4 (16 epilogue warps), 128/4, 128/2, 64/1
+// (tile width, epilogue column groups) variants: 256/4 (16 epilogue warps), 128/4, 128/2, 64/1; `ctas` = 2
+// selects the CTA-pair kernel (256 x 256 tile per pair, 5-stage ring of 32 KB stages)
 template <bool A_MN, bool B_MN>
-int dispatch(int bn, int ew, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx,
-             const CUtensorMap& mi, const GemmParams& p, cudaStream_t st) {
-  if (bn == 64) return launch<64, 6, 1, A_MN, B_MN>(ma, mb, mc, mx, mi, p, st);
-  if (bn == 256) return launch<256, 3, 4, A_MN, B_MN>(ma, mb, mc, mx, mi, p, st);
-  if (ew == 4) return launch<128, 5, 4, A_MN, B_MN>(ma, mb, mc, mx, mi, p, st);
-  return launch<128, 5, 2, A_MN, B_MN>(ma, mb, mc, mx, mi, p, st);
+int dispatch(int bn, int ew, int ctas, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
+             const CUtensorMap& mx, const CUtensorMap& mi, const GemmParams& p, cudaStream_t st) {
+  if (bn == 64) return launch<64, 6, 1, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
+  if (bn == 256 && ctas == 2) return launch<256, 5, 4, A_MN, B_MN, 2>(ma, mb, mc, mx, mi, p, st);
+  if (bn == 256) return launch<256, 3, 4, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
+  if (ew == 4) return launch<128, 5, 4, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
+  return launch<128, 5, 2, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
 }
 
 // tile width: 128 x 256 (85 flop per operand byte from L2) once it still gives every SM a tile, else
@@ -771,18 +874,32 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   K3M_REQUIRE(!(act == ACT_DGELU || act == ACT_DTANH) || aux_in, "gemm: activation-derivative epilogue needs aux_in");
   const bool a_mn = layout == 2, b_mn = layout != 0;
   static const int force_bn = getenv("K3M_GEMM_BN") ? atoi(getenv("K3M_GEMM_BN")) : 0;
-  const int bn = pick_bn(M, N, K, force_bn);
+  int bn = pick_bn(M, N, K, force_bn);
+  const int total_kb = (K + BK - 1) / BK;
+  // CTA pairs (cta_group::2, 256 x 256 tile per pair): each CTA streams 32 KB per k-block instead of
+  // 48 KB for the same MMA work, so the 5-stage ring covers ~1.3 us of load latency instead of ~0.8 us —
+  // these K <= 3072 GEMMs are bound by bytes in flight, not by the tensor pipe.  Used when the problem
+  // still fills the 74 pairs.
+  static const int mode_2cta = getenv("K3M_GEMM_2CTA") ? atoi(getenv("K3M_GEMM_2CTA")) : 1;
+  int ctas = 1;
+  if (mode_2cta && N >= 256 && M >= 256 && force_bn == 0) {
+    const long pt = (long)((M + 255) / 256) * ((N + 255) / 256);
+    const long pairs = num_sms() / 2;
+    if (mode_2cta == 2 || (accumulate ? (pt * 4 >= pairs && total_kb >= 32) : (pt * 5 >= pairs * 3))) {
+      ctas = 2;
+      bn = 256;
+    }
+  }
   CUtensorMap ma, mb;
   // A: K-major -> tensor [M, K]; MN-major -> tensor [K, M]
   if (!(a_mn ? get_map(a, M, K, lda, 64, 64, &ma) : get_map(a, K, M, lda, 64, BM, &ma))) return K3M_ERR_CUDA;
-  if (!(b_mn ? get_map(b, N, K, ldb, 64, 64, &mb) : get_map(b, K, N, ldb, 64, bn, &mb))) return K3M_ERR_CUDA;
+  if (!(b_mn ? get_map(b, N, K, ldb, 64, 64, &mb) : get_map(b, K, N, ldb, 64, bn / ctas, &mb))) return K3M_ERR_CUDA;
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
-  const int total_kb = (K + BK - 1) / BK;
   int splits = 1;
   if (accumulate) {
-    const int tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
-    const int resident = num_sms();
+    const int tiles = ((M + BM * ctas - 1) / (BM * ctas)) * ((N + bn - 1) / bn);
+    const int resident = num_sms() / ctas;
     while (tiles * splits * 2 <= resident && total_kb / (splits * 2) >= 4) splits *= 2;
   }
   p.kb_per_split = (total_kb + splits - 1) / splits;
@@ -847,7 +964,7 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
       p.fast = F_DGELU;
     }
   }
-  if (layout == 0) return dispatch<false, false>(bn, ew, ma, mb, mc, mx, mi, p, st);
-  if (layout == 1) return dispatch<false, true>(bn, ew, ma, mb, mc, mx, mi, p, st);
-  return dispatch<true, true>(bn, ew, ma, mb, mc, mx, mi, p, st);
+  if (layout == 0) return dispatch<false, false>(bn, ew, ctas, ma, mb, mc, mx, mi, p, st);
+  if (layout == 1) return dispatch<false, true>(bn, ew, ctas, ma, mb, mc, mx, mi, p, st);
+  return dispatch<true, true>(bn, ew, ctas, ma, mb, mc, mx, mi, p, st);
 }
