@@ -245,10 +245,25 @@ def run_gpu_arm(args):
     ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
     note("end-to-end loop done: %.3f ms/step" % ms_e2e)
     clk = clocks.stop() if clocks is not None else None
+    def finish():
+        """Leave cleanly at N > 1: the captured graph holds NCCL kernels, and tearing the communicator down
+        under it has been seen to block forever (N = 2, exit only by the launcher's timeout).  Release the
+        graph first, and never let teardown outlive the result: a watchdog ends the process with status 0."""
+        sys.stdout.flush()
+        sys.stderr.flush()
+        if world == 1:
+            return
+        t = threading.Timer(20.0, lambda: os._exit(0))
+        t.daemon = True
+        t.start()
+        step.graph = None
+        torch.cuda.synchronize()
+        dist.barrier()
+        dist.destroy_process_group()
+        t.cancel()
+
     if rank != 0:
-        if world > 1:
-            dist.barrier()
-            dist.destroy_process_group()
+        finish()
         return 0
     peaks = load_peaks()
     kb = kernel_breakdown(step, host[0])
@@ -294,9 +309,7 @@ def run_gpu_arm(args):
                                 "sample": "2 steps of batch %d (BASELINE configs[0]) after 1 warm-up: oracle port "
                                           "(fp32 autograd restatement + torch.optim.AdamW), %.1f s/step" % (batch, sec)}
     print(json.dumps(line))
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    finish()
     return 0
 
 

@@ -69,17 +69,29 @@ __global__ void __launch_bounds__(128) ln_fwd_kernel(const bf16* __restrict__ x,
 }
 
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void unpack8(const uint4& u, float v[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __bfloat1622float2(h[i]);
+    v[2 * i] = f.x; v[2 * i + 1] = f.y;
+  }
+}
+
 // LayerNorm backward.  dy is optionally masked first by the post-LN dropout (drop_out).
 // dx -> bf16; if drop_in is set a second output dxm = dx * mask_in * scale is written (gradient of
 // the GEMM output that was dropped out before the residual add).  Column sums: dgamma += dy*xhat,
 // dbeta += dy, dbias += dxm  (fp32 atomics, one set per CTA after a grid-stride loop over rows).
 template <int NV>
-__global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
-                                                     const bf16* __restrict__ gamma, const float* __restrict__ mean_in,
-                                                     const float* __restrict__ rstd_in, bf16* __restrict__ dx,
-                                                     bf16* __restrict__ dxm, float* __restrict__ dgamma,
-                                                     float* __restrict__ dbeta, float* __restrict__ dbias, int M, int H,
-                                                     DropSpec drop_out, DropSpec drop_in) {
+__global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+                                                        const bf16* __restrict__ gamma, const float* __restrict__ mean_in,
+                                                        const float* __restrict__ rstd_in, bf16* __restrict__ dx,
+                                                        bf16* __restrict__ dxm, float* __restrict__ dgamma,
+                                                        float* __restrict__ dbeta, float* __restrict__ dbias, int M, int H,
+                                                        DropSpec drop_out, DropSpec drop_in) {
+  // Register budget: two CTAs (16 warps) per SM keep enough rows in flight to cover HBM latency; the
+  // row's dy / x stay packed as loaded (bf16) between the two passes and gamma is re-read (L1) per row,
+  // so the live state is the 3 x NV x 8 fp32 column-sum accumulators.
   extern __shared__ float sred[];  // [8 warps][3][H]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float ag[NV][8], ab[NV][8], ac[NV][8];
@@ -87,23 +99,26 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ dy
   for (int i = 0; i < NV; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) ag[i][j] = ab[i][j] = ac[i][j] = 0.f;
-  float gm[NV][8];
-#pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int c = (lane + 32 * i) * 8;
-    if (c < H) ld8(gamma + c, gm[i]);
-  }
   for (int row = blockIdx.x * 8 + warp; row < M; row += gridDim.x * 8) {
     const float mean = mean_in[row], rstd = rstd_in[row];
-    float g[NV][8], xh[NV][8];
+    uint4 pd[NV], px[NV];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = (lane + 32 * i) * 8;
       if (c < H) {
-        float d[8], xv[8];
-        ld8(dy + (size_t)row * H + c, d);
-        ld8(x + (size_t)row * H + c, xv);
+        pd[i] = *reinterpret_cast<const uint4*>(dy + (size_t)row * H + c);
+        px[i] = *reinterpret_cast<const uint4*>(x + (size_t)row * H + c);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (lane + 32 * i) * 8;
+      if (c < H) {
+        float d[8], xv[8], gm[8];
+        unpack8(pd[i], d);
+        unpack8(px[i], xv);
+        ld8(gamma + c, gm);
         if (drop_out.thresh) {
           uint32_t w[4];
           rng_words(drop_out.rng, drop_out.site, ((unsigned long long)row * H + c) >> 3, w);
@@ -112,12 +127,12 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ dy
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          xh[i][j] = (xv[j] - mean) * rstd;
-          ag[i][j] += d[j] * xh[i][j];
+          const float xh = (xv[j] - mean) * rstd;
+          const float g = d[j] * gm[j];
+          ag[i][j] += d[j] * xh;
           ab[i][j] += d[j];
-          g[i][j] = d[j] * gm[i][j];
-          s1 += g[i][j];
-          s2 += g[i][j] * xh[i][j];
+          s1 += g;
+          s2 += g * xh;
         }
       }
     }
@@ -127,9 +142,18 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ dy
     for (int i = 0; i < NV; ++i) {
       const int c = (lane + 32 * i) * 8;
       if (c < H) {
-        float o[8];
+        float d[8], xv[8], gm[8], o[8];
+        unpack8(pd[i], d);
+        unpack8(px[i], xv);
+        ld8(gamma + c, gm);
+        if (drop_out.thresh) {
+          uint32_t w[4];
+          rng_words(drop_out.rng, drop_out.site, ((unsigned long long)row * H + c) >> 3, w);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = (g[i][j] - s1 - xh[i][j] * s2) * rstd;
+          for (int j = 0; j < 8; ++j) d[j] *= drop_mult(drop_out, w, j);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (d[j] * gm[j] - s1 - (xv[j] - mean) * rstd * s2) * rstd;
         st8(dx + (size_t)row * H + c, o);
         if (drop_in.thresh) {
           uint32_t w[4];
@@ -172,6 +196,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ dy
 
 // ---------------------------------------------------------------------------------------------
 // out[n] += sum_m x[m, n]   (x bf16 or fp32, row stride ld)
+// generic: one column per lane (any ld / alignment)
 template <typename T>
 __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, int ld, float* __restrict__ out, int M, int N,
                                                      int rows_per_cta) {
@@ -191,6 +216,49 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, in
 #pragma unroll
     for (int w = 0; w < 8; ++w) t += sred[w][lane];
     atomicAdd(out + col, t);
+  }
+}
+
+// bf16, 16-byte aligned rows: a warp reads 512 contiguous bytes of a row per instruction (8 columns per
+// lane), four rows in flight per warp; 256 columns per CTA, rows split over blockIdx.y
+__global__ void __launch_bounds__(256) colsum8_kernel(const bf16* __restrict__ x, int ld, float* __restrict__ out, int M,
+                                                      int N, int rows_per_cta) {
+  __shared__ float sred[8][256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int col = blockIdx.x * 256 + lane * 8;
+  const int r0 = blockIdx.y * rows_per_cta;
+  int r1 = r0 + rows_per_cta;
+  if (r1 > M) r1 = M;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (col < N) {
+    int r = r0 + warp;
+    for (; r + 24 < r1; r += 32) {
+      float v[4][8];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) ld8(x + (size_t)(r + 8 * u) * ld + col, v[u]);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += v[u][j];
+    }
+    for (; r < r1; r += 8) {
+      float v[8];
+      ld8(x + (size_t)r * ld + col, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sred[warp][lane * 8 + j] = acc[j];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += sred[w][threadIdx.x];
+    atomicAdd(out + c, t);
   }
 }
 
@@ -303,7 +371,7 @@ extern "C" int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, cons
   DropSpec dout = make_drop(rng, site_out, p_out), din = make_drop(rng, site_in, p_in);
   K3M_REQUIRE(!din.thresh || dxm, "ln_bwd: drop_in needs the dxm output");
   int grid = (M + 7) / 8;
-  if (grid > 148 * 2) grid = 148 * 2;
+  if (grid > 148 * 2) grid = 148 * 2;            // two resident CTAs per SM
   const size_t smem = (size_t)8 * 3 * H * sizeof(float);
   const int nv = (H + 255) / 256;
 #define LN_BWD(NV)                                                                                                   \
@@ -318,6 +386,7 @@ extern "C" int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, cons
   } while (0)
   if (nv <= 1) LN_BWD(1);
   else if (nv <= 2) LN_BWD(2);
+  else if (nv <= 3) LN_BWD(3);
   else LN_BWD(4);
 #undef LN_BWD
   return k3m_check_launch("k3m_ln_bwd");
@@ -326,6 +395,15 @@ extern "C" int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, cons
 extern "C" int k3m_colsum(const void* x, int ld, int x_f32, float* out, int M, int N, void* stream) {
   K3M_REQUIRE(M > 0 && N > 0, "colsum: empty");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!x_f32 && N % 8 == 0 && ld % 8 == 0 && (((uintptr_t)x) & 15) == 0) {
+    const int gx = (N + 255) / 256;
+    int gy = (148 * 4 + gx - 1) / gx;             // ~4 CTAs per SM
+    if (gy > (M + 63) / 64) gy = (M + 63) / 64;   // at least 64 rows per CTA
+    if (gy < 1) gy = 1;
+    const int rows_per = (M + gy - 1) / gy;
+    colsum8_kernel<<<dim3(gx, gy), 256, 0, st>>>((const bf16*)x, ld, out, M, N, rows_per);
+    return k3m_check_launch("k3m_colsum");
+  }
   int gy = (M + 255) / 256;
   if (gy > 64) gy = 64;
   const int rows_per = (M + gy - 1) / gy;

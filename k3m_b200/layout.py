@@ -57,20 +57,10 @@ def _connection(spec, p, h1, i1, h2, i2, bi):
     _ln(spec, p + ".t_output.LayerNorm", h2)
 
 
-def param_spec(cfg):
-    """OrderedDict name -> shape, in the reference's `named_parameters()` order."""
-    if not (cfg.use_image and cfg.with_coattention):
-        raise ValueError("k3m_b200 implements the tri-modal path (use_image and with_coattention)")
-    if cfg.task_specific_tokens or cfg.dynamic_attention:
-        raise ValueError("task_specific_tokens / dynamic_attention are off on the K3M path")
+def _encoder(s, cfg):
     H, Hv, Hb = cfg.hidden_size, cfg.v_hidden_size, cfg.bi_hidden_size
     I, Iv = cfg.intermediate_size, cfg.v_intermediate_size
     nc = len(cfg.v_biattention_id)
-    s = OrderedDict()
-    s["embeddings.word_embeddings.weight"] = (cfg.vocab_size, H)
-    s["embeddings.position_embeddings.weight"] = (cfg.max_position_embeddings, H)
-    s["embeddings.token_type_embeddings.weight"] = (cfg.type_vocab_size, H)
-    _ln(s, "embeddings.LayerNorm", H)
     for i in range(cfg.num_hidden_layers):
         _bert_layer(s, "encoder.layer.%d" % i, H, I)
     for i in range(cfg.v_num_hidden_layers):
@@ -81,18 +71,10 @@ def param_spec(cfg):
         _connection(s, "encoder.c_layer_pv_v.%d" % i, Hv, Iv, H, I, Hb)
     for i in range(nc):
         _connection(s, "encoder.c_layer_pv_t.%d" % i, H, I, H, I, H)
-    _linear(s, "t_pooler.dense", Hb, H)
-    _linear(s, "v_embeddings.image_embeddings", Hv, cfg.v_feature_size)
-    _linear(s, "v_embeddings.image_location_embeddings", Hv, 5)
-    _ln(s, "v_embeddings.LayerNorm", Hv)
-    _linear(s, "v_pooler.dense", Hb, Hv)
-    s["cls.predictions.bias"] = (cfg.vocab_size,)
-    _linear(s, "cls.predictions.transform.dense", H, H)
-    _ln(s, "cls.predictions.transform.LayerNorm", H)
-    _linear(s, "cls.seq_relationship", 2, H)
-    _linear(s, "cls.imagePredictions.transform.dense", Hv, Hv)
-    _ln(s, "cls.imagePredictions.transform.LayerNorm", Hv)
-    _linear(s, "cls.imagePredictions.decoder", cfg.v_target_size, Hv)
+
+
+def _fusion_and_aggregator_head(s, cfg):
+    H, Hb = cfg.hidden_size, cfg.bi_hidden_size
     _linear(s, "map_individual_to_bi", Hb, H)
     _linear(s, "map_bi_to_individual", H, Hb)
     for n in ("score_self_v", "score_cross1_v", "score_cross2_v", "soft_v"):
@@ -100,6 +82,51 @@ def param_spec(cfg):
     for m in ("t", "pv"):
         for n in ("score_self_", "score_cross1_", "score_cross2_", "soft_"):
             _linear(s, n + m, H, H * 3)
+
+
+def param_spec(cfg, kind="pretrain"):
+    """OrderedDict name -> shape, in the reference's `named_parameters()` order.
+    kind "pretrain": `BertForMultiModalPreTraining_tri_stru` (`vilbert_k3m.py:2190-2264`);
+    kind "alignment": `K3MForItemAlignment` (`:2866-2943`; registration order checked against the
+    unmodified reference by `tools/make_golden.py`)."""
+    if not (cfg.use_image and cfg.with_coattention):
+        raise ValueError("k3m_b200 implements the tri-modal path (use_image and with_coattention)")
+    if cfg.task_specific_tokens or cfg.dynamic_attention:
+        raise ValueError("task_specific_tokens / dynamic_attention are off on the K3M path")
+    H, Hv, Hb = cfg.hidden_size, cfg.v_hidden_size, cfg.bi_hidden_size
+    s = OrderedDict()
+    s["embeddings.word_embeddings.weight"] = (cfg.vocab_size, H)
+    s["embeddings.position_embeddings.weight"] = (cfg.max_position_embeddings, H)
+    s["embeddings.token_type_embeddings.weight"] = (cfg.type_vocab_size, H)
+    _ln(s, "embeddings.LayerNorm", H)
+    if kind == "alignment":
+        _linear(s, "v_embeddings.image_embeddings", Hv, cfg.v_feature_size)
+        _linear(s, "v_embeddings.image_location_embeddings", Hv, 5)
+        _ln(s, "v_embeddings.LayerNorm", Hv)
+        _linear(s, "v_pooler.dense", Hb, Hv)
+        _encoder(s, cfg)
+        _linear(s, "t_pooler.dense", Hb, H)
+        _fusion_and_aggregator_head(s, cfg)
+        if getattr(cfg, "loss_type", "ce") == "ce":
+            _linear(s, "classifier.dense", H, H * 2)          # ClassificationHead `:2164-2183`
+            _linear(s, "classifier.out_proj", 2, H)
+    elif kind == "pretrain":
+        _encoder(s, cfg)
+        _linear(s, "t_pooler.dense", Hb, H)
+        _linear(s, "v_embeddings.image_embeddings", Hv, cfg.v_feature_size)
+        _linear(s, "v_embeddings.image_location_embeddings", Hv, 5)
+        _ln(s, "v_embeddings.LayerNorm", Hv)
+        _linear(s, "v_pooler.dense", Hb, Hv)
+        s["cls.predictions.bias"] = (cfg.vocab_size,)
+        _linear(s, "cls.predictions.transform.dense", H, H)
+        _ln(s, "cls.predictions.transform.LayerNorm", H)
+        _linear(s, "cls.seq_relationship", 2, H)
+        _linear(s, "cls.imagePredictions.transform.dense", Hv, Hv)
+        _ln(s, "cls.imagePredictions.transform.LayerNorm", Hv)
+        _linear(s, "cls.imagePredictions.decoder", cfg.v_target_size, Hv)
+        _fusion_and_aggregator_head(s, cfg)
+    else:
+        raise ValueError("kind must be 'pretrain' or 'alignment'")
     _linear(s, "struc_w1", H, H * 3)
     _linear(s, "struc_w2", 1, H)
     _linear(s, "struc_w3", H, H)
@@ -201,8 +228,9 @@ class ArenaLayout(object):
 
     ALIGN = 64
 
-    def __init__(self, cfg):
-        self.spec = param_spec(cfg)
+    def __init__(self, cfg, kind="pretrain"):
+        self.kind = kind
+        self.spec = param_spec(cfg, kind)
         self.offsets = OrderedDict()
         self.fused = OrderedDict()      # fused name -> (offset, shape)
         names = list(self.spec.keys())
