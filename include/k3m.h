@@ -135,6 +135,17 @@ int k3m_itm_loss(const float* pool_t, const float* pool_pv, const float* pool_v,
                  const long long* l1, const long long* l2, const long long* l3, int B, int H, const void* rng,
                  unsigned int site, float drop_p, float* loss, void* stream);
 
+/* item-alignment head, "ce" branch of K3MForItemAlignment.forward (vilbert_k3m.py:3443-3450): logits fp32
+ * [B, 2] -> probs = softmax [B, 2], loss = mean cross-entropy, dlogits (bf16, row stride ldd) =
+ * grad_scale * (probs - onehot) / B.  probs / dlogits may be NULL.                                  */
+int k3m_pair_cls_loss(const float* logits, int ld, const long long* labels, int B, float grad_scale,
+                      float* loss, float* probs, void* dlogits, int ldd, void* stream);
+/* nn.Dropout outside a GEMM epilogue (ClassificationHead.forward, vilbert_k3m.py:2176-2180): y = x *
+ * keep * 1/(1-p); element (r, c) uses counter r * round_up(cols, 8) + c of `site`, so a GEMM epilogue
+ * with the same site and N = cols regenerates the mask in backward.                                 */
+int k3m_dropout(const void* x, int ldx, int x_f32, void* y, int ldy, int y_f32, int rows, int cols,
+                const void* rng, unsigned int site, float drop_p, void* stream);
+
 /* torch.optim.AdamW step (pretrain.py:919-924) over a flat range; hyper = device fp32[8]
  * {lr, beta1, beta2, eps, weight_decay, step, grad_scale, -}.                                     */
 int k3m_adamw(float* p32, float* g32, float* m, float* v, void* p16, const float* hyper, long long n,

@@ -120,6 +120,51 @@ __global__ void __launch_bounds__(128) itm_kernel(const float* pt, const float* 
   }
 }
 
+// ---- item-alignment head (K3MForItemAlignment.forward "ce" branch, vilbert_k3m.py:3443-3450) ----------
+// logits fp32 [B, 2] (row stride ld) -> probs = softmax(logits) [B, 2]; loss = mean CE(logits, labels);
+// dlogits (bf16, row stride ldd, columns 0..1) = grad_scale * (probs - onehot) / B
+__global__ void __launch_bounds__(128) pair_cls_kernel(const float* __restrict__ logits, int ld,
+                                                       const long long* __restrict__ labels, int B, float grad_scale,
+                                                       float* __restrict__ loss, float* __restrict__ probs,
+                                                       bf16* __restrict__ dlogits, int ldd) {
+  __shared__ float red[32];
+  float acc = 0.f;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    const float a0 = logits[(size_t)b * ld], a1 = logits[(size_t)b * ld + 1];
+    const float mx = fmaxf(a0, a1);
+    const float e0 = __expf(a0 - mx), e1 = __expf(a1 - mx);
+    const float inv = 1.0f / (e0 + e1);
+    const float p0 = e0 * inv, p1 = e1 * inv;
+    const int lab = labels[b] != 0 ? 1 : 0;
+    acc += (mx + __logf(e0 + e1)) - (lab ? a1 : a0);
+    if (probs) {
+      probs[(size_t)b * 2] = p0;
+      probs[(size_t)b * 2 + 1] = p1;
+    }
+    if (dlogits) {
+      const float s = grad_scale / (float)B;
+      dlogits[(size_t)b * ldd] = __float2bfloat16(s * (p0 - (lab ? 0.f : 1.f)));
+      dlogits[(size_t)b * ldd + 1] = __float2bfloat16(s * (p1 - (lab ? 1.f : 0.f)));
+    }
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) *loss = acc / (float)B;
+}
+
+// y = x * keep-mask * 1/(1-p): nn.Dropout applied outside a GEMM epilogue (ClassificationHead, :2176-2180);
+// the same (site, element index) regenerates the mask for the backward pass
+template <typename TX, typename TY>
+__global__ void dropout_kernel(const TX* __restrict__ x, int ldx, TY* __restrict__ y, int ldy, int rows, int cols,
+                               int ld_drop, DropSpec drop) {
+  const size_t n = (size_t)rows * cols;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols), c = (int)(i % cols);
+    float v = ld_f(x + (size_t)r * ldx + c);
+    if (drop.thresh) v *= drop_mult_at(drop, (unsigned long long)r * ld_drop + c);
+    st_f(y + (size_t)r * ldy + c, v);
+  }
+}
+
 // ---- structure aggregator (structure_aggregator, vilbert_k3m.py:2437-2467) ---------------------------
 // X[p] = [c_init[item] | mean(seq[r0], seq[r1]) | mean(seq[r2], seq[r3])]  (bf16 for the W1 GEMM);
 // PV[p] = the two means in fp32 for the LPM norms.
@@ -352,6 +397,32 @@ extern "C" int k3m_itm_loss(const float* pool_t, const float* pool_pv, const flo
   d.scale = 1.0f / (1.0f - drop_p);
   itm_kernel<<<B, 128, 0, ST(stream)>>>(pool_t, pool_pv, pool_v, (const bf16*)w, (const bf16*)b, l1, l2, l3, B, H, d, loss);
   return k3m_check_launch("k3m_itm_loss");
+}
+
+extern "C" int k3m_pair_cls_loss(const float* logits, int ld, const long long* labels, int B, float grad_scale,
+                                 float* loss, float* probs, void* dlogits, int ldd, void* stream) {
+  K3M_REQUIRE(B > 0 && ld >= 2, "pair_cls_loss: bad shape");
+  pair_cls_kernel<<<1, 128, 0, ST(stream)>>>(logits, ld, labels, B, grad_scale, loss, probs, (bf16*)dlogits, ldd);
+  return k3m_check_launch("k3m_pair_cls_loss");
+}
+
+extern "C" int k3m_dropout(const void* x, int ldx, int x_f32, void* y, int ldy, int y_f32, int rows, int cols,
+                           const void* rng, unsigned int site, float drop_p, void* stream) {
+  K3M_REQUIRE(rows > 0 && cols > 0, "dropout: empty");
+  DropSpec d;
+  d.rng = reinterpret_cast<const unsigned long long*>(rng);
+  d.site = site;
+  d.thresh = (rng && drop_p > 0.f) ? (unsigned int)(drop_p * 65536.0f + 0.5f) : 0u;
+  d.scale = 1.0f / (1.0f - drop_p);
+  const int ld_drop = (cols + 7) / 8 * 8;
+  size_t n = (size_t)rows * cols;
+  int g = (int)((n + 255) / 256);
+  if (g > 148 * 8) g = 148 * 8;
+  if (x_f32 && y_f32) dropout_kernel<float, float><<<g, 256, 0, ST(stream)>>>((const float*)x, ldx, (float*)y, ldy, rows, cols, ld_drop, d);
+  else if (x_f32) dropout_kernel<float, bf16><<<g, 256, 0, ST(stream)>>>((const float*)x, ldx, (bf16*)y, ldy, rows, cols, ld_drop, d);
+  else if (y_f32) dropout_kernel<bf16, float><<<g, 256, 0, ST(stream)>>>((const bf16*)x, ldx, (float*)y, ldy, rows, cols, ld_drop, d);
+  else dropout_kernel<bf16, bf16><<<g, 256, 0, ST(stream)>>>((const bf16*)x, ldx, (bf16*)y, ldy, rows, cols, ld_drop, d);
+  return k3m_check_launch("k3m_dropout");
 }
 
 extern "C" int k3m_pair_gather_fwd(const float* c_init, const void* seq, int lds, const int* pair_item, const int* pair_rows,

@@ -377,8 +377,9 @@ class Engine(object):
         self.dgrad(dpre, p + ".transform.dense.weight", addend=dx, out=dx)
 
     # ---- structure aggregator + LPM ----------------------------------------------------------
-    def struct_fwd(self, c_init, seq_pv, plan):
-        """`structure_aggregator` `:2413-2505` as batched kernels over the host-built plan."""
+    def struct_fwd(self, c_init, seq_pv, plan, lpm=True):
+        """`structure_aggregator` `:2413-2505` as batched kernels over the host-built plan
+        (`lpm=False`: the alignment model's aggregator, `:3105-3161`, which has no LPM loss)."""
         ops, f32 = self.ops, torch.float32
         B, H = c_init.shape
         X, PV = ops.pair_gather_fwd(c_init, seq_pv, plan["pair_item"], plan["pair_rows"])
@@ -389,8 +390,10 @@ class Engine(object):
                            addend=c_init, out_dtype=f32)
         dc_final = self.zeros(B, H, f32)
         dPV = self.zeros(PV.shape[0], 2 * H, f32)
-        loss = ops.lpm_fwd_bwd(c_final, PV, plan["terms"], float(self.cfg.margin), dc_final, dPV,
-                               n_valid=plan.get("n_terms"))
+        loss = None
+        if lpm:
+            loss = ops.lpm_fwd_bwd(c_final, PV, plan["terms"], float(self.cfg.margin), dc_final, dPV,
+                                   n_valid=plan.get("n_terms"))
         return c_final, loss, (plan, X, t, att, s_a, dc_final, dPV)
 
     def struct_bwd(self, saved, w_lpm, dc_init, dseq_pv):
@@ -422,6 +425,41 @@ class Engine(object):
         loss_weights: (mlm_t, mrm, mlm_pv, lpm) weights of the summed loss (`pretrain.py:1055`).
         Returns dict(loss_t, loss_v, loss_pv, loss_itm, loss_lpm (each fp32 [1]), c_initial,
         c_final)."""
+        c, ops, f32 = self.cfg, self.ops, torch.float32
+        tw = self.tower_fwd(batch, noise)
+        B, Lt, Lpv, Lv1, Mt, Mp, Mv = self.saved["dims"]
+        S, seqV, c_init = tw["S"], tw["seqV"], tw["c_init"]
+        pool_t, pool_pv, pool_v = tw["pools"]
+        c_final, loss_lpm, sv_s = self.struct_fwd(c_init, S[Mt:], plan)
+        loss_itm = ops.itm_loss(pool_t, pool_pv, pool_v, self.W("cls.seq_relationship.weight"),
+                                self.W("cls.seq_relationship.bias"), batch["next_sentence_label"],
+                                batch["next_sentence_label_pv_v"], batch["next_sentence_label_pv_t"],
+                                drop=self.site(0.1), rng=self.rng)
+        w_t, w_v, w_pv, w_lpm = [float(x) for x in loss_weights]
+        V, Tv = c.vocab_size, c.v_target_size
+        logits, sv_h = self.head_fwd("cls.predictions", S, "embeddings.word_embeddings.weight",
+                                     "cls.predictions.bias", self.adt, V)
+        lab_t, lab_pv = batch["masked_lm_labels"].reshape(-1), batch["masked_lm_labels_pv"].reshape(-1)
+        loss_t = ops.xent_fwd_bwd(logits[:Mt], lab_t, ops.count_valid(lab_t, -1), V,
+                                  dlogits=logits[:Mt], grad_scale=w_t)
+        loss_pv = ops.xent_fwd_bwd(logits[Mt:], lab_pv, ops.count_valid(lab_pv, -1), V,
+                                   dlogits=logits[Mt:], grad_scale=w_pv)
+        logits_v, sv_hv = self.head_fwd("cls.imagePredictions", seqV,
+                                        "cls.imagePredictions.decoder.weight",
+                                        "cls.imagePredictions.decoder.bias", f32, Tv)
+        dlv = self.zeros(Mv, logits_v.shape[1])
+        il = batch["image_label"].reshape(-1)
+        loss_v = ops.kl_fwd_bwd(logits_v, batch["image_target"].reshape(-1, Tv), il,
+                                ops.count_eq(il, 1), Tv, Lv1, dlogits=dlv, grad_scale=w_v)
+        self.saved.update(struct=sv_s, w_lpm=w_lpm, head=(logits, sv_h), head_v=(dlv, sv_hv))
+        return dict(loss_t=loss_t, loss_v=loss_v, loss_pv=loss_pv, loss_itm=loss_itm,
+                    loss_lpm=loss_lpm, c_initial=c_init, c_final=c_final)
+
+    def tower_fwd(self, batch, noise=None):
+        """Everything up to the initial item embedding (`bert_tri` `:2507-2671`, the three-pass
+        encoder, fusion `:2376-2411`, pooling, `c_initial`): shared by the pretraining model and the
+        item-alignment towers (`item_embedding`, `:3329-3377`).  Fills `self.saved` for
+        `tower_bwd`; returns dict(S [title | PV fused sequences], seqV, c_init, pools)."""
         c, ops, f32 = self.cfg, self.ops, torch.float32
         self.tape, self._site = [], 0
         noise = noise or {}
@@ -513,32 +551,9 @@ class Engine(object):
         pool_v = ops.gemm(pool_vr, self.W("map_bi_to_individual.weight"), "nt",
                           bias=self.W("map_bi_to_individual.bias"), out_dtype=f32)
         c_init = ops.lincomb3(pool_v, pool_t, pool_pv, 1.0 / 3, 1.0 / 3, 1.0 / 3, out_dtype=f32)
-        c_final, loss_lpm, sv_s = self.struct_fwd(c_init, S[Mt:], plan)
-        loss_itm = ops.itm_loss(pool_t, pool_pv, pool_v, self.W("cls.seq_relationship.weight"),
-                                self.W("cls.seq_relationship.bias"), batch["next_sentence_label"],
-                                batch["next_sentence_label_pv_v"], batch["next_sentence_label_pv_t"],
-                                drop=self.site(0.1), rng=self.rng)
-        w_t, w_v, w_pv, w_lpm = [float(x) for x in loss_weights]
-        V, Tv = c.vocab_size, c.v_target_size
-        logits, sv_h = self.head_fwd("cls.predictions", S, "embeddings.word_embeddings.weight",
-                                     "cls.predictions.bias", self.adt, V)
-        lab_t, lab_pv = batch["masked_lm_labels"].reshape(-1), batch["masked_lm_labels_pv"].reshape(-1)
-        loss_t = ops.xent_fwd_bwd(logits[:Mt], lab_t, ops.count_valid(lab_t, -1), V,
-                                  dlogits=logits[:Mt], grad_scale=w_t)
-        loss_pv = ops.xent_fwd_bwd(logits[Mt:], lab_pv, ops.count_valid(lab_pv, -1), V,
-                                   dlogits=logits[Mt:], grad_scale=w_pv)
-        logits_v, sv_hv = self.head_fwd("cls.imagePredictions", seqV,
-                                        "cls.imagePredictions.decoder.weight",
-                                        "cls.imagePredictions.decoder.bias", f32, Tv)
-        dlv = self.zeros(Mv, logits_v.shape[1])
-        il = batch["image_label"].reshape(-1)
-        loss_v = ops.kl_fwd_bwd(logits_v, batch["image_target"].reshape(-1, Tv), il,
-                                ops.count_eq(il, 1), Tv, Lv1, dlogits=dlv, grad_scale=w_v)
         self.saved = dict(dims=(B, Lt, Lpv, Lv1, Mt, Mp, Mv), stages=stages, emb=(sv_et, sv_epv, sv_ev),
-                          fuse=(sv_fv, sv_ft, sv_fp), struct=sv_s, w_lpm=w_lpm, pool_vr=pool_vr,
-                          head=(logits, sv_h), head_v=(dlv, sv_hv))
-        return dict(loss_t=loss_t, loss_v=loss_v, loss_pv=loss_pv, loss_itm=loss_itm,
-                    loss_lpm=loss_lpm, c_initial=c_init, c_final=c_final)
+                          fuse=(sv_fv, sv_ft, sv_fp), pool_vr=pool_vr)
+        return dict(S=S, seqV=seqV, c_init=c_init, pools=(pool_t, pool_pv, pool_v))
 
     def backward(self, grad_scales=None):
         """Gradient of w_t*loss_t + w_v*loss_v + w_pv*loss_pv + w_lpm*loss_lpm, accumulated into
@@ -558,15 +573,24 @@ class Engine(object):
             ops.scale_dev_(sv["struct"][5], g_lpm)      # dc_final
             ops.scale_dev_(sv["struct"][6], g_lpm)      # dPV
         H, Hv = c.hidden_size, c.v_hidden_size
-        T1, T3 = slice(0, Mt), slice(Mt, 2 * Mt)
-        P2, P3 = slice(2 * Mt, 2 * Mt + Mp), slice(2 * Mt + Mp, 2 * Mt + 2 * Mp)
-        V1, V2 = slice(0, Mv), slice(Mv, 2 * Mv)
         dS = self.zeros(Mt + Mp, H)
         dseqV = self.zeros(Mv, Hv)
         self.head_bwd(sv["head"][0], sv["head"][1], dS)
         self.head_bwd(sv["head_v"][0], sv["head_v"][1], dseqV)
         dc_init = self.zeros(B, H, f32)
         self.struct_bwd(sv["struct"], sv["w_lpm"], dc_init, dS[Mt:])
+        self.tower_bwd(dS, dseqV, dc_init)
+
+    def tower_bwd(self, dS, dseqV, dc_init):
+        """Backward of `tower_fwd`: dS [Mt + Mp, H] / dseqV [Mv, Hv] (act dtype) and dc_init [B, H] fp32
+        are the gradients of its outputs (consumed / modified in place)."""
+        c, ops, f32 = self.cfg, self.ops, torch.float32
+        sv = self.saved
+        B, Lt, Lpv, Lv1, Mt, Mp, Mv = sv["dims"]
+        H, Hv = c.hidden_size, c.v_hidden_size
+        T1, T3 = slice(0, Mt), slice(Mt, 2 * Mt)
+        P2, P3 = slice(2 * Mt, 2 * Mt + Mp), slice(2 * Mt + Mp, 2 * Mt + 2 * Mp)
+        V1, V2 = slice(0, Mv), slice(Mv, 2 * Mv)
         ops.scale_(dc_init, 1.0 / 3)                       # c_initial = (v + t + pv) / 3
         ops.mean_pool_bwd(dc_init, dS[:Mt], B, Lt)
         ops.mean_pool_bwd(dc_init, dS[Mt:], B, Lpv)
@@ -624,3 +648,60 @@ class Engine(object):
         self.image_embed_bwd(d_ev, sv_ev)
         self._join_aux()
         self.saved = None
+
+    # ---- item alignment (K3MForItemAlignment, `vilbert_k3m.py:2862-3454`) ----------------------
+    def forward_alignment(self, batch, plan, labels, noise=None):
+        """Both items of every pair run through ONE tower pass: `batch` holds item 1 of the B pairs
+        followed by item 2 (rows [0, B) and [B, 2B) of every tensor; the reference calls
+        `item_embedding` twice with the same weights, `:3408-3433`), `plan` is the aggregator plan
+        of the stacked 2B items, `labels` int64 [B].  "ce" head (`:3443-3450`, ClassificationHead
+        `:2164-2183`): logits = out_proj(dropout(tanh(dense(dropout(cat(c_final_1, c_final_2)))))).
+        Returns dict(loss [1], probs [B, 2], c_initial [2B, H], c_final [2B, H])."""
+        c, ops, f32 = self.cfg, self.ops, torch.float32
+        tw = self.tower_fwd(batch, noise)
+        B2, Lt, Lpv, Lv1, Mt, Mp, Mv = self.saved["dims"]
+        B, H = B2 // 2, c.hidden_size
+        c_final, _, sv_s = self.struct_fwd(tw["c_init"], tw["S"][Mt:], plan, lpm=False)
+        feat = self.empty(B, 2 * H)
+        ops.dropout(c_final[:B], None, self.rng, out=feat[:, :H])
+        ops.dropout(c_final[B:], None, self.rng, out=feat[:, H:])
+        s_in = self.site(c.hidden_dropout_prob)
+        feat_d = ops.dropout(feat, s_in, self.rng)
+        h = ops.gemm(feat_d, self.W("classifier.dense.weight"), "nt", bias=self.W("classifier.dense.bias"),
+                     act=ACT_TANH)
+        s_h = self.site(c.hidden_dropout_prob)
+        h_d = ops.dropout(h, s_h, self.rng)
+        logits = ops.gemm(h_d, self.W("classifier.out_proj.weight"), "nt",
+                          bias=self.W("classifier.out_proj.bias"), out_dtype=f32)
+        dlog = self.zeros(B, 8)                        # bf16, columns 0..1 used (K = 2 operand, 16 B rows)
+        loss, probs = ops.pair_cls_loss(logits, labels, dlogits=dlog)
+        self.saved.update(struct=sv_s, cls=(feat_d, h, h_d, dlog, s_in, s_h))
+        return dict(loss=loss, probs=probs, c_initial=tw["c_init"], c_final=c_final)
+
+    def backward_alignment(self, grad_scale=None):
+        """Gradient of the pair loss into the fp32 gradient arena; `grad_scale`: optional fp32 device
+        scalar (autograd's upstream gradient)."""
+        c, ops, f32 = self.cfg, self.ops, torch.float32
+        sv = self.saved
+        B2, Lt, Lpv, Lv1, Mt, Mp, Mv = sv["dims"]
+        B, H, Hv = B2 // 2, c.hidden_size, c.v_hidden_size
+        feat_d, h, h_d, dlog, s_in, s_h = sv["cls"]
+        if grad_scale is not None:
+            ops.scale_dev_(dlog, grad_scale)
+        dl = dlog[:, :2]
+        self.bgrad(dl, "classifier.out_proj.bias")
+        self.wgrad(dl, h_d, "classifier.out_proj.weight")
+        # dropout mask of h and tanh' in the dgrad epilogue: dz = (dl W_out) * keep/(1-p) * (1 - h^2)
+        dz = self.dgrad(dl, "classifier.out_proj.weight", act=ACT_DTANH, aux_in=h, drop=s_h)
+        self.bgrad(dz, "classifier.dense.bias")
+        self.wgrad(dz, feat_d, "classifier.dense.weight")
+        dfeat = self.dgrad(dz, "classifier.dense.weight", drop=s_in)
+        dc_final = sv["struct"][5]
+        ops.dropout(dfeat[:, :H], None, self.rng, out=dc_final[:B])
+        ops.dropout(dfeat[:, H:], None, self.rng, out=dc_final[B:])
+        dS = self.zeros(Mt + Mp, H)
+        dseqV = self.zeros(Mv, Hv)
+        dc_init = self.zeros(B2, H, f32)
+        self.struct_bwd(sv["struct"], 1.0, dc_init, dS[Mt:])
+        self.tower_bwd(dS, dseqV, dc_init)
+

@@ -422,6 +422,26 @@ class CudaOps(object):
                    _i(B), _i(H), r, s, p, _p(loss), self._st())
         return loss
 
+    def pair_cls_loss(self, logits, labels, dlogits=None, grad_scale=1.0):
+        """[B, 2] fp32 logits -> (loss [1], probs [B, 2]); dlogits: bf16 [B, >=2] gets the gradient."""
+        assert logits.dtype == torch.float32 and logits.shape[1] == 2
+        B = logits.shape[0]
+        loss = torch.zeros(1, dtype=torch.float32, device=logits.device)
+        probs = torch.empty(B, 2, dtype=torch.float32, device=logits.device)
+        self._call("k3m_pair_cls_loss", _p(logits), _i(_ld(logits)), _p(labels), _i(B), _f(grad_scale), _p(loss),
+                   _p(probs), _p(dlogits), _i(_ld(dlogits)), self._st())
+        return loss, probs
+
+    def dropout(self, x, drop, rng, out=None, out_dtype=None):
+        """nn.Dropout outside a GEMM epilogue; `drop` = (p, site) or None (copy / cast only)."""
+        rows, cols = x.shape
+        if out is None:
+            out = torch.empty(rows, cols, dtype=out_dtype or x.dtype, device=x.device)
+        r, s, p = self._drop(drop, rng)
+        self._call("k3m_dropout", _p(x), _i(_ld(x)), _i(_isf32(x)), _p(out), _i(_ld(out)), _i(_isf32(out)),
+                   _i(rows), _i(cols), r, s, p, self._st())
+        return out
+
     # ---- optimizer -------------------------------------------------------------------------
     def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True):
         self._call("k3m_adamw", _p(p32), _p(g32), _p(m), _p(v), _p(p_act), _p(hyper), _ll(p32.numel()),

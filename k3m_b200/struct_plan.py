@@ -14,8 +14,11 @@ import random
 import numpy as np
 
 
-def build_struct_plan(index_p, index_v, L_pv, num_negative_pv, rng=random):
+def build_struct_plan(index_p, index_v, L_pv, num_negative_pv, rng=random, halves=1):
     """index_p / index_v: integer arrays [B, max_num_pv, 2] (numpy or nested lists).
+    `halves=2`: the batch stacks the two towers of the item-alignment model (`item_embedding` is called
+    once per item of the pair, `vilbert_k3m.py:3408-3433`): the stale-`t` fallback of an item without
+    PVs does not cross from one call into the next, and there are no LPM terms (`:3105-3161`).
 
     Returns a dict of int32 numpy arrays:
       pair_item [P]      item of each valid (item, PV) pair, in reference loop order
@@ -29,6 +32,8 @@ def build_struct_plan(index_p, index_v, L_pv, num_negative_pv, rng=random):
     pair_item, pair_rows, seg, first = [], [], [], []
     last = None
     for i in range(B):
+        if halves > 1 and i % (B // halves) == 0:
+            last = None                   # a new `structure_aggregator` call: `t` is unbound again
         start = len(pair_item)
         for j in range(J):
             if ip[i, j, 0] == 0:          # loop stops at the first [0, *] row (`:2441`)
@@ -52,6 +57,8 @@ def build_struct_plan(index_p, index_v, L_pv, num_negative_pv, rng=random):
     for i in pair_item:
         counts[i] += 1
     terms = []
+    if halves > 1:
+        counts = [0] * B                  # alignment: no link-prediction terms, no random draws
     n_ent = num_negative_pv // 2
     n_val = num_negative_pv - n_ent
     for i in range(B):

@@ -80,6 +80,7 @@ class K3MPreTrainedModel(nn.Module):
 
     config_class = BertConfig
     base_model_prefix = "bert"
+    _kind = "pretrain"                      # parameter inventory (`layout.param_spec`)
 
     def __init__(self, config, ops=None):
         super(K3MPreTrainedModel, self).__init__()
@@ -91,7 +92,7 @@ class K3MPreTrainedModel(nn.Module):
                     self.__class__.__name__, self.__class__.__name__))
         self.config = config
         self._ops = ops
-        self._layout = ArenaLayout(config)
+        self._layout = ArenaLayout(config, self._kind)
         self._arena = torch.zeros(self._layout.total, dtype=torch.float32)
         self._engine = None
         self._w16 = self._g32 = self._rng = None
@@ -112,8 +113,9 @@ class K3MPreTrainedModel(nn.Module):
             self._node_for(name).register_parameter(name.rsplit(".", 1)[1], p)
         # the tied decoder (`tie_weights`, `vilbert_k3m.py:2266-2272`): same Parameter object under a
         # second name -> named_parameters() lists it once, state_dict() twice (999 keys)
-        self._node_for(TIED_ALIAS[0]).register_parameter(TIED_ALIAS[0].rsplit(".", 1)[1],
-                                                         self._params[TIED_ALIAS[1]])
+        if self._kind == "pretrain":
+            self._node_for(TIED_ALIAS[0]).register_parameter(TIED_ALIAS[0].rsplit(".", 1)[1],
+                                                             self._params[TIED_ALIAS[1]])
 
     def _node_for(self, dotted):
         node = self
@@ -259,7 +261,10 @@ class K3MPreTrainedModel(nn.Module):
             if g is None:
                 g = torch.zeros(1, dtype=torch.float32, device=dev)
             scales.append(g.reshape(1).to(torch.float32).contiguous())
-        self._engine.backward(tuple(scales))
+        if self._kind == "alignment":
+            self._engine.backward_alignment(scales[0])
+        else:
+            self._engine.backward(tuple(scales))
         if self._group is not None and self._world > 1:
             torch.distributed.all_reduce(self._g32[:L.trained_end], group=self._group)
             ops.scale_(self._g32[:L.trained_end], 1.0 / self._world)
@@ -370,6 +375,92 @@ class BertForMultiModalPreTraining_tri_stru(K3MPreTrainedModel):
         self._rng[1:].add_(1)
         return (lt.reshape(1), lv.reshape(1), 0, lpv.reshape(1), 0, 0, litm.reshape(1), c_init, c_fin,
                 llpm.reshape(1))
+
+
+class _PairFunction(torch.autograd.Function):
+    """Autograd node of the item-alignment step: the pair loss is differentiable, the rest is value-only."""
+
+    @staticmethod
+    def forward(ctx, anchor, owner, batch, plan, labels):
+        out = owner._engine.forward_alignment(batch, plan, labels, None)
+        ctx.owner = owner
+        ctx.token = owner._fwd_token
+        res = (out["loss"], out["probs"], out["c_final"])
+        ctx.mark_non_differentiable(res[1], res[2])
+        return res
+
+    @staticmethod
+    def backward(ctx, g_loss, *unused):
+        owner = ctx.owner
+        if ctx.token != owner._fwd_token:
+            raise RuntimeError("backward() of an alignment step whose activations were released by a later forward()")
+        owner._run_backward((g_loss,))
+        return None, None, None, None, None
+
+
+class K3MForItemAlignment(K3MPreTrainedModel):
+    """`vilbert_k3m/vilbert_k3m.py:2862-3454`: two item towers with shared weights -> `c_final` of each
+    item -> ClassificationHead on their concatenation -> cross-entropy (`loss_type == "ce"`, the mode of
+    `run_finetune_item_alignment.sh`).  Both towers run as ONE stacked pass of 2B items."""
+
+    _kind = "alignment"
+
+    def __init__(self, config, ops=None):
+        if getattr(config, "loss_type", "ce") != "ce":
+            raise NotImplementedError("loss_type %r: only the \"ce\" head of K3MForItemAlignment is built "
+                                      "(\"cosine\" compares item 1 with itself in the reference, vilbert_k3m.py:3442; "
+                                      "\"inner\" has no loss_fct, :2925-2931)" % (config.loss_type,))
+        super(K3MForItemAlignment, self).__init__(config, ops)
+
+    def forward(
+            self,
+            labels,
+            # item 1
+            input_ids_1, token_type_ids_1, attention_mask_1, input_ids_pv_1, token_type_ids_pv_1,
+            attention_mask_pv_1, index_p_1, index_v_1, image_feat_1, image_loc_1, image_attention_mask_1,
+            # item 2
+            input_ids_2, token_type_ids_2, attention_mask_2, input_ids_pv_2, token_type_ids_pv_2,
+            attention_mask_pv_2, index_p_2, index_v_2, image_feat_2, image_loc_2, image_attention_mask_2,
+            output_all_attention_masks=False,
+    ):
+        """Same 23 positional arguments and return as the reference (`:3379-3454`):
+        (probs[:, 0], probs[:, 1], probs[:, 1], loss) — in "ce" mode the two "embeddings" slots are
+        overwritten with the class probabilities (`:3446-3450`)."""
+        self._ensure_engine()
+        dev = self._arena.device
+        i64, f32 = torch.int64, torch.float32
+
+        def both(a, b, dtype):
+            return torch.cat((_as_dev(a, dev, dtype), _as_dev(b, dev, dtype)), dim=0)
+
+        batch = dict(
+            input_ids=both(input_ids_1, input_ids_2, i64),
+            token_type_ids=both(token_type_ids_1, token_type_ids_2, i64),
+            attention_mask=both(attention_mask_1, attention_mask_2, i64),
+            input_ids_pv=both(input_ids_pv_1, input_ids_pv_2, i64),
+            token_type_ids_pv=both(token_type_ids_pv_1, token_type_ids_pv_2, i64),
+            attention_mask_pv=both(attention_mask_pv_1, attention_mask_pv_2, i64),
+            image_feat=both(image_feat_1, image_feat_2, f32),
+            image_loc=both(image_loc_1, image_loc_2, f32),
+            image_attention_mask=both(image_attention_mask_1, image_attention_mask_2, i64),
+        )
+        ip = torch.cat((index_p_1.detach().cpu(), index_p_2.detach().cpu()), dim=0).numpy()
+        iv = torch.cat((index_v_1.detach().cpu(), index_v_2.detach().cpu()), dim=0).numpy()
+        plan = build_struct_plan(ip, iv, batch["input_ids_pv"].shape[1], self.config.num_negative_pv, halves=2)
+        plan = self._ops.plan_to_device(plan, dev)
+        lab = _as_dev(labels.reshape(-1), dev, i64)
+        self._ops.cast(self._arena, self._w16.dtype, out=self._w16)
+        eng = self._engine
+        eng.training = self.training
+        self._fwd_token += 1
+        if torch.is_grad_enabled():
+            loss, probs, _ = _PairFunction.apply(self._anchor, self, batch, plan, lab)
+        else:
+            out = eng.forward_alignment(batch, plan, lab, None)
+            eng.saved = None
+            loss, probs = out["loss"], out["probs"]
+        self._rng[1:].add_(1)
+        return probs[:, 0], probs[:, 1], probs[:, 1], loss.reshape(())
 
 
 def install_as_reference():

@@ -179,7 +179,7 @@ class Oracle(object):
         return s[0] * a[:, :, 0] + s[1] * a[:, :, 1] + s[2] * a[:, :, 2]
 
     # ---- structure aggregation + LPM -------------------------------------------------------
-    def structure_aggregator(self, c_initial, seq_pv, index_p, index_v):
+    def structure_aggregator(self, c_initial, seq_pv, index_p, index_v, lpm=True):
         """`structure_aggregator` `:2413-2505`.  Same loop order and the same `random.sample`
         call sequence as the reference, so seeding `random` identically gives identical
         negatives.  Items without any PV reuse the previous item's `t` (the reference's bare
@@ -209,6 +209,8 @@ class Oracle(object):
             att = torch.softmax(self.lin("struc_w2", F.leaky_relu(t)), dim=0)
             finals.append(c_initial[i] + self.lin("struc_w3", (att * t).sum(0)))
         c_final = torch.stack(finals)
+        if not lpm:          # the alignment model's aggregator (`:3105-3161`) stops here
+            return c_final, None
         nneg = self.cfg.num_negative_pv
         pos, neg = [], []
         for i in range(B):
@@ -255,6 +257,49 @@ class Oracle(object):
         """Returns the reference's 10-tuple (`:2834-2846`)."""
         c = self.cfg
         f32 = torch.float32
+        seq_v, seq_t, seq_pv, pool_v, pool_t, pool_pv, c_initial = self.tower(batch, gumbel_noise)
+        c_final, loss_lpm = self.structure_aggregator(c_initial, seq_pv, batch["index_p"],
+                                                      batch["index_v"])
+        # heads `:1875-1909`
+        itm = self.lin("cls.seq_relationship", self.drop(pool_t + pool_pv + pool_v, 0.1))
+        sc_t = self.mlm_scores(seq_t)
+        sc_pv = self.mlm_scores(seq_pv)
+        sc_v = self.image_scores(seq_v)[:, 1:]                                # `:2745`
+        # losses `:2754-2832`
+        lab = (batch["image_label"] == 1)
+        kl = F.kl_div(F.log_softmax(sc_v, dim=2), batch["image_target"], reduction="none")
+        # reference divides by max(count, 0) (`:2760`): NaN/inf when nothing is masked
+        loss_v = (kl * lab.unsqueeze(2).to(f32)).sum() / max(int(lab.sum()), 0) \
+            if int(lab.sum()) > 0 else (kl * 0).sum() / 0.0
+        V = c.vocab_size
+        loss_t = F.cross_entropy(sc_t.reshape(-1, V), batch["masked_lm_labels"].reshape(-1),
+                                 ignore_index=-1)
+        loss_pv = F.cross_entropy(sc_pv.reshape(-1, V), batch["masked_lm_labels_pv"].reshape(-1),
+                                  ignore_index=-1)
+        nsl = 1 - 1 * ((batch["next_sentence_label"] + batch["next_sentence_label_pv_v"]
+                        + batch["next_sentence_label_pv_t"]) == 0)
+        loss_itm = F.cross_entropy(itm.view(-1, 2), nsl.view(-1).long(), ignore_index=-1)
+        return (loss_t[None], loss_v[None], 0, loss_pv[None], 0, 0, loss_itm[None],
+                c_initial, c_final, loss_lpm[None])
+
+    def forward_alignment(self, labels, item1, item2, noise1=None, noise2=None):
+        """`K3MForItemAlignment.forward`, "ce" branch (`:3379-3454`): two `item_embedding` calls with
+        shared weights (`:3329-3377`), ClassificationHead (`:2164-2183`) on cat(c_final_1, c_final_2),
+        cross-entropy.  Returns (probs [B, 2], loss [1], c_final_1, c_final_2)."""
+        finals = []
+        for item, gn in ((item1, noise1), (item2, noise2)):
+            seq_v, seq_t, seq_pv, pool_v, pool_t, pool_pv, c_initial = self.tower(item, gn)
+            finals.append(self.structure_aggregator(c_initial, seq_pv, item["index_p"], item["index_v"],
+                                                    lpm=False)[0])
+        x = self.drop(torch.cat(finals, dim=1), self.cfg.hidden_dropout_prob)
+        x = torch.tanh(self.lin("classifier.dense", x))
+        logits = self.lin("classifier.out_proj", self.drop(x, self.cfg.hidden_dropout_prob))
+        loss = F.cross_entropy(logits.view(-1, 2), labels.view(-1).long())
+        return torch.softmax(logits, dim=1), loss[None], finals[0], finals[1]
+
+    def tower(self, batch, gumbel_noise=None):
+        """`bert_tri` `:2507-2671` + fusion / pooling `:2376-2411` + `c_initial` `:2723` (`:3368-3373`)."""
+        f32 = torch.float32
 
         def ext(m):  # `:2547-2580`
             return ((1.0 - m.to(f32)) * -10000.0)[:, None, None, :]
@@ -281,29 +326,7 @@ class Oracle(object):
         pool_t = seq_t[:, 1:].mean(1)
         pool_pv = seq_pv[:, 1:].mean(1)
         c_initial = (pool_v + pool_t + pool_pv) / 3                           # `:2723`
-        c_final, loss_lpm = self.structure_aggregator(c_initial, seq_pv, batch["index_p"],
-                                                      batch["index_v"])
-        # heads `:1875-1909`
-        itm = self.lin("cls.seq_relationship", self.drop(pool_t + pool_pv + pool_v, 0.1))
-        sc_t = self.mlm_scores(seq_t)
-        sc_pv = self.mlm_scores(seq_pv)
-        sc_v = self.image_scores(seq_v)[:, 1:]                                # `:2745`
-        # losses `:2754-2832`
-        lab = (batch["image_label"] == 1)
-        kl = F.kl_div(F.log_softmax(sc_v, dim=2), batch["image_target"], reduction="none")
-        # reference divides by max(count, 0) (`:2760`): NaN/inf when nothing is masked
-        loss_v = (kl * lab.unsqueeze(2).to(f32)).sum() / max(int(lab.sum()), 0) \
-            if int(lab.sum()) > 0 else (kl * 0).sum() / 0.0
-        V = c.vocab_size
-        loss_t = F.cross_entropy(sc_t.reshape(-1, V), batch["masked_lm_labels"].reshape(-1),
-                                 ignore_index=-1)
-        loss_pv = F.cross_entropy(sc_pv.reshape(-1, V), batch["masked_lm_labels_pv"].reshape(-1),
-                                  ignore_index=-1)
-        nsl = 1 - 1 * ((batch["next_sentence_label"] + batch["next_sentence_label_pv_v"]
-                        + batch["next_sentence_label_pv_t"]) == 0)
-        loss_itm = F.cross_entropy(itm.view(-1, 2), nsl.view(-1).long(), ignore_index=-1)
-        return (loss_t[None], loss_v[None], 0, loss_pv[None], 0, 0, loss_itm[None],
-                c_initial, c_final, loss_lpm[None])
+        return seq_v, seq_t, seq_pv, pool_v, pool_t, pool_pv, c_initial
 
 
 def total_loss(out, loss_img_weight=1.0):

@@ -487,6 +487,23 @@ class RefOps(object):
         labels = 1 - ((l1 + l2 + l3) == 0).long()
         return torch.nn.functional.cross_entropy(lg, labels, ignore_index=-1).reshape(1)
 
+    def pair_cls_loss(self, logits, labels, dlogits=None, grad_scale=1.0):
+        """"ce" branch of K3MForItemAlignment.forward (`:3443-3450`)."""
+        lg = logits.float()
+        probs = torch.softmax(lg, dim=1)
+        loss = torch.nn.functional.cross_entropy(lg, labels.long()).reshape(1)
+        if dlogits is not None:
+            oh = torch.nn.functional.one_hot((labels != 0).long(), 2).float()
+            dlogits[:, :2] = (grad_scale * (probs - oh) / lg.shape[0]).to(dlogits.dtype)
+        return loss, probs
+
+    def dropout(self, x, drop, rng, out=None, out_dtype=None):
+        y = _apply_drop(x.float(), drop, rng).to(out_dtype or (out.dtype if out is not None else x.dtype))
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y
+
     # ---- optimizer -------------------------------------------------------------------------
     def plan_to_device(self, plan, device):
         return {k: torch.from_numpy(v).to(device) for k, v in plan.items()}

@@ -481,6 +481,33 @@ def test_itm(ops, ref):
               ref.itm_loss(pt, pp, pv, w, b, l1, z, z, drop=drop, rng=r), 1e-5, 1e-6, "itm")
 
 
+def test_pair_cls_loss_and_dropout(ops, ref):
+    """item-alignment head kernels (K3MForItemAlignment "ce" branch, ClassificationHead dropout)"""
+    B = 37
+    logits = rnd(B, 2, dtype=F32, scale=2.0)
+    labels = (torch.arange(B, device=DEV) % 3 == 0).to(torch.int64)
+    d1 = torch.zeros(B, 8, dtype=BF, device=DEV)
+    d2 = torch.zeros(B, 8, dtype=BF, device=DEV)
+    l1, p1 = ops.pair_cls_loss(logits, labels, dlogits=d1, grad_scale=0.5)
+    l2, p2 = ref.pair_cls_loss(logits, labels, dlogits=d2, grad_scale=0.5)
+    close(l1, l2, 1e-6, 1e-6, "pair loss")
+    close(p1, p2, 1e-6, 1e-6, "pair probs")
+    close_bf16(d1, d2, "pair dlogits")
+    assert float(d1[:, 2:].abs().max()) == 0.0
+    r = rng_state()
+    x = rnd(33, 1536, seed=5)
+    for drop in (None, (0.1, 9)):
+        y = ops.dropout(x, drop, r)
+        close_bf16(y, ref.dropout(x, drop, r), "dropout")
+        if drop is not None:                         # keep-mask bit-exact against the counter RNG restatement
+            assert torch.equal(y != 0, dropout_keep(r, 9, 33, 1536, 0.1) & (x != 0))
+    # strided fp32 -> bf16 copy used to build cat(c_final_1, c_final_2)
+    c = rnd(8, 768, dtype=F32, seed=6)
+    feat = torch.zeros(8, 1536, dtype=BF, device=DEV)
+    ops.dropout(c, None, r, out=feat[:, 768:])
+    assert torch.equal(feat[:, 768:], c.to(BF)) and float(feat[:, :768].abs().max()) == 0.0
+
+
 # ---- optimizer -------------------------------------------------------------------------------------
 def test_adamw_matches_torch_optim(ops, ref):
     n = 1 << 20

@@ -109,3 +109,78 @@ def compare_with_golden(fx, out, L, g, loss_rtol, grad_tol, key_bias_atol=None, 
         if not (e1 <= grad_tol and e2 <= grad_tol):
             errs.append("%s: norm err %.3e sampled rel-L2 err %.3e" % (n, e1, e2))
     return errs, worst
+
+
+# ---- item alignment (K3MForItemAlignment) ---------------------------------------------------------
+ITEM_KEYS = ("input_ids", "token_type_ids", "attention_mask", "input_ids_pv", "token_type_ids_pv",
+             "attention_mask_pv", "index_p", "index_v", "image_feat", "image_loc", "image_attention_mask")
+
+
+def align_case_setup(fx):
+    """alignment fixture -> (cfg, state_dict, stacked batch of 2B items, labels [B], noise or None)"""
+    cfg = BertConfig.from_dict(fx["config"])
+    for k, v in fx["overrides"].items():
+        setattr(cfg, k, v)
+    B, Lt, Lv, Lpv, mpv = fx["dims"]
+    sd = synth_state_dict(param_spec(cfg, "alignment"), seed=fx["seeds"]["weights"])
+    batch = synth_batch(cfg, 2 * B, Lt, Lv, Lpv, max_num_pv=mpv, seed=fx["seeds"]["batch"])
+    labels = torch.randint(0, 2, (B,), generator=torch.Generator().manual_seed(fx["seeds"]["batch"]))
+    noise = make_noise(cfg, 2 * B, Lt, Lv + 1, Lpv, fx["seeds"]["noise"]) if cfg.if_pre_sampling == 1 else None
+    return cfg, sd, batch, labels, noise
+
+
+def run_engine_alignment(cfg, sd, batch, labels, noise, ops, device, adt, training=False):
+    """One forward+backward of the alignment path; returns (outputs dict, layout, fp32 grad arena)."""
+    L = ArenaLayout(cfg, "alignment")
+    w32 = torch.zeros(L.total)
+    for n, (off, num, _) in L.offsets.items():
+        w32[off:off + num] = sd[n].reshape(-1)
+    w = w32.to(device=device, dtype=adt)
+    g = torch.zeros(L.total, dtype=torch.float32, device=device)
+    rng = torch.tensor([1234, 0], dtype=torch.int64, device=device)
+    eng = Engine(cfg, L, ops, w, g, rng, adt)
+    eng.training = training
+    plan = build_struct_plan(batch["index_p"].numpy(), batch["index_v"].numpy(), batch["input_ids_pv"].shape[1],
+                             cfg.num_negative_pv, halves=2)
+    plan = ops.plan_to_device(plan, device)
+    b = {k: v.to(device) for k, v in batch.items()}
+    en = None
+    if noise is not None:
+        en = {m: x.reshape(-1, 3, x.shape[-1]).contiguous().to(device) for m, x in noise.items()}
+    out = eng.forward_alignment(b, plan, labels.to(device), en)
+    eng.backward_alignment()
+    return out, L, g
+
+
+def compare_alignment_with_golden(fx, out, L, g, loss_rtol, grad_tol, prob_atol):
+    errs = []
+    got = float(out["loss"].reshape(-1)[0])
+    if not abs(got - fx["loss"]) <= loss_rtol * abs(fx["loss"]):
+        errs.append("loss: got %.6f want %.6f" % (got, fx["loss"]))
+    pe = float((out["probs"].float().cpu() - fx["probs"]).abs().max())
+    if not pe <= prob_atol:
+        errs.append("probs: max abs err %.3e" % pe)
+    for k in ("c_initial", "c_final"):
+        ref = fx[k]
+        e = float((out[k].float().cpu() - ref).norm()) / (float(ref.norm()) + 1e-12)
+        if not e <= max(grad_tol, 10 * loss_rtol):
+            errs.append("%s: rel err %.3e" % (k, e))
+    gc = g.cpu()
+    for n, (off, num, shape) in L.offsets.items():
+        ref = fx["grads"][n]
+        got = gc[off:off + num]
+        if ref is None:
+            if float(got.abs().max()) != 0.0:
+                errs.append("%s: reference has no gradient, got max %.3e" % (n, float(got.abs().max())))
+            continue
+        scale = ref["maxabs"]
+        if scale < 1e-9:
+            if not float(got.abs().max()) <= 1e-6:
+                errs.append("%s: expected ~0 gradient, got %.3e" % (n, float(got.abs().max())))
+            continue
+        e1 = abs(float(got.norm()) - ref["norm"]) / ref["norm"]
+        smp = ref["sample"]
+        e2 = float((got[sample_index(num)] - smp).norm()) / (float(smp.norm()) + 1e-3 * scale)
+        if not (e1 <= grad_tol and e2 <= grad_tol):
+            errs.append("%s: norm err %.3e sampled rel-L2 err %.3e" % (n, e1, e2))
+    return errs

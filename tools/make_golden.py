@@ -101,6 +101,90 @@ def run_case(name):
     print(name, fx["losses"], os.path.getsize(path))
 
 
+# ---- item alignment (K3MForItemAlignment, finetune.py / run_finetune_item_alignment.sh) ---------------
+ALIGN_CASES = {
+    # name: (config, overrides, pairs, Lt, Lv, Lpv, max_num_pv, weight seed, batch seed, noise seed)
+    "align_tiny_mean": (K3M_TINY, dict(if_pre_sampling=0, loss_type="ce"), 3, 12, 9, 20, 4, 11, 17, 0),
+    "align_tiny_hard": (K3M_TINY, dict(if_pre_sampling=1, loss_type="ce"), 4, 10, 8, 16, 3, 12, 18, 6),
+}
+ITEM_KEYS = ("input_ids", "token_type_ids", "attention_mask", "input_ids_pv", "token_type_ids_pv",
+             "attention_mask_pv", "index_p", "index_v", "image_feat", "image_loc", "image_attention_mask")
+
+
+def split_items(batch, B):
+    """stacked synthetic batch of 2B items -> (item-1 dict, item-2 dict) of B items each"""
+    return ({k: batch[k][:B] for k in ITEM_KEYS}, {k: batch[k][B:] for k in ITEM_KEYS})
+
+
+def align_labels(B, seed):
+    return torch.randint(0, 2, (B,), generator=torch.Generator().manual_seed(seed))
+
+
+def run_align_case(name):
+    d, ov, B, Lt, Lv, Lpv, mpv, wseed, bseed, nseed = ALIGN_CASES[name]
+    ref = ref_harness.import_reference()
+    rcfg = ref.BertConfig.from_dict(dict(d))
+    cfg = BertConfig.from_dict(d)
+    for k, v in ov.items():
+        setattr(rcfg, k, v)
+        setattr(cfg, k, v)
+    model = ref.K3MForItemAlignment(rcfg)
+    spec = param_spec(cfg, "alignment")
+    assert [n for n, _ in model.named_parameters()] == list(spec.keys()), "alignment parameter order"
+    sd = synth_state_dict(spec, seed=wseed)
+    model.load_state_dict(sd)
+    model.eval()
+    batch = synth_batch(cfg, 2 * B, Lt, Lv, Lpv, max_num_pv=mpv, seed=bseed)
+    it1, it2 = split_items(batch, B)
+    labels = align_labels(B, bseed)
+    noise = make_noise(cfg, 2 * B, Lt, Lv + 1, Lpv, nseed) if cfg.if_pre_sampling == 1 else None
+    orig = F.gumbel_softmax
+    if noise is not None:
+        # two item_embedding calls (:3408-3433), each fusing v, t, pv (:2387-2392)
+        order = iter([("v", 0), ("t", 0), ("pv", 0), ("v", 1), ("t", 1), ("pv", 1)])
+
+        def patched(logits, tau=1, hard=False, eps=1e-10, dim=-1):
+            m, half = next(order)
+            y = ((logits + noise[m][half * B:(half + 1) * B]) / tau).softmax(dim)
+            idx = y.max(dim, keepdim=True)[1]
+            yh = torch.zeros_like(logits).scatter_(dim, idx, 1.0)
+            return yh - y.detach() + y
+        F.gumbel_softmax = patched
+    args = [labels]
+    for it in (it1, it2):
+        args += [it[k] for k in ITEM_KEYS]
+    out = model(*args)
+    out[3].backward()
+    finals = []
+    with torch.no_grad():
+        for half, it in enumerate((it1, it2)):
+            if noise is not None:
+                order = iter([("v", half), ("t", half), ("pv", half)])
+            finals.append(model.item_embedding(it["input_ids"], it["image_feat"], it["image_loc"], it["token_type_ids"],
+                                               it["attention_mask"], it["image_attention_mask"], False,
+                                               it["input_ids_pv"], it["token_type_ids_pv"], it["attention_mask_pv"],
+                                               it["index_p"], it["index_v"]))
+    F.gumbel_softmax = orig
+    grads = {}
+    for n, p in model.named_parameters():
+        if p.grad is None:
+            grads[n] = None
+            continue
+        g = p.grad.reshape(-1)
+        grads[n] = dict(norm=float(g.norm()), maxabs=float(g.abs().max()), sample=g[sample_index(g.numel())].clone())
+    fx = dict(case=name, kind="alignment", config=d, overrides=ov, dims=(B, Lt, Lv, Lpv, mpv),
+              seeds=dict(weights=wseed, batch=bseed, noise=nseed), noise=None,
+              loss=float(out[3]), probs=torch.stack((out[0], out[1]), dim=1).detach().clone(),
+              c_initial=torch.cat([f[0] for f in finals]).clone(), c_final=torch.cat([f[1] for f in finals]).clone(),
+              grads=grads)
+    path = os.path.join(ROOT, "tests", "golden", name + ".pt")
+    torch.save(fx, path)
+    print(name, fx["loss"], fx["probs"][:, 1].tolist(), os.path.getsize(path))
+
+
 if __name__ == "__main__":
-    for n in (sys.argv[1:] or CASES):
-        run_case(n)
+    for n in (sys.argv[1:] or list(CASES) + list(ALIGN_CASES)):
+        if n in ALIGN_CASES:
+            run_align_case(n)
+        else:
+            run_case(n)
