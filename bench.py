@@ -33,6 +33,13 @@ PER_GPU_BATCH = 64
 FLOPS_PER_SAMPLE = 159.6e9
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of the GEMM kernel, mean per launch over the launches captured by
+# `ncu --set full -k regex:gemm_kernel -s 700 -c 6 python bench.py --steps 1 --warmup 1` (round 1, third capture)
+NCU_GEMM_TRAFFIC_BYTES = 51.0e6
+NCU_GEMM_TRAFFIC_NOTE = ("mean DRAM bytes per launch over 6 captured launches of the text-stack forward GEMMs "
+                         "(profiles/r01c_ncu_full_gemm.csv); their algorithmic bytes average 54 MB")
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -237,9 +244,12 @@ def run_gpu_arm(args):
     # ---- (2) end to end: host batch -> H2D -> step -> D2H losses, every step ----
     barrier()
     e0.record()
+    # every step: H2D of its inputs from pinned memory, the step, a D2H read of a step's losses — the
+    # read lags one step (the host prepares step i+1 while the device runs step i); the last read drains
     for i in range(args.steps):
         step.step(host[i % 4])
-        last = step.read_losses()
+        step.read_losses_lagged()
+    last = step.read_losses()
     e1.record()
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
@@ -290,7 +300,8 @@ def run_gpu_arm(args):
         "launches_per_step": step.launches_per_step,
         "roofline": {"bound": "tensor", "kernel": "gemm_kernel (k3m_gemm_bf16: tcgen05/TMEM/TMA)",
                      "achieved": gemm_tflops, "peak": peaks["tflops"], "unit": "TFLOP/s",
-                     "frac": gemm_tflops / peaks["tflops"], "traffic": None, "peak_source": peaks["source"],
+                     "frac": gemm_tflops / peaks["tflops"], "traffic": NCU_GEMM_TRAFFIC_BYTES, "traffic_note": NCU_GEMM_TRAFFIC_NOTE,
+                     "peak_source": peaks["source"],
                      "launches_per_step": g_n, "ms_per_step_in_kernel": g_ms,
                      "share_of_step_kernel_time": g_ms / tot_ms,
                      "flops_per_step_in_kernel": g_fl,

@@ -100,6 +100,7 @@ class PretrainStep(object):
         self.hyper = torch.zeros(2, 8, dtype=f32, device=dev)
         self._hyper_host = [pin(torch.zeros(2, 8, dtype=f32)) for _ in range(2)]
         self._slot_events = [None, None]
+        self._stage, self._copy_stream = None, None
         self.losses = torch.zeros(8, dtype=f32, device=dev)
         self.losses_host = pin(torch.zeros(8, dtype=f32))
         self.h2d_bytes = sum(int(np.prod(s)) * (8 if d == torch.int64 else 4) for s, d in self.spec.values())
@@ -270,7 +271,7 @@ class PretrainStep(object):
         self.launches_per_step = self.ops.launches - n0
 
     # ---- host side -----------------------------------------------------------------------------
-    def _write_hyper(self, slot):
+    def _fill_hyper(self, slot):
         step = self.global_step + 1
         f = 1.0
         if self.total_steps > 0:
@@ -279,7 +280,6 @@ class PretrainStep(object):
         for gi, wd in enumerate((self.weight_decay, 0.0)):
             h[gi] = torch.tensor([self.lr * f, self.betas[0], self.betas[1], self.eps, wd, float(step),
                                   1.0 / self.world, 0.0])
-        self.hyper.copy_(h, non_blocking=True)
 
     def step(self, batch):
         """batch: dict of HOST tensors named as the reference's forward() arguments (pinned memory
@@ -289,24 +289,52 @@ class PretrainStep(object):
         `.cpu()` at `pretrain.py:1071-1075`)."""
         slot = self.global_step & 1
         if self._slot_events[slot] is not None:
-            self._slot_events[slot].synchronize()           # pinned staging of step-2 has been consumed
+            self._slot_events[slot].synchronize()           # staging of step-2 has been consumed
         plan = build_struct_plan(batch["index_p"].numpy(), batch["index_v"].numpy(), self.Lpv,
                                  self.cfg.num_negative_pv)
         plan = pad_struct_plan(plan, self.B, self.max_num_pv, self.cfg.num_negative_pv)
         ph = self._plan_host[slot]
         for k, v in plan.items():
             ph[k].copy_(torch.from_numpy(v).reshape(ph[k].shape))
-            self.plan[k].copy_(ph[k], non_blocking=True)
         for k, dst in self.inputs.items():
             src = batch[k]
             if tuple(src.shape) != tuple(dst.shape) or src.dtype != dst.dtype:
                 raise ValueError("%s: got %s %s, this step was built for %s %s" % (
                     k, tuple(src.shape), src.dtype, tuple(dst.shape), dst.dtype))
-            dst.copy_(src, non_blocking=True)
-        self._write_hyper(slot)
-        if self._cuda:
+        self._fill_hyper(slot)
+        if not self._cuda:
+            for k, v in ph.items():
+                self.plan[k].copy_(v)
+            for k, dst in self.inputs.items():
+                dst.copy_(batch[k])
+            self.hyper.copy_(self._hyper_host[slot])
+        else:
+            # host -> device on a copy stream into per-slot device staging (overlaps the previous step's
+            # kernels), then a device-to-device hop into the graph's static input buffers on the main stream
+            if self._stage is None:
+                self._copy_stream = torch.cuda.Stream(device=self.device)
+                mk = lambda t: torch.empty_like(t)          # noqa: E731
+                self._stage = [dict(inputs={k: mk(v) for k, v in self.inputs.items()},
+                                    plan={k: mk(v) for k, v in self.plan.items()}, hyper=mk(self.hyper))
+                               for _ in range(2)]
+            st = self._stage[slot]
+            main = torch.cuda.current_stream()
+            with torch.cuda.stream(self._copy_stream):
+                for k, v in ph.items():
+                    st["plan"][k].copy_(v, non_blocking=True)
+                for k in self.inputs:
+                    st["inputs"][k].copy_(batch[k], non_blocking=True)
+                st["hyper"].copy_(self._hyper_host[slot], non_blocking=True)
+                landed = torch.cuda.Event()
+                landed.record(self._copy_stream)
+            main.wait_event(landed)
+            for k in self.plan:
+                self.plan[k].copy_(st["plan"][k], non_blocking=True)
+            for k in self.inputs:
+                self.inputs[k].copy_(st["inputs"][k], non_blocking=True)
+            self.hyper.copy_(st["hyper"], non_blocking=True)
             ev = torch.cuda.Event()
-            ev.record()
+            ev.record(main)                                 # slot's pinned + device staging free again
             self._slot_events[slot] = ev
         if self.use_graph:
             if self.graph is None:
@@ -318,6 +346,33 @@ class PretrainStep(object):
             self.launches_per_step = getattr(self.ops, "launches", 0) - n0
         self.global_step += 1
         return self.losses
+
+    def read_losses_lagged(self):
+        """Asynchronous loss logging: enqueue the device->host copy of THIS step's losses and return the
+        PREVIOUS step's (None after the first step), waiting only for that older copy.  The host then
+        prepares step i+1 (index plan, H2D) while the device runs step i — the reference's drivers block
+        on five `.cpu()` calls per step instead (`pretrain.py:1071-1075`).  `read_losses()` drains."""
+        if not hasattr(self, "_loss_ring"):
+            pin = (lambda t: t.pin_memory()) if self._cuda else (lambda t: t)
+            self._loss_ring = [pin(torch.zeros(8, dtype=torch.float32)) for _ in range(2)]
+            self._loss_events = [None, None]
+            self._loss_reads = 0
+        slot = self._loss_reads & 1
+        prev = slot ^ 1
+        had_prev = self._loss_reads > 0
+        self._loss_reads += 1
+        out = None
+        if had_prev:                       # the copy enqueued one call ago (it is the older one: wait for it first)
+            if self._loss_events[prev] is not None:
+                self._loss_events[prev].synchronize()
+            h = self._loss_ring[prev]
+            out = {k: float(h[i]) for i, k in enumerate(LOSS_NAMES + ("loss",))}
+        self._loss_ring[slot].copy_(self.losses, non_blocking=True)
+        if self._cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+            self._loss_events[slot] = ev
+        return out
 
     def read_losses(self):
         self.losses_host.copy_(self.losses, non_blocking=True)
