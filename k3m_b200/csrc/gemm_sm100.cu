@@ -472,6 +472,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   else __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
+  // Programmatic dependent launch: everything above (barrier init, TMEM allocation, cluster sync) touches no
+  // global memory and may run while the previous kernel of the stream drains; from here on its results are
+  // needed.  Both instructions are no-ops when the launch did not carry the attribute.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   if (warp == 0) {
     if (lane == 0) {
@@ -814,7 +819,8 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
   const int total = p.tiles_m * p.tiles_n * p.splits;
   const int slots = num_sms() / CTAS;                 // CTAs (or CTA pairs) resident at once
   const int grid = (total < slots ? total : slots) * CTAS;
-  if (CTAS == 1) {
+  static const int pdl = getenv("K3M_GEMM_PDL") ? atoi(getenv("K3M_GEMM_PDL")) : 0;
+  if (CTAS == 1 && !pdl) {
     kern<<<grid, 64 + 128 * EW, SMEM, st>>>(ma, mb, mc, mx, mi, p);
   } else {
     cudaLaunchConfig_t cfg = {};
@@ -822,15 +828,24 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
     cfg.blockDim = dim3(64 + 128 * EW);
     cfg.dynamicSmemBytes = SMEM;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CTAS;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (CTAS == 2) {
+      attr[na].id = cudaLaunchAttributeClusterDimension;
+      attr[na].val.clusterDim.x = CTAS;
+      attr[na].val.clusterDim.y = 1;
+      attr[na].val.clusterDim.z = 1;
+      ++na;
+    }
+    if (pdl) {
+      attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[na].val.programmaticStreamSerializationAllowed = 1;
+      ++na;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = na;
     if (cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, mx, mi, p) != cudaSuccess) {
-      k3m_set_error("gemm: cluster launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+      k3m_set_error("gemm: launch failed: %s", cudaGetErrorString(cudaGetLastError()));
       return K3M_ERR_CUDA;
     }
   }

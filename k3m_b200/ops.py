@@ -50,6 +50,9 @@ class CudaOps(object):
         self._aux = {}
         import os
         self.use_aux = os.environ.get("K3M_WGRAD_STREAM", "1") != "0"
+        # the dgrad chain is the critical path of backward: its streams outrank the auxiliary (weight-gradient)
+        # and optimizer streams, whose kernels then fill the SMs the chain leaves idle instead of delaying it
+        self.hi_prio = -1 if os.environ.get("K3M_STREAM_PRIO", "0") != "0" else 0
 
     def parallel(self, fns):
         """Run independent closures on concurrent CUDA streams (fork after the current stream, join back
@@ -64,7 +67,7 @@ class CudaOps(object):
             return
         main = torch.cuda.current_stream()
         while len(self._side) < len(fns) - 1:
-            self._side.append(torch.cuda.Stream(device=self.device))
+            self._side.append(torch.cuda.Stream(device=self.device, priority=self.hi_prio))
         fork = torch.cuda.Event()
         fork.record(main)
         joins = []

@@ -253,7 +253,7 @@ class PretrainStep(object):
 
     def _capture(self):
         # warm-up on a side stream (lazy module loading, cudaFuncSetAttribute, NCCL setup), then capture
-        s = torch.cuda.Stream(device=self.device)
+        s = torch.cuda.Stream(device=self.device, priority=getattr(self.ops, "hi_prio", 0))
         s.wait_stream(torch.cuda.current_stream())
         snap = (self.p32.clone(), self.m.clone(), self.v.clone(), self.w16.clone(), self.rng.clone())
         with torch.cuda.stream(s):
