@@ -50,6 +50,9 @@ def input_spec(cfg, B, Lt, Lv1, Lpv, max_num_pv):
 
 
 class PretrainStep(object):
+    KIND = "pretrain"       # parameter inventory / engine entry points (AlignmentStep: "alignment")
+    HALVES = 1              # item groups that get their own `structure_aggregator` call
+
     def __init__(self, cfg, batch_size, len_t=36, len_v=36, len_pv=36, max_num_pv=8, device="cuda",
                  state_dict=None, init_seed=0, lr=1e-4, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01,
                  warmup_steps=0, total_steps=0, loss_img_weight=1.0, training=True, rng_seed=1234,
@@ -61,7 +64,8 @@ class PretrainStep(object):
         self.ops = ops if ops is not None else CudaOps(self.device)
         self._cuda = self.device.type == "cuda"
         adt = getattr(self.ops, "adt", torch.bfloat16)
-        self.layout = L = ArenaLayout(cfg)
+        self.layout = L = ArenaLayout(cfg, self.KIND)
+        self.n_items = batch_size * self.HALVES
         dev, f32 = self.device, torch.float32
         self.p32 = torch.zeros(L.total, dtype=f32, device=dev)
         self.m = torch.zeros(L.total, dtype=f32, device=dev)
@@ -83,13 +87,13 @@ class PretrainStep(object):
         else:
             self.init_weights(init_seed)
         # static graph inputs
-        self.spec = input_spec(cfg, self.B, self.Lt, self.Lv1, self.Lpv, max_num_pv)
+        self.spec = self._input_spec()
         self.inputs = {k: torch.zeros(s, dtype=d, device=dev) for k, (s, d) in self.spec.items()}
-        P_cap, T_cap, maxn = plan_capacity(self.B, max_num_pv, cfg.num_negative_pv)
+        P_cap, T_cap, maxn = plan_capacity(self.n_items, max_num_pv, cfg.num_negative_pv)
         i32 = torch.int32
         self.plan = dict(pair_item=torch.zeros(P_cap, dtype=i32, device=dev),
                          pair_rows=torch.zeros(P_cap, 4, dtype=i32, device=dev),
-                         seg=torch.zeros(self.B, 2, dtype=i32, device=dev),
+                         seg=torch.zeros(self.n_items, 2, dtype=i32, device=dev),
                          terms=torch.zeros(T_cap, 4, dtype=i32, device=dev),
                          n_terms=torch.zeros(1, dtype=i32, device=dev))
         self.plan["seg"]._k3m_maxn = maxn
@@ -115,6 +119,19 @@ class PretrainStep(object):
         self.use_graph = use_graph and self._cuda
         self.graph = None
         self.launches_per_step = 0
+
+    def _input_spec(self):
+        return input_spec(self.cfg, self.B, self.Lt, self.Lv1, self.Lpv, self.max_num_pv)
+
+    def _forward_backward(self):
+        """-> the eight fp32 values of `self.losses` as a list of [1] tensors / None."""
+        out = self.engine.forward(self.inputs, self.plan, None, self.loss_weights)
+        self.engine.on_ready = self._on_ready
+        self.engine.backward()
+        w = self.loss_weights
+        total = out["loss_t"] * w[0] + out["loss_v"] * w[1] + out["loss_pv"] * w[2] + out["loss_lpm"] * w[3]
+        self.c_initial, self.c_final = out["c_initial"], out["c_final"]
+        return [out[k] for k in LOSS_NAMES] + [total]
 
     # ---- parameters ------------------------------------------------------------------------
     def init_weights(self, seed):
@@ -160,7 +177,8 @@ class PretrainStep(object):
         for n in self.layout.spec:
             off, num, shape = self.layout.offsets[n]
             out[n] = self.p32[off:off + num].view(*shape)
-        out[TIED_ALIAS[0]] = out[TIED_ALIAS[1]]
+        if self.KIND == "pretrain":
+            out[TIED_ALIAS[0]] = out[TIED_ALIAS[1]]
         return out
 
     def grad(self, name):
@@ -240,16 +258,10 @@ class PretrainStep(object):
     def _device_step(self):
         L, ops = self.layout, self.ops
         self._ready_lo, self._next_bucket = L.decay_end, 0
-        out = self.engine.forward(self.inputs, self.plan, None, self.loss_weights)
-        self.engine.on_ready = self._on_ready
-        self.engine.backward()
+        vals = self._forward_backward()
         self._finish_buckets()
         self.rng[1:].add_(1)
-        w = self.loss_weights
-        torch.stack([out[k].reshape(()) for k in LOSS_NAMES], out=self.losses[:5])
-        self.losses[5] = (out["loss_t"] * w[0] + out["loss_v"] * w[1] + out["loss_pv"] * w[2]
-                          + out["loss_lpm"] * w[3]).reshape(())
-        self.c_initial, self.c_final = out["c_initial"], out["c_final"]
+        torch.stack([v.reshape(()) for v in vals], out=self.losses[:len(vals)])
 
     def _capture(self):
         # warm-up on a side stream (lazy module loading, cudaFuncSetAttribute, NCCL setup), then capture
@@ -291,8 +303,8 @@ class PretrainStep(object):
         if self._slot_events[slot] is not None:
             self._slot_events[slot].synchronize()           # staging of step-2 has been consumed
         plan = build_struct_plan(batch["index_p"].numpy(), batch["index_v"].numpy(), self.Lpv,
-                                 self.cfg.num_negative_pv)
-        plan = pad_struct_plan(plan, self.B, self.max_num_pv, self.cfg.num_negative_pv)
+                                 self.cfg.num_negative_pv, halves=self.HALVES)
+        plan = pad_struct_plan(plan, self.n_items, self.max_num_pv, self.cfg.num_negative_pv)
         ph = self._plan_host[slot]
         for k, v in plan.items():
             ph[k].copy_(torch.from_numpy(v).reshape(ph[k].shape))
@@ -379,3 +391,31 @@ class PretrainStep(object):
         if self._cuda:
             torch.cuda.current_stream().synchronize()
         return {k: float(self.losses_host[i]) for i, k in enumerate(LOSS_NAMES + ("loss",))}
+
+
+class AlignmentStep(PretrainStep):
+    """The item-alignment finetune step (`finetune.py:885-1010` around `K3MForItemAlignment.forward`,
+    `vilbert_k3m.py:3379-3454`, "ce" head) as one CUDA graph: both items of the `batch_size` pairs run as ONE
+    stacked tower pass of 2 * batch_size items, then ClassificationHead + cross-entropy, backward, gradient
+    all-reduce and AdamW exactly as in `PretrainStep`.  `step(batch)`: the eleven per-item tensors stacked
+    item-1-first along the batch axis (`[2B, ...]`) plus `labels` int64 [B].
+    `losses` = [pair loss, 0, 0, 0, 0, pair loss]; `probs` [B, 2] holds the class probabilities."""
+    KIND = "alignment"
+    HALVES = 2
+
+    def _input_spec(self):
+        full = input_spec(self.cfg, self.n_items, self.Lt, self.Lv1, self.Lpv, self.max_num_pv)
+        keep = ("input_ids", "token_type_ids", "attention_mask", "input_ids_pv", "token_type_ids_pv",
+                "attention_mask_pv", "image_feat", "image_loc", "image_attention_mask")
+        spec = {k: full[k] for k in keep}
+        spec["labels"] = ((self.B,), torch.int64)
+        return spec
+
+    def _forward_backward(self):
+        out = self.engine.forward_alignment(self.inputs, self.plan, self.inputs["labels"], None)
+        self.engine.on_ready = self._on_ready
+        self.engine.backward_alignment()
+        self.c_initial, self.c_final, self.probs = out["c_initial"], out["c_final"], out["probs"]
+        zero = torch.zeros(1, dtype=torch.float32, device=self.device)
+        return [out["loss"], zero, zero, zero, zero, out["loss"]]
+

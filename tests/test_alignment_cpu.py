@@ -79,3 +79,33 @@ def test_alignment_class_api_matches_reference():
     with torch.no_grad():
         again = model(*args)
     assert again[3].grad_fn is None and abs(float(again[3]) - fx["loss"]) <= 1e-5 * abs(fx["loss"])
+
+
+def test_alignment_step_object_matches_oracle_and_adamw():
+    """`AlignmentStep` (the fused finetune step: stacked towers, pair loss, AdamW groups) on the fp32
+    restatement: two optimizer steps against oracle gradients + torch.optim.AdamW."""
+    from k3m_b200.trainer import AlignmentStep
+    from tests.test_trainer_cpu import check_params, reference_update
+    fx = load_golden("align_tiny_mean")
+    cfg, sd, batch, labels, noise = align_case_setup(fx)
+    B, Lt, Lv, Lpv, mpv = fx["dims"]
+    step = AlignmentStep(cfg, B, len_t=Lt, len_v=Lv, len_pv=Lpv, max_num_pv=mpv, device="cpu", state_dict=sd,
+                         training=False, lr=1e-3, ops=RefOps(torch.float32), use_graph=False)
+    assert set(step.state_dict().keys()) == set(sd.keys())
+    hb = {k: batch[k] for k in ITEM_KEYS}
+    hb["labels"] = labels
+    cur, grads, want_losses = sd, [], []
+    for it in range(2):
+        sdo = {k: v.clone().requires_grad_(True) for k, v in cur.items()}
+        it1 = {k: batch[k][:B] for k in ITEM_KEYS}
+        it2 = {k: batch[k][B:] for k in ITEM_KEYS}
+        probs, loss, _, _ = Oracle(cfg, sdo).forward_alignment(labels, it1, it2)
+        loss.backward()
+        grads.append({k: v.grad for k, v in sdo.items()})
+        want_losses.append(float(loss))
+        cur = reference_update(sd, grads, [1e-3] * len(grads))
+        step.step(hb)
+        got = step.read_losses()
+        assert abs(got["loss"] - want_losses[-1]) <= 1e-5 * abs(want_losses[-1]), (it, got, want_losses)
+        assert float((step.probs - probs.detach()).abs().max()) <= 1e-5
+        check_params(step, cur)

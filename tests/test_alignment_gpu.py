@@ -55,3 +55,46 @@ def test_alignment_training_mode_runs_and_is_deterministic(ops):
     assert float((g1 - g2).abs().max()) <= 1e-4 * float(g1.abs().max())
     assert float((g1 - g3).abs().max()) > 1e-3 * float(g1.abs().max())
     assert torch.isfinite(g1).all()
+
+
+def test_alignment_step_graph_on_cuda():
+    """`AlignmentStep` (one CUDA graph per finetune step, fused AdamW): first-step loss against the reference
+    fixture, then the pair loss falls over a few steps on a fixed batch."""
+    from k3m_b200.trainer import AlignmentStep
+    from tests.util import ITEM_KEYS
+    fx = load_golden("align_tiny_mean")
+    cfg, sd, batch, labels, noise = align_case_setup(fx)
+    B, Lt, Lv, Lpv, mpv = fx["dims"]
+    step = AlignmentStep(cfg, B, len_t=Lt, len_v=Lv, len_pv=Lpv, max_num_pv=mpv, device="cuda", state_dict=sd,
+                         training=False, lr=2e-3, use_graph=True)
+    hb = {k: batch[k] for k in ITEM_KEYS}
+    hb["labels"] = labels
+    losses = []
+    for it in range(6):
+        step.step(hb)
+        losses.append(step.read_losses()["loss"])
+    assert abs(losses[0] - fx["loss"]) <= 1e-3 * abs(fx["loss"]), (losses[0], fx["loss"])
+    assert float((step.probs.cpu() - fx["probs"]).abs().max()) < 0.5          # probs of the LAST step: finite, sane
+    assert all(l == l for l in losses) and losses[-1] < losses[0], losses
+    assert step.launches_per_step > 100
+
+
+def test_alignment_base_config_runs():
+    """bert_base_6layer_6conect towers at finetune-like lengths (50 title tokens, 36 + 1 regions, 128 PV tokens;
+    `run_finetune_item_alignment.sh` uses 256 PV tokens — the attention kernels hold at most 128 x 128 per head)."""
+    from k3m_b200.config import BertConfig, K3M_BASE_6LAYER_6CONNECT
+    from k3m_b200.synth import synth_batch
+    from k3m_b200.trainer import AlignmentStep
+    from tests.util import ITEM_KEYS
+    cfg = BertConfig.from_dict(K3M_BASE_6LAYER_6CONNECT)
+    cfg.if_pre_sampling, cfg.loss_type = 1, "ce"
+    B = 4
+    step = AlignmentStep(cfg, B, len_t=50, len_v=36, len_pv=128, max_num_pv=30, device="cuda", init_seed=1,
+                         training=True, lr=1e-4, use_graph=True)
+    batch = synth_batch(cfg, 2 * B, 50, 36, 128, max_num_pv=30, seed=3)
+    hb = {k: batch[k] for k in ITEM_KEYS}
+    hb["labels"] = torch.tensor([0, 1, 1, 0])
+    for it in range(3):
+        step.step(hb)
+    out = step.read_losses()
+    assert out["loss"] == out["loss"] and 0.2 < out["loss"] < 2.0, out
