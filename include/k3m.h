@@ -78,12 +78,15 @@ int k3m_dgelu_mul(const void* dy, const void* pre, void* dx, long long n, void* 
 int k3m_mask_additive(const long long* mask, float* out, int n, void* stream);
 
 /* BertSelfAttention.forward (vilbert_k3m.py:449-464) and both directions of
- * BertBiAttention.forward (:786-824): softmax(q k^T / sqrt(d) + mask) -> dropout -> @ v.         */
+ * BertBiAttention.forward (:786-824): softmax(q k^T / sqrt(d) + mask) -> dropout -> @ v.
+ * `lse` is [2, B*H*Lq] fp32: row 0 receives the log-sum-exp of every query row (forward), row 1 is
+ * scratch of the backward pass (the per-row sum p . dp when more than 128 x 128 tokens per head
+ * make the backward a two-kernel, blocked pass).  Any Lq / Lk for d in {16, 64, 96, 128}.         */
 int k3m_attn_fwd(const void* q, int ldq, int q_off, const void* kv, int ldkv, int k_off, int v_off,
                  const float* mask, int B, int H, int Lq, int Lk, int d, void* ctx, int ldo, float* lse,
                  const void* rng, unsigned int site, float drop_p, void* stream);
 int k3m_attn_bwd(const void* dctx, int ldo, const void* q, int ldq, int q_off, const void* kv, int ldkv,
-                 int k_off, int v_off, const float* mask, const float* lse, void* dq, int lddq, void* dkv,
+                 int k_off, int v_off, const float* mask, float* lse, void* dq, int lddq, void* dkv,
                  int lddkv, int B, int H, int Lq, int Lk, int d, const void* rng, unsigned int site,
                  float drop_p, void* stream);
 

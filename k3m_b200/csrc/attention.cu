@@ -270,6 +270,60 @@ int bwd_mma(const AttnArgs& a, const bf16* dctx, int ldo, const float* lse, bf16
   K3M_ATTN_DISPATCH(launch_bwd_mma, a, dctx, ldo, lse, dq, lddq, dkv, lddkv, st);
 }
 
+// ---- long sequences: flash-style kernels, any Lq / Lk, d in {16, 64, 96, 128} --------------------------
+bool long_ok(const AttnArgs& a) { return a.d == 16 || a.d == 64 || a.d == 96 || a.d == 128; }
+
+template <int D>
+int launch_fwd_long(const AttnArgs& a, bf16* ctx, int ldo, float* lse, cudaStream_t st) {
+  const size_t smem = (size_t)(LONG_BQ + 2 * LONG_BK) * (D + 8) * 2;
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(attn_fwd_long<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    configured = true;
+  }
+  attn_fwd_long<D><<<dim3(a.H, a.B, (a.Lq + LONG_BQ - 1) / LONG_BQ), 128, smem, st>>>(a, ctx, ldo, lse);
+  return k3m_check_launch("k3m_attn_fwd");
+}
+
+template <int D>
+int launch_bwd_long(const AttnArgs& a, const bf16* dctx, int ldo, float* lse, bf16* dq, int lddq, bf16* dkv,
+                    int lddkv, cudaStream_t st) {
+  float* dsum = lse + (size_t)a.B * a.H * a.Lq;      // second half of the [2, B*H*Lq] buffer
+  const size_t smem_q = (size_t)(2 * LONG_BQ + 2 * LONG_BK) * (D + 8) * 2;
+  const size_t smem_k = (size_t)(2 * LONG_BK + 2 * LONG_BQ2) * (D + 8) * 2 + 2 * LONG_BQ2 * sizeof(float);
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(attn_bwd_long_dq<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_q);
+    cudaFuncSetAttribute(attn_bwd_long_dkv<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_k);
+    configured = true;
+  }
+  attn_bwd_long_dq<D><<<dim3(a.H, a.B, (a.Lq + LONG_BQ - 1) / LONG_BQ), 128, smem_q, st>>>(a, dctx, ldo, lse, dsum,
+                                                                                           dq, lddq);
+  int rc = k3m_check_launch("k3m_attn_bwd(dq)");
+  if (rc) return rc;
+  attn_bwd_long_dkv<D><<<dim3(a.H, a.B, (a.Lk + LONG_BK - 1) / LONG_BK), 128, smem_k, st>>>(a, dctx, ldo, lse, dsum,
+                                                                                            dkv, lddkv);
+  return k3m_check_launch("k3m_attn_bwd(dkv)");
+}
+
+#define K3M_ATTN_LONG_DISPATCH(FN, ...)                \
+  do {                                                 \
+    switch (a.d) {                                     \
+      case 16: return FN<16>(__VA_ARGS__);             \
+      case 64: return FN<64>(__VA_ARGS__);             \
+      case 96: return FN<96>(__VA_ARGS__);             \
+      default: return FN<128>(__VA_ARGS__);            \
+    }                                                  \
+  } while (0)
+
+int fwd_long(const AttnArgs& a, bf16* ctx, int ldo, float* lse, cudaStream_t st) {
+  K3M_ATTN_LONG_DISPATCH(launch_fwd_long, a, ctx, ldo, lse, st);
+}
+int bwd_long(const AttnArgs& a, const bf16* dctx, int ldo, float* lse, bf16* dq, int lddq, bf16* dkv, int lddkv,
+             cudaStream_t st) {
+  K3M_ATTN_LONG_DISPATCH(launch_bwd_long, a, dctx, ldo, lse, dq, lddq, dkv, lddkv, st);
+}
+
 }  // namespace
 
 extern "C" int k3m_attn_fwd(const void* q, int ldq, int q_off, const void* kv, int ldkv, int k_off, int v_off,
@@ -279,6 +333,7 @@ extern "C" int k3m_attn_fwd(const void* q, int ldq, int q_off, const void* kv, i
   int rc = fill_args(&a, q, ldq, q_off, kv, ldkv, k_off, v_off, mask, B, H, Lq, Lk, d, rng, site, drop_p);
   if (rc) return rc;
   if (mma_ok(a)) return fwd_mma(a, (bf16*)ctx, ldo, lse, reinterpret_cast<cudaStream_t>(stream));
+  if (long_ok(a)) return fwd_long(a, (bf16*)ctx, ldo, lse, reinterpret_cast<cudaStream_t>(stream));
   K3M_REQUIRE(Lk <= 32 * MAX_NJ, "attn_fwd: at most %d keys (Lk=%d)", 32 * MAX_NJ, Lk);
   const int lkp = (Lk + 7) & ~7;
   const size_t smem = (size_t)2 * Lk * (d + 2) * 2 + 4 + (size_t)4 * d * 4 + (size_t)4 * lkp * 4;
@@ -293,7 +348,7 @@ extern "C" int k3m_attn_fwd(const void* q, int ldq, int q_off, const void* kv, i
 }
 
 extern "C" int k3m_attn_bwd(const void* dctx, int ldo, const void* q, int ldq, int q_off, const void* kv, int ldkv,
-                            int k_off, int v_off, const float* mask, const float* lse, void* dq, int lddq, void* dkv,
+                            int k_off, int v_off, const float* mask, float* lse, void* dq, int lddq, void* dkv,
                             int lddkv, int B, int H, int Lq, int Lk, int d, const void* rng, unsigned int site,
                             float drop_p, void* stream) {
   AttnArgs a;
@@ -302,6 +357,8 @@ extern "C" int k3m_attn_bwd(const void* dctx, int ldo, const void* q, int ldq, i
   K3M_REQUIRE(lddq % 8 == 0 && lddkv % 8 == 0 && ldo % 8 == 0, "attn_bwd: strides must be multiples of 8");
   if (mma_ok(a))
     return bwd_mma(a, (const bf16*)dctx, ldo, lse, (bf16*)dq, lddq, (bf16*)dkv, lddkv, reinterpret_cast<cudaStream_t>(stream));
+  if (long_ok(a))
+    return bwd_long(a, (const bf16*)dctx, ldo, lse, (bf16*)dq, lddq, (bf16*)dkv, lddkv, reinterpret_cast<cudaStream_t>(stream));
   K3M_REQUIRE(Lk <= 128 && Lq <= 128, "attn_bwd: at most 128 x 128 tokens per head (Lq=%d Lk=%d)", Lq, Lk);
   K3M_REQUIRE(lddq % 8 == 0 && lddkv % 8 == 0 && ldo % 8 == 0, "attn_bwd: strides must be multiples of 8");
   const int lkp = (Lk + 7) & ~7;

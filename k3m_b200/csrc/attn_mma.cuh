@@ -299,3 +299,334 @@ __global__ void __launch_bounds__(256) attn_bwd_mma(AttnArgs a, const bf16* __re
     }
   }
 }
+
+// ---- long sequences (more than 128 x 128 tokens per head) ------------------------------------------------
+// The item-alignment finetune runs 256-token PV sequences (run_finetune_item_alignment.sh:40-43).  Same
+// warp-level MMA building blocks, flash-style: a CTA owns 64 queries (forward, dQ) or 64 keys (dK / dV) and
+// walks the other side in blocks through shared memory.
+//   forward : online softmax over key blocks of 64 (running max / sum per row, O rescaled per block)
+//   backward: D_i = sum_j p_ij dp_ij needs every key of row i, so the dQ kernel makes a first sweep for D
+//             (stored in the second half of the lse buffer), a second for dQ; the dK / dV kernel computes the
+//             TRANSPOSED tiles S^T = K Q^T and dP^T = V dO^T directly, so no probabilities are staged.
+__device__ __forceinline__ float drop_one(const DropSpec& dr, unsigned long long prow, int lkp, int j) {
+  uint32_t w[4];
+  rng_words(dr.rng, dr.site, (prow * (unsigned long long)lkp >> 3) + (unsigned long long)(j >> 3), w);
+  const uint32_t x = w[(j & 7) >> 1];
+  const uint32_t u = (j & 1) ? (x >> 16) : (x & 0xFFFFu);
+  return u >= dr.thresh ? dr.scale : 0.f;
+}
+
+constexpr int LONG_BQ = 64, LONG_BK = 64;
+
+template <int D>
+__global__ void __launch_bounds__(128) attn_fwd_long(AttnArgs a, bf16* __restrict__ ctx, int ldo,
+                                                     float* __restrict__ lse_out) {
+  constexpr int DS = D + 8, NKT = LONG_BK / 8;
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int h = blockIdx.x, b = blockIdx.y, q_base = blockIdx.z * LONG_BQ;
+  const int Lq = a.Lq, Lk = a.Lk;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  bf16* Qs = reinterpret_cast<bf16*>(smem);
+  bf16* Ks = Qs + (size_t)LONG_BQ * DS;
+  bf16* Vs = Ks + (size_t)LONG_BK * DS;
+  const int nq = Lq - q_base < LONG_BQ ? Lq - q_base : LONG_BQ;
+  load_tile_z<D, DS>(Qs, a.q + (size_t)(b * Lq + q_base) * a.ldq + a.q_off + h * D, a.ldq, nq, LONG_BQ);
+  const int g = lane >> 2, q = lane & 3, i0 = warp * 16;
+  const int r0 = q_base + i0 + g, r1 = r0 + 8;                      // query rows of this thread
+  const unsigned long long prow0 = (unsigned long long)(b * a.H + h) * Lq + r0, prow1 = prow0 + 8;
+  const float* mrow = a.mask + (size_t)b * Lk;
+  const int lkp = (Lk + 7) & ~7;
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+  float o[D / 8][4];
+#pragma unroll
+  for (int c = 0; c < D / 8; ++c) o[c][0] = o[c][1] = o[c][2] = o[c][3] = 0.f;
+  for (int k_base = 0; k_base < Lk; k_base += LONG_BK) {
+    const int nk = Lk - k_base < LONG_BK ? Lk - k_base : LONG_BK;
+    __syncthreads();
+    load_tile_z<D, DS>(Ks, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.k_off + h * D, a.ldkv, nk, LONG_BK);
+    load_tile_z<D, DS>(Vs, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.v_off + h * D, a.ldkv, nk, LONG_BK);
+    __syncthreads();
+    float s[NKT][4];
+#pragma unroll
+    for (int t = 0; t < NKT; ++t) s[t][0] = s[t][1] = s[t][2] = s[t][3] = 0.f;
+    qk_mma<D, DS, NKT>(s, Qs, i0, Ks, lane);
+    float bm0 = -INFINITY, bm1 = -INFINITY;
+#pragma unroll
+    for (int t = 0; t < NKT; ++t) {
+      const int j = k_base + t * 8 + 2 * q;
+      const float ma = j < Lk ? mrow[j] : -INFINITY, mb = j + 1 < Lk ? mrow[j + 1] : -INFINITY;
+      s[t][0] = fmaf(s[t][0], a.scale, ma); s[t][1] = fmaf(s[t][1], a.scale, mb);
+      s[t][2] = fmaf(s[t][2], a.scale, ma); s[t][3] = fmaf(s[t][3], a.scale, mb);
+      bm0 = fmaxf(bm0, fmaxf(s[t][0], s[t][1]));
+      bm1 = fmaxf(bm1, fmaxf(s[t][2], s[t][3]));
+    }
+    bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 1)); bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
+    bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1)); bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
+    const float n0 = fmaxf(m0, bm0), n1 = fmaxf(m1, bm1);           // finite: every block holds a valid key
+    const float c0 = __expf(m0 - n0), c1 = __expf(m1 - n1);         // exp(-inf) = 0 on the first block
+    m0 = n0; m1 = n1;
+    float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+    for (int t = 0; t < NKT; ++t) {
+      s[t][0] = __expf(s[t][0] - n0); s[t][1] = __expf(s[t][1] - n0);
+      s[t][2] = __expf(s[t][2] - n1); s[t][3] = __expf(s[t][3] - n1);
+      sum0 += s[t][0] + s[t][1];
+      sum1 += s[t][2] + s[t][3];
+    }
+    sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+    sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+    l0 = l0 * c0 + sum0;
+    l1 = l1 * c1 + sum1;
+#pragma unroll
+    for (int c = 0; c < D / 8; ++c) { o[c][0] *= c0; o[c][1] *= c0; o[c][2] *= c1; o[c][3] *= c1; }
+    if (a.drop.thresh) {
+#pragma unroll
+      for (int t = 0; t < NKT; ++t) {
+        if (k_base + t * 8 < Lk) {
+          float m00 = 1.f, m01 = 1.f, m10 = 1.f, m11 = 1.f;
+          if (r0 < Lq) drop_pair(a.drop, prow0, lkp, (k_base >> 3) + t, q, m00, m01);
+          if (r1 < Lq) drop_pair(a.drop, prow1, lkp, (k_base >> 3) + t, q, m10, m11);
+          s[t][0] *= m00; s[t][1] *= m01; s[t][2] *= m10; s[t][3] *= m11;
+        }
+      }
+    }
+#pragma unroll
+    for (int kt = 0; kt < NKT / 2; ++kt) {
+      uint32_t pf[4];
+      pf[0] = pack_bf16(s[2 * kt][0], s[2 * kt][1]);
+      pf[1] = pack_bf16(s[2 * kt][2], s[2 * kt][3]);
+      pf[2] = pack_bf16(s[2 * kt + 1][0], s[2 * kt + 1][1]);
+      pf[3] = pack_bf16(s[2 * kt + 1][2], s[2 * kt + 1][3]);
+#pragma unroll
+      for (int c = 0; c < D / 8; c += 2) {
+        uint32_t vf[4];
+        ldsm_x4_t(vf, Vs + (size_t)(kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * DS + c * 8 + (lane >> 4) * 8);
+        mma16816(o[c], pf, vf[0], vf[1]);
+        mma16816(o[c + 1], pf, vf[2], vf[3]);
+      }
+    }
+  }
+  if (q == 0) {
+    if (r0 < Lq) lse_out[prow0] = m0 + __logf(l0);
+    if (r1 < Lq) lse_out[prow1] = m1 + __logf(l1);
+  }
+  const float inv0 = 1.0f / l0, inv1 = 1.0f / l1;
+  bf16* o0 = ctx + (size_t)(b * Lq + r0) * ldo + h * D + 2 * q;
+  bf16* o1 = ctx + (size_t)(b * Lq + r1) * ldo + h * D + 2 * q;
+#pragma unroll
+  for (int c = 0; c < D / 8; ++c) {
+    if (r0 < Lq) *reinterpret_cast<uint32_t*>(o0 + c * 8) = pack_bf16(o[c][0] * inv0, o[c][1] * inv0);
+    if (r1 < Lq) *reinterpret_cast<uint32_t*>(o1 + c * 8) = pack_bf16(o[c][2] * inv1, o[c][3] * inv1);
+  }
+}
+
+// dQ for 64 queries of one (b, h); sweep 0 reduces D_i over all keys and stores it at dsum[prow] for
+// the dK / dV kernel, sweep 1 forms dS = P (dP - D) block by block and accumulates dQ = scale dS K.
+template <int D>
+__global__ void __launch_bounds__(128) attn_bwd_long_dq(AttnArgs a, const bf16* __restrict__ dctx, int ldo,
+                                                        const float* __restrict__ lse, float* __restrict__ dsum,
+                                                        bf16* __restrict__ dq, int lddq) {
+  constexpr int DS = D + 8, NKT = LONG_BK / 8;
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int h = blockIdx.x, b = blockIdx.y, q_base = blockIdx.z * LONG_BQ;
+  const int Lq = a.Lq, Lk = a.Lk;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  bf16* Qs = reinterpret_cast<bf16*>(smem);
+  bf16* dOs = Qs + (size_t)LONG_BQ * DS;
+  bf16* Ks = dOs + (size_t)LONG_BQ * DS;
+  bf16* Vs = Ks + (size_t)LONG_BK * DS;
+  const int nq = Lq - q_base < LONG_BQ ? Lq - q_base : LONG_BQ;
+  load_tile_z<D, DS>(Qs, a.q + (size_t)(b * Lq + q_base) * a.ldq + a.q_off + h * D, a.ldq, nq, LONG_BQ);
+  load_tile_z<D, DS>(dOs, dctx + (size_t)(b * Lq + q_base) * ldo + h * D, ldo, nq, LONG_BQ);
+  const int g = lane >> 2, q = lane & 3, i0 = warp * 16;
+  const int r0 = q_base + i0 + g, r1 = r0 + 8;
+  const bool ok0 = r0 < Lq, ok1 = r1 < Lq;
+  const unsigned long long prow0 = (unsigned long long)(b * a.H + h) * Lq + r0, prow1 = prow0 + 8;
+  const float ls0 = ok0 ? lse[prow0] : 0.f, ls1 = ok1 ? lse[prow1] : 0.f;
+  const float* mrow = a.mask + (size_t)b * Lk;
+  const int lkp = (Lk + 7) & ~7;
+  float D0 = 0.f, D1 = 0.f;
+  float o[D / 8][4];
+#pragma unroll
+  for (int c = 0; c < D / 8; ++c) o[c][0] = o[c][1] = o[c][2] = o[c][3] = 0.f;
+  for (int sweep = 0; sweep < 2; ++sweep) {
+    for (int k_base = 0; k_base < Lk; k_base += LONG_BK) {
+      const int nk = Lk - k_base < LONG_BK ? Lk - k_base : LONG_BK;
+      __syncthreads();
+      load_tile_z<D, DS>(Ks, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.k_off + h * D, a.ldkv, nk, LONG_BK);
+      load_tile_z<D, DS>(Vs, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.v_off + h * D, a.ldkv, nk, LONG_BK);
+      __syncthreads();
+      float s[NKT][4], dp[NKT][4];
+#pragma unroll
+      for (int t = 0; t < NKT; ++t) {
+        s[t][0] = s[t][1] = s[t][2] = s[t][3] = 0.f;
+        dp[t][0] = dp[t][1] = dp[t][2] = dp[t][3] = 0.f;
+      }
+      qk_mma<D, DS, NKT>(s, Qs, i0, Ks, lane);
+      qk_mma<D, DS, NKT>(dp, dOs, i0, Vs, lane);
+#pragma unroll
+      for (int t = 0; t < NKT; ++t) {
+        const int j = k_base + t * 8 + 2 * q;
+        const bool v0 = j < Lk, v1 = j + 1 < Lk;
+        const float ma = v0 ? mrow[j] : 0.f, mb = v1 ? mrow[j + 1] : 0.f;
+        const float p00 = (v0 && ok0) ? __expf(fmaf(s[t][0], a.scale, ma) - ls0) : 0.f;
+        const float p01 = (v1 && ok0) ? __expf(fmaf(s[t][1], a.scale, mb) - ls0) : 0.f;
+        const float p10 = (v0 && ok1) ? __expf(fmaf(s[t][2], a.scale, ma) - ls1) : 0.f;
+        const float p11 = (v1 && ok1) ? __expf(fmaf(s[t][3], a.scale, mb) - ls1) : 0.f;
+        float m00 = 1.f, m01 = 1.f, m10 = 1.f, m11 = 1.f;
+        if (a.drop.thresh && k_base + t * 8 < Lk) {
+          if (ok0) drop_pair(a.drop, prow0, lkp, (k_base >> 3) + t, q, m00, m01);
+          if (ok1) drop_pair(a.drop, prow1, lkp, (k_base >> 3) + t, q, m10, m11);
+        }
+        dp[t][0] *= m00; dp[t][1] *= m01; dp[t][2] *= m10; dp[t][3] *= m11;
+        if (sweep == 0) {
+          D0 += p00 * dp[t][0] + p01 * dp[t][1];
+          D1 += p10 * dp[t][2] + p11 * dp[t][3];
+        } else {
+          s[t][0] = p00 * (dp[t][0] - D0); s[t][1] = p01 * (dp[t][1] - D0);
+          s[t][2] = p10 * (dp[t][2] - D1); s[t][3] = p11 * (dp[t][3] - D1);
+        }
+      }
+      if (sweep == 1) {
+#pragma unroll
+        for (int kt = 0; kt < NKT / 2; ++kt) {
+          uint32_t af[4];
+          af[0] = pack_bf16(s[2 * kt][0], s[2 * kt][1]);
+          af[1] = pack_bf16(s[2 * kt][2], s[2 * kt][3]);
+          af[2] = pack_bf16(s[2 * kt + 1][0], s[2 * kt + 1][1]);
+          af[3] = pack_bf16(s[2 * kt + 1][2], s[2 * kt + 1][3]);
+#pragma unroll
+          for (int c = 0; c < D / 8; c += 2) {
+            uint32_t kf[4];
+            ldsm_x4_t(kf, Ks + (size_t)(kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * DS + c * 8 + (lane >> 4) * 8);
+            mma16816(o[c], af, kf[0], kf[1]);
+            mma16816(o[c + 1], af, kf[2], kf[3]);
+          }
+        }
+      }
+    }
+    if (sweep == 0) {
+      D0 += __shfl_xor_sync(0xffffffffu, D0, 1); D0 += __shfl_xor_sync(0xffffffffu, D0, 2);
+      D1 += __shfl_xor_sync(0xffffffffu, D1, 1); D1 += __shfl_xor_sync(0xffffffffu, D1, 2);
+      if (q == 0) {
+        if (ok0) dsum[prow0] = D0;
+        if (ok1) dsum[prow1] = D1;
+      }
+    }
+  }
+  bf16* q0 = dq + (size_t)(b * Lq + r0) * lddq + a.q_off + h * D + 2 * q;
+  bf16* q1 = dq + (size_t)(b * Lq + r1) * lddq + a.q_off + h * D + 2 * q;
+#pragma unroll
+  for (int c = 0; c < D / 8; ++c) {
+    if (ok0) *reinterpret_cast<uint32_t*>(q0 + c * 8) = pack_bf16(o[c][0] * a.scale, o[c][1] * a.scale);
+    if (ok1) *reinterpret_cast<uint32_t*>(q1 + c * 8) = pack_bf16(o[c][2] * a.scale, o[c][3] * a.scale);
+  }
+}
+
+// dK / dV for 64 keys of one (b, h): a warp owns 16 keys and walks the queries in blocks of 32, computing
+// S^T (keys x queries) and dP^T on the tensor cores so the accumulator fragments are already the A
+// operands of dV += P^T dO and dK += dS^T Q.
+constexpr int LONG_BQ2 = 32;
+template <int D>
+__global__ void __launch_bounds__(128) attn_bwd_long_dkv(AttnArgs a, const bf16* __restrict__ dctx, int ldo,
+                                                         const float* __restrict__ lse,
+                                                         const float* __restrict__ dsum, bf16* __restrict__ dkv,
+                                                         int lddkv) {
+  constexpr int DS = D + 8, NQT = LONG_BQ2 / 8;
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int h = blockIdx.x, b = blockIdx.y, k_base = blockIdx.z * LONG_BK;
+  const int Lq = a.Lq, Lk = a.Lk;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  bf16* Ks = reinterpret_cast<bf16*>(smem);
+  bf16* Vs = Ks + (size_t)LONG_BK * DS;
+  bf16* Qs = Vs + (size_t)LONG_BK * DS;
+  bf16* dOs = Qs + (size_t)LONG_BQ2 * DS;
+  float* lse_s = reinterpret_cast<float*>(dOs + (size_t)LONG_BQ2 * DS);
+  float* d_s = lse_s + LONG_BQ2;
+  const int nk = Lk - k_base < LONG_BK ? Lk - k_base : LONG_BK;
+  load_tile_z<D, DS>(Ks, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.k_off + h * D, a.ldkv, nk, LONG_BK);
+  load_tile_z<D, DS>(Vs, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.v_off + h * D, a.ldkv, nk, LONG_BK);
+  const int g = lane >> 2, q = lane & 3, j0 = warp * 16;
+  const int jr0 = k_base + j0 + g, jr1 = jr0 + 8;                   // key rows of this thread
+  const float* mrow = a.mask + (size_t)b * Lk;
+  const float mk0 = jr0 < Lk ? mrow[jr0] : 0.f, mk1 = jr1 < Lk ? mrow[jr1] : 0.f;
+  const int lkp = (Lk + 7) & ~7;
+  const unsigned long long pbase = (unsigned long long)(b * a.H + h) * Lq;
+  float dv[D / 8][4], dk[D / 8][4];
+#pragma unroll
+  for (int c = 0; c < D / 8; ++c) {
+    dv[c][0] = dv[c][1] = dv[c][2] = dv[c][3] = 0.f;
+    dk[c][0] = dk[c][1] = dk[c][2] = dk[c][3] = 0.f;
+  }
+  for (int q_base = 0; q_base < Lq; q_base += LONG_BQ2) {
+    const int nq = Lq - q_base < LONG_BQ2 ? Lq - q_base : LONG_BQ2;
+    __syncthreads();
+    load_tile_z<D, DS>(Qs, a.q + (size_t)(b * Lq + q_base) * a.ldq + a.q_off + h * D, a.ldq, nq, LONG_BQ2);
+    load_tile_z<D, DS>(dOs, dctx + (size_t)(b * Lq + q_base) * ldo + h * D, ldo, nq, LONG_BQ2);
+    if (threadIdx.x < LONG_BQ2) {
+      const bool ok = (int)threadIdx.x < nq;
+      lse_s[threadIdx.x] = ok ? lse[pbase + q_base + threadIdx.x] : 0.f;
+      d_s[threadIdx.x] = ok ? dsum[pbase + q_base + threadIdx.x] : 0.f;
+    }
+    __syncthreads();
+    float s[NQT][4], dp[NQT][4];
+#pragma unroll
+    for (int t = 0; t < NQT; ++t) {
+      s[t][0] = s[t][1] = s[t][2] = s[t][3] = 0.f;
+      dp[t][0] = dp[t][1] = dp[t][2] = dp[t][3] = 0.f;
+    }
+    qk_mma<D, DS, NQT>(s, Ks, j0, Qs, lane);       // rows = keys, columns = queries
+    qk_mma<D, DS, NQT>(dp, Vs, j0, dOs, lane);
+#pragma unroll
+    for (int t = 0; t < NQT; ++t) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int il = t * 8 + 2 * q + (e & 1), i = q_base + il;
+        const int j = (e & 2) ? jr1 : jr0;
+        const bool ok = i < Lq && j < Lk;
+        const float p = ok ? __expf(fmaf(s[t][e], a.scale, (e & 2) ? mk1 : mk0) - lse_s[il]) : 0.f;
+        float m = 1.f;
+        if (a.drop.thresh && ok) m = drop_one(a.drop, pbase + i, lkp, j);
+        const float dpm = dp[t][e] * m;
+        s[t][e] = p * m;                              // dropped probability (transposed)
+        dp[t][e] = p * (dpm - d_s[il]);               // dS (transposed)
+      }
+    }
+#pragma unroll
+    for (int kt = 0; kt < NQT / 2; ++kt) {
+      uint32_t pa[4], sa[4];
+      pa[0] = pack_bf16(s[2 * kt][0], s[2 * kt][1]);
+      pa[1] = pack_bf16(s[2 * kt][2], s[2 * kt][3]);
+      pa[2] = pack_bf16(s[2 * kt + 1][0], s[2 * kt + 1][1]);
+      pa[3] = pack_bf16(s[2 * kt + 1][2], s[2 * kt + 1][3]);
+      sa[0] = pack_bf16(dp[2 * kt][0], dp[2 * kt][1]);
+      sa[1] = pack_bf16(dp[2 * kt][2], dp[2 * kt][3]);
+      sa[2] = pack_bf16(dp[2 * kt + 1][0], dp[2 * kt + 1][1]);
+      sa[3] = pack_bf16(dp[2 * kt + 1][2], dp[2 * kt + 1][3]);
+#pragma unroll
+      for (int c = 0; c < D / 8; c += 2) {
+        uint32_t of[4], qf[4];
+        const size_t boff = (size_t)(kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * DS + c * 8 + (lane >> 4) * 8;
+        ldsm_x4_t(of, dOs + boff);
+        ldsm_x4_t(qf, Qs + boff);
+        mma16816(dv[c], pa, of[0], of[1]);
+        mma16816(dv[c + 1], pa, of[2], of[3]);
+        mma16816(dk[c], sa, qf[0], qf[1]);
+        mma16816(dk[c + 1], sa, qf[2], qf[3]);
+      }
+    }
+  }
+  bf16* k0 = dkv + (size_t)(b * Lk + jr0) * lddkv + h * D + 2 * q;
+  bf16* k1 = dkv + (size_t)(b * Lk + jr1) * lddkv + h * D + 2 * q;
+#pragma unroll
+  for (int c = 0; c < D / 8; ++c) {
+    if (jr0 < Lk) {
+      *reinterpret_cast<uint32_t*>(k0 + a.k_off + c * 8) = pack_bf16(dk[c][0] * a.scale, dk[c][1] * a.scale);
+      *reinterpret_cast<uint32_t*>(k0 + a.v_off + c * 8) = pack_bf16(dv[c][0], dv[c][1]);
+    }
+    if (jr1 < Lk) {
+      *reinterpret_cast<uint32_t*>(k1 + a.k_off + c * 8) = pack_bf16(dk[c][2] * a.scale, dk[c][3] * a.scale);
+      *reinterpret_cast<uint32_t*>(k1 + a.v_off + c * 8) = pack_bf16(dv[c][2], dv[c][3]);
+    }
+  }
+}

@@ -209,7 +209,7 @@ class CudaOps(object):
                  out=None):
         if out is None:
             out = torch.empty(B * Lq, H * d, dtype=self.adt, device=qbuf.device)
-        lse = torch.empty(B * H * Lq, dtype=torch.float32, device=qbuf.device)
+        lse = torch.empty(2, B * H * Lq, dtype=torch.float32, device=qbuf.device)   # row 1: backward scratch
         r, s, p = self._drop(drop, rng)
         self._call("k3m_attn_fwd", _p(qbuf), _i(_ld(qbuf)), _i(q_off), _p(kvbuf), _i(_ld(kvbuf)), _i(k_off),
                    _i(v_off), _p(mask_add), _i(B), _i(H), _i(Lq), _i(Lk), _i(d), _p(out), _i(_ld(out)),

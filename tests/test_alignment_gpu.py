@@ -80,8 +80,9 @@ def test_alignment_step_graph_on_cuda():
 
 
 def test_alignment_base_config_runs():
-    """bert_base_6layer_6conect towers at finetune-like lengths (50 title tokens, 36 + 1 regions, 128 PV tokens;
-    `run_finetune_item_alignment.sh` uses 256 PV tokens — the attention kernels hold at most 128 x 128 per head)."""
+    """bert_base_6layer_6conect towers at the finetune script's lengths (50 title tokens, 36 + 1 regions, 256 PV
+    tokens: run_finetune_item_alignment.sh:40-43) — PV self-attention and both PV co-attentions take the blocked
+    attention kernels."""
     from k3m_b200.config import BertConfig, K3M_BASE_6LAYER_6CONNECT
     from k3m_b200.synth import synth_batch
     from k3m_b200.trainer import AlignmentStep
@@ -89,9 +90,9 @@ def test_alignment_base_config_runs():
     cfg = BertConfig.from_dict(K3M_BASE_6LAYER_6CONNECT)
     cfg.if_pre_sampling, cfg.loss_type = 1, "ce"
     B = 4
-    step = AlignmentStep(cfg, B, len_t=50, len_v=36, len_pv=128, max_num_pv=30, device="cuda", init_seed=1,
+    step = AlignmentStep(cfg, B, len_t=50, len_v=36, len_pv=256, max_num_pv=30, device="cuda", init_seed=1,
                          training=True, lr=1e-4, use_graph=True)
-    batch = synth_batch(cfg, 2 * B, 50, 36, 128, max_num_pv=30, seed=3)
+    batch = synth_batch(cfg, 2 * B, 50, 36, 256, max_num_pv=30, seed=3)
     hb = {k: batch[k] for k in ITEM_KEYS}
     hb["labels"] = torch.tensor([0, 1, 1, 0])
     for it in range(3):

@@ -69,9 +69,11 @@ def test_alignment_class_on_cuda_matches_reference():
     assert not errs, errs[:10]
 
 
-def test_long_context_dims_run_and_match_restatement():
-    """BASELINE configs[3] geometry (128-token titles, 100 regions + 1, 128 PV tokens) on the tiny model:
-    CUDA kernels against the bf16-storage restatement on the same device."""
+@pytest.mark.parametrize("lens", [(128, 100, 128), (50, 36, 256), (200, 140, 256)])
+def test_long_context_dims_run_and_match_restatement(lens):
+    """BASELINE configs[3] geometry (128-token titles, 100 regions + 1, 128 PV tokens), the finetune scripts'
+    256 PV tokens, and every stream beyond 128 tokens (the blocked attention kernels in all nine attention
+    sites) on the tiny model: CUDA kernels against the bf16-storage restatement on the same device."""
     from k3m_b200.config import BertConfig, K3M_TINY
     from k3m_b200.layout import param_spec
     from k3m_b200.ops import CudaOps
@@ -80,9 +82,9 @@ def test_long_context_dims_run_and_match_restatement():
     from tests.util import run_engine
     cfg = BertConfig.from_dict(K3M_TINY)
     cfg.if_pre_sampling, cfg.margin, cfg.num_negative_pv = 0, 1.0, 4
-    cfg.max_position_embeddings = 128
+    cfg.max_position_embeddings = 256
     sd = synth_state_dict(param_spec(cfg), seed=5)
-    batch = synth_batch(cfg, 3, 128, 100, 128, max_num_pv=8, seed=31)
+    batch = synth_batch(cfg, 3, lens[0], lens[1], lens[2], max_num_pv=8, seed=31)
     out, L, g = run_engine(cfg, sd, batch, None, CudaOps("cuda"), "cuda", torch.bfloat16, 7)
     outr, _, gr = run_engine(cfg, sd, batch, None, RefOps(torch.bfloat16), "cuda", torch.bfloat16, 7)
     for k in ("loss_t", "loss_v", "loss_pv", "loss_lpm"):
