@@ -222,10 +222,10 @@ int fill_args(AttnArgs* a, const void* q, int ldq, int q_off, const void* kv, in
 template <int D, int NKT>
 int launch_fwd_mma(const AttnArgs& a, bf16* ctx, int ldo, float* lse, cudaStream_t st) {
   const int nw = (a.Lq + 15) / 16;
-  const size_t smem = (size_t)(nw * 16 + 2 * NKT * 8) * (D + 8) * 2;
+  const size_t smem = (size_t)(nw * 16 + 2 * NKT * 8) * (D + 8) * 2 + nw * 16 * 16;    // + dropout keep-bytes
   static bool configured = false;
   if (!configured) {
-    cudaFuncSetAttribute(attn_fwd_mma<D, NKT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 16 * 3 * (D + 8) * 2);
+    cudaFuncSetAttribute(attn_fwd_mma<D, NKT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 16 * 3 * (D + 8) * 2 + 8 * 16 * 16);
     configured = true;
   }
   attn_fwd_mma<D, NKT><<<dim3(a.H, a.B), nw * 32, smem, st>>>(a, ctx, ldo, lse);
@@ -236,11 +236,11 @@ template <int D, int NKT>
 int launch_bwd_mma(const AttnArgs& a, const bf16* dctx, int ldo, const float* lse, bf16* dq, int lddq, bf16* dkv,
                    int lddkv, cudaStream_t st) {
   const int nw = (a.Lq + 15) / 16;
-  const size_t smem = (size_t)2 * (nw * 16 + NKT * 8) * (D + 8) * 2 + (size_t)2 * nw * 16 * (NKT * 8 + 8) * 2;
+  const size_t smem = (size_t)2 * (nw * 16 + NKT * 8) * (D + 8) * 2 + (size_t)2 * nw * 16 * (NKT * 8 + 8) * 2 + nw * 16 * 16;
   static bool configured = false;
   if (!configured) {
     cudaFuncSetAttribute(attn_bwd_mma<D, NKT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         2 * (128 + NKT * 8) * (D + 8) * 2 + 2 * 128 * (NKT * 8 + 8) * 2);
+                         2 * (128 + NKT * 8) * (D + 8) * 2 + 2 * 128 * (NKT * 8 + 8) * 2 + 8 * 16 * 16);
     configured = true;
   }
   attn_bwd_mma<D, NKT><<<dim3(a.H, a.B), nw * 32, smem, st>>>(a, dctx, ldo, lse, dq, lddq, dkv, lddkv);
@@ -275,7 +275,7 @@ bool long_ok(const AttnArgs& a) { return a.d == 16 || a.d == 64 || a.d == 96 || 
 
 template <int D>
 int launch_fwd_long(const AttnArgs& a, bf16* ctx, int ldo, float* lse, cudaStream_t st) {
-  const size_t smem = (size_t)(LONG_BQ + 2 * LONG_BK) * (D + 8) * 2;
+  const size_t smem = (size_t)(LONG_BQ + 4 * LONG_BK) * (D + 8) * 2 + 4 * 16 * 8;   // Q + two (K, V) buffers + keep-bytes
   static bool configured = false;
   if (!configured) {
     cudaFuncSetAttribute(attn_fwd_long<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -289,8 +289,9 @@ template <int D>
 int launch_bwd_long(const AttnArgs& a, const bf16* dctx, int ldo, float* lse, bf16* dq, int lddq, bf16* dkv,
                     int lddkv, cudaStream_t st) {
   float* dsum = lse + (size_t)a.B * a.H * a.Lq;      // second half of the [2, B*H*Lq] buffer
-  const size_t smem_q = (size_t)(2 * LONG_BQ + 2 * LONG_BK) * (D + 8) * 2;
-  const size_t smem_k = (size_t)(2 * LONG_BK + 2 * LONG_BQ2) * (D + 8) * 2 + 2 * LONG_BQ2 * sizeof(float);
+  const size_t smem_q = (size_t)(2 * LONG_BQ + 4 * LONG_BK) * (D + 8) * 2 + 4 * 16 * 8;   // Q, dO + two (K, V) + keep-bytes
+  const size_t smem_k = (size_t)(2 * LONG_BK + 4 * LONG_BQ2) * (D + 8) * 2 + 4 * LONG_BQ2 * sizeof(float) +
+                        2 * LONG_BQ2 * 8;                                                  // K, V + two (Q, dO, lse, D, keep-bytes)
   static bool configured = false;
   if (!configured) {
     cudaFuncSetAttribute(attn_bwd_long_dq<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_q);

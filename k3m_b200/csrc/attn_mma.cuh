@@ -57,14 +57,53 @@ __device__ __forceinline__ void qk_mma(float (*acc)[4], const bf16* As, int i0, 
   }
 }
 
-// dropout multipliers of one accumulator tile: row `prow`, key tile t, this thread's 2 columns (2q, 2q+1)
-__device__ __forceinline__ void drop_pair(const DropSpec& dr, unsigned long long prow, int lkp, int t, int q,
-                                          float& m0, float& m1) {
+// ---- dropout masks --------------------------------------------------------------------------------------
+// One Philox call yields the 8 x 16 random bits of one 8-key tile of one dropout row (element (row, j):
+// counter (row * lkp + j) >> 3, see common.cuh).  In the accumulator layout those 8 elements sit in the 4
+// lanes of a quad, so instead of every lane running the generator for its 2 columns the warp computes each
+// (row, tile) ONCE, keeps the 8 keep-bits as a byte in shared memory and the lanes pick their bits.
+__device__ __forceinline__ uint32_t drop_tile_bits(const DropSpec& dr, unsigned long long prow, int lkp, int t) {
   uint32_t w[4];
   rng_words(dr.rng, dr.site, (prow * (unsigned long long)lkp >> 3) + (unsigned long long)t, w);
-  const uint32_t x = w[q];
-  m0 = (x & 0xFFFFu) >= dr.thresh ? dr.scale : 0.f;
-  m1 = (x >> 16) >= dr.thresh ? dr.scale : 0.f;
+  uint32_t m = 0;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const uint32_t u = (w[e >> 1] >> (16 * (e & 1))) & 0xFFFFu;
+    m |= (u >= dr.thresh ? 1u : 0u) << e;
+  }
+  return m;
+}
+
+// keep-bytes of a warp's 16 dropout rows x NT key tiles -> mw[16][NTP]; rows / tiles beyond the problem get 0xFF
+template <int NT, int NTP>
+__device__ __forceinline__ void warp_drop_bits(uint8_t* mw, const DropSpec& dr, unsigned long long prow_first,
+                                               int rows_valid, int lkp, int tile0, int tiles_valid, int lane) {
+  for (int c = lane; c < 16 * NT; c += 32) {
+    const int r = c / NT, t = c % NT;
+    uint32_t bits = 0xFFu;
+    if (r < rows_valid && t < tiles_valid) bits = drop_tile_bits(dr, prow_first + r, lkp, tile0 + t);
+    mw[r * NTP + t] = (uint8_t)bits;
+  }
+  __syncwarp();
+}
+
+// the keep-bytes of one row (NTP bytes, 8-byte aligned) as 32-bit words
+template <int NTP>
+__device__ __forceinline__ void load_drop_row(uint32_t (&bw)[NTP / 4], const uint8_t* row) {
+  const uint2* p = reinterpret_cast<const uint2*>(row);
+#pragma unroll
+  for (int i = 0; i < NTP / 8; ++i) {
+    const uint2 v = p[i];
+    bw[2 * i] = v.x; bw[2 * i + 1] = v.y;
+  }
+}
+// multipliers of this thread's columns (2q, 2q + 1) of key tile t
+template <int NTP>
+__device__ __forceinline__ void drop_pair(const uint32_t (&bw)[NTP / 4], int t, int q, float scale, float& m0,
+                                          float& m1) {
+  const uint32_t bits = bw[t >> 2] >> (8 * (t & 3) + 2 * q);
+  m0 = (bits & 1u) ? scale : 0.f;
+  m1 = (bits & 2u) ? scale : 0.f;
 }
 
 template <int D, int NKT>
@@ -78,11 +117,16 @@ __global__ void __launch_bounds__(256) attn_fwd_mma(AttnArgs a, bf16* __restrict
   bf16* Qs = reinterpret_cast<bf16*>(smem);
   bf16* Ks = Qs + (size_t)LQP * DS;
   bf16* Vs = Ks + (size_t)LKP * DS;
+  constexpr int NTP = NKT <= 8 ? 8 : 16;
+  uint8_t* mw = reinterpret_cast<uint8_t*>(Vs + (size_t)LKP * DS) + warp * 16 * NTP;
   load_tile_z<D, DS>(Qs, a.q + (size_t)b * Lq * a.ldq + a.q_off + h * D, a.ldq, Lq, LQP);
   load_tile_z<D, DS>(Ks, a.kv + (size_t)b * Lk * a.ldkv + a.k_off + h * D, a.ldkv, Lk, LKP);
   load_tile_z<D, DS>(Vs, a.kv + (size_t)b * Lk * a.ldkv + a.v_off + h * D, a.ldkv, Lk, LKP);
-  __syncthreads();
   const int g = lane >> 2, q = lane & 3, i0 = warp * 16;
+  const int lkp = (Lk + 7) & ~7;
+  if (a.drop.thresh)     // while the tile loads are in flight
+    warp_drop_bits<NKT, NTP>(mw, a.drop, (unsigned long long)(b * a.H + h) * Lq + i0, Lq - i0, lkp, 0, lkp >> 3, lane);
+  __syncthreads();
   float s[NKT][4];
 #pragma unroll
   for (int t = 0; t < NKT; ++t) s[t][0] = s[t][1] = s[t][2] = s[t][3] = 0.f;
@@ -117,13 +161,17 @@ __global__ void __launch_bounds__(256) attn_fwd_mma(AttnArgs a, bf16* __restrict
     if (r1 < Lq) lse_out[prow1] = mx1 + __logf(sum1);
   }
   const float inv0 = 1.0f / sum0, inv1 = 1.0f / sum1;
-  const int lkp = (Lk + 7) & ~7;
+  uint32_t bw0[NTP / 4], bw1[NTP / 4];
+  if (a.drop.thresh) {
+    load_drop_row<NTP>(bw0, mw + g * NTP);
+    load_drop_row<NTP>(bw1, mw + (g + 8) * NTP);
+  }
 #pragma unroll
   for (int t = 0; t < NKT; ++t) {
     float m00 = 1.f, m01 = 1.f, m10 = 1.f, m11 = 1.f;
-    if (a.drop.thresh && t * 8 < Lk) {
-      if (r0 < Lq) drop_pair(a.drop, prow0, lkp, t, q, m00, m01);
-      if (r1 < Lq) drop_pair(a.drop, prow1, lkp, t, q, m10, m11);
+    if (a.drop.thresh) {
+      drop_pair<NTP>(bw0, t, q, a.drop.scale, m00, m01);
+      drop_pair<NTP>(bw1, t, q, a.drop.scale, m10, m11);
     }
     s[t][0] *= inv0 * m00; s[t][1] *= inv0 * m01;
     s[t][2] *= inv1 * m10; s[t][3] *= inv1 * m11;
@@ -177,13 +225,17 @@ __global__ void __launch_bounds__(256) attn_bwd_mma(AttnArgs a, const bf16* __re
   bf16* Vs = Ks + (size_t)LKP * DS;
   bf16* Ps = Vs + (size_t)LKP * DS;      // [LQP][PS]  dropped probabilities
   bf16* Ss = Ps + (size_t)LQP * PS;      // [LQP][PS]  dS
+  constexpr int NTP = NKT <= 8 ? 8 : 16;
+  uint8_t* mw = reinterpret_cast<uint8_t*>(Ss + (size_t)LQP * PS) + warp * 16 * NTP;
   load_tile_z<D, DS>(Qs, a.q + (size_t)b * Lq * a.ldq + a.q_off + h * D, a.ldq, Lq, LQP);
   load_tile_z<D, DS>(dOs, dctx + (size_t)b * Lq * ldo + h * D, ldo, Lq, LQP);
   load_tile_z<D, DS>(Ks, a.kv + (size_t)b * Lk * a.ldkv + a.k_off + h * D, a.ldkv, Lk, LKP);
   load_tile_z<D, DS>(Vs, a.kv + (size_t)b * Lk * a.ldkv + a.v_off + h * D, a.ldkv, Lk, LKP);
-  __syncthreads();
   const int g = lane >> 2, q = lane & 3, i0 = warp * 16;
   const int lkp = (Lk + 7) & ~7;
+  if (a.drop.thresh)
+    warp_drop_bits<NKT, NTP>(mw, a.drop, (unsigned long long)(b * a.H + h) * Lq + i0, Lq - i0, lkp, 0, lkp >> 3, lane);
+  __syncthreads();
   {
     float s[NKT][4], dp[NKT][4];
 #pragma unroll
@@ -199,6 +251,11 @@ __global__ void __launch_bounds__(256) attn_bwd_mma(AttnArgs a, const bf16* __re
     const float* mrow = a.mask + (size_t)b * Lk;
     float D0 = 0.f, D1 = 0.f;
     uint32_t pm[NKT][2];     // dropped P, packed, kept for the smem store
+    uint32_t bw0[NTP / 4], bw1[NTP / 4];
+    if (a.drop.thresh) {
+      load_drop_row<NTP>(bw0, mw + g * NTP);
+      load_drop_row<NTP>(bw1, mw + (g + 8) * NTP);
+    }
 #pragma unroll
     for (int t = 0; t < NKT; ++t) {
       const int j = t * 8 + 2 * q;
@@ -209,9 +266,9 @@ __global__ void __launch_bounds__(256) attn_bwd_mma(AttnArgs a, const bf16* __re
       float p10 = (v0 && r1 < Lq) ? __expf(fmaf(s[t][2], a.scale, ma) - l1) : 0.f;
       float p11 = (v1 && r1 < Lq) ? __expf(fmaf(s[t][3], a.scale, mb) - l1) : 0.f;
       float m00 = 1.f, m01 = 1.f, m10 = 1.f, m11 = 1.f;
-      if (a.drop.thresh && t * 8 < Lk) {
-        if (r0 < Lq) drop_pair(a.drop, prow0, lkp, t, q, m00, m01);
-        if (r1 < Lq) drop_pair(a.drop, prow1, lkp, t, q, m10, m11);
+      if (a.drop.thresh) {
+        drop_pair<NTP>(bw0, t, q, a.drop.scale, m00, m01);
+        drop_pair<NTP>(bw1, t, q, a.drop.scale, m10, m11);
       }
       dp[t][0] *= m00; dp[t][1] *= m01; dp[t][2] *= m10; dp[t][3] *= m11;
       D0 += p00 * dp[t][0] + p01 * dp[t][1];
@@ -308,15 +365,31 @@ __global__ void __launch_bounds__(256) attn_bwd_mma(AttnArgs a, const bf16* __re
 //   backward: D_i = sum_j p_ij dp_ij needs every key of row i, so the dQ kernel makes a first sweep for D
 //             (stored in the second half of the lse buffer), a second for dQ; the dK / dV kernel computes the
 //             TRANSPOSED tiles S^T = K Q^T and dP^T = V dO^T directly, so no probabilities are staged.
-__device__ __forceinline__ float drop_one(const DropSpec& dr, unsigned long long prow, int lkp, int j) {
-  uint32_t w[4];
-  rng_words(dr.rng, dr.site, (prow * (unsigned long long)lkp >> 3) + (unsigned long long)(j >> 3), w);
-  const uint32_t x = w[(j & 7) >> 1];
-  const uint32_t u = (j & 1) ? (x >> 16) : (x & 0xFFFFu);
-  return u >= dr.thresh ? dr.scale : 0.f;
-}
-
 constexpr int LONG_BQ = 64, LONG_BK = 64;
+
+// asynchronous global -> shared copies (LDGSTS): the next block streams in while the tensor cores work on
+// the current one; src-size 0 zero-fills rows beyond the sequence
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, bool valid) {
+  const int sz = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_addr(dst)), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* dst, const void* src, bool valid) {
+  const int sz = valid ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_addr(dst)), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int D, int DS>
+__device__ __forceinline__ void load_tile_async(bf16* dst, const bf16* src, int ld, int valid, int rows) {
+  constexpr int VPR = D / 8;
+  for (int idx = threadIdx.x; idx < rows * VPR; idx += blockDim.x) {
+    const int r = idx / VPR, c = (idx % VPR) * 8;
+    const bool ok = r < valid;
+    cp_async16(dst + (size_t)r * DS + c, ok ? src + (size_t)r * ld + c : src, ok);
+  }
+}
 
 template <int D>
 __global__ void __launch_bounds__(128) attn_fwd_long(AttnArgs a, bf16* __restrict__ ctx, int ldo,
@@ -327,10 +400,19 @@ __global__ void __launch_bounds__(128) attn_fwd_long(AttnArgs a, bf16* __restric
   const int Lq = a.Lq, Lk = a.Lk;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   bf16* Qs = reinterpret_cast<bf16*>(smem);
-  bf16* Ks = Qs + (size_t)LONG_BQ * DS;
-  bf16* Vs = Ks + (size_t)LONG_BK * DS;
+  bf16* KV = Qs + (size_t)LONG_BQ * DS;                             // [2 buffers][K | V][LONG_BK][DS]
+  uint8_t* mw = reinterpret_cast<uint8_t*>(KV + (size_t)4 * LONG_BK * DS) + warp * 16 * 8;   // keep-bytes [16][8]
   const int nq = Lq - q_base < LONG_BQ ? Lq - q_base : LONG_BQ;
-  load_tile_z<D, DS>(Qs, a.q + (size_t)(b * Lq + q_base) * a.ldq + a.q_off + h * D, a.ldq, nq, LONG_BQ);
+  auto load_block = [&](int k_base, int buf) {
+    const int nk = Lk - k_base < LONG_BK ? Lk - k_base : LONG_BK;
+    bf16* Kb = KV + (size_t)buf * 2 * LONG_BK * DS;
+    load_tile_async<D, DS>(Kb, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.k_off + h * D, a.ldkv, nk, LONG_BK);
+    load_tile_async<D, DS>(Kb + (size_t)LONG_BK * DS, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.v_off + h * D,
+                           a.ldkv, nk, LONG_BK);
+  };
+  load_tile_async<D, DS>(Qs, a.q + (size_t)(b * Lq + q_base) * a.ldq + a.q_off + h * D, a.ldq, nq, LONG_BQ);
+  load_block(0, 0);
+  cp_async_commit();
   const int g = lane >> 2, q = lane & 3, i0 = warp * 16;
   const int r0 = q_base + i0 + g, r1 = r0 + 8;                      // query rows of this thread
   const unsigned long long prow0 = (unsigned long long)(b * a.H + h) * Lq + r0, prow1 = prow0 + 8;
@@ -340,12 +422,19 @@ __global__ void __launch_bounds__(128) attn_fwd_long(AttnArgs a, bf16* __restric
   float o[D / 8][4];
 #pragma unroll
   for (int c = 0; c < D / 8; ++c) o[c][0] = o[c][1] = o[c][2] = o[c][3] = 0.f;
-  for (int k_base = 0; k_base < Lk; k_base += LONG_BK) {
-    const int nk = Lk - k_base < LONG_BK ? Lk - k_base : LONG_BK;
+  for (int k_base = 0, it = 0; k_base < Lk; k_base += LONG_BK, ++it) {
+    if (k_base + LONG_BK < Lk) {
+      load_block(k_base + LONG_BK, (it + 1) & 1);                   // buffer released by the barrier below
+      cp_async_commit();
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    if (a.drop.thresh)     // this block's keep-bytes (the barrier at the end of the last block released mw)
+      warp_drop_bits<NKT, 8>(mw, a.drop, prow0 - g, Lq - (q_base + i0), lkp, k_base >> 3, (lkp - k_base) >> 3, lane);
     __syncthreads();
-    load_tile_z<D, DS>(Ks, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.k_off + h * D, a.ldkv, nk, LONG_BK);
-    load_tile_z<D, DS>(Vs, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.v_off + h * D, a.ldkv, nk, LONG_BK);
-    __syncthreads();
+    const bf16* Ks = KV + (size_t)(it & 1) * 2 * LONG_BK * DS;
+    const bf16* Vs = Ks + (size_t)LONG_BK * DS;
     float s[NKT][4];
 #pragma unroll
     for (int t = 0; t < NKT; ++t) s[t][0] = s[t][1] = s[t][2] = s[t][3] = 0.f;
@@ -380,14 +469,15 @@ __global__ void __launch_bounds__(128) attn_fwd_long(AttnArgs a, bf16* __restric
 #pragma unroll
     for (int c = 0; c < D / 8; ++c) { o[c][0] *= c0; o[c][1] *= c0; o[c][2] *= c1; o[c][3] *= c1; }
     if (a.drop.thresh) {
+      uint32_t bw0[2], bw1[2];
+      load_drop_row<8>(bw0, mw + g * 8);
+      load_drop_row<8>(bw1, mw + (g + 8) * 8);
 #pragma unroll
       for (int t = 0; t < NKT; ++t) {
-        if (k_base + t * 8 < Lk) {
-          float m00 = 1.f, m01 = 1.f, m10 = 1.f, m11 = 1.f;
-          if (r0 < Lq) drop_pair(a.drop, prow0, lkp, (k_base >> 3) + t, q, m00, m01);
-          if (r1 < Lq) drop_pair(a.drop, prow1, lkp, (k_base >> 3) + t, q, m10, m11);
-          s[t][0] *= m00; s[t][1] *= m01; s[t][2] *= m10; s[t][3] *= m11;
-        }
+        float m00, m01, m10, m11;
+        drop_pair<8>(bw0, t, q, a.drop.scale, m00, m01);
+        drop_pair<8>(bw1, t, q, a.drop.scale, m10, m11);
+        s[t][0] *= m00; s[t][1] *= m01; s[t][2] *= m10; s[t][3] *= m11;
       }
     }
 #pragma unroll
@@ -405,6 +495,7 @@ __global__ void __launch_bounds__(128) attn_fwd_long(AttnArgs a, bf16* __restric
         mma16816(o[c + 1], pf, vf[2], vf[3]);
       }
     }
+    __syncthreads();                                                // every warp is done with this buffer
   }
   if (q == 0) {
     if (r0 < Lq) lse_out[prow0] = m0 + __logf(l0);
@@ -433,11 +524,22 @@ __global__ void __launch_bounds__(128) attn_bwd_long_dq(AttnArgs a, const bf16* 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   bf16* Qs = reinterpret_cast<bf16*>(smem);
   bf16* dOs = Qs + (size_t)LONG_BQ * DS;
-  bf16* Ks = dOs + (size_t)LONG_BQ * DS;
-  bf16* Vs = Ks + (size_t)LONG_BK * DS;
+  bf16* KV = dOs + (size_t)LONG_BQ * DS;                            // [2 buffers][K | V][LONG_BK][DS]
+  uint8_t* mw = reinterpret_cast<uint8_t*>(KV + (size_t)4 * LONG_BK * DS) + warp * 16 * 8;   // keep-bytes [16][8]
   const int nq = Lq - q_base < LONG_BQ ? Lq - q_base : LONG_BQ;
-  load_tile_z<D, DS>(Qs, a.q + (size_t)(b * Lq + q_base) * a.ldq + a.q_off + h * D, a.ldq, nq, LONG_BQ);
-  load_tile_z<D, DS>(dOs, dctx + (size_t)(b * Lq + q_base) * ldo + h * D, ldo, nq, LONG_BQ);
+  const int nkb = (Lk + LONG_BK - 1) / LONG_BK;
+  auto load_block = [&](int kb, int buf) {
+    const int k_base = kb * LONG_BK;
+    const int nk = Lk - k_base < LONG_BK ? Lk - k_base : LONG_BK;
+    bf16* Kb = KV + (size_t)buf * 2 * LONG_BK * DS;
+    load_tile_async<D, DS>(Kb, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.k_off + h * D, a.ldkv, nk, LONG_BK);
+    load_tile_async<D, DS>(Kb + (size_t)LONG_BK * DS, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.v_off + h * D,
+                           a.ldkv, nk, LONG_BK);
+  };
+  load_tile_async<D, DS>(Qs, a.q + (size_t)(b * Lq + q_base) * a.ldq + a.q_off + h * D, a.ldq, nq, LONG_BQ);
+  load_tile_async<D, DS>(dOs, dctx + (size_t)(b * Lq + q_base) * ldo + h * D, ldo, nq, LONG_BQ);
+  load_block(0, 0);
+  cp_async_commit();
   const int g = lane >> 2, q = lane & 3, i0 = warp * 16;
   const int r0 = q_base + i0 + g, r1 = r0 + 8;
   const bool ok0 = r0 < Lq, ok1 = r1 < Lq;
@@ -449,13 +551,27 @@ __global__ void __launch_bounds__(128) attn_bwd_long_dq(AttnArgs a, const bf16* 
   float o[D / 8][4];
 #pragma unroll
   for (int c = 0; c < D / 8; ++c) o[c][0] = o[c][1] = o[c][2] = o[c][3] = 0.f;
+  int it = 0;                                                       // block counter over both sweeps
   for (int sweep = 0; sweep < 2; ++sweep) {
-    for (int k_base = 0; k_base < Lk; k_base += LONG_BK) {
-      const int nk = Lk - k_base < LONG_BK ? Lk - k_base : LONG_BK;
+    for (int kb = 0; kb < nkb; ++kb, ++it) {
+      const int k_base = kb * LONG_BK;
+      if (it + 1 < 2 * nkb) {
+        load_block(kb + 1 < nkb ? kb + 1 : 0, (it + 1) & 1);        // sweep 1 starts again at block 0
+        cp_async_commit();
+        cp_async_wait<1>();
+      } else {
+        cp_async_wait<0>();
+      }
+      if (a.drop.thresh)
+        warp_drop_bits<NKT, 8>(mw, a.drop, prow0 - g, Lq - (q_base + i0), lkp, k_base >> 3, (lkp - k_base) >> 3, lane);
       __syncthreads();
-      load_tile_z<D, DS>(Ks, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.k_off + h * D, a.ldkv, nk, LONG_BK);
-      load_tile_z<D, DS>(Vs, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.v_off + h * D, a.ldkv, nk, LONG_BK);
-      __syncthreads();
+      const bf16* Ks = KV + (size_t)(it & 1) * 2 * LONG_BK * DS;
+      const bf16* Vs = Ks + (size_t)LONG_BK * DS;
+      uint32_t bw0[2], bw1[2];
+      if (a.drop.thresh) {
+        load_drop_row<8>(bw0, mw + g * 8);
+        load_drop_row<8>(bw1, mw + (g + 8) * 8);
+      }
       float s[NKT][4], dp[NKT][4];
 #pragma unroll
       for (int t = 0; t < NKT; ++t) {
@@ -474,9 +590,9 @@ __global__ void __launch_bounds__(128) attn_bwd_long_dq(AttnArgs a, const bf16* 
         const float p10 = (v0 && ok1) ? __expf(fmaf(s[t][2], a.scale, ma) - ls1) : 0.f;
         const float p11 = (v1 && ok1) ? __expf(fmaf(s[t][3], a.scale, mb) - ls1) : 0.f;
         float m00 = 1.f, m01 = 1.f, m10 = 1.f, m11 = 1.f;
-        if (a.drop.thresh && k_base + t * 8 < Lk) {
-          if (ok0) drop_pair(a.drop, prow0, lkp, (k_base >> 3) + t, q, m00, m01);
-          if (ok1) drop_pair(a.drop, prow1, lkp, (k_base >> 3) + t, q, m10, m11);
+        if (a.drop.thresh) {
+          drop_pair<8>(bw0, t, q, a.drop.scale, m00, m01);
+          drop_pair<8>(bw1, t, q, a.drop.scale, m10, m11);
         }
         dp[t][0] *= m00; dp[t][1] *= m01; dp[t][2] *= m10; dp[t][3] *= m11;
         if (sweep == 0) {
@@ -504,6 +620,7 @@ __global__ void __launch_bounds__(128) attn_bwd_long_dq(AttnArgs a, const bf16* 
           }
         }
       }
+      __syncthreads();                                              // every warp is done with this buffer
     }
     if (sweep == 0) {
       D0 += __shfl_xor_sync(0xffffffffu, D0, 1); D0 += __shfl_xor_sync(0xffffffffu, D0, 2);
@@ -539,36 +656,65 @@ __global__ void __launch_bounds__(128) attn_bwd_long_dkv(AttnArgs a, const bf16*
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   bf16* Ks = reinterpret_cast<bf16*>(smem);
   bf16* Vs = Ks + (size_t)LONG_BK * DS;
-  bf16* Qs = Vs + (size_t)LONG_BK * DS;
-  bf16* dOs = Qs + (size_t)LONG_BQ2 * DS;
-  float* lse_s = reinterpret_cast<float*>(dOs + (size_t)LONG_BQ2 * DS);
-  float* d_s = lse_s + LONG_BQ2;
+  bf16* QO = Vs + (size_t)LONG_BK * DS;                             // [2 buffers][Q | dO][LONG_BQ2][DS]
+  float* stats = reinterpret_cast<float*>(QO + (size_t)4 * LONG_BQ2 * DS);   // [2 buffers][lse | D][LONG_BQ2]
+  uint8_t* msk = reinterpret_cast<uint8_t*>(stats + 4 * LONG_BQ2);           // [2 buffers][LONG_BQ2][8] keep-bytes
   const int nk = Lk - k_base < LONG_BK ? Lk - k_base : LONG_BK;
-  load_tile_z<D, DS>(Ks, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.k_off + h * D, a.ldkv, nk, LONG_BK);
-  load_tile_z<D, DS>(Vs, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.v_off + h * D, a.ldkv, nk, LONG_BK);
+  const int lkp = (Lk + 7) & ~7;
+  const unsigned long long pbase = (unsigned long long)(b * a.H + h) * Lq;
+  // keep-bytes of a query block x this CTA's 8 key tiles, one generator call per (query, tile); written one
+  // block ahead, so the barriers of the pipeline publish them
+  auto gen_mask = [&](int q_base, int buf) {
+    for (int c = threadIdx.x; c < LONG_BQ2 * 8; c += 128) {
+      const int i = q_base + (c >> 3), T = (k_base >> 3) + (c & 7);
+      uint32_t bits = 0xFFu;
+      if (i < Lq && T * 8 < Lk) bits = drop_tile_bits(a.drop, pbase + i, lkp, T);
+      msk[buf * LONG_BQ2 * 8 + c] = (uint8_t)bits;
+    }
+  };
+  auto load_block = [&](int q_base, int buf) {
+    const int nq = Lq - q_base < LONG_BQ2 ? Lq - q_base : LONG_BQ2;
+    bf16* Qb = QO + (size_t)buf * 2 * LONG_BQ2 * DS;
+    load_tile_async<D, DS>(Qb, a.q + (size_t)(b * Lq + q_base) * a.ldq + a.q_off + h * D, a.ldq, nq, LONG_BQ2);
+    load_tile_async<D, DS>(Qb + (size_t)LONG_BQ2 * DS, dctx + (size_t)(b * Lq + q_base) * ldo + h * D, ldo, nq,
+                           LONG_BQ2);
+    if (threadIdx.x < 2 * LONG_BQ2) {
+      const int i = threadIdx.x & (LONG_BQ2 - 1);
+      const float* src = threadIdx.x < LONG_BQ2 ? lse : dsum;
+      const bool ok = i < nq;
+      cp_async4(stats + buf * 2 * LONG_BQ2 + threadIdx.x, ok ? src + pbase + q_base + i : src, ok);
+    }
+  };
+  load_tile_async<D, DS>(Ks, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.k_off + h * D, a.ldkv, nk, LONG_BK);
+  load_tile_async<D, DS>(Vs, a.kv + (size_t)(b * Lk + k_base) * a.ldkv + a.v_off + h * D, a.ldkv, nk, LONG_BK);
+  load_block(0, 0);
+  cp_async_commit();
+  if (a.drop.thresh) gen_mask(0, 0);
   const int g = lane >> 2, q = lane & 3, j0 = warp * 16;
   const int jr0 = k_base + j0 + g, jr1 = jr0 + 8;                   // key rows of this thread
   const float* mrow = a.mask + (size_t)b * Lk;
   const float mk0 = jr0 < Lk ? mrow[jr0] : 0.f, mk1 = jr1 < Lk ? mrow[jr1] : 0.f;
-  const int lkp = (Lk + 7) & ~7;
-  const unsigned long long pbase = (unsigned long long)(b * a.H + h) * Lq;
   float dv[D / 8][4], dk[D / 8][4];
 #pragma unroll
   for (int c = 0; c < D / 8; ++c) {
     dv[c][0] = dv[c][1] = dv[c][2] = dv[c][3] = 0.f;
     dk[c][0] = dk[c][1] = dk[c][2] = dk[c][3] = 0.f;
   }
-  for (int q_base = 0; q_base < Lq; q_base += LONG_BQ2) {
-    const int nq = Lq - q_base < LONG_BQ2 ? Lq - q_base : LONG_BQ2;
-    __syncthreads();
-    load_tile_z<D, DS>(Qs, a.q + (size_t)(b * Lq + q_base) * a.ldq + a.q_off + h * D, a.ldq, nq, LONG_BQ2);
-    load_tile_z<D, DS>(dOs, dctx + (size_t)(b * Lq + q_base) * ldo + h * D, ldo, nq, LONG_BQ2);
-    if (threadIdx.x < LONG_BQ2) {
-      const bool ok = (int)threadIdx.x < nq;
-      lse_s[threadIdx.x] = ok ? lse[pbase + q_base + threadIdx.x] : 0.f;
-      d_s[threadIdx.x] = ok ? dsum[pbase + q_base + threadIdx.x] : 0.f;
+  for (int q_base = 0, it = 0; q_base < Lq; q_base += LONG_BQ2, ++it) {
+    if (q_base + LONG_BQ2 < Lq) {
+      load_block(q_base + LONG_BQ2, (it + 1) & 1);                  // buffer released by the barrier below
+      cp_async_commit();
+      if (a.drop.thresh) gen_mask(q_base + LONG_BQ2, (it + 1) & 1);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
     }
     __syncthreads();
+    const bf16* Qs = QO + (size_t)(it & 1) * 2 * LONG_BQ2 * DS;
+    const bf16* dOs = Qs + (size_t)LONG_BQ2 * DS;
+    const float* lse_s = stats + (it & 1) * 2 * LONG_BQ2;
+    const float* d_s = lse_s + LONG_BQ2;
+    const uint8_t* mk = msk + (it & 1) * LONG_BQ2 * 8 + warp * 2;   // this warp's two key tiles
     float s[NQT][4], dp[NQT][4];
 #pragma unroll
     for (int t = 0; t < NQT; ++t) {
@@ -579,14 +725,19 @@ __global__ void __launch_bounds__(128) attn_bwd_long_dkv(AttnArgs a, const bf16*
     qk_mma<D, DS, NQT>(dp, Vs, j0, dOs, lane);
 #pragma unroll
     for (int t = 0; t < NQT; ++t) {
+      uint32_t kb[2] = {0xFFFFu, 0xFFFFu};                          // keep-bytes of queries 2q, 2q + 1 of tile t
+      if (a.drop.thresh) {
+        kb[0] = *reinterpret_cast<const uint16_t*>(mk + (t * 8 + 2 * q) * 8);
+        kb[1] = *reinterpret_cast<const uint16_t*>(mk + (t * 8 + 2 * q + 1) * 8);
+      }
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const int il = t * 8 + 2 * q + (e & 1), i = q_base + il;
         const int j = (e & 2) ? jr1 : jr0;
         const bool ok = i < Lq && j < Lk;
         const float p = ok ? __expf(fmaf(s[t][e], a.scale, (e & 2) ? mk1 : mk0) - lse_s[il]) : 0.f;
-        float m = 1.f;
-        if (a.drop.thresh && ok) m = drop_one(a.drop, pbase + i, lkp, j);
+        float m = 1.f;                                              // key jr0: bit g of byte 0, jr1: of byte 1
+        if (a.drop.thresh) m = ((kb[e & 1] >> (g + ((e & 2) ? 8 : 0))) & 1u) ? a.drop.scale : 0.f;
         const float dpm = dp[t][e] * m;
         s[t][e] = p * m;                              // dropped probability (transposed)
         dp[t][e] = p * (dpm - d_s[il]);               // dS (transposed)
@@ -615,6 +766,7 @@ __global__ void __launch_bounds__(128) attn_bwd_long_dkv(AttnArgs a, const bf16*
         mma16816(dk[c + 1], sa, qf[2], qf[3]);
       }
     }
+    __syncthreads();                                                // every warp is done with this buffer
   }
   bf16* k0 = dkv + (size_t)(b * Lk + jr0) * lddkv + h * D + 2 * q;
   bf16* k1 = dkv + (size_t)(b * Lk + jr1) * lddkv + h * D + 2 * q;

@@ -211,6 +211,8 @@ class CudaOps(object):
             out = torch.empty(B * Lq, H * d, dtype=self.adt, device=qbuf.device)
         lse = torch.empty(2, B * H * Lq, dtype=torch.float32, device=qbuf.device)   # row 1: backward scratch
         r, s, p = self._drop(drop, rng)
+        if self.timing is not None:
+            self._tag, self._work = " %dx%dx%d h%d" % (Lq, Lk, d, H), 4.0 * B * H * Lq * Lk * d
         self._call("k3m_attn_fwd", _p(qbuf), _i(_ld(qbuf)), _i(q_off), _p(kvbuf), _i(_ld(kvbuf)), _i(k_off),
                    _i(v_off), _p(mask_add), _i(B), _i(H), _i(Lq), _i(Lk), _i(d), _p(out), _i(_ld(out)),
                    _p(lse), r, s, p, self._st())
@@ -219,6 +221,8 @@ class CudaOps(object):
     def attn_bwd(self, dctx, ctx, qbuf, q_off, kvbuf, k_off, v_off, mask_add, lse, dqbuf, dkvbuf, B, H, Lq,
                  Lk, d, drop=None, rng=None):
         r, s, p = self._drop(drop, rng)
+        if self.timing is not None:
+            self._tag, self._work = " %dx%dx%d h%d" % (Lq, Lk, d, H), 10.0 * B * H * Lq * Lk * d
         self._call("k3m_attn_bwd", _p(dctx), _i(_ld(dctx)), _p(qbuf), _i(_ld(qbuf)), _i(q_off), _p(kvbuf),
                    _i(_ld(kvbuf)), _i(k_off), _i(v_off), _p(mask_add), _p(lse), _p(dqbuf), _i(_ld(dqbuf)),
                    _p(dkvbuf), _i(_ld(dkvbuf)), _i(B), _i(H), _i(Lq), _i(Lk), _i(d), r, s, p, self._st())

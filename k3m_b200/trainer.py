@@ -19,6 +19,7 @@ that the loader produced on the host anyway), (2) copies the batch host->device 
 static input buffers, (3) writes the learning rate, (4) replays the graph.
 """
 import math
+import os
 
 import numpy as np
 import torch
@@ -110,10 +111,9 @@ class PretrainStep(object):
         self.h2d_bytes = sum(int(np.prod(s)) * (8 if d == torch.int64 else 4) for s, d in self.spec.values())
         self.h2d_bytes += sum(v.numel() * 4 for v in self.plan.values()) + self.hyper.numel() * 4
         self.d2h_bytes = self.losses.numel() * 4
-        self._buckets = self._make_buckets(bucket_mb)
+        self._buckets = self._make_buckets(float(os.environ.get("K3M_BUCKET_MB", bucket_mb)))
         # side stream of the optimizer pipeline: all-reduce of a gradient bucket (world > 1) followed by
         # AdamW on the same range, while backward is still producing the earlier layers' gradients
-        import os
         self.overlap_opt = overlap and os.environ.get("K3M_OPT_OVERLAP", "1") != "0"
         self._comm_stream = torch.cuda.Stream(device=dev) if (self._cuda and (self.world > 1 or self.overlap_opt)) else None
         self.use_graph = use_graph and self._cuda

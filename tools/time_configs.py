@@ -29,11 +29,22 @@ def time_step(step, batches, steps, warmup):
     return e0.elapsed_time(e1) / steps, step.read_losses()
 
 
+def breakdown(step, batch, top=28):
+    from bench import kernel_breakdown
+    rows = kernel_breakdown(step, batch)
+    tot = sum(v[1] for v in rows.values())
+    sys.stderr.write("  eager step, %.2f ms of kernels in %d launches\n" % (tot, sum(v[0] for v in rows.values())))
+    for name, (n, ms, fl) in sorted(rows.items(), key=lambda kv: -kv[1][1])[:top]:
+        sys.stderr.write("  %8.3f ms %5.1f%% %5d x  %s%s\n" % (ms, 100 * ms / tot, n, name,
+                                                               "  %.0f TF/s" % (fl / ms / 1e9) if fl else ""))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--only", default="")
+    ap.add_argument("--breakdown", action="store_true", help="per entry point device time of one eager step")
     args = ap.parse_args()
     import torch
     from k3m_b200.config import BertConfig, K3M_BASE_6LAYER_6CONNECT
@@ -55,6 +66,8 @@ def main():
                           "dims": dims, "ms_per_step": round(ms, 3), "samples_per_s": round(B / ms * 1e3, 1),
                           "gpu_launches": step.launches_per_step,
                           "losses": {k: round(float(v), 4) for k, v in losses.items()}}))
+        if args.breakdown:
+            breakdown(step, hb[0])
         del step
         torch.cuda.empty_cache()
 
@@ -74,6 +87,8 @@ def main():
                           "dims": dims, "ms_per_step": round(ms, 3), "pairs_per_s": round(B / ms * 1e3, 1),
                           "gpu_launches": step.launches_per_step,
                           "losses": {k: round(float(v), 4) for k, v in losses.items()}}))
+        if args.breakdown:
+            breakdown(step, hb[0])
 
 
 if __name__ == "__main__":
