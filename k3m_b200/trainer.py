@@ -57,7 +57,7 @@ class PretrainStep(object):
     def __init__(self, cfg, batch_size, len_t=36, len_v=36, len_pv=36, max_num_pv=8, device="cuda",
                  state_dict=None, init_seed=0, lr=1e-4, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01,
                  warmup_steps=0, total_steps=0, loss_img_weight=1.0, training=True, rng_seed=1234,
-                 use_graph=True, process_group=None, bucket_mb=64, overlap=True, ops=None):
+                 use_graph=True, process_group=None, bucket_mb=None, overlap=True, ops=None):
         """`ops`: kernel table; default (and the only product path) is `CudaOps`, which raises without
         a CUDA device.  Tests inject the fp32 PyTorch restatement to check this host logic on CPU."""
         self.cfg, self.device = cfg, torch.device(device)
@@ -111,11 +111,19 @@ class PretrainStep(object):
         self.h2d_bytes = sum(int(np.prod(s)) * (8 if d == torch.int64 else 4) for s, d in self.spec.values())
         self.h2d_bytes += sum(v.numel() * 4 for v in self.plan.values()) + self.hyper.numel() * 4
         self.d2h_bytes = self.losses.numel() * 4
+        # data-parallel runs reduce in 256 MB pieces on a high-priority stream: measured at 8 GPUs (NVLS
+        # all-reduce of the 1.85 GB fp32 gradient arena overlapping backward) 64 MB -> 25.3 ms / step,
+        # 256 MB -> 24.5, 256 MB + priority -> 24.3, 512 MB -> 24.9 (profiles/r01e_n8_sweep.txt); one GPU keeps
+        # 64 MB pieces, which only pace the AdamW launches that overlap backward
+        if bucket_mb is None:
+            bucket_mb = 256 if self.world > 1 else 64
         self._buckets = self._make_buckets(float(os.environ.get("K3M_BUCKET_MB", bucket_mb)))
         # side stream of the optimizer pipeline: all-reduce of a gradient bucket (world > 1) followed by
         # AdamW on the same range, while backward is still producing the earlier layers' gradients
         self.overlap_opt = overlap and os.environ.get("K3M_OPT_OVERLAP", "1") != "0"
-        self._comm_stream = torch.cuda.Stream(device=dev) if (self._cuda and (self.world > 1 or self.overlap_opt)) else None
+        prio = -1 if os.environ.get("K3M_COMM_PRIO", "1" if self.world > 1 else "0") != "0" else 0
+        self._comm_stream = (torch.cuda.Stream(device=dev, priority=prio)
+                             if (self._cuda and (self.world > 1 or self.overlap_opt)) else None)
         self.use_graph = use_graph and self._cuda
         self.graph = None
         self.launches_per_step = 0
