@@ -141,4 +141,7 @@ def load_checkpoint(step, path_or_dict, map_location="cpu"):
     if sch.get("last_epoch", step.global_step) != step.global_step:
         raise ValueError("scheduler epoch %s and optimizer step %s differ: not a checkpoint of this driver"
                          % (sch.get("last_epoch"), step.global_step))
+    # the dropout / Gumbel counter stream advances once per step (trainer._device_step): continue it, so a
+    # resumed run with the same seed draws the masks the uninterrupted run would have drawn
+    step.rng[1] = step.global_step
     return step.global_step

@@ -90,3 +90,51 @@ def test_training_mode_is_deterministic_given_rng_state(ops):
     assert float((g1 - g2).abs().max()) <= 1e-4 * float(g1.abs().max())
     assert float((g1 - g3).abs().max()) > 1e-3 * float(g1.abs().max())
     assert float(o1["loss_t"]) == pytest.approx(float(o2["loss_t"]), rel=1e-6)
+
+
+def test_checkpoint_resume_continues_the_run_on_gpu(tmp_path):
+    """Three graph-replayed training steps (dropout on) vs two steps, reference-layout `.tar`, a fresh step
+    object, `load_checkpoint`, one more step: parameters, moments and the dropout stream all continue."""
+    from k3m_b200 import checkpoint as ckpt
+    from k3m_b200.config import BertConfig, K3M_TINY
+    from k3m_b200.synth import synth_batch
+    from k3m_b200.trainer import PretrainStep
+    cfg = BertConfig.from_dict(K3M_TINY)
+    cfg.if_pre_sampling, cfg.margin, cfg.num_negative_pv = 1, 1.0, 4
+    dims = dict(len_t=12, len_v=9, len_pv=20, max_num_pv=4)
+    kw = dict(device="cuda", init_seed=2, lr=1e-3, warmup_steps=2, total_steps=10, training=True, rng_seed=99,
+              use_graph=True, **dims)
+    batches = [synth_batch(cfg, 4, 12, 9, 20, max_num_pv=4, seed=60 + i) for i in range(3)]
+    import random
+    a = PretrainStep(cfg, 4, **kw)
+    for i in range(3):
+        random.seed(i)
+        a.step(batches[i])
+    b = PretrainStep(cfg, 4, **kw)
+    for i in range(2):
+        random.seed(i)
+        b.step(batches[i])
+    path = str(tmp_path / "resume.tar")
+    ckpt.save_checkpoint(b, path)
+    c = PretrainStep(cfg, 4, **dict(kw, init_seed=5))
+    assert ckpt.load_checkpoint(c, path) == 2
+    random.seed(2)
+    c.step(batches[2])
+    torch.cuda.synchronize()
+    # fp32 reductions whose order is not fixed (split-K reduce-adds, embedding scatter-adds) keep two runs of
+    # the same step from being bit-identical, and Adam turns a last-bit change of a ~0 gradient into a change
+    # of up to lr: compare norms, and the losses (which see the restored dropout stream and weights)
+    for x, y, tol in ((c.p32, a.p32, 1e-5), (c.m, a.m, 1e-3), (c.v, a.v, 1e-3)):
+        assert float((x - y).norm()) <= tol * float(y.norm())
+    assert float((c.p32 - a.p32).abs().max()) <= 2.5e-3
+    la, lc = a.read_losses(), c.read_losses()
+    for k in la:
+        assert lc[k] == pytest.approx(la[k], rel=1e-4, abs=1e-6), k
+    # without the moments / step count the same third step lands elsewhere
+    d = PretrainStep(cfg, 4, **kw)
+    d.load_state_dict(b.state_dict())
+    d.global_step = 2
+    random.seed(2)
+    d.step(batches[2])
+    torch.cuda.synchronize()
+    assert float((d.p32 - a.p32).norm()) > 50 * float((c.p32 - a.p32).norm())
