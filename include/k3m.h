@@ -154,6 +154,32 @@ int k3m_dropout(const void* x, int ldx, int x_f32, void* y, int ldy, int y_f32, 
 int k3m_adamw(float* p32, float* g32, float* m, float* v, void* p16, const float* hyper, long long n,
               int zero_grad, void* stream);
 
+/* ---- batch preprocessing on the GPU: BertPreprocessBatch + the loader's prepend ----------
+ * (vilbert_k3m/datasets/concept_cap_dataset_struc.py).  Inputs are a padded raw batch in device memory and the
+ * random draws the reference takes from random.random() (doubles: one per title token, one per region) and
+ * np.random.randint (replacement ids); given the same draws the outputs equal the reference's bit for bit.
+ * All id / mask / label / index outputs are int64 like the tensors the reference's loader yields.
+ *
+ * title: mask_word :763-783, specials + padding :664-690.  tokens [B, L] ids WITHOUT specials (n_tok[b] <= L-2
+ * of them), u / rnd [B, L] indexed like tokens -> ids / att / seg / labels [B, L].                          */
+int k3m_prep_title(const long long* tokens, const int* n_tok, const double* u, const long long* rnd, int B,
+                   int L, long long cls_id, long long sep_id, long long mask_id, long long* ids, long long* att,
+                   long long* seg, long long* labels, void* stream);
+/* PV string: mask_word_pv :815-839 (every value span but the first pair's -> [MASK]), then index_pv :785-813
+ * on the masked row with specials -> index_p / index_v [B, max_num_pv, 2] (zero padded).                     */
+int k3m_prep_pv(const long long* tokens, const int* n_tok, int B, int L, int max_num_pv, long long cls_id,
+                long long sep_id, long long mask_id, long long* ids, long long* att, long long* seg,
+                long long* labels, long long* index_p, long long* index_v, void* stream);
+/* regions: location normalisation :585-596, iou :40-78, mask_region :887-933, global feature / whole-image
+ * box / mask prepend :372-413.  boxes [B, R, 4] pixel corners (num_boxes[b] valid), whp [B, 3] = {w, h,
+ * float32(double w * double h)}, u [B, R], feat [B, R, F] (rows >= num_boxes zero) -> image_feat [B, R+1, F],
+ * image_loc [B, R+1, 5], image_mask [B, R+1], image_label [B, R]; zero_flag [B, R] bytes and count0 [B] ints
+ * are scratch (which regions were zeroed; the divisor of the global feature).                               */
+int k3m_prep_regions(const float* boxes, const int* num_boxes, const float* whp, const double* u,
+                     const float* feat, int B, int R, int F, float* image_feat, float* image_loc,
+                     long long* image_mask, long long* image_label, unsigned char* zero_flag, int* count0,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

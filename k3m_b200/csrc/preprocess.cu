@@ -1,0 +1,236 @@
+// GPU-side batch preprocessing (SURVEY §8 f, row N2): what `BertPreprocessBatch` and the loader's
+// `__iter__` do per sample in Python (`vilbert_k3m/datasets/concept_cap_dataset_struc.py:532-933`, `:372-413`)
+// as four small kernels over a padded raw batch that is already in HBM.  Integer / byte work, HBM-bound:
+// nothing here goes near the tensor cores.  The random decisions are INPUTS (one double per title token and
+// per region, as `random.random()` hands them out), so results are bit-identical to the reference given
+// the same draws; in production the draws come from a device generator.
+//
+// Floating point follows numpy's float32 evaluation order with explicit round-to-nearest intrinsics (no
+// FMA contraction), and float64 where numpy promotes (`sum / int64 count`, the `prob / 0.15` chain).
+#include "common.cuh"
+
+namespace {
+
+constexpr int PV_COLON = 131, PV_SEMI = 132;   // ":" and ";" of the PV string (`:785-790`)
+
+// ---- title: mask_word (`:763-783`) + specials + padding (`:664-690`) ------------------------------------
+__global__ void prep_title_kernel(const long long* __restrict__ tokens, const int* __restrict__ n_tok,
+                                  const double* __restrict__ u, const long long* __restrict__ rnd, int L,
+                                  long long cls_id, long long sep_id, long long mask_id,
+                                  long long* __restrict__ ids, long long* __restrict__ att,
+                                  long long* __restrict__ seg, long long* __restrict__ labels) {
+  const int b = blockIdx.x, n = n_tok[b] < L - 2 ? n_tok[b] : L - 2;
+  for (int i = threadIdx.x; i < L; i += blockDim.x) {
+    long long id = 0, lab = -1, m = 0;
+    if (i == 0) { id = cls_id; m = 1; }
+    else if (i <= n) {
+      const long long t = tokens[(size_t)b * L + i - 1];
+      double prob = u[(size_t)b * L + i - 1];
+      id = t; m = 1;
+      if (prob < 0.15) {
+        prob /= 0.15;
+        if (prob < 0.8) id = mask_id;
+        else if (prob < 0.9) id = rnd[(size_t)b * L + i - 1];
+        lab = t;
+      }
+    } else if (i == n + 1) { id = sep_id; m = 1; }
+    ids[(size_t)b * L + i] = id;
+    att[(size_t)b * L + i] = m;
+    seg[(size_t)b * L + i] = 0;
+    labels[(size_t)b * L + i] = lab;
+  }
+}
+
+// ---- PV: mask_word_pv (`:815-839`) + specials + index_pv (`:785-813`) -----------------------------------
+// The pairing rules are sequential list surgery (drop-first, zip to the shorter list, early stop), so one
+// thread walks the row; the row is at most a few hundred tokens and the kernel runs B rows in parallel.
+__global__ void prep_pv_kernel(const long long* __restrict__ tokens, const int* __restrict__ n_tok, int L,
+                               int max_num_pv, long long cls_id, long long sep_id, long long mask_id,
+                               long long* __restrict__ ids, long long* __restrict__ att, long long* __restrict__ seg,
+                               long long* __restrict__ labels, long long* __restrict__ index_p,
+                               long long* __restrict__ index_v) {
+  extern __shared__ int sh[];                 // [L] positions of 131, [L + 1] positions of 132
+  int* p131 = sh;
+  int* p132 = sh + L;
+  const int b = blockIdx.x, n = n_tok[b] < L - 2 ? n_tok[b] : L - 2;
+  const long long* tk = tokens + (size_t)b * L;
+  long long* o_ids = ids + (size_t)b * L;
+  long long* o_lab = labels + (size_t)b * L;
+  for (int i = threadIdx.x; i < L; i += blockDim.x) {
+    long long id = 0, m = 0;
+    if (i == 0) { id = cls_id; m = 1; }
+    else if (i <= n) { id = tk[i - 1]; m = 1; }
+    else if (i == n + 1) { id = sep_id; m = 1; }
+    o_ids[i] = id;
+    att[(size_t)b * L + i] = m;
+    seg[(size_t)b * L + i] = 0;
+    o_lab[i] = -1;
+  }
+  for (int i = threadIdx.x; i < 2 * max_num_pv; i += blockDim.x) {
+    index_p[(size_t)b * 2 * max_num_pv + i] = 0;
+    index_v[(size_t)b * 2 * max_num_pv + i] = 0;
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  int n131 = 0, n132 = 0;
+  for (int i = 0; i < n; ++i) {               // positions in the list WITHOUT specials
+    if (tk[i] == PV_COLON) p131[n131++] = i;
+    if (tk[i] == PV_SEMI) p132[n132++] = i;
+  }
+  // mask_word_pv: every value span except the first pair's becomes [MASK]; the label is the token the
+  // span held WHEN it was visited (a second visit of an overlapping span records the mask id, as the
+  // reference's in-place edit does)
+  if (n132 == n131 - 1) p132[n132++] = n;
+  const int first = n132 > 1 ? 1 : 0;
+  int pairs = n131 < n132 ? n131 : n132;
+  for (int k = first; k < pairs; ++k)
+    for (int i = p131[k] + 1; i < p132[k]; ++i) {
+      o_lab[i + 1] = o_ids[i + 1];
+      o_ids[i + 1] = mask_id;
+    }
+  // index_pv reads the row AFTER masking and WITH the specials (`:671-674`): a malformed string whose
+  // span swallowed a separator changes what it finds
+  n131 = n132 = 0;
+  for (int i = 0; i < n + 2; ++i) {
+    if (o_ids[i] == PV_COLON) p131[n131++] = i;
+    if (o_ids[i] == PV_SEMI) p132[n132++] = i;
+  }
+  if (n132 == n131) {}
+  else if (n132 == n131 - 1) n131 -= 1;
+  else n131 = n132 = 0;
+  pairs = n131 < n132 ? n131 : n132;
+  int pv_begin = 1, cnt = 0;
+  for (int k = 0; k < pairs && cnt < max_num_pv; ++k, ++cnt) {
+    const int i131 = p131[k], i132 = p132[k];
+    index_p[((size_t)b * max_num_pv + cnt) * 2 + 0] = pv_begin;
+    index_p[((size_t)b * max_num_pv + cnt) * 2 + 1] = i131;
+    index_v[((size_t)b * max_num_pv + cnt) * 2 + 0] = i131 + 1;
+    index_v[((size_t)b * max_num_pv + cnt) * 2 + 1] = i132;
+    pv_begin = i132 + 1;
+  }
+}
+
+// ---- regions: image_loc (`:585-596`), iou (`:40-78`), mask_region (`:887-933`), loader prepend (`:388-397`)
+__device__ __forceinline__ float box_area(const float* bx) {
+  return __fmul_rn(__fadd_rn(__fsub_rn(bx[2], bx[0]), 1.0f), __fadd_rn(__fsub_rn(bx[3], bx[1]), 1.0f));
+}
+
+__global__ void prep_regions_kernel(const float* __restrict__ boxes, const int* __restrict__ num_boxes,
+                                    const float* __restrict__ whp, const double* __restrict__ u, int R,
+                                    float* __restrict__ image_loc, long long* __restrict__ image_mask,
+                                    long long* __restrict__ image_label, unsigned char* __restrict__ zero_flag,
+                                    int* __restrict__ count0) {
+  extern __shared__ float shf[];              // [R][4] boxes, then int sel[R], masked[R]
+  float* bx = shf;
+  int* sel = reinterpret_cast<int*>(shf + 4 * R);
+  int* msk = sel + R;
+  __shared__ int cnt;
+  const int b = blockIdx.x, nb = num_boxes[b];
+  const float w = whp[b * 3 + 0], h = whp[b * 3 + 1], wh = whp[b * 3 + 2];
+  if (threadIdx.x == 0) cnt = 0;
+  for (int r = threadIdx.x; r < R; r += blockDim.x) {
+    int s = 0, z = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) bx[r * 4 + k] = r < nb ? boxes[((size_t)b * R + r) * 4 + k] : 0.f;
+    if (r < nb) {
+      double prob = u[(size_t)b * R + r];
+      if (prob < 0.15) {
+        prob /= 0.15;
+        s = 1;
+        z = prob < 0.9;
+      }
+    }
+    sel[r] = s;
+    zero_flag[(size_t)b * R + r] = (unsigned char)z;
+    image_label[(size_t)b * R + r] = s ? 1 : -1;
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < R; j += blockDim.x) {
+    int m = 0;
+    if (j < nb) {
+      const float aj = box_area(bx + 4 * j);
+      for (int i = 0; i < nb; ++i) {
+        if (!sel[i]) continue;
+        float iw = __fadd_rn(__fsub_rn(fminf(bx[4 * i + 2], bx[4 * j + 2]), fmaxf(bx[4 * i + 0], bx[4 * j + 0])), 1.0f);
+        float ih = __fadd_rn(__fsub_rn(fminf(bx[4 * i + 3], bx[4 * j + 3]), fmaxf(bx[4 * i + 1], bx[4 * j + 1])), 1.0f);
+        if (iw < 0.f) iw = 0.f;
+        if (ih < 0.f) ih = 0.f;
+        const float inter = __fmul_rn(iw, ih);
+        const float ua = __fsub_rn(__fadd_rn(box_area(bx + 4 * i), aj), inter);
+        if (__fdiv_rn(inter, ua) > 0.4f) m = 1;
+      }
+    }
+    msk[j] = m;
+    // location row j + 1: area fraction from the RAW corners first, then the corners scaled (`:586-595`)
+    const float x1 = bx[4 * j], y1 = bx[4 * j + 1], x2 = bx[4 * j + 2], y2 = bx[4 * j + 3];
+    float* o = image_loc + ((size_t)b * (R + 1) + j + 1) * 5;
+    o[4] = __fdiv_rn(__fmul_rn(__fsub_rn(y2, y1), __fsub_rn(x2, x1)), wh);
+    o[0] = __fdiv_rn(x1, w); o[1] = __fdiv_rn(y1, h); o[2] = __fdiv_rn(x2, w); o[3] = __fdiv_rn(y2, h);
+    image_mask[(size_t)b * (R + 1) + j + 1] = j < nb ? 1 : 0;
+  }
+  __syncthreads();
+  int local = 0;
+  for (int j = threadIdx.x; j < R; j += blockDim.x) local += msk[j] == 0;
+  atomicAdd(&cnt, local);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    count0[b] = cnt > 0 ? cnt : 1;            // `sum_count[sum_count == 0] = 1` (`:384-385`)
+    float* g = image_loc + (size_t)b * (R + 1) * 5;
+    g[0] = 0.f; g[1] = 0.f; g[2] = 1.f; g[3] = 1.f; g[4] = 1.f;
+    image_mask[(size_t)b * (R + 1)] = 1;
+  }
+}
+
+// features: zero the selected regions (`:906-907`), sum over regions in order (numpy reduces a
+// non-contiguous axis slice by slice), global feature = float32(float64 sum / int64 count) in front
+__global__ void prep_feat_kernel(const float* __restrict__ feat, const unsigned char* __restrict__ zero_flag,
+                                 const int* __restrict__ count0, int R, int F, float* __restrict__ out) {
+  const int b = blockIdx.y, c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= F) return;
+  float s = 0.f;
+  for (int r = 0; r < R; ++r) {
+    const float v = zero_flag[(size_t)b * R + r] ? 0.f : feat[((size_t)b * R + r) * F + c];
+    out[((size_t)b * (R + 1) + r + 1) * F + c] = v;
+    s = __fadd_rn(s, v);
+  }
+  out[(size_t)b * (R + 1) * F + c] = (float)((double)s / (double)count0[b]);
+}
+
+}  // namespace
+
+extern "C" int k3m_prep_title(const long long* tokens, const int* n_tok, const double* u, const long long* rnd, int B,
+                              int L, long long cls_id, long long sep_id, long long mask_id, long long* ids,
+                              long long* att, long long* seg, long long* labels, void* stream) {
+  K3M_REQUIRE(B > 0 && L >= 2, "prep_title: empty batch");
+  prep_title_kernel<<<B, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(tokens, n_tok, u, rnd, L, cls_id, sep_id,
+                                                                           mask_id, ids, att, seg, labels);
+  return k3m_check_launch("k3m_prep_title");
+}
+
+extern "C" int k3m_prep_pv(const long long* tokens, const int* n_tok, int B, int L, int max_num_pv, long long cls_id,
+                           long long sep_id, long long mask_id, long long* ids, long long* att, long long* seg,
+                           long long* labels, long long* index_p, long long* index_v, void* stream) {
+  K3M_REQUIRE(B > 0 && L >= 2 && max_num_pv > 0, "prep_pv: empty batch");
+  const size_t smem = (size_t)(2 * L + 1) * sizeof(int);
+  K3M_REQUIRE(smem <= 48 * 1024, "prep_pv: sequence too long (L=%d)", L);
+  prep_pv_kernel<<<B, 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tokens, n_tok, L, max_num_pv, cls_id, sep_id,
+                                                                           mask_id, ids, att, seg, labels, index_p,
+                                                                           index_v);
+  return k3m_check_launch("k3m_prep_pv");
+}
+
+extern "C" int k3m_prep_regions(const float* boxes, const int* num_boxes, const float* whp, const double* u,
+                                const float* feat, int B, int R, int F, float* image_feat, float* image_loc,
+                                long long* image_mask, long long* image_label, unsigned char* zero_flag, int* count0,
+                                void* stream) {
+  K3M_REQUIRE(B > 0 && R > 0 && F > 0, "prep_regions: empty batch");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const size_t smem = (size_t)R * (4 * sizeof(float) + 2 * sizeof(int));
+  K3M_REQUIRE(smem <= 48 * 1024, "prep_regions: too many regions (R=%d)", R);
+  prep_regions_kernel<<<B, 128, smem, st>>>(boxes, num_boxes, whp, u, R, image_loc, image_mask, image_label, zero_flag,
+                                            count0);
+  int rc = k3m_check_launch("k3m_prep_regions");
+  if (rc) return rc;
+  prep_feat_kernel<<<dim3((F + 255) / 256, B), 256, 0, st>>>(feat, zero_flag, count0, R, F, image_feat);
+  return k3m_check_launch("k3m_prep_regions(features)");
+}
