@@ -196,6 +196,38 @@ __global__ void prep_feat_kernel(const float* __restrict__ feat, const unsigned 
   out[(size_t)b * (R + 1) * F + c] = (float)((double)s / (double)count0[b]);
 }
 
+// same, 4 columns per thread through 16-byte accesses and 8 rows of loads in flight before the (ordered) adds
+__global__ void __launch_bounds__(128) prep_feat4_kernel(const float4* __restrict__ feat,
+                                                         const unsigned char* __restrict__ zero_flag,
+                                                         const int* __restrict__ count0, int R, int F4,
+                                                         float4* __restrict__ out) {
+  const int b = blockIdx.y, c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= F4) return;
+  const unsigned char* zf = zero_flag + (size_t)b * R;
+  const float4* src = feat + (size_t)b * R * F4 + c;
+  float4* dst = out + ((size_t)b * (R + 1) + 1) * F4 + c;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int r0 = 0; r0 < R; r0 += 8) {
+    float4 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r0 + k < R && !zf[r0 + k]) v[k] = __ldcs(src + (size_t)(r0 + k) * F4);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (r0 + k < R) {
+        __stcs(dst + (size_t)(r0 + k) * F4, v[k]);
+        s.x = __fadd_rn(s.x, v[k].x); s.y = __fadd_rn(s.y, v[k].y);
+        s.z = __fadd_rn(s.z, v[k].z); s.w = __fadd_rn(s.w, v[k].w);
+      }
+    }
+  }
+  const double n = (double)count0[b];
+  out[(size_t)b * (R + 1) * F4 + c] = make_float4((float)((double)s.x / n), (float)((double)s.y / n),
+                                                  (float)((double)s.z / n), (float)((double)s.w / n));
+}
+
 }  // namespace
 
 extern "C" int k3m_prep_title(const long long* tokens, const int* n_tok, const double* u, const long long* rnd, int B,
@@ -231,6 +263,11 @@ extern "C" int k3m_prep_regions(const float* boxes, const int* num_boxes, const 
                                             count0);
   int rc = k3m_check_launch("k3m_prep_regions");
   if (rc) return rc;
-  prep_feat_kernel<<<dim3((F + 255) / 256, B), 256, 0, st>>>(feat, zero_flag, count0, R, F, image_feat);
+  if (F % 4 == 0 && (((uintptr_t)feat | (uintptr_t)image_feat) & 15) == 0)
+    prep_feat4_kernel<<<dim3((F / 4 + 127) / 128, B), 128, 0, st>>>(reinterpret_cast<const float4*>(feat), zero_flag,
+                                                                    count0, R, F / 4,
+                                                                    reinterpret_cast<float4*>(image_feat));
+  else
+    prep_feat_kernel<<<dim3((F + 255) / 256, B), 256, 0, st>>>(feat, zero_flag, count0, R, F, image_feat);
   return k3m_check_launch("k3m_prep_regions(features)");
 }
