@@ -859,6 +859,7 @@ int dispatch(int bn, int ew, int ctas, const CUtensorMap& ma, const CUtensorMap&
              const CUtensorMap& mx, const CUtensorMap& mi, const GemmParams& p, cudaStream_t st) {
   if (bn == 64) return launch<64, 6, 1, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
   if (bn == 256 && ctas == 2) return launch<256, 5, 4, A_MN, B_MN, 2>(ma, mb, mc, mx, mi, p, st);
+  if (bn == 128 && ctas == 2) return launch<128, 6, 4, A_MN, B_MN, 2>(ma, mb, mc, mx, mi, p, st);
   if (bn == 256) return launch<256, 3, 4, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
   if (ew == 4) return launch<128, 5, 4, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
   return launch<128, 5, 2, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
@@ -903,6 +904,19 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
     if (mode_2cta == 2 || (accumulate ? (pt * 4 >= pairs && total_kb >= 32) : (pt * 5 >= pairs * 3))) {
       ctas = 2;
       bn = 256;
+      // wave quantisation: 108 pair tiles on 74 pairs are 2 waves at 73 % (M = 9216 x N = 768, M = 2304 x
+      // N = 3072), 76 tiles (M = 4736 x N = 1024) 2 waves at 51 %.  256 x 128 pair tiles (24 KB per k-block
+      // and CTA, 6 stages) halve the granule — and were measured SLOWER on every such shape (9216x768x3072:
+      // 40.5 -> 53.4 us; 2304x3072x768: 17.5 -> 19.8 us; step 22.2 -> 23.1 ms): they move 1.5x the operand
+      // bytes per flop, and bytes in flight, not the wave count, is what bounds these GEMMs.  Kept behind
+      // K3M_GEMM_P128=1 (rule) / 2 (always) as the record of that experiment; off by default.
+      static const int mode_p128 = getenv("K3M_GEMM_P128") ? atoi(getenv("K3M_GEMM_P128")) : 0;
+      if (mode_p128 && !accumulate) {
+        const long pt2 = (long)((M + 255) / 256) * ((N + 127) / 128);
+        const double e256 = (double)pt / (double)(pairs * ((pt + pairs - 1) / pairs));
+        const double e128 = 0.92 * (double)pt2 / (double)(pairs * ((pt2 + pairs - 1) / pairs));
+        if (mode_p128 == 2 || e128 > e256 + 0.04) bn = 128;
+      }
     }
   }
   CUtensorMap ma, mb;
@@ -945,7 +959,7 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   // epilogue warps: 16 (4 column groups) when the epilogue does real work per element, else 8
   static const int force_ew = getenv("K3M_GEMM_EW") ? atoi(getenv("K3M_GEMM_EW")) : 0;
   const bool heavy = act != ACT_NONE || p.drop.thresh != 0 || addend != nullptr;
-  const int ew = bn == 256 ? 4 : bn == 64 ? 1 : (force_ew ? force_ew : (heavy ? 4 : 2));
+  const int ew = (bn == 256 || ctas == 2) ? 4 : bn == 64 ? 1 : (force_ew ? force_ew : (heavy ? 4 : 2));
   const int cw = bn / ew;
   CUtensorMap mi = ma;
   p.tin = 0;
