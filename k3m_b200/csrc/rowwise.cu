@@ -82,7 +82,27 @@ __device__ __forceinline__ void unpack8(const uint4& u, float v[8]) {
 // dx -> bf16; if drop_in is set a second output dxm = dx * mask_in * scale is written (gradient of
 // the GEMM output that was dropped out before the residual add).  Column sums: dgamma += dy*xhat,
 // dbeta += dy, dbias += dxm  (fp32 atomics, one set per CTA after a grid-stride loop over rows).
-template <int NV>
+// cluster helpers: the column sums of the CTAs of a cluster are combined through distributed shared memory
+__device__ __forceinline__ uint32_t cluster_rank_x() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_barrier() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ld_dsmem(const float* local, uint32_t rank) {
+  uint32_t a = (uint32_t)__cvta_generic_to_shared(local), ra;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(rank));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+  return v;
+}
+
+// CL = CTAs per cluster (1: no cluster).  With CL > 1 the per-CTA column sums meet in distributed shared
+// memory and each CTA of the cluster issues the atomics of 1/CL of the columns: CL x fewer same-address
+// atomics (296 CTAs adding into 768 addresses three times was most of the M = 2304 launches' time).
+template <int NV, int CL>
 __global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
                                                         const bf16* __restrict__ gamma, const float* __restrict__ mean_in,
                                                         const float* __restrict__ rstd_in, bf16* __restrict__ dx,
@@ -189,8 +209,26 @@ __global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const bf16
     float t = 0.f;
 #pragma unroll
     for (int w = 0; w < 8; ++w) t += sred[(size_t)w * 3 * H + idx];
-    float* dst = idx < H ? dgamma + idx : (idx < 2 * H ? dbeta + (idx - H) : dbias + (idx - 2 * H));
-    atomicAdd(dst, t);
+    if (CL > 1) {
+      sred[idx] = t;                 // slot of warp 0: this thread is the only reader and writer of element idx
+    } else {
+      float* dst = idx < H ? dgamma + idx : (idx < 2 * H ? dbeta + (idx - H) : dbias + (idx - 2 * H));
+      atomicAdd(dst, t);
+    }
+  }
+  if (CL > 1) {
+    cluster_barrier();               // every CTA's totals are in its sred[0 .. nsets*H)
+    const uint32_t rank = cluster_rank_x();
+    const int n = nsets * H, chunk = (n + CL - 1) / CL;
+    const int hi = (int)(rank + 1) * chunk < n ? (int)(rank + 1) * chunk : n;
+    for (int idx = (int)rank * chunk + threadIdx.x; idx < hi; idx += blockDim.x) {
+      float t = 0.f;
+#pragma unroll
+      for (int r = 0; r < CL; ++r) t += ld_dsmem(sred + idx, (uint32_t)r);
+      float* dst = idx < H ? dgamma + idx : (idx < 2 * H ? dbeta + (idx - H) : dbias + (idx - 2 * H));
+      atomicAdd(dst, t);
+    }
+    cluster_barrier();               // nobody leaves while its shared memory is still being read
   }
 }
 
@@ -372,17 +410,39 @@ extern "C" int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, cons
   K3M_REQUIRE(!din.thresh || dxm, "ln_bwd: drop_in needs the dxm output");
   int grid = (M + 7) / 8;
   if (grid > 148 * 2) grid = 148 * 2;            // two resident CTAs per SM
+  static const int use_cluster = getenv("K3M_LN_CLUSTER") ? atoi(getenv("K3M_LN_CLUSTER")) : 1;
+  constexpr int CL = 8;
+  const bool cl = use_cluster && grid >= 2 * CL;
+  if (cl) grid = (grid + CL - 1) / CL * CL;      // whole clusters (CTAs without rows add zeros)
   const size_t smem = (size_t)8 * 3 * H * sizeof(float);
   const int nv = (H + 255) / 256;
 #define LN_BWD(NV)                                                                                                   \
   do {                                                                                                               \
     static bool cfg = false;                                                                                         \
     if (!cfg) {                                                                                                      \
-      cudaFuncSetAttribute(ln_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 3 * 1024 * 4);        \
+      cudaFuncSetAttribute(ln_bwd_kernel<NV, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 3 * 1024 * 4);     \
+      cudaFuncSetAttribute(ln_bwd_kernel<NV, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 3 * 1024 * 4);    \
       cfg = true;                                                                                                    \
     }                                                                                                                \
-    ln_bwd_kernel<NV><<<grid, 256, smem, st>>>((const bf16*)dy, (const bf16*)x, (const bf16*)gamma, mean, rstd,       \
-                                               (bf16*)dx, (bf16*)dxm, dgamma, dbeta, dbias, M, H, dout, din);         \
+    if (cl) {                                                                                                        \
+      cudaLaunchConfig_t lc = {};                                                                                    \
+      lc.gridDim = dim3(grid);                                                                                       \
+      lc.blockDim = dim3(256);                                                                                       \
+      lc.dynamicSmemBytes = smem;                                                                                    \
+      lc.stream = st;                                                                                                \
+      cudaLaunchAttribute at[1];                                                                                     \
+      at[0].id = cudaLaunchAttributeClusterDimension;                                                                \
+      at[0].val.clusterDim.x = CL;                                                                                   \
+      at[0].val.clusterDim.y = 1;                                                                                    \
+      at[0].val.clusterDim.z = 1;                                                                                    \
+      lc.attrs = at;                                                                                                 \
+      lc.numAttrs = 1;                                                                                               \
+      cudaLaunchKernelEx(&lc, ln_bwd_kernel<NV, CL>, (const bf16*)dy, (const bf16*)x, (const bf16*)gamma, mean, rstd, \
+                         (bf16*)dx, (bf16*)dxm, dgamma, dbeta, dbias, M, H, dout, din);                              \
+    } else {                                                                                                         \
+      ln_bwd_kernel<NV, 1><<<grid, 256, smem, st>>>((const bf16*)dy, (const bf16*)x, (const bf16*)gamma, mean, rstd,  \
+                                                    (bf16*)dx, (bf16*)dxm, dgamma, dbeta, dbias, M, H, dout, din);   \
+    }                                                                                                                \
   } while (0)
   if (nv <= 1) LN_BWD(1);
   else if (nv <= 2) LN_BWD(2);
