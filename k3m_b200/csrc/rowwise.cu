@@ -101,7 +101,7 @@ __device__ __forceinline__ float ld_dsmem(const float* local, uint32_t rank) {
 
 // CL = CTAs per cluster (1: no cluster).  With CL > 1 the per-CTA column sums meet in distributed shared
 // memory and each CTA of the cluster issues the atomics of 1/CL of the columns: CL x fewer same-address
-// atomics (296 CTAs adding into 768 addresses three times was most of the M = 2304 launches' time).
+// atomics.  An experiment that did not pay (see k3m_ln_bwd below); selectable with K3M_LN_CLUSTER=1.
 template <int NV, int CL>
 __global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
                                                         const bf16* __restrict__ gamma, const float* __restrict__ mean_in,
@@ -410,7 +410,9 @@ extern "C" int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, cons
   K3M_REQUIRE(!din.thresh || dxm, "ln_bwd: drop_in needs the dxm output");
   int grid = (M + 7) / 8;
   if (grid > 148 * 2) grid = 148 * 2;            // two resident CTAs per SM
-  static const int use_cluster = getenv("K3M_LN_CLUSTER") ? atoi(getenv("K3M_LN_CLUSTER")) : 1;
+  // measured: with clusters of 8 the 113 launches of a step take 4.58 ms instead of 3.20 ms (cluster
+  // co-scheduling and two cluster barriers cost more than the 8x fewer atomics save) -> off by default
+  static const int use_cluster = getenv("K3M_LN_CLUSTER") ? atoi(getenv("K3M_LN_CLUSTER")) : 0;
   constexpr int CL = 8;
   const bool cl = use_cluster && grid >= 2 * CL;
   if (cl) grid = (grid + CL - 1) / CL * CL;      // whole clusters (CTAs without rows add zeros)
