@@ -40,6 +40,30 @@ __device__ __forceinline__ void load_tile_z(bf16* dst, const bf16* src, int ld, 
   }
 }
 
+// asynchronous global -> shared copies (LDGSTS): the next block streams in while the tensor cores work on
+// the current one; src-size 0 zero-fills rows beyond the sequence
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, bool valid) {
+  const int sz = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_addr(dst)), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* dst, const void* src, bool valid) {
+  const int sz = valid ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_addr(dst)), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int D, int DS>
+__device__ __forceinline__ void load_tile_async(bf16* dst, const bf16* src, int ld, int valid, int rows) {
+  constexpr int VPR = D / 8;
+  for (int idx = threadIdx.x; idx < rows * VPR; idx += blockDim.x) {
+    const int r = idx / VPR, c = (idx % VPR) * 8;
+    const bool ok = r < valid;
+    cp_async16(dst + (size_t)r * DS + c, ok ? src + (size_t)r * ld + c : src, ok);
+  }
+}
+
 // acc[t] (16 x 8 per key tile t) += A(16 x D rows i0.. of As) * B^T, B = rows of Bs (keys), both [.][DS]
 template <int D, int DS, int NKT>
 __device__ __forceinline__ void qk_mma(float (*acc)[4], const bf16* As, int i0, const bf16* Bs, int lane) {
@@ -119,13 +143,17 @@ __global__ void __launch_bounds__(256) attn_fwd_mma(AttnArgs a, bf16* __restrict
   bf16* Vs = Ks + (size_t)LKP * DS;
   constexpr int NTP = NKT <= 8 ? 8 : 16;
   uint8_t* mw = reinterpret_cast<uint8_t*>(Vs + (size_t)LKP * DS) + warp * 16 * NTP;
-  load_tile_z<D, DS>(Qs, a.q + (size_t)b * Lq * a.ldq + a.q_off + h * D, a.ldq, Lq, LQP);
-  load_tile_z<D, DS>(Ks, a.kv + (size_t)b * Lk * a.ldkv + a.k_off + h * D, a.ldkv, Lk, LKP);
-  load_tile_z<D, DS>(Vs, a.kv + (size_t)b * Lk * a.ldkv + a.v_off + h * D, a.ldkv, Lk, LKP);
+  // all three tiles in flight at once (cp.async): a register-staged copy loop serialises one global-load
+  // latency per 16 bytes and thread, which was most of this CTA's life
+  load_tile_async<D, DS>(Qs, a.q + (size_t)b * Lq * a.ldq + a.q_off + h * D, a.ldq, Lq, LQP);
+  load_tile_async<D, DS>(Ks, a.kv + (size_t)b * Lk * a.ldkv + a.k_off + h * D, a.ldkv, Lk, LKP);
+  load_tile_async<D, DS>(Vs, a.kv + (size_t)b * Lk * a.ldkv + a.v_off + h * D, a.ldkv, Lk, LKP);
+  cp_async_commit();
   const int g = lane >> 2, q = lane & 3, i0 = warp * 16;
   const int lkp = (Lk + 7) & ~7;
   if (a.drop.thresh)     // while the tile loads are in flight
     warp_drop_bits<NKT, NTP>(mw, a.drop, (unsigned long long)(b * a.H + h) * Lq + i0, Lq - i0, lkp, 0, lkp >> 3, lane);
+  cp_async_wait<0>();
   __syncthreads();
   float s[NKT][4];
 #pragma unroll
@@ -227,14 +255,16 @@ __global__ void __launch_bounds__(256) attn_bwd_mma(AttnArgs a, const bf16* __re
   bf16* Ss = Ps + (size_t)LQP * PS;      // [LQP][PS]  dS
   constexpr int NTP = NKT <= 8 ? 8 : 16;
   uint8_t* mw = reinterpret_cast<uint8_t*>(Ss + (size_t)LQP * PS) + warp * 16 * NTP;
-  load_tile_z<D, DS>(Qs, a.q + (size_t)b * Lq * a.ldq + a.q_off + h * D, a.ldq, Lq, LQP);
-  load_tile_z<D, DS>(dOs, dctx + (size_t)b * Lq * ldo + h * D, ldo, Lq, LQP);
-  load_tile_z<D, DS>(Ks, a.kv + (size_t)b * Lk * a.ldkv + a.k_off + h * D, a.ldkv, Lk, LKP);
-  load_tile_z<D, DS>(Vs, a.kv + (size_t)b * Lk * a.ldkv + a.v_off + h * D, a.ldkv, Lk, LKP);
+  load_tile_async<D, DS>(Qs, a.q + (size_t)b * Lq * a.ldq + a.q_off + h * D, a.ldq, Lq, LQP);
+  load_tile_async<D, DS>(dOs, dctx + (size_t)b * Lq * ldo + h * D, ldo, Lq, LQP);
+  load_tile_async<D, DS>(Ks, a.kv + (size_t)b * Lk * a.ldkv + a.k_off + h * D, a.ldkv, Lk, LKP);
+  load_tile_async<D, DS>(Vs, a.kv + (size_t)b * Lk * a.ldkv + a.v_off + h * D, a.ldkv, Lk, LKP);
+  cp_async_commit();
   const int g = lane >> 2, q = lane & 3, i0 = warp * 16;
   const int lkp = (Lk + 7) & ~7;
   if (a.drop.thresh)
     warp_drop_bits<NKT, NTP>(mw, a.drop, (unsigned long long)(b * a.H + h) * Lq + i0, Lq - i0, lkp, 0, lkp >> 3, lane);
+  cp_async_wait<0>();
   __syncthreads();
   {
     float s[NKT][4], dp[NKT][4];
@@ -366,30 +396,6 @@ __global__ void __launch_bounds__(256) attn_bwd_mma(AttnArgs a, const bf16* __re
 //             (stored in the second half of the lse buffer), a second for dQ; the dK / dV kernel computes the
 //             TRANSPOSED tiles S^T = K Q^T and dP^T = V dO^T directly, so no probabilities are staged.
 constexpr int LONG_BQ = 64, LONG_BK = 64;
-
-// asynchronous global -> shared copies (LDGSTS): the next block streams in while the tensor cores work on
-// the current one; src-size 0 zero-fills rows beyond the sequence
-__device__ __forceinline__ void cp_async16(void* dst, const void* src, bool valid) {
-  const int sz = valid ? 16 : 0;
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_addr(dst)), "l"(src), "r"(sz) : "memory");
-}
-__device__ __forceinline__ void cp_async4(void* dst, const void* src, bool valid) {
-  const int sz = valid ? 4 : 0;
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_addr(dst)), "l"(src), "r"(sz) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-template <int D, int DS>
-__device__ __forceinline__ void load_tile_async(bf16* dst, const bf16* src, int ld, int valid, int rows) {
-  constexpr int VPR = D / 8;
-  for (int idx = threadIdx.x; idx < rows * VPR; idx += blockDim.x) {
-    const int r = idx / VPR, c = (idx % VPR) * 8;
-    const bool ok = r < valid;
-    cp_async16(dst + (size_t)r * DS + c, ok ? src + (size_t)r * ld + c : src, ok);
-  }
-}
 
 template <int D>
 __global__ void __launch_bounds__(128) attn_fwd_long(AttnArgs a, bf16* __restrict__ ctx, int ldo,
