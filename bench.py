@@ -165,9 +165,10 @@ def kernel_breakdown(step, batch):
     # barrier), so the step runs as a single-rank step
     world, step.world = step.world, 1
     step.ops.timing = []
-    # keep the device ~100 ms behind the host: the event pairs then bracket kernels that run back to back,
-    # not the host's launch gaps (a ctypes launch costs more host time than a small kernel runs)
-    torch.cuda._sleep(int(2.0e8))
+    # keep the device ~400 ms behind the host for the WHOLE eager step (1215 launches at ~40 us of host time
+    # each outrun a 100 ms head start, after which the pairs of the late backward kernels measured the
+    # host's launch gaps): the event pairs then bracket kernels that run back to back
+    torch.cuda._sleep(int(8.0e8))
     step.step(batch)
     torch.cuda.synchronize()
     rows, step.ops.timing = step.ops.timing, None

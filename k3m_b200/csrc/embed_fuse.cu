@@ -43,8 +43,8 @@ __global__ void __launch_bounds__(128) embed_bwd_kernel(const bf16* __restrict__
 // out[m, n] = sum_k loc[m, k] w[n, k] + b[n],  k < 5
 __global__ void loc_fwd_kernel(const float* __restrict__ loc, const bf16* __restrict__ w, const bf16* __restrict__ b,
                                bf16* __restrict__ out, int M, int N) {
-  const size_t n = (size_t)M * N;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+  const unsigned n = (unsigned)(M * N);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = (int)(i / N), c = (int)(i % N);
     float acc = ld_f(b + c);
 #pragma unroll
@@ -76,8 +76,8 @@ __global__ void __launch_bounds__(128) loc_bwd_kernel(const bf16* __restrict__ d
 // cat[m] = [relu(a[m]) | relu(b[m]) | relu(c[m])]
 __global__ void relu_cat3_kernel(const bf16* a, int lda, const bf16* b, int ldb, const bf16* c, int ldc, bf16* out, int M, int H) {
   const int hv = H / 8;
-  const size_t n = (size_t)M * 3 * hv;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+  const unsigned n = (unsigned)(M * 3 * hv);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = (int)(i / (3 * hv)), r = (int)(i % (3 * hv)), k = r / hv, col = (r % hv) * 8;
     const bf16* src = k == 0 ? a + (size_t)m * lda : (k == 1 ? b + (size_t)m * ldb : c + (size_t)m * ldc);
     float v[8];
@@ -124,8 +124,8 @@ __device__ __forceinline__ void ysoft3(const float* gates, const float* noise, c
 
 __global__ void fuse_fwd_kernel(const bf16* __restrict__ cat, const float* __restrict__ gates, const float* __restrict__ noise,
                                 const unsigned long long* rng, unsigned int site, bf16* __restrict__ out, int ldo, int M, int H) {
-  const size_t n = (size_t)M * H;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+  const unsigned n = (unsigned)(M * H);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = (int)(i / H), h = (int)(i % H);
     float ak[3], y[3];
     int pick;
@@ -139,8 +139,8 @@ __global__ void fuse_bwd_kernel(const bf16* __restrict__ dout, int ldd, const bf
                                 const float* __restrict__ gates, const float* __restrict__ noise,
                                 const unsigned long long* rng, unsigned int site, bf16* __restrict__ dgates,
                                 bf16* __restrict__ dcat, int M, int H) {
-  const size_t n = (size_t)M * H;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+  const unsigned n = (unsigned)(M * H);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = (int)(i / H), h = (int)(i % H);
     float ak[3], y[3];
     int pick;
@@ -164,8 +164,8 @@ __global__ void fuse_bwd_kernel(const bf16* __restrict__ dout, int ldd, const bf
 // d{a,b,c}[m,h] += dcat[m, k*H + h] * (cat[m, k*H + h] > 0)
 __global__ void relu_split3_kernel(const bf16* __restrict__ dcat, const bf16* __restrict__ cat, bf16* da, int lda, bf16* db,
                                    int ldb, bf16* dc, int ldc, int M, int H) {
-  const size_t n = (size_t)M * 3 * H;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+  const unsigned n = (unsigned)(M * 3 * H);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = (int)(i / (3 * H)), r = (int)(i % (3 * H)), k = r / H, h = r % H;
     if (__bfloat162float(cat[i]) > 0.f) {
       bf16* dst = k == 0 ? da + (size_t)m * lda + h : (k == 1 ? db + (size_t)m * ldb + h : dc + (size_t)m * ldc + h);
@@ -187,8 +187,8 @@ __global__ void pool_fwd_kernel(const bf16* __restrict__ seq, int ld, TO* __rest
 
 // dseq[b*L + i, h] += dpool[b, h] / (L-1), i >= 1
 __global__ void pool_bwd_kernel(const float* __restrict__ dpool, bf16* __restrict__ dseq, int ld, int B, int L, int H) {
-  const size_t n = (size_t)B * L * H;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+  const unsigned n = (unsigned)(B * L * H);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int h = (int)(i % H);
     const int r = (int)(i / H), b = r / L, t = r % L;
     if (t == 0) continue;

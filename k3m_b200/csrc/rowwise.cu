@@ -331,6 +331,22 @@ __global__ void axpy_kernel(const TX* x, TY* y, float alpha, int rows, int cols,
   }
 }
 
+// 8 elements per thread through 16 / 32-byte accesses (cols, row strides multiples of 8, aligned bases)
+template <typename TX, typename TY>
+__global__ void axpy8_kernel(const TX* __restrict__ x, TY* __restrict__ y, float alpha, int rows, int cols8, int ldx,
+                             int ldy) {
+  const int n = rows * cols8;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int r = i / cols8, k = (i - r * cols8) * 8;
+    float a[8], b[8];
+    ld8(x + (size_t)r * ldx + k, a);
+    ld8(y + (size_t)r * ldy + k, b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) b[j] = fmaf(alpha, a[j], b[j]);
+    st8(y + (size_t)r * ldy + k, b);
+  }
+}
+
 __global__ void scale_kernel(float* x, float alpha, size_t n) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) x[i] *= alpha;
 }
@@ -507,6 +523,15 @@ extern "C" int k3m_lincomb3(const void* a, int lda, const void* b, int ldb, cons
 extern "C" int k3m_axpy(const void* x, int ldx, int x_f32, void* y, int ldy, int y_f32, float alpha, int rows, int cols,
                         void* stream) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  auto ok = [](const void* q, int ld, int f32) { return (((uintptr_t)q) & (f32 ? 31 : 15)) == 0 && ld % 8 == 0; };
+  if (cols % 8 == 0 && ok(x, ldx, x_f32) && ok(y, ldy, y_f32) && (size_t)rows * cols < (1u << 31)) {
+    const int g8 = grid_for((size_t)rows * cols / 8, 256);
+    if (x_f32 && y_f32) axpy8_kernel<float, float><<<g8, 256, 0, st>>>((const float*)x, (float*)y, alpha, rows, cols / 8, ldx, ldy);
+    else if (!x_f32 && !y_f32) axpy8_kernel<bf16, bf16><<<g8, 256, 0, st>>>((const bf16*)x, (bf16*)y, alpha, rows, cols / 8, ldx, ldy);
+    else if (x_f32) axpy8_kernel<float, bf16><<<g8, 256, 0, st>>>((const float*)x, (bf16*)y, alpha, rows, cols / 8, ldx, ldy);
+    else axpy8_kernel<bf16, float><<<g8, 256, 0, st>>>((const bf16*)x, (float*)y, alpha, rows, cols / 8, ldx, ldy);
+    return k3m_check_launch("k3m_axpy");
+  }
   const int g = grid_for((size_t)rows * cols, 256);
   if (x_f32 && y_f32) axpy_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, (float*)y, alpha, rows, cols, ldx, ldy);
   else if (!x_f32 && !y_f32) axpy_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)x, (bf16*)y, alpha, rows, cols, ldx, ldy);
