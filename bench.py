@@ -164,6 +164,9 @@ def kernel_breakdown(step, batch):
     # rank 0 profiles alone: no collective may be issued here (the other ranks are already at the final
     # barrier), so the step runs as a single-rank step
     world, step.world = step.world, 1
+    # ... and with the optimizer after backward instead of under it: AdamW saturates HBM, and a kernel timed
+    # while it runs on the other stream is not that kernel's duration (the 2 us axpy measured 38 us)
+    overlap_opt, step.overlap_opt = step.overlap_opt, False
     step.ops.timing = []
     # keep the device ~400 ms behind the host for the WHOLE eager step (1215 launches at ~40 us of host time
     # each outrun a 100 ms head start, after which the pairs of the late backward kernels measured the
@@ -174,6 +177,7 @@ def kernel_breakdown(step, batch):
     rows, step.ops.timing = step.ops.timing, None
     step.use_graph = use_graph
     step.world = world
+    step.overlap_opt = overlap_opt
     step.global_step -= 1
     for dst, src in zip((step.p32, step.m, step.v, step.w16, step.rng), snap):
         dst.copy_(src)
