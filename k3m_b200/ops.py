@@ -42,6 +42,7 @@ class CudaOps(object):
         # profiling aid (bench.py): when a list, every launch is bracketed by CUDA events on the
         # launching stream and (entry point, work, event pair) is appended; never on in the product path
         self.timing = None
+        self.record = None          # {entry point: [argument tuples]} while a measurement collects launches
         self._work = 0.0
         self._tag = ""
         self._side = []
@@ -124,6 +125,8 @@ class CudaOps(object):
 
     def _call(self, name, *args):
         self.launches += 1
+        if self.record is not None and name in self.record:
+            self.record[name].append(args)
         if self.timing is None:
             _lib.check(getattr(self.lib, name)(*args), name)
             return

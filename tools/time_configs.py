@@ -31,7 +31,7 @@ def time_step(step, batches, steps, warmup):
 
 def breakdown(step, batch, top=28):
     from bench import kernel_breakdown
-    rows = kernel_breakdown(step, batch)
+    rows, _ = kernel_breakdown(step, batch)
     tot = sum(v[1] for v in rows.values())
     sys.stderr.write("  eager step, %.2f ms of kernels in %d launches\n" % (tot, sum(v[0] for v in rows.values())))
     for name, (n, ms, fl) in sorted(rows.items(), key=lambda kv: -kv[1][1])[:top]:
