@@ -408,8 +408,11 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
 // (tile = (split, m, n), n fastest so neighbouring CTAs share the A panel in L2).  The smem ring
 // (TMA -> MMA) runs across tile boundaries and the accumulator is double-buffered in TMEM, so the
 // epilogue of tile i overlaps the main loop of tile i + 1.
+// STAGES == 2 marks the "dual" variant: a 2-stage ring and one staging buffer per epilogue warp keep a CTA
+// under 100 KB of shared memory and 256 TMEM columns, so TWO of them (of the same or of different launches)
+// share an SM — for the single-wave M = 2304 GEMMs that run concurrently on several streams.
 template <int BN, int STAGES, int EW, bool A_MN, bool B_MN, int CTAS>
-__global__ void __launch_bounds__(64 + 128 * EW, 1)
+__global__ void __launch_bounds__(64 + 128 * EW, STAGES <= 2 ? 2 : 1)
 gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
             const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_aux,
             const __grid_constant__ CUtensorMap map_in, GemmParams p) {
@@ -422,7 +425,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   constexpr int B_BYTES = BNL * BK * 2;
   constexpr int CW = BN / EW;
   static_assert(CW == 32 || CW == 64, "an epilogue warp owns 32 or 64 output columns");
-  constexpr int NBUF = EW <= 2 ? 2 : 1;        // staging buffers (4 KB each) per epilogue warp
+  constexpr int NBUF = (EW <= 2 && STAGES > 2) ? 2 : 1;        // staging buffers (4 KB each) per epilogue warp
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -801,7 +804,7 @@ template <int BN, int STAGES, int EW, bool A_MN, bool B_MN, int CTAS>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx,
            const CUtensorMap& mi, GemmParams p, cudaStream_t st) {
   // operand ring + epilogue staging (4*EW warps x NBUF x 4 KB) + barriers + 1 KB alignment slack
-  constexpr int NBUF = EW <= 2 ? 2 : 1;
+  constexpr int NBUF = (EW <= 2 && STAGES > 2) ? 2 : 1;
   constexpr int SMEM = STAGES * (BM * BK * 2 + (BN / CTAS) * BK * 2) + 4 * EW * NBUF * 4096 +
                        (2 * STAGES + 4 + 4 * EW) * 8 + 16 + 1024;
   static_assert(SMEM <= 227 * 1024, "shared memory budget");
@@ -817,7 +820,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
   p.tiles_m = (p.M + BM * CTAS - 1) / (BM * CTAS);
   p.tiles_n = (p.N + BN - 1) / BN;
   const int total = p.tiles_m * p.tiles_n * p.splits;
-  const int slots = num_sms() / CTAS;                 // CTAs (or CTA pairs) resident at once
+  const int slots = num_sms() * (STAGES <= 2 ? 2 : 1) / CTAS;     // CTAs (or CTA pairs) resident at once
   const int grid = (total < slots ? total : slots) * CTAS;
   static const int pdl = getenv("K3M_GEMM_PDL") ? atoi(getenv("K3M_GEMM_PDL")) : 0;
   if (CTAS == 1 && !pdl) {
@@ -861,6 +864,7 @@ int dispatch(int bn, int ew, int ctas, const CUtensorMap& ma, const CUtensorMap&
   if (bn == 256 && ctas == 2) return launch<256, 5, 4, A_MN, B_MN, 2>(ma, mb, mc, mx, mi, p, st);
   if (bn == 128 && ctas == 2) return launch<128, 6, 4, A_MN, B_MN, 2>(ma, mb, mc, mx, mi, p, st);
   if (bn == 256) return launch<256, 3, 4, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
+  if (ew == 0) return launch<128, 2, 2, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);      // dual: two CTAs per SM
   if (ew == 4) return launch<128, 5, 4, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
   return launch<128, 5, 2, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
 }
@@ -959,7 +963,19 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   // epilogue warps: 16 (4 column groups) when the epilogue does real work per element, else 8
   static const int force_ew = getenv("K3M_GEMM_EW") ? atoi(getenv("K3M_GEMM_EW")) : 0;
   const bool heavy = act != ACT_NONE || p.drop.thresh != 0 || addend != nullptr;
-  const int ew = (bn == 256 || ctas == 2) ? 4 : bn == 64 ? 1 : (force_ew ? force_ew : (heavy ? 4 : 2));
+  int ew = (bn == 256 || ctas == 2) ? 4 : bn == 64 ? 1 : (force_ew ? force_ew : (heavy ? 4 : 2));
+  // dual variant (K3M_GEMM_DUAL=1): single-wave 128-wide problems, where a CTA holds one tile and nothing of
+  // its prologue / epilogue overlaps anything unless another CTA shares the SM.  Measured: each launch gets
+  // slower alone (2304x768x768 8.4 -> 9.5 us; the step's GEMMs back to back 19.1 -> 20.5 ms) and the graph
+  // step, where launches of three streams do share SMs, stays at 21.7-21.8 ms: what the sharing wins the
+  // 2-stage ring loses.  Off by default.
+  static const int mode_dual = getenv("K3M_GEMM_DUAL") ? atoi(getenv("K3M_GEMM_DUAL")) : 0;
+  bool dual = false;
+  if (mode_dual && bn == 128 && ctas == 1) {
+    const long tiles = (long)((M + BM - 1) / BM) * ((N + 127) / 128) * p.splits;
+    dual = mode_dual == 2 || tiles <= num_sms();
+  }
+  if (dual) ew = 2;
   const int cw = bn / ew;
   CUtensorMap mi = ma;
   p.tin = 0;
@@ -993,7 +1009,7 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
       p.fast = F_DGELU;
     }
   }
-  if (layout == 0) return dispatch<false, false>(bn, ew, ctas, ma, mb, mc, mx, mi, p, st);
-  if (layout == 1) return dispatch<false, true>(bn, ew, ctas, ma, mb, mc, mx, mi, p, st);
-  return dispatch<true, true>(bn, ew, ctas, ma, mb, mc, mx, mi, p, st);
+  if (layout == 0) return dispatch<false, false>(bn, dual ? 0 : ew, ctas, ma, mb, mc, mx, mi, p, st);
+  if (layout == 1) return dispatch<false, true>(bn, dual ? 0 : ew, ctas, ma, mb, mc, mx, mi, p, st);
+  return dispatch<true, true>(bn, dual ? 0 : ew, ctas, ma, mb, mc, mx, mi, p, st);
 }
