@@ -200,11 +200,23 @@ class PretrainStep(object):
         (small) no-decay region as one last bucket."""
         L = self.layout
         step = max(1, int(bucket_mb * (1 << 20) // 4))
+        # the embedding tables open the arena and get their gradients last (their backward closes the step):
+        # they are a bucket of their own, so that only THEIR all-reduce + AdamW is left when backward ends
+        # instead of whatever piece of up to `bucket_mb` happened to straddle them
+        emb_end = 0
+        for n, (off, num, _) in L.offsets.items():
+            if off < L.decay_end and n.split(".")[0] in ("embeddings", "v_embeddings"):
+                emb_end = max(emb_end, off + num)
+        if any(off < emb_end and n.split(".")[0] not in ("embeddings", "v_embeddings")
+               for n, (off, num, _) in L.offsets.items()):
+            emb_end = 0                                    # not a clean prefix: fall back to uniform pieces
         out, hi = [], L.decay_end
-        while hi > 0:
-            lo = max(0, hi - step)
+        while hi > emb_end:
+            lo = max(emb_end, hi - step)
             out.append((lo, hi))
             hi = lo
+        if emb_end > 0:
+            out.append((0, emb_end))
         out.append((L.decay_end, L.trained_end))
         # stage prefix -> lowest decay-region offset of its parameters
         self._stage_lo = {}
