@@ -180,6 +180,17 @@ int k3m_prep_regions(const float* boxes, const int* num_boxes, const float* whp,
                      long long* image_mask, long long* image_label, unsigned char* zero_flag, int* count0,
                      void* stream);
 
+/* all of the above in two launches (title / PV / regions rows in one, the feature pass after it): what
+ * k3m_b200/preprocess.py calls per batch.  Arguments as in the three entry points above.                      */
+int k3m_prep_batch(const long long* tokens, const int* n_tok, const double* u_tok, const long long* rnd_tok,
+                   const long long* tokens_pv, const int* n_tok_pv, const float* boxes, const int* num_boxes,
+                   const float* whp, const double* u_reg, const float* feat, int B, int Lt, int Lpv, int R, int F,
+                   int max_num_pv, long long cls_id, long long sep_id, long long mask_id, long long* ids,
+                   long long* att, long long* seg, long long* labels, long long* ids_pv, long long* att_pv,
+                   long long* seg_pv, long long* labels_pv, long long* index_p, long long* index_v,
+                   float* image_feat, float* image_loc, long long* image_mask, long long* image_label,
+                   unsigned char* zero_flag, int* count0, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

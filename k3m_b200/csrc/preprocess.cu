@@ -14,12 +14,12 @@ namespace {
 constexpr int PV_COLON = 131, PV_SEMI = 132;   // ":" and ";" of the PV string (`:785-790`)
 
 // ---- title: mask_word (`:763-783`) + specials + padding (`:664-690`) ------------------------------------
-__global__ void prep_title_kernel(const long long* __restrict__ tokens, const int* __restrict__ n_tok,
+__device__ void prep_title_body(int b, const long long* __restrict__ tokens, const int* __restrict__ n_tok,
                                   const double* __restrict__ u, const long long* __restrict__ rnd, int L,
                                   long long cls_id, long long sep_id, long long mask_id,
                                   long long* __restrict__ ids, long long* __restrict__ att,
                                   long long* __restrict__ seg, long long* __restrict__ labels) {
-  const int b = blockIdx.x, n = n_tok[b] < L - 2 ? n_tok[b] : L - 2;
+  const int n = n_tok[b] < L - 2 ? n_tok[b] : L - 2;
   for (int i = threadIdx.x; i < L; i += blockDim.x) {
     long long id = 0, lab = -1, m = 0;
     if (i == 0) { id = cls_id; m = 1; }
@@ -44,15 +44,14 @@ __global__ void prep_title_kernel(const long long* __restrict__ tokens, const in
 // ---- PV: mask_word_pv (`:815-839`) + specials + index_pv (`:785-813`) -----------------------------------
 // The pairing rules are sequential list surgery (drop-first, zip to the shorter list, early stop), so one
 // thread walks the row; the row is at most a few hundred tokens and the kernel runs B rows in parallel.
-__global__ void prep_pv_kernel(const long long* __restrict__ tokens, const int* __restrict__ n_tok, int L,
+__device__ void prep_pv_body(int b, int* sh, const long long* __restrict__ tokens, const int* __restrict__ n_tok, int L,
                                int max_num_pv, long long cls_id, long long sep_id, long long mask_id,
                                long long* __restrict__ ids, long long* __restrict__ att, long long* __restrict__ seg,
                                long long* __restrict__ labels, long long* __restrict__ index_p,
                                long long* __restrict__ index_v) {
-  extern __shared__ int sh[];                 // [L] positions of 131, [L + 1] positions of 132
-  int* p131 = sh;
+  int* p131 = sh;                             // [L] positions of 131, [L + 1] positions of 132
   int* p132 = sh + L;
-  const int b = blockIdx.x, n = n_tok[b] < L - 2 ? n_tok[b] : L - 2;
+  const int n = n_tok[b] < L - 2 ? n_tok[b] : L - 2;
   const long long* tk = tokens + (size_t)b * L;
   long long* o_ids = ids + (size_t)b * L;
   long long* o_lab = labels + (size_t)b * L;
@@ -115,17 +114,16 @@ __device__ __forceinline__ float box_area(const float* bx) {
   return __fmul_rn(__fadd_rn(__fsub_rn(bx[2], bx[0]), 1.0f), __fadd_rn(__fsub_rn(bx[3], bx[1]), 1.0f));
 }
 
-__global__ void prep_regions_kernel(const float* __restrict__ boxes, const int* __restrict__ num_boxes,
+__device__ void prep_regions_body(int b, float* shf, const float* __restrict__ boxes, const int* __restrict__ num_boxes,
                                     const float* __restrict__ whp, const double* __restrict__ u, int R,
                                     float* __restrict__ image_loc, long long* __restrict__ image_mask,
                                     long long* __restrict__ image_label, unsigned char* __restrict__ zero_flag,
                                     int* __restrict__ count0) {
-  extern __shared__ float shf[];              // [R][4] boxes, then int sel[R], masked[R]
-  float* bx = shf;
+  float* bx = shf;                            // [R][4] boxes, then int sel[R], masked[R]
   int* sel = reinterpret_cast<int*>(shf + 4 * R);
   int* msk = sel + R;
   __shared__ int cnt;
-  const int b = blockIdx.x, nb = num_boxes[b];
+  const int nb = num_boxes[b];
   const float w = whp[b * 3 + 0], h = whp[b * 3 + 1], wh = whp[b * 3 + 2];
   if (threadIdx.x == 0) cnt = 0;
   for (int r = threadIdx.x; r < R; r += blockDim.x) {
@@ -181,6 +179,36 @@ __global__ void prep_regions_kernel(const float* __restrict__ boxes, const int* 
   }
 }
 
+// One launch for the three row-wise jobs (blockIdx.y + job0: 0 title, 1 PV string, 2 regions): they are
+// microseconds of work each, so a launch apiece was most of their time.
+struct PrepArgs {
+  const long long *tokens, *rnd, *tokens_pv;
+  const int *n_tok, *n_tok_pv, *num_boxes;
+  const double *u_tok, *u_reg;
+  const float *boxes, *whp;
+  long long *ids, *att, *seg, *labels, *ids_pv, *att_pv, *seg_pv, *labels_pv, *index_p, *index_v;
+  float* image_loc;
+  long long *image_mask, *image_label;
+  unsigned char* zero_flag;
+  int* count0;
+  long long cls_id, sep_id, mask_id;
+  int Lt, Lpv, R, max_num_pv;
+};
+
+__global__ void __launch_bounds__(128) prep_rows_kernel(PrepArgs a, int job0) {
+  extern __shared__ __align__(16) unsigned char dyn[];
+  const int b = blockIdx.x, job = job0 + blockIdx.y;
+  if (job == 0)
+    prep_title_body(b, a.tokens, a.n_tok, a.u_tok, a.rnd, a.Lt, a.cls_id, a.sep_id, a.mask_id, a.ids, a.att, a.seg,
+                    a.labels);
+  else if (job == 1)
+    prep_pv_body(b, reinterpret_cast<int*>(dyn), a.tokens_pv, a.n_tok_pv, a.Lpv, a.max_num_pv, a.cls_id, a.sep_id,
+                 a.mask_id, a.ids_pv, a.att_pv, a.seg_pv, a.labels_pv, a.index_p, a.index_v);
+  else
+    prep_regions_body(b, reinterpret_cast<float*>(dyn), a.boxes, a.num_boxes, a.whp, a.u_reg, a.R, a.image_loc,
+                      a.image_mask, a.image_label, a.zero_flag, a.count0);
+}
+
 // features: zero the selected regions (`:906-907`), sum over regions in order (numpy reduces a
 // non-contiguous axis slice by slice), global feature = float32(float64 sum / int64 count) in front
 __global__ void prep_feat_kernel(const float* __restrict__ feat, const unsigned char* __restrict__ zero_flag,
@@ -228,14 +256,33 @@ __global__ void __launch_bounds__(128) prep_feat4_kernel(const float4* __restric
                                                   (float)((double)s.z / n), (float)((double)s.w / n));
 }
 
+int launch_feat(const float* feat, const unsigned char* zero_flag, const int* count0, int B, int R, int F,
+                float* image_feat, cudaStream_t st) {
+  if (F % 4 == 0 && (((uintptr_t)feat | (uintptr_t)image_feat) & 15) == 0)
+    prep_feat4_kernel<<<dim3((F / 4 + 127) / 128, B), 128, 0, st>>>(reinterpret_cast<const float4*>(feat), zero_flag,
+                                                                    count0, R, F / 4,
+                                                                    reinterpret_cast<float4*>(image_feat));
+  else
+    prep_feat_kernel<<<dim3((F + 255) / 256, B), 256, 0, st>>>(feat, zero_flag, count0, R, F, image_feat);
+  return k3m_check_launch("k3m_prep_regions(features)");
+}
+
+size_t rows_smem(int Lpv, int R) {
+  const size_t a = (size_t)(2 * Lpv + 1) * sizeof(int), b = (size_t)R * (4 * sizeof(float) + 2 * sizeof(int));
+  return a > b ? a : b;
+}
+
 }  // namespace
 
 extern "C" int k3m_prep_title(const long long* tokens, const int* n_tok, const double* u, const long long* rnd, int B,
                               int L, long long cls_id, long long sep_id, long long mask_id, long long* ids,
                               long long* att, long long* seg, long long* labels, void* stream) {
   K3M_REQUIRE(B > 0 && L >= 2, "prep_title: empty batch");
-  prep_title_kernel<<<B, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(tokens, n_tok, u, rnd, L, cls_id, sep_id,
-                                                                           mask_id, ids, att, seg, labels);
+  PrepArgs a = {};
+  a.tokens = tokens; a.n_tok = n_tok; a.u_tok = u; a.rnd = rnd; a.Lt = L;
+  a.cls_id = cls_id; a.sep_id = sep_id; a.mask_id = mask_id;
+  a.ids = ids; a.att = att; a.seg = seg; a.labels = labels;
+  prep_rows_kernel<<<dim3(B, 1), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, 0);
   return k3m_check_launch("k3m_prep_title");
 }
 
@@ -243,11 +290,13 @@ extern "C" int k3m_prep_pv(const long long* tokens, const int* n_tok, int B, int
                            long long sep_id, long long mask_id, long long* ids, long long* att, long long* seg,
                            long long* labels, long long* index_p, long long* index_v, void* stream) {
   K3M_REQUIRE(B > 0 && L >= 2 && max_num_pv > 0, "prep_pv: empty batch");
-  const size_t smem = (size_t)(2 * L + 1) * sizeof(int);
+  const size_t smem = rows_smem(L, 0);
   K3M_REQUIRE(smem <= 48 * 1024, "prep_pv: sequence too long (L=%d)", L);
-  prep_pv_kernel<<<B, 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(tokens, n_tok, L, max_num_pv, cls_id, sep_id,
-                                                                           mask_id, ids, att, seg, labels, index_p,
-                                                                           index_v);
+  PrepArgs a = {};
+  a.tokens_pv = tokens; a.n_tok_pv = n_tok; a.Lpv = L; a.max_num_pv = max_num_pv;
+  a.cls_id = cls_id; a.sep_id = sep_id; a.mask_id = mask_id;
+  a.ids_pv = ids; a.att_pv = att; a.seg_pv = seg; a.labels_pv = labels; a.index_p = index_p; a.index_v = index_v;
+  prep_rows_kernel<<<dim3(B, 1), 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(a, 1);
   return k3m_check_launch("k3m_prep_pv");
 }
 
@@ -257,17 +306,43 @@ extern "C" int k3m_prep_regions(const float* boxes, const int* num_boxes, const 
                                 void* stream) {
   K3M_REQUIRE(B > 0 && R > 0 && F > 0, "prep_regions: empty batch");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  const size_t smem = (size_t)R * (4 * sizeof(float) + 2 * sizeof(int));
+  const size_t smem = rows_smem(0, R);
   K3M_REQUIRE(smem <= 48 * 1024, "prep_regions: too many regions (R=%d)", R);
-  prep_regions_kernel<<<B, 128, smem, st>>>(boxes, num_boxes, whp, u, R, image_loc, image_mask, image_label, zero_flag,
-                                            count0);
+  PrepArgs a = {};
+  a.boxes = boxes; a.num_boxes = num_boxes; a.whp = whp; a.u_reg = u; a.R = R;
+  a.image_loc = image_loc; a.image_mask = image_mask; a.image_label = image_label;
+  a.zero_flag = zero_flag; a.count0 = count0;
+  prep_rows_kernel<<<dim3(B, 1), 128, smem, st>>>(a, 2);
   int rc = k3m_check_launch("k3m_prep_regions");
   if (rc) return rc;
-  if (F % 4 == 0 && (((uintptr_t)feat | (uintptr_t)image_feat) & 15) == 0)
-    prep_feat4_kernel<<<dim3((F / 4 + 127) / 128, B), 128, 0, st>>>(reinterpret_cast<const float4*>(feat), zero_flag,
-                                                                    count0, R, F / 4,
-                                                                    reinterpret_cast<float4*>(image_feat));
-  else
-    prep_feat_kernel<<<dim3((F + 255) / 256, B), 256, 0, st>>>(feat, zero_flag, count0, R, F, image_feat);
-  return k3m_check_launch("k3m_prep_regions(features)");
+  return launch_feat(feat, zero_flag, count0, B, R, F, image_feat, st);
+}
+
+extern "C" int k3m_prep_batch(const long long* tokens, const int* n_tok, const double* u_tok, const long long* rnd_tok,
+                              const long long* tokens_pv, const int* n_tok_pv, const float* boxes,
+                              const int* num_boxes, const float* whp, const double* u_reg, const float* feat, int B,
+                              int Lt, int Lpv, int R, int F, int max_num_pv, long long cls_id, long long sep_id,
+                              long long mask_id, long long* ids, long long* att, long long* seg, long long* labels,
+                              long long* ids_pv, long long* att_pv, long long* seg_pv, long long* labels_pv,
+                              long long* index_p, long long* index_v, float* image_feat, float* image_loc,
+                              long long* image_mask, long long* image_label, unsigned char* zero_flag, int* count0,
+                              void* stream) {
+  K3M_REQUIRE(B > 0 && Lt >= 2 && Lpv >= 2 && R > 0 && F > 0 && max_num_pv > 0, "prep_batch: empty batch");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const size_t smem = rows_smem(Lpv, R);
+  K3M_REQUIRE(smem <= 48 * 1024, "prep_batch: sequence / region count too large (Lpv=%d R=%d)", Lpv, R);
+  PrepArgs a = {};
+  a.tokens = tokens; a.n_tok = n_tok; a.u_tok = u_tok; a.rnd = rnd_tok; a.Lt = Lt;
+  a.tokens_pv = tokens_pv; a.n_tok_pv = n_tok_pv; a.Lpv = Lpv; a.max_num_pv = max_num_pv;
+  a.boxes = boxes; a.num_boxes = num_boxes; a.whp = whp; a.u_reg = u_reg; a.R = R;
+  a.cls_id = cls_id; a.sep_id = sep_id; a.mask_id = mask_id;
+  a.ids = ids; a.att = att; a.seg = seg; a.labels = labels;
+  a.ids_pv = ids_pv; a.att_pv = att_pv; a.seg_pv = seg_pv; a.labels_pv = labels_pv;
+  a.index_p = index_p; a.index_v = index_v;
+  a.image_loc = image_loc; a.image_mask = image_mask; a.image_label = image_label;
+  a.zero_flag = zero_flag; a.count0 = count0;
+  prep_rows_kernel<<<dim3(B, 3), 128, smem, st>>>(a, 0);
+  int rc = k3m_check_launch("k3m_prep_batch");
+  if (rc) return rc;
+  return launch_feat(feat, zero_flag, count0, B, R, F, image_feat, st);
 }

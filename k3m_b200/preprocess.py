@@ -59,7 +59,9 @@ class GpuBatchPreprocessor(object):
         self.max_num_pv, self.vocab = max_num_pv, vocab_size
         self.gen = torch.Generator(device=self.device).manual_seed(seed)
 
-    def __call__(self, raw, draws=None):
+    def __call__(self, raw, draws=None, fused=True):
+        """`fused=False` goes through the three per-job entry points (one launch each) instead of
+        `k3m_prep_batch`; same results."""
         dev, i64 = self.device, torch.int64
         B, Lt = raw["tokens"].shape
         Lpv = raw["tokens_pv"].shape[1]
@@ -76,6 +78,17 @@ class GpuBatchPreprocessor(object):
                    image_feat=e(B, R + 1, F, dtype=torch.float32), image_loc=e(B, R + 1, 5, dtype=torch.float32),
                    image_attention_mask=e(B, R + 1), image_label=e(B, R), image_target=raw["targets"])
         zero_flag, count0 = e(B, R, dtype=torch.uint8), e(B, dtype=torch.int32)
+        if fused:
+            _lib.check(self.lib.k3m_prep_batch(
+                _p(raw["tokens"]), _p(raw["n_tok"]), _p(draws["u_tok"]), _p(draws["rnd_tok"]), _p(raw["tokens_pv"]),
+                _p(raw["n_tok_pv"]), _p(raw["boxes"]), _p(raw["num_boxes"]), _p(raw["whp"]), _p(draws["u_reg"]),
+                _p(raw["features"]), _i(B), _i(Lt), _i(Lpv), _i(R), _i(F), _i(self.max_num_pv), _ll(CLS), _ll(SEP),
+                _ll(MASK), _p(out["input_ids"]), _p(out["attention_mask"]), _p(out["token_type_ids"]),
+                _p(out["masked_lm_labels"]), _p(out["input_ids_pv"]), _p(out["attention_mask_pv"]),
+                _p(out["token_type_ids_pv"]), _p(out["masked_lm_labels_pv"]), _p(out["index_p"]), _p(out["index_v"]),
+                _p(out["image_feat"]), _p(out["image_loc"]), _p(out["image_attention_mask"]), _p(out["image_label"]),
+                _p(zero_flag), _p(count0), st), "k3m_prep_batch")
+            return self._finish(out, B)
         _lib.check(self.lib.k3m_prep_title(_p(raw["tokens"]), _p(raw["n_tok"]), _p(draws["u_tok"]), _p(draws["rnd_tok"]),
                                            _i(B), _i(Lt), _ll(CLS), _ll(SEP), _ll(MASK), _p(out["input_ids"]),
                                            _p(out["attention_mask"]), _p(out["token_type_ids"]),
@@ -89,7 +102,10 @@ class GpuBatchPreprocessor(object):
                                              _p(raw["features"]), _i(B), _i(R), _i(F), _p(out["image_feat"]),
                                              _p(out["image_loc"]), _p(out["image_attention_mask"]),
                                              _p(out["image_label"]), _p(zero_flag), _p(count0), st), "k3m_prep_regions")
+        return self._finish(out, B)
+
+    def _finish(self, out, B):
         # the three ITM labels are constant 0 in this loader (`:606`)
-        z = torch.zeros(B, dtype=i64, device=dev)
+        z = torch.zeros(B, dtype=torch.int64, device=self.device)
         out.update(next_sentence_label=z, next_sentence_label_pv_v=z, next_sentence_label_pv_t=z)
         return out

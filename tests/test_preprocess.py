@@ -51,23 +51,25 @@ def synth_raws(rng, B, Lt, Lpv, R, F, T, max_num_pv):
     return raws, draw(B, Lt), rng.randint(0, 21128, (B, Lt)), draw(B, R)
 
 
-def run_gpu(raws, u_tok, rnd_tok, u_reg, Lt, Lpv, R, max_num_pv):
+def run_gpu(raws, u_tok, rnd_tok, u_reg, Lt, Lpv, R, max_num_pv, fused=True):
     from k3m_b200.preprocess import GpuBatchPreprocessor, pack_raw_batch
     raw = pack_raw_batch(raws, Lt, Lpv, R, device="cuda")
     draws = dict(u_tok=torch.from_numpy(np.ascontiguousarray(u_tok, np.float64)).cuda(),
                  rnd_tok=torch.from_numpy(np.ascontiguousarray(rnd_tok, np.int64)).cuda(),
                  u_reg=torch.from_numpy(np.ascontiguousarray(u_reg, np.float64)).cuda())
-    out = GpuBatchPreprocessor(max_num_pv)(raw, draws)
+    out = GpuBatchPreprocessor(max_num_pv)(raw, draws, fused=fused)
     torch.cuda.synchronize()
     return {k: v.cpu().numpy() for k, v in out.items()}
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("name", CASES)
-def test_kernels_match_reference_bit_for_bit(name):
+def test_kernels_match_reference_bit_for_bit(name, fused):
     fx = load_golden(name)
     d = fx["dims"]
-    got = run_gpu(fx["raws"], fx["u_tok"], fx["rnd_tok"], fx["u_reg"], d["Lt"], d["Lpv"], d["R"], d["max_num_pv"])
+    got = run_gpu(fx["raws"], fx["u_tok"], fx["rnd_tok"], fx["u_reg"], d["Lt"], d["Lpv"], d["R"], d["max_num_pv"],
+                  fused=fused)
     for k, w in fx["want"].items():
         if k == "item_id":
             continue

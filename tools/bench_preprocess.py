@@ -54,7 +54,7 @@ def main():
     for _ in range(reps):
         preprocess_batch(raws, u_tok, rnd_tok, u_reg, Lt, Lpv, R, P)
     cpu_s = (time.perf_counter() - t0) / reps
-    print(json.dumps({"what": "GPU batch preprocessing, B=64, 36/36+1/36 tokens, 2048-d features (4 kernels)",
+    print(json.dumps({"what": "GPU batch preprocessing, B=64, 36/36+1/36 tokens, 2048-d features (2 launches: k3m_prep_batch)",
                       "us_per_batch": round(us, 2), "samples_per_s": round(B / us * 1e6),
                       "roofline": {"bound": "hbm", "achieved": round(bytes_alg / us / 1e3, 1), "peak": peak,
                                    "unit": "GB/s", "frac": round(bytes_alg / us / 1e3 / peak, 3),
