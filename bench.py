@@ -140,8 +140,8 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    steps = max(1, min(args.steps, 3))
-    warm = 1
+    steps = max(1, min(args.steps, 10))           # ~1.4 s per step on the GPU box's 16 cores: bounded to ~15 s
+    warm = max(1, min(args.warmup, 2))
     v, sec, threads, batch = cpu_reference_step_rate(steps, warm)
     sample = "%d step(s) of batch %d (BASELINE configs[0]) after %d warm-up, fp32, %d threads" % (steps, batch, warm, threads)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
@@ -358,9 +358,9 @@ def run_gpu_arm(args):
         "losses_first": loss0, "losses_last": last,
     }
     if world == 1 and not args.no_cpu_baseline:
-        v, sec, threads, batch = cpu_reference_step_rate(2, 1)
+        v, sec, threads, batch = cpu_reference_step_rate(8, 2)       # ~10-15 s of host work on the GPU box
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": "2 steps of batch %d (BASELINE configs[0]) after 1 warm-up: oracle port "
+                                "sample": "8 steps of batch %d (BASELINE configs[0]) after 2 warm-ups: oracle port "
                                           "(fp32 autograd restatement + torch.optim.AdamW), %.1f s/step" % (batch, sec)}
     print(json.dumps(line))
     finish()
