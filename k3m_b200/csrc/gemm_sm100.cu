@@ -47,6 +47,7 @@ struct GemmParams {
   int vec_ok;  // all epilogue pointers 16 B aligned with ld % 8 == 0
   int tma_out; // out (and aux_out) leave through TMA bulk stores
   int fast;    // specialised epilogue (F_* below), 0 = generic
+  int probe;     // K3M_GEMM_PROBE (measurement only, results are garbage): 1 = no TMA loads, 2 = no MMAs
   int tin;     // epilogue operand that ARRIVES through TMA into the staging buffer: 0 none, 1 aux_in, 2 addend
 };
 
@@ -497,6 +498,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(&empty[s], ph ^ 1);
+          if (p.probe == 1) {                    // bottleneck bisect: stages turn "full" without any bytes moving
+            if (leader) mbar_expect_tx(&full[s], 0);
+            continue;
+          }
           if (leader) mbar_expect_tx(&full[s], CTAS * (A_BYTES + B_BYTES));
           const int k0 = (kb0 + i) * BK;
           uint8_t* a = sA + s * A_BYTES;
@@ -557,6 +562,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t da = A_MN ? make_desc(a + k * 2048, 8192, 1024) : make_desc(a + k * 32, 0, 1024);
             const uint64_t db = B_MN ? make_desc(b + k * 2048, 8192, 1024) : make_desc(b + k * 32, 0, 1024);
+            if (p.probe == 2) continue;          // bottleneck bisect: the ring drains at the pace of the loads alone
             if (CTAS == 2) umma_bf16_pair(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
             else umma_bf16(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
@@ -996,6 +1002,8 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
       if (p.tin && !get_map(src, N, M, ld_src, cw, 32, &mi, 2)) return K3M_ERR_CUDA;
     }
   }
+  static const int probe = getenv("K3M_GEMM_PROBE") ? atoi(getenv("K3M_GEMM_PROBE")) : 0;
+  p.probe = probe;
   p.fast = F_NONE;
   static const int no_fast = getenv("K3M_GEMM_NO_FAST") ? atoi(getenv("K3M_GEMM_NO_FAST")) : 0;
   if (!no_fast && p.tma_out && !out_f32 && !accumulate && p.vec_ok && N % 8 == 0) {
