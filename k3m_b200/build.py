@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "libk3m_sm100a.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC"]
+         "-Xcompiler", "-fPIC"] + os.environ.get("K3M_NVCC_EXTRA", "").split()    # e.g. -DK3M_GEMM_PROBE_BUILD
 
 
 def sources():

@@ -47,7 +47,9 @@ struct GemmParams {
   int vec_ok;  // all epilogue pointers 16 B aligned with ld % 8 == 0
   int tma_out; // out (and aux_out) leave through TMA bulk stores
   int fast;    // specialised epilogue (F_* below), 0 = generic
-  int probe;     // K3M_GEMM_PROBE (measurement only, results are garbage): 1 = no TMA loads, 2 = no MMAs
+  int probe;     // K3M_GEMM_PROBE, honoured only by a -DK3M_GEMM_PROBE_BUILD library (measurement only, results are
+                 // garbage): 1 = no TMA loads, 2 = no MMAs.  The product build carries no probe branch: one extra
+                 // predicate per MMA in the issuing thread cost 3 % of GEMM throughput (r01j vs r01i).
   int tin;     // epilogue operand that ARRIVES through TMA into the staging buffer: 0 none, 1 aux_in, 2 addend
 };
 
@@ -128,6 +130,17 @@ __device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t da, uin
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
       "}" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+// one lane of a converged warp (elect.sync)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}" : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster) : "memory");
@@ -440,7 +453,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   uint64_t* in_bars = tmem_empty + 2;     // [4 * EW] one per epilogue warp: TMA-fed epilogue operand landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(in_bars + 4 * EW);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // the broadcast tells the compiler that `warp` is warp-uniform: the role branches below are then uniform control
+  // flow and the MMA warp's addresses / descriptors live in uniform registers (see the MMA branch)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int total_kb = (p.K + BK - 1) / BK;
   const int tiles_mn = p.tiles_m * p.tiles_n;
   const int total_tiles = tiles_mn * p.splits;
@@ -498,10 +513,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(&empty[s], ph ^ 1);
+#ifdef K3M_GEMM_PROBE_BUILD
           if (p.probe == 1) {                    // bottleneck bisect: stages turn "full" without any bytes moving
             if (leader) mbar_expect_tx(&full[s], 0);
             continue;
           }
+#endif
           if (leader) mbar_expect_tx(&full[s], CTAS * (A_BYTES + B_BYTES));
           const int k0 = (kb0 + i) * BK;
           uint8_t* a = sA + s * A_BYTES;
@@ -538,7 +555,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && leader) {
+    // All 32 lanes walk the loops and wait on the barriers; one elected lane issues.  Issuing from inside an
+    // `if (lane == 0)` region made every operand of tcgen05.mma a per-thread value: the compiler moved five of them
+    // into uniform registers with an ELECT / R2UR / branch loop before EACH MMA (~20 instructions, ~150 clocks —
+    // longer than a 128 x 128 x 16 MMA runs).
+    if (leader) {
+      const bool issuer = elect_one();
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) |
                                  ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) |
                                  ((uint32_t)((BM * CTAS) >> 4) << 24);
@@ -562,15 +584,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t da = A_MN ? make_desc(a + k * 2048, 8192, 1024) : make_desc(a + k * 32, 0, 1024);
             const uint64_t db = B_MN ? make_desc(b + k * 2048, 8192, 1024) : make_desc(b + k * 32, 0, 1024);
+#ifdef K3M_GEMM_PROBE_BUILD
             if (p.probe == 2) continue;          // bottleneck bisect: the ring drains at the pace of the loads alone
-            if (CTAS == 2) umma_bf16_pair(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
-            else umma_bf16(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+#endif
+            if (issuer) {
+              if (CTAS == 2) umma_bf16_pair(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+              else umma_bf16(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            }
           }
-          if (CTAS == 2) umma_commit_pair(&empty[s]);
-          else umma_commit(&empty[s]);
+          if (issuer) {
+            if (CTAS == 2) umma_commit_pair(&empty[s]);
+            else umma_commit(&empty[s]);
+          }
+          __syncwarp();
         }
-        if (CTAS == 2) umma_commit_pair(&tmem_full[as]);
-        else umma_commit(&tmem_full[as]);
+        if (issuer) {
+          if (CTAS == 2) umma_commit_pair(&tmem_full[as]);
+          else umma_commit(&tmem_full[as]);
+        }
+        __syncwarp();
       }
     }
   } else {
