@@ -109,6 +109,12 @@ int k3m_fuse_select_bwd(const void* dout, int ldd, const void* cat, const float*
                         void* stream);
 int k3m_relu_bwd_split3(const void* dcat, const void* cat, void* da, int lda, void* db, int ldb, void* dc,
                         int ldc, int M, int H, void* stream);
+/* pre_sampling_sequence_soft (vilbert_k3m.py:2300-2329), if_pre_sampling = 2: alpha = sigmoid(score GEMM)
+ * comes from k3m_gemm_bf16 (ACT_SIGMOID); gated = cat * alpha feeds the soft_* GEMM.  bf16, contiguous,
+ * n elements (multiple of 8).  Backward: dcat = dgated * alpha, dscore = dgated * cat * alpha * (1 - alpha). */
+int k3m_gate_mul(const void* cat, const void* alpha, void* out, long long n, void* stream);
+int k3m_gate_bwd(const void* dgated, const void* cat, const void* alpha, void* dcat, void* dscore,
+                 long long n, void* stream);
 /* token-mean pooling over positions 1.. (vilbert_k3m.py:2405-2409)                               */
 int k3m_mean_pool_fwd(const void* seq, int ld, void* out, int out_f32, int B, int L, int H, void* stream);
 int k3m_mean_pool_bwd(const float* dpool, void* dseq, int ld, int B, int L, int H, void* stream);
@@ -118,6 +124,11 @@ int k3m_pair_gather_fwd(const float* c_init, const void* seq, int lds, const int
                         const int* pair_rows, void* X, float* PV, int P, int H, void* stream);
 int k3m_pair_gather_bwd(const float* dX, const float* dPV, const int* pair_item, const int* pair_rows,
                         float* dc_init, float* dseq32, int P, int H, void* stream);
+/* Leading items without a property/value pair (NameError -> bare except -> t = c_initial[i],
+ * vilbert_k3m.py:2452-2456): fb int32 [n, 2] = (row of t, item) or (-1, -1) per aggregator call.
+ * fwd: t[row] = c_init[item].  bwd: dc_init[item] += dt[row]; dt[row] = 0.                        */
+int k3m_struct_fallback_fwd(float* t, const float* c_init, const int* fb, int n, int H, void* stream);
+int k3m_struct_fallback_bwd(float* dt, float* dc_init, const int* fb, int n, int H, void* stream);
 int k3m_struct_attn_fwd(const float* t, const void* w2, const void* b2, const int* seg, float* s_out,
                         float* att, int B, int maxn, int H, void* stream);
 int k3m_struct_attn_bwd(const float* ds, const float* t, const float* att, const void* w2, const int* seg,

@@ -197,6 +197,38 @@ __global__ void pool_bwd_kernel(const float* __restrict__ dpool, bf16* __restric
   }
 }
 
+// ---- soft fusion (if_pre_sampling = 2, pre_sampling_sequence_soft, vilbert_k3m.py:2300-2329) --------------
+// gated = cat * alpha  (cat = relu(cat3), alpha = sigmoid(score GEMM), both bf16 [M, 3H], 8 elements per thread)
+__global__ void gate_mul_kernel(const bf16* __restrict__ cat, const bf16* __restrict__ alpha, bf16* __restrict__ out,
+                                size_t n8) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    float a[8], b[8];
+    ld8(cat + i * 8, a);
+    ld8(alpha + i * 8, b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] *= b[j];
+    st8(out + i * 8, a);
+  }
+}
+// dgated -> dcat (direct path) = dgated * alpha ;  dscore = dgated * cat * alpha * (1 - alpha)
+__global__ void gate_bwd_kernel(const bf16* __restrict__ dgated, const bf16* __restrict__ cat,
+                                const bf16* __restrict__ alpha, bf16* __restrict__ dcat, bf16* __restrict__ dscore,
+                                size_t n8) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    float d[8], c[8], a[8], o1[8], o2[8];
+    ld8(dgated + i * 8, d);
+    ld8(cat + i * 8, c);
+    ld8(alpha + i * 8, a);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      o1[j] = d[j] * a[j];
+      o2[j] = d[j] * c[j] * a[j] * (1.0f - a[j]);
+    }
+    st8(dcat + i * 8, o1);
+    st8(dscore + i * 8, o2);
+  }
+}
+
 inline int grid_for(size_t n, int block) {
   size_t g = (n + block - 1) / block;
   if (g > 148 * 16) g = 148 * 16;
@@ -256,6 +288,22 @@ extern "C" int k3m_fuse_select_bwd(const void* dout, int ldd, const void* cat, c
   fuse_bwd_kernel<<<grid_for((size_t)M * H, 256), 256, 0, ST(stream)>>>(
       (const bf16*)dout, ldd, (const bf16*)cat, gates, noise, (const unsigned long long*)rng, site, (bf16*)dgates, (bf16*)dcat, M, H);
   return k3m_check_launch("k3m_fuse_select_bwd");
+}
+
+extern "C" int k3m_gate_mul(const void* cat, const void* alpha, void* out, long long n, void* stream) {
+  K3M_REQUIRE(n > 0 && n % 8 == 0, "gate_mul: element count must be a positive multiple of 8");
+  gate_mul_kernel<<<grid_for((size_t)n / 8, 256), 256, 0, ST(stream)>>>((const bf16*)cat, (const bf16*)alpha, (bf16*)out,
+                                                                       (size_t)n / 8);
+  return k3m_check_launch("k3m_gate_mul");
+}
+
+extern "C" int k3m_gate_bwd(const void* dgated, const void* cat, const void* alpha, void* dcat, void* dscore, long long n,
+                            void* stream) {
+  K3M_REQUIRE(n > 0 && n % 8 == 0, "gate_bwd: element count must be a positive multiple of 8");
+  gate_bwd_kernel<<<grid_for((size_t)n / 8, 256), 256, 0, ST(stream)>>>((const bf16*)dgated, (const bf16*)cat,
+                                                                       (const bf16*)alpha, (bf16*)dcat, (bf16*)dscore,
+                                                                       (size_t)n / 8);
+  return k3m_check_launch("k3m_gate_bwd");
 }
 
 extern "C" int k3m_relu_bwd_split3(const void* dcat, const void* cat, void* da, int lda, void* db, int ldb, void* dc,

@@ -206,6 +206,27 @@ __global__ void pair_gather_bwd_kernel(const float* __restrict__ dX, const float
   }
 }
 
+// Leading items without any property/value pair: the reference's `t` is unbound there, its bare `except`
+// sets t = c_initial[i] (vilbert_k3m.py:2452-2456) and later items without pairs keep reusing that row.
+// The plan holds one pseudo pair row per `structure_aggregator` call for it: fb = (row of t, item) or (-1, -1).
+// Forward: t[row] = c_init[item] (bypassing struc_w1).  Backward: the row's gradient goes straight to
+// dc_init[item] and is zeroed, so nothing flows into struc_w1 / the gathered sequence rows from it.
+__global__ void struct_fallback_fwd_kernel(float* __restrict__ t, const float* __restrict__ c_init,
+                                           const int* __restrict__ fb, int H) {
+  const int row = fb[2 * blockIdx.x], item = fb[2 * blockIdx.x + 1];
+  if (row < 0) return;
+  for (int h = threadIdx.x; h < H; h += blockDim.x) t[(size_t)row * H + h] = c_init[(size_t)item * H + h];
+}
+__global__ void struct_fallback_bwd_kernel(float* __restrict__ dt, float* __restrict__ dc_init,
+                                           const int* __restrict__ fb, int H) {
+  const int row = fb[2 * blockIdx.x], item = fb[2 * blockIdx.x + 1];
+  if (row < 0) return;
+  for (int h = threadIdx.x; h < H; h += blockDim.x) {
+    atomicAdd(dc_init + (size_t)item * H + h, dt[(size_t)row * H + h]);
+    dt[(size_t)row * H + h] = 0.f;
+  }
+}
+
 // one CTA per item: scores b_j = w2 . leaky_relu(t_j) + b2 over the item's pair range, softmax,
 // s = sum_j att_j t_j.  att is stored [B, maxn].
 __global__ void __launch_bounds__(256) struct_attn_fwd_kernel(const float* __restrict__ t, const bf16* __restrict__ w2,
@@ -442,6 +463,18 @@ extern "C" int k3m_pair_gather_bwd(const float* dX, const float* dPV, const int*
   if (g > 148 * 8) g = 148 * 8;
   pair_gather_bwd_kernel<<<g, 256, 0, ST(stream)>>>(dX, dPV, pair_item, pair_rows, dc_init, dseq32, P, H);
   return k3m_check_launch("k3m_pair_gather_bwd");
+}
+
+extern "C" int k3m_struct_fallback_fwd(float* t, const float* c_init, const int* fb, int n, int H, void* stream) {
+  K3M_REQUIRE(n > 0 && H > 0, "struct_fallback: empty");
+  struct_fallback_fwd_kernel<<<n, 256, 0, ST(stream)>>>(t, c_init, fb, H);
+  return k3m_check_launch("k3m_struct_fallback_fwd");
+}
+
+extern "C" int k3m_struct_fallback_bwd(float* dt, float* dc_init, const int* fb, int n, int H, void* stream) {
+  K3M_REQUIRE(n > 0 && H > 0, "struct_fallback: empty");
+  struct_fallback_bwd_kernel<<<n, 256, 0, ST(stream)>>>(dt, dc_init, fb, H);
+  return k3m_check_launch("k3m_struct_fallback_bwd");
 }
 
 extern "C" int k3m_struct_attn_fwd(const float* t, const void* w2, const void* b2, const int* seg, float* s_out, float* att,

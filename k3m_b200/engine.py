@@ -60,6 +60,10 @@ class Engine(object):
         self._site = 0
         self._wv, self._gv = {}, {}
         self.on_ready = None     # callback(prefixes | None): weight gradients of these blocks are final
+        # per-layer parity taps (tests only; never set inside a captured step): when a dict, `tower_fwd` stores the
+        # output of every BertLayer / BertImageLayer / BertConnectionLayer application under the key the reference's
+        # module call would have: "<module name>#<call index>[/<output index>]" (tools/make_golden.py install_taps)
+        self.taps = None
 
     # ---- views / small helpers -------------------------------------------------------------
     def W(self, name):
@@ -315,7 +319,13 @@ class Engine(object):
             ops.lincomb3(indiv, c1, c2, 1.0 / 3, 1.0 / 3, 1.0 / 3, out=out)
             return (mode,)
         if mode == 2:
-            raise NotImplementedError("if_pre_sampling=2 (soft fusion) is not on the K3M hot path")
+            # `pre_sampling_sequence_soft` `:2300-2329`: soft_m(cat(relu(.) * sigmoid(score_*(cat))))
+            cat = ops.relu_cat3(indiv, c1, c2)
+            alpha = ops.gemm(cat, self.W("score_%s.weight" % mod), "nt", bias=self.W("score_%s.bias" % mod),
+                             act=ACT_SIGMOID)
+            gated = ops.gate_mul(cat, alpha)
+            ops.gemm(gated, self.W("soft_%s.weight" % mod), "nt", bias=self.W("soft_%s.bias" % mod), out=out)
+            return (mode, mod, cat, alpha, gated)
         if mode != 1:
             ops.lincomb3(c1, c2, None, 0.5, 0.5, 0.0, out=out)
             return (mode,)
@@ -333,6 +343,17 @@ class Engine(object):
         if mode == 0:
             for t in (d_indiv, d_c1, d_c2):
                 ops.axpy(dout, t, 1.0 / 3)
+            return
+        if mode == 2:
+            _, mod, cat, alpha, gated = saved
+            self.bgrad(dout, "soft_%s.bias" % mod)
+            self.wgrad(dout, gated, "soft_%s.weight" % mod)
+            dgated = self.dgrad(dout, "soft_%s.weight" % mod)
+            dcat, dscore = ops.gate_bwd(dgated, cat, alpha)
+            self.bgrad(dscore, "score_%s.bias" % mod)
+            self.wgrad(dscore, cat, "score_%s.weight" % mod)
+            self.dgrad(dscore, "score_%s.weight" % mod, addend=dcat, out=dcat)
+            ops.relu_bwd_split3(dcat, cat, d_indiv, d_c1, d_c2)
             return
         if mode != 1:
             ops.axpy(dout, d_c1, 0.5)
@@ -384,6 +405,7 @@ class Engine(object):
         B, H = c_init.shape
         X, PV = ops.pair_gather_fwd(c_init, seq_pv, plan["pair_item"], plan["pair_rows"])
         t = ops.gemm(X, self.W("struc_w1.weight"), "nt", bias=self.W("struc_w1.bias"), out_dtype=f32)
+        ops.struct_fallback_fwd(t, c_init, plan["fallback"])      # leading items without PVs (`:2452-2456`)
         s, att = ops.struct_attn_fwd(t, self.W("struc_w2.weight"), self.W("struc_w2.bias"), plan["seg"])
         s_a = ops.cast(s, self.adt)
         c_final = ops.gemm(s_a, self.W("struc_w3.weight"), "nt", bias=self.W("struc_w3.bias"),
@@ -411,6 +433,7 @@ class Engine(object):
         dt = self.zeros(t.shape[0], t.shape[1], f32)
         ops.struct_attn_bwd(ds, t, att, self.W("struc_w2.weight"), plan["seg"], dt,
                             self.G("struc_w2.weight"), self.G("struc_w2.bias"))
+        ops.struct_fallback_bwd(dt, dc_init, plan["fallback"])
         self.bgrad(dt, "struc_w1.bias")
         dta = ops.cast(dt, self.adt)
         self.wgrad(dta, X, "struc_w1.weight")
@@ -499,6 +522,9 @@ class Engine(object):
         s1 = s2 = 0
         box = {"X": X, "Y": Y}
 
+        taps = self.taps
+        t_last = c.t_biattention_id[-1]
+
         def run_layers(t_range, v_range):
             tsv, vsv = [], []
 
@@ -506,11 +532,21 @@ class Engine(object):
                 for i in t_range:
                     box["X"], sv = self.layer_fwd("encoder.layer.%d" % i, box["X"], segs_x, False)
                     tsv.append(sv)
+                    if taps is not None:
+                        # call order of the shared module over the three passes (`:1686-1750`): title (t<->v), PV
+                        # (pv<->v), then the two-text pass — title before PV inside its loop (`:1552-1576`), PV
+                        # before title in the closing loops (`:1655-1672`)
+                        order = (T1, P2, P3, T3) if i >= t_last else (T1, P2, T3, P3)
+                        for k, sl in enumerate(order):
+                            taps["encoder.layer.%d#%d" % (i, k)] = box["X"][sl]
 
             def image():
                 for i in v_range:
                     box["Y"], sv = self.layer_fwd("encoder.v_layer.%d" % i, box["Y"], segs_y, True)
                     vsv.append(sv)
+                    if taps is not None:
+                        for k, sl in enumerate((V1, V2)):
+                            taps["encoder.v_layer.%d#%d" % (i, k)] = box["Y"][sl]
 
             ops.parallel([text if len(t_range) else None, image if len(v_range) else None])
             stages.append(("tv", tsv, vsv))
@@ -535,6 +571,11 @@ class Engine(object):
 
             ops.parallel([conn_a, conn_b, conn_c])
             stages.append(("c", sv_c[0], sv_c[1], sv_c[2]))
+            if taps is not None:
+                for nm, o0, o1 in (("c_layer", Yn[V1], Xn[T1]), ("c_layer_pv_v", Yn[V2], Xn[P2]),
+                                   ("c_layer_pv_t", Xn[P3], Xn[T3])):
+                    taps["encoder.%s.%d#0/0" % (nm, count)] = o0
+                    taps["encoder.%s.%d#0/1" % (nm, count)] = o1
             box["X"], box["Y"] = Xn, Yn
             s1, s2 = e1, e2
         run_layers(range(s2, c.num_hidden_layers), range(s1, c.v_num_hidden_layers))

@@ -150,17 +150,19 @@ def _round_up(x, m):
 def no_grad_names(cfg, names):
     """Parameters that never receive a gradient in the K3M pretraining step:
     `q_dense1/2` are never called (`vilbert_k3m.py:976,983`), the pooler outputs are discarded by
-    `forward` (`:2620-2631`), `map_individual_to_bi` and `soft_*` are only used by
-    `if_pre_sampling == 2`, the `score_*` gates only by `if_pre_sampling == 1`, and the ITM loss is
+    `forward` (`:2620-2631`), `map_individual_to_bi` is never called on this path, `soft_*` are only used by
+    `if_pre_sampling == 2`, the `score_*` gates only by `if_pre_sampling` 1 and 2, and the ITM loss is
     never added to the training loss (`pretrain.py:1055`) so `cls.seq_relationship` is value-only.
     torch.optim.AdamW skips such parameters entirely (no decay, no state)."""
     out = set()
     for n in names:
         if (".q_dense" in n or n.startswith("t_pooler.") or n.startswith("v_pooler.")
-                or n.startswith("map_individual_to_bi.") or n.startswith("soft_")
+                or n.startswith("map_individual_to_bi.")
                 or n.startswith("cls.seq_relationship.")):
             out.add(n)
-        elif n.startswith("score_") and getattr(cfg, "if_pre_sampling", 1) != 1:
+        elif n.startswith("soft_") and getattr(cfg, "if_pre_sampling", 1) != 2:
+            out.add(n)
+        elif n.startswith("score_") and getattr(cfg, "if_pre_sampling", 1) not in (1, 2):
             out.add(n)
     return out
 

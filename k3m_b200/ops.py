@@ -283,6 +283,18 @@ class CudaOps(object):
                    _u(site), _p(dg), _p(dc), _i(M), _i(H), self._st())
         return dg, dc
 
+    def gate_mul(self, cat, alpha):
+        assert cat.is_contiguous() and alpha.is_contiguous() and cat.shape == alpha.shape
+        out = torch.empty_like(cat)
+        self._call("k3m_gate_mul", _p(cat), _p(alpha), _p(out), _ll(cat.numel()), self._st())
+        return out
+
+    def gate_bwd(self, dgated, cat, alpha):
+        assert dgated.is_contiguous() and cat.is_contiguous() and alpha.is_contiguous()
+        dcat, dscore = torch.empty_like(cat), torch.empty_like(cat)
+        self._call("k3m_gate_bwd", _p(dgated), _p(cat), _p(alpha), _p(dcat), _p(dscore), _ll(cat.numel()), self._st())
+        return dcat, dscore
+
     def relu_bwd_split3(self, dcat, cat, da, db, dc):
         M, H = da.shape
         self._call("k3m_relu_bwd_split3", _p(dcat), _p(cat), _p(da), _i(_ld(da)), _p(db), _i(_ld(db)), _p(dc),
@@ -359,6 +371,12 @@ class CudaOps(object):
         self._call("k3m_pair_gather_bwd", _p(dx), _p(dpv), _p(pair_item), _p(pair_rows), _p(dc_init), _p(scratch),
                    _i(P), _i(H), self._st())
         self.axpy(scratch, dseq, 1.0)
+
+    def struct_fallback_fwd(self, t, c_init, fb):
+        self._call("k3m_struct_fallback_fwd", _p(t), _p(c_init), _p(fb), _i(fb.shape[0]), _i(t.shape[1]), self._st())
+
+    def struct_fallback_bwd(self, dt, dc_init, fb):
+        self._call("k3m_struct_fallback_bwd", _p(dt), _p(dc_init), _p(fb), _i(fb.shape[0]), _i(dt.shape[1]), self._st())
 
     def struct_attn_fwd(self, t, w2, b2, seg):
         B, H = seg.shape[0], t.shape[1]

@@ -25,12 +25,18 @@ def build_struct_plan(index_p, index_v, L_pv, num_negative_pv, rng=random, halve
       pair_rows [P, 4]   rows of the stacked PV sequence [B*L_pv, H]: (p0, p1, v0, v1)
       seg       [B, 2]   (start, end) pair range whose `t` rows item i attends over
       terms     [T, 4]   LPM terms (item, pair, negative item, negative value pair)
+      fallback  [halves, 2]  per aggregator call (row of `t`, item) of the pseudo pair that stands for the
+                         reference's `t = c_initial[i]` fallback (`:2452-2456`: leading items without any
+                         pair), or (-1, -1).  The pseudo pair gathers row 0 of its item (value unused: its `t`
+                         row is overwritten), takes part in no LPM term and gets no struc_w1 gradient.
     """
     ip = np.asarray(index_p).astype(np.int64)
     iv = np.asarray(index_v).astype(np.int64)
     B, J = ip.shape[0], ip.shape[1]
     pair_item, pair_rows, seg, first = [], [], [], []
     last = None
+    fallback = [(-1, -1)] * halves
+    counts = [0] * B
     for i in range(B):
         if halves > 1 and i % (B // halves) == 0:
             last = None                   # a new `structure_aggregator` call: `t` is unbound again
@@ -42,20 +48,20 @@ def build_struct_plan(index_p, index_v, L_pv, num_negative_pv, rng=random, halve
             pair_item.append(i)
             pair_rows.append((base + ip[i, j, 0], base + ip[i, j, 1],
                               base + iv[i, j, 0], base + iv[i, j, 1]))
+            counts[i] += 1
         end = len(pair_item)
         first.append(start)
         if end > start:
             last = (start, end)
         elif last is None:
             # reference: NameError -> bare except -> t = c_initial[i] (`:2452-2456`); only for
-            # leading items without PVs.  Not representable as a pair range.
-            raise ValueError("item %d has no property/value pair and no earlier item has one; "
-                             "the reference's fallback for this case is not supported" % i)
+            # leading items without PVs: a pseudo pair whose `t` row the device overwrites with c_initial[i]
+            fallback[i // max(1, B // halves)] = (start, i)
+            pair_item.append(i)
+            pair_rows.append((i * L_pv,) * 4)
+            last = (start, start + 1)
         # an item without PVs silently reuses the previous item's `t` (stale variable)
         seg.append(last)
-    counts = [0] * B
-    for i in pair_item:
-        counts[i] += 1
     terms = []
     if halves > 1:
         counts = [0] * B                  # alignment: no link-prediction terms, no random draws
@@ -77,6 +83,7 @@ def build_struct_plan(index_p, index_v, L_pv, num_negative_pv, rng=random, halve
         pair_rows=np.asarray(pair_rows, dtype=np.int32).reshape(-1, 4),
         seg=np.asarray(seg, dtype=np.int32).reshape(-1, 2),
         terms=np.asarray(terms, dtype=np.int32).reshape(-1, 4),
+        fallback=np.asarray(fallback, dtype=np.int32).reshape(-1, 2),
     )
 
 
@@ -97,6 +104,7 @@ def pad_struct_plan(plan, B, max_num_pv, num_negative_pv):
         raise ValueError("struct plan exceeds its capacity (P=%d/%d, T=%d/%d)" % (P, P_cap, T, T_cap))
     out = dict(pair_item=np.zeros(P_cap, dtype=np.int32), pair_rows=np.zeros((P_cap, 4), dtype=np.int32),
                seg=plan["seg"].copy(), terms=np.zeros((T_cap, 4), dtype=np.int32),
+               fallback=plan["fallback"].copy(),
                n_terms=np.asarray([T], dtype=np.int32))
     out["pair_item"][:P] = plan["pair_item"]
     out["pair_rows"][:P] = plan["pair_rows"]

@@ -11,7 +11,12 @@ batch with the same names, shapes, dtypes and structural invariants (SURVEY §8d
   * 15 % MLM labels on valid positions (>= 1 per batch), -1 elsewhere;
   * image row 0 is the mean feature with box [0,0,1,1,1] (`:382-397`); `image_target` is a
     soft distribution over `v_target_size` classes; `image_label` in {-1, 1} (>= 1 per batch);
-  * next-sentence labels are all 0 (the loader never emits anything else, `:604`).
+  * `ragged=True` (default): every item has its own `num_boxes` in [len_v/2, len_v]; rows beyond it are what the
+    loader pads with (`:580-586`, `:716-724`): zero feature / box / target rows, `image_label` -1 and
+    `image_attention_mask` 0, and the global feature is the mean over the valid boxes (`:382-397`);
+  * next-sentence labels: the loader only ever emits 0 (`:604`), but `forward` accepts any 0/1 triple and
+    turns it into the ITM target `1 - ((l1 + l2 + l3) == 0)` (`vilbert_k3m.py:2823-2824`), so with
+    `ragged=True` the three labels are random 0/1 draws (both ITM classes are exercised).
 
 Everything is generated with numpy's PCG64 from the given seed, so the GPU box and this
 container produce bit-identical batches.
@@ -23,7 +28,9 @@ CLS, SEP, COLON, SEMI = 101, 102, 131, 132
 
 
 def synth_batch(cfg, batch, len_t=36, len_v=36, len_pv=36, max_num_pv=8, seed=1234,
-                ragged=True):
+                ragged=True, no_pv=()):
+    """`no_pv`: items that get no property/value group at all (`[CLS] [SEP]` PV row, all-zero index rows) —
+    the case the reference's aggregator handles through its bare `except` (`vilbert_k3m.py:2452-2456`)."""
     rng = np.random.Generator(np.random.PCG64(seed))
     V = cfg.vocab_size
     lo = min(1000, V // 2)
@@ -56,6 +63,8 @@ def synth_batch(cfg, batch, len_t=36, len_v=36, len_pv=36, max_num_pv=8, seed=12
         pos = 1
         ids_pv[i, 0] = CLS
         n_target = int(rng.integers(1, max_num_pv + 1))
+        if i in no_pv:
+            n_target = 0
         j = 0
         while j < n_target:
             lp = int(rng.integers(1, 3))
@@ -91,7 +100,10 @@ def synth_batch(cfg, batch, len_t=36, len_v=36, len_pv=36, max_num_pv=8, seed=12
     feat = np.abs(rng.standard_normal((B, len_v, Fv), dtype=np.float32))
     zero = rng.random((B, len_v)) < 0.15
     feat[zero] = 0.0
-    g = feat.mean(axis=1, keepdims=True)
+    nbox = rng.integers(max(1, len_v // 2), len_v + 1, size=B) if ragged else np.full(B, len_v)
+    box_ok = np.arange(len_v)[None, :] < nbox[:, None]
+    feat[~box_ok] = 0.0
+    g = feat.sum(axis=1, keepdims=True) / nbox[:, None, None].astype(np.float32)
     image_feat = np.concatenate([g, feat], axis=1).astype(np.float32)
     xy = np.sort(rng.random((B, len_v, 2, 2), dtype=np.float32), axis=2)
     loc = np.zeros((B, len_v, 5), dtype=np.float32)
@@ -100,28 +112,31 @@ def synth_batch(cfg, batch, len_t=36, len_v=36, len_pv=36, max_num_pv=8, seed=12
     loc[..., 2] = xy[:, :, 1, 0]
     loc[..., 3] = xy[:, :, 1, 1]
     loc[..., 4] = (loc[..., 2] - loc[..., 0]) * (loc[..., 3] - loc[..., 1])
+    loc[~box_ok] = 0.0
     gl = np.tile(np.array([0, 0, 1, 1, 1], dtype=np.float32), (B, 1, 1))
     image_loc = np.concatenate([gl, loc], axis=1)
     logits = rng.standard_normal((B, len_v, Tv), dtype=np.float32) * 2.0
     logits -= logits.max(axis=-1, keepdims=True)
     e = np.exp(logits)
     image_target = (e / e.sum(axis=-1, keepdims=True)).astype(np.float32)
-    image_label = np.where(rng.random((B, len_v)) < 0.15, 1, -1).astype(np.int64)
+    image_target[~box_ok] = 0.0
+    image_label = np.where((rng.random((B, len_v)) < 0.15) & box_ok, 1, -1).astype(np.int64)
     if (image_label == 1).sum() == 0:
         image_label[0, 0] = 1
-    image_mask = np.ones((B, len_v + 1), dtype=np.int64)
+    image_mask = np.concatenate([np.ones((B, 1), dtype=np.int64), box_ok.astype(np.int64)], axis=1)
 
     z = np.zeros(B, dtype=np.int64)
+    nsl = [rng.integers(0, 2, size=B).astype(np.int64) if ragged else z.copy() for _ in range(3)]
     t = torch.from_numpy
     return dict(
         input_ids=t(input_ids), image_feat=t(image_feat), image_loc=t(image_loc),
         token_type_ids=t(np.zeros_like(input_ids)), attention_mask=t(attention_mask),
         image_attention_mask=t(image_mask), masked_lm_labels=t(labels),
         image_label=t(image_label), image_target=t(image_target),
-        next_sentence_label=t(z.copy()),
+        next_sentence_label=t(nsl[0]),
         input_ids_pv=t(ids_pv), token_type_ids_pv=t(np.zeros_like(ids_pv)),
         attention_mask_pv=t(mask_pv), masked_lm_labels_pv=t(labels_pv),
-        next_sentence_label_pv_v=t(z.copy()), next_sentence_label_pv_t=t(z.copy()),
+        next_sentence_label_pv_v=t(nsl[1]), next_sentence_label_pv_t=t(nsl[2]),
         index_p=t(index_p), index_v=t(index_v),
     )
 

@@ -96,7 +96,8 @@ class PretrainStep(object):
                          pair_rows=torch.zeros(P_cap, 4, dtype=i32, device=dev),
                          seg=torch.zeros(self.n_items, 2, dtype=i32, device=dev),
                          terms=torch.zeros(T_cap, 4, dtype=i32, device=dev),
-                         n_terms=torch.zeros(1, dtype=i32, device=dev))
+                         n_terms=torch.zeros(1, dtype=i32, device=dev),
+                         fallback=torch.full((self.HALVES, 2), -1, dtype=i32, device=dev))
         self.plan["seg"]._k3m_maxn = maxn
         pin = (lambda t: t.pin_memory()) if self._cuda else (lambda t: t)
         self._plan_host = [{k: pin(torch.zeros(v.shape, dtype=i32)) for k, v in self.plan.items()}

@@ -41,6 +41,7 @@ class Oracle(object):
         self.sd = state_dict
         self.training = training
         self.taps = None  # optional dict: name -> activation (for per-layer parity)
+        self._calls = {}
 
     # ---- small helpers -------------------------------------------------------------------
     def lin(self, name, x):
@@ -55,6 +56,16 @@ class Oracle(object):
     def tap(self, name, x):
         if self.taps is not None:
             self.taps[name] = x
+
+    def tap_call(self, module, outs):
+        """Same keys as the forward hooks `tools/make_golden.py` puts on the unmodified reference's
+        BertLayer / BertImageLayer / BertConnectionLayer modules: "<module>#<call index>[/<output>]"."""
+        if self.taps is None:
+            return
+        k = self._calls.get(module, 0)
+        self._calls[module] = k + 1
+        for j, x in enumerate(outs):
+            self.taps["%s#%d" % (module, k) + ("/%d" % j if len(outs) > 1 else "")] = x
 
     # ---- embeddings ------------------------------------------------------------------------
     def text_embeddings(self, ids, type_ids):
@@ -97,7 +108,9 @@ class Oracle(object):
         a = self.ln(p + ".attention.output.LayerNorm",
                     self.drop(self.lin(p + ".attention.output.dense", ctx), ph) + x)
         h = gelu(self.lin(p + ".intermediate.dense", a))
-        return self.ln(p + ".output.LayerNorm", self.drop(self.lin(p + ".output.dense", h), ph) + a)
+        y = self.ln(p + ".output.LayerNorm", self.drop(self.lin(p + ".output.dense", h), ph) + a)
+        self.tap_call(p, (y,))
+        return y
 
     def connection(self, p, x1, m1, x2, m2):
         # BertConnectionLayer `:1030-1071` / _two_text `:1074-1111`.  Stream 1 = image (or PV),
@@ -124,6 +137,7 @@ class Oracle(object):
         h2 = gelu(self.lin(p + ".t_intermediate.dense", a2))
         y2 = self.ln(p + ".t_output.LayerNorm",
                      self.drop(self.lin(p + ".t_output.dense", h2), c.hidden_dropout_prob) + a2)
+        self.tap_call(p, (y1, y2))
         return y1, y2
 
     def encoder_pass(self, tag, x_txt, m_txt, x_1, m_1, conn, image):

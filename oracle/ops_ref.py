@@ -307,6 +307,14 @@ class RefOps(object):
         dg = dlog * ak * (1.0 - ak)
         return dg.reshape(M, H3).to(self.adt), (do * hard).reshape(M, H3).to(self.adt)
 
+    def gate_mul(self, cat, alpha):
+        """soft fusion (`:2300-2329`): cat * alpha, stored in the activation dtype."""
+        return (cat.float() * alpha.float()).to(self.adt)
+
+    def gate_bwd(self, dgated, cat, alpha):
+        d, c, a = dgated.float(), cat.float(), alpha.float()
+        return (d * a).to(self.adt), (d * c * a * (1.0 - a)).to(self.adt)
+
     def relu_bwd_split3(self, dcat, cat, da, db, dc):
         """d{a,b,c} += dcat[:, k*H:(k+1)*H] * (cat[:, k*H:(k+1)*H] > 0)."""
         H = dcat.shape[1] // 3
@@ -376,6 +384,18 @@ class RefOps(object):
         pr = pair_rows.long()
         for col, sl in ((0, slice(0, H)), (1, slice(0, H)), (2, slice(H, 2 * H)), (3, slice(H, 2 * H))):
             dseq.index_add_(0, pr[:, col], g[:, sl].to(dseq.dtype))
+
+    def struct_fallback_fwd(self, t, c_init, fb):
+        """fb [n,2] int32 (row of t, item) or (-1,-1): t[row] = c_init[item]  (`:2452-2456`)."""
+        for row, item in fb.tolist():
+            if row >= 0:
+                t[row] = c_init[item].to(t.dtype)
+
+    def struct_fallback_bwd(self, dt, dc_init, fb):
+        for row, item in fb.tolist():
+            if row >= 0:
+                dc_init[item] += dt[row].to(dc_init.dtype)
+                dt[row] = 0
 
     def struct_attn_fwd(self, t, w2, b2, seg):
         """seg [B,2] int32 (start,end) pair range per item.  b = w2.leaky_relu(t)+b2 ; att =

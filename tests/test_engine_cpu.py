@@ -5,17 +5,23 @@ import pytest
 import torch
 
 from oracle.ops_ref import RefOps
-from tests.util import case_setup, compare_with_golden, load_golden, run_engine
+from tests.util import case_setup, compare_taps, compare_with_golden, load_golden, run_engine
 
 
-@pytest.mark.parametrize("name", ["tiny_hard", "tiny_mean", "tiny_inter", "base_hard", "base_mean"])
+@pytest.mark.parametrize("name", ["tiny_hard", "tiny_mean", "tiny_inter", "tiny_soft", "tiny_nopv", "base_hard",
+                                  "base_mean", "long_hard"])
 def test_schedule_matches_reference_fp32(name):
     fx = load_golden(name)
     cfg, sd, batch, noise = case_setup(fx)
+    taps = {}
     out, L, g = run_engine(cfg, sd, batch, noise, RefOps(torch.float32), "cpu", torch.float32,
-                           fx["seeds"]["python"])
+                           fx["seeds"]["python"], taps=taps)
     errs, worst = compare_with_golden(fx, out, L, g, loss_rtol=1e-5, grad_tol=2e-4)
     assert not errs, errs[:10]
+    # every BertLayer / BertImageLayer / BertConnectionLayer output of the unmodified reference (forward hooks)
+    terrs, stats = compare_taps(fx, taps, 1e-5)
+    assert not terrs, terrs[:10]
+    assert len(stats) == len(fx["taps"]) > 0
 
 
 def test_dropout_mask_is_regenerated_consistently():

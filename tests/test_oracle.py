@@ -9,22 +9,30 @@ from oracle import ref_harness
 from oracle.k3m_oracle import Oracle, total_loss, warmup_linear_lambda
 from tests.util import case_setup, load_golden, sample_index
 
-CASES = ["tiny_hard", "tiny_mean", "tiny_inter"]
+CASES = ["tiny_hard", "tiny_mean", "tiny_inter", "tiny_soft", "tiny_nopv"]
 
 
 def _run_oracle(fx):
     cfg, sd, batch, noise = case_setup(fx)
     sdo = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
     random.seed(fx["seeds"]["python"])
-    out = Oracle(cfg, sdo).forward(batch, noise)
+    orc = Oracle(cfg, sdo)
+    orc.taps = {}
+    out = orc.forward(batch, noise)
     total_loss(out).backward()
-    return out, sdo
+    return out, sdo, orc.taps
 
 
 @pytest.mark.parametrize("name", CASES + ["base_hard", "base_mean"])
 def test_oracle_matches_golden(name):
     fx = load_golden(name)
-    out, sdo = _run_oracle(fx)
+    out, sdo, taps = _run_oracle(fx)
+    # per-layer activations: the forward hooks on the unmodified reference's layer modules
+    assert len(fx["taps"]) > 0
+    for key, ref in fx["taps"].items():
+        x = taps[key].detach().reshape(-1)
+        assert abs(float(x.norm()) - ref["norm"]) <= 1e-5 * ref["norm"], key
+        assert float((x[sample_index(x.numel())] - ref["sample"]).abs().max()) <= 1e-5 * float(ref["sample"].abs().max()) + 1e-6, key
     got = dict(loss_t=out[0], loss_v=out[1], loss_pv=out[3], loss_itm=out[6], loss_lpm=out[9])
     for k, ref in fx["losses"].items():
         assert abs(float(got[k]) - ref) <= 1e-5 * max(1.0, abs(ref)), (k, float(got[k]), ref)
@@ -44,6 +52,8 @@ def test_oracle_matches_golden(name):
     if name in ("base_hard", "base_mean"):
         # 86 never-trained tensors; the 18 score_* gate tensors join them unless if_pre_sampling == 1
         assert n_none == (86 if name == "base_hard" else 104) and len(fx["grads"]) == 998
+    if name == "tiny_soft":
+        assert fx["grads"]["soft_t.weight"] is not None and fx["grads"]["score_self_v.weight"] is not None
 
 
 @pytest.mark.skipif(not ref_harness.available(), reason="reference tree not mounted")

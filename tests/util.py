@@ -41,13 +41,14 @@ def case_setup(fx):
         setattr(cfg, k, v)
     B, Lt, Lv, Lpv, mpv = fx["dims"]
     sd = synth_state_dict(param_spec(cfg), seed=fx["seeds"]["weights"])
-    batch = synth_batch(cfg, B, Lt, Lv, Lpv, max_num_pv=mpv, seed=fx["seeds"]["batch"])
+    batch = synth_batch(cfg, B, Lt, Lv, Lpv, max_num_pv=mpv, seed=fx["seeds"]["batch"], no_pv=fx.get("no_pv", ()))
     noise = make_noise(cfg, B, Lt, Lv + 1, Lpv, fx["seeds"]["noise"]) if cfg.if_pre_sampling == 1 else None
     return cfg, sd, batch, noise
 
 
-def run_engine(cfg, sd, batch, noise, ops, device, adt, py_seed, training=False):
-    """One forward+backward of the engine; returns (outputs dict, layout, fp32 grad arena)."""
+def run_engine(cfg, sd, batch, noise, ops, device, adt, py_seed, training=False, taps=None):
+    """One forward+backward of the engine; returns (outputs dict, layout, fp32 grad arena).
+    `taps`: optional dict that receives the per-layer outputs (see `Engine.taps`)."""
     L = ArenaLayout(cfg)
     w32 = torch.zeros(L.total)
     for n, (off, num, _) in L.offsets.items():
@@ -57,6 +58,7 @@ def run_engine(cfg, sd, batch, noise, ops, device, adt, py_seed, training=False)
     rng = torch.tensor([1234, 0], dtype=torch.int64, device=device)
     eng = Engine(cfg, L, ops, w, g, rng, adt)
     eng.training = training
+    eng.taps = taps
     random.seed(py_seed)
     plan = build_struct_plan(batch["index_p"].numpy(), batch["index_v"].numpy(), batch["input_ids_pv"].shape[1],
                              cfg.num_negative_pv)
@@ -109,6 +111,31 @@ def compare_with_golden(fx, out, L, g, loss_rtol, grad_tol, key_bias_atol=None, 
         if not (e1 <= grad_tol and e2 <= grad_tol):
             errs.append("%s: norm err %.3e sampled rel-L2 err %.3e" % (n, e1, e2))
     return errs, worst
+
+
+def compare_taps(fx, taps, tol):
+    """Per-layer activations against the hooks on the unmodified reference (fixture `taps`): for every
+    BertLayer / BertImageLayer / BertConnectionLayer call, |norm - ref| / ref and the relative L2 error over
+    256 sampled elements.  -> (error strings, list of (sampled rel-L2, key))."""
+    errs, stats = [], []
+    ref_taps = fx["taps"]
+    missing = sorted(set(ref_taps) - set(taps))
+    if missing:
+        errs.append("missing taps: %s" % missing[:4])
+    for key, ref in ref_taps.items():
+        if key not in taps:
+            continue
+        got = taps[key].float().reshape(-1).cpu()
+        if got.numel() != ref["sample"].numel() and tuple(taps[key].shape) != (ref["shape"][0] * ref["shape"][1], ref["shape"][2]):
+            errs.append("%s: shape %s vs reference %s" % (key, tuple(taps[key].shape), ref["shape"]))
+            continue
+        e1 = abs(float(got.norm()) - ref["norm"]) / ref["norm"]
+        smp = ref["sample"]
+        e2 = float((got[sample_index(got.numel())] - smp).norm()) / float(smp.norm())
+        stats.append((e2, key))
+        if not (e1 <= tol and e2 <= tol):
+            errs.append("%s: norm err %.3e sampled rel-L2 err %.3e" % (key, e1, e2))
+    return errs, stats
 
 
 # ---- item alignment (K3MForItemAlignment) ---------------------------------------------------------

@@ -24,7 +24,7 @@ from k3m_b200.synth import FORWARD_ORDER, synth_batch, synth_state_dict  # noqa:
 from oracle import ref_harness  # noqa: E402
 
 CASES = {
-    # name: (config, overrides, B, Lt, Lv, Lpv, max_num_pv, weight seed, batch seed, noise seed, py seed)
+    # name: (config, overrides, B, Lt, Lv, Lpv, max_num_pv, weight seed, batch seed, noise seed, py seed[, no_pv items])
     "tiny_hard": (K3M_TINY, dict(if_pre_sampling=1, margin=10.0, num_negative_pv=4), 4, 12, 9, 20, 4, 1, 7, 5, 3),
     "tiny_mean": (K3M_TINY, dict(if_pre_sampling=0, margin=1.0, num_negative_pv=4), 3, 16, 8, 24, 5, 2, 8, 0, 4),
     "tiny_inter": (K3M_TINY, dict(if_pre_sampling=3, margin=10.0, num_negative_pv=2), 5, 8, 12, 16, 3, 3, 9, 0, 5),
@@ -32,6 +32,19 @@ CASES = {
                   4, 36, 36, 36, 8, 1, 7, 0, 3),
     "base_hard": (K3M_BASE_6LAYER_6CONNECT, dict(if_pre_sampling=1, margin=10.0, num_negative_pv=4),
                   4, 36, 36, 36, 8, 1, 7, 5, 3),
+    # if_pre_sampling = 2: `pre_sampling_sequence_soft` (`vilbert_k3m.py:2300-2329`)
+    "tiny_soft": (K3M_TINY, dict(if_pre_sampling=2, margin=10.0, num_negative_pv=4), 4, 12, 9, 20, 4, 4, 10, 0, 6),
+    # items 0 and 1 without any property/value pair: the aggregator's bare `except` (`:2452-2456`) and the stale `t`
+    "tiny_nopv": (K3M_TINY, dict(if_pre_sampling=0, margin=1.0, num_negative_pv=4), 5, 12, 9, 20, 4, 5, 11, 0, 7, (0, 1, 3)),
+    # the benchmark's batch (BASELINE configs[1]): the CTA-pair GEMM variants and their fused epilogues only run at
+    # these sizes (M = 9216 / 4736 / 2304 rows)
+    "base_hard_b64": (K3M_BASE_6LAYER_6CONNECT, dict(if_pre_sampling=1, margin=10.0, num_negative_pv=4),
+                      64, 36, 36, 36, 8, 1, 7, 5, 3),
+    "base_mean_b64": (K3M_BASE_6LAYER_6CONNECT, dict(if_pre_sampling=0, margin=10.0, num_negative_pv=4),
+                      64, 36, 36, 36, 8, 1, 7, 0, 3),
+    # BASELINE configs[3] geometry (128-token titles, 100 regions, 128 PV tokens): the > 128-token attention kernels
+    "long_hard": (K3M_BASE_6LAYER_6CONNECT, dict(if_pre_sampling=1, margin=10.0, num_negative_pv=4),
+                  2, 128, 100, 128, 16, 6, 12, 8, 9),
 }
 
 
@@ -48,8 +61,38 @@ def make_noise(cfg, B, Lt, Lv1, Lpv, seed):
     return out
 
 
+TAP_PREFIXES = ("encoder.layer.", "encoder.v_layer.", "encoder.c_layer.", "encoder.c_layer_pv_v.",
+                "encoder.c_layer_pv_t.")
+
+
+def install_taps(model, taps):
+    """Forward hooks on every `BertLayer` (`vilbert_k3m.py:535-548`), `BertImageLayer` (`:696-709`) and
+    `BertConnectionLayer` / `_two_text` (`:1030-1111`) of the unmodified reference: per call, the L2 norm and
+    256 sampled elements of each hidden-state output.  Key: "<module name>#<call index>[/<output index>]";
+    the call order of a shared module is the order of the three encoder passes (`:1686-1750`)."""
+    calls = {}
+
+    def hook_for(name, n_out):
+        def hook(mod, args, out):
+            k = calls.get(name, 0)
+            calls[name] = k + 1
+            for j in range(n_out):
+                x = out[j].detach().reshape(-1)
+                key = "%s#%d" % (name, k) + ("/%d" % j if n_out > 1 else "")
+                taps[key] = dict(norm=float(x.norm()), sample=x[sample_index(x.numel())].clone(), shape=tuple(out[j].shape))
+        return hook
+
+    handles = []
+    for name, mod in model.named_modules():
+        for p in TAP_PREFIXES:
+            if name.startswith(p) and name[len(p):].isdigit():
+                handles.append(mod.register_forward_hook(hook_for(name, 2 if ".c_layer" in name else 1)))
+    return handles
+
+
 def run_case(name):
-    d, ov, B, Lt, Lv, Lpv, mpv, wseed, bseed, nseed, pyseed = CASES[name]
+    d, ov, B, Lt, Lv, Lpv, mpv, wseed, bseed, nseed, pyseed = CASES[name][:11]
+    no_pv = CASES[name][11] if len(CASES[name]) > 11 else ()
     ref, rcfg, model = ref_harness.make_reference_model(d, ov)
     cfg = BertConfig.from_dict(d)
     for k, v in ov.items():
@@ -60,8 +103,10 @@ def run_case(name):
     model.load_state_dict(full)
     model.tie_weights()
     model.eval()
-    batch = synth_batch(cfg, B, Lt, Lv, Lpv, max_num_pv=mpv, seed=bseed)
+    batch = synth_batch(cfg, B, Lt, Lv, Lpv, max_num_pv=mpv, seed=bseed, no_pv=no_pv)
     noise = make_noise(cfg, B, Lt, Lv + 1, Lpv, nseed) if cfg.if_pre_sampling == 1 else None
+    taps = {}
+    handles = install_taps(model, taps)
     orig = F.gumbel_softmax
     if noise is not None:
         order = iter(["v", "t", "pv"])   # call order in get_sequence_pooled_output_final (:2387-2392)
@@ -80,6 +125,8 @@ def run_case(name):
                 next_sentence_label_pv_t=batch["next_sentence_label_pv_t"],
                 index_p=batch["index_p"], index_v=batch["index_v"], device="cpu")
     F.gumbel_softmax = orig
+    for h in handles:
+        h.remove()
     (out[0] + out[1] + out[3] + out[9]).backward()      # pretrain.py:1055
     grads = {}
     for n, p in model.named_parameters():
@@ -88,7 +135,7 @@ def run_case(name):
             continue
         g = p.grad.reshape(-1)
         grads[n] = dict(norm=float(g.norm()), maxabs=float(g.abs().max()), sample=g[sample_index(g.numel())].clone())
-    fx = dict(case=name, config=d, overrides=ov, dims=(B, Lt, Lv, Lpv, mpv),
+    fx = dict(case=name, config=d, overrides=ov, dims=(B, Lt, Lv, Lpv, mpv), no_pv=tuple(no_pv), taps=taps,
               seeds=dict(weights=wseed, batch=bseed, noise=nseed, python=pyseed),
               noise=noise,
               losses=dict(loss_t=float(out[0]), loss_v=float(out[1]), loss_pv=float(out[3]),
@@ -106,6 +153,8 @@ ALIGN_CASES = {
     # name: (config, overrides, pairs, Lt, Lv, Lpv, max_num_pv, weight seed, batch seed, noise seed)
     "align_tiny_mean": (K3M_TINY, dict(if_pre_sampling=0, loss_type="ce"), 3, 12, 9, 20, 4, 11, 17, 0),
     "align_tiny_hard": (K3M_TINY, dict(if_pre_sampling=1, loss_type="ce"), 4, 10, 8, 16, 3, 12, 18, 6),
+    # run_finetune_item_alignment.sh:40-43 lengths (50-token titles, 36 regions, 256 PV tokens), base config
+    "align_base_hard": (K3M_BASE_6LAYER_6CONNECT, dict(if_pre_sampling=1, loss_type="ce"), 2, 50, 36, 256, 16, 13, 19, 7),
 }
 ITEM_KEYS = ("input_ids", "token_type_ids", "attention_mask", "input_ids_pv", "token_type_ids_pv",
              "attention_mask_pv", "index_p", "index_v", "image_feat", "image_loc", "image_attention_mask")
