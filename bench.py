@@ -27,17 +27,47 @@ sys.path.insert(0, ROOT)
 
 METRIC = "pretrain samples/sec (fwd+bwd+opt)"
 UNIT = "samples/s"
-DIMS = dict(len_t=36, len_v=36, len_pv=36, max_num_pv=8)
-PER_GPU_BATCH = 64
-# algorithmic FLOPs of the reference graph as written, fwd+bwd, 36/37/36 (FlopCounterMode probe)
-FLOPS_PER_SAMPLE = 159.6e9
+# algorithmic FLOPs of the reference graph as written, fwd+bwd (FlopCounterMode probe)
+WORKLOADS = {
+    # BASELINE configs[1] (N = 1) / configs[2] (N = 8, global batch 512): the headline
+    "base": dict(kind="pretrain", per_gpu=64, dims=dict(len_t=36, len_v=36, len_pv=36, max_num_pv=8),
+                 flops_per_unit=159.6e9, metric=METRIC, unit="samples/s",
+                 text="K3M pretrain step, bert_base_6layer_6conect, batch 64/GPU, 36 title / 36+1 regions x 2048 / "
+                      "36 PV tokens, MLM-t + MRM-KL + MLM-pv + LPM (+ITM value), dropout on"),
+    # BASELINE configs[3]: 128-token titles, 100 regions, 128 PV tokens, batch 128 on 8 GPUs = 16 per GPU
+    "long": dict(kind="pretrain", per_gpu=16, dims=dict(len_t=128, len_v=100, len_pv=128, max_num_pv=30),
+                 flops_per_unit=546.7e9, metric=METRIC + ", long-context variant", unit="samples/s",
+                 text="K3M pretrain step, long-context variant (BASELINE configs[3]): batch 16/GPU (128 on 8 GPUs), 128 "
+                      "title / 100+1 regions x 2048 / 128 PV tokens, all losses, dropout on"),
+    # BASELINE configs[4]: item-alignment finetune (run_finetune_item_alignment.sh:40-43), 256 pairs on 8 GPUs
+    "align": dict(kind="alignment", per_gpu=32, dims=dict(len_t=50, len_v=36, len_pv=256, max_num_pv=30),
+                  flops_per_unit=1081e9, metric="item-alignment finetune pairs/sec (fwd+bwd+opt)", unit="pairs/s",
+                  text="K3MForItemAlignment finetune step (BASELINE configs[4]): 32 pairs/GPU (256 on 8 GPUs), 50 title / "
+                       "36+1 regions / 256 PV tokens per item, ce head, dropout on"),
+}
+DIMS = WORKLOADS["base"]["dims"]
+PER_GPU_BATCH = WORKLOADS["base"]["per_gpu"]
+FLOPS_PER_SAMPLE = WORKLOADS["base"]["flops_per_unit"]
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of the GEMM kernel, mean per launch over the launches captured by
-# `ncu --set full -k regex:gemm_kernel -s 700 -c 6 python bench.py --steps 1 --warmup 1` (round 1, third capture)
-NCU_GEMM_TRAFFIC_BYTES = 51.0e6
-NCU_GEMM_TRAFFIC_NOTE = ("mean DRAM bytes per launch over 6 captured launches of the text-stack forward GEMMs "
-                         "(profiles/r01c_ncu_full_gemm.csv); their algorithmic bytes average 54 MB")
+def ncu_gemm_traffic():
+    """`roofline.traffic`: mean dram__bytes_read.sum + dram__bytes_write.sum per launch of the GEMM kernel, read
+    from the committed `ncu --set full` capture of THIS round's build (profiles/r02_ncu_gemm_full.csv, written by
+    tools/ncu_summary.py from the .ncu-rep).  None (unmeasured) when the file is absent."""
+    p = os.path.join(ROOT, "profiles", "r02_ncu_gemm_full.csv")
+    if not os.path.exists(p):
+        return None, "unmeasured: profiles/r02_ncu_gemm_full.csv absent"
+    import csv
+    tot, n = 0.0, 0
+    for row in csv.DictReader(open(p)):
+        try:
+            tot += float(row["dram_bytes_read"]) + float(row["dram_bytes_write"])
+            n += 1
+        except (KeyError, ValueError):
+            continue
+    if n == 0:
+        return None, "unmeasured: no launches in profiles/r02_ncu_gemm_full.csv"
+    return tot / n, "mean over the %d gemm_kernel launches in profiles/r02_ncu_gemm_full.csv (ncu --set full)" % n
 
 
 def load_peaks():
@@ -49,10 +79,10 @@ def load_peaks():
     return dict(hbm_gbs=6650.0, tflops=1590.0, tflops_sustained=1400.0, source="fallback")
 
 
-def workload_config(n_gpus):
-    return {"workload": "K3M pretrain step, bert_base_6layer_6conect, batch %d/GPU, 36 title / 36+1 regions x 2048 / "
-                        "36 PV tokens, MLM-t + MRM-KL + MLM-pv + LPM (+ITM value), dropout on" % PER_GPU_BATCH,
-            "global_batch": PER_GPU_BATCH * n_gpus, "per_gpu_batch": PER_GPU_BATCH,
+def workload_config(n_gpus, workload="base"):
+    w = WORKLOADS[workload]
+    return {"workload": w["text"], "name": workload,
+            "global_batch": w["per_gpu"] * n_gpus, "per_gpu_batch": w["per_gpu"],
             "parallelism": "dp%d" % n_gpus,
             "l2": "no explicit flush: one step streams > 20 GB (weights, moments, gradients) through a 126 MB L2"}
 
@@ -101,11 +131,16 @@ class ClockSampler(object):
 
 
 # ---- CPU arm: the oracle port of the reference step on the host cores ---------------------------------
+CPU_ARM_NOTE = ("oracle port (oracle/k3m_oracle.py: fp32 autograd restatement of the reference step + torch.optim.AdamW with "
+                "the reference's two groups), train mode (dropout ON, on-host Gumbel noise), batch 8 = BASELINE configs[0] "
+                "of the same 36/37/36 workload; the unmodified reference itself cannot travel to the GPU box and measured "
+                "~1.4x SLOWER than this port in the build container (4.0 vs 2.7-3.0 s/step, 8 threads), so the ratio "
+                "against this arm is conservative")
+
+
 def cpu_reference_step_rate(steps, warmup, batch=8, threads=None):
-    """samples/s of the CPU restatement of the reference step (oracle/k3m_oracle.py: fp32 forward
-    through autograd, backward, torch.optim.AdamW with the reference's two groups), dropout off
-    (the restatement is deterministic; dropout is < 1 % of the reference's CPU time).  One step =
-    BASELINE configs[0]: batch 8 of the same 36/37/36 workload."""
+    """samples/s of the CPU restatement of the reference step: fp32 forward through autograd, backward,
+    torch.optim.AdamW (two groups), dropout on.  One step = BASELINE configs[0]: batch 8 at 36/37/36."""
     import random
     import torch
     from k3m_b200.layout import is_no_decay, param_spec
@@ -119,7 +154,7 @@ def cpu_reference_step_rate(steps, warmup, batch=8, threads=None):
     groups = [dict(params=[p for n, p in params.items() if not is_no_decay(n)], weight_decay=0.01),
               dict(params=[p for n, p in params.items() if is_no_decay(n)], weight_decay=0.0)]
     opt = torch.optim.AdamW(groups, lr=1e-4, betas=(0.9, 0.98), eps=1e-8)
-    orc = Oracle(cfg, params)
+    orc = Oracle(cfg, params, training=True)
     batches = [synth_batch(cfg, batch, DIMS["len_t"], DIMS["len_v"], DIMS["len_pv"], DIMS["max_num_pv"], seed=100 + i)
                for i in range(2)]
     times = []
@@ -140,24 +175,37 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    steps = max(1, min(args.steps, 10))           # ~1.4 s per step on the GPU box's 16 cores: bounded to ~15 s
-    warm = max(1, min(args.warmup, 2))
+    # 3 warm-up + 10 timed steps (~1.5-3 s each on the GPU box's host cores: well under a minute)
+    steps = max(1, min(args.steps, 10))
+    warm = max(1, min(args.warmup, 3))
     v, sec, threads, batch = cpu_reference_step_rate(steps, warm)
-    sample = "%d step(s) of batch %d (BASELINE configs[0]) after %d warm-up, fp32, %d threads" % (steps, batch, warm, threads)
+    sample = "%d step(s) of batch %d (BASELINE configs[0]) after %d warm-up, fp32, dropout on, %d threads" % (steps, batch, warm, threads)
+    # `config` is the GPU arm's (the driver pairs the two lines by it); what THIS arm actually ran — a bounded sample
+    # of that workload — is spelled out in `sample` / `reference_arm_note`
+    cfgd = workload_config(args.gpus)
+    note = ("bounded sample of the configured workload: batch %d per step (BASELINE configs[0]) instead of 64/GPU, same "
+            "36 title / 36+1 regions x 2048 / 36 PV shapes, all losses, dropout ON, fp32, %d host threads; samples/s is "
+            "the comparable unit.  " % (batch, threads)) + CPU_ARM_NOTE
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": warm, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.gpus),
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfgd,
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "reference_arm_note": note, "gpu_launches": 0}
     print(json.dumps(line))
     return 0
 
 
 # ---- GPU arm ------------------------------------------------------------------------------------------
+HBM_KERNELS = ("k3m_ln_fwd", "k3m_ln_bwd", "k3m_colsum", "k3m_xent_fwd_bwd", "k3m_kl_fwd_bwd", "k3m_adamw",
+               "k3m_embed_fwd", "k3m_embed_bwd", "k3m_relu_cat3", "k3m_fuse_select_fwd", "k3m_fuse_select_bwd",
+               "k3m_relu_bwd_split3", "k3m_axpy", "k3m_cast")
+
+
 def kernel_breakdown(step, batch):
     """One eager (non-graph) step with every launch bracketed by CUDA events on the launching stream:
-    -> {entry point: (launches, total ms, total FLOPs)}.  Parameters/optimizer state are restored."""
+    -> ({entry point: (launches, total ms, total FLOPs)}, serial GEMM pass ms, hbm kernel rows).
+    Parameters/optimizer state are restored."""
     import torch
     snap = (step.p32.clone(), step.m.clone(), step.v.clone(), step.w16.clone(), step.rng.clone())
     use_graph, step.use_graph = step.use_graph, False
@@ -168,7 +216,7 @@ def kernel_breakdown(step, batch):
     # while it runs on the other stream is not that kernel's duration (the 2 us axpy measured 38 us)
     overlap_opt, step.overlap_opt = step.overlap_opt, False
     step.ops.timing = []
-    step.ops.record = {"k3m_gemm_bf16": []}
+    step.ops.record = {n: [] for n in ("k3m_gemm_bf16", "k3m_gemm_grouped_bf16") + HBM_KERNELS}
     # keep the device ~400 ms behind the host for the WHOLE eager step (1215 launches at ~40 us of host time
     # each outrun a 100 ms head start, after which the pairs of the late backward kernels measured the
     # host's launch gaps): the event pairs then bracket kernels that run back to back
@@ -176,54 +224,95 @@ def kernel_breakdown(step, batch):
     step.step(batch)
     torch.cuda.synchronize()
     rows, step.ops.timing = step.ops.timing, None
-    gemm_calls, step.ops.record = step.ops.record["k3m_gemm_bf16"], None
+    rec, step.ops.record = step.ops.record, None
     step.use_graph = use_graph
     step.world = world
     step.overlap_opt = overlap_opt
     step.global_step -= 1
-    for dst, src in zip((step.p32, step.m, step.v, step.w16, step.rng), snap):
-        dst.copy_(src)
     out = {}
     for name, work, e0, e1 in rows:
         n, ms, fl = out.get(name, (0, 0.0, 0.0))
         out[name] = (n + 1, ms + e0.elapsed_time(e1), fl + work)
-    return out, replay_serial(step, "k3m_gemm_bf16", gemm_calls)
+    gemm_calls = [(n, a) for n in ("k3m_gemm_bf16", "k3m_gemm_grouped_bf16") for a, _ in rec[n]]
+    # GEMM launches in issue order do not matter for a serial pass; single and grouped entry points are replayed together
+    gemm_ms = replay_serial(step, gemm_calls)
+    hbm = []
+    for n in HBM_KERNELS:
+        calls = rec[n]
+        if not calls:
+            continue
+        ms = replay_serial(step, [(n, a) for a, _ in calls])
+        nbytes = sum(b for _, b in calls)
+        hbm.append({"kernel": n, "launches": len(calls), "bytes_per_step": nbytes, "ms_serial": round(ms, 4),
+                    "gbs": round(nbytes / (ms * 1e-3) / 1e9, 1) if ms > 0 else None})
+    for dst, src in zip((step.p32, step.m, step.v, step.w16, step.rng), snap):
+        dst.copy_(src)
+    step.g32.zero_()
+    torch.cuda.synchronize()
+    return out, gemm_ms, hbm
 
 
-def replay_serial(step, name, calls, reps=3):
-    """The step's launches of one entry point (same pointers, shapes, epilogues) re-issued back to back on one
+def replay_serial(step, calls, reps=3):
+    """The step's launches of one kernel family (same pointers, shapes, epilogues) re-issued back to back on one
     stream and timed with ONE event pair: an event pair per launch costs several microseconds of its own,
     which is a third of a small GEMM.  Operands are whatever the finished step left at those addresses
-    (duration does not depend on values); accumulating weight-gradient launches land in the gradient arena,
-    which is zeroed again afterwards.  -> ms for one pass over all the launches."""
+    (duration does not depend on values); accumulating launches land in the gradient arena / parameters, which the
+    caller restores afterwards.  `calls`: [(entry point, ctypes argument tuple)].  -> ms for one pass."""
     import ctypes
     import torch
-    fn = getattr(step.ops.lib, name)
     s = torch.cuda.Stream(device=step.device)
     s.wait_stream(torch.cuda.current_stream())
     st = ctypes.c_void_p(s.cuda_stream)
+    fns = [(getattr(step.ops.lib, n), a[:-1]) for n, a in calls]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with torch.cuda.stream(s):
-        for a in calls:                                  # warm-up pass
-            fn(*a[:-1], st)
+        for fn, a in fns:                                # warm-up pass
+            fn(*a, st)
         torch.cuda._sleep(int(4.0e7))                    # ~20 ms head start for the host
         e0.record(s)
         for _ in range(reps):
-            for a in calls:
-                fn(*a[:-1], st)
+            for fn, a in fns:
+                fn(*a, st)
         e1.record(s)
     s.synchronize()
     torch.cuda.current_stream().wait_stream(s)
-    step.g32.zero_()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / reps
+
+
+def build_step(workload, dev, group):
+    """-> (step object, list of pinned host batches, units per step per GPU)"""
+    import torch
+    from k3m_b200.synth import synth_batch
+    from k3m_b200.trainer import AlignmentStep, PretrainStep
+    rank = int(os.environ.get("RANK", "0"))
+    w = WORKLOADS[workload]
+    cfg = make_cfg()
+    B, d = w["per_gpu"], w["dims"]
+    host = []
+    if w["kind"] == "pretrain":
+        step = PretrainStep(cfg, B, device=dev, init_seed=0, lr=1e-4, warmup_steps=100, total_steps=100000,
+                            training=True, rng_seed=1234, use_graph=True, process_group=group, **d)
+        for i in range(4):
+            b = synth_batch(cfg, B, d["len_t"], d["len_v"], d["len_pv"], d["max_num_pv"], seed=1234 + 97 * rank + i)
+            host.append({k: v.pin_memory() for k, v in b.items()})
+    else:
+        cfg.loss_type = "ce"
+        keys = ("input_ids", "token_type_ids", "attention_mask", "input_ids_pv", "token_type_ids_pv",
+                "attention_mask_pv", "index_p", "index_v", "image_feat", "image_loc", "image_attention_mask")
+        step = AlignmentStep(cfg, B, device=dev, init_seed=1, lr=1e-4, warmup_steps=100, total_steps=100000,
+                             training=True, rng_seed=1234, use_graph=True, process_group=group, **d)
+        for i in range(4):
+            b = synth_batch(cfg, 2 * B, d["len_t"], d["len_v"], d["len_pv"], d["max_num_pv"], seed=1234 + 97 * rank + i)
+            hb = {k: b[k].pin_memory() for k in keys}
+            hb["labels"] = torch.randint(0, 2, (B,), generator=torch.Generator().manual_seed(i + 7 * rank)).pin_memory()
+            host.append(hb)
+    return step, host, B
 
 
 def run_gpu_arm(args):
     import torch
     import torch.distributed as dist
-    from k3m_b200.synth import synth_batch
-    from k3m_b200.trainer import PretrainStep
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -236,15 +325,8 @@ def run_gpu_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
-    cfg = make_cfg()
-    B = PER_GPU_BATCH
-    step = PretrainStep(cfg, B, device=dev, init_seed=0, lr=1e-4, warmup_steps=100, total_steps=100000,
-                        training=True, rng_seed=1234, use_graph=True, process_group=group, **DIMS)
-    host = []
-    for i in range(4):
-        b = synth_batch(cfg, B, DIMS["len_t"], DIMS["len_v"], DIMS["len_pv"], DIMS["max_num_pv"],
-                        seed=1234 + 97 * rank + i)
-        host.append({k: v.pin_memory() for k, v in b.items()})
+    W = WORKLOADS[args.workload]
+    step, host, B = build_step(args.workload, dev, group)
 
     def barrier():
         if world > 1:
@@ -294,6 +376,11 @@ def run_gpu_arm(args):
     ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
     note("end-to-end loop done: %.3f ms/step" % ms_e2e)
     clk = clocks.stop() if clocks is not None else None
+    comm = None
+    if world > 1 and hasattr(step, "comm_timing"):
+        comm = step.comm_timing(host[0])           # one instrumented non-graph step, every rank takes part
+        barrier()
+
     def finish():
         """Leave cleanly at N > 1: the captured graph holds NCCL kernels, and tearing the communicator down
         under it has been seen to block forever (N = 2, exit only by the launcher's timeout).  Release the
@@ -315,31 +402,36 @@ def run_gpu_arm(args):
         finish()
         return 0
     peaks = load_peaks()
-    kb, gemm_serial_ms = kernel_breakdown(step, host[0])
+    kb, gemm_serial_ms, hbm = kernel_breakdown(step, host[0])
+    for h in hbm:
+        h["frac_of_hbm_peak"] = round(h["gbs"] / peaks["hbm_gbs"], 3) if h["gbs"] else None
     tot_ms = sum(v[1] for v in kb.values())
-    shapes = {k: v for k, v in kb.items() if k.startswith("k3m_gemm_bf16 ")}
+    shapes = {k: v for k, v in kb.items() if k.startswith("k3m_gemm")}
     merged = {}
     for k, v in kb.items():
         n = k.split(" ")[0]
         a = merged.get(n, (0, 0.0, 0.0))
         merged[n] = (a[0] + v[0], a[1] + v[1], a[2] + v[2])
     kb = merged
-    g_n, g_ms, g_fl = kb.get("k3m_gemm_bf16", (0, 1e-9, 0.0))
+    g_n = sum(v[0] for k, v in kb.items() if k.startswith("k3m_gemm"))
+    g_ms = sum(v[1] for k, v in kb.items() if k.startswith("k3m_gemm")) or 1e-9
+    g_fl = sum(v[2] for k, v in kb.items() if k.startswith("k3m_gemm"))
     gemm_tflops = g_fl / (gemm_serial_ms * 1e-3) / 1e12
-    samples = B * world
-    step_tflops = FLOPS_PER_SAMPLE * B / (ms_dev * 1e-3) / 1e12        # per GPU
+    units = B * world
+    step_tflops = W["flops_per_unit"] * B / (ms_dev * 1e-3) / 1e12        # per GPU
+    traffic, traffic_note = ncu_gemm_traffic()
     line = {
-        "metric": METRIC, "value": samples / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "metric": W["metric"], "value": units / (ms_dev * 1e-3), "unit": W["unit"], "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(world),
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(world, args.workload),
         "clocks": clk,
-        "e2e": {"value": samples / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+        "e2e": {"value": units / (ms_e2e * 1e-3), "unit": W["unit"], "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": step.h2d_bytes, "d2h_bytes_per_step": step.d2h_bytes},
         "gpu_launches": step.launches_per_step * args.steps * 2,
         "launches_per_step": step.launches_per_step,
-        "roofline": {"bound": "tensor", "kernel": "gemm_kernel (k3m_gemm_bf16: tcgen05/TMEM/TMA)",
+        "roofline": {"bound": "tensor", "kernel": "gemm_kernel (k3m_gemm_bf16 / k3m_gemm_grouped_bf16: tcgen05/TMEM/TMA)",
                      "achieved": gemm_tflops, "peak": peaks["tflops"], "unit": "TFLOP/s",
-                     "frac": gemm_tflops / peaks["tflops"], "traffic": NCU_GEMM_TRAFFIC_BYTES, "traffic_note": NCU_GEMM_TRAFFIC_NOTE,
+                     "frac": gemm_tflops / peaks["tflops"], "traffic": traffic, "traffic_note": traffic_note,
                      "peak_source": peaks["source"],
                      "launches_per_step": g_n, "ms_per_step_in_kernel": gemm_serial_ms,
                      "ms_per_step_in_kernel_event_pair_per_launch": g_ms,
@@ -349,19 +441,24 @@ def run_gpu_arm(args):
                             "stream, one CUDA-event pair around the pass, mean of 3 passes; "
                             "ms_per_step_in_kernel_event_pair_per_launch and kernel_ms bracket EVERY launch of one eager "
                             "step with its own event pair, which adds several microseconds to each" % g_n},
-        "step_roofline": {"bound": "tensor", "flops_per_sample": FLOPS_PER_SAMPLE, "achieved": step_tflops,
+        "step_roofline": {"bound": "tensor", "flops_per_unit": W["flops_per_unit"], "achieved": step_tflops,
                           "peak": peaks["tflops_sustained"], "unit": "TFLOP/s per GPU",
                           "frac": step_tflops / peaks["tflops_sustained"], "frac_of_burst": step_tflops / peaks["tflops"]},
+        "hbm_kernels": {"peak_gbs": peaks["hbm_gbs"], "how": "algorithmic bytes of the step's launches of each row-wise kernel "
+                        "(inputs read once + outputs written once) / one serial back-to-back replay of exactly those launches",
+                        "rows": hbm},
         "kernel_ms": {k: {"launches": v[0], "ms": round(v[1], 4)} for k, v in sorted(kb.items(), key=lambda kv: -kv[1][1])},
-        "gemm_shapes": {k[len("k3m_gemm_bf16 "):]: {"launches": v[0], "ms": round(v[1], 4), "tflops": round(v[2] / max(v[1], 1e-9) / 1e9, 1)}
+        "gemm_shapes": {k: {"launches": v[0], "ms": round(v[1], 4), "tflops": round(v[2] / max(v[1], 1e-9) / 1e9, 1)}
                         for k, v in sorted(shapes.items(), key=lambda kv: -kv[1][1])},
         "losses_first": loss0, "losses_last": last,
     }
-    if world == 1 and not args.no_cpu_baseline:
-        v, sec, threads, batch = cpu_reference_step_rate(8, 2)       # ~10-15 s of host work on the GPU box
+    if comm is not None:
+        line["comm"] = comm
+    if world == 1 and not args.no_cpu_baseline and args.workload == "base":
+        v, sec, threads, batch = cpu_reference_step_rate(8, 2)       # ~15-25 s of host work on the GPU box
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": "8 steps of batch %d (BASELINE configs[0]) after 2 warm-ups: oracle port "
-                                          "(fp32 autograd restatement + torch.optim.AdamW), %.1f s/step" % (batch, sec)}
+                                "sample": "8 steps of batch %d (BASELINE configs[0]) after 2 warm-ups, dropout on, %.1f s/step: %s"
+                                          % (batch, sec, CPU_ARM_NOTE)}
     print(json.dumps(line))
     finish()
     return 0
@@ -374,6 +471,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="k3m_b200", choices=["k3m_b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="base", choices=sorted(WORKLOADS),
+                    help="base = BASELINE configs[1]/[2] (the headline); long = configs[3]; align = configs[4]")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)

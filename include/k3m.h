@@ -54,6 +54,10 @@ int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int layout, in
                   const void* addend, int ld_add, int addend_f32, const void* rng,
                   unsigned int drop_site, float drop_p, void* stream);
 
+/* Debug aid: a description of the kernel variant the calling thread's last GEMM call dispatched
+ * ("bn=256 ctas=2 ew=4 ... epi=F_ADD ...").  Parity tests assert that they ran the benchmark's variant. */
+const char* k3m_gemm_last_variant(void);
+
 /* BertLayerNorm (vilbert_k3m.py:319-332): TF style, biased variance, eps inside the sqrt.      */
 int k3m_ln_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
                int M, int H, float eps, const void* rng, unsigned int site, float drop_p, void* stream);

@@ -26,6 +26,7 @@ def load():
     lib = ctypes.CDLL(LIB_PATH)
     lib.k3m_last_error_string.restype = ctypes.c_char_p
     lib.k3m_get_version.restype = ctypes.c_int
+    lib.k3m_gemm_last_variant.restype = ctypes.c_char_p
     _lib = lib
     return lib
 

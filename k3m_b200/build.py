@@ -15,8 +15,14 @@ def sources():
     return sorted(glob.glob(os.path.join(HERE, "csrc", "*.cu")))
 
 
+STAMP = os.path.join(HERE, "csrc", "build", "flags.txt")
+
+
 def needs_build():
     if not os.path.exists(LIB):
+        return True
+    # a library built with other flags (e.g. a -DK3M_GEMM_PROBE_BUILD measurement build) is stale for this run
+    if not os.path.exists(STAMP) or open(STAMP).read() != " ".join(FLAGS):
         return True
     t = os.path.getmtime(LIB)
     deps = sources() + glob.glob(os.path.join(HERE, "csrc", "*.cuh"))
@@ -44,6 +50,8 @@ def build(force=False, verbose=False):
             raise RuntimeError("nvcc failed on %s" % src)
     cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-lcudart"]
     subprocess.check_call(cmd)
+    with open(STAMP, "w") as f:
+        f.write(" ".join(FLAGS))
     return LIB
 
 

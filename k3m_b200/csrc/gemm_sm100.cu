@@ -917,7 +917,13 @@ int pick_bn(int M, int N, int K, int force) {
   return (N >= 256 && tiles256 >= (long)num_sms() * 3 / 4) ? 256 : 128;
 }
 
+// what the last k3m_gemm_bf16 / k3m_gemm_grouped_bf16 call of this thread dispatched (tests assert that the
+// benchmark's kernel variant is the one they exercised)
+thread_local char g_variant[160] = "";
+
 }  // namespace
+
+extern "C" const char* k3m_gemm_last_variant(void) { return g_variant; }
 
 extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int layout, int M, int N, int K,
                              void* out, int ldc, int out_f32, int accumulate, const void* bias, int act,
@@ -1048,6 +1054,11 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
     } else if (act == ACT_DGELU && p.tin == 1 && addend == nullptr && bias == nullptr && !has_drop) {
       p.fast = F_DGELU;
     }
+  }
+  {
+    static const char* fast_names[] = {"generic", "F_PLAIN", "F_ADD", "F_GELU", "F_DGELU"};
+    snprintf(g_variant, sizeof(g_variant), "bn=%d ctas=%d ew=%d dual=%d splits=%d epi=%s tin=%d tma_out=%d acc=%d",
+             bn, ctas, dual ? 2 : ew, dual ? 1 : 0, p.splits, fast_names[p.fast], p.tin, p.tma_out, accumulate);
   }
   if (layout == 0) return dispatch<false, false>(bn, dual ? 0 : ew, ctas, ma, mb, mc, mx, mi, p, st);
   if (layout == 1) return dispatch<false, true>(bn, dual ? 0 : ew, ctas, ma, mb, mc, mx, mi, p, st);

@@ -25,7 +25,10 @@ __global__ void __launch_bounds__(256) xent_kernel(bf16* __restrict__ logits, in
   const int row = blockIdx.x;
   bf16* lr = logits + (size_t)row * ld;
   const long long lab = labels[row];
-  if (lab < 0) {
+  if (lab < 0 || lab >= V) {
+    // ignore_index = -1 (`vilbert_k3m.py:2207`); any other label outside [0, V) makes torch's CrossEntropyLoss
+    // raise — no exception can leave a captured graph, so the loss turns NaN instead of reading out of bounds
+    if ((lab < -1 || lab >= V) && threadIdx.x == 0) atomicAdd(loss, __int_as_float(0x7fc00000));
     if (write_grad)
       for (int c = threadIdx.x; c < ld; c += blockDim.x) lr[c] = __float2bfloat16(0.f);
     return;

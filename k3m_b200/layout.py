@@ -93,6 +93,14 @@ def param_spec(cfg, kind="pretrain"):
         raise ValueError("k3m_b200 implements the tri-modal path (use_image and with_coattention)")
     if cfg.task_specific_tokens or cfg.dynamic_attention:
         raise ValueError("task_specific_tokens / dynamic_attention are off on the K3M path")
+    # driver flags that change the computation (`pretrain.py:1350-1366` -> `vilbert_k3m.py:1185-1195` frozen
+    # leading layers, `:1228-1260` in-batch pairs, `:1262-1273` fast mode): not built — refuse instead of
+    # silently computing the default
+    for flag, default in (("fixed_t_layer", 0), ("fixed_v_layer", 0), ("in_batch_pairs", False), ("fast_mode", False)):
+        if getattr(cfg, flag, default) not in (default, None):
+            raise ValueError("%s=%r is not supported by k3m_b200 (only the default %r)" % (flag, getattr(cfg, flag), default))
+    if getattr(cfg, "visual_target", 0) != 0:
+        raise ValueError("visual_target=%r is not supported (only 0: KL against detector class distributions)" % cfg.visual_target)
     H, Hv, Hb = cfg.hidden_size, cfg.v_hidden_size, cfg.bi_hidden_size
     s = OrderedDict()
     s["embeddings.word_embeddings.weight"] = (cfg.vocab_size, H)

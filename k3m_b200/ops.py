@@ -44,6 +44,7 @@ class CudaOps(object):
         self.timing = None
         self.record = None          # {entry point: [argument tuples]} while a measurement collects launches
         self._work = 0.0
+        self._bytes = 0.0           # algorithmic HBM bytes of the next launch (set by HBM-bound ops while profiling)
         self._tag = ""
         self._side = []
         # auxiliary stream per launching stream for off-critical-path work (weight gradients):
@@ -126,7 +127,7 @@ class CudaOps(object):
     def _call(self, name, *args):
         self.launches += 1
         if self.record is not None and name in self.record:
-            self.record[name].append(args)
+            self.record[name].append((args, self._bytes))
         if self.timing is None:
             _lib.check(getattr(self.lib, name)(*args), name)
             return
@@ -136,7 +137,13 @@ class CudaOps(object):
         e1.record()
         self.timing.append((name + self._tag, self._work, e0, e1))
         self._work = 0.0
+        self._bytes = 0.0
         self._tag = ""
+
+    @staticmethod
+    def _nb(*tensors):
+        """bytes of the given tensors (None skipped): the algorithmic HBM traffic of a row-wise kernel"""
+        return float(sum(t.numel() * t.element_size() for t in tensors if t is not None))
 
     def _drop(self, drop, rng):
         if drop is None:
@@ -176,7 +183,12 @@ class CudaOps(object):
                    r, s, p, self._st())
         return out
 
+    def gemm_last_variant(self):
+        return self.lib.k3m_gemm_last_variant().decode()
+
     def colsum(self, x, out):
+        if self.timing is not None:
+            self._bytes = self._nb(x, out)
         self._call("k3m_colsum", _p(x), _i(_ld(x)), _i(_isf32(x)), _p(out), _i(x.shape[0]), _i(x.shape[1]),
                    self._st())
 
@@ -190,6 +202,8 @@ class CudaOps(object):
         mean = torch.empty(M, dtype=torch.float32, device=x.device)
         rstd = torch.empty(M, dtype=torch.float32, device=x.device)
         r, s, p = self._drop(drop, rng)
+        if self.timing is not None:
+            self._bytes = self._nb(x, out, mean, rstd, gamma, beta)
         self._call("k3m_ln_fwd", _p(x), _p(gamma), _p(beta), _p(out), _p(mean), _p(rstd), _i(M), _i(H),
                    _f(eps), r, s, p, self._st())
         return out, mean, rstd
@@ -202,6 +216,8 @@ class CudaOps(object):
         dxm = torch.empty(M, H, dtype=self.adt, device=x.device) if drop_in is not None else None
         po = drop_out if drop_out is not None else (0.0, 0)
         pi = drop_in if drop_in is not None else (0.0, 0)
+        if self.timing is not None:
+            self._bytes = self._nb(dy, x, dx, dxm, mean, rstd, gamma)
         self._call("k3m_ln_bwd", _p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dx), _p(dxm), _p(dgamma),
                    _p(dbeta), _p(dbias), _i(M), _i(H), _p(rng), _u(po[1]), _f(po[0]), _u(pi[1]), _f(pi[0]),
                    self._st())
@@ -235,12 +251,16 @@ class CudaOps(object):
         M, H = ids.numel(), word.shape[1]
         if out is None:
             out = torch.empty(M, H, dtype=self.adt, device=word.device)
+        if self.timing is not None:
+            self._bytes = 2.0 * self._nb(out) + ids.numel() * 16.0
         self._call("k3m_embed_fwd", _p(ids), _p(type_ids), _p(word), _p(pos), _p(typ), _p(out), _i(M), _i(L),
                    _i(H), self._st())
         return out
 
     def embed_bwd(self, dx, ids, type_ids, L, dword, dpos, dtyp):
         M, H = dx.shape
+        if self.timing is not None:      # read dx, fp32 read-modify-write of the touched word / position / type rows
+            self._bytes = self._nb(dx) + 3 * 8.0 * M * H
         self._call("k3m_embed_bwd", _p(dx), _p(ids), _p(type_ids), _p(dword), _p(dpos), _p(dtyp), _i(M), _i(L),
                    _i(H), self._st())
 
@@ -262,6 +282,8 @@ class CudaOps(object):
         M, H = a.shape
         if out is None:
             out = torch.empty(M, 3 * H, dtype=self.adt, device=a.device)
+        if self.timing is not None:
+            self._bytes = 2.0 * self._nb(out)
         self._call("k3m_relu_cat3", _p(a), _i(_ld(a)), _p(b), _i(_ld(b)), _p(c), _i(_ld(c)), _p(out), _i(M),
                    _i(H), self._st())
         return out
@@ -271,6 +293,8 @@ class CudaOps(object):
         assert gates.dtype == torch.float32 and gates.is_contiguous() and cat.is_contiguous()
         if out is None:
             out = torch.empty(M, H, dtype=self.adt, device=cat.device)
+        if self.timing is not None:
+            self._bytes = self._nb(cat, gates, out)
         self._call("k3m_fuse_select_fwd", _p(cat), _p(gates), _p(noise), _p(rng), _u(site), _p(out),
                    _i(_ld(out)), _i(M), _i(H), self._st())
         return out
@@ -279,6 +303,8 @@ class CudaOps(object):
         M, H = cat.shape[0], cat.shape[1] // 3
         dg = torch.empty(M, 3 * H, dtype=self.adt, device=cat.device)
         dc = torch.empty(M, 3 * H, dtype=self.adt, device=cat.device)
+        if self.timing is not None:
+            self._bytes = self._nb(cat, gates, dg, dc) + 2.0 * M * H
         self._call("k3m_fuse_select_bwd", _p(dout), _i(_ld(dout)), _p(cat), _p(gates), _p(noise), _p(rng),
                    _u(site), _p(dg), _p(dc), _i(M), _i(H), self._st())
         return dg, dc
@@ -297,6 +323,8 @@ class CudaOps(object):
 
     def relu_bwd_split3(self, dcat, cat, da, db, dc):
         M, H = da.shape
+        if self.timing is not None:      # read dcat, cat; read-modify-write the three gradient slices
+            self._bytes = self._nb(dcat, cat) + 2 * 3 * 2.0 * M * H
         self._call("k3m_relu_bwd_split3", _p(dcat), _p(cat), _p(da), _i(_ld(da)), _p(db), _i(_ld(db)), _p(dc),
                    _i(_ld(dc)), _i(M), _i(H), self._st())
 
@@ -310,6 +338,8 @@ class CudaOps(object):
 
     def axpy(self, x, y, alpha=1.0):
         rows, cols = x.shape
+        if self.timing is not None:
+            self._bytes = self._nb(x) + 2.0 * rows * cols * y.element_size()
         self._call("k3m_axpy", _p(x), _i(_ld(x)), _i(_isf32(x)), _p(y), _i(_ld(y)), _i(_isf32(y)), _f(alpha),
                    _i(rows), _i(cols), self._st())
 
@@ -317,6 +347,8 @@ class CudaOps(object):
         assert x.is_contiguous()
         y = out if out is not None else torch.empty(x.shape, dtype=dtype, device=x.device)
         assert y.is_contiguous() and y.dtype == dtype and y.numel() == x.numel()
+        if self.timing is not None:
+            self._bytes = self._nb(x, y)
         self._call("k3m_cast", _p(x), _i(_isf32(x)), _p(y), _i(_isf32(y)), _ll(x.numel()), self._st())
         return y
 
@@ -429,6 +461,8 @@ class CudaOps(object):
     def xent_fwd_bwd(self, logits, labels, count, n_cols, dlogits=None, grad_scale=1.0):
         assert dlogits is None or dlogits.data_ptr() == logits.data_ptr(), "gradient is written in place"
         loss = torch.zeros(1, dtype=torch.float32, device=logits.device)
+        if self.timing is not None:      # logits read once, gradient written once (the row stays in L1/L2 between passes)
+            self._bytes = 2.0 * self._nb(logits) if dlogits is not None else self._nb(logits)
         self._call("k3m_xent_fwd_bwd", _p(logits), _i(_ld(logits)), _p(labels), _p(count), _i(logits.shape[0]),
                    _i(n_cols), _f(grad_scale), _p(loss), _i(1 if dlogits is not None else 0), self._st())
         return loss
@@ -437,6 +471,8 @@ class CudaOps(object):
         assert logits.dtype == torch.float32 and target.dtype == torch.float32 and target.is_contiguous()
         assert dlogits is None or _ld(dlogits) == _ld(logits)
         loss = torch.zeros(1, dtype=torch.float32, device=logits.device)
+        if self.timing is not None:
+            self._bytes = self._nb(logits, target, dlogits)
         self._call("k3m_kl_fwd_bwd", _p(logits), _i(_ld(logits)), _p(target), _p(image_label), _p(count),
                    _i(logits.shape[0] // Lv1), _i(Lv1), _i(n_cols), _f(grad_scale), _p(loss), _p(dlogits),
                    self._st())
@@ -472,5 +508,7 @@ class CudaOps(object):
 
     # ---- optimizer -------------------------------------------------------------------------
     def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True):
+        if self.timing is not None:      # read p, g, m, v; write p, m, v, bf16 shadow, zeroed g: 34 B per parameter
+            self._bytes = p32.numel() * (34.0 if zero_grad else 30.0)
         self._call("k3m_adamw", _p(p32), _p(g32), _p(m), _p(v), _p(p_act), _p(hyper), _ll(p32.numel()),
                    _i(1 if zero_grad else 0), self._st())

@@ -17,7 +17,10 @@ def ops():
 
 # bf16 activations: loss 1e-3 (north_star), probabilities 2e-3 absolute, gradients at the bf16 storage
 # floor of the tiny configs (tests/test_step_gpu.py header); hard Gumbel pick: 2e-3 / floor-sized bound
-@pytest.mark.parametrize("name,loss_rtol,grad_tol", [("align_tiny_mean", 1e-3, 0.1), ("align_tiny_hard", 2e-3, 0.4)])
+# align_base_hard: the real bert_base_6layer_6conect towers at the finetune script's lengths (50 / 36+1 / 256 tokens,
+# run_finetune_item_alignment.sh:40-43) from the unmodified reference: pins the > 128-token attention kernels
+@pytest.mark.parametrize("name,loss_rtol,grad_tol", [("align_tiny_mean", 1e-3, 0.1), ("align_tiny_hard", 2e-3, 0.4),
+                                                     ("align_base_hard", 2e-3, 0.5)])
 def test_alignment_matches_reference(ops, name, loss_rtol, grad_tol):
     fx = load_golden(name)
     cfg, sd, batch, labels, noise = align_case_setup(fx)

@@ -128,6 +128,80 @@ def test_gemm_accumulate_split_k(ops, ref):
     close(got, want, 1e-4, 1e-4, "split-K accumulate")
 
 
+# ---- the benchmark's shapes (B = 64: M = 9216 text rows, 4736 image rows, 2304 / 2368 connection rows) ----------
+# The CTA-pair kernel (cta_group::2, 256 x 256 tile per pair) is only selected once a problem has >= 45 pair
+# tiles, so every fused epilogue is also checked at the sizes the timed step runs, and the test asserts which
+# variant the library dispatched.
+BENCH_EPILOGUES = [
+    # name, layout, M, N, K, kwargs builder, expected variant substrings
+    ("attn_out_text", "nt", 9216, 768, 768, "bias_drop_add", ("ctas=2", "epi=F_ADD", "tin=2")),
+    ("ffn_down_text", "nt", 9216, 768, 3072, "bias_drop_add", ("ctas=2", "epi=F_ADD", "tin=2")),
+    ("ffn_up_text", "nt", 9216, 3072, 768, "bias_gelu", ("ctas=2", "epi=F_GELU")),
+    ("qkv_text", "nt", 9216, 2304, 768, "bias", ("ctas=2", "epi=F_PLAIN")),
+    ("ffn_down_dgrad_text", "nn", 9216, 3072, 768, "dgelu", ("ctas=2", "epi=F_DGELU", "tin=1")),
+    ("ffn_up_dgrad_text", "nn", 9216, 768, 3072, "add", ("ctas=2", "epi=F_ADD", "tin=2")),
+    ("out_image", "nt", 4736, 1024, 1024, "bias_drop_add", ("ctas=2", "epi=F_ADD")),
+    ("ffn_up_conn", "nt", 2304, 3072, 768, "bias_gelu", ("ctas=2", "epi=F_GELU")),
+    ("ffn_down_conn", "nt", 2304, 768, 3072, "bias_drop_add", ("epi=F_ADD",)),
+    ("out_conn_image", "nt", 2368, 1024, 1024, "bias_drop_add", ("epi=F_ADD",)),
+    ("dgrad_conn", "nn", 2304, 3072, 768, "dgelu", ("ctas=2", "epi=F_DGELU")),
+    ("vocab", "nt", 4608, 21128, 768, "bias", ("ctas=2", "epi=F_PLAIN")),
+    ("vocab_dgrad", "nn", 4608, 768, 21128, "plain", ("ctas=2", "epi=F_PLAIN")),
+]
+
+
+@pytest.mark.parametrize("name,layout,M,N,K,kind,variant", BENCH_EPILOGUES, ids=[c[0] for c in BENCH_EPILOGUES])
+def test_gemm_bench_shapes_fused_epilogues(ops, ref, name, layout, M, N, K, kind, variant):
+    s = 1.0 / math.sqrt(K)
+    a = rnd(M, K)
+    b = rnd(N, K, seed=1, scale=s) if layout == "nt" else rnd(K, N, seed=1, scale=s)
+    r = rng_state()
+    kw = {}
+    if kind.startswith("bias"):
+        kw["bias"] = rnd(N, seed=2)
+    if kind == "bias_drop_add":
+        kw.update(drop=(0.1, 23), rng=r, addend=rnd(M, N, seed=3))
+    if kind == "add":
+        kw.update(addend=rnd(M, N, seed=3))
+    if kind == "dgelu":
+        kw.update(act=2, aux_in=rnd(M, N, seed=4, scale=1.5))
+    aux_g = aux_r = None
+    if kind == "bias_gelu":
+        aux_g = torch.zeros(M, N, dtype=BF, device=DEV)
+        aux_r = torch.zeros(M, N, dtype=F32, device=DEV)
+    got = ops.gemm(a, b, layout, act=1, aux_out=aux_g, **kw) if kind == "bias_gelu" else ops.gemm(a, b, layout, **kw)
+    v = ops.gemm_last_variant()
+    print("%s %s %dx%dx%d: %s" % (name, layout, M, N, K, v))
+    for sub in variant:
+        assert sub in v, (name, v, sub)
+    want = (ref.gemm(a, b, layout, act=1, aux_out=aux_r, out_dtype=F32, **kw) if kind == "bias_gelu"
+            else ref.gemm(a, b, layout, out_dtype=F32, **kw))
+    close_bf16(got, want, name, atol=4e-3)
+    if aux_g is not None:
+        close_bf16(aux_g, aux_r, name + " aux_out", atol=4e-3)
+    # (with dropout the comparison above also pins the keep mask: a flipped element of |value| ~ 1 is far outside
+    # the tolerance; the mask alone is checked bit for bit in test_gemm_dropout_mask_bit_exact)
+
+
+BENCH_WGRADS = [("wffn2_text", 768, 3072, 9216), ("wffn1_text", 3072, 768, 9216), ("wqkv_text", 2304, 768, 9216),
+                ("wout_text", 768, 768, 9216), ("w_image", 1024, 1024, 4736), ("w_conn", 1024, 1024, 2368),
+                ("wffn1_conn", 3072, 768, 2304), ("w_small_conn", 768, 768, 2304), ("w_vocab", 21128, 768, 4608)]
+
+
+@pytest.mark.parametrize("name,M,N,K", BENCH_WGRADS, ids=[c[0] for c in BENCH_WGRADS])
+def test_gemm_bench_shapes_weight_gradients(ops, ref, name, M, N, K):
+    """tn, fp32 reduce-add onto a non-zero gradient (TMA bulk reduce, split-K where the rule picks it)."""
+    a, b = rnd(K, M, scale=0.05), rnd(K, N, seed=1, scale=0.05)
+    base = rnd(M, N, seed=2, dtype=F32)
+    got, want = base.clone(), base.clone()
+    ops.gemm(a, b, "tn", out=got, accumulate=True)
+    v = ops.gemm_last_variant()
+    print("%s tn %dx%dx%d: %s" % (name, M, N, K, v))
+    assert "acc=1" in v and "tma_out=1" in v
+    ref.gemm(a, b, "tn", out=want, accumulate=True)
+    close(got, want, 2e-4, 2e-4 * math.sqrt(K) * 0.05 * 0.05 * 8, name)
+
+
 def test_gemm_strided_views(ops, ref):
     # operands / outputs that are column slices of wider buffers (qkv, logits[:, :V])
     M, K, N = 192, 256, 200
@@ -270,6 +344,27 @@ def test_attn_bwd(ops, ref, B, H, Lq, Lk, d, drop):
     close_bf16(dkv_g, dkv_r, "dkv", atol=4e-3 * float(dkv_r.abs().max()), ulps=3)
 
 
+def test_attn_key_mask_with_trailing_padding(ops, ref):
+    """Image self-attention / co-attention over padded regions (num_boxes < max_region_len): the key mask has
+    trailing zeros for Lk = 37; masked keys get ~0 probability (the reference adds -10000, `:2580`, `:449`)."""
+    B, H, Lq, Lk, d = 16, 8, 36, 37, 128
+    qbuf = rnd(B * Lq, 3 * H * d)
+    kvbuf = rnd(B * Lk, 3 * H * d, seed=1)
+    nbox = torch.randint(18, 37, (B,), generator=torch.Generator().manual_seed(9))
+    mask = torch.cat([torch.ones(B, 1, dtype=torch.long), (torch.arange(36)[None, :] < nbox[:, None]).long()], 1).to(DEV)
+    madd = ops.mask_additive(mask)
+    assert torch.equal(madd, ref.mask_additive(mask))
+    ctx, lse = ops.attn_fwd(qbuf, 0, kvbuf, H * d, 2 * H * d, madd, B, H, Lq, Lk, d)
+    ctxr, lser = ref.attn_fwd(qbuf, 0, kvbuf, H * d, 2 * H * d, madd, B, H, Lq, Lk, d)
+    close(lse[0], lser, 1e-5, 1e-4, "lse")
+    close_bf16(ctx, ctxr, "ctx", atol=8e-3)
+    # changing the VALUES of masked keys must not change the output beyond exp(-10000) = 0
+    kv2 = kvbuf.clone().reshape(B, Lk, -1)
+    kv2[~mask.bool()] = 7.0
+    ctx2, _ = ops.attn_fwd(qbuf, 0, kv2.reshape(B * Lk, -1), H * d, 2 * H * d, madd, B, H, Lq, Lk, d)
+    assert torch.equal(ctx, ctx2)
+
+
 # ---- embeddings ------------------------------------------------------------------------------------
 def test_embed_fwd_bwd_bit_exact_gather(ops, ref):
     V, L, H, B = 21128, 36, 768, 16
@@ -308,6 +403,34 @@ def test_loc_embed(ops, ref):
         res.append((dw, db))
     close(res[0][0], res[1][0], 1e-4, 1e-3, "loc dw")
     close(res[0][1], res[1][1], 1e-4, 1e-3, "loc db")
+
+
+def test_soft_fusion_gate_kernels(ops, ref):
+    """if_pre_sampling = 2 (`vilbert_k3m.py:2300-2329`): gated = cat * alpha and its backward."""
+    M, H = 333, 768
+    cat = ops.relu_cat3(rnd(M, H), rnd(M, H, seed=1), rnd(M, H, seed=2))
+    alpha = torch.sigmoid(rnd(M, 3 * H, seed=3).float()).to(BF)
+    assert torch.equal(ops.gate_mul(cat, alpha), ref.gate_mul(cat, alpha).to(BF))
+    dg = rnd(M, 3 * H, seed=4)
+    (dc, dsc), (dcr, dscr) = ops.gate_bwd(dg, cat, alpha), ref.gate_bwd(dg, cat, alpha)
+    close_bf16(dc, dcr.float(), "dcat", ulps=1.01)
+    close_bf16(dsc, dscr.float(), "dscore", ulps=1.01)
+
+
+def test_struct_fallback_rows(ops, ref):
+    """Leading items without a PV pair (`:2452-2456`): t[row] = c_init[item]; backward moves the row's gradient."""
+    P, B, H = 9, 4, 768
+    t, c = rnd(P, H, dtype=F32), rnd(B, H, seed=1, dtype=F32)
+    fb = torch.tensor([[2, 1], [-1, -1]], dtype=torch.int32, device=DEV)
+    t1, t2 = t.clone(), t.clone()
+    ops.struct_fallback_fwd(t1, c, fb)
+    ref.struct_fallback_fwd(t2, c, fb)
+    assert torch.equal(t1, t2) and torch.equal(t1[2], c[1]) and torch.equal(t1[3], t[3])
+    dt1, dc1 = rnd(P, H, seed=2, dtype=F32), rnd(B, H, seed=3, dtype=F32)
+    dt2, dc2 = dt1.clone(), dc1.clone()
+    ops.struct_fallback_bwd(dt1, dc1, fb)
+    ref.struct_fallback_bwd(dt2, dc2, fb)
+    assert torch.equal(dt1, dt2) and torch.equal(dc1, dc2) and float(dt1[2].abs().max()) == 0.0
 
 
 # ---- fusion (hard Gumbel pick) ----------------------------------------------------------------------
