@@ -197,7 +197,7 @@ def run_reference_arm(args):
 
 
 # ---- GPU arm ------------------------------------------------------------------------------------------
-HBM_KERNELS = ("k3m_ln_fwd", "k3m_ln_bwd", "k3m_colsum", "k3m_xent_fwd_bwd", "k3m_kl_fwd_bwd", "k3m_adamw",
+HBM_KERNELS = ("k3m_ln_fwd", "k3m_ln_bwd", "k3m_colsum", "k3m_xent_fwd_bwd", "k3m_kl_fwd_bwd", "k3m_adamw", "k3m_adamw_bg",
                "k3m_embed_fwd", "k3m_embed_bwd", "k3m_relu_cat3", "k3m_fuse_select_fwd", "k3m_fuse_select_bwd",
                "k3m_relu_bwd_split3", "k3m_axpy", "k3m_cast")
 
@@ -402,6 +402,13 @@ def run_gpu_arm(args):
         finish()
         return 0
     peaks = load_peaks()
+    if args.no_breakdown or os.environ.get("K3M_BENCH_SKIP"):
+        print(json.dumps({"metric": W["metric"], "value": B * world / (ms_dev * 1e-3), "unit": W["unit"], "n_gpus": world,
+                          "ms_per_step": ms_dev, "e2e_ms_per_step": ms_e2e, "skip": os.environ.get("K3M_BENCH_SKIP", ""),
+                          "launches_per_step": step.launches_per_step, "note": "timing only (no kernel breakdown)",
+                          "comm": comm}))
+        finish()
+        return 0
     kb, gemm_serial_ms, hbm = kernel_breakdown(step, host[0])
     for h in hbm:
         h["frac_of_hbm_peak"] = round(h["gbs"] / peaks["hbm_gbs"], 3) if h["gbs"] else None
@@ -471,6 +478,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="k3m_b200", choices=["k3m_b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-breakdown", action="store_true", help="timing only: skip the per-kernel breakdown / roofline replays")
     ap.add_argument("--workload", default="base", choices=sorted(WORKLOADS),
                     help="base = BASELINE configs[1]/[2] (the headline); long = configs[3]; align = configs[4]")
     args = ap.parse_args()

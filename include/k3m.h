@@ -54,6 +54,19 @@ int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int layout, in
                   const void* addend, int ld_add, int addend_f32, const void* rng,
                   unsigned int drop_site, float drop_p, void* stream);
 
+/* Grouped form: n (1..8) independent problems of ONE layout in one persistent launch — the tile scheduler
+ * walks the concatenated tile list (longest-k problems first), so the small M ~ 2304 problems of the three
+ * connection layers of a stage (vilbert_k3m.py:1030-1111, called at :1686-1750 once per pass), a text and an
+ * image layer, or a stage's weight gradients fill whole waves of CTA pairs together.  Each K3MGemmDesc holds
+ * the arguments of k3m_gemm_bf16 (same meaning, same epilogues).                                         */
+typedef struct K3MGemmDesc {
+  const void* a; int lda; const void* b; int ldb; int layout; int M, N, K;
+  void* out; int ldc; int out_f32; int accumulate; const void* bias; int act;
+  const void* aux_in; int ld_aux_in; void* aux_out; int ld_aux_out;
+  const void* addend; int ld_add; int addend_f32; const void* rng; unsigned int drop_site; float drop_p;
+} K3MGemmDesc;
+int k3m_gemm_grouped_bf16(const K3MGemmDesc* problems, int n, void* stream);
+
 /* Debug aid: a description of the kernel variant the calling thread's last GEMM call dispatched
  * ("bn=256 ctas=2 ew=4 ... epi=F_ADD ...").  Parity tests assert that they ran the benchmark's variant. */
 const char* k3m_gemm_last_variant(void);
@@ -66,6 +79,18 @@ int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, const float* me
                void* dx, void* dxm, float* dgamma, float* dbeta, float* dbias, int M, int H,
                const void* rng, unsigned int site_out, float p_out, unsigned int site_in, float p_in,
                void* stream);
+/* Grouped forms: n (1..8) independent LayerNorms in one launch (the six streams of a connection stage, a text and
+ * an image layer); hidden sizes may differ.  Same arithmetic as k3m_ln_fwd / k3m_ln_bwd per problem.          */
+typedef struct K3MLnFwdDesc {
+  const void *x, *gamma, *beta; void* y; float *mean, *rstd; int M, H;
+  const void* rng; unsigned int site; float drop_p;
+} K3MLnFwdDesc;
+typedef struct K3MLnBwdDesc {
+  const void *dy, *x, *gamma; const float *mean, *rstd; void *dx, *dxm; float *dgamma, *dbeta, *dbias; int M, H;
+  const void* rng; unsigned int site_out; float p_out; unsigned int site_in; float p_in;
+} K3MLnBwdDesc;
+int k3m_ln_fwd_grouped(const K3MLnFwdDesc* problems, int n, float eps, void* stream);
+int k3m_ln_bwd_grouped(const K3MLnBwdDesc* problems, int n, void* stream);
 int k3m_colsum(const void* x, int ld, int x_f32, float* out, int M, int N, void* stream);
 int k3m_cast(const void* x, int x_f32, void* y, int y_f32, long long n, void* stream);
 int k3m_lincomb3(const void* a, int lda, const void* b, int ldb, const void* c, int ldc, float wa,
@@ -167,6 +192,10 @@ int k3m_dropout(const void* x, int ldx, int x_f32, void* y, int ldy, int y_f32, 
 /* torch.optim.AdamW step (pretrain.py:919-924) over a flat range; hyper = device fp32[8]
  * {lr, beta1, beta2, eps, weight_decay, step, grad_scale, -}.                                     */
 int k3m_adamw(float* p32, float* g32, float* m, float* v, void* p16, const float* hyper, long long n,
+              int zero_grad, void* stream);
+/* The same update sized to co-reside with a running GEMM (two 128-thread, <= 32-register CTAs per SM, no shared
+ * memory): used for the gradient buckets that become final while backward is still running.               */
+int k3m_adamw_bg(float* p32, float* g32, float* m, float* v, void* p16, const float* hyper, long long n,
               int zero_grad, void* stream);
 
 /* ---- batch preprocessing on the GPU: BertPreprocessBatch + the loader's prepend ----------

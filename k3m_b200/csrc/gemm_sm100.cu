@@ -53,6 +53,25 @@ struct GemmParams {
   int tin;     // epilogue operand that ARRIVES through TMA into the staging buffer: 0 none, 1 aux_in, 2 addend
 };
 
+// One problem of a (possibly grouped) launch, in kernel-parameter space: its five tensor maps, its epilogue
+// description and where its tiles start in the launch's concatenated tile list.
+struct ProblemArgs {
+  CUtensorMap map_a, map_b, map_c, map_aux, map_in;
+  GemmParams p;
+  int tile_begin;
+  int total_kb;
+};
+// MAXP = 1: the single-problem entry point (every index is a compile-time 0).  MAXP = 8: k3m_gemm_grouped_bf16 —
+// several independent problems of one layout (the three connection layers of a stage, a text and an image layer,
+// a stage's weight gradients) share ONE persistent launch: the tile scheduler walks the concatenated tile list,
+// so small problems fill whole waves together instead of each leaving SMs idle behind its own launch latency.
+template <int MAXP>
+struct GroupArgs {
+  int n;
+  int total_tiles;
+  ProblemArgs prob[MAXP];
+};
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -419,17 +438,16 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
 }
 
 // Persistent, warp-specialised: every CTA walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...
-// (tile = (split, m, n), n fastest so neighbouring CTAs share the A panel in L2).  The smem ring
-// (TMA -> MMA) runs across tile boundaries and the accumulator is double-buffered in TMEM, so the
-// epilogue of tile i overlaps the main loop of tile i + 1.
+// of the launch's tile list (problem after problem; inside a problem tile = (split, m, n), n fastest so
+// neighbouring CTAs share the A panel in L2).  The smem ring (TMA -> MMA) runs across tile boundaries and the
+// accumulator is double-buffered in TMEM, so the epilogue of tile i overlaps the main loop of tile i + 1 —
+// also when the two tiles belong to different problems of a grouped launch.
 // STAGES == 2 marks the "dual" variant: a 2-stage ring and one staging buffer per epilogue warp keep a CTA
 // under 100 KB of shared memory and 256 TMEM columns, so TWO of them (of the same or of different launches)
 // share an SM — for the single-wave M = 2304 GEMMs that run concurrently on several streams.
-template <int BN, int STAGES, int EW, bool A_MN, bool B_MN, int CTAS>
+template <int BN, int STAGES, int EW, bool A_MN, bool B_MN, int CTAS, int MAXP>
 __global__ void __launch_bounds__(64 + 128 * EW, STAGES <= 2 ? 2 : 1)
-gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-            const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_aux,
-            const __grid_constant__ CUtensorMap map_in, GemmParams p) {
+gemm_kernel(const __grid_constant__ GroupArgs<MAXP> g) {
   // warps: 0 = TMA producer, 1 = MMA issuer, 2 .. 2+4*EW-1 = epilogue.  Epilogue warp e handles the
   // TMEM lane quarter (warp % 4) and the column group e / 4 (CW = BN / EW columns) of every tile.
   // CTAS == 2: CTA pair, 256 x BN tile per pair, this CTA holds rows rank*128.. of A / D and columns
@@ -456,12 +474,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
   // the broadcast tells the compiler that `warp` is warp-uniform: the role branches below are then uniform control
   // flow and the MMA warp's addresses / descriptors live in uniform registers (see the MMA branch)
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
-  const int total_kb = (p.K + BK - 1) / BK;
-  const int tiles_mn = p.tiles_m * p.tiles_n;
-  const int total_tiles = tiles_mn * p.splits;
+  const int total_tiles = g.total_tiles;
   const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;
   const bool leader = rank == 0;
   const int tile0 = blockIdx.x / CTAS, tstride = gridDim.x / CTAS;     // tiles are walked per CTA pair
+  // problem of a tile of the launch's list: tiles only grow along a CTA's walk, so `pi` only moves forward
+  auto locate = [&](int tile, int& pi) {
+    if (MAXP > 1) {
+      while (pi + 1 < g.n && tile >= g.prob[pi + 1].tile_begin) ++pi;
+    }
+  };
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -499,15 +521,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
 
   if (warp == 0) {
     if (lane == 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+      for (int i = 0; i < (MAXP > 1 ? g.n : 1); ++i) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&g.prob[i].map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&g.prob[i].map_b) : "memory");
+      }
       uint32_t it = 0;
+      int pi = 0;
       const uint32_t full0 = CTAS == 2 ? mapa_u32(smem_u32(&full[0]), 0) : 0u;   // the leader's full barriers
       for (int tile = tile0; tile < total_tiles; tile += tstride) {
-        const int split = tile / tiles_mn, mn = tile % tiles_mn;
+        locate(tile, pi);
+        const ProblemArgs& pr = g.prob[MAXP > 1 ? pi : 0];
+        const GemmParams& p = pr.p;
+        const CUtensorMap* map_a = &pr.map_a;
+        const CUtensorMap* map_b = &pr.map_b;
+        const int lt_ = tile - pr.tile_begin;
+        const int tiles_mn = p.tiles_m * p.tiles_n;
+        const int split = lt_ / tiles_mn, mn = lt_ % tiles_mn;
         const int m0 = (mn / p.tiles_n) * (BM * CTAS) + (int)rank * BM, n0 = (mn % p.tiles_n) * BN + (int)rank * BNL;
         const int kb0 = split * p.kb_per_split;
-        int nkb = total_kb - kb0;
+        int nkb = pr.total_kb - kb0;
         if (nkb > p.kb_per_split) nkb = p.kb_per_split;
         for (int i = 0; i < nkb; ++i, ++it) {
           const int s = it % STAGES;
@@ -527,28 +559,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
             const uint32_t bar = full0 + (uint32_t)s * 8u;
             if (A_MN) {
 #pragma unroll
-              for (int c = 0; c < BM / 64; ++c) tma_load_2d_pair(a + c * 8192, &map_a, bar, m0 + c * 64, k0);
+              for (int c = 0; c < BM / 64; ++c) tma_load_2d_pair(a + c * 8192, map_a, bar, m0 + c * 64, k0);
             } else {
-              tma_load_2d_pair(a, &map_a, bar, k0, m0);
+              tma_load_2d_pair(a, map_a, bar, k0, m0);
             }
             if (B_MN) {
 #pragma unroll
-              for (int c = 0; c < BNL / 64; ++c) tma_load_2d_pair(b + c * 8192, &map_b, bar, n0 + c * 64, k0);
+              for (int c = 0; c < BNL / 64; ++c) tma_load_2d_pair(b + c * 8192, map_b, bar, n0 + c * 64, k0);
             } else {
-              tma_load_2d_pair(b, &map_b, bar, k0, n0);
+              tma_load_2d_pair(b, map_b, bar, k0, n0);
             }
           } else {
             if (A_MN) {
 #pragma unroll
-              for (int c = 0; c < BM / 64; ++c) tma_load_2d(a + c * 8192, &map_a, &full[s], m0 + c * 64, k0);
+              for (int c = 0; c < BM / 64; ++c) tma_load_2d(a + c * 8192, map_a, &full[s], m0 + c * 64, k0);
             } else {
-              tma_load_2d(a, &map_a, &full[s], k0, m0);
+              tma_load_2d(a, map_a, &full[s], k0, m0);
             }
             if (B_MN) {
 #pragma unroll
-              for (int c = 0; c < BN / 64; ++c) tma_load_2d(b + c * 8192, &map_b, &full[s], n0 + c * 64, k0);
+              for (int c = 0; c < BN / 64; ++c) tma_load_2d(b + c * 8192, map_b, &full[s], n0 + c * 64, k0);
             } else {
-              tma_load_2d(b, &map_b, &full[s], k0, n0);
+              tma_load_2d(b, map_b, &full[s], k0, n0);
             }
           }
         }
@@ -565,11 +597,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
                                  ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) |
                                  ((uint32_t)((BM * CTAS) >> 4) << 24);
       uint32_t it = 0, lt = 0;
+      int pi = 0;
       for (int tile = tile0; tile < total_tiles; tile += tstride, ++lt) {
-        const int split = tile / tiles_mn;
-        const int kb0 = split * p.kb_per_split;
-        int nkb = total_kb - kb0;
-        if (nkb > p.kb_per_split) nkb = p.kb_per_split;
+        locate(tile, pi);
+        const ProblemArgs& pr = g.prob[MAXP > 1 ? pi : 0];
+        const int tiles_mn = pr.p.tiles_m * pr.p.tiles_n;
+        const int split = (tile - pr.tile_begin) / tiles_mn;
+        const int kb0 = split * pr.p.kb_per_split;
+        int nkb = pr.total_kb - kb0;
+        if (nkb > pr.p.kb_per_split) nkb = pr.p.kb_per_split;
         const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
         mbar_wait(&tmem_empty[as], aph ^ 1);          // epilogue (of both CTAs) has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -585,7 +621,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
             const uint64_t da = A_MN ? make_desc(a + k * 2048, 8192, 1024) : make_desc(a + k * 32, 0, 1024);
             const uint64_t db = B_MN ? make_desc(b + k * 2048, 8192, 1024) : make_desc(b + k * 32, 0, 1024);
 #ifdef K3M_GEMM_PROBE_BUILD
-            if (p.probe == 2) continue;          // bottleneck bisect: the ring drains at the pace of the loads alone
+            if (pr.p.probe == 2) continue;       // bottleneck bisect: the ring drains at the pace of the loads alone
 #endif
             if (issuer) {
               if (CTAS == 2) umma_bf16_pair(tacc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
@@ -615,40 +651,57 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
     // (row-per-thread global loads cost 32 L1 wavefronts per instruction and made these epilogues
     // longer than the K = 768 main loop).
     const int e = warp - 2, q = warp & 3, cg = e >> 2;
-    const bool has_drop = p.drop.thresh != 0;
-    const bool want_aux = p.act == ACT_GELU && p.aux_out != nullptr;
     uint8_t* my_stage = sStage + e * NBUF * 4096;
-    const int esz = p.out_f32 ? 4 : 2;
-    const int chunk_cols = (CW * esz > 128) ? 128 / esz : CW;      // columns per staged box (<= 128 B per row)
-    const uint32_t row_bytes = (uint32_t)(chunk_cols * esz);
-    const uint32_t smask = row_bytes == 64 ? 3u : 7u, amask = CW * 2 == 64 ? 3u : 7u;   // 64 B rows use SWIZZLE_64B
-    const int tin = p.tin;                                          // host: only with tma_out, bf16 out, !want_aux
     uint64_t* in_bar = in_bars + e;
     uint32_t in_phase = 0;
     uint32_t nstore = 0;
-    if (lane == 0 && p.tma_out) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
-      if (want_aux) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_aux) : "memory");
-      if (tin) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_in) : "memory");
+    if (lane == 0) {
+      for (int i = 0; i < (MAXP > 1 ? g.n : 1); ++i) {
+        const ProblemArgs& pr = g.prob[i];
+        if (!pr.p.tma_out) continue;
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&pr.map_c) : "memory");
+        if (pr.p.act == ACT_GELU && pr.p.aux_out != nullptr) asm volatile("prefetch.tensormap [%0];" ::"l"(&pr.map_aux) : "memory");
+        if (pr.p.tin) asm volatile("prefetch.tensormap [%0];" ::"l"(&pr.map_in) : "memory");
+      }
     }
-    // bulk-load the operand box of `tile` into the buffer its result will be staged in
-    auto prefetch_in = [&](int tile) {
-      const int mn = tile % tiles_mn;
-      const int m0 = (mn / p.tiles_n) * (BM * CTAS) + (int)rank * BM, n0 = (mn % p.tiles_n) * BN + cg * CW;
-      if (n0 >= p.N) return;
+    // bulk-load the epilogue operand box of `tile` (of problem `pj`) into the buffer its result will be staged in
+    auto prefetch_in = [&](int tile, int pj) {
+      const ProblemArgs& pr = g.prob[MAXP > 1 ? pj : 0];
+      if (!pr.p.tin) return;
+      const int tiles_mn = pr.p.tiles_m * pr.p.tiles_n;
+      const int mn = (tile - pr.tile_begin) % tiles_mn;
+      const int m0 = (mn / pr.p.tiles_n) * (BM * CTAS) + (int)rank * BM, n0 = (mn % pr.p.tiles_n) * BN + cg * CW;
+      if (n0 >= pr.p.N) return;
       if (lane == 0) {
         // the bulk store that last read this buffer must have finished reading it
         if (NBUF == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         else asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
         mbar_expect_tx(in_bar, 32 * CW * 2);
-        tma_load_2d(my_stage + (nstore % NBUF) * 4096, &map_in, in_bar, n0, m0 + q * 32);
+        tma_load_2d(my_stage + (nstore % NBUF) * 4096, &pr.map_in, in_bar, n0, m0 + q * 32);
       }
     };
-    if (tin && tile0 < total_tiles) prefetch_in(tile0);
+    int pi = 0, pnext = 0;
+    if (tile0 < total_tiles) {
+      locate(tile0, pnext);
+      prefetch_in(tile0, pnext);
+    }
     const uint32_t tmem_empty0 = CTAS == 2 ? mapa_u32(smem_u32(&tmem_empty[0]), 0) : 0u;   // the leader's
     uint32_t lt = 0;
     for (int tile = tile0; tile < total_tiles; tile += tstride, ++lt) {
-      const int mn = tile % tiles_mn;
+      locate(tile, pi);
+      const ProblemArgs& pr = g.prob[MAXP > 1 ? pi : 0];
+      const GemmParams& p = pr.p;
+      const CUtensorMap* map_c = &pr.map_c;
+      const CUtensorMap* map_aux = &pr.map_aux;
+      const bool has_drop = p.drop.thresh != 0;
+      const bool want_aux = p.act == ACT_GELU && p.aux_out != nullptr;
+      const int esz = p.out_f32 ? 4 : 2;
+      const int chunk_cols = (CW * esz > 128) ? 128 / esz : CW;      // columns per staged box (<= 128 B per row)
+      const uint32_t row_bytes = (uint32_t)(chunk_cols * esz);
+      const uint32_t smask = row_bytes == 64 ? 3u : 7u, amask = CW * 2 == 64 ? 3u : 7u;   // 64 B rows use SWIZZLE_64B
+      const int tin = p.tin;                                          // host: only with tma_out, bf16 out, !want_aux
+      const int tiles_mn = p.tiles_m * p.tiles_n;
+      const int mn = (tile - pr.tile_begin) % tiles_mn;
       const int m0 = (mn / p.tiles_n) * (BM * CTAS) + (int)rank * BM, n0 = (mn % p.tiles_n) * BN + cg * CW;
       const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
       const int row = m0 + q * 32 + lane;
@@ -666,10 +719,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         if (p.fast) {
           const int row0 = m0 + q * 32;
           switch (p.fast) {
-            case F_PLAIN: fast_tile<CW, NBUF, F_PLAIN>(p, &map_c, &map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
-            case F_ADD: fast_tile<CW, NBUF, F_ADD>(p, &map_c, &map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
-            case F_GELU: fast_tile<CW, NBUF, F_GELU>(p, &map_c, &map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
-            default: fast_tile<CW, NBUF, F_DGELU>(p, &map_c, &map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
+            case F_PLAIN: fast_tile<CW, NBUF, F_PLAIN>(p, map_c, map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
+            case F_ADD: fast_tile<CW, NBUF, F_ADD>(p, map_c, map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
+            case F_GELU: fast_tile<CW, NBUF, F_GELU>(p, map_c, map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
+            default: fast_tile<CW, NBUF, F_DGELU>(p, map_c, map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
           }
         } else {
 #pragma unroll 1
@@ -690,12 +743,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
             uint32_t r[32];
             tmem_ld32(tbase + (uint32_t)cc, r);
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              const int col = n0 + cc + g * 8;
+            for (int gq = 0; gq < 4; ++gq) {
+              const int col = n0 + cc + gq * 8;
               const int nv = (p.N - col) < 8 ? (p.N - col) : 8;
               const bool ok = row_ok && nv > 0;
               const bool vec = p.vec_ok && nv == 8;
-              const uint32_t off = (uint32_t)lane * row_bytes + (uint32_t)((lc + g * 8) * esz);
+              const uint32_t off = (uint32_t)lane * row_bytes + (uint32_t)((lc + gq * 8) * esz);
               float v[8], pre[8], staged[8];
               if (tin) {
                 const uint4 u = *reinterpret_cast<const uint4*>(buf + swz(off, smask));
@@ -707,7 +760,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
                 }
               }
               if (ok) {
-                compute_group(p, r + g * 8, row, col, nv, vec, has_drop, v, pre, staged, tin);
+                compute_group(p, r + gq * 8, row, col, nv, vec, has_drop, v, pre, staged, tin);
               } else {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) v[j] = pre[j] = 0.f;
@@ -718,7 +771,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
                   else stage_bf16(buf, off, smask, v);
                   if (want_aux) {
                     if (NBUF > 1) {
-                      stage_bf16(abuf, (uint32_t)lane * (uint32_t)(CW * 2) + (uint32_t)((cc + g * 8) * 2), amask, pre);
+                      stage_bf16(abuf, (uint32_t)lane * (uint32_t)(CW * 2) + (uint32_t)((cc + gq * 8) * 2), amask, pre);
                     } else if (ok) {   // fp32 out + pre-activation with one buffer: row-per-thread store
                       bf16* ao = p.aux_out + (size_t)row * p.ld_aux_out + col;
                       if (vec) st8(ao, pre);
@@ -735,9 +788,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
               __syncwarp();
               if (lane == 0) {
                 const int c0 = n0 + cc + 32 - chunk_cols;
-                if (p.accumulate) tma_reduce_add_2d(&map_c, buf, c0, m0 + q * 32);
-                else tma_store_2d(&map_c, buf, c0, m0 + q * 32);
-                if (want_aux && NBUF > 1) tma_store_2d(&map_aux, abuf, n0, m0 + q * 32);
+                if (p.accumulate) tma_reduce_add_2d(map_c, buf, c0, m0 + q * 32);
+                else tma_store_2d(map_c, buf, c0, m0 + q * 32);
+                if (want_aux && NBUF > 1) tma_store_2d(map_aux, abuf, n0, m0 + q * 32);
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
               }
               nstore += (want_aux && NBUF > 1) ? 2 : 1;
@@ -751,7 +804,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ C
         if (CTAS == 2) mbar_arrive_cluster(tmem_empty0 + as * 8u);
         else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[as])) : "memory");
       }
-      if (tin && tile + tstride < total_tiles) prefetch_in(tile + tstride);
+      if (tile + tstride < total_tiles) {
+        locate(tile + tstride, pnext);
+        prefetch_in(tile + tstride, pnext);
+      }
     }
     // the staging buffers must outlive the bulk stores' READS only; global visibility of the writes is
     // given by grid completion
@@ -838,16 +894,15 @@ int num_sms() {
   return n;
 }
 
-template <int BN, int STAGES, int EW, bool A_MN, bool B_MN, int CTAS>
-int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx,
-           const CUtensorMap& mi, GemmParams p, cudaStream_t st) {
+template <int BN, int STAGES, int EW, bool A_MN, bool B_MN, int CTAS, int MAXP>
+int launch(GroupArgs<MAXP>& g, cudaStream_t st) {
   // operand ring + epilogue staging (4*EW warps x NBUF x 4 KB) + barriers + 1 KB alignment slack
   constexpr int NBUF = (EW <= 2 && STAGES > 2) ? 2 : 1;
   constexpr int SMEM = STAGES * (BM * BK * 2 + (BN / CTAS) * BK * 2) + 4 * EW * NBUF * 4096 +
                        (2 * STAGES + 4 + 4 * EW) * 8 + 16 + 1024;
   static_assert(SMEM <= 227 * 1024, "shared memory budget");
   static bool configured = false;
-  auto kern = gemm_kernel<BN, STAGES, EW, A_MN, B_MN, CTAS>;
+  auto kern = gemm_kernel<BN, STAGES, EW, A_MN, B_MN, CTAS, MAXP>;
   if (!configured) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess) {
       k3m_set_error("gemm: cannot set dynamic shared memory to %d", SMEM);
@@ -855,40 +910,42 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
     }
     configured = true;
   }
-  p.tiles_m = (p.M + BM * CTAS - 1) / (BM * CTAS);
-  p.tiles_n = (p.N + BN - 1) / BN;
-  const int total = p.tiles_m * p.tiles_n * p.splits;
+  int total = 0;
+  for (int i = 0; i < g.n; ++i) {
+    GemmParams& p = g.prob[i].p;
+    p.tiles_m = (p.M + BM * CTAS - 1) / (BM * CTAS);
+    p.tiles_n = (p.N + BN - 1) / BN;
+    g.prob[i].tile_begin = total;
+    total += p.tiles_m * p.tiles_n * p.splits;
+  }
+  g.total_tiles = total;
   const int slots = num_sms() * (STAGES <= 2 ? 2 : 1) / CTAS;     // CTAs (or CTA pairs) resident at once
   const int grid = (total < slots ? total : slots) * CTAS;
   static const int pdl = getenv("K3M_GEMM_PDL") ? atoi(getenv("K3M_GEMM_PDL")) : 0;
-  if (CTAS == 1 && !pdl) {
-    kern<<<grid, 64 + 128 * EW, SMEM, st>>>(ma, mb, mc, mx, mi, p);
-  } else {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(64 + 128 * EW);
-    cfg.dynamicSmemBytes = SMEM;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[2];
-    int na = 0;
-    if (CTAS == 2) {
-      attr[na].id = cudaLaunchAttributeClusterDimension;
-      attr[na].val.clusterDim.x = CTAS;
-      attr[na].val.clusterDim.y = 1;
-      attr[na].val.clusterDim.z = 1;
-      ++na;
-    }
-    if (pdl) {
-      attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-      attr[na].val.programmaticStreamSerializationAllowed = 1;
-      ++na;
-    }
-    cfg.attrs = attr;
-    cfg.numAttrs = na;
-    if (cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, mx, mi, p) != cudaSuccess) {
-      k3m_set_error("gemm: launch failed: %s", cudaGetErrorString(cudaGetLastError()));
-      return K3M_ERR_CUDA;
-    }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(64 + 128 * EW);
+  cfg.dynamicSmemBytes = SMEM;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (CTAS == 2) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = CTAS;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  if (cudaLaunchKernelEx(&cfg, kern, g) != cudaSuccess) {
+    k3m_set_error("gemm: launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return K3M_ERR_CUDA;
   }
   return k3m_check_launch("k3m_gemm_bf16");
 }
@@ -896,15 +953,20 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
 // (tile width, epilogue column groups) variants: 256/4 (16 epilogue warps), 128/4, 128/2, 64/1; `ctas` = 2
 // selects the CTA-pair kernel (256 x 256 tile per pair, 5-stage ring of 32 KB stages)
 template <bool A_MN, bool B_MN>
-int dispatch(int bn, int ew, int ctas, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
-             const CUtensorMap& mx, const CUtensorMap& mi, const GemmParams& p, cudaStream_t st) {
-  if (bn == 64) return launch<64, 6, 1, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
-  if (bn == 256 && ctas == 2) return launch<256, 5, 4, A_MN, B_MN, 2>(ma, mb, mc, mx, mi, p, st);
-  if (bn == 128 && ctas == 2) return launch<128, 6, 4, A_MN, B_MN, 2>(ma, mb, mc, mx, mi, p, st);
-  if (bn == 256) return launch<256, 3, 4, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
-  if (ew == 0) return launch<128, 2, 2, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);      // dual: two CTAs per SM
-  if (ew == 4) return launch<128, 5, 4, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
-  return launch<128, 5, 2, A_MN, B_MN, 1>(ma, mb, mc, mx, mi, p, st);
+int dispatch(int bn, int ew, int ctas, GroupArgs<1>& g, cudaStream_t st) {
+  if (bn == 64) return launch<64, 6, 1, A_MN, B_MN, 1, 1>(g, st);
+  if (bn == 256 && ctas == 2) return launch<256, 5, 4, A_MN, B_MN, 2, 1>(g, st);
+  if (bn == 128 && ctas == 2) return launch<128, 6, 4, A_MN, B_MN, 2, 1>(g, st);
+  if (bn == 256) return launch<256, 3, 4, A_MN, B_MN, 1, 1>(g, st);
+  if (ew == 0) return launch<128, 2, 2, A_MN, B_MN, 1, 1>(g, st);      // dual: two CTAs per SM
+  if (ew == 4) return launch<128, 5, 4, A_MN, B_MN, 1, 1>(g, st);
+  return launch<128, 5, 2, A_MN, B_MN, 1, 1>(g, st);
+}
+// grouped launches: the CTA-pair kernel, or 128 x 128 single-CTA tiles for problems too small for it
+template <bool A_MN, bool B_MN>
+int dispatch_group(int ctas, GroupArgs<8>& g, cudaStream_t st) {
+  if (ctas == 2) return launch<256, 5, 4, A_MN, B_MN, 2, 8>(g, st);
+  return launch<128, 5, 4, A_MN, B_MN, 1, 8>(g, st);
 }
 
 // tile width: 128 x 256 (85 flop per operand byte from L2) once it still gives every SM a tile, else
@@ -921,6 +983,102 @@ int pick_bn(int M, int N, int K, int force) {
 // benchmark's kernel variant is the one they exercised)
 thread_local char g_variant[160] = "";
 
+struct Desc {      // == K3MGemmDesc of include/k3m.h
+  const void* a; int lda; const void* b; int ldb; int layout; int M, N, K;
+  void* out; int ldc; int out_f32; int accumulate; const void* bias; int act;
+  const void* aux_in; int ld_aux_in; void* aux_out; int ld_aux_out;
+  const void* addend; int ld_add; int addend_f32; const void* rng; unsigned int drop_site; float drop_p;
+};
+
+int check_desc(const Desc& d) {
+  K3M_REQUIRE(d.M > 0 && d.N > 0 && d.K > 0, "gemm: empty problem M=%d N=%d K=%d", d.M, d.N, d.K);
+  K3M_REQUIRE(d.layout >= 0 && d.layout <= 2, "gemm: layout must be 0 (nt), 1 (nn) or 2 (tn)");
+  K3M_REQUIRE(d.lda % 8 == 0 && d.ldb % 8 == 0, "gemm: operand row strides must be multiples of 8 elements (lda=%d ldb=%d)", d.lda, d.ldb);
+  K3M_REQUIRE(((uintptr_t)d.a & 15) == 0 && ((uintptr_t)d.b & 15) == 0, "gemm: operands must be 16-byte aligned");
+  K3M_REQUIRE(!d.accumulate || d.out_f32, "gemm: accumulate needs an fp32 output");
+  K3M_REQUIRE(!(d.act == ACT_DGELU || d.act == ACT_DTANH) || d.aux_in, "gemm: activation-derivative epilogue needs aux_in");
+  return K3M_OK;
+}
+
+// Fills one problem of a launch for the chosen variant (bn, ctas, ew) and K split: operand / output / epilogue
+// tensor maps, epilogue mode.  `dual`: the 2-stage two-CTAs-per-SM variant (ew = 2 there).
+int setup_problem(const Desc& d, int bn, int ctas, int ew, int splits, ProblemArgs* out) {
+  const bool a_mn = d.layout == 2, b_mn = d.layout != 0;
+  const int M = d.M, N = d.N, K = d.K;
+  const int total_kb = (K + BK - 1) / BK;
+  // A: K-major -> tensor [M, K]; MN-major -> tensor [K, M]
+  if (!(a_mn ? get_map(d.a, M, K, d.lda, 64, 64, &out->map_a) : get_map(d.a, K, M, d.lda, 64, BM, &out->map_a))) return K3M_ERR_CUDA;
+  if (!(b_mn ? get_map(d.b, N, K, d.ldb, 64, 64, &out->map_b) : get_map(d.b, K, N, d.ldb, 64, bn / ctas, &out->map_b))) return K3M_ERR_CUDA;
+  GemmParams& p = out->p;
+  p.M = M; p.N = N; p.K = K;
+  p.kb_per_split = (total_kb + splits - 1) / splits;
+  p.splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.tiles_m = p.tiles_n = 0;
+  out->total_kb = total_kb;
+  out->tile_begin = 0;
+  p.out = d.out; p.ldc = d.ldc; p.out_f32 = d.out_f32; p.accumulate = d.accumulate;
+  p.bias = reinterpret_cast<const bf16*>(d.bias);
+  p.act = d.act;
+  p.aux_in = reinterpret_cast<const bf16*>(d.aux_in); p.ld_aux_in = d.ld_aux_in;
+  p.aux_out = reinterpret_cast<bf16*>(d.aux_out); p.ld_aux_out = d.ld_aux_out;
+  p.addend = d.addend; p.ld_add = d.ld_add; p.addend_f32 = d.addend_f32;
+  p.drop.rng = reinterpret_cast<const unsigned long long*>(d.rng);
+  p.drop.site = d.drop_site;
+  p.drop.thresh = (d.rng && d.drop_p > 0.f) ? (unsigned int)(d.drop_p * 65536.0f + 0.5f) : 0u;
+  p.drop.scale = 1.0f / (1.0f - d.drop_p);
+  p.drop_ld = (N + 7) / 8 * 8;
+  auto al = [](const void* q, int ld, int esz) { return q == nullptr || ((((uintptr_t)q) & 15) == 0 && (ld * esz) % 16 == 0); };
+  p.vec_ok = al(d.out, d.ldc, d.out_f32 ? 4 : 2) && al(d.bias, 8, 2) && al(d.aux_in, d.ld_aux_in, 2) && al(d.aux_out, d.ld_aux_out, 2) &&
+             al(d.addend, d.ld_add, d.addend_f32 ? 4 : 2) && (!d.out_f32 || (d.ldc % 8 == 0 && (((uintptr_t)d.out) & 31) == 0));
+  // TMA-store epilogue when the outputs can be described by tensor maps (16-byte aligned base and row pitch)
+  out->map_c = out->map_a; out->map_aux = out->map_a; out->map_in = out->map_a;
+  const int esz = d.out_f32 ? 4 : 2;
+  auto tma_able = [](const void* q, long pitch_bytes) { return q != nullptr && (((uintptr_t)q) & 15) == 0 && pitch_bytes % 16 == 0; };
+  static const int no_tma_store = getenv("K3M_GEMM_NO_TMA_STORE") ? atoi(getenv("K3M_GEMM_NO_TMA_STORE")) : 0;
+  const bool want_aux = d.act == ACT_GELU && d.aux_out != nullptr;
+  p.tma_out = !no_tma_store && tma_able(d.out, (long)d.ldc * esz) && (!want_aux || (!d.out_f32 && tma_able(d.aux_out, (long)d.ld_aux_out * 2)));
+  const int cw = bn / ew;
+  p.tin = 0;
+  if (p.tma_out) {
+    const int box = (cw * esz > 128) ? 128 / esz : cw;
+    if (!get_map(d.out, N, M, d.ldc, box, 32, &out->map_c, esz)) return K3M_ERR_CUDA;
+    if (want_aux && !get_map(d.aux_out, N, M, d.ld_aux_out, cw, 32, &out->map_aux, 2)) return K3M_ERR_CUDA;
+    // one bf16 epilogue operand can arrive through TMA into the staging buffer (same box as the output)
+    static const int no_tma_in = getenv("K3M_GEMM_NO_TMA_IN") ? atoi(getenv("K3M_GEMM_NO_TMA_IN")) : 0;
+    if (!no_tma_in && !d.out_f32 && !want_aux) {
+      const void* src = nullptr;
+      int ld_src = 0;
+      if ((d.act == ACT_DGELU || d.act == ACT_DTANH) && tma_able(d.aux_in, (long)d.ld_aux_in * 2)) {
+        p.tin = 1; src = d.aux_in; ld_src = d.ld_aux_in;
+      } else if (d.addend != nullptr && !d.addend_f32 && tma_able(d.addend, (long)d.ld_add * 2)) {
+        p.tin = 2; src = d.addend; ld_src = d.ld_add;
+      }
+      if (p.tin && !get_map(src, N, M, ld_src, cw, 32, &out->map_in, 2)) return K3M_ERR_CUDA;
+    }
+  }
+  static const int probe = getenv("K3M_GEMM_PROBE") ? atoi(getenv("K3M_GEMM_PROBE")) : 0;
+  p.probe = probe;
+  p.fast = F_NONE;
+  static const int no_fast = getenv("K3M_GEMM_NO_FAST") ? atoi(getenv("K3M_GEMM_NO_FAST")) : 0;
+  if (!no_fast && p.tma_out && !d.out_f32 && !d.accumulate && p.vec_ok && N % 8 == 0) {
+    const bool has_drop = p.drop.thresh != 0;
+    if (d.act == ACT_NONE && d.aux_out == nullptr) {
+      if (d.addend == nullptr) p.fast = F_PLAIN;
+      else if (p.tin == 2) p.fast = F_ADD;
+    } else if (d.act == ACT_GELU && want_aux && d.addend == nullptr && !has_drop) {
+      p.fast = F_GELU;
+    } else if (d.act == ACT_DGELU && p.tin == 1 && d.addend == nullptr && d.bias == nullptr && !has_drop) {
+      p.fast = F_DGELU;
+    }
+  }
+  return K3M_OK;
+}
+
+const char* fast_name(int f) {
+  static const char* names[] = {"generic", "F_PLAIN", "F_ADD", "F_GELU", "F_DGELU"};
+  return names[f];
+}
+
 }  // namespace
 
 extern "C" const char* k3m_gemm_last_variant(void) { return g_variant; }
@@ -930,13 +1088,9 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
                              const void* aux_in, int ld_aux_in, void* aux_out, int ld_aux_out, const void* addend,
                              int ld_add, int addend_f32, const void* rng, unsigned int drop_site, float drop_p,
                              void* stream) {
-  K3M_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem M=%d N=%d K=%d", M, N, K);
-  K3M_REQUIRE(layout >= 0 && layout <= 2, "gemm: layout must be 0 (nt), 1 (nn) or 2 (tn)");
-  K3M_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm: operand row strides must be multiples of 8 elements (lda=%d ldb=%d)", lda, ldb);
-  K3M_REQUIRE(((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0, "gemm: operands must be 16-byte aligned");
-  K3M_REQUIRE(!accumulate || out_f32, "gemm: accumulate needs an fp32 output");
-  K3M_REQUIRE(!(act == ACT_DGELU || act == ACT_DTANH) || aux_in, "gemm: activation-derivative epilogue needs aux_in");
-  const bool a_mn = layout == 2, b_mn = layout != 0;
+  Desc d = {a, lda, b, ldb, layout, M, N, K, out, ldc, out_f32, accumulate, bias, act, aux_in, ld_aux_in, aux_out,
+            ld_aux_out, addend, ld_add, addend_f32, rng, drop_site, drop_p};
+  if (int rc = check_desc(d)) return rc;
   static const int force_bn = getenv("K3M_GEMM_BN") ? atoi(getenv("K3M_GEMM_BN")) : 0;
   int bn = pick_bn(M, N, K, force_bn);
   const int total_kb = (K + BK - 1) / BK;
@@ -967,46 +1121,16 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
       }
     }
   }
-  CUtensorMap ma, mb;
-  // A: K-major -> tensor [M, K]; MN-major -> tensor [K, M]
-  if (!(a_mn ? get_map(a, M, K, lda, 64, 64, &ma) : get_map(a, K, M, lda, 64, BM, &ma))) return K3M_ERR_CUDA;
-  if (!(b_mn ? get_map(b, N, K, ldb, 64, 64, &mb) : get_map(b, K, N, ldb, 64, bn / ctas, &mb))) return K3M_ERR_CUDA;
-  GemmParams p;
-  p.M = M; p.N = N; p.K = K;
   int splits = 1;
   if (accumulate) {
     const int tiles = ((M + BM * ctas - 1) / (BM * ctas)) * ((N + bn - 1) / bn);
     const int resident = num_sms() / ctas;
     while (tiles * splits * 2 <= resident && total_kb / (splits * 2) >= 4) splits *= 2;
   }
-  p.kb_per_split = (total_kb + splits - 1) / splits;
-  splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
-  p.splits = splits;
-  p.out = out; p.ldc = ldc; p.out_f32 = out_f32; p.accumulate = accumulate;
-  p.bias = reinterpret_cast<const bf16*>(bias);
-  p.act = act;
-  p.aux_in = reinterpret_cast<const bf16*>(aux_in); p.ld_aux_in = ld_aux_in;
-  p.aux_out = reinterpret_cast<bf16*>(aux_out); p.ld_aux_out = ld_aux_out;
-  p.addend = addend; p.ld_add = ld_add; p.addend_f32 = addend_f32;
-  p.drop.rng = reinterpret_cast<const unsigned long long*>(rng);
-  p.drop.site = drop_site;
-  p.drop.thresh = (rng && drop_p > 0.f) ? (unsigned int)(drop_p * 65536.0f + 0.5f) : 0u;
-  p.drop.scale = 1.0f / (1.0f - drop_p);
-  p.drop_ld = (N + 7) / 8 * 8;
-  auto al = [](const void* q, int ld, int esz) { return q == nullptr || ((((uintptr_t)q) & 15) == 0 && (ld * esz) % 16 == 0); };
-  p.vec_ok = al(out, ldc, out_f32 ? 4 : 2) && al(bias, 8, 2) && al(aux_in, ld_aux_in, 2) && al(aux_out, ld_aux_out, 2) &&
-             al(addend, ld_add, addend_f32 ? 4 : 2) && (!out_f32 || (ldc % 8 == 0 && (((uintptr_t)out) & 31) == 0));
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  // TMA-store epilogue when the outputs can be described by tensor maps (16-byte aligned base and row pitch)
-  CUtensorMap mc = ma, mx = ma;
-  const int esz = out_f32 ? 4 : 2;
-  auto tma_able = [](const void* q, long pitch_bytes) { return q != nullptr && (((uintptr_t)q) & 15) == 0 && pitch_bytes % 16 == 0; };
-  static const int no_tma_store = getenv("K3M_GEMM_NO_TMA_STORE") ? atoi(getenv("K3M_GEMM_NO_TMA_STORE")) : 0;
-  const bool want_aux = act == ACT_GELU && aux_out != nullptr;
-  p.tma_out = !no_tma_store && tma_able(out, (long)ldc * esz) && (!want_aux || (!out_f32 && tma_able(aux_out, (long)ld_aux_out * 2)));
   // epilogue warps: 16 (4 column groups) when the epilogue does real work per element, else 8
   static const int force_ew = getenv("K3M_GEMM_EW") ? atoi(getenv("K3M_GEMM_EW")) : 0;
-  const bool heavy = act != ACT_NONE || p.drop.thresh != 0 || addend != nullptr;
+  const bool has_drop = rng && drop_p > 0.f;
+  const bool heavy = act != ACT_NONE || has_drop || addend != nullptr;
   int ew = (bn == 256 || ctas == 2) ? 4 : bn == 64 ? 1 : (force_ew ? force_ew : (heavy ? 4 : 2));
   // dual variant (K3M_GEMM_DUAL=1): single-wave 128-wide problems, where a CTA holds one tile and nothing of
   // its prologue / epilogue overlaps anything unless another CTA shares the SM.  Measured: each launch gets
@@ -1016,51 +1140,80 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   static const int mode_dual = getenv("K3M_GEMM_DUAL") ? atoi(getenv("K3M_GEMM_DUAL")) : 0;
   bool dual = false;
   if (mode_dual && bn == 128 && ctas == 1) {
-    const long tiles = (long)((M + BM - 1) / BM) * ((N + 127) / 128) * p.splits;
+    const int kbps = (total_kb + splits - 1) / splits;
+    const long tiles = (long)((M + BM - 1) / BM) * ((N + 127) / 128) * ((total_kb + kbps - 1) / kbps);
     dual = mode_dual == 2 || tiles <= num_sms();
   }
   if (dual) ew = 2;
-  const int cw = bn / ew;
-  CUtensorMap mi = ma;
-  p.tin = 0;
-  if (p.tma_out) {
-    const int box = (cw * esz > 128) ? 128 / esz : cw;
-    if (!get_map(out, N, M, ldc, box, 32, &mc, esz)) return K3M_ERR_CUDA;
-    if (want_aux && !get_map(aux_out, N, M, ld_aux_out, cw, 32, &mx, 2)) return K3M_ERR_CUDA;
-    // one bf16 epilogue operand can arrive through TMA into the staging buffer (same box as the output)
-    static const int no_tma_in = getenv("K3M_GEMM_NO_TMA_IN") ? atoi(getenv("K3M_GEMM_NO_TMA_IN")) : 0;
-    if (!no_tma_in && !out_f32 && !want_aux) {
-      const void* src = nullptr;
-      int ld_src = 0;
-      if ((act == ACT_DGELU || act == ACT_DTANH) && tma_able(aux_in, (long)ld_aux_in * 2)) {
-        p.tin = 1; src = aux_in; ld_src = ld_aux_in;
-      } else if (addend != nullptr && !addend_f32 && tma_able(addend, (long)ld_add * 2)) {
-        p.tin = 2; src = addend; ld_src = ld_add;
+  GroupArgs<1> g;
+  g.n = 1;
+  if (int rc = setup_problem(d, bn, ctas, ew, splits, &g.prob[0])) return rc;
+  const GemmParams& p = g.prob[0].p;
+  snprintf(g_variant, sizeof(g_variant), "bn=%d ctas=%d ew=%d dual=%d splits=%d epi=%s tin=%d tma_out=%d acc=%d group=1",
+           bn, ctas, ew, dual ? 1 : 0, p.splits, fast_name(p.fast), p.tin, p.tma_out, accumulate);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (layout == 0) return dispatch<false, false>(bn, dual ? 0 : ew, ctas, g, st);
+  if (layout == 1) return dispatch<false, true>(bn, dual ? 0 : ew, ctas, g, st);
+  return dispatch<true, true>(bn, dual ? 0 : ew, ctas, g, st);
+}
+
+// Several independent problems of ONE layout in one persistent launch (see GroupArgs).  Problems are ordered
+// longest-k first in the tile list so that the static round-robin walk ends on the short tiles.
+extern "C" int k3m_gemm_grouped_bf16(const void* descs, int n, void* stream) {
+  const Desc* d = reinterpret_cast<const Desc*>(descs);
+  K3M_REQUIRE(n >= 1 && n <= 8, "gemm_grouped: 1..8 problems per launch (got %d)", n);
+  for (int i = 0; i < n; ++i) {
+    if (int rc = check_desc(d[i])) return rc;
+    K3M_REQUIRE(d[i].layout == d[0].layout, "gemm_grouped: every problem of a group must have the same layout");
+  }
+  // variant: CTA pairs (256 x 256 tile per pair) when every problem is at least one pair tile in both directions
+  // and the group as a whole fills the pairs; else 128 x 128 single-CTA tiles
+  static const int mode_2cta = getenv("K3M_GEMM_2CTA") ? atoi(getenv("K3M_GEMM_2CTA")) : 1;
+  bool all_big = mode_2cta != 0;
+  long pt = 0;
+  for (int i = 0; i < n; ++i) {
+    all_big = all_big && d[i].M >= 256 && d[i].N >= 256;
+    pt += (long)((d[i].M + 255) / 256) * ((d[i].N + 255) / 256);
+  }
+  const long pairs = num_sms() / 2;
+  const int ctas = (all_big && pt * 5 >= pairs * 3) ? 2 : 1;
+  const int bn = ctas == 2 ? 256 : 128, ew = 4;
+  // split-K of accumulating problems (weight gradients): until the group has ~3 waves of tiles
+  int splits[8], order[8];
+  const long resident = num_sms() / ctas;
+  long tiles_total = 0;
+  long base_tiles[8];
+  for (int i = 0; i < n; ++i) {
+    base_tiles[i] = (long)((d[i].M + BM * ctas - 1) / (BM * ctas)) * ((d[i].N + bn - 1) / bn);
+    tiles_total += base_tiles[i];
+    splits[i] = 1;
+    order[i] = i;
+  }
+  for (bool grew = true; grew && tiles_total < 3 * resident;) {
+    grew = false;
+    for (int i = 0; i < n && tiles_total < 3 * resident; ++i) {
+      const int kb = (d[i].K + BK - 1) / BK;
+      if (d[i].accumulate && kb / (splits[i] * 2) >= 4) {
+        tiles_total += base_tiles[i] * splits[i];
+        splits[i] *= 2;
+        grew = true;
       }
-      if (p.tin && !get_map(src, N, M, ld_src, cw, 32, &mi, 2)) return K3M_ERR_CUDA;
     }
   }
-  static const int probe = getenv("K3M_GEMM_PROBE") ? atoi(getenv("K3M_GEMM_PROBE")) : 0;
-  p.probe = probe;
-  p.fast = F_NONE;
-  static const int no_fast = getenv("K3M_GEMM_NO_FAST") ? atoi(getenv("K3M_GEMM_NO_FAST")) : 0;
-  if (!no_fast && p.tma_out && !out_f32 && !accumulate && p.vec_ok && N % 8 == 0) {
-    const bool has_drop = p.drop.thresh != 0;
-    if (act == ACT_NONE && aux_out == nullptr) {
-      if (addend == nullptr) p.fast = F_PLAIN;
-      else if (p.tin == 2) p.fast = F_ADD;
-    } else if (act == ACT_GELU && want_aux && addend == nullptr && !has_drop) {
-      p.fast = F_GELU;
-    } else if (act == ACT_DGELU && p.tin == 1 && addend == nullptr && bias == nullptr && !has_drop) {
-      p.fast = F_DGELU;
-    }
-  }
-  {
-    static const char* fast_names[] = {"generic", "F_PLAIN", "F_ADD", "F_GELU", "F_DGELU"};
-    snprintf(g_variant, sizeof(g_variant), "bn=%d ctas=%d ew=%d dual=%d splits=%d epi=%s tin=%d tma_out=%d acc=%d",
-             bn, ctas, dual ? 2 : ew, dual ? 1 : 0, p.splits, fast_names[p.fast], p.tin, p.tma_out, accumulate);
-  }
-  if (layout == 0) return dispatch<false, false>(bn, dual ? 0 : ew, ctas, ma, mb, mc, mx, mi, p, st);
-  if (layout == 1) return dispatch<false, true>(bn, dual ? 0 : ew, ctas, ma, mb, mc, mx, mi, p, st);
-  return dispatch<true, true>(bn, dual ? 0 : ew, ctas, ma, mb, mc, mx, mi, p, st);
+  // longest tiles first
+  auto kb_of = [&](int i) { const int kb = (d[i].K + BK - 1) / BK; return (kb + splits[i] - 1) / splits[i]; };
+  for (int i = 1; i < n; ++i)
+    for (int j = i; j > 0 && kb_of(order[j]) > kb_of(order[j - 1]); --j) { const int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t; }
+  GroupArgs<8> g;
+  g.n = n;
+  for (int i = 0; i < n; ++i)
+    if (int rc = setup_problem(d[order[i]], bn, ctas, ew, splits[order[i]], &g.prob[i])) return rc;
+  for (int i = n; i < 8; ++i) g.prob[i] = g.prob[0];
+  snprintf(g_variant, sizeof(g_variant), "bn=%d ctas=%d ew=%d dual=0 splits=%d epi=%s tin=%d tma_out=%d acc=%d group=%d",
+           bn, ctas, ew, g.prob[0].p.splits, fast_name(g.prob[0].p.fast), g.prob[0].p.tin, g.prob[0].p.tma_out,
+           d[0].accumulate, n);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (d[0].layout == 0) return dispatch_group<false, false>(ctas, g, st);
+  if (d[0].layout == 1) return dispatch_group<false, true>(ctas, g, st);
+  return dispatch_group<true, true>(ctas, g, st);
 }

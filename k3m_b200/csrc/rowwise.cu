@@ -9,62 +9,127 @@ namespace {
 // LayerNorm forward: y = (x - mean) * rstd * gamma + beta   [TF style: eps inside the sqrt,
 // biased variance — vilbert_k3m.py:328-332], optional dropout on y (embeddings).
 // NV = 8-element vectors per lane (H <= 256 * NV).
+// Grouped form: up to 8 independent LayerNorms (the six streams of a connection stage, a text and an image layer)
+// in ONE launch; NV is sized for the widest of them.  A CTA (four rows) belongs to one problem.
+struct LnFwdProb {
+  const bf16 *x, *gamma, *beta;
+  bf16* y;
+  float *mean, *rstd;
+  int M, H;
+  DropSpec drop;
+  int cta_begin;
+};
+struct LnFwdGroup {
+  int n;
+  float eps;
+  LnFwdProb p[8];
+};
+// Warps walk the concatenated row list of all problems (row = warp, warp + #warps, ...) and load the NEXT row
+// (kept packed, NV x 16 bytes per lane) before they reduce the current one: CTAs that live for a single 1.5 KB row
+// spent their time being scheduled (1.9 TB/s over the 113 launches of a step), two rows in flight per warp hide
+// the HBM latency instead.
 template <int NV>
-__global__ void __launch_bounds__(128) ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ gamma,
-                                                     const bf16* __restrict__ beta, bf16* __restrict__ y,
-                                                     float* __restrict__ mean_out, float* __restrict__ rstd_out,
-                                                     int M, int H, float eps, DropSpec drop) {
+__global__ void __launch_bounds__(256) ln_fwd_group_kernel(const __grid_constant__ LnFwdGroup g) {
   const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
-  if (row >= M) return;
-  const bf16* xr = x + (size_t)row * H;
-  float v[NV][8];
-  float s = 0.f;
+  const int nwarps = gridDim.x * 8;
+  int total = 0;
+  for (int i = 0; i < g.n; ++i) total += g.p[i].M;
+  int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (r >= total) return;
+  auto locate = [&](int row, int& pi, int& local) {
+    pi = 0;
+    local = row;
+    while (pi + 1 < g.n && local >= g.p[pi].M) {
+      local -= g.p[pi].M;
+      ++pi;
+    }
+  };
+  int pi, lr;
+  locate(r, pi, lr);
+  uint4 cur[NV], nxt[NV];
+  {
+    const LnFwdProb& P = g.p[pi];
+    const bf16* xr = P.x + (size_t)lr * P.H;
 #pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int c = (lane + 32 * i) * 8;
-    if (c < H) {
-      ld8(xr + c, v[i]);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) s += v[i][j];
+    for (int i = 0; i < NV; ++i) {
+      const int c = (lane + 32 * i) * 8;
+      if (c < P.H) cur[i] = *reinterpret_cast<const uint4*>(xr + c);
     }
   }
-  const float mean = warp_sum(s) / (float)H;
-  float q = 0.f;
+  while (true) {
+    const int rn = r + nwarps;
+    int pn = 0, ln_ = 0;
+    const bool more = rn < total;
+    if (more) {
+      locate(rn, pn, ln_);
+      const LnFwdProb& Q = g.p[pn];
+      const bf16* xr = Q.x + (size_t)ln_ * Q.H;
 #pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int c = (lane + 32 * i) * 8;
-    if (c < H) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float d = v[i][j] - mean;
-        q += d * d;
+      for (int i = 0; i < NV; ++i) {
+        const int c = (lane + 32 * i) * 8;
+        if (c < Q.H) nxt[i] = *reinterpret_cast<const uint4*>(xr + c);
       }
     }
-  }
-  const float rstd = rsqrtf(warp_sum(q) / (float)H + eps);
-  if (lane == 0) {
-    mean_out[row] = mean;
-    rstd_out[row] = rstd;
-  }
-  bf16* yr = y + (size_t)row * H;
+    {
+      const LnFwdProb& P = g.p[pi];
+      const int H = P.H;
+      float v[NV][8];
+      float s = 0.f;
 #pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int c = (lane + 32 * i) * 8;
-    if (c < H) {
-      float g[8], b[8], o[8];
-      ld8(gamma + c, g);
-      ld8(beta + c, b);
+      for (int i = 0; i < NV; ++i) {
+        const int c = (lane + 32 * i) * 8;
+        if (c < H) {
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&cur[i]);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * g[j] + b[j];
-      if (drop.thresh) {
-        uint32_t w[4];
-        rng_words(drop.rng, drop.site, ((unsigned long long)row * H + c) >> 3, w);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] *= drop_mult(drop, w, j);
+          for (int j = 0; j < 4; ++j) {
+            const float2 f = __bfloat1622float2(h[j]);
+            v[i][2 * j] = f.x; v[i][2 * j + 1] = f.y;
+            s += f.x + f.y;
+          }
+        }
       }
-      st8(yr + c, o);
+      const float mean = warp_sum(s) / (float)H;
+      float q = 0.f;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int c = (lane + 32 * i) * 8;
+        if (c < H) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float d = v[i][j] - mean;
+            q += d * d;
+          }
+        }
+      }
+      const float rstd = rsqrtf(warp_sum(q) / (float)H + g.eps);
+      if (lane == 0) {
+        P.mean[lr] = mean;
+        P.rstd[lr] = rstd;
+      }
+      bf16* yr = P.y + (size_t)lr * H;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int c = (lane + 32 * i) * 8;
+        if (c < H) {
+          float gm[8], b[8], o[8];
+          ld8(P.gamma + c, gm);
+          ld8(P.beta + c, b);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * gm[j] + b[j];
+          if (P.drop.thresh) {
+            uint32_t w[4];
+            rng_words(P.drop.rng, P.drop.site, ((unsigned long long)lr * H + c) >> 3, w);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] *= drop_mult(P.drop, w, j);
+          }
+          st8(yr + c, o);
+        }
+      }
     }
+    if (!more) break;
+    r = rn; pi = pn; lr = ln_;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) cur[i] = nxt[i];
   }
 }
 
@@ -103,12 +168,12 @@ __device__ __forceinline__ float ld_dsmem(const float* local, uint32_t rank) {
 // memory and each CTA of the cluster issues the atomics of 1/CL of the columns: CL x fewer same-address
 // atomics.  An experiment that did not pay (see k3m_ln_bwd below); selectable with K3M_LN_CLUSTER=1.
 template <int NV, int CL>
-__global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
-                                                        const bf16* __restrict__ gamma, const float* __restrict__ mean_in,
-                                                        const float* __restrict__ rstd_in, bf16* __restrict__ dx,
-                                                        bf16* __restrict__ dxm, float* __restrict__ dgamma,
-                                                        float* __restrict__ dbeta, float* __restrict__ dbias, int M, int H,
-                                                        DropSpec drop_out, DropSpec drop_in) {
+__device__ __forceinline__ void ln_bwd_body(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+                                            const bf16* __restrict__ gamma, const float* __restrict__ mean_in,
+                                            const float* __restrict__ rstd_in, bf16* __restrict__ dx,
+                                            bf16* __restrict__ dxm, float* __restrict__ dgamma,
+                                            float* __restrict__ dbeta, float* __restrict__ dbias, int M, int H,
+                                            const DropSpec& drop_out, const DropSpec& drop_in, int cta, int nctas) {
   // Register budget: two CTAs (16 warps) per SM keep enough rows in flight to cover HBM latency; the
   // row's dy / x stay packed as loaded (bf16) between the two passes and gamma is re-read (L1) per row,
   // so the live state is the 3 x NV x 8 fp32 column-sum accumulators.
@@ -119,7 +184,7 @@ __global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const bf16
   for (int i = 0; i < NV; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) ag[i][j] = ab[i][j] = ac[i][j] = 0.f;
-  for (int row = blockIdx.x * 8 + warp; row < M; row += gridDim.x * 8) {
+  for (int row = cta * 8 + warp; row < M; row += nctas * 8) {
     const float mean = mean_in[row], rstd = rstd_in[row];
     uint4 pd[NV], px[NV];
     float s1 = 0.f, s2 = 0.f;
@@ -230,6 +295,40 @@ __global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const bf16
     }
     cluster_barrier();               // nobody leaves while its shared memory is still being read
   }
+}
+
+template <int NV, int CL>
+__global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+                                                        const bf16* __restrict__ gamma, const float* __restrict__ mean_in,
+                                                        const float* __restrict__ rstd_in, bf16* __restrict__ dx,
+                                                        bf16* __restrict__ dxm, float* __restrict__ dgamma,
+                                                        float* __restrict__ dbeta, float* __restrict__ dbias, int M, int H,
+                                                        DropSpec drop_out, DropSpec drop_in) {
+  ln_bwd_body<NV, CL>(dy, x, gamma, mean_in, rstd_in, dx, dxm, dgamma, dbeta, dbias, M, H, drop_out, drop_in,
+                      (int)blockIdx.x, (int)gridDim.x);
+}
+
+// Grouped form (see LnFwdGroup): every problem owns a contiguous range of CTAs, sized by its share of the rows.
+struct LnBwdProb {
+  const bf16 *dy, *x, *gamma;
+  const float *mean, *rstd;
+  bf16 *dx, *dxm;
+  float *dgamma, *dbeta, *dbias;
+  int M, H;
+  DropSpec drop_out, drop_in;
+  int cta_begin, nctas;
+};
+struct LnBwdGroup {
+  int n;
+  LnBwdProb p[8];
+};
+template <int NV>
+__global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_group_kernel(const __grid_constant__ LnBwdGroup g) {
+  int pi = 0;
+  while (pi + 1 < g.n && (int)blockIdx.x >= g.p[pi + 1].cta_begin) ++pi;
+  const LnBwdProb& P = g.p[pi];
+  ln_bwd_body<NV, 1>(P.dy, P.x, P.gamma, P.mean, P.rstd, P.dx, P.dxm, P.dgamma, P.dbeta, P.dbias, P.M, P.H, P.drop_out,
+                     P.drop_in, (int)blockIdx.x - P.cta_begin, P.nctas);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -403,17 +502,23 @@ extern "C" int k3m_ln_fwd(const void* x, const void* gamma, const void* beta, vo
   K3M_REQUIRE(M > 0 && H > 0 && H % 8 == 0 && H <= 4096, "ln_fwd: need H %% 8 == 0 and H <= 4096 (H=%d)", H);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   DropSpec d = make_drop(rng, site, drop_p);
-  const int grid = (M + 3) / 4;
+  // one problem of the grouped (persistent, prefetching) kernel
+  LnFwdGroup g;
+  g.n = 1;
+  g.eps = eps;
+  LnFwdProb& P = g.p[0];
+  P.x = (const bf16*)x; P.gamma = (const bf16*)gamma; P.beta = (const bf16*)beta; P.y = (bf16*)y;
+  P.mean = mean; P.rstd = rstd; P.M = M; P.H = H; P.drop = d; P.cta_begin = 0;
+  for (int i = 1; i < 8; ++i) g.p[i] = g.p[0];
+  int ctas = (M + 7) / 8;
+  if (ctas > 148 * 4) ctas = 148 * 4;
   const int nv = (H + 255) / 256;
-#define LN_FWD(NV)                                                                                             \
-  ln_fwd_kernel<NV><<<grid, 128, 0, st>>>((const bf16*)x, (const bf16*)gamma, (const bf16*)beta, (bf16*)y, mean, \
-                                          rstd, M, H, eps, d)
-  if (nv <= 1) LN_FWD(1);
-  else if (nv <= 2) LN_FWD(2);
-  else if (nv <= 4) LN_FWD(4);
-  else if (nv <= 8) LN_FWD(8);
-  else LN_FWD(16);
-#undef LN_FWD
+  if (nv <= 1) ln_fwd_group_kernel<1><<<ctas, 256, 0, st>>>(g);
+  else if (nv <= 2) ln_fwd_group_kernel<2><<<ctas, 256, 0, st>>>(g);
+  else if (nv <= 3) ln_fwd_group_kernel<3><<<ctas, 256, 0, st>>>(g);
+  else if (nv <= 4) ln_fwd_group_kernel<4><<<ctas, 256, 0, st>>>(g);
+  else if (nv <= 8) ln_fwd_group_kernel<8><<<ctas, 256, 0, st>>>(g);
+  else ln_fwd_group_kernel<16><<<ctas, 256, 0, st>>>(g);
   return k3m_check_launch("k3m_ln_fwd");
 }
 
@@ -468,6 +573,111 @@ extern "C" int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, cons
   else LN_BWD(4);
 #undef LN_BWD
   return k3m_check_launch("k3m_ln_bwd");
+}
+
+struct LnFwdDesc {      // == K3MLnFwdDesc of include/k3m.h
+  const void *x, *gamma, *beta;
+  void* y;
+  float *mean, *rstd;
+  int M, H;
+  const void* rng;
+  unsigned int site;
+  float drop_p;
+};
+struct LnBwdDesc {      // == K3MLnBwdDesc
+  const void *dy, *x, *gamma;
+  const float *mean, *rstd;
+  void *dx, *dxm;
+  float *dgamma, *dbeta, *dbias;
+  int M, H;
+  const void* rng;
+  unsigned int site_out;
+  float p_out;
+  unsigned int site_in;
+  float p_in;
+};
+
+extern "C" int k3m_ln_fwd_grouped(const void* descs, int n, float eps, void* stream) {
+  const LnFwdDesc* d = reinterpret_cast<const LnFwdDesc*>(descs);
+  K3M_REQUIRE(n >= 1 && n <= 8, "ln_fwd_grouped: 1..8 problems per launch (got %d)", n);
+  LnFwdGroup g;
+  g.n = n;
+  g.eps = eps;
+  int ctas = 0, hmax = 0;
+  for (int i = 0; i < n; ++i) {
+    K3M_REQUIRE(d[i].M > 0 && d[i].H > 0 && d[i].H % 8 == 0 && d[i].H <= 4096, "ln_fwd_grouped: need H %% 8 == 0 and H <= 4096 (H=%d)", d[i].H);
+    LnFwdProb& P = g.p[i];
+    P.x = (const bf16*)d[i].x; P.gamma = (const bf16*)d[i].gamma; P.beta = (const bf16*)d[i].beta;
+    P.y = (bf16*)d[i].y; P.mean = d[i].mean; P.rstd = d[i].rstd; P.M = d[i].M; P.H = d[i].H;
+    P.drop = make_drop(d[i].rng, d[i].site, d[i].drop_p);
+    P.cta_begin = 0;
+    ctas += d[i].M;
+    if (d[i].H > hmax) hmax = d[i].H;
+  }
+  for (int i = n; i < 8; ++i) g.p[i] = g.p[0];
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int nv = (hmax + 255) / 256;
+  // rows per warp >= 2 once there are enough rows: at most 148 SMs x 4 CTAs of 8 warps
+  ctas = (ctas + 7) / 8;
+  if (ctas > 148 * 4) ctas = 148 * 4;
+  if (nv <= 1) ln_fwd_group_kernel<1><<<ctas, 256, 0, st>>>(g);
+  else if (nv <= 2) ln_fwd_group_kernel<2><<<ctas, 256, 0, st>>>(g);
+  else if (nv <= 3) ln_fwd_group_kernel<3><<<ctas, 256, 0, st>>>(g);
+  else if (nv <= 4) ln_fwd_group_kernel<4><<<ctas, 256, 0, st>>>(g);
+  else if (nv <= 8) ln_fwd_group_kernel<8><<<ctas, 256, 0, st>>>(g);
+  else ln_fwd_group_kernel<16><<<ctas, 256, 0, st>>>(g);
+  return k3m_check_launch("k3m_ln_fwd_grouped");
+}
+
+extern "C" int k3m_ln_bwd_grouped(const void* descs, int n, void* stream) {
+  const LnBwdDesc* d = reinterpret_cast<const LnBwdDesc*>(descs);
+  K3M_REQUIRE(n >= 1 && n <= 8, "ln_bwd_grouped: 1..8 problems per launch (got %d)", n);
+  LnBwdGroup g;
+  g.n = n;
+  long rows = 0;
+  int hmax = 0;
+  for (int i = 0; i < n; ++i) {
+    K3M_REQUIRE(d[i].M > 0 && d[i].H > 0 && d[i].H % 8 == 0 && d[i].H <= 1024, "ln_bwd_grouped: need H %% 8 == 0 and H <= 1024 (H=%d)", d[i].H);
+    rows += d[i].M;
+    if (d[i].H > hmax) hmax = d[i].H;
+  }
+  const int nv = (hmax + 255) / 256;
+  const int target = 148 * (nv >= 4 ? 1 : 2) * 2;        // about two waves of resident CTAs over the whole group
+  int ctas = 0;
+  for (int i = 0; i < n; ++i) {
+    LnBwdProb& P = g.p[i];
+    P.dy = (const bf16*)d[i].dy; P.x = (const bf16*)d[i].x; P.gamma = (const bf16*)d[i].gamma;
+    P.mean = d[i].mean; P.rstd = d[i].rstd; P.dx = (bf16*)d[i].dx; P.dxm = (bf16*)d[i].dxm;
+    P.dgamma = d[i].dgamma; P.dbeta = d[i].dbeta; P.dbias = d[i].dbias; P.M = d[i].M; P.H = d[i].H;
+    P.drop_out = make_drop(d[i].rng, d[i].site_out, d[i].p_out);
+    P.drop_in = make_drop(d[i].rng, d[i].site_in, d[i].p_in);
+    K3M_REQUIRE(!P.drop_in.thresh || P.dxm, "ln_bwd_grouped: drop_in needs the dxm output");
+    int c = (int)(((long)target * d[i].M + rows - 1) / rows);
+    const int cmax = (d[i].M + 7) / 8;
+    if (c > cmax) c = cmax;
+    if (c < 1) c = 1;
+    P.cta_begin = ctas;
+    P.nctas = c;
+    ctas += c;
+  }
+  for (int i = n; i < 8; ++i) g.p[i] = g.p[0];
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const size_t smem = (size_t)8 * 3 * hmax * sizeof(float);
+#define LN_BWD_G(NV)                                                                                              \
+  do {                                                                                                            \
+    static bool cfg = false;                                                                                      \
+    if (!cfg) {                                                                                                   \
+      cudaFuncSetAttribute(ln_bwd_group_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 3 * 1024 * 4); \
+      cfg = true;                                                                                                 \
+    }                                                                                                             \
+    ln_bwd_group_kernel<NV><<<ctas, 256, smem, st>>>(g);                                                          \
+  } while (0)
+  if (nv <= 1) LN_BWD_G(1);
+  else if (nv <= 2) LN_BWD_G(2);
+  else if (nv <= 3) LN_BWD_G(3);
+  else LN_BWD_G(4);
+#undef LN_BWD_G
+  return k3m_check_launch("k3m_ln_bwd_grouped");
 }
 
 extern "C" int k3m_colsum(const void* x, int ld, int x_f32, float* out, int M, int N, void* stream) {

@@ -120,147 +120,239 @@ class Engine(object):
         return self.ops.gemm(dy, self.W(wname), "nn", rng=self.rng, **kw)
 
     # ---- blocks ------------------------------------------------------------------------------
-    def attn_out_fwd(self, ctx, x, p_dense, p_ln, p_drop):
-        """LN(dropout(ctx W^T + b) + x)  — BertSelfOutput `:485-489` and the BertBiOutput halves
-        `:986-996`."""
+    # Every block works on a LIST of independent streams in lock-step (the three connection layers of a stage;
+    # the text and the image layer of a stage): the same projection of all of them is ONE grouped GEMM launch
+    # (`ops.gemm_group` -> k3m_gemm_grouped_bf16), so M ~ 2304-row problems fill whole waves of CTA pairs
+    # together.  Attention and LayerNorm launches of the streams run on concurrent CUDA streams (`ops.parallel`),
+    # weight / bias gradients leave for the auxiliary stream, grouped as well.
+    def gemms(self, calls):
+        grp = getattr(self.ops, "gemm_group", None)
+        if grp is None or len(calls) == 1:
+            return [self.ops.gemm(**c) for c in calls]
+        return grp(calls)
+
+    def wgrads(self, items):
+        """G[w] += dy^T x for every (dy, x, wname): one grouped launch on the auxiliary stream."""
+        calls = [dict(a=dy, b=x, layout="tn", out=self.G(w), accumulate=True) for dy, x, w in items]
+        keep = tuple(t for dy, x, _ in items for t in (dy, x))
+        self._aux(lambda: self.gemms(calls), keep)
+
+    def lns_fwd(self, items):
+        """LayerNorm of every stream of a group: one grouped launch when the op table has one -> [(y, mean, rstd)]"""
+        grp = getattr(self.ops, "ln_fwd_group", None)
+        if grp is None or len(items) == 1:
+            return [self.ops.ln_fwd(**it) for it in items]
+        return grp(items)
+
+    def lns_bwd(self, items):
+        grp = getattr(self.ops, "ln_bwd_group", None)
+        if grp is None or len(items) == 1:
+            return [self.ops.ln_bwd(**it) for it in items]
+        return grp(items)
+
+    def _each(self, fns):
+        """independent non-GEMM launches of the streams of a group: concurrent CUDA streams"""
+        if len(fns) == 1:
+            fns[0]()
+        else:
+            self.ops.parallel(fns)
+
+    def attn_out_fwd_m(self, items):
+        """LN(dropout(ctx W^T + b) + x)  — BertSelfOutput `:485-489` and the BertBiOutput halves `:986-996`.
+        items: (ctx, x, p_dense, p_ln, p_drop) -> [(a, saved)]."""
         ops = self.ops
-        s = self.site(p_drop)
-        z = ops.gemm(ctx, self.W(p_dense + ".weight"), "nt", bias=self.W(p_dense + ".bias"),
-                     drop=s, rng=self.rng, addend=x)
-        a, mean, rstd = ops.ln_fwd(z, self.W(p_ln + ".weight"), self.W(p_ln + ".bias"))
-        return a, (ctx, z, mean, rstd, s, p_dense, p_ln)
+        sites = [self.site(it[4]) for it in items]
+        zs = self.gemms([dict(a=ctx, b=self.W(pd + ".weight"), layout="nt", bias=self.W(pd + ".bias"), drop=s,
+                              rng=self.rng, addend=x) for (ctx, x, pd, pl, _), s in zip(items, sites)])
+        lns = self.lns_fwd([dict(x=zs[i], gamma=self.W(it[3] + ".weight"), beta=self.W(it[3] + ".bias"))
+                            for i, it in enumerate(items)])
+        return [(lns[i][0], (it[0], zs[i], lns[i][1], lns[i][2], sites[i], it[2], it[3])) for i, it in enumerate(items)]
 
-    def attn_out_bwd(self, da, saved):
-        """-> (dx residual grad, dctx)."""
-        ctx, z, mean, rstd, s, p_dense, p_ln = saved
-        dz, dzm = self.ops.ln_bwd(da, z, self.W(p_ln + ".weight"), mean, rstd,
-                                  self.G(p_ln + ".weight"), self.G(p_ln + ".bias"),
-                                  drop_in=s, rng=self.rng, dbias=self.G(p_dense + ".bias"))
-        self.wgrad(dzm, ctx, p_dense + ".weight")
-        dctx = self.dgrad(dzm, p_dense + ".weight")
-        return dz, dctx
+    def attn_out_bwd_m(self, items):
+        """items: (da, saved) -> [(dx residual grad, dctx)]."""
+        lns = self.lns_bwd([dict(dy=da, x=z, gamma=self.W(pl + ".weight"), mean=mean, rstd=rstd,
+                                 dgamma=self.G(pl + ".weight"), dbeta=self.G(pl + ".bias"), drop_in=s, rng=self.rng,
+                                 dbias=self.G(pd + ".bias")) for da, (ctx, z, mean, rstd, s, pd, pl) in items])
+        self.wgrads([(lns[i][1], it[1][0], it[1][5] + ".weight") for i, it in enumerate(items)])
+        dctxs = self.gemms([dict(a=lns[i][1], b=self.W(it[1][5] + ".weight"), layout="nn", rng=self.rng)
+                            for i, it in enumerate(items)])
+        return [(lns[i][0], dctxs[i]) for i in range(len(items))]
 
-    def ffn_fwd(self, a, p_int, p_out, p_drop, out=None):
-        """LN(dropout(gelu(a W1^T + b1) W2^T + b2) + a) — BertIntermediate `:515-518` +
-        BertOutput `:528-532` (and the image twins)."""
+    def ffn_fwd_m(self, items):
+        """LN(dropout(gelu(a W1^T + b1) W2^T + b2) + a) — BertIntermediate `:515-518` + BertOutput `:528-532`
+        (and the image twins).  items: (a, p_int, p_out, p_drop, out) -> [(y, saved)]."""
         ops = self.ops
-        M = a.shape[0]
-        w1 = self.W(p_int + ".dense.weight")
-        pre = self.empty(M, w1.shape[0])
-        h = ops.gemm(a, w1, "nt", bias=self.W(p_int + ".dense.bias"), act=ACT_GELU, aux_out=pre)
-        s = self.site(p_drop)
-        z = ops.gemm(h, self.W(p_out + ".dense.weight"), "nt", bias=self.W(p_out + ".dense.bias"),
-                     drop=s, rng=self.rng, addend=a)
-        y, mean, rstd = ops.ln_fwd(z, self.W(p_out + ".LayerNorm.weight"),
-                                   self.W(p_out + ".LayerNorm.bias"), out=out)
-        return y, (a, pre, h, z, mean, rstd, s, p_int, p_out)
+        pres = [self.empty(a.shape[0], self.W(pi + ".dense.weight").shape[0]) for a, pi, _, _, _ in items]
+        hs = self.gemms([dict(a=a, b=self.W(pi + ".dense.weight"), layout="nt", bias=self.W(pi + ".dense.bias"),
+                              act=ACT_GELU, aux_out=pre) for (a, pi, _, _, _), pre in zip(items, pres)])
+        sites = [self.site(it[3]) for it in items]
+        zs = self.gemms([dict(a=h, b=self.W(po + ".dense.weight"), layout="nt", bias=self.W(po + ".dense.bias"),
+                              drop=s, rng=self.rng, addend=a) for (a, _, po, _, _), h, s in zip(items, hs, sites)])
+        lns = self.lns_fwd([dict(x=zs[i], gamma=self.W(it[2] + ".LayerNorm.weight"), beta=self.W(it[2] + ".LayerNorm.bias"),
+                                 out=it[4]) for i, it in enumerate(items)])
+        return [(lns[i][0], (it[0], pres[i], hs[i], zs[i], lns[i][1], lns[i][2], sites[i], it[1], it[2]))
+                for i, it in enumerate(items)]
 
-    def ffn_bwd(self, dy, saved):
-        a, pre, h, z, mean, rstd, s, p_int, p_out = saved
-        ops = self.ops
-        dz, dzm = ops.ln_bwd(dy, z, self.W(p_out + ".LayerNorm.weight"), mean, rstd,
-                             self.G(p_out + ".LayerNorm.weight"), self.G(p_out + ".LayerNorm.bias"),
-                             drop_in=s, rng=self.rng, dbias=self.G(p_out + ".dense.bias"))
-        self.wgrad(dzm, h, p_out + ".dense.weight")
-        dpre = self.dgrad(dzm, p_out + ".dense.weight", act=ACT_DGELU, aux_in=pre)
-        self.bgrad(dpre, p_int + ".dense.bias")
-        self.wgrad(dpre, a, p_int + ".dense.weight")
-        return self.dgrad(dpre, p_int + ".dense.weight", addend=dz)
+    def ffn_bwd_m(self, items):
+        """items: (dy, saved) -> [da]."""
+        lns = self.lns_bwd([dict(dy=dy, x=z, gamma=self.W(po + ".LayerNorm.weight"), mean=mean, rstd=rstd,
+                                 dgamma=self.G(po + ".LayerNorm.weight"), dbeta=self.G(po + ".LayerNorm.bias"),
+                                 drop_in=s, rng=self.rng, dbias=self.G(po + ".dense.bias"))
+                            for dy, (a, pre, h, z, mean, rstd, s, pi, po) in items])
+        self.wgrads([(lns[i][1], it[1][2], it[1][8] + ".dense.weight") for i, it in enumerate(items)])
+        dpres = self.gemms([dict(a=lns[i][1], b=self.W(it[1][8] + ".dense.weight"), layout="nn", rng=self.rng,
+                                 act=ACT_DGELU, aux_in=it[1][1]) for i, it in enumerate(items)])
+        for i, it in enumerate(items):
+            self.bgrad(dpres[i], it[1][7] + ".dense.bias")
+        self.wgrads([(dpres[i], it[1][0], it[1][7] + ".dense.weight") for i, it in enumerate(items)])
+        return self.gemms([dict(a=dpres[i], b=self.W(it[1][7] + ".dense.weight"), layout="nn", rng=self.rng,
+                                addend=lns[i][0]) for i, it in enumerate(items)])
 
-    def layer_fwd(self, p, x, segs, image, out=None):
-        """BertLayer `:535-548` / BertImageLayer `:696-709` on a stacked activation."""
+    def layers_fwd_m(self, items):
+        """BertLayer `:535-548` / BertImageLayer `:696-709` on stacked activations.
+        items: (p, x, segs, image, out) -> [(y, saved)]."""
         c, ops = self.cfg, self.ops
-        H = x.shape[1]
-        heads = c.v_num_attention_heads if image else c.num_attention_heads
-        p_att = c.v_attention_probs_dropout_prob if image else c.attention_probs_dropout_prob
-        p_hid = c.v_hidden_dropout_prob if image else c.hidden_dropout_prob
-        d = H // heads
-        qkv = ops.gemm(x, self.W(p + ".attention.self.qkv.weight"), "nt",
-                       bias=self.W(p + ".attention.self.qkv.bias"))
-        ctx = self.empty(x.shape[0], H)
-        att = []
-        for sg in segs:
-            s = self.site(p_att)
-            v = qkv[sg.r0:sg.r1]
-            _, lse = ops.attn_fwd(v, 0, v, H, 2 * H, sg.mask, sg.B, heads, sg.L, sg.L, d,
-                                  drop=s, rng=self.rng, out=ctx[sg.r0:sg.r1])
-            att.append((sg, s, lse))
-        a, sv_o = self.attn_out_fwd(ctx, x, p + ".attention.output.dense",
-                                    p + ".attention.output.LayerNorm", p_hid)
-        y, sv_f = self.ffn_fwd(a, p + ".intermediate", p + ".output", p_hid, out=out)
-        saved = (p, x, qkv, att, heads, d, sv_o, sv_f)
-        return y, saved
+        qkvs = self.gemms([dict(a=x, b=self.W(p + ".attention.self.qkv.weight"), layout="nt",
+                                bias=self.W(p + ".attention.self.qkv.bias")) for p, x, _, _, _ in items])
+        ctxs = [self.empty(x.shape[0], x.shape[1]) for _, x, _, _, _ in items]
+        atts = [[] for _ in items]
+        meta = []
+        for p, x, segs, image, _ in items:
+            H = x.shape[1]
+            heads = c.v_num_attention_heads if image else c.num_attention_heads
+            meta.append((H, heads, H // heads, c.v_attention_probs_dropout_prob if image else c.attention_probs_dropout_prob,
+                         c.v_hidden_dropout_prob if image else c.hidden_dropout_prob))
 
-    def layer_bwd(self, dy, saved):
-        p, x, qkv, att, heads, d, sv_o, sv_f = saved
+        def attn(i):
+            def run():
+                H, heads, d, p_att, _ = meta[i]
+                for sg in items[i][2]:
+                    s = self.site(p_att)
+                    v = qkvs[i][sg.r0:sg.r1]
+                    _, lse = ops.attn_fwd(v, 0, v, H, 2 * H, sg.mask, sg.B, heads, sg.L, sg.L, d, drop=s, rng=self.rng,
+                                          out=ctxs[i][sg.r0:sg.r1])
+                    atts[i].append((sg, s, lse))
+            return run
+        self._each([attn(i) for i in range(len(items))])
+        ao = self.attn_out_fwd_m([(ctxs[i], it[1], it[0] + ".attention.output.dense", it[0] + ".attention.output.LayerNorm",
+                                   meta[i][4]) for i, it in enumerate(items)])
+        ff = self.ffn_fwd_m([(ao[i][0], it[0] + ".intermediate", it[0] + ".output", meta[i][4], it[4])
+                             for i, it in enumerate(items)])
+        return [(ff[i][0], (it[0], it[1], qkvs[i], atts[i], meta[i][1], meta[i][2], ao[i][1], ff[i][1]))
+                for i, it in enumerate(items)]
+
+    def layers_bwd_m(self, items):
+        """items: (dy, saved) -> [dx]."""
         ops = self.ops
-        H = x.shape[1]
-        da = self.ffn_bwd(dy, sv_f)
-        dz1, dctx = self.attn_out_bwd(da, sv_o)
-        ctx = sv_o[0]
-        dqkv = self.empty(x.shape[0], 3 * H)
-        for sg, s, lse in att:
-            v = qkv[sg.r0:sg.r1]
-            dv = dqkv[sg.r0:sg.r1]
-            ops.attn_bwd(dctx[sg.r0:sg.r1], ctx[sg.r0:sg.r1], v, 0, v, H, 2 * H, sg.mask, lse,
-                         dv, dv, sg.B, heads, sg.L, sg.L, d, drop=s, rng=self.rng)
-        self.bgrad(dqkv, p + ".attention.self.qkv.bias")
-        self.wgrad(dqkv, x, p + ".attention.self.qkv.weight")
-        return self.dgrad(dqkv, p + ".attention.self.qkv.weight", addend=dz1)
+        das = self.ffn_bwd_m([(dy, sv[7]) for dy, sv in items])
+        ao = self.attn_out_bwd_m([(das[i], sv[6]) for i, (_, sv) in enumerate(items)])
+        dqkvs = [self.empty(sv[1].shape[0], 3 * sv[1].shape[1]) for _, sv in items]
 
-    def connection_fwd(self, p, x1, sg1, x2, sg2, two_text, out1, out2):
-        """BertConnectionLayer `:1030-1071` / `_two_text` `:1074-1111`.  Stream 1 = image (PV in
-        the two-text pass), stream 2 = text.  ctx1 (text-length) = queries of 2 over K/V of 1,
-        masked by mask1 (`:786-800`); ctx2 = queries of 1 over K/V of 2.  The image stream gets
-        ctx2 through dense1, the text stream ctx1 through dense2 (`:1061-1063`)."""
+        def attn(i):
+            def run():
+                p, x, qkv, att, heads, d, sv_o, sv_f = items[i][1]
+                H, ctx, dctx = x.shape[1], sv_o[0], ao[i][1]
+                for sg, s, lse in att:
+                    v, dv = qkv[sg.r0:sg.r1], dqkvs[i][sg.r0:sg.r1]
+                    ops.attn_bwd(dctx[sg.r0:sg.r1], ctx[sg.r0:sg.r1], v, 0, v, H, 2 * H, sg.mask, lse, dv, dv,
+                                 sg.B, heads, sg.L, sg.L, d, drop=s, rng=self.rng)
+            return run
+        self._each([attn(i) for i in range(len(items))])
+        for i, (_, sv) in enumerate(items):
+            self.bgrad(dqkvs[i], sv[0] + ".attention.self.qkv.bias")
+        self.wgrads([(dqkvs[i], sv[1], sv[0] + ".attention.self.qkv.weight") for i, (_, sv) in enumerate(items)])
+        return self.gemms([dict(a=dqkvs[i], b=self.W(sv[0] + ".attention.self.qkv.weight"), layout="nn", rng=self.rng,
+                                addend=ao[i][0]) for i, (_, sv) in enumerate(items)])
+
+    def connections_fwd_m(self, specs):
+        """BertConnectionLayer `:1030-1071` / `_two_text` `:1074-1111`, the independent connection layers of one
+        stage in lock-step.  specs: (p, x1, sg1, x2, sg2, two_text, out1, out2).  Stream 1 = image (PV in the
+        two-text pass), stream 2 = text.  ctx1 (text-length) = queries of 2 over K/V of 1, masked by mask1
+        (`:786-800`); ctx2 = queries of 1 over K/V of 2.  The image stream gets ctx2 through dense1, the text
+        stream ctx1 through dense2 (`:1061-1063`).  -> [saved]."""
         c, ops = self.cfg, self.ops
         heads = c.bi_num_attention_heads
-        Hb = c.hidden_size if two_text else c.bi_hidden_size
-        d = Hb // heads
-        B, L1, L2 = sg1.B, sg1.L, sg2.L
-        b = p + ".biattention."
-        qkv1 = ops.gemm(x1, self.W(b + "qkv1.weight"), "nt", bias=self.W(b + "qkv1.bias"))
-        qkv2 = ops.gemm(x2, self.W(b + "qkv2.weight"), "nt", bias=self.W(b + "qkv2.bias"))
-        s1 = self.site(c.v_attention_probs_dropout_prob)
-        ctx1, lse1 = ops.attn_fwd(qkv2, 0, qkv1, Hb, 2 * Hb, sg1.mask, B, heads, L2, L1, d,
-                                  drop=s1, rng=self.rng)
-        s2 = self.site(c.attention_probs_dropout_prob)
-        ctx2, lse2 = ops.attn_fwd(qkv1, 0, qkv2, Hb, 2 * Hb, sg2.mask, B, heads, L1, L2, d,
-                                  drop=s2, rng=self.rng)
-        o = p + ".biOutput."
-        a1, sv_o1 = self.attn_out_fwd(ctx2, x1, o + "dense1", o + "LayerNorm1", c.v_hidden_dropout_prob)
-        a2, sv_o2 = self.attn_out_fwd(ctx1, x2, o + "dense2", o + "LayerNorm2", c.hidden_dropout_prob)
-        p1 = c.hidden_dropout_prob if two_text else c.v_hidden_dropout_prob
-        y1, sv_f1 = self.ffn_fwd(a1, p + ".v_intermediate", p + ".v_output", p1, out=out1)
-        y2, sv_f2 = self.ffn_fwd(a2, p + ".t_intermediate", p + ".t_output", c.hidden_dropout_prob,
-                                 out=out2)
-        saved = (p, x1, sg1, x2, sg2, Hb, heads, d, qkv1, qkv2, (s1, lse1), (s2, lse2),
-                 sv_o1, sv_o2, sv_f1, sv_f2)
-        return y1, y2, saved
+        calls = []
+        for p, x1, sg1, x2, sg2, two_text, _, _ in specs:
+            b = p + ".biattention."
+            calls.append(dict(a=x1, b=self.W(b + "qkv1.weight"), layout="nt", bias=self.W(b + "qkv1.bias")))
+            calls.append(dict(a=x2, b=self.W(b + "qkv2.weight"), layout="nt", bias=self.W(b + "qkv2.bias")))
+        qk = self.gemms(calls)
+        att = [None] * len(specs)
 
-    def connection_bwd(self, dy1, dy2, saved, dx1_out, dx2_out):
-        (p, x1, sg1, x2, sg2, Hb, heads, d, qkv1, qkv2, (s1, lse1), (s2, lse2),
-         sv_o1, sv_o2, sv_f1, sv_f2) = saved
+        def attn(i):
+            def run():
+                p, x1, sg1, x2, sg2, two_text, _, _ = specs[i]
+                Hb = c.hidden_size if two_text else c.bi_hidden_size
+                d = Hb // heads
+                qkv1, qkv2 = qk[2 * i], qk[2 * i + 1]
+                s1 = self.site(c.v_attention_probs_dropout_prob)
+                ctx1, lse1 = ops.attn_fwd(qkv2, 0, qkv1, Hb, 2 * Hb, sg1.mask, sg1.B, heads, sg2.L, sg1.L, d,
+                                          drop=s1, rng=self.rng)
+                s2 = self.site(c.attention_probs_dropout_prob)
+                ctx2, lse2 = ops.attn_fwd(qkv1, 0, qkv2, Hb, 2 * Hb, sg2.mask, sg1.B, heads, sg1.L, sg2.L, d,
+                                          drop=s2, rng=self.rng)
+                att[i] = (Hb, d, ctx1, ctx2, (s1, lse1), (s2, lse2))
+            return run
+        self._each([attn(i) for i in range(len(specs))])
+        items = []
+        for i, (p, x1, sg1, x2, sg2, two_text, _, _) in enumerate(specs):
+            o = p + ".biOutput."
+            items.append((att[i][3], x1, o + "dense1", o + "LayerNorm1", c.v_hidden_dropout_prob))
+            items.append((att[i][2], x2, o + "dense2", o + "LayerNorm2", c.hidden_dropout_prob))
+        ao = self.attn_out_fwd_m(items)
+        items = []
+        for i, (p, x1, sg1, x2, sg2, two_text, out1, out2) in enumerate(specs):
+            p1 = c.hidden_dropout_prob if two_text else c.v_hidden_dropout_prob
+            items.append((ao[2 * i][0], p + ".v_intermediate", p + ".v_output", p1, out1))
+            items.append((ao[2 * i + 1][0], p + ".t_intermediate", p + ".t_output", c.hidden_dropout_prob, out2))
+        ff = self.ffn_fwd_m(items)
+        saved = []
+        for i, (p, x1, sg1, x2, sg2, two_text, _, _) in enumerate(specs):
+            Hb, d, ctx1, ctx2, a1, a2 = att[i]
+            saved.append((p, x1, sg1, x2, sg2, Hb, heads, d, qk[2 * i], qk[2 * i + 1], a1, a2,
+                          ao[2 * i][1], ao[2 * i + 1][1], ff[2 * i][1], ff[2 * i + 1][1]))
+        return saved
+
+    def connections_bwd_m(self, items):
+        """items: (dy1, dy2, saved, dx1_out, dx2_out)."""
         ops = self.ops
-        B, L1, L2 = sg1.B, sg1.L, sg2.L
-        da1 = self.ffn_bwd(dy1, sv_f1)
-        da2 = self.ffn_bwd(dy2, sv_f2)
-        dz1, dctx2 = self.attn_out_bwd(da1, sv_o1)      # residual grads of x1 / x2
-        dz2, dctx1 = self.attn_out_bwd(da2, sv_o2)
-        ctx2, ctx1 = sv_o1[0], sv_o2[0]
-        dqkv1 = self.empty(x1.shape[0], 3 * Hb)
-        dqkv2 = self.empty(x2.shape[0], 3 * Hb)
-        ops.attn_bwd(dctx1, ctx1, qkv2, 0, qkv1, Hb, 2 * Hb, sg1.mask, lse1, dqkv2, dqkv1,
-                     B, heads, L2, L1, d, drop=s1, rng=self.rng)
-        ops.attn_bwd(dctx2, ctx2, qkv1, 0, qkv2, Hb, 2 * Hb, sg2.mask, lse2, dqkv1, dqkv2,
-                     B, heads, L1, L2, d, drop=s2, rng=self.rng)
-        b = p + ".biattention."
-        self.bgrad(dqkv1, b + "qkv1.bias")
-        self.bgrad(dqkv2, b + "qkv2.bias")
-        self.wgrad(dqkv1, x1, b + "qkv1.weight")
-        self.wgrad(dqkv2, x2, b + "qkv2.weight")
-        self.dgrad(dqkv1, b + "qkv1.weight", addend=dz1, out=dx1_out)
-        self.dgrad(dqkv2, b + "qkv2.weight", addend=dz2, out=dx2_out)
+        ffi = []
+        for dy1, dy2, sv, _, _ in items:
+            ffi += [(dy1, sv[14]), (dy2, sv[15])]
+        das = self.ffn_bwd_m(ffi)
+        aoi = []
+        for i, (_, _, sv, _, _) in enumerate(items):
+            aoi += [(das[2 * i], sv[12]), (das[2 * i + 1], sv[13])]
+        ao = self.attn_out_bwd_m(aoi)         # [2i] -> (dz1 residual grad of x1, dctx2), [2i+1] -> (dz2, dctx1)
+        dq = []
+        for _, _, sv, _, _ in items:
+            dq.append((self.empty(sv[1].shape[0], 3 * sv[5]), self.empty(sv[3].shape[0], 3 * sv[5])))
+
+        def attn(i):
+            def run():
+                (p, x1, sg1, x2, sg2, Hb, heads, d, qkv1, qkv2, (s1, lse1), (s2, lse2), sv_o1, sv_o2, _, _) = items[i][2]
+                dqkv1, dqkv2 = dq[i]
+                dctx2, dctx1 = ao[2 * i][1], ao[2 * i + 1][1]
+                ctx2, ctx1 = sv_o1[0], sv_o2[0]
+                ops.attn_bwd(dctx1, ctx1, qkv2, 0, qkv1, Hb, 2 * Hb, sg1.mask, lse1, dqkv2, dqkv1,
+                             sg1.B, heads, sg2.L, sg1.L, d, drop=s1, rng=self.rng)
+                ops.attn_bwd(dctx2, ctx2, qkv1, 0, qkv2, Hb, 2 * Hb, sg2.mask, lse2, dqkv1, dqkv2,
+                             sg1.B, heads, sg1.L, sg2.L, d, drop=s2, rng=self.rng)
+            return run
+        self._each([attn(i) for i in range(len(items))])
+        wg, calls = [], []
+        for i, (_, _, sv, dx1_out, dx2_out) in enumerate(items):
+            b = sv[0] + ".biattention."
+            self.bgrad(dq[i][0], b + "qkv1.bias")
+            self.bgrad(dq[i][1], b + "qkv2.bias")
+            wg += [(dq[i][0], sv[1], b + "qkv1.weight"), (dq[i][1], sv[3], b + "qkv2.weight")]
+            calls.append(dict(a=dq[i][0], b=self.W(b + "qkv1.weight"), layout="nn", rng=self.rng, addend=ao[2 * i][0],
+                              out=dx1_out))
+            calls.append(dict(a=dq[i][1], b=self.W(b + "qkv2.weight"), layout="nn", rng=self.rng, addend=ao[2 * i + 1][0],
+                              out=dx2_out))
+        self.wgrads(wg)
+        self.gemms(calls)
 
     # ---- embeddings ------------------------------------------------------------------------
     def text_embed_fwd(self, ids, type_ids, L):
@@ -525,51 +617,52 @@ class Engine(object):
         taps = self.taps
         t_last = c.t_biattention_id[-1]
 
+        def tap_text(i):
+            if taps is not None:
+                # call order of the shared module over the three passes (`:1686-1750`): title (t<->v), PV
+                # (pv<->v), then the two-text pass — title before PV inside its loop (`:1552-1576`), PV
+                # before title in the closing loops (`:1655-1672`)
+                order = (T1, P2, P3, T3) if i >= t_last else (T1, P2, T3, P3)
+                for k, sl in enumerate(order):
+                    taps["encoder.layer.%d#%d" % (i, k)] = box["X"][sl]
+
+        def tap_image(i):
+            if taps is not None:
+                for k, sl in enumerate((V1, V2)):
+                    taps["encoder.v_layer.%d#%d" % (i, k)] = box["Y"][sl]
+
         def run_layers(t_range, v_range):
+            """text layers `t_range` and image layers `v_range` (independent stacks): pairs of one text and one image
+            layer in lock-step (grouped GEMM launches), the rest of the longer stack alone"""
             tsv, vsv = [], []
-
-            def text():
-                for i in t_range:
-                    box["X"], sv = self.layer_fwd("encoder.layer.%d" % i, box["X"], segs_x, False)
+            t_list, v_list = list(t_range), list(v_range)
+            for k in range(max(len(t_list), len(v_list))):
+                items = []
+                if k < len(t_list):
+                    items.append(("encoder.layer.%d" % t_list[k], box["X"], segs_x, False, None))
+                if k < len(v_list):
+                    items.append(("encoder.v_layer.%d" % v_list[k], box["Y"], segs_y, True, None))
+                res = self.layers_fwd_m(items)
+                j = 0
+                if k < len(t_list):
+                    box["X"], sv = res[j]
                     tsv.append(sv)
-                    if taps is not None:
-                        # call order of the shared module over the three passes (`:1686-1750`): title (t<->v), PV
-                        # (pv<->v), then the two-text pass — title before PV inside its loop (`:1552-1576`), PV
-                        # before title in the closing loops (`:1655-1672`)
-                        order = (T1, P2, P3, T3) if i >= t_last else (T1, P2, T3, P3)
-                        for k, sl in enumerate(order):
-                            taps["encoder.layer.%d#%d" % (i, k)] = box["X"][sl]
-
-            def image():
-                for i in v_range:
-                    box["Y"], sv = self.layer_fwd("encoder.v_layer.%d" % i, box["Y"], segs_y, True)
+                    tap_text(t_list[k])
+                    j += 1
+                if k < len(v_list):
+                    box["Y"], sv = res[j]
                     vsv.append(sv)
-                    if taps is not None:
-                        for k, sl in enumerate((V1, V2)):
-                            taps["encoder.v_layer.%d#%d" % (i, k)] = box["Y"][sl]
-
-            ops.parallel([text if len(t_range) else None, image if len(v_range) else None])
+                    tap_image(v_list[k])
             stages.append(("tv", tsv, vsv))
 
         for count, (e1, e2) in enumerate(zip(c.v_biattention_id, c.t_biattention_id)):
             run_layers(range(s2, e2), range(s1, e1))
             X, Y = box["X"], box["Y"]
             Xn, Yn = torch.empty_like(X), torch.empty_like(Y)
-            sv_c = [None, None, None]
-
-            def conn_a():
-                sv_c[0] = self.connection_fwd("encoder.c_layer.%d" % count, Y[V1], sgV, X[T1], sgT,
-                                              False, Yn[V1], Xn[T1])[2]
-
-            def conn_b():
-                sv_c[1] = self.connection_fwd("encoder.c_layer_pv_v.%d" % count, Y[V2], sgV, X[P2], sgP,
-                                              False, Yn[V2], Xn[P2])[2]
-
-            def conn_c():
-                sv_c[2] = self.connection_fwd("encoder.c_layer_pv_t.%d" % count, X[P3], sgP, X[T3], sgT,
-                                              True, Xn[P3], Xn[T3])[2]
-
-            ops.parallel([conn_a, conn_b, conn_c])
+            sv_c = self.connections_fwd_m([
+                ("encoder.c_layer.%d" % count, Y[V1], sgV, X[T1], sgT, False, Yn[V1], Xn[T1]),
+                ("encoder.c_layer_pv_v.%d" % count, Y[V2], sgV, X[P2], sgP, False, Yn[V2], Xn[P2]),
+                ("encoder.c_layer_pv_t.%d" % count, X[P3], sgP, X[T3], sgT, True, Xn[P3], Xn[T3])])
             stages.append(("c", sv_c[0], sv_c[1], sv_c[2]))
             if taps is not None:
                 for nm, o0, o1 in (("c_layer", Yn[V1], Xn[T1]), ("c_layer_pv_v", Yn[V2], Xn[P2]),
@@ -657,23 +750,27 @@ class Engine(object):
         box = {"dX": dX, "dY": dY}
         for st in reversed(sv["stages"]):
             if st[0] == "tv":
-                def text(tsv=st[1]):
-                    for s_ in reversed(tsv):
-                        box["dX"] = self.layer_bwd(box["dX"], s_)
-
-                def image(vsv=st[2]):
-                    for s_ in reversed(vsv):
-                        box["dY"] = self.layer_bwd(box["dY"], s_)
-
-                ops.parallel([text if st[1] else None, image if st[2] else None])
-                ready([s_[0] for s_ in st[1]] + [s_[0] for s_ in st[2]])
+                tsv, vsv = st[1], st[2]
+                for k in reversed(range(max(len(tsv), len(vsv)))):
+                    items = []
+                    if k < len(tsv):
+                        items.append((box["dX"], tsv[k]))
+                    if k < len(vsv):
+                        items.append((box["dY"], vsv[k]))
+                    res = self.layers_bwd_m(items)
+                    j = 0
+                    if k < len(tsv):
+                        box["dX"] = res[j]
+                        j += 1
+                    if k < len(vsv):
+                        box["dY"] = res[j]
+                ready([s_[0] for s_ in tsv] + [s_[0] for s_ in vsv])
             else:
                 dX, dY = box["dX"], box["dY"]
                 dXn, dYn = torch.empty_like(dX), torch.empty_like(dY)
-                ops.parallel([
-                    lambda: self.connection_bwd(dY[V1], dX[T1], st[1], dYn[V1], dXn[T1]),
-                    lambda: self.connection_bwd(dY[V2], dX[P2], st[2], dYn[V2], dXn[P2]),
-                    lambda: self.connection_bwd(dX[P3], dX[T3], st[3], dXn[P3], dXn[T3])])
+                self.connections_bwd_m([(dY[V1], dX[T1], st[1], dYn[V1], dXn[T1]),
+                                        (dY[V2], dX[P2], st[2], dYn[V2], dXn[P2]),
+                                        (dX[P3], dX[T3], st[3], dXn[P3], dXn[T3])])
                 box["dX"], box["dY"] = dXn, dYn
                 ready([st[1][0], st[2][0], st[3][0]])
         dX, dY = box["dX"], box["dY"]

@@ -31,6 +31,27 @@ def _isf32(t):
     return 0
 
 
+class _GemmDesc(_c.Structure):
+    """K3MGemmDesc of include/k3m.h"""
+    _fields_ = [("a", _vp), ("lda", _i), ("b", _vp), ("ldb", _i), ("layout", _i), ("M", _i), ("N", _i), ("K", _i),
+                ("out", _vp), ("ldc", _i), ("out_f32", _i), ("accumulate", _i), ("bias", _vp), ("act", _i),
+                ("aux_in", _vp), ("ld_aux_in", _i), ("aux_out", _vp), ("ld_aux_out", _i), ("addend", _vp),
+                ("ld_add", _i), ("addend_f32", _i), ("rng", _vp), ("drop_site", _u), ("drop_p", _f)]
+
+
+class _LnFwdDesc(_c.Structure):
+    """K3MLnFwdDesc of include/k3m.h"""
+    _fields_ = [("x", _vp), ("gamma", _vp), ("beta", _vp), ("y", _vp), ("mean", _vp), ("rstd", _vp), ("M", _i), ("H", _i),
+                ("rng", _vp), ("site", _u), ("drop_p", _f)]
+
+
+class _LnBwdDesc(_c.Structure):
+    """K3MLnBwdDesc of include/k3m.h"""
+    _fields_ = [("dy", _vp), ("x", _vp), ("gamma", _vp), ("mean", _vp), ("rstd", _vp), ("dx", _vp), ("dxm", _vp),
+                ("dgamma", _vp), ("dbeta", _vp), ("dbias", _vp), ("M", _i), ("H", _i), ("rng", _vp), ("site_out", _u),
+                ("p_out", _f), ("site_in", _u), ("p_in", _f)]
+
+
 class CudaOps(object):
     def __init__(self, device=None):
         if not torch.cuda.is_available():
@@ -55,6 +76,14 @@ class CudaOps(object):
         # the dgrad chain is the critical path of backward: its streams outrank the auxiliary (weight-gradient)
         # and optimizer streams, whose kernels then fill the SMs the chain leaves idle instead of delaying it
         self.hi_prio = -1 if os.environ.get("K3M_STREAM_PRIO", "0") != "0" else 0
+        # grouped GEMM launches (k3m_gemm_grouped_bf16); K3M_GEMM_GROUP=0 issues every problem as its own launch
+        self.use_groups = os.environ.get("K3M_GEMM_GROUP", "1") != "0"
+        self.use_parallel = os.environ.get("K3M_PARALLEL", "1") != "0"      # concurrent streams for independent launches
+        # k3m_adamw_bg (a variant sized to co-reside with a GEMM CTA) measured SLOWER: GEMM + AdamW on two streams took
+        # 3.6 ms together against 2.6 + 0.8 ms alone (tools/micro_overlap.py, profiles/r02_overlap_micro.txt) — a
+        # co-resident CTA starves next to 18 spinning GEMM warps and its HBM traffic slows the GEMM's L2 fills.  Off.
+        self.use_adamw_bg = os.environ.get("K3M_ADAMW_BG", "0") != "0"
+        self.skip = frozenset(x for x in os.environ.get("K3M_BENCH_SKIP", "").split(",") if x)
 
     def parallel(self, fns):
         """Run independent closures on concurrent CUDA streams (fork after the current stream, join back
@@ -63,7 +92,7 @@ class CudaOps(object):
         under CUDA-graph capture (the side streams join the capture).  Closures run in list order on the
         host, so dropout-site numbering is the same as in a sequential run."""
         fns = [f for f in fns if f is not None]
-        if len(fns) <= 1 or self.timing is not None:
+        if len(fns) <= 1 or self.timing is not None or not self.use_parallel:
             for f in fns:
                 f()
             return
@@ -125,6 +154,8 @@ class CudaOps(object):
         return _vp(torch.cuda.current_stream().cuda_stream)
 
     def _call(self, name, *args):
+        if self.skip and name in self.skip:      # measurement aid only (bench.py --skip): exposed time of a kernel family
+            return
         self.launches += 1
         if self.record is not None and name in self.record:
             self.record[name].append((args, self._bytes))
@@ -183,6 +214,64 @@ class CudaOps(object):
                    r, s, p, self._st())
         return out
 
+    def gemm_group(self, calls):
+        """Several independent GEMMs of ONE layout as one persistent launch (`k3m_gemm_grouped_bf16`): `calls` is a
+        list of dicts with the keyword arguments of `gemm` (a, b, layout, out, out_dtype, bias, act, aux_in, aux_out,
+        addend, drop, rng, accumulate).  Returns the list of outputs.  Small problems (the three connection layers
+        of a stage, a text and an image layer, a stage's weight gradients) then fill whole waves of CTA pairs
+        together instead of each paying its own launch latency with half the SMs idle."""
+        n = len(calls)
+        if n == 1 or not self.use_groups:
+            return [self.gemm(**c) for c in calls]
+        outs = []
+        for i0 in range(0, n, 8):
+            chunk = calls[i0:i0 + 8]
+            if len(chunk) == 1:
+                outs.append(self.gemm(**chunk[0]))
+                continue
+            arr = (_GemmDesc * len(chunk))()
+            work, tags = 0.0, []
+            for d, c in zip(arr, chunk):
+                a, b, layout = c["a"], c["b"], c["layout"]
+                assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and layout == chunk[0]["layout"]
+                if layout == "nt":
+                    (M, K), N = a.shape, b.shape[0]
+                    assert b.shape[1] == K
+                elif layout == "nn":
+                    (M, K), N = a.shape, b.shape[1]
+                    assert b.shape[0] == K
+                else:
+                    (K, M), N = a.shape, b.shape[1]
+                    assert b.shape[0] == K
+                out, accumulate = c.get("out"), bool(c.get("accumulate", False))
+                if out is None:
+                    out = torch.empty(M, N, dtype=c.get("out_dtype") or self.adt, device=a.device)
+                    accumulate = False
+                assert tuple(out.shape) == (M, N)
+                bias, aux_in, aux_out, addend = c.get("bias"), c.get("aux_in"), c.get("aux_out"), c.get("addend")
+                drop, rng = c.get("drop"), c.get("rng")
+                d.a, d.lda, d.b, d.ldb, d.layout = a.data_ptr(), _ld(a), b.data_ptr(), _ld(b), _LAYOUT[layout]
+                d.M, d.N, d.K = M, N, K
+                d.out, d.ldc, d.out_f32, d.accumulate = out.data_ptr(), _ld(out), _isf32(out), 1 if accumulate else 0
+                d.bias = bias.data_ptr() if bias is not None else None
+                d.act = c.get("act", ACT_NONE)
+                d.aux_in, d.ld_aux_in = (aux_in.data_ptr(), _ld(aux_in)) if aux_in is not None else (None, 0)
+                d.aux_out, d.ld_aux_out = (aux_out.data_ptr(), _ld(aux_out)) if aux_out is not None else (None, 0)
+                d.addend, d.ld_add = (addend.data_ptr(), _ld(addend)) if addend is not None else (None, 0)
+                d.addend_f32 = _isf32(addend) if addend is not None else 0
+                if drop is not None:
+                    d.rng, d.drop_site, d.drop_p = rng.data_ptr(), drop[1], drop[0]
+                else:
+                    d.rng, d.drop_site, d.drop_p = None, 0, 0.0
+                work += 2.0 * M * N * K
+                tags.append("%dx%dx%d" % (M, N, K))
+                outs.append(out)
+            self._work = work
+            if self.timing is not None:
+                self._tag = " %s group[%s]" % (chunk[0]["layout"], " ".join(tags))
+            self._call("k3m_gemm_grouped_bf16", arr, _i(len(chunk)), self._st())
+        return outs
+
     def gemm_last_variant(self):
         return self.lib.k3m_gemm_last_variant().decode()
 
@@ -207,6 +296,62 @@ class CudaOps(object):
         self._call("k3m_ln_fwd", _p(x), _p(gamma), _p(beta), _p(out), _p(mean), _p(rstd), _i(M), _i(H),
                    _f(eps), r, s, p, self._st())
         return out, mean, rstd
+
+    def ln_fwd_group(self, items, eps=1e-12):
+        """Independent LayerNorms as one launch (`k3m_ln_fwd_grouped`): items = dicts with the arguments of `ln_fwd`
+        (x, gamma, beta, out, drop, rng).  -> [(y, mean, rstd)]."""
+        if len(items) == 1 or not self.use_groups:
+            return [self.ln_fwd(eps=eps, **it) for it in items]
+        res, nbytes = [], 0.0
+        arr = (_LnFwdDesc * len(items))()
+        for d, it in zip(arr, items):
+            x, out, drop = it["x"], it.get("out"), it.get("drop")
+            M, H = x.shape
+            assert x.is_contiguous()
+            if out is None:
+                out = torch.empty(M, H, dtype=self.adt, device=x.device)
+            assert out.is_contiguous()
+            mean = torch.empty(M, dtype=torch.float32, device=x.device)
+            rstd = torch.empty(M, dtype=torch.float32, device=x.device)
+            d.x, d.gamma, d.beta, d.y = x.data_ptr(), it["gamma"].data_ptr(), it["beta"].data_ptr(), out.data_ptr()
+            d.mean, d.rstd, d.M, d.H = mean.data_ptr(), rstd.data_ptr(), M, H
+            d.rng, d.site, d.drop_p = (it["rng"].data_ptr(), drop[1], drop[0]) if drop is not None else (None, 0, 0.0)
+            nbytes += self._nb(x, out, mean, rstd, it["gamma"], it["beta"])
+            res.append((out, mean, rstd))
+        if self.timing is not None:
+            self._bytes = nbytes
+        self._call("k3m_ln_fwd_grouped", arr, _i(len(items)), _f(eps), self._st())
+        return res
+
+    def ln_bwd_group(self, items):
+        """Independent LayerNorm backwards as one launch: items = dicts with the arguments of `ln_bwd`.
+        -> [(dx, dxm or dx)]."""
+        if len(items) == 1 or not self.use_groups:
+            return [self.ln_bwd(**it) for it in items]
+        res, nbytes = [], 0.0
+        arr = (_LnBwdDesc * len(items))()
+        for d, it in zip(arr, items):
+            dy, x = it["dy"], it["x"]
+            M, H = x.shape
+            assert dy.is_contiguous() and x.is_contiguous()
+            drop_out, drop_in, dbias = it.get("drop_out"), it.get("drop_in"), it.get("dbias")
+            dx = torch.empty(M, H, dtype=self.adt, device=x.device)
+            dxm = torch.empty(M, H, dtype=self.adt, device=x.device) if drop_in is not None else None
+            po = drop_out if drop_out is not None else (0.0, 0)
+            pi = drop_in if drop_in is not None else (0.0, 0)
+            d.dy, d.x, d.gamma, d.mean, d.rstd = dy.data_ptr(), x.data_ptr(), it["gamma"].data_ptr(), it["mean"].data_ptr(), it["rstd"].data_ptr()
+            d.dx, d.dxm = dx.data_ptr(), (dxm.data_ptr() if dxm is not None else None)
+            d.dgamma, d.dbeta = it["dgamma"].data_ptr(), it["dbeta"].data_ptr()
+            d.dbias = dbias.data_ptr() if dbias is not None else None
+            d.M, d.H = M, H
+            d.rng = it["rng"].data_ptr() if it.get("rng") is not None else None
+            d.site_out, d.p_out, d.site_in, d.p_in = po[1], po[0], pi[1], pi[0]
+            nbytes += self._nb(dy, x, dx, dxm, it["mean"], it["rstd"], it["gamma"])
+            res.append((dx, dxm if dxm is not None else dx))
+        if self.timing is not None:
+            self._bytes = nbytes
+        self._call("k3m_ln_bwd_grouped", arr, _i(len(items)), self._st())
+        return res
 
     def ln_bwd(self, dy, x, gamma, mean, rstd, dgamma, dbeta, drop_out=None, drop_in=None, rng=None,
                dbias=None, want_masked=False):
@@ -507,8 +652,9 @@ class CudaOps(object):
         return out
 
     # ---- optimizer -------------------------------------------------------------------------
-    def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True):
+    def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True, background=False):
+        """`background`: the variant sized to co-reside with a running GEMM (buckets stepped under backward)."""
         if self.timing is not None:      # read p, g, m, v; write p, m, v, bf16 shadow, zeroed g: 34 B per parameter
             self._bytes = p32.numel() * (34.0 if zero_grad else 30.0)
-        self._call("k3m_adamw", _p(p32), _p(g32), _p(m), _p(v), _p(p_act), _p(hyper), _ll(p32.numel()),
+        self._call("k3m_adamw_bg" if (background and self.use_adamw_bg) else "k3m_adamw", _p(p32), _p(g32), _p(m), _p(v), _p(p_act), _p(hyper), _ll(p32.numel()),
                    _i(1 if zero_grad else 0), self._st())

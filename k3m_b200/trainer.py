@@ -231,7 +231,7 @@ class PretrainStep(object):
             self._stage_lo[key] = min(self._stage_lo.get(key, L.decay_end), off)
         return out
 
-    def _bucket_step(self, bi):
+    def _bucket_step(self, bi, background=False):
         """All-reduce (world > 1) then AdamW of bucket `bi`, on the side stream when there is one.  A
         bucket's parameters are no longer read by backward once its gradients are final (`_on_ready`), so
         updating them under the rest of backward is safe; AdamW is HBM-bound and the GEMMs it runs
@@ -245,7 +245,7 @@ class PretrainStep(object):
                 torch.distributed.all_reduce(t, group=self.group)
             # gradients are summed over ranks; hyper[:, 6] = 1/world turns that into DDP's mean
             self.ops.adamw(self.p32[lo:hi], t, self.m[lo:hi], self.v[lo:hi], self.w16[lo:hi], self.hyper[gi],
-                           zero_grad=True)
+                           zero_grad=True, background=background)
 
         if self._comm_stream is None:
             work()
@@ -265,7 +265,8 @@ class PretrainStep(object):
         for k in keys:
             self._ready_lo = min(self._ready_lo, self._stage_lo.get(k, self._ready_lo))
         while self._next_bucket < len(self._buckets) - 1 and self._buckets[self._next_bucket][0] >= self._ready_lo:
-            self._bucket_step(self._next_bucket)
+            # backward is still running: the update shares the SMs with its GEMMs (k3m_adamw_bg)
+            self._bucket_step(self._next_bucket, background=True)
             self._next_bucket += 1
 
     def _finish_buckets(self):

@@ -145,6 +145,10 @@ class RefOps(object):
             out.copy_(v)
         return out
 
+    def gemm_group(self, calls):
+        """independent problems of one layout (one grouped launch in the CUDA table): one after the other here"""
+        return [self.gemm(**c) for c in calls]
+
     def colsum(self, x, out):
         """out[n] += sum_m x[m, n]  (fp32 accumulate; bias gradients)."""
         out.add_(x.float().sum(0))
@@ -162,6 +166,12 @@ class RefOps(object):
             out = torch.empty(x.shape, dtype=self.adt, device=x.device)
         out.copy_(y)
         return out, mean, rstd
+
+    def ln_fwd_group(self, items, eps=1e-12):
+        return [self.ln_fwd(eps=eps, **it) for it in items]
+
+    def ln_bwd_group(self, items):
+        return [self.ln_bwd(**it) for it in items]
 
     def ln_bwd(self, dy, x, gamma, mean, rstd, dgamma, dbeta, drop_out=None, drop_in=None,
                rng=None, dbias=None, want_masked=False):
@@ -528,7 +538,7 @@ class RefOps(object):
     def plan_to_device(self, plan, device):
         return {k: torch.from_numpy(v).to(device) for k, v in plan.items()}
 
-    def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True):
+    def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True, background=False):
         """torch.optim.AdamW step on a flat range.  hyper fp32 [8] = (lr, beta1, beta2, eps, wd,
         step, grad_scale, -).  Writes the act-dtype shadow copy and (optionally) zeroes the grad."""
         lr, b1, b2, eps, wd, step, grad_scale = [float(x) for x in hyper[:7]]

@@ -202,6 +202,91 @@ def test_gemm_bench_shapes_weight_gradients(ops, ref, name, M, N, K):
     close(got, want, 2e-4, 2e-4 * math.sqrt(K) * 0.05 * 0.05 * 8, name)
 
 
+# ---- grouped launches (k3m_gemm_grouped_bf16) ---------------------------------------------------------------
+def _group_case(kind, M, N, K, seed):
+    """one problem of a group with epilogue `kind`; returns (kwargs for ops.gemm / gemm_group, extra outputs)"""
+    s = 1.0 / math.sqrt(K)
+    layout = {"bias": "nt", "bias_drop_add": "nt", "bias_gelu": "nt", "dgelu": "nn", "add": "nn", "acc": "tn"}[kind]
+    if layout == "nt":
+        a, b = rnd(M, K, seed=seed), rnd(N, K, seed=seed + 1, scale=s)
+    elif layout == "nn":
+        a, b = rnd(M, K, seed=seed), rnd(K, N, seed=seed + 1, scale=s)
+    else:
+        a, b = rnd(K, M, seed=seed, scale=0.05), rnd(K, N, seed=seed + 1, scale=0.05)
+    kw = dict(a=a, b=b, layout=layout)
+    if kind.startswith("bias"):
+        kw["bias"] = rnd(N, seed=seed + 2)
+    if kind == "bias_drop_add":
+        kw.update(drop=(0.1, 40 + seed), rng=rng_state(), addend=rnd(M, N, seed=seed + 3))
+    if kind == "add":
+        kw.update(addend=rnd(M, N, seed=seed + 3))
+    if kind == "dgelu":
+        kw.update(act=2, aux_in=rnd(M, N, seed=seed + 4, scale=1.5))
+    if kind == "bias_gelu":
+        kw.update(act=1)
+    return kw
+
+
+GROUPS = {
+    # the six problems of a connection stage (three connection layers x two streams), B = 64
+    "conn_qkv": [("bias", 2368, 3072, 1024), ("bias", 2304, 3072, 768), ("bias", 2368, 3072, 1024),
+                 ("bias", 2304, 3072, 768), ("bias", 2304, 2304, 768), ("bias", 2304, 2304, 768)],
+    "conn_out": [("bias_drop_add", 2368, 1024, 1024), ("bias_drop_add", 2304, 768, 1024), ("bias_drop_add", 2368, 1024, 1024),
+                 ("bias_drop_add", 2304, 768, 1024), ("bias_drop_add", 2304, 768, 768), ("bias_drop_add", 2304, 768, 768)],
+    "conn_ffn_up": [("bias_gelu", 2368, 1024, 1024), ("bias_gelu", 2304, 3072, 768), ("bias_gelu", 2368, 1024, 1024),
+                    ("bias_gelu", 2304, 3072, 768), ("bias_gelu", 2304, 3072, 768), ("bias_gelu", 2304, 3072, 768)],
+    "conn_dgrad_mixed": [("dgelu", 2368, 1024, 1024), ("dgelu", 2304, 3072, 768), ("add", 2304, 768, 3072),
+                         ("add", 2368, 1024, 3072)],
+    "conn_wgrad": [("acc", 1024, 1024, 2368), ("acc", 3072, 768, 2304), ("acc", 768, 3072, 2304), ("acc", 768, 768, 2304),
+                   ("acc", 1024, 1024, 2368), ("acc", 768, 1024, 2304)],
+    # a text and an image layer in lock-step
+    "text_image": [("bias_drop_add", 9216, 768, 3072), ("bias_drop_add", 4736, 1024, 1024)],
+    # small problems (tiny configs): 128 x 128 single-CTA tiles, ragged edges
+    "small": [("bias_gelu", 100, 256, 128), ("bias_gelu", 48, 128, 256), ("bias_gelu", 300, 776, 264)],
+    "small_wgrad": [("acc", 256, 128, 100), ("acc", 128, 256, 48), ("acc", 384, 384, 300)],
+    # nine problems: more than one launch's worth (8 per launch)
+    "nine": [("bias", 256, 256, 128)] * 9,
+}
+
+
+@pytest.mark.parametrize("name", list(GROUPS))
+def test_gemm_grouped_matches_single_problem_restatement(ops, ref, name):
+    probs = [_group_case(kind, M, N, K, 10 * i) for i, (kind, M, N, K) in enumerate(GROUPS[name])]
+    calls, wants, auxs = [], [], []
+    for kw in probs:
+        c = dict(kw)
+        M = kw["a"].shape[1] if kw["layout"] == "tn" else kw["a"].shape[0]
+        N = kw["b"].shape[0] if kw["layout"] == "nt" else kw["b"].shape[1]
+        r = dict(kw)
+        aux_g = aux_r = None
+        if kw.get("act") == 1:
+            aux_g, aux_r = torch.zeros(M, N, dtype=BF, device=DEV), torch.zeros(M, N, dtype=F32, device=DEV)
+            c["aux_out"], r["aux_out"] = aux_g, aux_r
+        if kw["layout"] == "tn":
+            base = rnd(M, N, seed=99, dtype=F32)
+            c.update(out=base.clone(), accumulate=True)
+            r.update(out=base.clone(), accumulate=True)
+            wants.append(ref.gemm(**r))
+        else:
+            wants.append(ref.gemm(out_dtype=F32, **r))
+        calls.append(c)
+        auxs.append((aux_g, aux_r))
+    outs = ops.gemm_group(calls)
+    v = ops.gemm_last_variant()
+    print("group %s: %s" % (name, v))
+    big = all(M >= 256 and N >= 256 for _, M, N, _ in GROUPS[name]) and name != "nine"
+    assert ("ctas=2" in v) == big, v
+    assert "group=%d" % (len(probs) if len(probs) <= 8 else len(probs) - 8) in v or len(probs) > 8, v
+    for i, (got, want, (aux_g, aux_r)) in enumerate(zip(outs, wants, auxs)):
+        kind, M, N, K = GROUPS[name][i]
+        if kind == "acc":
+            close(got, want, 2e-4, 2e-4 * math.sqrt(K) * 0.05 * 0.05 * 8, "%s[%d]" % (name, i))
+        else:
+            close_bf16(got, want, "%s[%d] %s" % (name, i, kind), atol=4e-3)
+        if aux_g is not None:
+            close_bf16(aux_g, aux_r, "%s[%d] aux_out" % (name, i), atol=4e-3)
+
+
 def test_gemm_strided_views(ops, ref):
     # operands / outputs that are column slices of wider buffers (qkv, logits[:, :V])
     M, K, N = 192, 256, 200
@@ -261,6 +346,42 @@ def test_ln_bwd(ops, ref, M, H, mode):
     close(dg, dgr, 2e-3, 2e-3 * s, "dgamma")
     close(db, dbr, 2e-3, 2e-3 * s, "dbeta")
     close(dbias, dbiasr, 2e-2, 2e-2 * s, "dbias")   # sums of bf16-rounded dx in the ref vs fp32 in the kernel
+
+
+def test_ln_grouped_mixed_hidden_sizes(ops, ref):
+    """k3m_ln_fwd_grouped / k3m_ln_bwd_grouped: the six LayerNorms of a connection stage (hidden 1024 and 768, 2368 /
+    2304 rows) in one launch each, against the single-problem restatement."""
+    shapes = [(2368, 1024), (2304, 768), (2368, 1024), (2304, 768), (2304, 768), (37, 768)]
+    r = rng_state()
+    items, items_r = [], []
+    for i, (M, H) in enumerate(shapes):
+        it = dict(x=rnd(M, H, seed=i, scale=2.0), gamma=rnd(H, seed=50 + i), beta=rnd(H, seed=60 + i))
+        if i == 1:
+            it.update(drop=(0.1, 7), rng=r)
+        items.append(it)
+    got = ops.ln_fwd_group(items)
+    want = [ref.ln_fwd(**it) for it in items]
+    for (y, mean, rstd), (yr, mr, rr) in zip(got, want):
+        close(mean, mr, 1e-5, 1e-5, "mean")
+        close(rstd, rr, 1e-4, 1e-6, "rstd")
+        close_bf16(y, yr, "ln y", atol=1e-3)
+    bw, res = [], []
+    for i, (M, H) in enumerate(shapes):
+        bw.append(dict(dy=rnd(M, H, seed=70 + i), x=items[i]["x"], gamma=items[i]["gamma"], mean=want[i][1], rstd=want[i][2],
+                       rng=r, drop_in=(0.1, 9 + i) if i % 2 == 0 else None))
+    for o, grouped in ((ops, True), (ref, False)):
+        accs = [(torch.zeros(H, dtype=F32, device=DEV) + 1.0, torch.zeros(H, dtype=F32, device=DEV) - 2.0,
+                 torch.zeros(H, dtype=F32, device=DEV) + 0.5) for _, H in shapes]
+        its = [dict(it, dgamma=a[0], dbeta=a[1], dbias=a[2]) for it, a in zip(bw, accs)]
+        outs = o.ln_bwd_group(its) if grouped else [o.ln_bwd(**it) for it in its]
+        res.append((outs, accs))
+    for i, (M, H) in enumerate(shapes):
+        (dx, dxm), (dxr, dxmr) = res[0][0][i], res[1][0][i]
+        close_bf16(dx, dxr, "dx[%d]" % i, atol=2e-3, ulps=3)
+        close_bf16(dxm, dxmr, "dxm[%d]" % i, atol=2e-3, ulps=3)
+        sc = math.sqrt(M)
+        for a, b, n, t in zip(res[0][1][i], res[1][1][i], ("dgamma", "dbeta", "dbias"), (2e-3, 2e-3, 2e-2)):
+            close(a, b, t, t * sc, "%s[%d]" % (n, i))
 
 
 def test_colsum_cast_axpy_lincomb_scale_mask(ops, ref):
