@@ -67,6 +67,10 @@ typedef struct K3MGemmDesc {
 } K3MGemmDesc;
 int k3m_gemm_grouped_bf16(const K3MGemmDesc* problems, int n, void* stream);
 
+/* Persistent GEMM grids use at most `n` SMs (0 = all): a data-parallel step leaves a few SMs to the collective's
+ * CTAs, which otherwise wait for an SM that a persistent GEMM CTA holds.                                      */
+void k3m_gemm_set_sm_limit(int n);
+
 /* Debug aid: a description of the kernel variant the calling thread's last GEMM call dispatched
  * ("bn=256 ctas=2 ew=4 ... epi=F_ADD ...").  Parity tests assert that they ran the benchmark's variant. */
 const char* k3m_gemm_last_variant(void);
@@ -193,6 +197,20 @@ int k3m_dropout(const void* x, int ldx, int x_f32, void* y, int ldy, int y_f32, 
  * {lr, beta1, beta2, eps, weight_decay, step, grad_scale, -}.                                     */
 int k3m_adamw(float* p32, float* g32, float* m, float* v, void* p16, const float* hyper, long long n,
               int zero_grad, void* stream);
+/* The same update with the gradient read from a bf16 buffer (the all-reduced send buffer of a data-parallel step,
+ * pretrain.py:166 DDP); g32 is the fp32 arena range that is zeroed for the next step.                        */
+int k3m_adamw_g16(float* p32, const void* g16, float* g32, float* m, float* v, void* p16, const float* hyper,
+                  long long n, int zero_grad, void* stream);
+/* Data parallel (pretrain.py:166 DDP all-reduce + :919-924 AdamW), fused over NVLink peer memory: every rank owns
+ * 1/world of a gradient bucket.  k3m_cast_zero: fp32 gradient range -> this rank's bf16 send arena, zeroing the
+ * fp32 range.  k3m_adamw_dp: for the shard [offset, offset + n) of the arena: sum the bf16 gradients of all ranks
+ * (peer-to-peer loads from g16_peers[r], host array of `world` device pointers to each rank's send arena), AdamW on
+ * the local fp32 master / moments (p32, m, v point AT the shard), store the new bf16 weights into every rank's
+ * weight arena (w16_peers[r]).  The caller synchronises the ranks before (casts visible) and after (weights
+ * visible).                                                                                                   */
+int k3m_cast_zero(float* g32, void* out16, long long n, void* stream);
+int k3m_adamw_dp(float* p32, float* m, float* v, const float* hyper, const void* const* g16_peers,
+                 void* const* w16_peers, int world, long long offset, long long n, void* stream);
 /* The same update sized to co-reside with a running GEMM (two 128-thread, <= 32-register CTAs per SM, no shared
  * memory): used for the gradient buckets that become final while backward is still running.               */
 int k3m_adamw_bg(float* p32, float* g32, float* m, float* v, void* p16, const float* hyper, long long n,

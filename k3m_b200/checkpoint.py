@@ -113,7 +113,10 @@ def checkpoint_dict(step):
 
 
 def save_checkpoint(step, tar_path, bin_path=None):
-    """Writes the reference's `.tar` checkpoint (and the weights-only `.bin` when asked)."""
+    """Writes the reference's `.tar` checkpoint (and the weights-only `.bin` when asked).  In fused data-parallel
+    mode this is a collective (every rank calls it: the owners of the optimizer shards broadcast them first)."""
+    if hasattr(step, "sync_shards"):
+        step.sync_shards(moments=True)
     ck = checkpoint_dict(step)
     torch.save(ck, tar_path)
     if bin_path is not None:

@@ -884,6 +884,7 @@ bool get_map(const void* ptr, int inner, int outer, int ld, int box_inner, int b
   return true;
 }
 
+int g_sm_limit = 0;      // k3m_gemm_set_sm_limit
 int num_sms() {
   static int n = 0;
   if (n == 0) {
@@ -891,7 +892,7 @@ int num_sms() {
     cudaGetDevice(&dev);
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
   }
-  return n;
+  return (g_sm_limit > 1 && g_sm_limit < n) ? (g_sm_limit & ~1) : n;
 }
 
 template <int BN, int STAGES, int EW, bool A_MN, bool B_MN, int CTAS, int MAXP>
@@ -1082,6 +1083,7 @@ const char* fast_name(int f) {
 }  // namespace
 
 extern "C" const char* k3m_gemm_last_variant(void) { return g_variant; }
+extern "C" void k3m_gemm_set_sm_limit(int n) { g_sm_limit = n; }
 
 extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int layout, int M, int N, int K,
                              void* out, int ldc, int out_f32, int accumulate, const void* bias, int act,

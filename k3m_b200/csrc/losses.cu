@@ -361,14 +361,25 @@ __global__ void __launch_bounds__(128) lpm_kernel(const float* __restrict__ c_fi
 // ---- multi-tensor AdamW over a flat arena range (torch.optim.AdamW semantics, pretrain.py:919-924) ----
 // hyper (device fp32[8]) = lr, beta1, beta2, eps, weight_decay, step, grad_scale, unused.  Reading the
 // hyper-parameters from device memory keeps the kernel node valid across CUDA-graph replays.
+// G16: the (all-reduced) gradient is read from a bf16 buffer `g16` instead of the fp32 arena `g`, which is still zeroed.
+template <bool G16>
 __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
                                                     float* __restrict__ v, bf16* __restrict__ p16,
-                                                    const float* __restrict__ hyper, size_t n4, int zero_grad) {
+                                                    const float* __restrict__ hyper, size_t n4, int zero_grad,
+                                                    const bf16* __restrict__ g16) {
   const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], step = hyper[5], gs = hyper[6];
   const float bc1 = 1.0f - powf(b1, step), bc2 = 1.0f - powf(b2, step);
   const float step_size = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2), decay = 1.0f - lr * wd;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
-    float4 pp = reinterpret_cast<float4*>(p)[i], gg = reinterpret_cast<float4*>(g)[i];
+    float4 pp = reinterpret_cast<float4*>(p)[i], gg;
+    if (G16) {
+      const uint2 gu = reinterpret_cast<const uint2*>(g16)[i];
+      const float2 ga2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gu.x));
+      const float2 gb2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gu.y));
+      gg = make_float4(ga2.x, ga2.y, gb2.x, gb2.y);
+    } else {
+      gg = reinterpret_cast<float4*>(g)[i];
+    }
     float4 mm = reinterpret_cast<float4*>(m)[i], vv = reinterpret_cast<float4*>(v)[i];
     float* pa = &pp.x; float* ga = &gg.x; float* ma = &mm.x; float* va = &vv.x;
 #pragma unroll
@@ -429,7 +440,108 @@ __global__ void __launch_bounds__(256, 6) adamw_bg_kernel(float* __restrict__ p,
   }
 }
 
+__device__ __forceinline__ uint4 pack8_bf16(const float v[8]) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+  return u;
+}
+
+// ---- data parallel: gradient reduce-scatter + AdamW + weight all-gather as ONE kernel over NVLink peer memory ----
+// Every rank owns 1/world of each gradient bucket (ZeRO-1 style).  For its shard the kernel
+//   * loads the bf16 gradient of every rank straight from that rank's HBM (peer-to-peer loads over NVLink /
+//     NVSwitch; `g[r]` = base of rank r's symmetric bf16 gradient arena) and sums in fp32,
+//   * applies torch.optim.AdamW's update to its fp32 master / moments (local HBM, 1/world of the optimizer traffic
+//     of a replicated update),
+//   * stores the new bf16 weight into EVERY rank's weight arena (`w[r]`, peer-to-peer stores),
+// which replaces all-reduce + a replicated AdamW: the same NVLink bytes as a ring all-reduce, no staging, no
+// NCCL kernel waiting for an SM, and 8x less optimizer traffic at 8 GPUs.  The caller brackets it with barriers
+// (all ranks' gradient casts are visible before / all weight stores before the next forward).
+struct DpPeers {
+  const bf16* g[16];
+  bf16* w[16];
+  int world;
+};
+__global__ void __launch_bounds__(256) adamw_dp_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
+                                                       const float* __restrict__ hyper, const __grid_constant__ DpPeers peers,
+                                                       size_t offset, size_t n8) {
+  const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], step = hyper[5], gs = hyper[6];
+  const float bc1 = 1.0f - powf(b1, step), bc2 = 1.0f - powf(b2, step);
+  const float step_size = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2), decay = 1.0f - lr * wd;
+  const int world = peers.world;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t e = offset + i * 8;                  // element index inside the arena
+    float g[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = 0.f;
+    for (int r = 0; r < world; ++r) {
+      float t[8];
+      ld8(peers.g[r] + e, t);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] += t[k];
+    }
+    float pa[8], ma[8], va[8];
+    ld8(p + i * 8, pa);
+    ld8(m + i * 8, ma);
+    ld8(v + i * 8, va);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float gr = g[k] * gs;
+      pa[k] *= decay;
+      ma[k] = b1 * ma[k] + (1.0f - b1) * gr;
+      va[k] = b2 * va[k] + (1.0f - b2) * gr * gr;
+      pa[k] -= step_size * ma[k] / (sqrtf(va[k]) * inv_sqrt_bc2 + eps);
+    }
+    st8(p + i * 8, pa);
+    st8(m + i * 8, ma);
+    st8(v + i * 8, va);
+    const uint4 wv = pack8_bf16(pa);
+    for (int r = 0; r < world; ++r) *reinterpret_cast<uint4*>(peers.w[r] + e) = wv;
+  }
+}
+
+// gradient bucket fp32 -> bf16 send buffer, zeroing the fp32 arena for the next step in the same pass
+__global__ void __launch_bounds__(256) cast_zero_kernel(float* __restrict__ g, bf16* __restrict__ out, size_t n8) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    float t[8];
+    ld8(g + i * 8, t);
+    st8(out + i * 8, t);
+    reinterpret_cast<float4*>(g + i * 8)[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    reinterpret_cast<float4*>(g + i * 8)[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
 }  // namespace
+
+extern "C" int k3m_cast_zero(float* g32, void* out16, long long n, void* stream) {
+  K3M_REQUIRE(n > 0 && n % 8 == 0 && (((uintptr_t)g32) & 31) == 0 && (((uintptr_t)out16) & 15) == 0,
+              "cast_zero: range must be a multiple of 8 elements, 32-byte aligned");
+  const size_t n8 = (size_t)n / 8;
+  size_t g = (n8 + 255) / 256;
+  if (g > 148 * 16) g = 148 * 16;
+  cast_zero_kernel<<<(int)g, 256, 0, ST(stream)>>>(g32, (bf16*)out16, n8);
+  return k3m_check_launch("k3m_cast_zero");
+}
+
+extern "C" int k3m_adamw_dp(float* p32, float* m, float* v, const float* hyper, const void* const* g16_peers,
+                            void* const* w16_peers, int world, long long offset, long long n, void* stream) {
+  K3M_REQUIRE(world >= 1 && world <= 16, "adamw_dp: 1..16 ranks (got %d)", world);
+  K3M_REQUIRE(n > 0 && n % 8 == 0 && offset % 8 == 0, "adamw_dp: shard offset / length must be multiples of 8 elements");
+  K3M_REQUIRE((((uintptr_t)p32 | (uintptr_t)m | (uintptr_t)v) & 31) == 0, "adamw_dp: misaligned shard");
+  DpPeers peers;
+  peers.world = world;
+  for (int r = 0; r < 16; ++r) {
+    peers.g[r] = (const bf16*)g16_peers[r < world ? r : 0];
+    peers.w[r] = (bf16*)w16_peers[r < world ? r : 0];
+    K3M_REQUIRE((((uintptr_t)peers.g[r] | (uintptr_t)peers.w[r]) & 15) == 0, "adamw_dp: misaligned peer arena");
+  }
+  const size_t n8 = (size_t)n / 8;
+  size_t g = (n8 + 255) / 256;
+  if (g > 148 * 8) g = 148 * 8;
+  adamw_dp_kernel<<<(int)g, 256, 0, ST(stream)>>>(p32, m, v, hyper, peers, (size_t)offset, n8);
+  return k3m_check_launch("k3m_adamw_dp");
+}
 
 extern "C" int k3m_count_labels(const long long* labels, int n, long long value, int equal, float* out, void* stream) {
   count_kernel<<<1, 1024, 0, ST(stream)>>>(labels, n, value, equal, out);
@@ -561,6 +673,20 @@ extern "C" int k3m_adamw(float* p32, float* g32, float* m, float* v, void* p16, 
   const size_t n4 = (size_t)n / 4;
   size_t g = (n4 + 255) / 256;
   if (g > 148 * 16) g = 148 * 16;
-  adamw_kernel<<<(int)g, 256, 0, ST(stream)>>>(p32, g32, m, v, (bf16*)p16, hyper, n4, zero_grad);
+  adamw_kernel<false><<<(int)g, 256, 0, ST(stream)>>>(p32, g32, m, v, (bf16*)p16, hyper, n4, zero_grad, nullptr);
   return k3m_check_launch("k3m_adamw");
+}
+
+// gradient in bf16 (`g16`, e.g. the all-reduced send buffer of a data-parallel step); `g32` is the fp32 arena
+// range to zero for the next step
+extern "C" int k3m_adamw_g16(float* p32, const void* g16, float* g32, float* m, float* v, void* p16, const float* hyper,
+                             long long n, int zero_grad, void* stream) {
+  K3M_REQUIRE(n % 4 == 0, "adamw: range length must be a multiple of 4");
+  K3M_REQUIRE((((uintptr_t)p32 | (uintptr_t)g32 | (uintptr_t)m | (uintptr_t)v) & 15) == 0 && (((uintptr_t)p16 | (uintptr_t)g16) & 7) == 0,
+              "adamw: misaligned range");
+  const size_t n4 = (size_t)n / 4;
+  size_t g = (n4 + 255) / 256;
+  if (g > 148 * 16) g = 148 * 16;
+  adamw_kernel<true><<<(int)g, 256, 0, ST(stream)>>>(p32, g32, m, v, (bf16*)p16, hyper, n4, zero_grad, (const bf16*)g16);
+  return k3m_check_launch("k3m_adamw_g16");
 }

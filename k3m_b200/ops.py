@@ -652,9 +652,33 @@ class CudaOps(object):
         return out
 
     # ---- optimizer -------------------------------------------------------------------------
-    def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True, background=False):
-        """`background`: the variant sized to co-reside with a running GEMM (buckets stepped under backward)."""
+    def cast_zero(self, g32, out16):
+        """fp32 gradient range -> bf16 send buffer, zeroing the fp32 range (data-parallel step)"""
+        assert g32.dtype == torch.float32 and out16.dtype == torch.bfloat16 and g32.numel() == out16.numel()
+        self._call("k3m_cast_zero", _p(g32), _p(out16), _ll(g32.numel()), self._st())
+
+    def adamw_dp(self, p32, m, v, hyper, g_ptrs, w_ptrs, offset):
+        """Gradient reduce-scatter + AdamW + weight all-gather over NVLink peer memory for the shard
+        [offset, offset + p32.numel()) of the arena; g_ptrs / w_ptrs: every rank's bf16 gradient / weight arena base."""
+        world = len(g_ptrs)
+        ga = (_vp * world)(*[int(x) for x in g_ptrs])
+        wa = (_vp * world)(*[int(x) for x in w_ptrs])
+        if self.timing is not None:
+            self._bytes = p32.numel() * (24.0 + 2.0 * world * 2)
+        self._call("k3m_adamw_dp", _p(p32), _p(m), _p(v), _p(hyper), ga, wa, _i(world), _ll(int(offset)),
+                   _ll(p32.numel()), self._st())
+
+    def gemm_set_sm_limit(self, n):
+        self.lib.k3m_gemm_set_sm_limit(_i(int(n)))
+
+    def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True, background=False, g16=None):
+        """`background`: the variant sized to co-reside with a running GEMM (buckets stepped under backward).
+        `g16`: read the gradient from this bf16 buffer (all-reduced in bf16) instead of `g32`, which is zeroed."""
         if self.timing is not None:      # read p, g, m, v; write p, m, v, bf16 shadow, zeroed g: 34 B per parameter
             self._bytes = p32.numel() * (34.0 if zero_grad else 30.0)
+        if g16 is not None:
+            self._call("k3m_adamw_g16", _p(p32), _p(g16), _p(g32), _p(m), _p(v), _p(p_act), _p(hyper), _ll(p32.numel()),
+                       _i(1 if zero_grad else 0), self._st())
+            return
         self._call("k3m_adamw_bg" if (background and self.use_adamw_bg) else "k3m_adamw", _p(p32), _p(g32), _p(m), _p(v), _p(p_act), _p(hyper), _ll(p32.numel()),
                    _i(1 if zero_grad else 0), self._st())

@@ -57,7 +57,8 @@ class PretrainStep(object):
     def __init__(self, cfg, batch_size, len_t=36, len_v=36, len_pv=36, max_num_pv=8, device="cuda",
                  state_dict=None, init_seed=0, lr=1e-4, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01,
                  warmup_steps=0, total_steps=0, loss_img_weight=1.0, training=True, rng_seed=1234,
-                 use_graph=True, process_group=None, bucket_mb=None, overlap=True, ops=None):
+                 use_graph=True, process_group=None, bucket_mb=None, overlap=True, ops=None, comm_bf16=None,
+                 dp_fused=None):
         """`ops`: kernel table; default (and the only product path) is `CudaOps`, which raises without
         a CUDA device.  Tests inject the fp32 PyTorch restatement to check this host logic on CPU."""
         self.cfg, self.device = cfg, torch.device(device)
@@ -72,14 +73,22 @@ class PretrainStep(object):
         self.m = torch.zeros(L.total, dtype=f32, device=dev)
         self.v = torch.zeros(L.total, dtype=f32, device=dev)
         self.g32 = torch.zeros(L.total, dtype=f32, device=dev)
-        self.w16 = torch.zeros(L.total, dtype=adt, device=dev)
+        self.group = process_group
+        self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
+        self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
+        self.w16 = None
+        self.dp_fused = False
+        if dp_fused is None:
+            dp_fused = os.environ.get("K3M_DP_FUSED", "1") != "0"
+        if self.world > 1 and self._cuda and adt == torch.bfloat16 and dp_fused:
+            self._setup_peer_memory(L, dev)
+        if self.w16 is None:
+            self.w16 = torch.zeros(L.total, dtype=adt, device=dev)
         self.rng = torch.tensor([rng_seed, 0], dtype=torch.int64, device=dev)
         self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
         self.warmup_steps, self.total_steps = warmup_steps, total_steps
         self.loss_weights = (1.0, float(loss_img_weight), 1.0, 1.0)     # `pretrain.py:1055`
         self.global_step = 0
-        self.group = process_group
-        self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.overlap = overlap
         self.engine = Engine(cfg, L, self.ops, self.w16, self.g32, self.rng, adt)
         self.engine.training = training
@@ -125,12 +134,80 @@ class PretrainStep(object):
         prio = -1 if os.environ.get("K3M_COMM_PRIO", "1" if self.world > 1 else "0") != "0" else 0
         self._comm_stream = (torch.cuda.Stream(device=dev, priority=prio)
                              if (self._cuda and (self.world > 1 or self.overlap_opt)) else None)
+        # data parallel: gradients cross NVLink in bf16 (0.92 GB per step instead of 1.85 GB) — each
+        # finished bucket is cast into a persistent bf16 send buffer on the optimizer stream, all-reduced, and AdamW
+        # reads the reduced bf16 gradient (k3m_adamw_g16).  K3M_COMM_BF16=0 reduces the fp32 arena itself.
+        if comm_bf16 is None:
+            comm_bf16 = os.environ.get("K3M_COMM_BF16", "1") != "0"
+        self.comm_bf16 = self.world > 1 and (bool(comm_bf16) or self.dp_fused)
+        self._send16 = (torch.zeros(L.trained_end, dtype=torch.bfloat16, device=dev)
+                        if (self.comm_bf16 and not self.dp_fused) else None)
+        # ... and the persistent GEMM grids leave a few SMs to the collective's CTAs (a GEMM CTA owns its SM: registers
+        # and shared memory), which otherwise wait for a GEMM to retire and then make the next one's CTAs wait
+        self.reserve_sms = int(os.environ.get("K3M_COMM_SMS", "0")) if self.world > 1 else 0
+        if self.reserve_sms > 0 and hasattr(self.ops, "gemm_set_sm_limit"):
+            self.ops.gemm_set_sm_limit(148 - self.reserve_sms)
+        self.comm_events = None       # comm_timing(): [(start event, end event, bytes)] of one instrumented step
         self.use_graph = use_graph and self._cuda
         self.graph = None
         self.launches_per_step = 0
 
     def _input_spec(self):
         return input_spec(self.cfg, self.B, self.Lt, self.Lv1, self.Lpv, self.max_num_pv)
+
+    # ---- data parallel over NVLink peer memory ---------------------------------------------------------
+    def _setup_peer_memory(self, L, dev):
+        """Symmetric (peer-mapped) allocations for the fused data-parallel optimizer (`k3m_adamw_dp`): the bf16 weight
+        arena every rank's kernels read, and a bf16 gradient send arena.  torch's symmetric-memory allocator does the
+        CUDA IPC / fabric handle exchange; what runs over the mapping is this repo's kernel.  Any failure (no peer
+        access, old driver) falls back to the NCCL all-reduce path, loudly."""
+        try:
+            import torch.distributed._symmetric_memory as symm
+            w16 = symm.empty(L.total, dtype=torch.bfloat16, device=dev)
+            g16 = symm.empty(L.trained_end, dtype=torch.bfloat16, device=dev)
+            w16.zero_()
+            g16.zero_()
+            self._h_w = symm.rendezvous(w16, self.group)
+            self._h_g = symm.rendezvous(g16, self.group)
+            self._w_ptrs = [int(x) for x in self._h_w.buffer_ptrs]
+            self._g_ptrs = [int(x) for x in self._h_g.buffer_ptrs]
+            assert len(self._w_ptrs) == self.world and self._w_ptrs[self.rank] == w16.data_ptr()
+            self.w16, self._g16 = w16, g16
+            self.dp_fused = True
+        except Exception as e:      # pragma: no cover - depends on the box
+            import sys
+            sys.stderr.write("[k3m_b200] peer-memory data-parallel path unavailable (%s: %s); using NCCL all-reduce\n"
+                             % (type(e).__name__, e))
+            self.dp_fused = False
+
+    def _shard(self, lo, hi):
+        """this rank's share [s0, s1) of the bucket [lo, hi): equal 1024-element-aligned pieces"""
+        n = hi - lo
+        piece = ((n + self.world - 1) // self.world + 1023) // 1024 * 1024
+        s0 = min(hi, lo + self.rank * piece)
+        return s0, min(hi, s0 + piece)
+
+    def _peer_barrier(self, handle, channel):
+        handle.barrier(channel=channel, timeout_ms=int(os.environ.get("K3M_DP_BARRIER_TIMEOUT_MS", "30000")))
+
+    def sync_shards(self, moments=False):
+        """Fused data-parallel mode keeps the fp32 master weights (and AdamW moments) of a shard only on the rank that
+        owns it.  Collective: broadcast every shard from its owner so that `state_dict()` / a checkpoint written by
+        any rank is complete.  No-op otherwise."""
+        if not self.dp_fused or self.world == 1:
+            return
+        rank = self.rank
+        try:
+            for lo, hi in self._buckets:
+                for r in range(self.world):
+                    self.rank = r
+                    s0, s1 = self._shard(lo, hi)
+                    if s1 > s0:
+                        src = torch.distributed.get_global_rank(self.group, r)
+                        for t in (self.p32,) + ((self.m, self.v) if moments else ()):
+                            torch.distributed.broadcast(t[s0:s1], src=src, group=self.group)
+        finally:
+            self.rank = rank
 
     def _forward_backward(self):
         """-> the eight fp32 values of `self.losses` as a list of [1] tensors / None."""
@@ -181,7 +258,9 @@ class PretrainStep(object):
         self.w16.copy_(self.p32)
 
     def state_dict(self):
+        """(collective in fused data-parallel mode: every rank must call it, see `sync_shards`)"""
         from .layout import TIED_ALIAS
+        self.sync_shards()
         out = {}
         for n in self.layout.spec:
             off, num, shape = self.layout.offsets[n]
@@ -201,6 +280,8 @@ class PretrainStep(object):
         (small) no-decay region as one last bucket."""
         L = self.layout
         step = max(1, int(bucket_mb * (1 << 20) // 4))
+        if self.dp_fused:
+            step = max(1024, step // 1024 * 1024)      # shards of the fused optimizer are 16-byte-vector aligned
         # the embedding tables open the arena and get their gradients last (their backward closes the step):
         # they are a bucket of their own, so that only THEIR all-reduce + AdamW is left when backward ends
         # instead of whatever piece of up to `bucket_mb` happened to straddle them
@@ -211,6 +292,7 @@ class PretrainStep(object):
         if any(off < emb_end and n.split(".")[0] not in ("embeddings", "v_embeddings")
                for n, (off, num, _) in L.offsets.items()):
             emb_end = 0                                    # not a clean prefix: fall back to uniform pieces
+        emb_end = (emb_end + 63) // 64 * 64                # the next tensor starts 64-aligned: the gap holds zeros
         out, hi = [], L.decay_end
         while hi > emb_end:
             lo = max(emb_end, hi - step)
@@ -241,11 +323,41 @@ class PretrainStep(object):
         t = self.g32[lo:hi]
 
         def work():
+            g16 = None
+            if self.world > 1 and self.dp_fused:
+                ev = None
+                if self.comm_events is not None:
+                    ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                    ev[0].record()
+                # gradients -> this rank's bf16 send arena (zeroing the fp32 arena); every rank's cast must be visible
+                # before anyone reads it; then reduce + AdamW + weight broadcast for the shard this rank owns
+                self.ops.cast_zero(t, self._g16[lo:hi])
+                self._peer_barrier(self._h_g, 0)
+                s0, s1 = self._shard(lo, hi)
+                if s1 > s0:
+                    self.ops.adamw_dp(self.p32[s0:s1], self.m[s0:s1], self.v[s0:s1], self.hyper[gi], self._g_ptrs,
+                                      self._w_ptrs, s0)
+                if ev is not None:
+                    ev[1].record()
+                    self.comm_events.append((ev[0], ev[1], (hi - lo) * 2))
+                return
             if self.world > 1:
-                torch.distributed.all_reduce(t, group=self.group)
+                ev = None
+                if self.comm_events is not None:
+                    ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                    ev[0].record()
+                if self.comm_bf16:
+                    g16 = self._send16[lo:hi]
+                    self.ops.cast(t, torch.bfloat16, out=g16)
+                    torch.distributed.all_reduce(g16, group=self.group)
+                else:
+                    torch.distributed.all_reduce(t, group=self.group)
+                if ev is not None:
+                    ev[1].record()
+                    self.comm_events.append((ev[0], ev[1], (hi - lo) * (2 if self.comm_bf16 else 4)))
             # gradients are summed over ranks; hyper[:, 6] = 1/world turns that into DDP's mean
             self.ops.adamw(self.p32[lo:hi], t, self.m[lo:hi], self.v[lo:hi], self.w16[lo:hi], self.hyper[gi],
-                           zero_grad=True, background=background)
+                           zero_grad=True, background=background, g16=g16)
 
         if self._comm_stream is None:
             work()
@@ -270,11 +382,51 @@ class PretrainStep(object):
             self._next_bucket += 1
 
     def _finish_buckets(self):
+        if self.comm_events is not None:
+            self._bwd_done = torch.cuda.Event(enable_timing=True)
+            self._bwd_done.record()
         while self._next_bucket < len(self._buckets):
             self._bucket_step(self._next_bucket)
             self._next_bucket += 1
+        if self.world > 1 and self.dp_fused:
+            # every rank's weight stores have landed everywhere before anybody's next forward reads them
+            with torch.cuda.stream(self._comm_stream):
+                self._peer_barrier(self._h_w, 1)
         if self._comm_stream is not None:
             torch.cuda.current_stream().wait_stream(self._comm_stream)
+        if self.comm_events is not None:
+            self._opt_done = torch.cuda.Event(enable_timing=True)
+            self._opt_done.record()
+
+    def comm_timing(self, batch):
+        """One instrumented, non-captured step (every rank must call it): CUDA events around each bucket's gradient
+        all-reduce on the optimizer stream, and around the part of the optimizer pipeline that is left when backward
+        has finished.  The device is kept behind the host so that the events bracket back-to-back kernels.
+        -> dict(comm_ms_total, tail_ms, buckets, bytes) — tail_ms is the exposed part: all-reduce + AdamW still to
+        run after the last backward kernel."""
+        snap = (self.p32.clone(), self.m.clone(), self.v.clone(), self.w16.clone(), self.rng.clone())
+        use_graph, self.use_graph = self.use_graph, False
+        self.comm_events = []
+        torch.cuda.synchronize()
+        torch.cuda._sleep(int(8.0e8))
+        self.step(batch)
+        torch.cuda.synchronize()
+        ev, self.comm_events = self.comm_events, None
+        self.use_graph = use_graph
+        self.global_step -= 1
+        for dst, src in zip((self.p32, self.m, self.v, self.w16, self.rng), snap):
+            dst.copy_(src)
+        self.g32.zero_()
+        torch.cuda.synchronize()
+        return dict(comm_ms_total=round(sum(a.elapsed_time(b) for a, b, _ in ev), 3),
+                    tail_ms=round(self._bwd_done.elapsed_time(self._opt_done), 3), buckets=len(ev),
+                    bytes=int(sum(n for _, _, n in ev)), dtype="bf16" if self.comm_bf16 else "f32",
+                    mode="fused peer-memory reduce-scatter + AdamW + weight all-gather (k3m_adamw_dp)" if self.dp_fused
+                    else "NCCL all-reduce + replicated AdamW",
+                    reserve_sms=self.reserve_sms,
+                    note="one non-captured step; comm_ms_total = sum over buckets of (cast +) all-reduce time on the "
+                         "optimizer stream (they run under backward); tail_ms = optimizer pipeline left after backward's "
+                         "last kernel (exposed)")
 
     # ---- the device side of one step ---------------------------------------------------------
     def _device_step(self):

@@ -538,11 +538,11 @@ class RefOps(object):
     def plan_to_device(self, plan, device):
         return {k: torch.from_numpy(v).to(device) for k, v in plan.items()}
 
-    def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True, background=False):
+    def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True, background=False, g16=None):
         """torch.optim.AdamW step on a flat range.  hyper fp32 [8] = (lr, beta1, beta2, eps, wd,
         step, grad_scale, -).  Writes the act-dtype shadow copy and (optionally) zeroes the grad."""
         lr, b1, b2, eps, wd, step, grad_scale = [float(x) for x in hyper[:7]]
-        g = g32 * grad_scale
+        g = (g16.float() if g16 is not None else g32) * grad_scale
         p32.mul_(1.0 - lr * wd)
         m.mul_(b1).add_(g, alpha=1.0 - b1)
         v.mul_(b2).addcmul_(g, g, value=1.0 - b2)

@@ -110,7 +110,7 @@ def test_single_rank_two_steps_match_oracle_plus_torch_adamw():
         assert torch.equal(step.state_dict()[n], sd[n]), n
 
 
-def _dp_worker(rank, world, port, q):
+def _dp_worker(rank, world, port, q, comm_bf16=False):
     try:
         os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
         dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -119,8 +119,9 @@ def _dp_worker(rank, world, port, q):
         sd = synth_state_dict(param_spec(cfg), seed=3)
         B = 3
         step = PretrainStep(cfg, B, device="cpu", state_dict=sd, ops=RefOps(torch.float32), training=False,
-                            use_graph=False, lr=1e-3, process_group=dist.group.WORLD, bucket_mb=0.05, **DIMS)
-        assert len(step._buckets) > 3
+                            use_graph=False, lr=1e-3, process_group=dist.group.WORLD, bucket_mb=0.05,
+                            comm_bf16=comm_bf16, **DIMS)
+        assert len(step._buckets) > 3 and step.comm_bf16 == comm_bf16
         shards = [synth_batch(cfg, B, DIMS["len_t"], DIMS["len_v"], DIMS["len_pv"], max_num_pv=4, seed=40 + r)
                   for r in range(world)]
         random.seed(70 + rank)
@@ -128,7 +129,23 @@ def _dp_worker(rank, world, port, q):
         # DDP semantics: mean over ranks of the rank-local gradients
         per_rank = [oracle_grads(cfg, sd, shards[r], seed=70 + r)[1] for r in range(world)]
         mean = {n: (None if per_rank[0][n] is None else sum(g[n] for g in per_rank) / world) for n in sd}
-        check_params(step, reference_update(sd, [mean], [1e-3]))
+        if comm_bf16:
+            # gradients cross the wire rounded to bf16 and are summed in bf16.  Adam's first step is lr * g / (|g| + eps):
+            # it normalises the gradient, so an element whose two rank gradients nearly cancel can flip the sign of its
+            # +-lr update — the per-element bound of the fp32 check does not apply.  What must hold: the UPDATE as a
+            # whole matches (relative L2 over all trained parameters), and no element moves by more than 2 lr.
+            ref = reference_update(sd, [mean], [1e-3])
+            num = den = 0.0
+            for n in step.layout.spec:
+                if n in step.layout.frozen:
+                    continue
+                got_u, ref_u = step.state_dict()[n] - sd[n], ref[n] - sd[n]
+                num += float((got_u - ref_u).pow(2).sum())
+                den += float(ref_u.pow(2).sum())
+                assert float((got_u - ref_u).abs().max()) <= 2.01e-3, n
+            assert (num / den) ** 0.5 <= 5e-2, (num / den) ** 0.5
+        else:
+            check_params(step, reference_update(sd, [mean], [1e-3]))
         assert step._next_bucket == len(step._buckets)
         dist.barrier()
         q.put((rank, "ok"))
@@ -140,15 +157,63 @@ def _dp_worker(rank, world, port, q):
             dist.destroy_process_group()
 
 
-def test_two_rank_gloo_bucketed_allreduce_matches_mean_of_shard_gradients():
+@pytest.mark.parametrize("comm_bf16", [False, True])
+def test_two_rank_gloo_bucketed_allreduce_matches_mean_of_shard_gradients(comm_bf16):
     world = 2
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29500 + os.getpid() % 2000
-    procs = [ctx.Process(target=_dp_worker, args=(r, world, port, q)) for r in range(world)]
+    port = 29500 + (os.getpid() + (977 if comm_bf16 else 0)) % 2000
+    procs = [ctx.Process(target=_dp_worker, args=(r, world, port, q, comm_bf16)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=600) for _ in range(world)]
     for p in procs:
         p.join(60)
     assert all(r[1] == "ok" for r in res), res
+
+
+def _traj_worker(rank, world, port, q, comm_bf16):
+    try:
+        os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        torch.set_num_threads(2)
+        cfg = tiny_cfg()
+        sd = synth_state_dict(param_spec(cfg), seed=3)
+        step = PretrainStep(cfg, 3, device="cpu", state_dict=sd, ops=RefOps(torch.float32), training=False,
+                            use_graph=False, lr=2e-3, process_group=dist.group.WORLD, bucket_mb=0.05,
+                            comm_bf16=comm_bf16, **DIMS)
+        losses = []
+        for it in range(20):
+            random.seed(500 + it)
+            step.step(synth_batch(cfg, 3, DIMS["len_t"], DIMS["len_v"], DIMS["len_pv"], max_num_pv=4, seed=900 + 2 * it + rank))
+            losses.append(step.read_losses()["loss"])
+        q.put((rank, losses))
+    except Exception:      # pragma: no cover
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def test_bf16_gradient_allreduce_tracks_fp32_allreduce_over_20_steps():
+    """K3M_COMM_BF16 (the data-parallel default): 20 optimizer steps on two ranks with gradients all-reduced in bf16
+    against the same run with the fp32 all-reduce — every step's training loss within 1e-3 relative."""
+    world, ctx = 2, mp.get_context("spawn")
+    traj = {}
+    for mode in (False, True):
+        q = ctx.Queue()
+        port = 31500 + (os.getpid() + (313 if mode else 0)) % 2000
+        procs = [ctx.Process(target=_traj_worker, args=(r, world, port, q, mode)) for r in range(world)]
+        for p in procs:
+            p.start()
+        res = dict(q.get(timeout=900) for _ in range(world))
+        for p in procs:
+            p.join(60)
+        assert all(isinstance(v, list) for v in res.values()), res
+        traj[mode] = res
+    for r in range(world):
+        a, b = traj[False][r], traj[True][r]
+        assert a[-1] < a[0]                       # the run trains
+        for i, (x, y) in enumerate(zip(a, b)):
+            assert abs(x - y) <= 1e-3 * abs(x), (r, i, x, y)
