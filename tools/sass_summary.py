@@ -27,7 +27,7 @@ for line in out.splitlines():
     for p in pats:
         if op == p or op.startswith(p + "."):
             counts[cur][p] += 1
-    if op.startswith("UTCHMMA") and ".2CTA" in op:
+    if op.startswith("UTCHMMA") and ".2CTA" in op and not op.startswith("UTCHMMA.2CTA"):
         counts[cur]["UTCHMMA.2CTA"] += 1
 
 
@@ -44,7 +44,9 @@ tot = collections.Counter()
 for fn, c in counts.items():
     if not sum(c.values()):
         continue
-    name = re.sub(r"\(.*", "", demangle(fn)).replace("void (anonymous namespace)::", "")
+    name = demangle(fn).replace("(int)", "").replace("(bool)", "").replace("void <unnamed>::", "")
+    name = re.sub(r">\(.*", ">", name)
+    name = re.sub(r"^([A-Za-z0-9_]+)\(.*", r"\1", name)
     print("%-70s %s" % (name[:70], " ".join("%s=%d" % (p, c[p]) for p in pats if c[p])))
     tot.update(c)
 print("TOTAL " + " ".join("%s=%d" % (p, tot[p]) for p in pats if tot[p]))
