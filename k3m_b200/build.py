@@ -29,17 +29,20 @@ def needs_build():
     return any(os.path.getmtime(s) > t for s in deps)
 
 
-def build(force=False, verbose=False):
-    if not force and not needs_build():
-        return LIB
-    objdir = os.path.join(HERE, "csrc", "build")
+# The fp32 CHECK library (tests only): the same row-wise / embedding / loss kernel sources compiled with fp32 storage
+# (-DK3M_ACT_F32) plus CUDA-core fp32 GEMM / attention behind the same entry points (gemm_f32.cu, attention_f32.cu);
+# the tcgen05 GEMM and the mma.sync attention are bf16 by construction and stay out of it.
+LIB_F32 = os.path.join(HERE, "libk3m_sm100a_f32.so")
+F32_EXCLUDE = ("gemm_sm100.cu", "attention.cu")
+
+
+def _compile(srcs, objdir, flags, lib, verbose):
     os.makedirs(objdir, exist_ok=True)
-    procs = []
-    objs = []
-    for src in sources():
+    procs, objs = [], []
+    for src in srcs:
         obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
-        cmd = [NVCC] + FLAGS + ["-c", src, "-o", obj]
+        cmd = [NVCC] + flags + ["-c", src, "-o", obj]
         if verbose:
             print(" ".join(cmd))
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
@@ -48,8 +51,15 @@ def build(force=False, verbose=False):
         if p.returncode != 0:
             sys.stderr.write(out.decode())
             raise RuntimeError("nvcc failed on %s" % src)
-    cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-lcudart"]
-    subprocess.check_call(cmd)
+    subprocess.check_call([NVCC, "-shared", "-o", lib] + objs + ["-lcudart"])
+
+
+def build(force=False, verbose=False):
+    if not force and not needs_build() and os.path.exists(LIB_F32) and os.path.getmtime(LIB_F32) >= os.path.getmtime(LIB):
+        return LIB
+    _compile(sources(), os.path.join(HERE, "csrc", "build"), FLAGS, LIB, verbose)
+    _compile([s for s in sources() if os.path.basename(s) not in F32_EXCLUDE], os.path.join(HERE, "csrc", "build", "f32"),
+             FLAGS + ["-DK3M_ACT_F32"], LIB_F32, verbose)
     with open(STAMP, "w") as f:
         f.write(" ".join(FLAGS))
     return LIB

@@ -6,6 +6,15 @@
 #include <stdint.h>
 
 typedef __nv_bfloat16 bf16;
+// Activation / weight element type of the row-wise, embedding and loss kernels.  The product library is bf16.  The
+// fp32 CHECK build (-DK3M_ACT_F32 -> libk3m_sm100a_f32.so, tests only: north_star's "1e-5 in an fp32 check mode")
+// compiles the very same kernel sources with fp32 storage; its GEMM and attention are plain CUDA-core fp32 kernels
+// (gemm_f32.cu, attention_f32.cu) behind the same entry points.
+#ifdef K3M_ACT_F32
+typedef float act_t;
+#else
+typedef bf16 act_t;
+#endif
 
 // ---- error handling across the C ABI (no exceptions) ------------------------------------------
 #define K3M_OK 0
@@ -177,3 +186,42 @@ __device__ __forceinline__ void st8(float* p, const float v[8]) {
   *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
   *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
 }
+
+// ---- value conversions / 8-element packs in the activation type ----------------------------------------------
+__device__ __forceinline__ float to_f(bf16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float to_f(float v) { return v; }
+__device__ __forceinline__ act_t act_from(float v) {
+#ifdef K3M_ACT_F32
+  return v;
+#else
+  return __float2bfloat16(v);
+#endif
+}
+// eight consecutive activation values kept as loaded (16 bytes of bf16, 32 bytes of fp32)
+#ifdef K3M_ACT_F32
+struct Pack8 { float4 a, b; };
+__device__ __forceinline__ Pack8 load_pack8(const float* p) {
+  Pack8 r;
+  r.a = *reinterpret_cast<const float4*>(p);
+  r.b = *reinterpret_cast<const float4*>(p + 4);
+  return r;
+}
+__device__ __forceinline__ void unpack8(const Pack8& u, float v[8]) {
+  v[0] = u.a.x; v[1] = u.a.y; v[2] = u.a.z; v[3] = u.a.w; v[4] = u.b.x; v[5] = u.b.y; v[6] = u.b.z; v[7] = u.b.w;
+}
+#else
+struct Pack8 { uint4 u; };
+__device__ __forceinline__ Pack8 load_pack8(const bf16* p) {
+  Pack8 r;
+  r.u = *reinterpret_cast<const uint4*>(p);
+  return r;
+}
+__device__ __forceinline__ void unpack8(const Pack8& u, float v[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u.u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __bfloat1622float2(h[i]);
+    v[2 * i] = f.x; v[2 * i + 1] = f.y;
+  }
+}
+#endif

@@ -6,13 +6,13 @@ namespace {
 
 // out[r] = word[ids[r]] + pos[r % L] + typ[type_ids[r]]     (BertEmbeddings, vilbert_k3m.py:361-376)
 __global__ void __launch_bounds__(128) embed_fwd_kernel(const long long* __restrict__ ids, const long long* __restrict__ tids,
-                                                        const bf16* __restrict__ word, const bf16* __restrict__ pos,
-                                                        const bf16* __restrict__ typ, bf16* __restrict__ out, int M, int L, int H) {
+                                                        const act_t* __restrict__ word, const act_t* __restrict__ pos,
+                                                        const act_t* __restrict__ typ, act_t* __restrict__ out, int M, int L, int H) {
   const int row = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= M) return;
-  const bf16* w = word + (size_t)ids[row] * H;
-  const bf16* p = pos + (size_t)(row % L) * H;
-  const bf16* t = typ + (size_t)tids[row] * H;
+  const act_t* w = word + (size_t)ids[row] * H;
+  const act_t* p = pos + (size_t)(row % L) * H;
+  const act_t* t = typ + (size_t)tids[row] * H;
   for (int c = lane * 8; c < H; c += 256) {
     float a[8], b[8], e[8];
     ld8(w + c, a); ld8(p + c, b); ld8(t + c, e);
@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(128) embed_fwd_kernel(const long long* __restr
 }
 
 // scatter-add of dx rows into the fp32 embedding gradients; word row 0 (padding_idx) is skipped
-__global__ void __launch_bounds__(128) embed_bwd_kernel(const bf16* __restrict__ dx, const long long* __restrict__ ids,
+__global__ void __launch_bounds__(128) embed_bwd_kernel(const act_t* __restrict__ dx, const long long* __restrict__ ids,
                                                         const long long* __restrict__ tids, float* __restrict__ dword,
                                                         float* __restrict__ dpos, float* __restrict__ dtyp, int M, int L, int H) {
   const int row = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(128) embed_bwd_kernel(const bf16* __restrict__
   float* p = dpos + (size_t)(row % L) * H;
   float* t = dtyp + (size_t)tids[row] * H;
   for (int c = lane; c < H; c += 32) {
-    const float g = __bfloat162float(dx[(size_t)row * H + c]);
+    const float g = to_f(dx[(size_t)row * H + c]);
     if (id != 0) atomicAdd(w + c, g);
     atomicAdd(p + c, g);
     atomicAdd(t + c, g);
@@ -41,20 +41,20 @@ __global__ void __launch_bounds__(128) embed_bwd_kernel(const bf16* __restrict__
 }
 
 // out[m, n] = sum_k loc[m, k] w[n, k] + b[n],  k < 5
-__global__ void loc_fwd_kernel(const float* __restrict__ loc, const bf16* __restrict__ w, const bf16* __restrict__ b,
-                               bf16* __restrict__ out, int M, int N) {
+__global__ void loc_fwd_kernel(const float* __restrict__ loc, const act_t* __restrict__ w, const act_t* __restrict__ b,
+                               act_t* __restrict__ out, int M, int N) {
   const unsigned n = (unsigned)(M * N);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = (int)(i / N), c = (int)(i % N);
     float acc = ld_f(b + c);
 #pragma unroll
     for (int k = 0; k < 5; ++k) acc = fmaf(loc[(size_t)m * 5 + k], ld_f(w + (size_t)c * 5 + k), acc);
-    out[i] = __float2bfloat16(acc);
+    out[i] = act_from(acc);
   }
 }
 
 // dw[n, k] += sum_m dy[m, n] loc[m, k] ; db[n] += sum_m dy[m, n]       one thread per column n
-__global__ void __launch_bounds__(128) loc_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ loc,
+__global__ void __launch_bounds__(128) loc_bwd_kernel(const act_t* __restrict__ dy, const float* __restrict__ loc,
                                                       float* __restrict__ dw, float* __restrict__ db, int M, int N, int rows_per) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= N) return;
@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(128) loc_bwd_kernel(const bf16* __restrict__ d
   if (r1 > M) r1 = M;
   float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   for (int m = r0; m < r1; ++m) {
-    const float g = __bfloat162float(dy[(size_t)m * N + c]);
+    const float g = to_f(dy[(size_t)m * N + c]);
 #pragma unroll
     for (int k = 0; k < 5; ++k) acc[k] = fmaf(g, loc[(size_t)m * 5 + k], acc[k]);
     acc[5] += g;
@@ -74,12 +74,12 @@ __global__ void __launch_bounds__(128) loc_bwd_kernel(const bf16* __restrict__ d
 }
 
 // cat[m] = [relu(a[m]) | relu(b[m]) | relu(c[m])]
-__global__ void relu_cat3_kernel(const bf16* a, int lda, const bf16* b, int ldb, const bf16* c, int ldc, bf16* out, int M, int H) {
+__global__ void relu_cat3_kernel(const act_t* a, int lda, const act_t* b, int ldb, const act_t* c, int ldc, act_t* out, int M, int H) {
   const int hv = H / 8;
   const unsigned n = (unsigned)(M * 3 * hv);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = (int)(i / (3 * hv)), r = (int)(i % (3 * hv)), k = r / hv, col = (r % hv) * 8;
-    const bf16* src = k == 0 ? a + (size_t)m * lda : (k == 1 ? b + (size_t)m * ldb : c + (size_t)m * ldc);
+    const act_t* src = k == 0 ? a + (size_t)m * lda : (k == 1 ? b + (size_t)m * ldb : c + (size_t)m * ldc);
     float v[8];
     ld8(src + col, v);
 #pragma unroll
@@ -122,8 +122,8 @@ __device__ __forceinline__ void ysoft3(const float* gates, const float* noise, c
   *pick = p;
 }
 
-__global__ void fuse_fwd_kernel(const bf16* __restrict__ cat, const float* __restrict__ gates, const float* __restrict__ noise,
-                                const unsigned long long* rng, unsigned int site, bf16* __restrict__ out, int ldo, int M, int H) {
+__global__ void fuse_fwd_kernel(const act_t* __restrict__ cat, const float* __restrict__ gates, const float* __restrict__ noise,
+                                const unsigned long long* rng, unsigned int site, act_t* __restrict__ out, int ldo, int M, int H) {
   const unsigned n = (unsigned)(M * H);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = (int)(i / H), h = (int)(i % H);
@@ -135,71 +135,71 @@ __global__ void fuse_fwd_kernel(const bf16* __restrict__ cat, const float* __res
 }
 
 // straight-through backward: dgates[m,k,h] and dcat_direct[m,k,h] = dout * onehot
-__global__ void fuse_bwd_kernel(const bf16* __restrict__ dout, int ldd, const bf16* __restrict__ cat,
+__global__ void fuse_bwd_kernel(const act_t* __restrict__ dout, int ldd, const act_t* __restrict__ cat,
                                 const float* __restrict__ gates, const float* __restrict__ noise,
-                                const unsigned long long* rng, unsigned int site, bf16* __restrict__ dgates,
-                                bf16* __restrict__ dcat, int M, int H) {
+                                const unsigned long long* rng, unsigned int site, act_t* __restrict__ dgates,
+                                act_t* __restrict__ dcat, int M, int H) {
   const unsigned n = (unsigned)(M * H);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = (int)(i / H), h = (int)(i % H);
     float ak[3], y[3];
     int pick;
     ysoft3(gates, noise, rng, site, m, h, H, ak, y, &pick);
-    const float go = __bfloat162float(dout[(size_t)m * ldd + h]);
+    const float go = to_f(dout[(size_t)m * ldd + h]);
     float dy[3], dot = 0.f;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-      dy[k] = go * __bfloat162float(cat[(size_t)m * 3 * H + k * H + h]);
+      dy[k] = go * to_f(cat[(size_t)m * 3 * H + k * H + h]);
       dot += y[k] * dy[k];
     }
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       const size_t o = (size_t)m * 3 * H + k * H + h;
-      dgates[o] = __float2bfloat16(y[k] * (dy[k] - dot) * ak[k] * (1.0f - ak[k]));
-      dcat[o] = __float2bfloat16(k == pick ? go : 0.f);
+      dgates[o] = act_from(y[k] * (dy[k] - dot) * ak[k] * (1.0f - ak[k]));
+      dcat[o] = act_from(k == pick ? go : 0.f);
     }
   }
 }
 
 // d{a,b,c}[m,h] += dcat[m, k*H + h] * (cat[m, k*H + h] > 0)
-__global__ void relu_split3_kernel(const bf16* __restrict__ dcat, const bf16* __restrict__ cat, bf16* da, int lda, bf16* db,
-                                   int ldb, bf16* dc, int ldc, int M, int H) {
+__global__ void relu_split3_kernel(const act_t* __restrict__ dcat, const act_t* __restrict__ cat, act_t* da, int lda, act_t* db,
+                                   int ldb, act_t* dc, int ldc, int M, int H) {
   const unsigned n = (unsigned)(M * 3 * H);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int m = (int)(i / (3 * H)), r = (int)(i % (3 * H)), k = r / H, h = r % H;
-    if (__bfloat162float(cat[i]) > 0.f) {
-      bf16* dst = k == 0 ? da + (size_t)m * lda + h : (k == 1 ? db + (size_t)m * ldb + h : dc + (size_t)m * ldc + h);
-      *dst = __float2bfloat16(__bfloat162float(*dst) + __bfloat162float(dcat[i]));
+    if (to_f(cat[i]) > 0.f) {
+      act_t* dst = k == 0 ? da + (size_t)m * lda + h : (k == 1 ? db + (size_t)m * ldb + h : dc + (size_t)m * ldc + h);
+      *dst = act_from(to_f(*dst) + to_f(dcat[i]));
     }
   }
 }
 
 // pooled[b, h] = mean_{i=1..L-1} seq[b*L + i, h]       (vilbert_k3m.py:2405-2409)
 template <typename TO>
-__global__ void pool_fwd_kernel(const bf16* __restrict__ seq, int ld, TO* __restrict__ out, int B, int L, int H) {
+__global__ void pool_fwd_kernel(const act_t* __restrict__ seq, int ld, TO* __restrict__ out, int B, int L, int H) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B * H) return;
   const int b = i / H, h = i % H;
   float acc = 0.f;
-  for (int t = 1; t < L; ++t) acc += __bfloat162float(seq[(size_t)(b * L + t) * ld + h]);
+  for (int t = 1; t < L; ++t) acc += to_f(seq[(size_t)(b * L + t) * ld + h]);
   st_f(out + i, acc / (float)(L - 1));
 }
 
 // dseq[b*L + i, h] += dpool[b, h] / (L-1), i >= 1
-__global__ void pool_bwd_kernel(const float* __restrict__ dpool, bf16* __restrict__ dseq, int ld, int B, int L, int H) {
+__global__ void pool_bwd_kernel(const float* __restrict__ dpool, act_t* __restrict__ dseq, int ld, int B, int L, int H) {
   const unsigned n = (unsigned)(B * L * H);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int h = (int)(i % H);
     const int r = (int)(i / H), b = r / L, t = r % L;
     if (t == 0) continue;
-    bf16* p = dseq + (size_t)r * ld + h;
-    *p = __float2bfloat16(__bfloat162float(*p) + dpool[(size_t)b * H + h] / (float)(L - 1));
+    act_t* p = dseq + (size_t)r * ld + h;
+    *p = act_from(to_f(*p) + dpool[(size_t)b * H + h] / (float)(L - 1));
   }
 }
 
 // ---- soft fusion (if_pre_sampling = 2, pre_sampling_sequence_soft, vilbert_k3m.py:2300-2329) --------------
-// gated = cat * alpha  (cat = relu(cat3), alpha = sigmoid(score GEMM), both bf16 [M, 3H], 8 elements per thread)
-__global__ void gate_mul_kernel(const bf16* __restrict__ cat, const bf16* __restrict__ alpha, bf16* __restrict__ out,
+// gated = cat * alpha  (cat = relu(cat3), alpha = sigmoid(score GEMM), both act_t [M, 3H], 8 elements per thread)
+__global__ void gate_mul_kernel(const act_t* __restrict__ cat, const act_t* __restrict__ alpha, act_t* __restrict__ out,
                                 size_t n8) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
     float a[8], b[8];
@@ -211,8 +211,8 @@ __global__ void gate_mul_kernel(const bf16* __restrict__ cat, const bf16* __rest
   }
 }
 // dgated -> dcat (direct path) = dgated * alpha ;  dscore = dgated * cat * alpha * (1 - alpha)
-__global__ void gate_bwd_kernel(const bf16* __restrict__ dgated, const bf16* __restrict__ cat,
-                                const bf16* __restrict__ alpha, bf16* __restrict__ dcat, bf16* __restrict__ dscore,
+__global__ void gate_bwd_kernel(const act_t* __restrict__ dgated, const act_t* __restrict__ cat,
+                                const act_t* __restrict__ alpha, act_t* __restrict__ dcat, act_t* __restrict__ dscore,
                                 size_t n8) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
     float d[8], c[8], a[8], o1[8], o2[8];
@@ -243,42 +243,42 @@ inline int grid_for(size_t n, int block) {
 extern "C" int k3m_embed_fwd(const long long* ids, const long long* type_ids, const void* word, const void* pos,
                              const void* typ, void* out, int M, int L, int H, void* stream) {
   K3M_REQUIRE(M > 0 && H % 8 == 0, "embed_fwd: H must be a multiple of 8");
-  embed_fwd_kernel<<<(M + 3) / 4, 128, 0, ST(stream)>>>(ids, type_ids, (const bf16*)word, (const bf16*)pos,
-                                                        (const bf16*)typ, (bf16*)out, M, L, H);
+  embed_fwd_kernel<<<(M + 3) / 4, 128, 0, ST(stream)>>>(ids, type_ids, (const act_t*)word, (const act_t*)pos,
+                                                        (const act_t*)typ, (act_t*)out, M, L, H);
   return k3m_check_launch("k3m_embed_fwd");
 }
 
 extern "C" int k3m_embed_bwd(const void* dx, const long long* ids, const long long* type_ids, float* dword, float* dpos,
                              float* dtyp, int M, int L, int H, void* stream) {
-  embed_bwd_kernel<<<(M + 3) / 4, 128, 0, ST(stream)>>>((const bf16*)dx, ids, type_ids, dword, dpos, dtyp, M, L, H);
+  embed_bwd_kernel<<<(M + 3) / 4, 128, 0, ST(stream)>>>((const act_t*)dx, ids, type_ids, dword, dpos, dtyp, M, L, H);
   return k3m_check_launch("k3m_embed_bwd");
 }
 
 extern "C" int k3m_loc_embed_fwd(const float* loc, const void* w, const void* b, void* out, int M, int N, void* stream) {
-  loc_fwd_kernel<<<grid_for((size_t)M * N, 256), 256, 0, ST(stream)>>>(loc, (const bf16*)w, (const bf16*)b, (bf16*)out, M, N);
+  loc_fwd_kernel<<<grid_for((size_t)M * N, 256), 256, 0, ST(stream)>>>(loc, (const act_t*)w, (const act_t*)b, (act_t*)out, M, N);
   return k3m_check_launch("k3m_loc_embed_fwd");
 }
 
 extern "C" int k3m_loc_embed_bwd(const void* dy, const float* loc, float* dw, float* db, int M, int N, void* stream) {
   int gy = (M + 127) / 128;
   if (gy > 64) gy = 64;
-  loc_bwd_kernel<<<dim3((N + 127) / 128, gy), 128, 0, ST(stream)>>>((const bf16*)dy, loc, dw, db, M, N, (M + gy - 1) / gy);
+  loc_bwd_kernel<<<dim3((N + 127) / 128, gy), 128, 0, ST(stream)>>>((const act_t*)dy, loc, dw, db, M, N, (M + gy - 1) / gy);
   return k3m_check_launch("k3m_loc_embed_bwd");
 }
 
 extern "C" int k3m_relu_cat3(const void* a, int lda, const void* b, int ldb, const void* c, int ldc, void* out, int M,
                              int H, void* stream) {
   K3M_REQUIRE(H % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "relu_cat3: widths must be multiples of 8");
-  relu_cat3_kernel<<<grid_for((size_t)M * 3 * H / 8, 256), 256, 0, ST(stream)>>>((const bf16*)a, lda, (const bf16*)b, ldb,
-                                                                                 (const bf16*)c, ldc, (bf16*)out, M, H);
+  relu_cat3_kernel<<<grid_for((size_t)M * 3 * H / 8, 256), 256, 0, ST(stream)>>>((const act_t*)a, lda, (const act_t*)b, ldb,
+                                                                                 (const act_t*)c, ldc, (act_t*)out, M, H);
   return k3m_check_launch("k3m_relu_cat3");
 }
 
 extern "C" int k3m_fuse_select_fwd(const void* cat, const float* gates, const float* noise, const void* rng,
                                    unsigned int site, void* out, int ldo, int M, int H, void* stream) {
   K3M_REQUIRE(noise || rng, "fuse_select: need either a noise tensor or the RNG state");
-  fuse_fwd_kernel<<<grid_for((size_t)M * H, 256), 256, 0, ST(stream)>>>((const bf16*)cat, gates, noise,
-                                                                        (const unsigned long long*)rng, site, (bf16*)out, ldo, M, H);
+  fuse_fwd_kernel<<<grid_for((size_t)M * H, 256), 256, 0, ST(stream)>>>((const act_t*)cat, gates, noise,
+                                                                        (const unsigned long long*)rng, site, (act_t*)out, ldo, M, H);
   return k3m_check_launch("k3m_fuse_select_fwd");
 }
 
@@ -286,13 +286,13 @@ extern "C" int k3m_fuse_select_bwd(const void* dout, int ldd, const void* cat, c
                                    const void* rng, unsigned int site, void* dgates, void* dcat, int M, int H, void* stream) {
   K3M_REQUIRE(noise || rng, "fuse_select: need either a noise tensor or the RNG state");
   fuse_bwd_kernel<<<grid_for((size_t)M * H, 256), 256, 0, ST(stream)>>>(
-      (const bf16*)dout, ldd, (const bf16*)cat, gates, noise, (const unsigned long long*)rng, site, (bf16*)dgates, (bf16*)dcat, M, H);
+      (const act_t*)dout, ldd, (const act_t*)cat, gates, noise, (const unsigned long long*)rng, site, (act_t*)dgates, (act_t*)dcat, M, H);
   return k3m_check_launch("k3m_fuse_select_bwd");
 }
 
 extern "C" int k3m_gate_mul(const void* cat, const void* alpha, void* out, long long n, void* stream) {
   K3M_REQUIRE(n > 0 && n % 8 == 0, "gate_mul: element count must be a positive multiple of 8");
-  gate_mul_kernel<<<grid_for((size_t)n / 8, 256), 256, 0, ST(stream)>>>((const bf16*)cat, (const bf16*)alpha, (bf16*)out,
+  gate_mul_kernel<<<grid_for((size_t)n / 8, 256), 256, 0, ST(stream)>>>((const act_t*)cat, (const act_t*)alpha, (act_t*)out,
                                                                        (size_t)n / 8);
   return k3m_check_launch("k3m_gate_mul");
 }
@@ -300,28 +300,28 @@ extern "C" int k3m_gate_mul(const void* cat, const void* alpha, void* out, long 
 extern "C" int k3m_gate_bwd(const void* dgated, const void* cat, const void* alpha, void* dcat, void* dscore, long long n,
                             void* stream) {
   K3M_REQUIRE(n > 0 && n % 8 == 0, "gate_bwd: element count must be a positive multiple of 8");
-  gate_bwd_kernel<<<grid_for((size_t)n / 8, 256), 256, 0, ST(stream)>>>((const bf16*)dgated, (const bf16*)cat,
-                                                                       (const bf16*)alpha, (bf16*)dcat, (bf16*)dscore,
+  gate_bwd_kernel<<<grid_for((size_t)n / 8, 256), 256, 0, ST(stream)>>>((const act_t*)dgated, (const act_t*)cat,
+                                                                       (const act_t*)alpha, (act_t*)dcat, (act_t*)dscore,
                                                                        (size_t)n / 8);
   return k3m_check_launch("k3m_gate_bwd");
 }
 
 extern "C" int k3m_relu_bwd_split3(const void* dcat, const void* cat, void* da, int lda, void* db, int ldb, void* dc,
                                    int ldc, int M, int H, void* stream) {
-  relu_split3_kernel<<<grid_for((size_t)M * 3 * H, 256), 256, 0, ST(stream)>>>((const bf16*)dcat, (const bf16*)cat, (bf16*)da,
-                                                                               lda, (bf16*)db, ldb, (bf16*)dc, ldc, M, H);
+  relu_split3_kernel<<<grid_for((size_t)M * 3 * H, 256), 256, 0, ST(stream)>>>((const act_t*)dcat, (const act_t*)cat, (act_t*)da,
+                                                                               lda, (act_t*)db, ldb, (act_t*)dc, ldc, M, H);
   return k3m_check_launch("k3m_relu_bwd_split3");
 }
 
 extern "C" int k3m_mean_pool_fwd(const void* seq, int ld, void* out, int out_f32, int B, int L, int H, void* stream) {
   K3M_REQUIRE(L >= 2, "mean_pool: need at least two tokens");
   const int g = (B * H + 255) / 256;
-  if (out_f32) pool_fwd_kernel<float><<<g, 256, 0, ST(stream)>>>((const bf16*)seq, ld, (float*)out, B, L, H);
-  else pool_fwd_kernel<bf16><<<g, 256, 0, ST(stream)>>>((const bf16*)seq, ld, (bf16*)out, B, L, H);
+  if (out_f32) pool_fwd_kernel<float><<<g, 256, 0, ST(stream)>>>((const act_t*)seq, ld, (float*)out, B, L, H);
+  else pool_fwd_kernel<act_t><<<g, 256, 0, ST(stream)>>>((const act_t*)seq, ld, (act_t*)out, B, L, H);
   return k3m_check_launch("k3m_mean_pool_fwd");
 }
 
 extern "C" int k3m_mean_pool_bwd(const float* dpool, void* dseq, int ld, int B, int L, int H, void* stream) {
-  pool_bwd_kernel<<<grid_for((size_t)B * L * H, 256), 256, 0, ST(stream)>>>(dpool, (bf16*)dseq, ld, B, L, H);
+  pool_bwd_kernel<<<grid_for((size_t)B * L * H, 256), 256, 0, ST(stream)>>>(dpool, (act_t*)dseq, ld, B, L, H);
   return k3m_check_launch("k3m_mean_pool_bwd");
 }

@@ -20,55 +20,55 @@ __global__ void count_kernel(const long long* __restrict__ lab, int n, long long
 // ---- masked-LM cross entropy (CrossEntropyLoss(ignore_index=-1), vilbert_k3m.py:2817-2826) -----------
 // One CTA per row.  loss += (lse - logit[label]) / count ; dlogits = (softmax - onehot) * gscale / count
 // written in place over the logits (rows without a label become zero).
-__global__ void __launch_bounds__(256) xent_kernel(bf16* __restrict__ logits, int ld, const long long* __restrict__ labels,
+__global__ void __launch_bounds__(256) xent_kernel(act_t* __restrict__ logits, int ld, const long long* __restrict__ labels,
                                                    const float* __restrict__ count, int V, float gscale,
                                                    float* __restrict__ loss, int write_grad) {
   __shared__ float red[32];
   const int row = blockIdx.x;
-  bf16* lr = logits + (size_t)row * ld;
+  act_t* lr = logits + (size_t)row * ld;
   const long long lab = labels[row];
   if (lab < 0 || lab >= V) {
     // ignore_index = -1 (`vilbert_k3m.py:2207`); any other label outside [0, V) makes torch's CrossEntropyLoss
     // raise — no exception can leave a captured graph, so the loss turns NaN instead of reading out of bounds
     if ((lab < -1 || lab >= V) && threadIdx.x == 0) atomicAdd(loss, __int_as_float(0x7fc00000));
     if (write_grad)
-      for (int c = threadIdx.x; c < ld; c += blockDim.x) lr[c] = __float2bfloat16(0.f);
+      for (int c = threadIdx.x; c < ld; c += blockDim.x) lr[c] = act_from(0.f);
     return;
   }
   float mx = -3.0e38f;
-  for (int c = threadIdx.x; c < V; c += blockDim.x) mx = fmaxf(mx, __bfloat162float(lr[c]));
+  for (int c = threadIdx.x; c < V; c += blockDim.x) mx = fmaxf(mx, to_f(lr[c]));
   mx = block_max(mx, red);
   float s = 0.f;
-  for (int c = threadIdx.x; c < V; c += blockDim.x) s += __expf(__bfloat162float(lr[c]) - mx);
+  for (int c = threadIdx.x; c < V; c += blockDim.x) s += __expf(to_f(lr[c]) - mx);
   s = block_sum(s, red);
   const float lse = mx + __logf(s);
   const float inv_cnt = 1.0f / count[0];
-  if (threadIdx.x == 0) atomicAdd(loss, (lse - __bfloat162float(lr[lab])) * inv_cnt);
+  if (threadIdx.x == 0) atomicAdd(loss, (lse - to_f(lr[lab])) * inv_cnt);
   if (write_grad) {
     const float g = gscale * inv_cnt;
     __syncthreads();
     for (int c = threadIdx.x; c < ld; c += blockDim.x) {
       float v = 0.f;
-      if (c < V) v = (__expf(__bfloat162float(lr[c]) - lse) - (c == lab ? 1.f : 0.f)) * g;
-      lr[c] = __float2bfloat16(v);
+      if (c < V) v = (__expf(to_f(lr[c]) - lse) - (c == lab ? 1.f : 0.f)) * g;
+      lr[c] = act_from(v);
     }
   }
 }
 
 // ---- masked-region KL (KLDivLoss(none)(log_softmax, target) * (label==1) / count, :2754-2760) ------
 // One CTA per (item, region) row of the fp32 logits [B*Lv1, ld]; row 0 of every item is the global
-// region (no target).  dlogits (bf16, same ld) = (softmax * sum(t) - t) * gscale / count.
+// region (no target).  dlogits (act_t, same ld) = (softmax * sum(t) - t) * gscale / count.
 __global__ void __launch_bounds__(256) kl_kernel(const float* __restrict__ logits, int ld, const float* __restrict__ target,
                                                  const long long* __restrict__ label, const float* __restrict__ count, int T,
-                                                 int Lv1, float gscale, float* __restrict__ loss, bf16* __restrict__ dlogits) {
+                                                 int Lv1, float gscale, float* __restrict__ loss, act_t* __restrict__ dlogits) {
   __shared__ float red[32];
   const int row = blockIdx.x;
   const int b = row / Lv1, i = row % Lv1;
-  bf16* dr = dlogits ? dlogits + (size_t)row * ld : nullptr;
+  act_t* dr = dlogits ? dlogits + (size_t)row * ld : nullptr;
   const bool active = i > 0 && label[(size_t)b * (Lv1 - 1) + (i - 1)] == 1;
   if (!active) {
     if (dr)
-      for (int c = threadIdx.x; c < ld; c += blockDim.x) dr[c] = __float2bfloat16(0.f);
+      for (int c = threadIdx.x; c < ld; c += blockDim.x) dr[c] = act_from(0.f);
     return;
   }
   const float* lr = logits + (size_t)row * ld;
@@ -97,14 +97,14 @@ __global__ void __launch_bounds__(256) kl_kernel(const float* __restrict__ logit
     for (int c = threadIdx.x; c < ld; c += blockDim.x) {
       float v = 0.f;
       if (c < T) v = (__expf(lr[c] - lse) * ts - tr[c]) * g;
-      dr[c] = __float2bfloat16(v);
+      dr[c] = act_from(v);
     }
   }
 }
 
 // ---- ITM value: CE(Linear_{H->2}(dropout(pool_t + pool_pv + pool_v)), 1 - ((l1+l2+l3)==0)) -----------
-__global__ void __launch_bounds__(128) itm_kernel(const float* pt, const float* ppv, const float* pv, const bf16* w,
-                                                  const bf16* bias, const long long* l1, const long long* l2,
+__global__ void __launch_bounds__(128) itm_kernel(const float* pt, const float* ppv, const float* pv, const act_t* w,
+                                                  const act_t* bias, const long long* l1, const long long* l2,
                                                   const long long* l3, int B, int H, DropSpec drop, float* loss) {
   __shared__ float red[32];
   const int b = blockIdx.x;
@@ -127,11 +127,11 @@ __global__ void __launch_bounds__(128) itm_kernel(const float* pt, const float* 
 
 // ---- item-alignment head (K3MForItemAlignment.forward "ce" branch, vilbert_k3m.py:3443-3450) ----------
 // logits fp32 [B, 2] (row stride ld) -> probs = softmax(logits) [B, 2]; loss = mean CE(logits, labels);
-// dlogits (bf16, row stride ldd, columns 0..1) = grad_scale * (probs - onehot) / B
+// dlogits (act_t, row stride ldd, columns 0..1) = grad_scale * (probs - onehot) / B
 __global__ void __launch_bounds__(128) pair_cls_kernel(const float* __restrict__ logits, int ld,
                                                        const long long* __restrict__ labels, int B, float grad_scale,
                                                        float* __restrict__ loss, float* __restrict__ probs,
-                                                       bf16* __restrict__ dlogits, int ldd) {
+                                                       act_t* __restrict__ dlogits, int ldd) {
   __shared__ float red[32];
   float acc = 0.f;
   for (int b = threadIdx.x; b < B; b += blockDim.x) {
@@ -148,8 +148,8 @@ __global__ void __launch_bounds__(128) pair_cls_kernel(const float* __restrict__
     }
     if (dlogits) {
       const float s = grad_scale / (float)B;
-      dlogits[(size_t)b * ldd] = __float2bfloat16(s * (p0 - (lab ? 0.f : 1.f)));
-      dlogits[(size_t)b * ldd + 1] = __float2bfloat16(s * (p1 - (lab ? 1.f : 0.f)));
+      dlogits[(size_t)b * ldd] = act_from(s * (p0 - (lab ? 0.f : 1.f)));
+      dlogits[(size_t)b * ldd + 1] = act_from(s * (p1 - (lab ? 1.f : 0.f)));
     }
   }
   acc = block_sum(acc, red);
@@ -171,21 +171,21 @@ __global__ void dropout_kernel(const TX* __restrict__ x, int ldx, TY* __restrict
 }
 
 // ---- structure aggregator (structure_aggregator, vilbert_k3m.py:2437-2467) ---------------------------
-// X[p] = [c_init[item] | mean(seq[r0], seq[r1]) | mean(seq[r2], seq[r3])]  (bf16 for the W1 GEMM);
+// X[p] = [c_init[item] | mean(seq[r0], seq[r1]) | mean(seq[r2], seq[r3])]  (act_t for the W1 GEMM);
 // PV[p] = the two means in fp32 for the LPM norms.
-__global__ void pair_gather_fwd_kernel(const float* __restrict__ c_init, const bf16* __restrict__ seq, int lds,
-                                       const int* __restrict__ item, const int* __restrict__ rows, bf16* __restrict__ X,
+__global__ void pair_gather_fwd_kernel(const float* __restrict__ c_init, const act_t* __restrict__ seq, int lds,
+                                       const int* __restrict__ item, const int* __restrict__ rows, act_t* __restrict__ X,
                                        float* __restrict__ PV, int P, int H) {
   const size_t n = (size_t)P * H;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     const int p = (int)(i / H), h = (int)(i % H);
     const int* r = rows + (size_t)p * 4;
-    const float pm = 0.5f * (__bfloat162float(seq[(size_t)r[0] * lds + h]) + __bfloat162float(seq[(size_t)r[1] * lds + h]));
-    const float vm = 0.5f * (__bfloat162float(seq[(size_t)r[2] * lds + h]) + __bfloat162float(seq[(size_t)r[3] * lds + h]));
-    bf16* x = X + (size_t)p * 3 * H;
-    x[h] = __float2bfloat16(c_init[(size_t)item[p] * H + h]);
-    x[H + h] = __float2bfloat16(pm);
-    x[2 * H + h] = __float2bfloat16(vm);
+    const float pm = 0.5f * (to_f(seq[(size_t)r[0] * lds + h]) + to_f(seq[(size_t)r[1] * lds + h]));
+    const float vm = 0.5f * (to_f(seq[(size_t)r[2] * lds + h]) + to_f(seq[(size_t)r[3] * lds + h]));
+    act_t* x = X + (size_t)p * 3 * H;
+    x[h] = act_from(c_init[(size_t)item[p] * H + h]);
+    x[H + h] = act_from(pm);
+    x[2 * H + h] = act_from(vm);
     PV[(size_t)p * 2 * H + h] = pm;
     PV[(size_t)p * 2 * H + H + h] = vm;
   }
@@ -234,8 +234,8 @@ __global__ void struct_fallback_bwd_kernel(float* __restrict__ dt, float* __rest
 
 // one CTA per item: scores b_j = w2 . leaky_relu(t_j) + b2 over the item's pair range, softmax,
 // s = sum_j att_j t_j.  att is stored [B, maxn].
-__global__ void __launch_bounds__(256) struct_attn_fwd_kernel(const float* __restrict__ t, const bf16* __restrict__ w2,
-                                                              const bf16* __restrict__ b2, const int* __restrict__ seg,
+__global__ void __launch_bounds__(256) struct_attn_fwd_kernel(const float* __restrict__ t, const act_t* __restrict__ w2,
+                                                              const act_t* __restrict__ b2, const int* __restrict__ seg,
                                                               float* __restrict__ s_out, float* __restrict__ att, int maxn, int H) {
   extern __shared__ float sc[];  // [maxn]
   __shared__ float red[32];
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(256) struct_attn_fwd_kernel(const float* __res
 }
 
 __global__ void __launch_bounds__(256) struct_attn_bwd_kernel(const float* __restrict__ ds, const float* __restrict__ t,
-                                                              const float* __restrict__ att, const bf16* __restrict__ w2,
+                                                              const float* __restrict__ att, const act_t* __restrict__ w2,
                                                               const int* __restrict__ seg, float* __restrict__ dt,
                                                               float* __restrict__ dw2, float* __restrict__ db2, int maxn, int H) {
   extern __shared__ float sm[];  // da[maxn], dsc[maxn]
@@ -551,7 +551,7 @@ extern "C" int k3m_count_labels(const long long* labels, int n, long long value,
 extern "C" int k3m_xent_fwd_bwd(void* logits, int ld, const long long* labels, const float* count, int M, int V,
                                 float grad_scale, float* loss, int write_grad, void* stream) {
   K3M_REQUIRE(M > 0 && V > 0 && ld >= V, "xent: bad shape");
-  xent_kernel<<<M, 256, 0, ST(stream)>>>((bf16*)logits, ld, labels, count, V, grad_scale, loss, write_grad);
+  xent_kernel<<<M, 256, 0, ST(stream)>>>((act_t*)logits, ld, labels, count, V, grad_scale, loss, write_grad);
   return k3m_check_launch("k3m_xent_fwd_bwd");
 }
 
@@ -559,7 +559,7 @@ extern "C" int k3m_kl_fwd_bwd(const float* logits, int ld, const float* target, 
                               const float* count, int B, int Lv1, int T, float grad_scale, float* loss, void* dlogits,
                               void* stream) {
   K3M_REQUIRE(B > 0 && Lv1 >= 2 && ld >= T, "kl: bad shape");
-  kl_kernel<<<B * Lv1, 256, 0, ST(stream)>>>(logits, ld, target, image_label, count, T, Lv1, grad_scale, loss, (bf16*)dlogits);
+  kl_kernel<<<B * Lv1, 256, 0, ST(stream)>>>(logits, ld, target, image_label, count, T, Lv1, grad_scale, loss, (act_t*)dlogits);
   return k3m_check_launch("k3m_kl_fwd_bwd");
 }
 
@@ -571,14 +571,14 @@ extern "C" int k3m_itm_loss(const float* pool_t, const float* pool_pv, const flo
   d.site = site;
   d.thresh = (rng && drop_p > 0.f) ? (unsigned int)(drop_p * 65536.0f + 0.5f) : 0u;
   d.scale = 1.0f / (1.0f - drop_p);
-  itm_kernel<<<B, 128, 0, ST(stream)>>>(pool_t, pool_pv, pool_v, (const bf16*)w, (const bf16*)b, l1, l2, l3, B, H, d, loss);
+  itm_kernel<<<B, 128, 0, ST(stream)>>>(pool_t, pool_pv, pool_v, (const act_t*)w, (const act_t*)b, l1, l2, l3, B, H, d, loss);
   return k3m_check_launch("k3m_itm_loss");
 }
 
 extern "C" int k3m_pair_cls_loss(const float* logits, int ld, const long long* labels, int B, float grad_scale,
                                  float* loss, float* probs, void* dlogits, int ldd, void* stream) {
   K3M_REQUIRE(B > 0 && ld >= 2, "pair_cls_loss: bad shape");
-  pair_cls_kernel<<<1, 128, 0, ST(stream)>>>(logits, ld, labels, B, grad_scale, loss, probs, (bf16*)dlogits, ldd);
+  pair_cls_kernel<<<1, 128, 0, ST(stream)>>>(logits, ld, labels, B, grad_scale, loss, probs, (act_t*)dlogits, ldd);
   return k3m_check_launch("k3m_pair_cls_loss");
 }
 
@@ -595,9 +595,9 @@ extern "C" int k3m_dropout(const void* x, int ldx, int x_f32, void* y, int ldy, 
   int g = (int)((n + 255) / 256);
   if (g > 148 * 8) g = 148 * 8;
   if (x_f32 && y_f32) dropout_kernel<float, float><<<g, 256, 0, ST(stream)>>>((const float*)x, ldx, (float*)y, ldy, rows, cols, ld_drop, d);
-  else if (x_f32) dropout_kernel<float, bf16><<<g, 256, 0, ST(stream)>>>((const float*)x, ldx, (bf16*)y, ldy, rows, cols, ld_drop, d);
-  else if (y_f32) dropout_kernel<bf16, float><<<g, 256, 0, ST(stream)>>>((const bf16*)x, ldx, (float*)y, ldy, rows, cols, ld_drop, d);
-  else dropout_kernel<bf16, bf16><<<g, 256, 0, ST(stream)>>>((const bf16*)x, ldx, (bf16*)y, ldy, rows, cols, ld_drop, d);
+  else if (x_f32) dropout_kernel<float, act_t><<<g, 256, 0, ST(stream)>>>((const float*)x, ldx, (act_t*)y, ldy, rows, cols, ld_drop, d);
+  else if (y_f32) dropout_kernel<act_t, float><<<g, 256, 0, ST(stream)>>>((const act_t*)x, ldx, (float*)y, ldy, rows, cols, ld_drop, d);
+  else dropout_kernel<act_t, act_t><<<g, 256, 0, ST(stream)>>>((const act_t*)x, ldx, (act_t*)y, ldy, rows, cols, ld_drop, d);
   return k3m_check_launch("k3m_dropout");
 }
 
@@ -607,7 +607,7 @@ extern "C" int k3m_pair_gather_fwd(const float* c_init, const void* seq, int lds
   size_t n = (size_t)P * H;
   int g = (int)((n + 255) / 256);
   if (g > 148 * 8) g = 148 * 8;
-  pair_gather_fwd_kernel<<<g, 256, 0, ST(stream)>>>(c_init, (const bf16*)seq, lds, pair_item, pair_rows, (bf16*)X, PV, P, H);
+  pair_gather_fwd_kernel<<<g, 256, 0, ST(stream)>>>(c_init, (const act_t*)seq, lds, pair_item, pair_rows, (act_t*)X, PV, P, H);
   return k3m_check_launch("k3m_pair_gather_fwd");
 }
 
@@ -635,13 +635,13 @@ extern "C" int k3m_struct_fallback_bwd(float* dt, float* dc_init, const int* fb,
 extern "C" int k3m_struct_attn_fwd(const float* t, const void* w2, const void* b2, const int* seg, float* s_out, float* att,
                                    int B, int maxn, int H, void* stream) {
   K3M_REQUIRE(maxn > 0 && maxn <= 8192, "struct_attn: bad maxn");
-  struct_attn_fwd_kernel<<<B, 256, maxn * sizeof(float), ST(stream)>>>(t, (const bf16*)w2, (const bf16*)b2, seg, s_out, att, maxn, H);
+  struct_attn_fwd_kernel<<<B, 256, maxn * sizeof(float), ST(stream)>>>(t, (const act_t*)w2, (const act_t*)b2, seg, s_out, att, maxn, H);
   return k3m_check_launch("k3m_struct_attn_fwd");
 }
 
 extern "C" int k3m_struct_attn_bwd(const float* ds, const float* t, const float* att, const void* w2, const int* seg,
                                    float* dt, float* dw2, float* db2, int B, int maxn, int H, void* stream) {
-  struct_attn_bwd_kernel<<<B, 256, 2 * maxn * sizeof(float), ST(stream)>>>(ds, t, att, (const bf16*)w2, seg, dt, dw2, db2, maxn, H);
+  struct_attn_bwd_kernel<<<B, 256, 2 * maxn * sizeof(float), ST(stream)>>>(ds, t, att, (const act_t*)w2, seg, dt, dw2, db2, maxn, H);
   return k3m_check_launch("k3m_struct_attn_bwd");
 }
 
@@ -677,7 +677,7 @@ extern "C" int k3m_adamw(float* p32, float* g32, float* m, float* v, void* p16, 
   return k3m_check_launch("k3m_adamw");
 }
 
-// gradient in bf16 (`g16`, e.g. the all-reduced send buffer of a data-parallel step); `g32` is the fp32 arena
+// gradient in act_t (`g16`, e.g. the all-reduced send buffer of a data-parallel step); `g32` is the fp32 arena
 // range to zero for the next step
 extern "C" int k3m_adamw_g16(float* p32, const void* g16, float* g32, float* m, float* v, void* p16, const float* hyper,
                              long long n, int zero_grad, void* stream) {

@@ -12,8 +12,8 @@ namespace {
 // Grouped form: up to 8 independent LayerNorms (the six streams of a connection stage, a text and an image layer)
 // in ONE launch; NV is sized for the widest of them.  A CTA (four rows) belongs to one problem.
 struct LnFwdProb {
-  const bf16 *x, *gamma, *beta;
-  bf16* y;
+  const act_t *x, *gamma, *beta;
+  act_t* y;
   float *mean, *rstd;
   int M, H;
   DropSpec drop;
@@ -46,14 +46,14 @@ __global__ void __launch_bounds__(256) ln_fwd_group_kernel(const __grid_constant
   };
   int pi, lr;
   locate(r, pi, lr);
-  uint4 cur[NV], nxt[NV];
+  Pack8 cur[NV], nxt[NV];
   {
     const LnFwdProb& P = g.p[pi];
-    const bf16* xr = P.x + (size_t)lr * P.H;
+    const act_t* xr = P.x + (size_t)lr * P.H;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = (lane + 32 * i) * 8;
-      if (c < P.H) cur[i] = *reinterpret_cast<const uint4*>(xr + c);
+      if (c < P.H) cur[i] = load_pack8(xr + c);
     }
   }
   while (true) {
@@ -63,11 +63,11 @@ __global__ void __launch_bounds__(256) ln_fwd_group_kernel(const __grid_constant
     if (more) {
       locate(rn, pn, ln_);
       const LnFwdProb& Q = g.p[pn];
-      const bf16* xr = Q.x + (size_t)ln_ * Q.H;
+      const act_t* xr = Q.x + (size_t)ln_ * Q.H;
 #pragma unroll
       for (int i = 0; i < NV; ++i) {
         const int c = (lane + 32 * i) * 8;
-        if (c < Q.H) nxt[i] = *reinterpret_cast<const uint4*>(xr + c);
+        if (c < Q.H) nxt[i] = load_pack8(xr + c);
       }
     }
     {
@@ -79,13 +79,9 @@ __global__ void __launch_bounds__(256) ln_fwd_group_kernel(const __grid_constant
       for (int i = 0; i < NV; ++i) {
         const int c = (lane + 32 * i) * 8;
         if (c < H) {
-          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&cur[i]);
+          unpack8(cur[i], v[i]);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float2 f = __bfloat1622float2(h[j]);
-            v[i][2 * j] = f.x; v[i][2 * j + 1] = f.y;
-            s += f.x + f.y;
-          }
+          for (int j = 0; j < 8; ++j) s += v[i][j];
         }
       }
       const float mean = warp_sum(s) / (float)H;
@@ -106,7 +102,7 @@ __global__ void __launch_bounds__(256) ln_fwd_group_kernel(const __grid_constant
         P.mean[lr] = mean;
         P.rstd[lr] = rstd;
       }
-      bf16* yr = P.y + (size_t)lr * H;
+      act_t* yr = P.y + (size_t)lr * H;
 #pragma unroll
       for (int i = 0; i < NV; ++i) {
         const int c = (lane + 32 * i) * 8;
@@ -134,17 +130,8 @@ __global__ void __launch_bounds__(256) ln_fwd_group_kernel(const __grid_constant
 }
 
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void unpack8(const uint4& u, float v[8]) {
-  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float2 f = __bfloat1622float2(h[i]);
-    v[2 * i] = f.x; v[2 * i + 1] = f.y;
-  }
-}
-
 // LayerNorm backward.  dy is optionally masked first by the post-LN dropout (drop_out).
-// dx -> bf16; if drop_in is set a second output dxm = dx * mask_in * scale is written (gradient of
+// dx -> act_t; if drop_in is set a second output dxm = dx * mask_in * scale is written (gradient of
 // the GEMM output that was dropped out before the residual add).  Column sums: dgamma += dy*xhat,
 // dbeta += dy, dbias += dxm  (fp32 atomics, one set per CTA after a grid-stride loop over rows).
 // cluster helpers: the column sums of the CTAs of a cluster are combined through distributed shared memory
@@ -168,14 +155,14 @@ __device__ __forceinline__ float ld_dsmem(const float* local, uint32_t rank) {
 // memory and each CTA of the cluster issues the atomics of 1/CL of the columns: CL x fewer same-address
 // atomics.  An experiment that did not pay (see k3m_ln_bwd below); selectable with K3M_LN_CLUSTER=1.
 template <int NV, int CL>
-__device__ __forceinline__ void ln_bwd_body(const bf16* __restrict__ dy, const bf16* __restrict__ x,
-                                            const bf16* __restrict__ gamma, const float* __restrict__ mean_in,
-                                            const float* __restrict__ rstd_in, bf16* __restrict__ dx,
-                                            bf16* __restrict__ dxm, float* __restrict__ dgamma,
+__device__ __forceinline__ void ln_bwd_body(const act_t* __restrict__ dy, const act_t* __restrict__ x,
+                                            const act_t* __restrict__ gamma, const float* __restrict__ mean_in,
+                                            const float* __restrict__ rstd_in, act_t* __restrict__ dx,
+                                            act_t* __restrict__ dxm, float* __restrict__ dgamma,
                                             float* __restrict__ dbeta, float* __restrict__ dbias, int M, int H,
                                             const DropSpec& drop_out, const DropSpec& drop_in, int cta, int nctas) {
   // Register budget: two CTAs (16 warps) per SM keep enough rows in flight to cover HBM latency; the
-  // row's dy / x stay packed as loaded (bf16) between the two passes and gamma is re-read (L1) per row,
+  // row's dy / x stay packed as loaded (act_t) between the two passes and gamma is re-read (L1) per row,
   // so the live state is the 3 x NV x 8 fp32 column-sum accumulators.
   extern __shared__ float sred[];  // [8 warps][3][H]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -186,14 +173,14 @@ __device__ __forceinline__ void ln_bwd_body(const bf16* __restrict__ dy, const b
     for (int j = 0; j < 8; ++j) ag[i][j] = ab[i][j] = ac[i][j] = 0.f;
   for (int row = cta * 8 + warp; row < M; row += nctas * 8) {
     const float mean = mean_in[row], rstd = rstd_in[row];
-    uint4 pd[NV], px[NV];
+    Pack8 pd[NV], px[NV];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = (lane + 32 * i) * 8;
       if (c < H) {
-        pd[i] = *reinterpret_cast<const uint4*>(dy + (size_t)row * H + c);
-        px[i] = *reinterpret_cast<const uint4*>(x + (size_t)row * H + c);
+        pd[i] = load_pack8(dy + (size_t)row * H + c);
+        px[i] = load_pack8(x + (size_t)row * H + c);
       }
     }
 #pragma unroll
@@ -298,10 +285,10 @@ __device__ __forceinline__ void ln_bwd_body(const bf16* __restrict__ dy, const b
 }
 
 template <int NV, int CL>
-__global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
-                                                        const bf16* __restrict__ gamma, const float* __restrict__ mean_in,
-                                                        const float* __restrict__ rstd_in, bf16* __restrict__ dx,
-                                                        bf16* __restrict__ dxm, float* __restrict__ dgamma,
+__global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const act_t* __restrict__ dy, const act_t* __restrict__ x,
+                                                        const act_t* __restrict__ gamma, const float* __restrict__ mean_in,
+                                                        const float* __restrict__ rstd_in, act_t* __restrict__ dx,
+                                                        act_t* __restrict__ dxm, float* __restrict__ dgamma,
                                                         float* __restrict__ dbeta, float* __restrict__ dbias, int M, int H,
                                                         DropSpec drop_out, DropSpec drop_in) {
   ln_bwd_body<NV, CL>(dy, x, gamma, mean_in, rstd_in, dx, dxm, dgamma, dbeta, dbias, M, H, drop_out, drop_in,
@@ -310,9 +297,9 @@ __global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_kernel(const bf16
 
 // Grouped form (see LnFwdGroup): every problem owns a contiguous range of CTAs, sized by its share of the rows.
 struct LnBwdProb {
-  const bf16 *dy, *x, *gamma;
+  const act_t *dy, *x, *gamma;
   const float *mean, *rstd;
-  bf16 *dx, *dxm;
+  act_t *dx, *dxm;
   float *dgamma, *dbeta, *dbias;
   int M, H;
   DropSpec drop_out, drop_in;
@@ -332,7 +319,7 @@ __global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_group_kernel(cons
 }
 
 // ---------------------------------------------------------------------------------------------
-// out[n] += sum_m x[m, n]   (x bf16 or fp32, row stride ld)
+// out[n] += sum_m x[m, n]   (x act_t or fp32, row stride ld)
 // generic: one column per lane (any ld / alignment)
 template <typename T>
 __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, int ld, float* __restrict__ out, int M, int N,
@@ -356,9 +343,9 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, in
   }
 }
 
-// bf16, 16-byte aligned rows: a warp reads 512 contiguous bytes of a row per instruction (8 columns per
+// act_t, 16-byte aligned rows: a warp reads 512 contiguous bytes of a row per instruction (8 columns per
 // lane), four rows in flight per warp; 256 columns per CTA, rows split over blockIdx.y
-__global__ void __launch_bounds__(256) colsum8_kernel(const bf16* __restrict__ x, int ld, float* __restrict__ out, int M,
+__global__ void __launch_bounds__(256) colsum8_kernel(const act_t* __restrict__ x, int ld, float* __restrict__ out, int M,
                                                       int N, int rows_per_cta) {
   __shared__ float sred[8][256];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -462,7 +449,7 @@ __global__ void scale_dev_kernel(T* x, const float* __restrict__ alpha, int rows
 }
 
 // dx = dy * gelu'(pre)
-__global__ void dgelu_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ pre, bf16* __restrict__ dx, size_t n8) {
+__global__ void dgelu_kernel(const act_t* __restrict__ dy, const act_t* __restrict__ pre, act_t* __restrict__ dx, size_t n8) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
     float a[8], b[8];
     ld8(dy + i * 8, a);
@@ -507,7 +494,7 @@ extern "C" int k3m_ln_fwd(const void* x, const void* gamma, const void* beta, vo
   g.n = 1;
   g.eps = eps;
   LnFwdProb& P = g.p[0];
-  P.x = (const bf16*)x; P.gamma = (const bf16*)gamma; P.beta = (const bf16*)beta; P.y = (bf16*)y;
+  P.x = (const act_t*)x; P.gamma = (const act_t*)gamma; P.beta = (const act_t*)beta; P.y = (act_t*)y;
   P.mean = mean; P.rstd = rstd; P.M = M; P.H = H; P.drop = d; P.cta_begin = 0;
   for (int i = 1; i < 8; ++i) g.p[i] = g.p[0];
   int ctas = (M + 7) / 8;
@@ -560,11 +547,11 @@ extern "C" int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, cons
       at[0].val.clusterDim.z = 1;                                                                                    \
       lc.attrs = at;                                                                                                 \
       lc.numAttrs = 1;                                                                                               \
-      cudaLaunchKernelEx(&lc, ln_bwd_kernel<NV, CL>, (const bf16*)dy, (const bf16*)x, (const bf16*)gamma, mean, rstd, \
-                         (bf16*)dx, (bf16*)dxm, dgamma, dbeta, dbias, M, H, dout, din);                              \
+      cudaLaunchKernelEx(&lc, ln_bwd_kernel<NV, CL>, (const act_t*)dy, (const act_t*)x, (const act_t*)gamma, mean, rstd, \
+                         (act_t*)dx, (act_t*)dxm, dgamma, dbeta, dbias, M, H, dout, din);                              \
     } else {                                                                                                         \
-      ln_bwd_kernel<NV, 1><<<grid, 256, smem, st>>>((const bf16*)dy, (const bf16*)x, (const bf16*)gamma, mean, rstd,  \
-                                                    (bf16*)dx, (bf16*)dxm, dgamma, dbeta, dbias, M, H, dout, din);   \
+      ln_bwd_kernel<NV, 1><<<grid, 256, smem, st>>>((const act_t*)dy, (const act_t*)x, (const act_t*)gamma, mean, rstd,  \
+                                                    (act_t*)dx, (act_t*)dxm, dgamma, dbeta, dbias, M, H, dout, din);   \
     }                                                                                                                \
   } while (0)
   if (nv <= 1) LN_BWD(1);
@@ -607,8 +594,8 @@ extern "C" int k3m_ln_fwd_grouped(const void* descs, int n, float eps, void* str
   for (int i = 0; i < n; ++i) {
     K3M_REQUIRE(d[i].M > 0 && d[i].H > 0 && d[i].H % 8 == 0 && d[i].H <= 4096, "ln_fwd_grouped: need H %% 8 == 0 and H <= 4096 (H=%d)", d[i].H);
     LnFwdProb& P = g.p[i];
-    P.x = (const bf16*)d[i].x; P.gamma = (const bf16*)d[i].gamma; P.beta = (const bf16*)d[i].beta;
-    P.y = (bf16*)d[i].y; P.mean = d[i].mean; P.rstd = d[i].rstd; P.M = d[i].M; P.H = d[i].H;
+    P.x = (const act_t*)d[i].x; P.gamma = (const act_t*)d[i].gamma; P.beta = (const act_t*)d[i].beta;
+    P.y = (act_t*)d[i].y; P.mean = d[i].mean; P.rstd = d[i].rstd; P.M = d[i].M; P.H = d[i].H;
     P.drop = make_drop(d[i].rng, d[i].site, d[i].drop_p);
     P.cta_begin = 0;
     ctas += d[i].M;
@@ -646,8 +633,8 @@ extern "C" int k3m_ln_bwd_grouped(const void* descs, int n, void* stream) {
   int ctas = 0;
   for (int i = 0; i < n; ++i) {
     LnBwdProb& P = g.p[i];
-    P.dy = (const bf16*)d[i].dy; P.x = (const bf16*)d[i].x; P.gamma = (const bf16*)d[i].gamma;
-    P.mean = d[i].mean; P.rstd = d[i].rstd; P.dx = (bf16*)d[i].dx; P.dxm = (bf16*)d[i].dxm;
+    P.dy = (const act_t*)d[i].dy; P.x = (const act_t*)d[i].x; P.gamma = (const act_t*)d[i].gamma;
+    P.mean = d[i].mean; P.rstd = d[i].rstd; P.dx = (act_t*)d[i].dx; P.dxm = (act_t*)d[i].dxm;
     P.dgamma = d[i].dgamma; P.dbeta = d[i].dbeta; P.dbias = d[i].dbias; P.M = d[i].M; P.H = d[i].H;
     P.drop_out = make_drop(d[i].rng, d[i].site_out, d[i].p_out);
     P.drop_in = make_drop(d[i].rng, d[i].site_in, d[i].p_in);
@@ -689,7 +676,7 @@ extern "C" int k3m_colsum(const void* x, int ld, int x_f32, float* out, int M, i
     if (gy > (M + 63) / 64) gy = (M + 63) / 64;   // at least 64 rows per CTA
     if (gy < 1) gy = 1;
     const int rows_per = (M + gy - 1) / gy;
-    colsum8_kernel<<<dim3(gx, gy), 256, 0, st>>>((const bf16*)x, ld, out, M, N, rows_per);
+    colsum8_kernel<<<dim3(gx, gy), 256, 0, st>>>((const act_t*)x, ld, out, M, N, rows_per);
     return k3m_check_launch("k3m_colsum");
   }
   int gy = (M + 255) / 256;
@@ -697,17 +684,17 @@ extern "C" int k3m_colsum(const void* x, int ld, int x_f32, float* out, int M, i
   const int rows_per = (M + gy - 1) / gy;
   dim3 grid((N + 31) / 32, gy);
   if (x_f32) colsum_kernel<float><<<grid, 256, 0, st>>>((const float*)x, ld, out, M, N, rows_per);
-  else colsum_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)x, ld, out, M, N, rows_per);
+  else colsum_kernel<act_t><<<grid, 256, 0, st>>>((const act_t*)x, ld, out, M, N, rows_per);
   return k3m_check_launch("k3m_colsum");
 }
 
 extern "C" int k3m_cast(const void* x, int x_f32, void* y, int y_f32, long long n, void* stream) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int g = grid_for((size_t)n, 256);
-  if (x_f32 && !y_f32) cast_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)x, (bf16*)y, (size_t)n);
-  else if (!x_f32 && y_f32) cast_kernel<bf16, float><<<g, 256, 0, st>>>((const bf16*)x, (float*)y, (size_t)n);
+  if (x_f32 && !y_f32) cast_kernel<float, act_t><<<g, 256, 0, st>>>((const float*)x, (act_t*)y, (size_t)n);
+  else if (!x_f32 && y_f32) cast_kernel<act_t, float><<<g, 256, 0, st>>>((const act_t*)x, (float*)y, (size_t)n);
   else if (x_f32) cast_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, (float*)y, (size_t)n);
-  else cast_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)x, (bf16*)y, (size_t)n);
+  else cast_kernel<act_t, act_t><<<g, 256, 0, st>>>((const act_t*)x, (act_t*)y, (size_t)n);
   return k3m_check_launch("k3m_cast");
 }
 
@@ -719,13 +706,13 @@ extern "C" int k3m_lincomb3(const void* a, int lda, const void* b, int ldb, cons
     lincomb3_kernel<float, float><<<g, 256, 0, st>>>((const float*)a, (const float*)b, (const float*)c, wa, wb, wc,
                                                      (float*)out, rows, cols, lda, ldb, ldc, ldo);
   else if (!in_f32 && !out_f32)
-    lincomb3_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)a, (const bf16*)b, (const bf16*)c, wa, wb, wc,
-                                                   (bf16*)out, rows, cols, lda, ldb, ldc, ldo);
+    lincomb3_kernel<act_t, act_t><<<g, 256, 0, st>>>((const act_t*)a, (const act_t*)b, (const act_t*)c, wa, wb, wc,
+                                                   (act_t*)out, rows, cols, lda, ldb, ldc, ldo);
   else if (in_f32)
-    lincomb3_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)a, (const float*)b, (const float*)c, wa, wb, wc,
-                                                    (bf16*)out, rows, cols, lda, ldb, ldc, ldo);
+    lincomb3_kernel<float, act_t><<<g, 256, 0, st>>>((const float*)a, (const float*)b, (const float*)c, wa, wb, wc,
+                                                    (act_t*)out, rows, cols, lda, ldb, ldc, ldo);
   else
-    lincomb3_kernel<bf16, float><<<g, 256, 0, st>>>((const bf16*)a, (const bf16*)b, (const bf16*)c, wa, wb, wc,
+    lincomb3_kernel<act_t, float><<<g, 256, 0, st>>>((const act_t*)a, (const act_t*)b, (const act_t*)c, wa, wb, wc,
                                                     (float*)out, rows, cols, lda, ldb, ldc, ldo);
   return k3m_check_launch("k3m_lincomb3");
 }
@@ -737,16 +724,16 @@ extern "C" int k3m_axpy(const void* x, int ldx, int x_f32, void* y, int ldy, int
   if (cols % 8 == 0 && ok(x, ldx, x_f32) && ok(y, ldy, y_f32) && (size_t)rows * cols < (1u << 31)) {
     const int g8 = grid_for((size_t)rows * cols / 8, 256);
     if (x_f32 && y_f32) axpy8_kernel<float, float><<<g8, 256, 0, st>>>((const float*)x, (float*)y, alpha, rows, cols / 8, ldx, ldy);
-    else if (!x_f32 && !y_f32) axpy8_kernel<bf16, bf16><<<g8, 256, 0, st>>>((const bf16*)x, (bf16*)y, alpha, rows, cols / 8, ldx, ldy);
-    else if (x_f32) axpy8_kernel<float, bf16><<<g8, 256, 0, st>>>((const float*)x, (bf16*)y, alpha, rows, cols / 8, ldx, ldy);
-    else axpy8_kernel<bf16, float><<<g8, 256, 0, st>>>((const bf16*)x, (float*)y, alpha, rows, cols / 8, ldx, ldy);
+    else if (!x_f32 && !y_f32) axpy8_kernel<act_t, act_t><<<g8, 256, 0, st>>>((const act_t*)x, (act_t*)y, alpha, rows, cols / 8, ldx, ldy);
+    else if (x_f32) axpy8_kernel<float, act_t><<<g8, 256, 0, st>>>((const float*)x, (act_t*)y, alpha, rows, cols / 8, ldx, ldy);
+    else axpy8_kernel<act_t, float><<<g8, 256, 0, st>>>((const act_t*)x, (float*)y, alpha, rows, cols / 8, ldx, ldy);
     return k3m_check_launch("k3m_axpy");
   }
   const int g = grid_for((size_t)rows * cols, 256);
   if (x_f32 && y_f32) axpy_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, (float*)y, alpha, rows, cols, ldx, ldy);
-  else if (!x_f32 && !y_f32) axpy_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)x, (bf16*)y, alpha, rows, cols, ldx, ldy);
-  else if (x_f32) axpy_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)x, (bf16*)y, alpha, rows, cols, ldx, ldy);
-  else axpy_kernel<bf16, float><<<g, 256, 0, st>>>((const bf16*)x, (float*)y, alpha, rows, cols, ldx, ldy);
+  else if (!x_f32 && !y_f32) axpy_kernel<act_t, act_t><<<g, 256, 0, st>>>((const act_t*)x, (act_t*)y, alpha, rows, cols, ldx, ldy);
+  else if (x_f32) axpy_kernel<float, act_t><<<g, 256, 0, st>>>((const float*)x, (act_t*)y, alpha, rows, cols, ldx, ldy);
+  else axpy_kernel<act_t, float><<<g, 256, 0, st>>>((const act_t*)x, (float*)y, alpha, rows, cols, ldx, ldy);
   return k3m_check_launch("k3m_axpy");
 }
 
@@ -761,14 +748,14 @@ extern "C" int k3m_scale_dev(void* x, int ld, int x_f32, const float* alpha, int
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int g = grid_for((size_t)rows * cols, 256);
   if (x_f32) scale_dev_kernel<float><<<g, 256, 0, st>>>((float*)x, alpha, rows, cols, ld);
-  else scale_dev_kernel<bf16><<<g, 256, 0, st>>>((bf16*)x, alpha, rows, cols, ld);
+  else scale_dev_kernel<act_t><<<g, 256, 0, st>>>((act_t*)x, alpha, rows, cols, ld);
   return k3m_check_launch("k3m_scale_dev");
 }
 
 extern "C" int k3m_dgelu_mul(const void* dy, const void* pre, void* dx, long long n, void* stream) {
   K3M_REQUIRE(n % 8 == 0, "dgelu_mul: n must be a multiple of 8");
   dgelu_kernel<<<grid_for((size_t)n / 8, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      (const bf16*)dy, (const bf16*)pre, (bf16*)dx, (size_t)n / 8);
+      (const act_t*)dy, (const act_t*)pre, (act_t*)dx, (size_t)n / 8);
   return k3m_check_launch("k3m_dgelu_mul");
 }
 

@@ -27,7 +27,7 @@ def _ld(t):
 def _isf32(t):
     if t.dtype == torch.float32:
         return 1
-    assert t.dtype == torch.bfloat16, t.dtype
+    assert t.dtype == torch.bfloat16, t.dtype       # (fp32 check build: every tensor is fp32 and takes the branch above)
     return 0
 
 
@@ -53,11 +53,14 @@ class _LnBwdDesc(_c.Structure):
 
 
 class CudaOps(object):
-    def __init__(self, device=None):
+    def __init__(self, device=None, act_dtype=torch.bfloat16):
+        """`act_dtype=torch.float32` selects the fp32 CHECK build of the library (tests only: every activation and
+        weight in fp32, CUDA-core GEMM / attention); the product is bf16."""
         if not torch.cuda.is_available():
             raise _lib.K3MError("k3m_b200 needs a CUDA device (sm_100a); there is no CPU path")
-        self.lib = _lib.load()
-        self.adt = torch.bfloat16
+        assert act_dtype in (torch.bfloat16, torch.float32)
+        self.adt = act_dtype
+        self.lib = _lib.load() if act_dtype == torch.bfloat16 else _lib.load_f32()
         self.device = torch.device(device if device is not None else "cuda")
         self.launches = 0
         # profiling aid (bench.py): when a list, every launch is bracketed by CUDA events on the
@@ -160,11 +163,11 @@ class CudaOps(object):
         if self.record is not None and name in self.record:
             self.record[name].append((args, self._bytes))
         if self.timing is None:
-            _lib.check(getattr(self.lib, name)(*args), name)
+            _lib.check(getattr(self.lib, name)(*args), name, self.lib)
             return
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        _lib.check(getattr(self.lib, name)(*args), name)
+        _lib.check(getattr(self.lib, name)(*args), name, self.lib)
         e1.record()
         self.timing.append((name + self._tag, self._work, e0, e1))
         self._work = 0.0
@@ -184,7 +187,7 @@ class CudaOps(object):
     # ---- GEMM ------------------------------------------------------------------------------
     def gemm(self, a, b, layout, out=None, out_dtype=None, bias=None, act=ACT_NONE, aux_in=None,
              aux_out=None, addend=None, drop=None, rng=None, accumulate=False):
-        assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+        assert a.dtype == self.adt and b.dtype == self.adt
         if layout == "nt":
             M, K = a.shape
             N = b.shape[0]
@@ -233,7 +236,7 @@ class CudaOps(object):
             work, tags = 0.0, []
             for d, c in zip(arr, chunk):
                 a, b, layout = c["a"], c["b"], c["layout"]
-                assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and layout == chunk[0]["layout"]
+                assert a.dtype == self.adt and b.dtype == self.adt and layout == chunk[0]["layout"]
                 if layout == "nt":
                     (M, K), N = a.shape, b.shape[0]
                     assert b.shape[1] == K
