@@ -310,6 +310,60 @@ def build_step(workload, dev, group):
     return step, host, B
 
 
+def class_api_rate(dev, steps, warmup=4):
+    """The same workload through the DROP-IN CLASS API a reference driver uses (`pretrain.py:986-1110`): host batch ->
+    `model(...)` -> `loss = out[0] + out[1] + out[3] + out[9]` -> `loss.backward()` -> `torch.optim.AdamW.step()` ->
+    `zero_grad()`, one loss read per step.  From the second step of a geometry on, forward and backward are two CUDA
+    graph replays.  -> (samples/s, ms per step)"""
+    import torch
+    from k3m_b200.layout import is_no_decay
+    from k3m_b200.synth import FORWARD_ORDER, synth_batch
+    from k3m_b200.vilbert_k3m import BertForMultiModalPreTraining_tri_stru
+    cfg = make_cfg()
+    torch.manual_seed(0)
+    model = BertForMultiModalPreTraining_tri_stru(cfg).to(dev)
+    model.train()
+    named = list(model.named_parameters())
+    groups = [dict(params=[p for n, p in named if not is_no_decay(n)], weight_decay=0.01),
+              dict(params=[p for n, p in named if is_no_decay(n)], weight_decay=0.0)]
+    opt = torch.optim.AdamW(groups, lr=1e-4, betas=(0.9, 0.98), eps=1e-8, fused=True)
+    B, d = PER_GPU_BATCH, DIMS
+    host = []
+    for i in range(4):
+        b = synth_batch(cfg, B, d["len_t"], d["len_v"], d["len_pv"], d["max_num_pv"], seed=4321 + i)
+        host.append({k: (v.pin_memory() if k not in ("index_p", "index_v") else v) for k, v in b.items()})
+
+    def one(b):
+        out = model(*[b[k] for k in FORWARD_ORDER], input_ids_pv=b["input_ids_pv"], token_type_ids_pv=b["token_type_ids_pv"],
+                    attention_mask_pv=b["attention_mask_pv"], masked_lm_labels_pv=b["masked_lm_labels_pv"],
+                    next_sentence_label_pv_v=b["next_sentence_label_pv_v"], next_sentence_label_pv_t=b["next_sentence_label_pv_t"],
+                    index_p=b["index_p"], index_v=b["index_v"])
+        loss = out[0] + out[1] + out[3] + out[9]
+        loss.backward()
+        opt.step()
+        opt.zero_grad(set_to_none=False)
+        return loss
+
+    for i in range(warmup):
+        one(host[i % 4])
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    last = None
+    for i in range(steps):
+        loss = one(host[i % 4])
+        if last is not None:
+            float(last)                  # the previous step's loss: one device -> host read per step, one step late
+        last = loss
+    float(last)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    del model, opt
+    torch.cuda.empty_cache()
+    return B / (ms * 1e-3), ms
+
+
 def run_gpu_arm(args):
     import torch
     import torch.distributed as dist
@@ -461,6 +515,14 @@ def run_gpu_arm(args):
     }
     if comm is not None:
         line["comm"] = comm
+    if world == 1 and args.workload == "base" and not args.no_class_api:
+        del step
+        torch.cuda.empty_cache()
+        v, ms = class_api_rate(dev, max(5, min(args.steps, 20)))
+        line["e2e_class_api"] = {"value": v, "unit": UNIT, "ms_per_step": ms, "api": "BertForMultiModalPreTraining_tri_stru(...) "
+                                 "forward -> loss.backward() -> torch.optim.AdamW(fused).step(), host batch in pinned memory, one "
+                                 "loss read per step (the drop-in class path of pretrain.py:986-1110; forward and backward replay "
+                                 "CUDA graphs)", "ratio_to_e2e": v / line["e2e"]["value"]}
     if world == 1 and not args.no_cpu_baseline and args.workload == "base":
         v, sec, threads, batch = cpu_reference_step_rate(8, 2)       # ~15-25 s of host work on the GPU box
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
@@ -478,6 +540,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="k3m_b200", choices=["k3m_b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-class-api", action="store_true", help="skip the class-API end-to-end measurement")
     ap.add_argument("--no-breakdown", action="store_true", help="timing only: skip the per-kernel breakdown / roofline replays")
     ap.add_argument("--workload", default="base", choices=sorted(WORKLOADS),
                     help="base = BASELINE configs[1]/[2] (the headline); long = configs[3]; align = configs[4]")

@@ -96,6 +96,9 @@ typedef struct K3MLnBwdDesc {
 int k3m_ln_fwd_grouped(const K3MLnFwdDesc* problems, int n, float eps, void* stream);
 int k3m_ln_bwd_grouped(const K3MLnBwdDesc* problems, int n, void* stream);
 int k3m_colsum(const void* x, int ld, int x_f32, float* out, int M, int N, void* stream);
+/* grouped form: n (1..8) column sums in one launch; x in the activation type, N % 8 == 0, ld % 8 == 0       */
+typedef struct K3MColsumDesc { const void* x; int ld; float* out; int M, N; } K3MColsumDesc;
+int k3m_colsum_grouped(const K3MColsumDesc* problems, int n, void* stream);
 int k3m_cast(const void* x, int x_f32, void* y, int y_f32, long long n, void* stream);
 int k3m_lincomb3(const void* a, int lda, const void* b, int ldb, const void* c, int ldc, float wa,
                  float wb, float wc, int in_f32, void* out, int ldo, int out_f32, int rows, int cols,

@@ -345,12 +345,12 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, in
 
 // act_t, 16-byte aligned rows: a warp reads 512 contiguous bytes of a row per instruction (8 columns per
 // lane), four rows in flight per warp; 256 columns per CTA, rows split over blockIdx.y
-__global__ void __launch_bounds__(256) colsum8_kernel(const act_t* __restrict__ x, int ld, float* __restrict__ out, int M,
-                                                      int N, int rows_per_cta) {
+__device__ __forceinline__ void colsum8_body(const act_t* __restrict__ x, int ld, float* __restrict__ out, int M, int N,
+                                             int rows_per_cta, int bx, int by) {
   __shared__ float sred[8][256];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int col = blockIdx.x * 256 + lane * 8;
-  const int r0 = blockIdx.y * rows_per_cta;
+  const int col = bx * 256 + lane * 8;
+  const int r0 = by * rows_per_cta;
   int r1 = r0 + rows_per_cta;
   if (r1 > M) r1 = M;
   float acc[8];
@@ -377,13 +377,34 @@ __global__ void __launch_bounds__(256) colsum8_kernel(const act_t* __restrict__ 
 #pragma unroll
   for (int j = 0; j < 8; ++j) sred[warp][lane * 8 + j] = acc[j];
   __syncthreads();
-  const int c = blockIdx.x * 256 + threadIdx.x;
+  const int c = bx * 256 + threadIdx.x;
   if (c < N) {
     float t = 0.f;
 #pragma unroll
     for (int w = 0; w < 8; ++w) t += sred[w][threadIdx.x];
     atomicAdd(out + c, t);
   }
+}
+__global__ void __launch_bounds__(256) colsum8_kernel(const act_t* __restrict__ x, int ld, float* __restrict__ out, int M,
+                                                      int N, int rows_per_cta) {
+  colsum8_body(x, ld, out, M, N, rows_per_cta, (int)blockIdx.x, (int)blockIdx.y);
+}
+// grouped form: the bias gradients of up to 8 independent problems (the streams of a lock-step stage) in one launch
+struct ColsumProb {
+  const act_t* x;
+  float* out;
+  int ld, M, N, rows_per, gx, cta_begin;
+};
+struct ColsumGroup {
+  int n;
+  ColsumProb p[8];
+};
+__global__ void __launch_bounds__(256) colsum8_group_kernel(const __grid_constant__ ColsumGroup g) {
+  int pi = 0;
+  while (pi + 1 < g.n && (int)blockIdx.x >= g.p[pi + 1].cta_begin) ++pi;
+  const ColsumProb& P = g.p[pi];
+  const int l = (int)blockIdx.x - P.cta_begin;
+  colsum8_body(P.x, P.ld, P.out, P.M, P.N, P.rows_per, l % P.gx, l / P.gx);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -686,6 +707,38 @@ extern "C" int k3m_colsum(const void* x, int ld, int x_f32, float* out, int M, i
   if (x_f32) colsum_kernel<float><<<grid, 256, 0, st>>>((const float*)x, ld, out, M, N, rows_per);
   else colsum_kernel<act_t><<<grid, 256, 0, st>>>((const act_t*)x, ld, out, M, N, rows_per);
   return k3m_check_launch("k3m_colsum");
+}
+
+struct ColsumDesc {      // == K3MColsumDesc of include/k3m.h
+  const void* x;
+  int ld;
+  float* out;
+  int M, N;
+};
+extern "C" int k3m_colsum_grouped(const void* descs, int n, void* stream) {
+  const ColsumDesc* d = reinterpret_cast<const ColsumDesc*>(descs);
+  K3M_REQUIRE(n >= 1 && n <= 8, "colsum_grouped: 1..8 problems per launch (got %d)", n);
+  ColsumGroup g;
+  g.n = n;
+  int total_cols = 0;
+  for (int i = 0; i < n; ++i) total_cols += (d[i].N + 255) / 256;
+  int ctas = 0;
+  for (int i = 0; i < n; ++i) {
+    K3M_REQUIRE(d[i].M > 0 && d[i].N > 0 && d[i].N % 8 == 0 && d[i].ld % 8 == 0 && (((uintptr_t)d[i].x) & 15) == 0,
+                "colsum_grouped: activation-type input with N %% 8 == 0, ld %% 8 == 0, 16-byte aligned");
+    ColsumProb& P = g.p[i];
+    P.x = (const act_t*)d[i].x; P.out = d[i].out; P.ld = d[i].ld; P.M = d[i].M; P.N = d[i].N;
+    P.gx = (d[i].N + 255) / 256;
+    int gy = (148 * 4 + total_cols - 1) / total_cols;      // ~4 CTAs per SM over the whole group
+    if (gy > (d[i].M + 63) / 64) gy = (d[i].M + 63) / 64;
+    if (gy < 1) gy = 1;
+    P.rows_per = (d[i].M + gy - 1) / gy;
+    P.cta_begin = ctas;
+    ctas += P.gx * gy;
+  }
+  for (int i = n; i < 8; ++i) g.p[i] = g.p[0];
+  colsum8_group_kernel<<<ctas, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(g);
+  return k3m_check_launch("k3m_colsum_grouped");
 }
 
 extern "C" int k3m_cast(const void* x, int x_f32, void* y, int y_f32, long long n, void* stream) {

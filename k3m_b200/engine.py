@@ -101,6 +101,16 @@ class Engine(object):
         g = self.G(bname)
         self._aux(lambda: self.ops.colsum(dy, g), (dy,))
 
+    def bgrads(self, items):
+        """G[b] += column sums of dy for every (dy, bname): one grouped launch on the auxiliary stream."""
+        grp = getattr(self.ops, "colsum_group", None)
+        if grp is None or len(items) == 1:
+            for dy, b in items:
+                self.bgrad(dy, b)
+            return
+        pairs = [(dy, self.G(b)) for dy, b in items]
+        self._aux(lambda: grp(pairs), tuple(dy for dy, _ in items))
+
     def _aux(self, fn, keep):
         """Weight / bias gradients feed only the optimizer: they leave the dgrad chain (the critical
         path of backward) for an auxiliary stream when the op table has one."""
@@ -202,8 +212,7 @@ class Engine(object):
         self.wgrads([(lns[i][1], it[1][2], it[1][8] + ".dense.weight") for i, it in enumerate(items)])
         dpres = self.gemms([dict(a=lns[i][1], b=self.W(it[1][8] + ".dense.weight"), layout="nn", rng=self.rng,
                                  act=ACT_DGELU, aux_in=it[1][1]) for i, it in enumerate(items)])
-        for i, it in enumerate(items):
-            self.bgrad(dpres[i], it[1][7] + ".dense.bias")
+        self.bgrads([(dpres[i], it[1][7] + ".dense.bias") for i, it in enumerate(items)])
         self.wgrads([(dpres[i], it[1][0], it[1][7] + ".dense.weight") for i, it in enumerate(items)])
         return self.gemms([dict(a=dpres[i], b=self.W(it[1][7] + ".dense.weight"), layout="nn", rng=self.rng,
                                 addend=lns[i][0]) for i, it in enumerate(items)])
@@ -258,8 +267,7 @@ class Engine(object):
                                  sg.B, heads, sg.L, sg.L, d, drop=s, rng=self.rng)
             return run
         self._each([attn(i) for i in range(len(items))])
-        for i, (_, sv) in enumerate(items):
-            self.bgrad(dqkvs[i], sv[0] + ".attention.self.qkv.bias")
+        self.bgrads([(dqkvs[i], sv[0] + ".attention.self.qkv.bias") for i, (_, sv) in enumerate(items)])
         self.wgrads([(dqkvs[i], sv[1], sv[0] + ".attention.self.qkv.weight") for i, (_, sv) in enumerate(items)])
         return self.gemms([dict(a=dqkvs[i], b=self.W(sv[0] + ".attention.self.qkv.weight"), layout="nn", rng=self.rng,
                                 addend=ao[i][0]) for i, (_, sv) in enumerate(items)])
@@ -341,16 +349,16 @@ class Engine(object):
                              sg1.B, heads, sg1.L, sg2.L, d, drop=s2, rng=self.rng)
             return run
         self._each([attn(i) for i in range(len(items))])
-        wg, calls = [], []
+        wg, bg, calls = [], [], []
         for i, (_, _, sv, dx1_out, dx2_out) in enumerate(items):
             b = sv[0] + ".biattention."
-            self.bgrad(dq[i][0], b + "qkv1.bias")
-            self.bgrad(dq[i][1], b + "qkv2.bias")
+            bg += [(dq[i][0], b + "qkv1.bias"), (dq[i][1], b + "qkv2.bias")]
             wg += [(dq[i][0], sv[1], b + "qkv1.weight"), (dq[i][1], sv[3], b + "qkv2.weight")]
             calls.append(dict(a=dq[i][0], b=self.W(b + "qkv1.weight"), layout="nn", rng=self.rng, addend=ao[2 * i][0],
                               out=dx1_out))
             calls.append(dict(a=dq[i][1], b=self.W(b + "qkv2.weight"), layout="nn", rng=self.rng, addend=ao[2 * i + 1][0],
                               out=dx2_out))
+        self.bgrads(bg)
         self.wgrads(wg)
         self.gemms(calls)
 

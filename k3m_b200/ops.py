@@ -39,6 +39,11 @@ class _GemmDesc(_c.Structure):
                 ("ld_add", _i), ("addend_f32", _i), ("rng", _vp), ("drop_site", _u), ("drop_p", _f)]
 
 
+class _ColsumDesc(_c.Structure):
+    """K3MColsumDesc of include/k3m.h"""
+    _fields_ = [("x", _vp), ("ld", _i), ("out", _vp), ("M", _i), ("N", _i)]
+
+
 class _LnFwdDesc(_c.Structure):
     """K3MLnFwdDesc of include/k3m.h"""
     _fields_ = [("x", _vp), ("gamma", _vp), ("beta", _vp), ("y", _vp), ("mean", _vp), ("rstd", _vp), ("M", _i), ("H", _i),
@@ -278,6 +283,23 @@ class CudaOps(object):
     def gemm_last_variant(self):
         return self.lib.k3m_gemm_last_variant().decode()
 
+    def colsum_group(self, items):
+        """items: [(x, out)] -> out += column sums of x, one launch (`k3m_colsum_grouped`)"""
+        ok = all(x.dtype == self.adt and x.dtype != torch.float32 and x.shape[1] % 8 == 0 and _ld(x) % 8 == 0
+                 and x.data_ptr() % 16 == 0 for x, _ in items)
+        if len(items) == 1 or not self.use_groups or not ok:
+            for x, out in items:
+                self.colsum(x, out)
+            return
+        for i0 in range(0, len(items), 8):
+            chunk = items[i0:i0 + 8]
+            arr = (_ColsumDesc * len(chunk))()
+            for d, (x, out) in zip(arr, chunk):
+                d.x, d.ld, d.out, d.M, d.N = x.data_ptr(), _ld(x), out.data_ptr(), x.shape[0], x.shape[1]
+            if self.timing is not None:
+                self._bytes = sum(self._nb(x, out) for x, out in chunk)
+            self._call("k3m_colsum_grouped", arr, _i(len(chunk)), self._st())
+
     def colsum(self, x, out):
         if self.timing is not None:
             self._bytes = self._nb(x, out)
@@ -331,6 +353,15 @@ class CudaOps(object):
         -> [(dx, dxm or dx)]."""
         if len(items) == 1 or not self.use_groups:
             return [self.ln_bwd(**it) for it in items]
+        # one launch per register class of the kernel: hidden <= 768 runs two CTAs per SM (3 vectors per lane), hidden
+        # 1024 only one — a mixed launch would run every problem at the wide kernel's occupancy (55 vs 22 us)
+        wide = [i for i, it in enumerate(items) if it["x"].shape[1] > 768]
+        if 0 < len(wide) < len(items):
+            res = [None] * len(items)
+            for idx in (wide, [i for i in range(len(items)) if i not in wide]):
+                for i, r in zip(idx, self.ln_bwd_group([items[i] for i in idx])):
+                    res[i] = r
+            return res
         res, nbytes = [], 0.0
         arr = (_LnBwdDesc * len(items))()
         for d, it in zip(arr, items):

@@ -36,7 +36,7 @@ from torch import nn
 from .config import BertConfig  # noqa: F401  (re-exported under the reference's module path)
 from .engine import Engine
 from .layout import ArenaLayout, TIED_ALIAS
-from .struct_plan import build_struct_plan
+from .struct_plan import build_struct_plan, pad_struct_plan, plan_capacity
 
 logger = logging.getLogger(__name__)
 
@@ -50,18 +50,76 @@ class _Node(nn.Module):
         raise RuntimeError("k3m_b200 modules are parameter containers; call the model's forward()")
 
 
+class _GraphedStep(object):
+    """Forward and backward of one input geometry as two CUDA graphs (shared memory pool): the class API then costs
+    two graph launches per step instead of ~640 Python -> ctypes launches (~25 ms of host time against an 18 ms
+    device step).  Inputs are copied into static buffers; the aggregator plan is padded to its capacity
+    (`pad_struct_plan`), the four upstream loss gradients live in static device scalars."""
+
+    def __init__(self, owner, batch, max_num_pv):
+        dev = owner._arena.device
+        cfg = owner.config
+        self.owner = owner
+        self.inputs = {k: torch.empty_like(v) for k, v in batch.items()}
+        self.B, self.max_num_pv = batch["input_ids"].shape[0], max_num_pv
+        P_cap, T_cap, maxn = plan_capacity(self.B, max_num_pv, cfg.num_negative_pv)
+        i32 = torch.int32
+        self.plan = dict(pair_item=torch.zeros(P_cap, dtype=i32, device=dev), pair_rows=torch.zeros(P_cap, 4, dtype=i32, device=dev),
+                         seg=torch.zeros(self.B, 2, dtype=i32, device=dev), terms=torch.zeros(T_cap, 4, dtype=i32, device=dev),
+                         n_terms=torch.zeros(1, dtype=i32, device=dev), fallback=torch.full((1, 2), -1, dtype=i32, device=dev))
+        self.plan["seg"]._k3m_maxn = maxn
+        self.scales = [torch.ones(1, dtype=torch.float32, device=dev) for _ in range(4)]
+        self.g_fwd = self.g_bwd = None
+        self.out = None
+
+    def load(self, batch, plan_np):
+        for k, v in batch.items():
+            self.inputs[k].copy_(v, non_blocking=True)
+        padded = pad_struct_plan(plan_np, self.B, self.max_num_pv, self.owner.config.num_negative_pv)
+        for k, v in padded.items():
+            self.plan[k].copy_(torch.from_numpy(v).reshape(self.plan[k].shape), non_blocking=False)
+
+    def capture(self):
+        eng = self.owner._engine
+        s = torch.cuda.Stream(device=self.owner._arena.device)
+        s.wait_stream(torch.cuda.current_stream())
+        self.g_fwd = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.g_fwd, stream=s):
+            self.out = eng.forward(self.inputs, self.plan, None, (1.0, 1.0, 1.0, 1.0))
+        saved = eng.saved
+        self.g_bwd = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.g_bwd, pool=self.g_fwd.pool(), stream=s):
+            eng.saved = saved
+            eng.backward(tuple(self.scales))
+        torch.cuda.current_stream().wait_stream(s)
+
+    def forward(self):
+        self.g_fwd.replay()
+        o = self.out
+        return tuple(o[k].clone() for k in ("loss_t", "loss_v", "loss_pv", "loss_lpm", "loss_itm", "c_initial", "c_final"))
+
+    def backward(self, scales):
+        for dst, src in zip(self.scales, scales):
+            dst.copy_(src)
+        self.g_bwd.replay()
+
+
 class _StepFunction(torch.autograd.Function):
     """One autograd node for the whole step.  Inputs: a dummy leaf (so that autograd records the
     node) and the owning module; outputs: the four training losses (differentiable) and the
     value-only results."""
 
     @staticmethod
-    def forward(ctx, anchor, owner, batch, plan):
-        out = owner._engine.forward(batch, plan, None, (1.0, 1.0, 1.0, 1.0))
+    def forward(ctx, anchor, owner, batch, plan, graphed=None):
         ctx.owner = owner
         ctx.token = owner._fwd_token
-        res = (out["loss_t"], out["loss_v"], out["loss_pv"], out["loss_lpm"], out["loss_itm"],
-               out["c_initial"], out["c_final"])
+        ctx.graphed = graphed
+        if graphed is not None:
+            res = graphed.forward()
+        else:
+            out = owner._engine.forward(batch, plan, None, (1.0, 1.0, 1.0, 1.0))
+            res = (out["loss_t"], out["loss_v"], out["loss_pv"], out["loss_lpm"], out["loss_itm"],
+                   out["c_initial"], out["c_final"])
         ctx.mark_non_differentiable(res[4], res[5], res[6])
         return res
 
@@ -71,8 +129,8 @@ class _StepFunction(torch.autograd.Function):
         if ctx.token != owner._fwd_token:
             raise RuntimeError("backward() of a K3M step whose activations were released by a later forward(); "
                                "call backward before the next forward (the reference's drivers do)")
-        owner._run_backward((g_t, g_v, g_pv, g_lpm))
-        return None, None, None, None
+        owner._run_backward((g_t, g_v, g_pv, g_lpm), ctx.graphed)
+        return None, None, None, None, None
 
 
 class K3MPreTrainedModel(nn.Module):
@@ -249,8 +307,22 @@ class K3MPreTrainedModel(nn.Module):
         self._g32 = torch.zeros(L.total, dtype=torch.float32, device=dev)
         self._rng = torch.tensor([getattr(self.config, "rng_seed", 1234), 0], dtype=torch.int64, device=dev)
         self._engine = Engine(self.config, L, self._ops, self._w16, self._g32, self._rng, adt)
+        self._w16_stamp = None
+        self._graphs = {}
 
-    def _run_backward(self, grads):
+    def _param_stamp(self):
+        """Changes whenever a parameter (or the arena) was written in place: the version counters torch keeps anyway."""
+        return (self._arena._version, self._arena.data_ptr(), sum(p._version for p in self._params.values()))
+
+    def _refresh_shadow(self):
+        """bf16 shadow of the fp32 masters, re-cast only after the masters changed (an optimizer step, a checkpoint
+        load): eval loops and gradient accumulation reuse it instead of moving 2.8 GB per forward."""
+        stamp = self._param_stamp()
+        if stamp != self._w16_stamp:
+            self._ops.cast(self._arena, self._w16.dtype, out=self._w16)
+            self._w16_stamp = stamp
+
+    def _run_backward(self, grads, graphed=None):
         L, ops = self._layout, self._ops
         dev = self._arena.device
         first = self._params[next(n for n in L.spec if n not in L.frozen)]
@@ -261,10 +333,19 @@ class K3MPreTrainedModel(nn.Module):
             if g is None:
                 g = torch.zeros(1, dtype=torch.float32, device=dev)
             scales.append(g.reshape(1).to(torch.float32).contiguous())
-        if self._kind == "alignment":
+        if graphed is not None:
+            graphed.backward(scales)
+        elif self._kind == "alignment":
             self._engine.backward_alignment(scales[0])
         else:
             self._engine.backward(tuple(scales))
+        if (self._group is None and torch.distributed.is_available() and torch.distributed.is_initialized()
+                and torch.distributed.get_world_size() > 1 and not getattr(self, "_allow_unsynced", False)):
+            # exactly the state a stock `DistributedDataParallel(model)` leaves this model in: its per-parameter
+            # hooks never fire (one autograd node for the whole step), so training would silently diverge per rank
+            raise RuntimeError("k3m_b200: torch.distributed is initialised with world size > 1 but this model has no "
+                               "process group: wrap it with k3m_b200.parallel.DistributedDataParallel(model) (or call "
+                               "model.set_process_group(group)); torch's DistributedDataParallel cannot reduce its gradients")
         if self._group is not None and self._world > 1:
             torch.distributed.all_reduce(self._g32[:L.trained_end], group=self._group)
             ops.scale_(self._g32[:L.trained_end], 1.0 / self._world)
@@ -357,16 +438,32 @@ class BertForMultiModalPreTraining_tri_stru(K3MPreTrainedModel):
         # the aggregator's pair lists and LPM negatives are drawn on the host with the reference's own
         # `random.sample` call sequence (`:2437-2502`) — one device->host copy of two small index
         # tensors replaces the reference's one sync per (item, PV) pair
-        plan = build_struct_plan(index_p.detach().cpu().numpy(), index_v.detach().cpu().numpy(),
-                                 batch["input_ids_pv"].shape[1], self.config.num_negative_pv)
-        plan = self._ops.plan_to_device(plan, dev)
-        ops = self._ops
-        ops.cast(self._arena, self._w16.dtype, out=self._w16)      # bf16 shadow of the (possibly just updated) masters
+        plan_np = build_struct_plan(index_p.detach().cpu().numpy(), index_v.detach().cpu().numpy(),
+                                    batch["input_ids_pv"].shape[1], self.config.num_negative_pv)
+        self._refresh_shadow()
         eng = self._engine
         eng.training = self.training
         self._fwd_token += 1
+        # training steps of a geometry seen before replay two CUDA graphs (K3M_CLASS_GRAPH=0: eager launches)
+        graphed = None
+        if (torch.is_grad_enabled() and dev.type == "cuda" and hasattr(self._ops, "lib")
+                and os.environ.get("K3M_CLASS_GRAPH", "1") != "0"):
+            key = (tuple(input_ids.shape), tuple(image_feat.shape), tuple(input_ids_pv.shape), tuple(index_p.shape),
+                   bool(self.training))
+            ent = self._graphs.get(key)
+            if ent is None:
+                self._graphs[key] = 0                    # first sight: eager (also the warm-up of every kernel variant)
+            else:
+                if ent == 0:
+                    ent = self._graphs[key] = _GraphedStep(self, batch, index_p.shape[1])
+                    ent.load(batch, plan_np)
+                    ent.capture()
+                else:
+                    ent.load(batch, plan_np)
+                graphed = ent
+        plan = None if graphed is not None else self._ops.plan_to_device(plan_np, dev)
         if torch.is_grad_enabled():
-            lt, lv, lpv, llpm, litm, c_init, c_fin = _StepFunction.apply(self._anchor, self, batch, plan)
+            lt, lv, lpv, llpm, litm, c_init, c_fin = _StepFunction.apply(self._anchor, self, batch, plan, graphed)
         else:
             out = eng.forward(batch, plan, None, (1.0, 1.0, 1.0, 1.0))
             eng.saved = None
@@ -449,7 +546,7 @@ class K3MForItemAlignment(K3MPreTrainedModel):
         plan = build_struct_plan(ip, iv, batch["input_ids_pv"].shape[1], self.config.num_negative_pv, halves=2)
         plan = self._ops.plan_to_device(plan, dev)
         lab = _as_dev(labels.reshape(-1), dev, i64)
-        self._ops.cast(self._arena, self._w16.dtype, out=self._w16)
+        self._refresh_shadow()
         eng = self._engine
         eng.training = self.training
         self._fwd_token += 1

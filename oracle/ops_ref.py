@@ -149,6 +149,10 @@ class RefOps(object):
         """independent problems of one layout (one grouped launch in the CUDA table): one after the other here"""
         return [self.gemm(**c) for c in calls]
 
+    def colsum_group(self, items):
+        for x, out in items:
+            self.colsum(x, out)
+
     def colsum(self, x, out):
         """out[n] += sum_m x[m, n]  (fp32 accumulate; bias gradients)."""
         out.add_(x.float().sum(0))

@@ -96,3 +96,38 @@ def test_long_context_dims_run_and_match_restatement(lens):
             rel.append(float((a - b).norm() / a.norm()))
     rel.sort()
     assert rel[len(rel) // 2] <= 2e-2, rel[len(rel) // 2]
+
+
+def test_class_api_graph_replay_matches_eager_launches():
+    """The drop-in class replays two CUDA graphs from the third call of a geometry on (call 1 eager, call 2 captures):
+    losses and every gradient of a replayed step equal the eagerly launched step (eval mode: no dropout)."""
+    from k3m_b200.config import BertConfig, K3M_TINY
+    from k3m_b200.synth import FORWARD_ORDER, synth_batch
+    from k3m_b200.vilbert_k3m import BertForMultiModalPreTraining_tri_stru, _GraphedStep
+    import random
+    cfg = BertConfig.from_dict(K3M_TINY)
+    cfg.if_pre_sampling, cfg.margin, cfg.num_negative_pv = 0, 1.0, 4
+    torch.manual_seed(1)
+    model = BertForMultiModalPreTraining_tri_stru(cfg).cuda()
+    model.eval()
+    batches = [synth_batch(cfg, 4, 12, 9, 20, max_num_pv=4, seed=31 + i) for i in range(2)]
+
+    def step(b, seed):
+        random.seed(seed)
+        model.zero_grad(set_to_none=True)
+        out = model(*[b[k] for k in FORWARD_ORDER], input_ids_pv=b["input_ids_pv"], token_type_ids_pv=b["token_type_ids_pv"],
+                    attention_mask_pv=b["attention_mask_pv"], masked_lm_labels_pv=b["masked_lm_labels_pv"],
+                    next_sentence_label_pv_v=b["next_sentence_label_pv_v"], next_sentence_label_pv_t=b["next_sentence_label_pv_t"],
+                    index_p=b["index_p"], index_v=b["index_v"])
+        (out[0] + 0.5 * out[1] + out[3] + out[9]).backward()
+        torch.cuda.synchronize()
+        return [float(out[i]) for i in (0, 1, 3, 6, 9)], model._g32.clone(), out[8].clone()
+
+    l0, g0, c0 = step(batches[0], 5)            # eager
+    step(batches[1], 6)                         # captures
+    assert any(isinstance(v, _GraphedStep) for v in model._graphs.values())
+    l2, g2, c2 = step(batches[0], 5)            # replay, same batch and negatives as the eager step
+    assert l2 == pytest.approx(l0, rel=1e-6)
+    assert torch.equal(c0, c2)
+    assert float((g0 - g2).abs().max()) <= 1e-5 * float(g0.abs().max())
+    assert float(g0.abs().max()) > 0
