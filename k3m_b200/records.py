@@ -145,14 +145,23 @@ class LMDBReader(object):
     # -- pages and nodes
     def _page(self, pgno):
         off = pgno * self.page_size
-        if off + _HDR > len(self._m):
+        if pgno < 0 or off + self.page_size > len(self._m):
             raise LMDBFormatError("page %d beyond the end of the file" % pgno)
         flags, lower = struct.unpack_from("<HH", self._m, off + 10)
-        return off, flags, (lower - _HDR) >> 1
+        n = (lower - _HDR) >> 1
+        if lower < _HDR or lower > self.page_size:
+            if not flags & _P_OVERFLOW:
+                raise LMDBFormatError("page %d: corrupt header (lower = %d)" % (pgno, lower))
+            n = 0
+        return off, flags, n
 
     def _node(self, off, i):
         p, = struct.unpack_from("<H", self._m, off + _HDR + 2 * i)
+        if p < _HDR or p + 8 > self.page_size:
+            raise LMDBFormatError("node pointer %d outside its page" % p)
         lo, hi, nflags, ksize = struct.unpack_from("<HHHH", self._m, off + p)
+        if p + 8 + ksize > self.page_size:
+            raise LMDBFormatError("node key runs past its page")
         return off + p + 8, lo, hi, nflags, ksize
 
     def _leaf_value(self, kpos, lo, hi, nflags, ksize):
@@ -166,6 +175,10 @@ class LMDBReader(object):
             if not oflags & _P_OVERFLOW:
                 raise LMDBFormatError("page %d is not an overflow page" % pg)
             d = ooff + _HDR
+        elif (d % self.page_size) + dsize > self.page_size:
+            raise LMDBFormatError("inline value runs past its page")
+        if d + dsize > len(self._m):
+            raise LMDBFormatError("value runs past the end of the file")
         return self._v[d:d + dsize]
 
     def get(self, key, default=None):
@@ -173,7 +186,7 @@ class LMDBReader(object):
         pg = self.meta["root"]
         if pg == _INVALID:
             return default
-        while True:
+        for _level in range(64):                       # a B+tree of 2^64 pages is < 64 levels deep: a longer walk is a cycle
             off, flags, n = self._page(pg)
             if flags & _P_LEAF2:
                 raise LMDBFormatError("LEAF2 pages are not supported")
@@ -203,14 +216,19 @@ class LMDBReader(object):
                 return default
             else:
                 raise LMDBFormatError("page %d: unexpected flags %#x" % (pg, flags))
+        raise LMDBFormatError("tree deeper than 64 levels (page cycle)")
 
     def items(self):
         """(key, value) in key order: depth-first walk of the tree."""
         if self.meta["root"] == _INVALID:
             return
         stack = [(self.meta["root"], 0)]
+        budget = 4 * (len(self._m) // self.page_size + 1)        # every page is entered a bounded number of times
         while stack:
             pg, i = stack.pop()
+            budget -= 1
+            if budget < 0 or len(stack) > 64:
+                raise LMDBFormatError("page cycle in the tree")
             off, flags, n = self._page(pg)
             if flags & _P_BRANCH:
                 if i < n:

@@ -272,3 +272,104 @@ def test_iter_raw_batches_cpu(tmp_path):
     assert b0["n_tok"].tolist() == [min(len(items[0][1]), 6), min(len(items[1][1]), 6)]     # L - 2
     assert b0["features"].shape == (2, 36, 64) and b0["whp"][1].tolist() == [800.0, 800.0, 640000.0]
     assert np.array_equal(b1["features"][0].numpy(), items[2][8][:36])
+
+
+# ---- LMDB layout: an independent walker and hostile files (the writer above is still this repo's own: parity with a
+# real `lmdb` writer stays unpinned) ------------------------------------------------------------------
+def _walk_independent(path):
+    """A second, deliberately different reader of the LMDB 0.9 page format (recursive descent, plain slicing, no shared
+    code with k3m_b200.records): meta page with the larger txnid -> root -> branch children left to right -> leaves."""
+    buf = open(path, "rb").read()
+    ps = struct.unpack_from("<I", buf, 16 + 24)[0]
+    metas = []
+    for pg in (0, 1):
+        o = pg * ps
+        root = struct.unpack_from("<Q", buf, o + 16 + 24 + 48 + 40)[0]
+        txn = struct.unpack_from("<Q", buf, o + 16 + 24 + 48 + 48 + 8)[0]
+        metas.append((txn, root))
+    root = max(metas)[1]
+    out = {}
+
+    def visit(pg):
+        o = pg * ps
+        flags, lower = struct.unpack_from("<HH", buf, o + 10)
+        for i in range((lower - 16) // 2):
+            p = struct.unpack_from("<H", buf, o + 16 + 2 * i)[0]
+            lo, hi, nf, ks = struct.unpack_from("<HHHH", buf, o + p)
+            key = buf[o + p + 8:o + p + 8 + ks]
+            if flags & 0x01:
+                visit(lo | hi << 16 | nf << 32)
+            else:
+                size = lo | hi << 16
+                d = o + p + 8 + ks
+                if nf & 0x01:
+                    d = struct.unpack_from("<Q", buf, d)[0] * ps + 16
+                out[key] = buf[d:d + size]
+    if root != (1 << 64) - 1:
+        visit(root)
+    return out
+
+
+@pytest.mark.parametrize("n,leaf_cap,branch_cap", [(1, 5, 4), (7, 3, 2), (60, 4, 3), (400, 5, 4)])
+def test_lmdb_reader_agrees_with_an_independent_walker(tmp_path, n, leaf_cap, branch_cap):
+    rng = np.random.default_rng(n)
+    kv = {("%08d" % i).encode(): bytes(rng.integers(0, 256, size=int(rng.integers(1, 3000)), dtype=np.uint8)) for i in range(n)}
+    path = str(tmp_path / "data.mdb")
+    write_lmdb(path, kv, leaf_cap=leaf_cap, branch_cap=branch_cap)
+    want = _walk_independent(path)
+    assert want == kv
+    with R.LMDBReader(path) as r:
+        got = {k: bytes(v) for k, v in r.items()}
+        assert got == want and len(r) == n
+        for k in list(kv)[::7]:
+            assert bytes(r.get(k)) == kv[k]
+        assert r.get(b"zzzz") is None
+
+
+@pytest.mark.timeout(120)
+def test_lmdb_reader_survives_truncated_and_bit_flipped_files(tmp_path):
+    """Hostile input: every prefix length class and 400 random bit flips of a depth-3 file.  The reader may return data
+    or raise a clean error; it must never hang, recurse without bound or read outside the mapping."""
+    rng = np.random.default_rng(5)
+    kv = {("%08d" % i).encode(): bytes(rng.integers(0, 256, size=int(rng.integers(1, 2500)), dtype=np.uint8)) for i in range(80)}
+    good = str(tmp_path / "good.mdb")
+    write_lmdb(good, kv, leaf_cap=4, branch_cap=3)
+    blob = open(good, "rb").read()
+    ok_err = (R.LMDBFormatError, struct.error, ValueError, IndexError, OverflowError)
+
+    def exercise(data, name):
+        p = str(tmp_path / name)
+        with open(p, "wb") as f:
+            f.write(data)
+        try:
+            r = R.LMDBReader(p)
+        except ok_err:
+            return "open"
+        try:
+            n = 0
+            for k, v in r.items():
+                assert len(v) <= len(data)
+                n += 1
+                assert n <= 10 * len(kv)
+            for k in list(kv)[::9]:
+                r.get(k)
+            return "read"
+        except ok_err:
+            return "err"
+        finally:
+            r.close()
+
+    outcomes = []
+    for cut in (0, 1, 100, 151, 152, PS - 1, PS, PS + 152, 2 * PS, 2 * PS + 17, len(blob) // 2, len(blob) - PS, len(blob) - 1):
+        outcomes.append(exercise(blob[:cut], "cut%d.mdb" % cut))
+    for t in range(400):
+        b = bytearray(blob)
+        # flips concentrated on structure: page headers, node pointers, node headers and the meta pages
+        pg = int(rng.integers(0, len(blob) // PS))
+        off = pg * PS + int(rng.integers(0, 64 if t % 2 else PS))
+        b[off] ^= 1 << int(rng.integers(0, 8))
+        if t % 5 == 0:
+            b[pg * PS + 12:pg * PS + 16] = bytes(rng.integers(0, 256, size=4, dtype=np.uint8))      # lower / upper
+        outcomes.append(exercise(bytes(b), "flip.mdb"))
+    assert "err" in outcomes or "open" in outcomes           # at least some corruptions are detected
+    assert outcomes.count("read") > 50                       # and harmless flips (value bytes) still read
