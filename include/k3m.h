@@ -213,7 +213,10 @@ int k3m_adamw_g16(float* p32, const void* g16, float* g32, float* m, float* v, v
  * visible).                                                                                                   */
 int k3m_cast_zero(float* g32, void* out16, long long n, void* stream);
 int k3m_adamw_dp(float* p32, float* m, float* v, const float* hyper, const void* const* g16_peers,
-                 void* const* w16_peers, int world, long long offset, long long n, void* stream);
+                 void* const* w16_peers, int world, long long offset, long long n, const void* g16_mc,
+                 void* w16_mc, void* stream);
+/* g16_mc / w16_mc: multicast (NVLS) addresses of the two symmetric arenas, or NULL: with them the gradient sum is
+ * one multimem.ld_reduce (added inside NVSwitch) and the weight broadcast one multimem.st.                     */
 /* The same update sized to co-reside with a running GEMM (two 128-thread, <= 32-register CTAs per SM, no shared
  * memory): used for the gradient buckets that become final while backward is still running.               */
 int k3m_adamw_bg(float* p32, float* g32, float* m, float* v, void* p16, const float* hyper, long long n,

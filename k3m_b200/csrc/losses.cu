@@ -463,9 +463,14 @@ struct DpPeers {
   bf16* w[16];
   int world;
 };
+// MC: the symmetric arenas also have a MULTICAST mapping (NVSwitch, NVLS): one multimem.ld_reduce returns the sum of
+// all ranks' gradients (added inside the switch, fp32 accumulation, bf16 result) and one multimem.st writes the new
+// weights into every rank's arena — 1/world of the peer-load bytes and one store instead of `world`.
+template <bool MC>
 __global__ void __launch_bounds__(256) adamw_dp_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
                                                        const float* __restrict__ hyper, const __grid_constant__ DpPeers peers,
-                                                       size_t offset, size_t n8) {
+                                                       size_t offset, size_t n8, const bf16* __restrict__ g_mc,
+                                                       bf16* __restrict__ w_mc) {
   const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], step = hyper[5], gs = hyper[6];
   const float bc1 = 1.0f - powf(b1, step), bc2 = 1.0f - powf(b2, step);
   const float step_size = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2), decay = 1.0f - lr * wd;
@@ -473,13 +478,25 @@ __global__ void __launch_bounds__(256) adamw_dp_kernel(float* __restrict__ p, fl
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
     const size_t e = offset + i * 8;                  // element index inside the arena
     float g[8];
+    if (MC) {
+      uint4 u;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "l"(g_mc + e) : "memory");
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) g[k] = 0.f;
-    for (int r = 0; r < world; ++r) {
-      float t[8];
-      ld8(peers.g[r] + e, t);
+      for (int k = 0; k < 4; ++k) {
+        const float2 f = __bfloat1622float2(h[k]);
+        g[2 * k] = f.x; g[2 * k + 1] = f.y;
+      }
+    } else {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] += t[k];
+      for (int k = 0; k < 8; ++k) g[k] = 0.f;
+      for (int r = 0; r < world; ++r) {
+        float t[8];
+        ld8(peers.g[r] + e, t);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] += t[k];
+      }
     }
     float pa[8], ma[8], va[8];
     ld8(p + i * 8, pa);
@@ -497,7 +514,12 @@ __global__ void __launch_bounds__(256) adamw_dp_kernel(float* __restrict__ p, fl
     st8(m + i * 8, ma);
     st8(v + i * 8, va);
     const uint4 wv = pack8_bf16(pa);
-    for (int r = 0; r < world; ++r) *reinterpret_cast<uint4*>(peers.w[r] + e) = wv;
+    if (MC) {
+      asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};"
+                   :: "l"(w_mc + e), "r"(wv.x), "r"(wv.y), "r"(wv.z), "r"(wv.w) : "memory");
+    } else {
+      for (int r = 0; r < world; ++r) *reinterpret_cast<uint4*>(peers.w[r] + e) = wv;
+    }
   }
 }
 
@@ -525,7 +547,8 @@ extern "C" int k3m_cast_zero(float* g32, void* out16, long long n, void* stream)
 }
 
 extern "C" int k3m_adamw_dp(float* p32, float* m, float* v, const float* hyper, const void* const* g16_peers,
-                            void* const* w16_peers, int world, long long offset, long long n, void* stream) {
+                            void* const* w16_peers, int world, long long offset, long long n, const void* g16_mc,
+                            void* w16_mc, void* stream) {
   K3M_REQUIRE(world >= 1 && world <= 16, "adamw_dp: 1..16 ranks (got %d)", world);
   K3M_REQUIRE(n > 0 && n % 8 == 0 && offset % 8 == 0, "adamw_dp: shard offset / length must be multiples of 8 elements");
   K3M_REQUIRE((((uintptr_t)p32 | (uintptr_t)m | (uintptr_t)v) & 31) == 0, "adamw_dp: misaligned shard");
@@ -539,7 +562,13 @@ extern "C" int k3m_adamw_dp(float* p32, float* m, float* v, const float* hyper, 
   const size_t n8 = (size_t)n / 8;
   size_t g = (n8 + 255) / 256;
   if (g > 148 * 8) g = 148 * 8;
-  adamw_dp_kernel<<<(int)g, 256, 0, ST(stream)>>>(p32, m, v, hyper, peers, (size_t)offset, n8);
+  if (g16_mc != nullptr && w16_mc != nullptr) {
+    K3M_REQUIRE((((uintptr_t)g16_mc | (uintptr_t)w16_mc) & 15) == 0, "adamw_dp: misaligned multicast arena");
+    adamw_dp_kernel<true><<<(int)g, 256, 0, ST(stream)>>>(p32, m, v, hyper, peers, (size_t)offset, n8, (const bf16*)g16_mc,
+                                                          (bf16*)w16_mc);
+  } else {
+    adamw_dp_kernel<false><<<(int)g, 256, 0, ST(stream)>>>(p32, m, v, hyper, peers, (size_t)offset, n8, nullptr, nullptr);
+  }
   return k3m_check_launch("k3m_adamw_dp");
 }
 

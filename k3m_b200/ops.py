@@ -691,7 +691,7 @@ class CudaOps(object):
         assert g32.dtype == torch.float32 and out16.dtype == torch.bfloat16 and g32.numel() == out16.numel()
         self._call("k3m_cast_zero", _p(g32), _p(out16), _ll(g32.numel()), self._st())
 
-    def adamw_dp(self, p32, m, v, hyper, g_ptrs, w_ptrs, offset):
+    def adamw_dp(self, p32, m, v, hyper, g_ptrs, w_ptrs, offset, g_mc=0, w_mc=0):
         """Gradient reduce-scatter + AdamW + weight all-gather over NVLink peer memory for the shard
         [offset, offset + p32.numel()) of the arena; g_ptrs / w_ptrs: every rank's bf16 gradient / weight arena base."""
         world = len(g_ptrs)
@@ -700,7 +700,7 @@ class CudaOps(object):
         if self.timing is not None:
             self._bytes = p32.numel() * (24.0 + 2.0 * world * 2)
         self._call("k3m_adamw_dp", _p(p32), _p(m), _p(v), _p(hyper), ga, wa, _i(world), _ll(int(offset)),
-                   _ll(p32.numel()), self._st())
+                   _ll(p32.numel()), _vp(int(g_mc) or None), _vp(int(w_mc) or None), self._st())
 
     def gemm_set_sm_limit(self, n):
         self.lib.k3m_gemm_set_sm_limit(_i(int(n)))

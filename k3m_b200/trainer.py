@@ -172,6 +172,17 @@ class PretrainStep(object):
             self._w_ptrs = [int(x) for x in self._h_w.buffer_ptrs]
             self._g_ptrs = [int(x) for x in self._h_g.buffer_ptrs]
             assert len(self._w_ptrs) == self.world and self._w_ptrs[self.rank] == w16.data_ptr()
+            # multicast (NVLS) mapping of the same allocations, when the fabric has one: in-switch reduction
+            self._g_mc = self._w_mc = 0
+            # measured (profiles/r02t_n2_multimem.txt, r02u_n8_multimem.txt): N = 2 19.18 ms with multimem vs 18.58 with
+            # peer loads (no bytes saved at two ranks, 16-byte switch requests); N = 8 18.63 vs 19.21 ms -> from 4 ranks on
+            if os.environ.get("K3M_DP_MULTIMEM", "1" if self.world >= 4 else "0") != "0":
+                try:
+                    g_mc, w_mc = int(self._h_g.multicast_ptr or 0), int(self._h_w.multicast_ptr or 0)
+                    if g_mc and w_mc:
+                        self._g_mc, self._w_mc = g_mc, w_mc
+                except Exception:
+                    pass
             self.w16, self._g16 = w16, g16
             self.dp_fused = True
         except Exception as e:      # pragma: no cover - depends on the box
@@ -336,7 +347,7 @@ class PretrainStep(object):
                 s0, s1 = self._shard(lo, hi)
                 if s1 > s0:
                     self.ops.adamw_dp(self.p32[s0:s1], self.m[s0:s1], self.v[s0:s1], self.hyper[gi], self._g_ptrs,
-                                      self._w_ptrs, s0)
+                                      self._w_ptrs, s0, self._g_mc, self._w_mc)
                 if ev is not None:
                     ev[1].record()
                     self.comm_events.append((ev[0], ev[1], (hi - lo) * 2))
@@ -421,7 +432,8 @@ class PretrainStep(object):
         return dict(comm_ms_total=round(sum(a.elapsed_time(b) for a, b, _ in ev), 3),
                     tail_ms=round(self._bwd_done.elapsed_time(self._opt_done), 3), buckets=len(ev),
                     bytes=int(sum(n for _, _, n in ev)), dtype="bf16" if self.comm_bf16 else "f32",
-                    mode="fused peer-memory reduce-scatter + AdamW + weight all-gather (k3m_adamw_dp)" if self.dp_fused
+                    mode=("fused peer-memory reduce-scatter + AdamW + weight all-gather (k3m_adamw_dp, %s)"
+                          % ("multimem / in-switch reduction" if getattr(self, "_g_mc", 0) else "peer loads / stores")) if self.dp_fused
                     else "NCCL all-reduce + replicated AdamW",
                     reserve_sms=self.reserve_sms,
                     note="one non-captured step; comm_ms_total = sum over buckets of (cast +) all-reduce time on the "
