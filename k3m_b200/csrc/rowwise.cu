@@ -154,7 +154,16 @@ __device__ __forceinline__ float ld_dsmem(const float* local, uint32_t rank) {
 // CL = CTAs per cluster (1: no cluster).  With CL > 1 the per-CTA column sums meet in distributed shared
 // memory and each CTA of the cluster issues the atomics of 1/CL of the columns: CL x fewer same-address
 // atomics.  An experiment that did not pay (see k3m_ln_bwd below); selectable with K3M_LN_CLUSTER=1.
-template <int NV, int CL>
+// SACC: the three column-sum sets live in this warp's slice of shared memory (read-modify-written per row, 16-byte
+// accesses, no bank conflicts: lane owns its columns) instead of 3 x NV x 8 registers per thread — 128-210 registers
+// allowed one or two CTAs per SM; ~70 allow three, i.e. 24 rows in flight per SM for this latency-bound kernel.
+__device__ __forceinline__ void sacc8(float* p, const float v[8]) {
+  float4 a = *reinterpret_cast<float4*>(p), b = *reinterpret_cast<float4*>(p + 4);
+  a.x += v[0]; a.y += v[1]; a.z += v[2]; a.w += v[3]; b.x += v[4]; b.y += v[5]; b.z += v[6]; b.w += v[7];
+  *reinterpret_cast<float4*>(p) = a;
+  *reinterpret_cast<float4*>(p + 4) = b;
+}
+template <int NV, int CL, bool SACC = false>
 __device__ __forceinline__ void ln_bwd_body(const act_t* __restrict__ dy, const act_t* __restrict__ x,
                                             const act_t* __restrict__ gamma, const float* __restrict__ mean_in,
                                             const float* __restrict__ rstd_in, act_t* __restrict__ dx,
@@ -166,11 +175,17 @@ __device__ __forceinline__ void ln_bwd_body(const act_t* __restrict__ dy, const 
   // so the live state is the 3 x NV x 8 fp32 column-sum accumulators.
   extern __shared__ float sred[];  // [8 warps][3][H]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float ag[NV][8], ab[NV][8], ac[NV][8];
+  constexpr int NA = SACC ? 1 : NV;
+  float ag[NA][8], ab[NA][8], ac[NA][8];
 #pragma unroll
-  for (int i = 0; i < NV; ++i)
+  for (int i = 0; i < NA; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) ag[i][j] = ab[i][j] = ac[i][j] = 0.f;
+  float* s0 = sred + (size_t)warp * 3 * H;
+  if (SACC) {
+    for (int c = lane * 4; c < 3 * H; c += 128) *reinterpret_cast<float4*>(s0 + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncwarp();
+  }
   for (int row = cta * 8 + warp; row < M; row += nctas * 8) {
     const float mean = mean_in[row], rstd = rstd_in[row];
     Pack8 pd[NV], px[NV];
@@ -197,14 +212,24 @@ __device__ __forceinline__ void ln_bwd_body(const act_t* __restrict__ dy, const 
 #pragma unroll
           for (int j = 0; j < 8; ++j) d[j] *= drop_mult(drop_out, w, j);
         }
+        float dxh[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float xh = (xv[j] - mean) * rstd;
           const float g = d[j] * gm[j];
-          ag[i][j] += d[j] * xh;
-          ab[i][j] += d[j];
+          dxh[j] = d[j] * xh;
           s1 += g;
           s2 += g * xh;
+        }
+        if (SACC) {
+          sacc8(s0 + c, dxh);
+          sacc8(s0 + H + c, d);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            ag[i][j] += dxh[j];
+            ab[i][j] += d[j];
+          }
         }
       }
     }
@@ -235,23 +260,28 @@ __device__ __forceinline__ void ln_bwd_body(const act_t* __restrict__ dy, const 
           st8(dxm + (size_t)row * H + c, o);
         }
         if (dbias) {
+          if (SACC) {
+            sacc8(s0 + 2 * H + c, o);
+          } else {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) ac[i][j] += o[j];
+            for (int j = 0; j < 8; ++j) ac[i][j] += o[j];
+          }
         }
       }
     }
   }
   // cross-warp reduction of the three column-sum sets, then one atomic per column per CTA
-  float* s0 = sred + (size_t)warp * 3 * H;
+  if (!SACC) {
 #pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int c = (lane + 32 * i) * 8;
-    if (c < H) {
+    for (int i = 0; i < NA; ++i) {
+      const int c = (lane + 32 * i) * 8;
+      if (c < H) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        s0[c + j] = ag[i][j];
-        s0[H + c + j] = ab[i][j];
-        s0[2 * H + c + j] = ac[i][j];
+        for (int j = 0; j < 8; ++j) {
+          s0[c + j] = ag[i][j];
+          s0[H + c + j] = ab[i][j];
+          s0[2 * H + c + j] = ac[i][j];
+        }
       }
     }
   }
@@ -316,6 +346,14 @@ __global__ void __launch_bounds__(256, NV >= 4 ? 1 : 2) ln_bwd_group_kernel(cons
   const LnBwdProb& P = g.p[pi];
   ln_bwd_body<NV, 1>(P.dy, P.x, P.gamma, P.mean, P.rstd, P.dx, P.dxm, P.dgamma, P.dbeta, P.dbias, P.M, P.H, P.drop_out,
                      P.drop_in, (int)blockIdx.x - P.cta_begin, P.nctas);
+}
+template <int NV>
+__global__ void __launch_bounds__(256, NV >= 4 ? 2 : 3) ln_bwd_group_sacc_kernel(const __grid_constant__ LnBwdGroup g) {
+  int pi = 0;
+  while (pi + 1 < g.n && (int)blockIdx.x >= g.p[pi + 1].cta_begin) ++pi;
+  const LnBwdProb& P = g.p[pi];
+  ln_bwd_body<NV, 1, true>(P.dy, P.x, P.gamma, P.mean, P.rstd, P.dx, P.dxm, P.dgamma, P.dbeta, P.dbias, P.M, P.H,
+                           P.drop_out, P.drop_in, (int)blockIdx.x - P.cta_begin, P.nctas);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -530,10 +568,29 @@ extern "C" int k3m_ln_fwd(const void* x, const void* gamma, const void* beta, vo
   return k3m_check_launch("k3m_ln_fwd");
 }
 
+extern "C" int k3m_ln_bwd_grouped(const void* descs, int n, void* stream);
+struct LnBwdDesc1 {      // == K3MLnBwdDesc (declared again further down for the grouped entry)
+  const void *dy, *x, *gamma;
+  const float *mean, *rstd;
+  void *dx, *dxm;
+  float *dgamma, *dbeta, *dbias;
+  int M, H;
+  const void* rng;
+  unsigned int site_out;
+  float p_out;
+  unsigned int site_in;
+  float p_in;
+};
+
 extern "C" int k3m_ln_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
                           void* dx, void* dxm, float* dgamma, float* dbeta, float* dbias, int M, int H, const void* rng,
                           unsigned int site_out, float p_out, unsigned int site_in, float p_in, void* stream) {
   K3M_REQUIRE(M > 0 && H > 0 && H % 8 == 0 && H <= 1024, "ln_bwd: need H %% 8 == 0 and H <= 1024 (H=%d)", H);
+  static const int use_cluster0 = getenv("K3M_LN_CLUSTER") ? atoi(getenv("K3M_LN_CLUSTER")) : 0;
+  if (!use_cluster0) {       // one problem of the grouped kernel (shared-memory column accumulators)
+    LnBwdDesc1 d = {dy, x, gamma, mean, rstd, dx, dxm, dgamma, dbeta, dbias, M, H, rng, site_out, p_out, site_in, p_in};
+    return k3m_ln_bwd_grouped(&d, 1, stream);
+  }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   DropSpec dout = make_drop(rng, site_out, p_out), din = make_drop(rng, site_in, p_in);
   K3M_REQUIRE(!din.thresh || dxm, "ln_bwd: drop_in needs the dxm output");
@@ -650,7 +707,9 @@ extern "C" int k3m_ln_bwd_grouped(const void* descs, int n, void* stream) {
     if (d[i].H > hmax) hmax = d[i].H;
   }
   const int nv = (hmax + 255) / 256;
-  const int target = 148 * (nv >= 4 ? 1 : 2) * 2;        // about two waves of resident CTAs over the whole group
+  static const int sacc = getenv("K3M_LN_BWD_SACC") ? atoi(getenv("K3M_LN_BWD_SACC")) : 1;
+  const int per_sm = sacc ? (nv >= 4 ? 2 : 3) : (nv >= 4 ? 1 : 2);
+  const int target = 148 * per_sm * (sacc ? 1 : 2);      // one (register accumulators: two) wave(s) of resident CTAs
   int ctas = 0;
   for (int i = 0; i < n; ++i) {
     LnBwdProb& P = g.p[i];
@@ -678,7 +737,16 @@ extern "C" int k3m_ln_bwd_grouped(const void* descs, int n, void* stream) {
       cudaFuncSetAttribute(ln_bwd_group_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 3 * 1024 * 4); \
       cfg = true;                                                                                                 \
     }                                                                                                             \
-    ln_bwd_group_kernel<NV><<<ctas, 256, smem, st>>>(g);                                                          \
+    if (sacc) {                                                                                                   \
+      static bool cfg2 = false;                                                                                   \
+      if (!cfg2) {                                                                                                \
+        cudaFuncSetAttribute(ln_bwd_group_sacc_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 3 * 1024 * 4); \
+        cfg2 = true;                                                                                              \
+      }                                                                                                           \
+      ln_bwd_group_sacc_kernel<NV><<<ctas, 256, smem, st>>>(g);                                                   \
+    } else {                                                                                                      \
+      ln_bwd_group_kernel<NV><<<ctas, 256, smem, st>>>(g);                                                        \
+    }                                                                                                             \
   } while (0)
   if (nv <= 1) LN_BWD_G(1);
   else if (nv <= 2) LN_BWD_G(2);
