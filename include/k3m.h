@@ -40,6 +40,8 @@ extern "C" {
 #define K3M_GEMM_TN 2 /* A[K,M] , B[K,N]  : dW = dY^T X  (weight gradient)                     */
 
 int k3m_get_version(void);
+/* debug aid: cudaStreamIsCapturing status of `stream` (0 none, 1 active, 2 invalidated, < 0 query error)  */
+int k3m_debug_capture_status(void* stream);
 const char* k3m_last_error_string(void);
 
 /* tcgen05/TMEM/TMA GEMM with fused epilogue.  Replaces every nn.Linear on the path
@@ -151,6 +153,11 @@ int k3m_relu_bwd_split3(const void* dcat, const void* cat, void* da, int lda, vo
 int k3m_gate_mul(const void* cat, const void* alpha, void* out, long long n, void* stream);
 int k3m_gate_bwd(const void* dgated, const void* cat, const void* alpha, void* dcat, void* dscore,
                  long long n, void* stream);
+/* Masked-LM head on the labelled rows only (vilbert_k3m.py:1836-1839 decoder on every position + :2817-2826
+ * CrossEntropyLoss(ignore_index=-1): unlabelled rows give neither loss nor gradient).  out[i] = src[idx[i]]
+ * (idx < 0: zero row); backward dst[idx[i]] += dsrc[i] (unique indices).  Bit-exact row copies.            */
+int k3m_gather_rows(const void* src, int ld, const int* idx, void* out, int n, int H, void* stream);
+int k3m_scatter_add_rows(const void* dsrc, const int* idx, void* dst, int ld, int n, int H, void* stream);
 /* token-mean pooling over positions 1.. (vilbert_k3m.py:2405-2409)                               */
 int k3m_mean_pool_fwd(const void* seq, int ld, void* out, int out_f32, int B, int L, int H, void* stream);
 int k3m_mean_pool_bwd(const float* dpool, void* dseq, int ld, int B, int L, int H, void* stream);

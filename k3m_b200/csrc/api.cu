@@ -25,3 +25,14 @@ int k3m_check_launch(const char* what) {
 
 extern "C" const char* k3m_last_error_string(void) { return g_err; }
 extern "C" int k3m_get_version(void) { return 1; }
+
+// Debug aid: cudaStreamIsCapturing status of `stream` (0 none, 1 active, 2 invalidated; < 0: the query itself failed).
+extern "C" int k3m_debug_capture_status(void* stream) {
+  cudaStreamCaptureStatus st;
+  cudaError_t e = cudaStreamIsCapturing(reinterpret_cast<cudaStream_t>(stream), &st);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return -(int)e;
+  }
+  return (int)st;
+}

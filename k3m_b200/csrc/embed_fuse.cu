@@ -229,6 +229,41 @@ __global__ void gate_bwd_kernel(const act_t* __restrict__ dgated, const act_t* _
   }
 }
 
+// ---- labelled-row gather for the masked-LM head --------------------------------------------------------------
+// The reference runs the vocabulary decoder on EVERY position and lets CrossEntropyLoss ignore the ~85 % of rows whose
+// label is -1 (vilbert_k3m.py:1836-1839, :2817-2826); rows without a label contribute neither loss nor gradient, so
+// the head runs on the labelled rows only: out[i] = src[idx[i]] (idx < 0: a zero row of padding), and its input
+// gradient goes back with dst[idx[i]] += dsrc[i] (indices are unique: plain read-modify-write).
+__global__ void gather_rows_kernel(const act_t* __restrict__ src, int ld, const int* __restrict__ idx,
+                                   act_t* __restrict__ out, int n, int H8) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)n * H8; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / H8), c = (int)(i % H8) * 8;
+    float v[8];
+    const int s_ = idx[r];
+    if (s_ >= 0) {
+      ld8(src + (size_t)s_ * ld + c, v);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = 0.f;
+    }
+    st8(out + (size_t)r * (H8 * 8) + c, v);
+  }
+}
+__global__ void scatter_add_rows_kernel(const act_t* __restrict__ dsrc, const int* __restrict__ idx,
+                                        act_t* __restrict__ dst, int ld, int n, int H8) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)n * H8; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / H8), c = (int)(i % H8) * 8;
+    const int s_ = idx[r];
+    if (s_ < 0) continue;
+    float a[8], b[8];
+    ld8(dsrc + (size_t)r * (H8 * 8) + c, a);
+    ld8(dst + (size_t)s_ * ld + c, b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) b[j] += a[j];
+    st8(dst + (size_t)s_ * ld + c, b);
+  }
+}
+
 inline int grid_for(size_t n, int block) {
   size_t g = (n + block - 1) / block;
   if (g > 148 * 16) g = 148 * 16;
@@ -288,6 +323,18 @@ extern "C" int k3m_fuse_select_bwd(const void* dout, int ldd, const void* cat, c
   fuse_bwd_kernel<<<grid_for((size_t)M * H, 256), 256, 0, ST(stream)>>>(
       (const act_t*)dout, ldd, (const act_t*)cat, gates, noise, (const unsigned long long*)rng, site, (act_t*)dgates, (act_t*)dcat, M, H);
   return k3m_check_launch("k3m_fuse_select_bwd");
+}
+
+extern "C" int k3m_gather_rows(const void* src, int ld, const int* idx, void* out, int n, int H, void* stream) {
+  K3M_REQUIRE(n > 0 && H > 0 && H % 8 == 0 && ld % 8 == 0, "gather_rows: widths must be multiples of 8");
+  gather_rows_kernel<<<grid_for((size_t)n * H / 8, 256), 256, 0, ST(stream)>>>((const act_t*)src, ld, idx, (act_t*)out, n, H / 8);
+  return k3m_check_launch("k3m_gather_rows");
+}
+
+extern "C" int k3m_scatter_add_rows(const void* dsrc, const int* idx, void* dst, int ld, int n, int H, void* stream) {
+  K3M_REQUIRE(n > 0 && H > 0 && H % 8 == 0 && ld % 8 == 0, "scatter_add_rows: widths must be multiples of 8");
+  scatter_add_rows_kernel<<<grid_for((size_t)n * H / 8, 256), 256, 0, ST(stream)>>>((const act_t*)dsrc, idx, (act_t*)dst, ld, n, H / 8);
+  return k3m_check_launch("k3m_scatter_add_rows");
 }
 
 extern "C" int k3m_gate_mul(const void* cat, const void* alpha, void* out, long long n, void* stream) {

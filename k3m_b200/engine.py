@@ -560,13 +560,31 @@ class Engine(object):
                                 drop=self.site(0.1), rng=self.rng)
         w_t, w_v, w_pv, w_lpm = [float(x) for x in loss_weights]
         V, Tv = c.vocab_size, c.v_target_size
-        logits, sv_h = self.head_fwd("cls.predictions", S, "embeddings.word_embeddings.weight",
-                                     "cls.predictions.bias", self.adt, V)
         lab_t, lab_pv = batch["masked_lm_labels"].reshape(-1), batch["masked_lm_labels_pv"].reshape(-1)
-        loss_t = ops.xent_fwd_bwd(logits[:Mt], lab_t, ops.count_valid(lab_t, -1), V,
-                                  dlogits=logits[:Mt], grad_scale=w_t)
-        loss_pv = ops.xent_fwd_bwd(logits[Mt:], lab_pv, ops.count_valid(lab_pv, -1), V,
-                                   dlogits=logits[Mt:], grad_scale=w_pv)
+        mlm_rows = plan.get("mlm_rows")
+        if mlm_rows is not None:
+            # The reference decodes EVERY position and lets CrossEntropyLoss ignore the unlabelled ~85 % (`:1836-1839`,
+            # `:2817-2826`): those rows give neither loss nor gradient, so transform + decoder + loss run on the
+            # labelled rows only, gathered by the host-built row list (`struct_plan.build_mlm_plan`; bit-exact row
+            # copies, same losses and gradients).  The gathered logits [~1.2 k, 21128] are materialised on purpose:
+            # recomputing them tile by tile in backward would cost two more vocabulary GEMM passes (75 GF) to save
+            # ~250 MB of traffic (40 us).
+            cap_t = plan["mlm_cap_t"]
+            Sg = ops.gather_rows(S, mlm_rows)
+            logits, sv_h = self.head_fwd("cls.predictions", Sg, "embeddings.word_embeddings.weight",
+                                         "cls.predictions.bias", self.adt, V)
+            lab_g = plan["mlm_labels"]
+            loss_t = ops.xent_fwd_bwd(logits[:cap_t], lab_g[:cap_t], ops.count_valid(lab_t, -1), V,
+                                      dlogits=logits[:cap_t], grad_scale=w_t)
+            loss_pv = ops.xent_fwd_bwd(logits[cap_t:], lab_g[cap_t:], ops.count_valid(lab_pv, -1), V,
+                                       dlogits=logits[cap_t:], grad_scale=w_pv)
+        else:
+            logits, sv_h = self.head_fwd("cls.predictions", S, "embeddings.word_embeddings.weight",
+                                         "cls.predictions.bias", self.adt, V)
+            loss_t = ops.xent_fwd_bwd(logits[:Mt], lab_t, ops.count_valid(lab_t, -1), V,
+                                      dlogits=logits[:Mt], grad_scale=w_t)
+            loss_pv = ops.xent_fwd_bwd(logits[Mt:], lab_pv, ops.count_valid(lab_pv, -1), V,
+                                       dlogits=logits[Mt:], grad_scale=w_pv)
         logits_v, sv_hv = self.head_fwd("cls.imagePredictions", seqV,
                                         "cls.imagePredictions.decoder.weight",
                                         "cls.imagePredictions.decoder.bias", f32, Tv)
@@ -574,7 +592,8 @@ class Engine(object):
         il = batch["image_label"].reshape(-1)
         loss_v = ops.kl_fwd_bwd(logits_v, batch["image_target"].reshape(-1, Tv), il,
                                 ops.count_eq(il, 1), Tv, Lv1, dlogits=dlv, grad_scale=w_v)
-        self.saved.update(struct=sv_s, w_lpm=w_lpm, head=(logits, sv_h), head_v=(dlv, sv_hv))
+        self.saved.update(struct=sv_s, w_lpm=w_lpm, head=(logits, sv_h), head_v=(dlv, sv_hv), mlm_rows=mlm_rows,
+                          mlm_cap_t=plan.get("mlm_cap_t"))
         return dict(loss_t=loss_t, loss_v=loss_v, loss_pv=loss_pv, loss_itm=loss_itm,
                     loss_lpm=loss_lpm, c_initial=c_init, c_final=c_final)
 
@@ -709,15 +728,21 @@ class Engine(object):
         if grad_scales is not None:
             g_t, g_v, g_pv, g_lpm = grad_scales
             dlog = sv["head"][0]
-            ops.scale_dev_(dlog[:Mt], g_t)
-            ops.scale_dev_(dlog[Mt:], g_pv)
+            cut = sv["mlm_cap_t"] if sv.get("mlm_rows") is not None else Mt
+            ops.scale_dev_(dlog[:cut], g_t)
+            ops.scale_dev_(dlog[cut:], g_pv)
             ops.scale_dev_(sv["head_v"][0], g_v)
             ops.scale_dev_(sv["struct"][5], g_lpm)      # dc_final
             ops.scale_dev_(sv["struct"][6], g_lpm)      # dPV
         H, Hv = c.hidden_size, c.v_hidden_size
         dS = self.zeros(Mt + Mp, H)
         dseqV = self.zeros(Mv, Hv)
-        self.head_bwd(sv["head"][0], sv["head"][1], dS)
+        if sv.get("mlm_rows") is not None:
+            dSg = self.zeros(sv["mlm_rows"].numel(), H)
+            self.head_bwd(sv["head"][0], sv["head"][1], dSg)
+            ops.scatter_add_rows(dSg, sv["mlm_rows"], dS)
+        else:
+            self.head_bwd(sv["head"][0], sv["head"][1], dS)
         self.head_bwd(sv["head_v"][0], sv["head_v"][1], dseqV)
         dc_init = self.zeros(B, H, f32)
         self.struct_bwd(sv["struct"], sv["w_lpm"], dc_init, dS[Mt:])

@@ -488,6 +488,17 @@ class CudaOps(object):
                    _u(site), _p(dg), _p(dc), _i(M), _i(H), self._st())
         return dg, dc
 
+    def gather_rows(self, src, idx):
+        n, H = idx.numel(), src.shape[1]
+        out = torch.empty(n, H, dtype=src.dtype, device=src.device)
+        self._call("k3m_gather_rows", _p(src), _i(_ld(src)), _p(idx), _p(out), _i(n), _i(H), self._st())
+        return out
+
+    def scatter_add_rows(self, dsrc, idx, dst):
+        assert dsrc.is_contiguous()
+        self._call("k3m_scatter_add_rows", _p(dsrc), _p(idx), _p(dst), _i(_ld(dst)), _i(idx.numel()), _i(dsrc.shape[1]),
+                   self._st())
+
     def gate_mul(self, cat, alpha):
         assert cat.is_contiguous() and alpha.is_contiguous() and cat.shape == alpha.shape
         out = torch.empty_like(cat)
@@ -609,6 +620,9 @@ class CudaOps(object):
         is recorded on the host so no device->host sync is needed later."""
         out = {}
         for k, v in plan.items():
+            if k == "cap_t":
+                out["mlm_cap_t"] = int(v)
+                continue
             out[k] = torch.from_numpy(v).to(device, non_blocking=True)
         seg = plan["seg"]
         out["seg"]._k3m_maxn = int((seg[:, 1] - seg[:, 0]).max())

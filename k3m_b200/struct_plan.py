@@ -110,3 +110,32 @@ def pad_struct_plan(plan, B, max_num_pv, num_negative_pv):
     out["pair_rows"][:P] = plan["pair_rows"]
     out["terms"][:T] = plan["terms"]
     return out
+
+
+def mlm_capacity(n_title_rows, n_pv_rows, frac=(0.25, 0.4)):
+    """Static capacities (multiples of 128 rows) of the labelled-row lists of the title / PV masked-LM losses: the
+    loader masks 15 % of the title tokens and a part of the PV value tokens (`concept_cap_dataset_struc.py:785-860`)."""
+    r = lambda x: max(128, (int(x) + 127) // 128 * 128)      # noqa: E731
+    return min(r(n_title_rows * frac[0]), r(n_title_rows)), min(r(n_pv_rows * frac[1]), r(n_pv_rows))
+
+
+def build_mlm_plan(labels_t, labels_pv, cap=None):
+    """Rows of the stacked fused sequence S = [title rows | PV rows] that carry a masked-LM label, for the gathered MLM
+    head (`Engine.forward`).  labels_*: integer arrays [B, L] (-1 = no label).  cap = (cap_t, cap_pv) pads both lists to
+    fixed sizes (CUDA graphs) and raises when a batch has more labels than that; None sizes them to the batch (eager).
+    -> dict(mlm_rows int32 [cap_t + cap_pv] (-1 = padding), mlm_labels int64 [cap_t + cap_pv], cap_t int)"""
+    lt = np.asarray(labels_t).reshape(-1)
+    lp = np.asarray(labels_pv).reshape(-1)
+    it, ip = np.nonzero(lt != -1)[0], np.nonzero(lp != -1)[0]
+    if cap is None:
+        cap = (max(8, (len(it) + 7) // 8 * 8), max(8, (len(ip) + 7) // 8 * 8))
+    if len(it) > cap[0] or len(ip) > cap[1]:
+        raise ValueError("batch has %d / %d masked-LM labels, the step was built for at most %d / %d "
+                         "(raise mlm_cap_frac)" % (len(it), len(ip), cap[0], cap[1]))
+    rows = np.full(cap[0] + cap[1], -1, dtype=np.int32)
+    labs = np.full(cap[0] + cap[1], -1, dtype=np.int64)
+    rows[:len(it)] = it
+    labs[:len(it)] = lt[it]
+    rows[cap[0]:cap[0] + len(ip)] = len(lt) + ip
+    labs[cap[0]:cap[0] + len(ip)] = lp[ip]
+    return dict(mlm_rows=rows, mlm_labels=labs, cap_t=int(cap[0]))

@@ -28,7 +28,7 @@ from . import optim
 from .engine import Engine
 from .layout import ArenaLayout
 from .ops import CudaOps
-from .struct_plan import build_struct_plan, pad_struct_plan, plan_capacity
+from .struct_plan import build_mlm_plan, build_struct_plan, mlm_capacity, pad_struct_plan, plan_capacity
 
 LOSS_NAMES = ("loss_t", "loss_v", "loss_pv", "loss_itm", "loss_lpm")
 
@@ -58,7 +58,7 @@ class PretrainStep(object):
                  state_dict=None, init_seed=0, lr=1e-4, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01,
                  warmup_steps=0, total_steps=0, loss_img_weight=1.0, training=True, rng_seed=1234,
                  use_graph=True, process_group=None, bucket_mb=None, overlap=True, ops=None, comm_bf16=None,
-                 dp_fused=None):
+                 dp_fused=None, mlm_cap_frac=(0.25, 0.4)):
         """`ops`: kernel table; default (and the only product path) is `CudaOps`, which raises without
         a CUDA device.  Tests inject the fp32 PyTorch restatement to check this host logic on CPU."""
         self.cfg, self.device = cfg, torch.device(device)
@@ -108,9 +108,18 @@ class PretrainStep(object):
                          n_terms=torch.zeros(1, dtype=i32, device=dev),
                          fallback=torch.full((self.HALVES, 2), -1, dtype=i32, device=dev))
         self.plan["seg"]._k3m_maxn = maxn
+        # masked-LM head on the labelled rows only: static row / label lists of a fixed capacity (`build_mlm_plan`)
+        self.mlm_cap = None
+        if self.KIND == "pretrain" and mlm_cap_frac is not None:
+            self.mlm_cap = mlm_capacity(batch_size * len_t, batch_size * len_pv, mlm_cap_frac)
+            n = self.mlm_cap[0] + self.mlm_cap[1]
+            self.plan["mlm_rows"] = torch.full((n,), -1, dtype=i32, device=dev)
+            self.plan["mlm_labels"] = torch.full((n,), -1, dtype=torch.int64, device=dev)
         pin = (lambda t: t.pin_memory()) if self._cuda else (lambda t: t)
-        self._plan_host = [{k: pin(torch.zeros(v.shape, dtype=i32)) for k, v in self.plan.items()}
+        self._plan_host = [{k: pin(torch.zeros(v.shape, dtype=v.dtype)) for k, v in self.plan.items()}
                            for _ in range(2)]
+        if self.mlm_cap is not None:
+            self.plan["mlm_cap_t"] = self.mlm_cap[0]
         # AdamW hyper-parameters live on the device (graph nodes stay valid); ring of pinned copies
         self.hyper = torch.zeros(2, 8, dtype=f32, device=dev)
         self._hyper_host = [pin(torch.zeros(2, 8, dtype=f32)) for _ in range(2)]
@@ -119,7 +128,7 @@ class PretrainStep(object):
         self.losses = torch.zeros(8, dtype=f32, device=dev)
         self.losses_host = pin(torch.zeros(8, dtype=f32))
         self.h2d_bytes = sum(int(np.prod(s)) * (8 if d == torch.int64 else 4) for s, d in self.spec.values())
-        self.h2d_bytes += sum(v.numel() * 4 for v in self.plan.values()) + self.hyper.numel() * 4
+        self.h2d_bytes += sum(v.numel() * v.element_size() for v in self.plan.values() if torch.is_tensor(v)) + self.hyper.numel() * 4
         self.d2h_bytes = self.losses.numel() * 4
         # data-parallel runs reduce in 256 MB pieces on a high-priority stream: measured at 8 GPUs (NVLS
         # all-reduce of the 1.85 GB fp32 gradient arena overlapping backward) 64 MB -> 25.3 ms / step,
@@ -464,8 +473,20 @@ class PretrainStep(object):
         del snap
         self.graph = torch.cuda.CUDAGraph()
         n0 = self.ops.launches
-        with torch.cuda.graph(self.graph, stream=s):
-            self._device_step()
+        # No garbage collection while the capture is open: a collected object whose finaliser frees CUDA resources (an
+        # older step's graph and its memory pool, pinned buffers) makes a prohibited call from inside a global-mode
+        # capture and invalidates it (seen as a flaky cudaErrorStreamCaptureInvalidated when several step objects
+        # are created in one process).  torch.cuda.graph collects once on entry; nothing may be collected after that.
+        import gc
+        gc.collect()
+        was_enabled = gc.isenabled()
+        gc.disable()
+        try:
+            with torch.cuda.graph(self.graph, stream=s):
+                self._device_step()
+        finally:
+            if was_enabled:
+                gc.enable()
         self.launches_per_step = self.ops.launches - n0
 
     # ---- host side -----------------------------------------------------------------------------
@@ -491,6 +512,9 @@ class PretrainStep(object):
         plan = build_struct_plan(batch["index_p"].numpy(), batch["index_v"].numpy(), self.Lpv,
                                  self.cfg.num_negative_pv, halves=self.HALVES)
         plan = pad_struct_plan(plan, self.n_items, self.max_num_pv, self.cfg.num_negative_pv)
+        if self.mlm_cap is not None:
+            mp = build_mlm_plan(batch["masked_lm_labels"].numpy(), batch["masked_lm_labels_pv"].numpy(), self.mlm_cap)
+            plan["mlm_rows"], plan["mlm_labels"] = mp["mlm_rows"], mp["mlm_labels"]
         ph = self._plan_host[slot]
         for k, v in plan.items():
             ph[k].copy_(torch.from_numpy(v).reshape(ph[k].shape))
@@ -513,7 +537,7 @@ class PretrainStep(object):
                 self._copy_stream = torch.cuda.Stream(device=self.device)
                 mk = lambda t: torch.empty_like(t)          # noqa: E731
                 self._stage = [dict(inputs={k: mk(v) for k, v in self.inputs.items()},
-                                    plan={k: mk(v) for k, v in self.plan.items()}, hyper=mk(self.hyper))
+                                    plan={k: mk(v) for k, v in self.plan.items() if torch.is_tensor(v)}, hyper=mk(self.hyper))
                                for _ in range(2)]
             st = self._stage[slot]
             main = torch.cuda.current_stream()
@@ -526,7 +550,7 @@ class PretrainStep(object):
                 landed = torch.cuda.Event()
                 landed.record(self._copy_stream)
             main.wait_event(landed)
-            for k in self.plan:
+            for k in st["plan"]:
                 self.plan[k].copy_(st["plan"][k], non_blocking=True)
             for k in self.inputs:
                 self.inputs[k].copy_(st["inputs"][k], non_blocking=True)

@@ -36,7 +36,7 @@ from torch import nn
 from .config import BertConfig  # noqa: F401  (re-exported under the reference's module path)
 from .engine import Engine
 from .layout import ArenaLayout, TIED_ALIAS
-from .struct_plan import build_struct_plan, pad_struct_plan, plan_capacity
+from .struct_plan import build_mlm_plan, build_struct_plan, mlm_capacity, pad_struct_plan, plan_capacity
 
 logger = logging.getLogger(__name__)
 
@@ -68,14 +68,22 @@ class _GraphedStep(object):
                          seg=torch.zeros(self.B, 2, dtype=i32, device=dev), terms=torch.zeros(T_cap, 4, dtype=i32, device=dev),
                          n_terms=torch.zeros(1, dtype=i32, device=dev), fallback=torch.full((1, 2), -1, dtype=i32, device=dev))
         self.plan["seg"]._k3m_maxn = maxn
+        self.mlm_cap = mlm_capacity(batch["input_ids"].numel(), batch["input_ids_pv"].numel(), (0.3, 0.5))
+        self.plan["mlm_rows"] = torch.full((sum(self.mlm_cap),), -1, dtype=i32, device=dev)
+        self.plan["mlm_labels"] = torch.full((sum(self.mlm_cap),), -1, dtype=torch.int64, device=dev)
+        self.plan["mlm_cap_t"] = self.mlm_cap[0]
         self.scales = [torch.ones(1, dtype=torch.float32, device=dev) for _ in range(4)]
         self.g_fwd = self.g_bwd = None
         self.out = None
 
-    def load(self, batch, plan_np):
+    def load(self, batch, plan_np, labels):
+        self._labels = labels
         for k, v in batch.items():
             self.inputs[k].copy_(v, non_blocking=True)
-        padded = pad_struct_plan(plan_np, self.B, self.max_num_pv, self.owner.config.num_negative_pv)
+        struct = {k: v for k, v in plan_np.items() if k not in ("mlm_rows", "mlm_labels", "cap_t")}
+        padded = pad_struct_plan(struct, self.B, self.max_num_pv, self.owner.config.num_negative_pv)
+        mp = build_mlm_plan(self._labels[0], self._labels[1], self.mlm_cap)
+        padded["mlm_rows"], padded["mlm_labels"] = mp["mlm_rows"], mp["mlm_labels"]
         for k, v in padded.items():
             self.plan[k].copy_(torch.from_numpy(v).reshape(self.plan[k].shape), non_blocking=False)
 
@@ -83,14 +91,22 @@ class _GraphedStep(object):
         eng = self.owner._engine
         s = torch.cuda.Stream(device=self.owner._arena.device)
         s.wait_stream(torch.cuda.current_stream())
-        self.g_fwd = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.g_fwd, stream=s):
-            self.out = eng.forward(self.inputs, self.plan, None, (1.0, 1.0, 1.0, 1.0))
-        saved = eng.saved
-        self.g_bwd = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.g_bwd, pool=self.g_fwd.pool(), stream=s):
-            eng.saved = saved
-            eng.backward(tuple(self.scales))
+        import gc
+        gc.collect()
+        was_enabled = gc.isenabled()
+        gc.disable()              # see PretrainStep._capture: no finaliser may run inside an open capture
+        try:
+            self.g_fwd = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.g_fwd, stream=s):
+                self.out = eng.forward(self.inputs, self.plan, None, (1.0, 1.0, 1.0, 1.0))
+            saved = eng.saved
+            self.g_bwd = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.g_bwd, pool=self.g_fwd.pool(), stream=s):
+                eng.saved = saved
+                eng.backward(tuple(self.scales))
+        finally:
+            if was_enabled:
+                gc.enable()
         torch.cuda.current_stream().wait_stream(s)
 
     def forward(self):
@@ -440,6 +456,9 @@ class BertForMultiModalPreTraining_tri_stru(K3MPreTrainedModel):
         # tensors replaces the reference's one sync per (item, PV) pair
         plan_np = build_struct_plan(index_p.detach().cpu().numpy(), index_v.detach().cpu().numpy(),
                                     batch["input_ids_pv"].shape[1], self.config.num_negative_pv)
+        # rows that carry a masked-LM label: the head runs on those only (`Engine.forward`)
+        labels_np = (masked_lm_labels.detach().cpu().numpy(), masked_lm_labels_pv.detach().cpu().numpy())
+        plan_np.update(build_mlm_plan(*labels_np))
         self._refresh_shadow()
         eng = self._engine
         eng.training = self.training
@@ -456,10 +475,10 @@ class BertForMultiModalPreTraining_tri_stru(K3MPreTrainedModel):
             else:
                 if ent == 0:
                     ent = self._graphs[key] = _GraphedStep(self, batch, index_p.shape[1])
-                    ent.load(batch, plan_np)
+                    ent.load(batch, plan_np, labels_np)
                     ent.capture()
                 else:
-                    ent.load(batch, plan_np)
+                    ent.load(batch, plan_np, labels_np)
                 graphed = ent
         plan = None if graphed is not None else self._ops.plan_to_device(plan_np, dev)
         if torch.is_grad_enabled():

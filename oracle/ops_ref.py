@@ -321,6 +321,18 @@ class RefOps(object):
         dg = dlog * ak * (1.0 - ak)
         return dg.reshape(M, H3).to(self.adt), (do * hard).reshape(M, H3).to(self.adt)
 
+    def gather_rows(self, src, idx):
+        """out[i] = src[idx[i]], zero rows where idx < 0 (labelled-row gather of the MLM head)"""
+        i = idx.long()
+        out = src[i.clamp_min(0)].clone()
+        out[i < 0] = 0
+        return out
+
+    def scatter_add_rows(self, dsrc, idx, dst):
+        i = idx.long()
+        ok = i >= 0
+        dst[i[ok]] = (dst[i[ok]].float() + dsrc[ok].float()).to(dst.dtype)
+
     def gate_mul(self, cat, alpha):
         """soft fusion (`:2300-2329`): cat * alpha, stored in the activation dtype."""
         return (cat.float() * alpha.float()).to(self.adt)
@@ -540,7 +552,10 @@ class RefOps(object):
 
     # ---- optimizer -------------------------------------------------------------------------
     def plan_to_device(self, plan, device):
-        return {k: torch.from_numpy(v).to(device) for k, v in plan.items()}
+        out = {k: torch.from_numpy(v).to(device) for k, v in plan.items() if k != "cap_t"}
+        if "cap_t" in plan:
+            out["mlm_cap_t"] = int(plan["cap_t"])
+        return out
 
     def adamw(self, p32, g32, m, v, p_act, hyper, zero_grad=True, background=False, g16=None):
         """torch.optim.AdamW step on a flat range.  hyper fp32 [8] = (lr, beta1, beta2, eps, wd,

@@ -36,3 +36,16 @@ def test_dropout_mask_is_regenerated_consistently():
     o3, _, g3 = run_engine(cfg, sd, batch, noise, ops, "cpu", torch.float32, 1, training=False)
     assert not torch.equal(g1, g3)
     assert abs(float(o1["loss_t"]) - float(o3["loss_t"])) > 1e-6
+
+
+def test_dense_and_gathered_mlm_head_agree():
+    """The masked-LM head on the labelled rows only (`build_mlm_plan`, the product path) gives the losses and gradients
+    of the reference's all-position decoder + ignore_index."""
+    fx = load_golden("tiny_hard")
+    cfg, sd, batch, noise = case_setup(fx)
+    o1, L, g1 = run_engine(cfg, sd, batch, noise, RefOps(torch.float32), "cpu", torch.float32, fx["seeds"]["python"])
+    o2, _, g2 = run_engine(cfg, sd, batch, noise, RefOps(torch.float32), "cpu", torch.float32, fx["seeds"]["python"],
+                           gather_mlm=False)
+    for k in ("loss_t", "loss_pv"):
+        assert float(o1[k]) == pytest.approx(float(o2[k]), rel=1e-6)
+    assert float((g1 - g2).abs().max()) <= 1e-6 * float(g2.abs().max())

@@ -526,6 +526,24 @@ def test_loc_embed(ops, ref):
     close(res[0][1], res[1][1], 1e-4, 1e-3, "loc db")
 
 
+def test_gather_and_scatter_rows_bit_exact(ops, ref):
+    """Labelled-row gather of the MLM head: row copies are bit-exact, padding (-1) gives zero rows / is skipped."""
+    M, H, n = 4608, 768, 1152
+    src = rnd(M, 3 * H)[:, H:2 * H]                       # a strided view
+    g = torch.Generator().manual_seed(3)
+    idx = torch.randperm(M, generator=g)[:n].to(torch.int32)
+    idx[-100:] = -1
+    idx = idx.to(DEV)
+    got, want = ops.gather_rows(src, idx), ref.gather_rows(src, idx)
+    assert torch.equal(got, want) and float(got[-100:].abs().max()) == 0.0
+    d = rnd(n, H, seed=5)
+    a, b = rnd(M, H, seed=6), None
+    b = a.clone()
+    ops.scatter_add_rows(d, idx, a)
+    ref.scatter_add_rows(d, idx, b)
+    assert torch.equal(a, b)
+
+
 def test_soft_fusion_gate_kernels(ops, ref):
     """if_pre_sampling = 2 (`vilbert_k3m.py:2300-2329`): gated = cat * alpha and its backward."""
     M, H = 333, 768

