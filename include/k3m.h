@@ -254,6 +254,17 @@ int k3m_prep_regions(const float* boxes, const int* num_boxes, const float* whp,
                      const float* feat, int B, int R, int F, float* image_feat, float* image_loc,
                      long long* image_mask, long long* image_label, unsigned char* zero_flag, int* count0,
                      void* stream);
+/* k3m_prep_regions for callers that cannot allocate.  NO counterpart in the reference: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.
+ * Same inputs, outputs and results (bit for bit) as k3m_prep_regions, but the zero_flag / count0 scratch lives in a
+ * static device array of the library (1 MiB + 16 KiB per GPU that loads it, held until exit) and the call performs
+ * no cudaMalloc / cudaFree / allocating library call.  Limits: B <= 4096 and B * R <= 1048576, beyond that the
+ * call returns an argument error (use k3m_prep_regions with caller scratch).  All calls on a device share the
+ * array: calls that overlap on the GPU (different streams without a dependency) race; calls on one stream, or
+ * ordered by events, are safe.  Nothing needs clearing between calls (every scratch byte read is written first). */
+int k3m_prep_regions_noalloc(const float* boxes, const int* num_boxes, const float* whp, const double* u,
+                             const float* feat, int B, int R, int F, float* image_feat, float* image_loc,
+                             long long* image_mask, long long* image_label, void* stream);
 
 /* all of the above in two launches (title / PV / regions rows in one, the feature pass after it): what
  * k3m_b200/preprocess.py calls per batch.  Arguments as in the three entry points above.                      */

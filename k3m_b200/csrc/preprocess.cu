@@ -346,3 +346,72 @@ extern "C" int k3m_prep_batch(const long long* tokens, const int* n_tok, const d
   if (rc) return rc;
   return launch_feat(feat, zero_flag, count0, B, R, F, image_feat, st);
 }
+
+// ---- k3m_prep_regions without any allocation on the caller's side ------------------------------------------------
+// For callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): the
+// two scratch ranges of k3m_prep_regions (zero_flag [B, R] bytes, count0 [B] ints) live in a file-scope device array
+// instead of caller memory.  Every GPU that loads the library holds K3M_PREP_SCRATCH_BYTES (1 MiB + 16 KiB) until
+// exit.  Layout: bytes [0, K3M_PREP_MAX_BR) zero_flag, then K3M_PREP_MAX_B ints count0.
+// The rows pass writes zero_flag[b, r] for EVERY r < R and count0[b] for every b before the feature pass (next launch
+// on the same stream) reads them, so nothing has to start at zero and nothing is cleared; what the previous call left
+// behind is overwritten or never read.  All calls on a device share the array: two calls that overlap on the GPU
+// (different streams, no dependency) race on it.
+#include <mutex>
+
+#define K3M_PREP_MAX_B 4096
+#define K3M_PREP_MAX_BR (1 << 20)
+#define K3M_PREP_SCRATCH_BYTES (K3M_PREP_MAX_BR + K3M_PREP_MAX_B * 4)
+
+static __device__ __align__(256) unsigned char k3m_prep_scratch[K3M_PREP_SCRATCH_BYTES];
+
+namespace {
+constexpr int MAX_DEVICES = 64;
+unsigned char* g_prep_scratch_addr[MAX_DEVICES];     // device address of k3m_prep_scratch, per device ordinal
+std::mutex g_prep_scratch_mu;
+
+// In host code `k3m_prep_scratch` is only a handle for the runtime, not a device address: ask the runtime, once per
+// device, with that device current, and cache the answer.
+int prep_scratch_addr(unsigned char** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) {
+    k3m_set_error("k3m_prep_regions_noalloc: cudaGetDevice -> %d (%s)", dev, cudaGetErrorString(e));
+    return K3M_ERR_CUDA;
+  }
+  std::lock_guard<std::mutex> lock(g_prep_scratch_mu);
+  if (!g_prep_scratch_addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, k3m_prep_scratch);
+    if (e != cudaSuccess || !p) {
+      k3m_set_error("k3m_prep_regions_noalloc: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+      return K3M_ERR_CUDA;
+    }
+    g_prep_scratch_addr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_prep_scratch_addr[dev];
+  return K3M_OK;
+}
+}  // namespace
+
+extern "C" int k3m_prep_regions_noalloc(const float* boxes, const int* num_boxes, const float* whp, const double* u,
+                                        const float* feat, int B, int R, int F, float* image_feat, float* image_loc,
+                                        long long* image_mask, long long* image_label, void* stream) {
+  K3M_REQUIRE(B > 0 && R > 0 && F > 0, "prep_regions_noalloc: empty batch");
+  K3M_REQUIRE(B <= K3M_PREP_MAX_B && (long long)B * R <= K3M_PREP_MAX_BR,
+              "prep_regions_noalloc: B=%d R=%d exceeds the static scratch (B <= %d, B*R <= %d); use k3m_prep_regions "
+              "with caller scratch", B, R, K3M_PREP_MAX_B, K3M_PREP_MAX_BR);
+  const size_t smem = rows_smem(0, R);
+  K3M_REQUIRE(smem <= 48 * 1024, "prep_regions_noalloc: too many regions (R=%d)", R);
+  unsigned char* scratch = nullptr;
+  if (int rc = prep_scratch_addr(&scratch)) return rc;
+  unsigned char* zero_flag = scratch;
+  int* count0 = reinterpret_cast<int*>(scratch + K3M_PREP_MAX_BR);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  PrepArgs a = {};
+  a.boxes = boxes; a.num_boxes = num_boxes; a.whp = whp; a.u_reg = u; a.R = R;
+  a.image_loc = image_loc; a.image_mask = image_mask; a.image_label = image_label;
+  a.zero_flag = zero_flag; a.count0 = count0;
+  prep_rows_kernel<<<dim3(B, 1), 128, smem, st>>>(a, 2);
+  if (int rc = k3m_check_launch("k3m_prep_regions_noalloc")) return rc;
+  return launch_feat(feat, zero_flag, count0, B, R, F, image_feat, st);
+}
