@@ -69,6 +69,7 @@ template <int MAXP>
 struct GroupArgs {
   int n;
   int total_tiles;
+  int snake;      // odd waves walk the tile list backwards (see tile_of in the kernel)
   ProblemArgs prob[MAXP];
 };
 
@@ -161,8 +162,11 @@ __device__ __forceinline__ bool elect_one() {
       "}" : "=r"(pred));
   return pred != 0;
 }
+// No .release.cluster here: what the arrive orders are this warp's TMEM reads, and those are ordered by
+// tcgen05.wait::ld + tcgen05.fence::before_thread_sync; a cluster-scope release compiles to MEMBAR.ALL.GPU + ERRBAR
+// in front of the arrive — 12-14 % of all stall samples of the K = 768 epilogues (profiles/r03a_gemm_*_hot.txt).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster) : "memory");
 }
 
 __device__ __forceinline__ void tmem_ld32(uint32_t addr, uint32_t r[32]) {
@@ -328,16 +332,35 @@ __device__ __forceinline__ void unpack_bf16x8(const uint4& u, float v[8]) {
   }
 }
 
-// acc (+ bias) of one 8-column group
-__device__ __forceinline__ void acc_bias(const GemmParams& p, const uint32_t* r, int col, float v[8]) {
+// 16-byte shared-memory accesses by 32-bit shared address (the staging buffers): `*reinterpret_cast<uint4*>(ptr)` on
+// a pointer derived from the dynamic shared array compiled to GENERIC ST.E.128 / LD.E.128 with 64-bit address math.
+// volatile keeps them ordered against the barrier waits / proxy fences around them (all volatile asm); no "memory"
+// clobber, so that ordinary global loads (bias, dropout counter) may still be hoisted across them.
+__device__ __forceinline__ void sts16(uint32_t saddr, const uint4& u) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(u.x), "r"(u.y), "r"(u.z), "r"(u.w));
+}
+__device__ __forceinline__ uint4 lds16(uint32_t saddr) {
+  uint4 u;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "r"(saddr));
+  return u;
+}
+
+// The bias of a 32-column slab (four 16-byte loads) is requested BEFORE the TMEM read of the slab, so that the two
+// latencies overlap; loading it per 8-column group right where it is added put a global-load round trip in front of
+// every group (long-scoreboard stalls on the unpack instructions, profiles/r03a_gemm_gelu_hot.txt).
+__device__ __forceinline__ void load_bias32(const GemmParams& p, int col0, uint4 braw[4]) {
 #pragma unroll
-  for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[j]);
-  if (p.bias != nullptr && col < p.N) {
-    float t[8];
-    ld8(p.bias + col, t);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] += t[j];
+  for (int g = 0; g < 4; ++g) {
+    const int col = col0 + g * 8;
+    braw[g] = (p.bias != nullptr && col < p.N) ? __ldg(reinterpret_cast<const uint4*>(p.bias + col)) : make_uint4(0u, 0u, 0u, 0u);
   }
+}
+// acc + bias of one 8-column group
+__device__ __forceinline__ void acc_bias(const uint32_t* r, const uint4& braw, float v[8]) {
+  float t[8];
+  unpack_bf16x8(braw, t);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[j]) + t[j];
 }
 
 // one 32-row x CW-column piece of an output tile, by one epilogue warp (row = lane)
@@ -349,6 +372,7 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
   constexpr uint32_t SM = RB == 64 ? 3u : 7u;     // 64-byte rows are SWIZZLE_64B boxes
   uint8_t* buf = my_stage + (nstore % NBUF) * 4096;
   uint8_t* abuf = my_stage + ((nstore + 1) % NBUF) * 4096;
+  const uint32_t sbuf = smem_u32(buf), sabuf = smem_u32(abuf);
   if (MODE == F_PLAIN || MODE == F_GELU) {        // (TMA-fed modes: the operand prefetch waited already)
     if (lane == 0) {
       if (MODE == F_GELU || NBUF == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -363,17 +387,19 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
     for (int pass = 0; pass < 2; ++pass) {
 #pragma unroll
       for (int cc = 0; cc < CW; cc += 32) {
+        uint4 braw[4];
+        load_bias32(p, n0 + cc, braw);
         uint32_t r[32];
         tmem_ld32(tbase + (uint32_t)cc, r);
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           float v[8];
-          acc_bias(p, r + g * 8, n0 + cc + g * 8, v);
+          acc_bias(r + g * 8, braw[g], v);
           if (pass == 1) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
           }
-          *reinterpret_cast<uint4*>(buf + swz((uint32_t)lane * RB + (uint32_t)((cc + g * 8) * 2), SM)) = pack_bf16x8(v);
+          sts16(sbuf + swz((uint32_t)lane * RB + (uint32_t)((cc + g * 8) * 2), SM), pack_bf16x8(v));
         }
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -390,8 +416,12 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
   }
   const bool has_drop = p.drop.thresh != 0;
   const int row = row0 + lane;
+  unsigned long long seed = 0ull, step = 0ull;     // read once per tile, not once per 8-column group
+  if (MODE != F_GELU && MODE != F_DGELU && has_drop) { seed = p.drop.rng[0]; step = p.drop.rng[1]; }
 #pragma unroll
   for (int cc = 0; cc < CW; cc += 32) {
+    uint4 braw[4];
+    load_bias32(p, n0 + cc, braw);
     uint32_t r[32];
     tmem_ld32(tbase + (uint32_t)cc, r);
 #pragma unroll
@@ -399,32 +429,34 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
       const int col = n0 + cc + g * 8;
       const uint32_t off = swz((uint32_t)lane * RB + (uint32_t)((cc + g * 8) * 2), SM);
       float v[8];
-      acc_bias(p, r + g * 8, col, v);
+      acc_bias(r + g * 8, braw[g], v);
       if (MODE == F_GELU) {
-        *reinterpret_cast<uint4*>(abuf + off) = pack_bf16x8(v);
+        sts16(sabuf + off, pack_bf16x8(v));
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
       }
       if (MODE == F_DGELU) {
         float t[8];
-        unpack_bf16x8(*reinterpret_cast<const uint4*>(buf + off), t);
+        unpack_bf16x8(lds16(sbuf + off), t);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] *= dgelu_f(t[j]);
       }
       if (MODE != F_GELU && MODE != F_DGELU && has_drop) {
         uint32_t w[4];
         const unsigned long long lin = (unsigned long long)row * (unsigned long long)p.drop_ld + (unsigned long long)col;
-        rng_words(p.drop.rng, p.drop.site, lin >> 3, w);
+        const unsigned long long idx = lin >> 3;      // == rng_words(p.drop.rng, p.drop.site, idx, w)
+        philox4x32((uint32_t)idx, (uint32_t)(idx >> 32), p.drop.site, (uint32_t)step, (uint32_t)seed,
+                   (uint32_t)(seed >> 32), w);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] *= drop_mult(p.drop, w, j);
       }
       if (MODE == F_ADD) {
         float t[8];
-        unpack_bf16x8(*reinterpret_cast<const uint4*>(buf + off), t);
+        unpack_bf16x8(lds16(sbuf + off), t);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] += t[j];
       }
-      *reinterpret_cast<uint4*>(buf + off) = pack_bf16x8(v);
+      sts16(sbuf + off, pack_bf16x8(v));
     }
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -478,6 +510,12 @@ gemm_kernel(const __grid_constant__ GroupArgs<MAXP> g) {
   const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;
   const bool leader = rank == 0;
   const int tile0 = blockIdx.x / CTAS, tstride = gridDim.x / CTAS;     // tiles are walked per CTA pair
+  // Wave w of the walk: tile w * tstride + tile0, and with `snake` the odd waves mirrored (tstride - 1 - tile0).  The
+  // tile list is ordered longest-k first, so the last waves of a grouped launch mix long and short tiles: the plain
+  // stride hands the same low-numbered CTAs the long tile of EVERY mixed wave (e.g. 108 tiles of 48 k-blocks + 76
+  // of 16 on 74 pairs: 48+48+16 against an average of 86), the mirrored walk alternates (48+16+16 / 48+48).
+  const int tile0m = g.snake ? tstride - 1 - tile0 : tile0;
+  auto tile_of = [&](int w) { return w * tstride + ((w & 1) ? tile0m : tile0); };
   // problem of a tile of the launch's list: tiles only grow along a CTA's walk, so `pi` only moves forward
   auto locate = [&](int tile, int& pi) {
     if (MAXP > 1) {
@@ -528,7 +566,7 @@ gemm_kernel(const __grid_constant__ GroupArgs<MAXP> g) {
       uint32_t it = 0;
       int pi = 0;
       const uint32_t full0 = CTAS == 2 ? mapa_u32(smem_u32(&full[0]), 0) : 0u;   // the leader's full barriers
-      for (int tile = tile0; tile < total_tiles; tile += tstride) {
+      for (int w = 0, tile; (tile = tile_of(w)) < total_tiles; ++w) {
         locate(tile, pi);
         const ProblemArgs& pr = g.prob[MAXP > 1 ? pi : 0];
         const GemmParams& p = pr.p;
@@ -598,7 +636,7 @@ gemm_kernel(const __grid_constant__ GroupArgs<MAXP> g) {
                                  ((uint32_t)((BM * CTAS) >> 4) << 24);
       uint32_t it = 0, lt = 0;
       int pi = 0;
-      for (int tile = tile0; tile < total_tiles; tile += tstride, ++lt) {
+      for (int tile; (tile = tile_of((int)lt)) < total_tiles; ++lt) {
         locate(tile, pi);
         const ProblemArgs& pr = g.prob[MAXP > 1 ? pi : 0];
         const int tiles_mn = pr.p.tiles_m * pr.p.tiles_n;
@@ -681,13 +719,13 @@ gemm_kernel(const __grid_constant__ GroupArgs<MAXP> g) {
       }
     };
     int pi = 0, pnext = 0;
-    if (tile0 < total_tiles) {
-      locate(tile0, pnext);
-      prefetch_in(tile0, pnext);
+    if (tile_of(0) < total_tiles) {
+      locate(tile_of(0), pnext);
+      prefetch_in(tile_of(0), pnext);
     }
     const uint32_t tmem_empty0 = CTAS == 2 ? mapa_u32(smem_u32(&tmem_empty[0]), 0) : 0u;   // the leader's
     uint32_t lt = 0;
-    for (int tile = tile0; tile < total_tiles; tile += tstride, ++lt) {
+    for (int tile; (tile = tile_of((int)lt)) < total_tiles; ++lt) {
       locate(tile, pi);
       const ProblemArgs& pr = g.prob[MAXP > 1 ? pi : 0];
       const GemmParams& p = pr.p;
@@ -804,9 +842,10 @@ gemm_kernel(const __grid_constant__ GroupArgs<MAXP> g) {
         if (CTAS == 2) mbar_arrive_cluster(tmem_empty0 + as * 8u);
         else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[as])) : "memory");
       }
-      if (tile + tstride < total_tiles) {
-        locate(tile + tstride, pnext);
-        prefetch_in(tile + tstride, pnext);
+      const int tnext = tile_of((int)lt + 1);
+      if (tnext < total_tiles) {
+        locate(tnext, pnext);
+        prefetch_in(tnext, pnext);
       }
     }
     // the staging buffers must outlive the bulk stores' READS only; global visibility of the writes is
@@ -920,6 +959,8 @@ int launch(GroupArgs<MAXP>& g, cudaStream_t st) {
     total += p.tiles_m * p.tiles_n * p.splits;
   }
   g.total_tiles = total;
+  static const int snake = getenv("K3M_GEMM_SNAKE") ? atoi(getenv("K3M_GEMM_SNAKE")) : 1;
+  g.snake = snake;
   const int slots = num_sms() * (STAGES <= 2 ? 2 : 1) / CTAS;     // CTAs (or CTA pairs) resident at once
   const int grid = (total < slots ? total : slots) * CTAS;
   static const int pdl = getenv("K3M_GEMM_PDL") ? atoi(getenv("K3M_GEMM_PDL")) : 0;

@@ -18,6 +18,8 @@ B200-first differences from the reference's eager graph (results are the same):
     gradients straight into one flat fp32 arena (the all-reduce / AdamW buffer).
   * Static shapes, no host synchronisation inside -> the whole step is CUDA-graph capturable.
 """
+import os
+
 import torch
 
 from .struct_plan import build_struct_plan
@@ -60,6 +62,12 @@ class Engine(object):
         self._site = 0
         self._wv, self._gv = {}, {}
         self.on_ready = None     # callback(prefixes | None): weight gradients of these blocks are final
+        # Weight / bias gradients of one layer group (or one connection stage) are collected while its backward runs
+        # and leave as grouped launches at its end (`_flush_grads`): a text + image layer has 4 x 2 weight gradients
+        # of one layout -> ONE persistent launch of 8 problems instead of four launches of two (each of which drains
+        # the GPU behind its own last wave).  None = not collecting (every caller outside those two blocks).
+        self._pend_w = self._pend_b = None
+        self.defer_grads = os.environ.get("K3M_DEFER_GRADS", "1") != "0"
         # per-layer parity taps (tests only; never set inside a captured step): when a dict, `tower_fwd` stores the
         # output of every BertLayer / BertImageLayer / BertConnectionLayer application under the key the reference's
         # module call would have: "<module name>#<call index>[/<output index>]" (tools/make_golden.py install_taps)
@@ -103,6 +111,9 @@ class Engine(object):
 
     def bgrads(self, items):
         """G[b] += column sums of dy for every (dy, bname): one grouped launch on the auxiliary stream."""
+        if self._pend_b is not None:
+            self._pend_b.extend(items)
+            return
         grp = getattr(self.ops, "colsum_group", None)
         if grp is None or len(items) == 1:
             for dy, b in items:
@@ -143,9 +154,30 @@ class Engine(object):
 
     def wgrads(self, items):
         """G[w] += dy^T x for every (dy, x, wname): one grouped launch on the auxiliary stream."""
+        if self._pend_w is not None:
+            self._pend_w.extend(items)
+            return
         calls = [dict(a=dy, b=x, layout="tn", out=self.G(w), accumulate=True) for dy, x, w in items]
         keep = tuple(t for dy, x, _ in items for t in (dy, x))
         self._aux(lambda: self.gemms(calls), keep)
+
+    def _collect_grads(self):
+        if self.defer_grads:
+            self._pend_w, self._pend_b = [], []
+
+    def _flush_grads(self):
+        """Launch what `wgrads` / `bgrads` collected since `_collect_grads`: operands are fresh outputs of this
+        block's backward or saved forward activations, none of which is written again before the flush."""
+        pw, pb = self._pend_w, self._pend_b
+        self._pend_w = self._pend_b = None
+        if pb:
+            for i in range(0, len(pb), 8):
+                self.bgrads(pb[i:i + 8])
+        if pw:
+            # same reduction length (rows of the stream) first, so that a launch's tiles have equal k extents
+            pw = sorted(pw, key=lambda it: -it[0].shape[0])
+            for i in range(0, len(pw), 8):
+                self.wgrads(pw[i:i + 8])
 
     def lns_fwd(self, items):
         """LayerNorm of every stream of a group: one grouped launch when the op table has one -> [(y, mean, rstd)]"""
@@ -253,6 +285,7 @@ class Engine(object):
     def layers_bwd_m(self, items):
         """items: (dy, saved) -> [dx]."""
         ops = self.ops
+        self._collect_grads()
         das = self.ffn_bwd_m([(dy, sv[7]) for dy, sv in items])
         ao = self.attn_out_bwd_m([(das[i], sv[6]) for i, (_, sv) in enumerate(items)])
         dqkvs = [self.empty(sv[1].shape[0], 3 * sv[1].shape[1]) for _, sv in items]
@@ -269,6 +302,7 @@ class Engine(object):
         self._each([attn(i) for i in range(len(items))])
         self.bgrads([(dqkvs[i], sv[0] + ".attention.self.qkv.bias") for i, (_, sv) in enumerate(items)])
         self.wgrads([(dqkvs[i], sv[1], sv[0] + ".attention.self.qkv.weight") for i, (_, sv) in enumerate(items)])
+        self._flush_grads()
         return self.gemms([dict(a=dqkvs[i], b=self.W(sv[0] + ".attention.self.qkv.weight"), layout="nn", rng=self.rng,
                                 addend=ao[i][0]) for i, (_, sv) in enumerate(items)])
 
@@ -325,6 +359,7 @@ class Engine(object):
     def connections_bwd_m(self, items):
         """items: (dy1, dy2, saved, dx1_out, dx2_out)."""
         ops = self.ops
+        self._collect_grads()
         ffi = []
         for dy1, dy2, sv, _, _ in items:
             ffi += [(dy1, sv[14]), (dy2, sv[15])]
@@ -360,6 +395,7 @@ class Engine(object):
                               out=dx2_out))
         self.bgrads(bg)
         self.wgrads(wg)
+        self._flush_grads()
         self.gemms(calls)
 
     # ---- embeddings ------------------------------------------------------------------------
