@@ -20,6 +20,7 @@
 #include <map>
 #include <mutex>
 #include <tuple>
+#include <vector>
 
 #include "common.cuh"
 
@@ -1021,6 +1022,60 @@ int pick_bn(int M, int N, int K, int force) {
   return (N >= 256 && tiles256 >= (long)num_sms() * 3 / 4) ? 256 : 128;
 }
 
+// Split-K plan of the accumulating (weight-gradient) problems of one launch.  The persistent walk hands tile t of the
+// list (problems ordered longest tile first, split-major inside a problem) to pair t % P of wave t / P, mirrored on odd
+// waves; a tile costs its k-blocks plus a fixed part (accumulator hand-over, fp32 reduce-add of a 128 KB tile).
+// Every "target k-blocks per tile" L gives one candidate plan (splits_i = round(kb_i / L), at least 4 k-blocks per
+// split); the plan with the smallest modelled makespan wins.  The earlier rule (double the splits until the launch
+// has three waves of tiles) ignored how the tile lengths of a mixed group fall onto the waves.
+double model_makespan(int n, const long* base_tiles, const int* kb, const int* splits, int P, bool snake) {
+  int ord[8];
+  int kbs[8];
+  for (int i = 0; i < n; ++i) { ord[i] = i; kbs[i] = (kb[i] + splits[i] - 1) / splits[i]; }
+  for (int i = 1; i < n; ++i)
+    for (int j = i; j > 0 && kbs[ord[j]] > kbs[ord[j - 1]]; --j) { const int t = ord[j]; ord[j] = ord[j - 1]; ord[j - 1] = t; }
+  static thread_local std::vector<double> load;
+  load.assign((size_t)P, 0.0);
+  const double TILE_FIXED = 1.5;
+  long t = 0;
+  for (int oi = 0; oi < n; ++oi) {
+    const int i = ord[oi];
+    const int ns = (kb[i] + kbs[i] - 1) / kbs[i];
+    for (int sp = 0; sp < ns; ++sp) {
+      const int nkb = sp + 1 < ns ? kbs[i] : kb[i] - (ns - 1) * kbs[i];
+      for (long m = 0; m < base_tiles[i]; ++m, ++t) {
+        const long w = t / P, pos = t % P;
+        load[(size_t)((snake && (w & 1)) ? P - 1 - pos : pos)] += nkb + TILE_FIXED;
+      }
+    }
+  }
+  double mx = 0.0;
+  for (int q = 0; q < P; ++q) mx = load[(size_t)q] > mx ? load[(size_t)q] : mx;
+  return mx + 2e-3 * (double)t;      // ties: fewer tiles (less reduce-add traffic)
+}
+void plan_splits(int n, const long* base_tiles, const int* kb, const bool* can_split, int P, int* splits) {
+  static const int snake = getenv("K3M_GEMM_SNAKE") ? atoi(getenv("K3M_GEMM_SNAKE")) : 1;
+  int kmax = 0;
+  bool any = false;
+  for (int i = 0; i < n; ++i) { splits[i] = 1; if (can_split[i]) { any = true; kmax = kb[i] > kmax ? kb[i] : kmax; } }
+  if (!any) return;
+  double best = model_makespan(n, base_tiles, kb, splits, P, snake != 0);
+  int cand[8];
+  for (int L = 4; L < kmax; ++L) {
+    for (int i = 0; i < n; ++i) {
+      int sp = 1;
+      if (can_split[i]) {
+        sp = (kb[i] + L / 2) / L;
+        if (sp > kb[i] / 4) sp = kb[i] / 4;
+        if (sp < 1) sp = 1;
+      }
+      cand[i] = sp;
+    }
+    const double m = model_makespan(n, base_tiles, kb, cand, P, snake != 0);
+    if (m < best) { best = m; for (int i = 0; i < n; ++i) splits[i] = cand[i]; }
+  }
+}
+
 // what the last k3m_gemm_bf16 / k3m_gemm_grouped_bf16 call of this thread dispatched (tests assert that the
 // benchmark's kernel variant is the one they exercised)
 thread_local char g_variant[160] = "";
@@ -1165,10 +1220,17 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
     }
   }
   int splits = 1;
+  static const int split_model = getenv("K3M_GEMM_SPLIT_MODEL") ? atoi(getenv("K3M_GEMM_SPLIT_MODEL")) : 1;
   if (accumulate) {
     const int tiles = ((M + BM * ctas - 1) / (BM * ctas)) * ((N + bn - 1) / bn);
     const int resident = num_sms() / ctas;
-    while (tiles * splits * 2 <= resident && total_kb / (splits * 2) >= 4) splits *= 2;
+    if (split_model) {
+      const long bt = tiles;
+      const bool can = true;
+      plan_splits(1, &bt, &total_kb, &can, resident, &splits);
+    } else {
+      while (tiles * splits * 2 <= resident && total_kb / (splits * 2) >= 4) splits *= 2;
+    }
   }
   // epilogue warps: 16 (4 column groups) when the epilogue does real work per element, else 8
   static const int force_ew = getenv("K3M_GEMM_EW") ? atoi(getenv("K3M_GEMM_EW")) : 0;
@@ -1232,7 +1294,14 @@ extern "C" int k3m_gemm_grouped_bf16(const void* descs, int n, void* stream) {
     splits[i] = 1;
     order[i] = i;
   }
-  for (bool grew = true; grew && tiles_total < 3 * resident;) {
+  static const int split_model = getenv("K3M_GEMM_SPLIT_MODEL") ? atoi(getenv("K3M_GEMM_SPLIT_MODEL")) : 1;
+  if (split_model) {
+    int kbv[8];
+    bool can[8];
+    for (int i = 0; i < n; ++i) { kbv[i] = (d[i].K + BK - 1) / BK; can[i] = d[i].accumulate != 0; }
+    plan_splits(n, base_tiles, kbv, can, (int)resident, splits);
+  }
+  for (bool grew = !split_model; grew && tiles_total < 3 * resident;) {
     grew = false;
     for (int i = 0; i < n && tiles_total < 3 * resident; ++i) {
       const int kb = (d[i].K + BK - 1) / BK;
