@@ -52,6 +52,7 @@ struct GemmParams {
                  // garbage): 1 = no TMA loads, 2 = no MMAs.  The product build carries no probe branch: one extra
                  // predicate per MMA in the issuing thread cost 3 % of GEMM throughput (r01j vs r01i).
   int tin;     // epilogue operand that ARRIVES through TMA into the staging buffer: 0 none, 1 aux_in, 2 addend
+  int a3d, b3d;  // MN-major operand described by a 3-D tensor map (see get_map_mn3d): one bulk copy per stage
 };
 
 // One problem of a (possibly grouped) launch, in kernel-parameter space: its five tensor maps, its epilogue
@@ -138,6 +139,16 @@ __device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* m
   asm volatile(
       "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_u32(dst)), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_pair(void* dst, const CUtensorMap* map, uint32_t bar_cluster, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
 // arrives on the barrier at the same shared-memory offset in BOTH CTAs of the pair
 __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
@@ -597,27 +608,43 @@ gemm_kernel(const __grid_constant__ GroupArgs<MAXP> g) {
           if (CTAS == 2) {
             const uint32_t bar = full0 + (uint32_t)s * 8u;
             if (A_MN) {
+              if (p.a3d) {
+                tma_load_3d_pair(a, map_a, bar, 0, k0, m0 >> 6);
+              } else {
 #pragma unroll
-              for (int c = 0; c < BM / 64; ++c) tma_load_2d_pair(a + c * 8192, map_a, bar, m0 + c * 64, k0);
+                for (int c = 0; c < BM / 64; ++c) tma_load_2d_pair(a + c * 8192, map_a, bar, m0 + c * 64, k0);
+              }
             } else {
               tma_load_2d_pair(a, map_a, bar, k0, m0);
             }
             if (B_MN) {
+              if (p.b3d) {
+                tma_load_3d_pair(b, map_b, bar, 0, k0, n0 >> 6);
+              } else {
 #pragma unroll
-              for (int c = 0; c < BNL / 64; ++c) tma_load_2d_pair(b + c * 8192, map_b, bar, n0 + c * 64, k0);
+                for (int c = 0; c < BNL / 64; ++c) tma_load_2d_pair(b + c * 8192, map_b, bar, n0 + c * 64, k0);
+              }
             } else {
               tma_load_2d_pair(b, map_b, bar, k0, n0);
             }
           } else {
             if (A_MN) {
+              if (p.a3d) {
+                tma_load_3d(a, map_a, &full[s], 0, k0, m0 >> 6);
+              } else {
 #pragma unroll
-              for (int c = 0; c < BM / 64; ++c) tma_load_2d(a + c * 8192, map_a, &full[s], m0 + c * 64, k0);
+                for (int c = 0; c < BM / 64; ++c) tma_load_2d(a + c * 8192, map_a, &full[s], m0 + c * 64, k0);
+              }
             } else {
               tma_load_2d(a, map_a, &full[s], k0, m0);
             }
             if (B_MN) {
+              if (p.b3d) {
+                tma_load_3d(b, map_b, &full[s], 0, k0, n0 >> 6);
+              } else {
 #pragma unroll
-              for (int c = 0; c < BN / 64; ++c) tma_load_2d(b + c * 8192, map_b, &full[s], n0 + c * 64, k0);
+                for (int c = 0; c < BN / 64; ++c) tma_load_2d(b + c * 8192, map_b, &full[s], n0 + c * 64, k0);
+              }
             } else {
               tma_load_2d(b, map_b, &full[s], k0, n0);
             }
@@ -924,6 +951,44 @@ bool get_map(const void* ptr, int inner, int outer, int ld, int box_inner, int b
   return true;
 }
 
+// MN-major operand [K, MN] (row stride ld) as a 3-D tensor (mn % 64, k, mn / 64) with strides (1, ld, 64): a box
+// (64, 64, chunks) lands in shared memory exactly like `chunks` separate 64 x 64 boxes 8 KB apart — the layout the
+// MN-major UMMA descriptors expect — but is ONE bulk copy.  The issuing thread manages one bulk copy per ~250 clocks
+// whatever its size (profiles/r01i_l2_fill_bw.txt): the four 8 KB copies per stage of the tn layout took ~1000 clocks
+// against ~820 for the stage's MMAs, which is why weight gradients topped out near 1000 TF/s.  Needs MN % 64 == 0
+// (the columns of the last chunk would otherwise alias the next row); failure falls back to the 2-D boxes.
+typedef std::tuple<const void*, int, int, int, int> Map3Key;
+std::map<Map3Key, CUtensorMap> g_maps3;
+bool get_map_mn3d(const void* ptr, int mn, int k, int ld, int chunks, CUtensorMap* out) {
+  static const int off = getenv("K3M_GEMM_NO_3D") ? atoi(getenv("K3M_GEMM_NO_3D")) : 0;
+  if (off || mn % 64 != 0) return false;
+  Map3Key key(ptr, mn, k, ld, chunks);
+  {
+    std::lock_guard<std::mutex> lk(g_maps_mu);
+    auto it = g_maps3.find(key);
+    if (it != g_maps3.end()) {
+      *out = it->second;
+      return true;
+    }
+  }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return false;
+  cuuint64_t dims[3] = {64, (cuuint64_t)k, (cuuint64_t)(mn / 64)};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, 128};
+  cuuint32_t box[3] = {64, 64, (cuuint32_t)chunks};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return false;
+  std::lock_guard<std::mutex> lk(g_maps_mu);
+  if (g_maps3.size() > 65536) g_maps3.clear();
+  g_maps3[key] = m;
+  *out = m;
+  return true;
+}
+
 int g_sm_limit = 0;      // k3m_gemm_set_sm_limit
 int num_sms() {
   static int n = 0;
@@ -1104,9 +1169,11 @@ int setup_problem(const Desc& d, int bn, int ctas, int ew, int splits, ProblemAr
   const int M = d.M, N = d.N, K = d.K;
   const int total_kb = (K + BK - 1) / BK;
   // A: K-major -> tensor [M, K]; MN-major -> tensor [K, M]
-  if (!(a_mn ? get_map(d.a, M, K, d.lda, 64, 64, &out->map_a) : get_map(d.a, K, M, d.lda, 64, BM, &out->map_a))) return K3M_ERR_CUDA;
-  if (!(b_mn ? get_map(d.b, N, K, d.ldb, 64, 64, &out->map_b) : get_map(d.b, K, N, d.ldb, 64, bn / ctas, &out->map_b))) return K3M_ERR_CUDA;
   GemmParams& p = out->p;
+  p.a3d = a_mn && get_map_mn3d(d.a, M, K, d.lda, BM / 64, &out->map_a);
+  p.b3d = b_mn && bn / ctas >= 64 && get_map_mn3d(d.b, N, K, d.ldb, bn / ctas / 64, &out->map_b);
+  if (!p.a3d && !(a_mn ? get_map(d.a, M, K, d.lda, 64, 64, &out->map_a) : get_map(d.a, K, M, d.lda, 64, BM, &out->map_a))) return K3M_ERR_CUDA;
+  if (!p.b3d && !(b_mn ? get_map(d.b, N, K, d.ldb, 64, 64, &out->map_b) : get_map(d.b, K, N, d.ldb, 64, bn / ctas, &out->map_b))) return K3M_ERR_CUDA;
   p.M = M; p.N = N; p.K = K;
   p.kb_per_split = (total_kb + splits - 1) / splits;
   p.splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
@@ -1254,8 +1321,8 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   g.n = 1;
   if (int rc = setup_problem(d, bn, ctas, ew, splits, &g.prob[0])) return rc;
   const GemmParams& p = g.prob[0].p;
-  snprintf(g_variant, sizeof(g_variant), "bn=%d ctas=%d ew=%d dual=%d splits=%d epi=%s tin=%d tma_out=%d acc=%d group=1",
-           bn, ctas, ew, dual ? 1 : 0, p.splits, fast_name(p.fast), p.tin, p.tma_out, accumulate);
+  snprintf(g_variant, sizeof(g_variant), "bn=%d ctas=%d ew=%d dual=%d splits=%d epi=%s tin=%d tma_out=%d acc=%d group=1 mn3d=%d%d",
+           bn, ctas, ew, dual ? 1 : 0, p.splits, fast_name(p.fast), p.tin, p.tma_out, accumulate, p.a3d, p.b3d);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (layout == 0) return dispatch<false, false>(bn, dual ? 0 : ew, ctas, g, st);
   if (layout == 1) return dispatch<false, true>(bn, dual ? 0 : ew, ctas, g, st);
@@ -1321,9 +1388,9 @@ extern "C" int k3m_gemm_grouped_bf16(const void* descs, int n, void* stream) {
   for (int i = 0; i < n; ++i)
     if (int rc = setup_problem(d[order[i]], bn, ctas, ew, splits[order[i]], &g.prob[i])) return rc;
   for (int i = n; i < 8; ++i) g.prob[i] = g.prob[0];
-  snprintf(g_variant, sizeof(g_variant), "bn=%d ctas=%d ew=%d dual=0 splits=%d epi=%s tin=%d tma_out=%d acc=%d group=%d",
+  snprintf(g_variant, sizeof(g_variant), "bn=%d ctas=%d ew=%d dual=0 splits=%d epi=%s tin=%d tma_out=%d acc=%d group=%d mn3d=%d%d",
            bn, ctas, ew, g.prob[0].p.splits, fast_name(g.prob[0].p.fast), g.prob[0].p.tin, g.prob[0].p.tma_out,
-           d[0].accumulate, n);
+           d[0].accumulate, n, g.prob[0].p.a3d, g.prob[0].p.b3d);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (d[0].layout == 0) return dispatch_group<false, false>(ctas, g, st);
   if (d[0].layout == 1) return dispatch_group<false, true>(ctas, g, st);
