@@ -99,38 +99,83 @@ __device__ __forceinline__ float gumbel_at(const unsigned long long* rng, unsign
 }
 
 // y_k = softmax_k(sigmoid(gate_k) + g_k), hard pick = first arg-max  (pre_sampling_sequence,
-// vilbert_k3m.py:2331-2374; F.gumbel_softmax(hard=True, tau=1))
-__device__ __forceinline__ void ysoft3(const float* gates, const float* noise, const unsigned long long* rng,
-                                       unsigned int site, int m, int h, int H, float ak[3], float y[3], int* pick) {
-  float z[3];
+// vilbert_k3m.py:2331-2374; F.gumbel_softmax(hard=True, tau=1)).
+// Four consecutive channels per thread: the Gumbel draws of elements lin .. lin + 3 (lin % 4 == 0) are the four words
+// of ONE Philox call, which the one-channel-per-thread form recomputed in each of its four threads — the generator was
+// two thirds of these ALU-bound kernels' instructions.  Same counters, same words, same arithmetic per element.
+__device__ __forceinline__ void ysoft3x4(const float* gates, const float* noise, const unsigned long long* rng,
+                                         unsigned int site, int m, int h, int H, float ak[3][4], float y[3][4], int pick[4]) {
+  float z[3][4];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    ak[k] = sigmoid_f(gates[(size_t)m * 3 * H + k * H + h]);
-    const size_t lin = ((size_t)m * 3 + k) * H + h;
-    const float g = noise ? noise[lin] : gumbel_at(rng, site, lin);
-    z[k] = ak[k] + g;
+    const size_t lin = ((size_t)m * 3 + k) * H + h;            // % 4 == 0 (H % 4 == 0, h % 4 == 0)
+    const float4 gt = *reinterpret_cast<const float4*>(gates + lin);
+    const float gk[4] = {gt.x, gt.y, gt.z, gt.w};
+    float g[4];
+    if (noise) {
+      const float4 nz = *reinterpret_cast<const float4*>(noise + lin);
+      g[0] = nz.x; g[1] = nz.y; g[2] = nz.z; g[3] = nz.w;
+    } else {
+      uint32_t w[4];
+      rng_words(rng, site, lin >> 2, w);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float u = ((float)(w[j] >> 9) + 0.5f) * (1.0f / 8388608.0f);     // == gumbel_at(rng, site, lin + j)
+        g[j] = -logf(-logf(u));
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      ak[k][j] = sigmoid_f(gk[j]);
+      z[k][j] = ak[k][j] + g[j];
+    }
   }
-  const float mx = fmaxf(z[0], fmaxf(z[1], z[2]));
-  float e[3], s = 0.f;
 #pragma unroll
-  for (int k = 0; k < 3; ++k) { e[k] = __expf(z[k] - mx); s += e[k]; }
+  for (int j = 0; j < 4; ++j) {
+    const float mx = fmaxf(z[0][j], fmaxf(z[1][j], z[2][j]));
+    float e[3], sum = 0.f;
 #pragma unroll
-  for (int k = 0; k < 3; ++k) y[k] = e[k] / s;
-  int p = 0;
-  if (y[1] > y[p]) p = 1;
-  if (y[2] > y[p]) p = 2;
-  *pick = p;
+    for (int k = 0; k < 3; ++k) { e[k] = __expf(z[k][j] - mx); sum += e[k]; }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) y[k][j] = e[k] / sum;
+    int p = 0;
+    if (y[1][j] > y[p][j]) p = 1;
+    if (y[2][j] > y[p][j]) p = 2;
+    pick[j] = p;
+  }
 }
+__device__ __forceinline__ void ld4(const bf16* p, float v[4]) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+  const float2 a = __bfloat1622float2(h[0]), b = __bfloat1622float2(h[1]);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+__device__ __forceinline__ void st4(bf16* p, const float v[4]) {
+  uint2 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+  h[0] = __floats2bfloat162_rn(v[0], v[1]);
+  h[1] = __floats2bfloat162_rn(v[2], v[3]);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+__device__ __forceinline__ void ld4(const float* p, float v[4]) {
+  const float4 u = *reinterpret_cast<const float4*>(p);
+  v[0] = u.x; v[1] = u.y; v[2] = u.z; v[3] = u.w;
+}
+__device__ __forceinline__ void st4(float* p, const float v[4]) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
 
 __global__ void fuse_fwd_kernel(const act_t* __restrict__ cat, const float* __restrict__ gates, const float* __restrict__ noise,
                                 const unsigned long long* rng, unsigned int site, act_t* __restrict__ out, int ldo, int M, int H) {
-  const unsigned n = (unsigned)(M * H);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
+  const unsigned H4 = (unsigned)(H >> 2), n = (unsigned)M * H4;   // 32-bit index math (64-bit div / mod dominated these kernels)
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const int m = (int)(i / H), h = (int)(i % H);
-    float ak[3], y[3];
-    int pick;
-    ysoft3(gates, noise, rng, site, m, h, H, ak, y, &pick);
-    out[(size_t)m * ldo + h] = cat[(size_t)m * 3 * H + pick * H + h];
+    const int m = (int)(i / H4), h = (int)(i % H4) * 4;
+    float ak[3][4], y[3][4], c[3][4], o[4];
+    int pick[4];
+    ysoft3x4(gates, noise, rng, site, m, h, H, ak, y, pick);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) ld4(cat + (size_t)m * 3 * H + k * H + h, c[k]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = pick[j] == 0 ? c[0][j] : (pick[j] == 1 ? c[1][j] : c[2][j]);
+    st4(out + (size_t)m * ldo + h, o);
   }
 }
 
@@ -139,24 +184,35 @@ __global__ void fuse_bwd_kernel(const act_t* __restrict__ dout, int ldd, const a
                                 const float* __restrict__ gates, const float* __restrict__ noise,
                                 const unsigned long long* rng, unsigned int site, act_t* __restrict__ dgates,
                                 act_t* __restrict__ dcat, int M, int H) {
-  const unsigned n = (unsigned)(M * H);   // B * L rows: far below 2^31 elements; 32-bit index math (64-bit div / mod dominated these kernels)
+  const unsigned H4 = (unsigned)(H >> 2), n = (unsigned)M * H4;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const int m = (int)(i / H), h = (int)(i % H);
-    float ak[3], y[3];
-    int pick;
-    ysoft3(gates, noise, rng, site, m, h, H, ak, y, &pick);
-    const float go = to_f(dout[(size_t)m * ldd + h]);
-    float dy[3], dot = 0.f;
+    const int m = (int)(i / H4), h = (int)(i % H4) * 4;
+    float ak[3][4], y[3][4], go[4], c[3][4];
+    int pick[4];
+    ysoft3x4(gates, noise, rng, site, m, h, H, ak, y, pick);
+    ld4(dout + (size_t)m * ldd + h, go);
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      dy[k] = go * to_f(cat[(size_t)m * 3 * H + k * H + h]);
-      dot += y[k] * dy[k];
+    for (int k = 0; k < 3; ++k) ld4(cat + (size_t)m * 3 * H + k * H + h, c[k]);
+    float dg[3][4], dc[3][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float dy[3], dot = 0.f;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        dy[k] = go[j] * c[k][j];
+        dot += y[k][j] * dy[k];
+      }
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        dg[k][j] = y[k][j] * (dy[k] - dot) * ak[k][j] * (1.0f - ak[k][j]);
+        dc[k][j] = k == pick[j] ? go[j] : 0.f;
+      }
     }
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       const size_t o = (size_t)m * 3 * H + k * H + h;
-      dgates[o] = act_from(y[k] * (dy[k] - dot) * ak[k] * (1.0f - ak[k]));
-      dcat[o] = act_from(k == pick ? go : 0.f);
+      st4(dgates + o, dg[k]);
+      st4(dcat + o, dc[k]);
     }
   }
 }
@@ -312,7 +368,8 @@ extern "C" int k3m_relu_cat3(const void* a, int lda, const void* b, int ldb, con
 extern "C" int k3m_fuse_select_fwd(const void* cat, const float* gates, const float* noise, const void* rng,
                                    unsigned int site, void* out, int ldo, int M, int H, void* stream) {
   K3M_REQUIRE(noise || rng, "fuse_select: need either a noise tensor or the RNG state");
-  fuse_fwd_kernel<<<grid_for((size_t)M * H, 256), 256, 0, ST(stream)>>>((const act_t*)cat, gates, noise,
+  K3M_REQUIRE(H % 4 == 0 && ldo % 4 == 0, "fuse_select: H and the output row stride must be multiples of 4 (H=%d ldo=%d)", H, ldo);
+  fuse_fwd_kernel<<<grid_for((size_t)M * H / 4, 256), 256, 0, ST(stream)>>>((const act_t*)cat, gates, noise,
                                                                         (const unsigned long long*)rng, site, (act_t*)out, ldo, M, H);
   return k3m_check_launch("k3m_fuse_select_fwd");
 }
@@ -320,7 +377,8 @@ extern "C" int k3m_fuse_select_fwd(const void* cat, const float* gates, const fl
 extern "C" int k3m_fuse_select_bwd(const void* dout, int ldd, const void* cat, const float* gates, const float* noise,
                                    const void* rng, unsigned int site, void* dgates, void* dcat, int M, int H, void* stream) {
   K3M_REQUIRE(noise || rng, "fuse_select: need either a noise tensor or the RNG state");
-  fuse_bwd_kernel<<<grid_for((size_t)M * H, 256), 256, 0, ST(stream)>>>(
+  K3M_REQUIRE(H % 4 == 0 && ldd % 4 == 0, "fuse_select: H and the gradient row stride must be multiples of 4 (H=%d ldd=%d)", H, ldd);
+  fuse_bwd_kernel<<<grid_for((size_t)M * H / 4, 256), 256, 0, ST(stream)>>>(
       (const act_t*)dout, ldd, (const act_t*)cat, gates, noise, (const unsigned long long*)rng, site, (act_t*)dgates, (act_t*)dcat, M, H);
   return k3m_check_launch("k3m_fuse_select_bwd");
 }

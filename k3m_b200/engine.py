@@ -68,6 +68,7 @@ class Engine(object):
         # the GPU behind its own last wave).  None = not collecting (every caller outside those two blocks).
         self._pend_w = self._pend_b = None
         self.defer_grads = os.environ.get("K3M_DEFER_GRADS", "1") != "0"
+        self.ready_per_layer = os.environ.get("K3M_READY_PER_LAYER", "0") != "0"
         # per-layer parity taps (tests only; never set inside a captured step): when a dict, `tower_fwd` stores the
         # output of every BertLayer / BertImageLayer / BertConnectionLayer application under the key the reference's
         # module call would have: "<module name>#<call index>[/<output index>]" (tools/make_golden.py install_taps)
@@ -833,6 +834,12 @@ class Engine(object):
                         j += 1
                     if k < len(vsv):
                         box["dY"] = res[j]
+                    if self.ready_per_layer and not (tsv and vsv):
+                        # (single-stack stage only: the arena lists a stage's text layers before its image layers,
+                        # so in a lock-step stage "text layer k done" says nothing about image layers < k.)  The
+                        # layer's weight gradients were launched a moment ago: an optimizer bucket that they
+                        # complete reads them while they still sit in the L2
+                        ready([sv_[k][0] for sv_ in (tsv, vsv) if k < len(sv_)])
                 ready([s_[0] for s_ in tsv] + [s_[0] for s_ in vsv])
             else:
                 dX, dY = box["dX"], box["dY"]
