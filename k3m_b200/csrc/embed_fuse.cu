@@ -230,6 +230,27 @@ __global__ void relu_split3_kernel(const act_t* __restrict__ dcat, const act_t* 
   }
 }
 
+// eight channels per thread (16-byte accesses); same arithmetic per element as the scalar form above
+__global__ void relu_split3_vec_kernel(const act_t* __restrict__ dcat, const act_t* __restrict__ cat, act_t* da, int lda,
+                                       act_t* db, int ldb, act_t* dc, int ldc, int M, int H) {
+  const unsigned hv = (unsigned)(H >> 3), n = (unsigned)M * 3 * hv;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int m = (int)(i / (3 * hv)), r = (int)(i % (3 * hv)), k = r / (int)hv, h = (r % (int)hv) * 8;
+    float c[8], d[8], o[8];
+    ld8(cat + (size_t)i * 8, c);
+    ld8(dcat + (size_t)i * 8, d);
+    act_t* dst = k == 0 ? da + (size_t)m * lda + h : (k == 1 ? db + (size_t)m * ldb + h : dc + (size_t)m * ldc + h);
+    ld8(dst, o);
+    bool any = false;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      // the scalar form leaves dst untouched where cat <= 0 and re-rounds (dst + dcat) elsewhere
+      if (c[j] > 0.f) { o[j] = to_f(act_from(o[j] + d[j])); any = true; }
+    }
+    if (any) st8(dst, o);
+  }
+}
+
 // pooled[b, h] = mean_{i=1..L-1} seq[b*L + i, h]       (vilbert_k3m.py:2405-2409)
 template <typename TO>
 __global__ void pool_fwd_kernel(const act_t* __restrict__ seq, int ld, TO* __restrict__ out, int B, int L, int H) {
@@ -413,6 +434,12 @@ extern "C" int k3m_gate_bwd(const void* dgated, const void* cat, const void* alp
 
 extern "C" int k3m_relu_bwd_split3(const void* dcat, const void* cat, void* da, int lda, void* db, int ldb, void* dc,
                                    int ldc, int M, int H, void* stream) {
+  auto al = [](const void* q) { return (((uintptr_t)q) & 15) == 0; };
+  if (H % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0 && al(dcat) && al(cat) && al(da) && al(db) && al(dc)) {
+    relu_split3_vec_kernel<<<grid_for((size_t)M * 3 * H / 8, 256), 256, 0, ST(stream)>>>(
+        (const act_t*)dcat, (const act_t*)cat, (act_t*)da, lda, (act_t*)db, ldb, (act_t*)dc, ldc, M, H);
+    return k3m_check_launch("k3m_relu_bwd_split3");
+  }
   relu_split3_kernel<<<grid_for((size_t)M * 3 * H, 256), 256, 0, ST(stream)>>>((const act_t*)dcat, (const act_t*)cat, (act_t*)da,
                                                                                lda, (act_t*)db, ldb, (act_t*)dc, ldc, M, H);
   return k3m_check_launch("k3m_relu_bwd_split3");
