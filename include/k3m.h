@@ -33,6 +33,8 @@ extern "C" {
 #define K3M_ACT_SIGMOID 3
 #define K3M_ACT_TANH 4
 #define K3M_ACT_DTANH 5   /* out = v * (1 - aux_in^2)                                        */
+#define K3M_ACT_GELU_GRAD 6 /* out = gelu(v), aux_out = gelu'(v): BertIntermediate forward storing what its backward multiplies by */
+#define K3M_ACT_MULAUX 7  /* out = v * aux_in (backward of K3M_ACT_GELU_GRAD)                   */
 
 /* GEMM operand layouts */
 #define K3M_GEMM_NT 0 /* A[M,K] , B[N,K]  : Y = X W^T    (nn.Linear forward)                   */

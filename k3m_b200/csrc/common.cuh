@@ -34,7 +34,9 @@ int k3m_check_launch(const char* what);
   } while (0)
 
 // ---- activation codes (same values in include/k3m.h and the Python op table) --------------------
-enum { ACT_NONE = 0, ACT_GELU = 1, ACT_DGELU = 2, ACT_SIGMOID = 3, ACT_TANH = 4, ACT_DTANH = 5 };
+enum { ACT_NONE = 0, ACT_GELU = 1, ACT_DGELU = 2, ACT_SIGMOID = 3, ACT_TANH = 4, ACT_DTANH = 5,
+       ACT_GELU_GRAD = 6,   // out = gelu(v), aux_out = gelu'(v): the derivative is computed where Phi(v) already is
+       ACT_MULAUX = 7 };    // out = v * aux_in (the backward of ACT_GELU_GRAD: a plain multiply)
 
 // ---- dropout / RNG ------------------------------------------------------------------------------
 // rng points to two device uint64: {seed, step}; site identifies the dropout application inside

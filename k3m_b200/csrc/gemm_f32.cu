@@ -86,6 +86,11 @@ __global__ void __launch_bounds__(256) gemm_f32_kernel(F32Gemm g) {
       if (g.act == ACT_GELU) {
         if (g.aux_out) g.aux_out[(size_t)row * g.ld_aux_out + col] = v;
         v = gelu_exact(v);
+      } else if (g.act == ACT_GELU_GRAD) {
+        if (g.aux_out) g.aux_out[(size_t)row * g.ld_aux_out + col] = dgelu_exact(v);
+        v = gelu_exact(v);
+      } else if (g.act == ACT_MULAUX) {
+        v *= g.aux_in[(size_t)row * g.ld_aux_in + col];
       } else if (g.act == ACT_DGELU) {
         v *= dgelu_exact(g.aux_in[(size_t)row * g.ld_aux_in + col]);
       } else if (g.act == ACT_DTANH) {
@@ -114,7 +119,7 @@ struct Desc {      // == K3MGemmDesc of include/k3m.h
 int run(const Desc& d, cudaStream_t st) {
   K3M_REQUIRE(d.M > 0 && d.N > 0 && d.K > 0, "gemm: empty problem M=%d N=%d K=%d", d.M, d.N, d.K);
   K3M_REQUIRE(d.layout >= 0 && d.layout <= 2, "gemm: layout must be 0 (nt), 1 (nn) or 2 (tn)");
-  K3M_REQUIRE(!(d.act == ACT_DGELU || d.act == ACT_DTANH) || d.aux_in, "gemm: activation-derivative epilogue needs aux_in");
+  K3M_REQUIRE(!(d.act == ACT_DGELU || d.act == ACT_DTANH || d.act == ACT_MULAUX) || d.aux_in, "gemm: activation-derivative epilogue needs aux_in");
   F32Gemm g;
   g.a = (const float*)d.a; g.b = (const float*)d.b; g.lda = d.lda; g.ldb = d.ldb; g.layout = d.layout;
   g.M = d.M; g.N = d.N; g.K = d.K;

@@ -221,7 +221,10 @@ __device__ __forceinline__ void compute_group(const GemmParams& p, const uint32_
   if (p.act == ACT_GELU) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) { pre[j] = v[j]; v[j] = gelu_f(v[j]); }
-  } else if (p.act == ACT_DGELU || p.act == ACT_DTANH) {
+  } else if (p.act == ACT_GELU_GRAD) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { pre[j] = dgelu_f(v[j]); v[j] = gelu_f(v[j]); }
+  } else if (p.act == ACT_DGELU || p.act == ACT_DTANH || p.act == ACT_MULAUX) {
     float t[8];
     if (tin == 1) {
 #pragma unroll
@@ -232,7 +235,7 @@ __device__ __forceinline__ void compute_group(const GemmParams& p, const uint32_
       else for (int j = 0; j < 8; ++j) t[j] = j < nv ? ld_f(ai + j) : 0.f;
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] *= (p.act == ACT_DGELU) ? dgelu_f(t[j]) : (1.0f - t[j] * t[j]);
+    for (int j = 0; j < 8; ++j) v[j] *= (p.act == ACT_DGELU) ? dgelu_f(t[j]) : (p.act == ACT_MULAUX ? t[j] : (1.0f - t[j] * t[j]));
   } else if (p.act == ACT_SIGMOID) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) v[j] = sigmoid_f(v[j]);
@@ -269,7 +272,7 @@ __device__ __forceinline__ void compute_group(const GemmParams& p, const uint32_
 // direct (row-per-thread) stores: fallback when the output cannot be described by a TMA tensor map
 __device__ __forceinline__ void store_group_direct(const GemmParams& p, int row, int col, int nv, bool vec,
                                                    const float v[8], const float pre[8]) {
-  if (p.act == ACT_GELU && p.aux_out) {
+  if ((p.act == ACT_GELU || p.act == ACT_GELU_GRAD) && p.aux_out) {
     bf16* ao = p.aux_out + (size_t)row * p.ld_aux_out + col;
     if (vec) st8(ao, pre);
     else for (int j = 0; j < nv; ++j) st_f(ao + j, pre[j]);
@@ -393,33 +396,45 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
     __syncwarp();
   }
   if (MODE == F_GELU && NBUF == 1) {
-    // one staging buffer, two outputs: two passes over the accumulator (TMEM reads are cheap) — the
-    // pre-activation leaves first, then the activation through the same buffer
+    // One 4 KB staging buffer, two outputs: the buffer is two 2 KB halves (32 rows x 32 columns, SWIZZLE_64B boxes) —
+    // half 0 takes the saved operand of a 32-column slab (pre-activation, or gelu' for ACT_GELU_GRAD), half 1 the
+    // activation; each slab reads its accumulator columns ONCE and evaluates Phi once for both outputs.  (The earlier
+    // form swept the accumulator twice through the whole buffer: two TMEM reads and two bias adds per element.)
+    const bool grad = p.act == ACT_GELU_GRAD;
 #pragma unroll
-    for (int pass = 0; pass < 2; ++pass) {
+    for (int cc = 0; cc < CW; cc += 32) {
+      if (n0 + cc >= p.N) break;
+      uint32_t r[32];
+      tmem_ld32(tbase + (uint32_t)cc, r);
+      if (cc > 0) {                      // the stores of the previous slab must have read both halves
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+      }
 #pragma unroll
-      for (int cc = 0; cc < CW; cc += 32) {
-        uint4 braw[4];
-        load_bias32(p, n0 + cc, braw);
-        uint32_t r[32];
-        tmem_ld32(tbase + (uint32_t)cc, r);
+      for (int g = 0; g < 4; ++g) {
+        // (bias per group here, not per slab: this path is the register-hungriest of the kernel and 18 warps cap a
+        // thread at 96 registers; the compiler is free to hoist the loads — sts16 carries no memory clobber)
+        const int col = n0 + cc + g * 8;
+        const uint4 braw = (p.bias != nullptr && col < p.N) ? __ldg(reinterpret_cast<const uint4*>(p.bias + col)) : make_uint4(0u, 0u, 0u, 0u);
+        float v[8], a[8];
+        acc_bias(r + g * 8, braw, v);
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          float v[8];
-          acc_bias(r + g * 8, braw[g], v);
-          if (pass == 1) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
-          }
-          sts16(sbuf + swz((uint32_t)lane * RB + (uint32_t)((cc + g * 8) * 2), SM), pack_bf16x8(v));
+        for (int j = 0; j < 8; ++j) {
+          float e;
+          const float c = gauss_cdf(v[j], e);
+          a[j] = grad ? fmaf(v[j] * e, 0.3989422804014327f, c) : v[j];
+          v[j] *= c;
         }
+        const uint32_t off = swz((uint32_t)lane * 64u + (uint32_t)(g * 16), 3u);
+        sts16(sbuf + off, pack_bf16x8(a));
+        sts16(sbuf + 2048u + off, pack_bf16x8(v));
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
       if (lane == 0) {
-        tma_store_2d(pass == 0 ? mx : mc, buf, n0, row0);
+        tma_store_2d(mx, buf, n0 + cc, row0);
+        tma_store_2d(mc, buf + 2048, n0 + cc, row0);
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        if (pass == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
       }
       __syncwarp();
     }
@@ -443,15 +458,27 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
       float v[8];
       acc_bias(r + g * 8, braw[g], v);
       if (MODE == F_GELU) {
-        sts16(sabuf + off, pack_bf16x8(v));
+        if (p.act == ACT_GELU_GRAD) {
+          float a[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
+          for (int j = 0; j < 8; ++j) { a[j] = dgelu_f(v[j]); v[j] = gelu_f(v[j]); }
+          sts16(sabuf + off, pack_bf16x8(a));
+        } else {
+          sts16(sabuf + off, pack_bf16x8(v));
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
+        }
       }
       if (MODE == F_DGELU) {
         float t[8];
         unpack_bf16x8(lds16(sbuf + off), t);
+        if (p.act == ACT_MULAUX) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] *= dgelu_f(t[j]);
+          for (int j = 0; j < 8; ++j) v[j] *= t[j];
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] *= dgelu_f(t[j]);
+        }
       }
       if (MODE != F_GELU && MODE != F_DGELU && has_drop) {
         uint32_t w[4];
@@ -726,7 +753,7 @@ gemm_kernel(const __grid_constant__ GroupArgs<MAXP> g) {
         const ProblemArgs& pr = g.prob[i];
         if (!pr.p.tma_out) continue;
         asm volatile("prefetch.tensormap [%0];" ::"l"(&pr.map_c) : "memory");
-        if (pr.p.act == ACT_GELU && pr.p.aux_out != nullptr) asm volatile("prefetch.tensormap [%0];" ::"l"(&pr.map_aux) : "memory");
+        if ((pr.p.act == ACT_GELU || pr.p.act == ACT_GELU_GRAD) && pr.p.aux_out != nullptr) asm volatile("prefetch.tensormap [%0];" ::"l"(&pr.map_aux) : "memory");
         if (pr.p.tin) asm volatile("prefetch.tensormap [%0];" ::"l"(&pr.map_in) : "memory");
       }
     }
@@ -760,7 +787,7 @@ gemm_kernel(const __grid_constant__ GroupArgs<MAXP> g) {
       const CUtensorMap* map_c = &pr.map_c;
       const CUtensorMap* map_aux = &pr.map_aux;
       const bool has_drop = p.drop.thresh != 0;
-      const bool want_aux = p.act == ACT_GELU && p.aux_out != nullptr;
+      const bool want_aux = (p.act == ACT_GELU || p.act == ACT_GELU_GRAD) && p.aux_out != nullptr;
       const int esz = p.out_f32 ? 4 : 2;
       const int chunk_cols = (CW * esz > 128) ? 128 / esz : CW;      // columns per staged box (<= 128 B per row)
       const uint32_t row_bytes = (uint32_t)(chunk_cols * esz);
@@ -1158,13 +1185,15 @@ int check_desc(const Desc& d) {
   K3M_REQUIRE(d.lda % 8 == 0 && d.ldb % 8 == 0, "gemm: operand row strides must be multiples of 8 elements (lda=%d ldb=%d)", d.lda, d.ldb);
   K3M_REQUIRE(((uintptr_t)d.a & 15) == 0 && ((uintptr_t)d.b & 15) == 0, "gemm: operands must be 16-byte aligned");
   K3M_REQUIRE(!d.accumulate || d.out_f32, "gemm: accumulate needs an fp32 output");
-  K3M_REQUIRE(!(d.act == ACT_DGELU || d.act == ACT_DTANH) || d.aux_in, "gemm: activation-derivative epilogue needs aux_in");
+  K3M_REQUIRE(!(d.act == ACT_DGELU || d.act == ACT_DTANH || d.act == ACT_MULAUX) || d.aux_in, "gemm: activation-derivative epilogue needs aux_in");
+  K3M_REQUIRE(d.act >= ACT_NONE && d.act <= ACT_MULAUX, "gemm: unknown activation code %d", d.act);
   return K3M_OK;
 }
 
-// Fills one problem of a launch for the chosen variant (bn, ctas, ew) and K split: operand / output / epilogue
+// Fills one problem of a launch for the chosen variant (bn, ctas, ew; nbuf = staging buffers per epilogue warp of
+// that kernel instantiation) and K split: operand / output / epilogue
 // tensor maps, epilogue mode.  `dual`: the 2-stage two-CTAs-per-SM variant (ew = 2 there).
-int setup_problem(const Desc& d, int bn, int ctas, int ew, int splits, ProblemArgs* out) {
+int setup_problem(const Desc& d, int bn, int ctas, int ew, int nbuf, int splits, ProblemArgs* out) {
   const bool a_mn = d.layout == 2, b_mn = d.layout != 0;
   const int M = d.M, N = d.N, K = d.K;
   const int total_kb = (K + BK - 1) / BK;
@@ -1199,7 +1228,7 @@ int setup_problem(const Desc& d, int bn, int ctas, int ew, int splits, ProblemAr
   const int esz = d.out_f32 ? 4 : 2;
   auto tma_able = [](const void* q, long pitch_bytes) { return q != nullptr && (((uintptr_t)q) & 15) == 0 && pitch_bytes % 16 == 0; };
   static const int no_tma_store = getenv("K3M_GEMM_NO_TMA_STORE") ? atoi(getenv("K3M_GEMM_NO_TMA_STORE")) : 0;
-  const bool want_aux = d.act == ACT_GELU && d.aux_out != nullptr;
+  const bool want_aux = (d.act == ACT_GELU || d.act == ACT_GELU_GRAD) && d.aux_out != nullptr;
   p.tma_out = !no_tma_store && tma_able(d.out, (long)d.ldc * esz) && (!want_aux || (!d.out_f32 && tma_able(d.aux_out, (long)d.ld_aux_out * 2)));
   const int cw = bn / ew;
   p.tin = 0;
@@ -1212,7 +1241,7 @@ int setup_problem(const Desc& d, int bn, int ctas, int ew, int splits, ProblemAr
     if (!no_tma_in && !d.out_f32 && !want_aux) {
       const void* src = nullptr;
       int ld_src = 0;
-      if ((d.act == ACT_DGELU || d.act == ACT_DTANH) && tma_able(d.aux_in, (long)d.ld_aux_in * 2)) {
+      if ((d.act == ACT_DGELU || d.act == ACT_DTANH || d.act == ACT_MULAUX) && tma_able(d.aux_in, (long)d.ld_aux_in * 2)) {
         p.tin = 1; src = d.aux_in; ld_src = d.ld_aux_in;
       } else if (d.addend != nullptr && !d.addend_f32 && tma_able(d.addend, (long)d.ld_add * 2)) {
         p.tin = 2; src = d.addend; ld_src = d.ld_add;
@@ -1229,11 +1258,17 @@ int setup_problem(const Desc& d, int bn, int ctas, int ew, int splits, ProblemAr
     if (d.act == ACT_NONE && d.aux_out == nullptr) {
       if (d.addend == nullptr) p.fast = F_PLAIN;
       else if (p.tin == 2) p.fast = F_ADD;
-    } else if (d.act == ACT_GELU && want_aux && d.addend == nullptr && !has_drop) {
+    } else if ((d.act == ACT_GELU || d.act == ACT_GELU_GRAD) && want_aux && d.addend == nullptr && !has_drop) {
       p.fast = F_GELU;
-    } else if (d.act == ACT_DGELU && p.tin == 1 && d.addend == nullptr && d.bias == nullptr && !has_drop) {
+    } else if ((d.act == ACT_DGELU || d.act == ACT_MULAUX) && p.tin == 1 && d.addend == nullptr && d.bias == nullptr && !has_drop) {
       p.fast = F_DGELU;
     }
+  }
+  // F_GELU with ONE staging buffer per epilogue warp stores 32-column slabs from the two halves of that buffer
+  // (fast_tile): output and saved-operand maps with 32 x 32 boxes (64-byte rows, SWIZZLE_64B)
+  if (p.fast == F_GELU && nbuf == 1 && cw == 64) {
+    if (!get_map(d.out, N, M, d.ldc, 32, 32, &out->map_c, 2)) return K3M_ERR_CUDA;
+    if (!get_map(d.aux_out, N, M, d.ld_aux_out, 32, 32, &out->map_aux, 2)) return K3M_ERR_CUDA;
   }
   return K3M_OK;
 }
@@ -1319,7 +1354,7 @@ extern "C" int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int
   if (dual) ew = 2;
   GroupArgs<1> g;
   g.n = 1;
-  if (int rc = setup_problem(d, bn, ctas, ew, splits, &g.prob[0])) return rc;
+  if (int rc = setup_problem(d, bn, ctas, ew, (ew <= 2 && !dual) ? 2 : 1, splits, &g.prob[0])) return rc;
   const GemmParams& p = g.prob[0].p;
   snprintf(g_variant, sizeof(g_variant), "bn=%d ctas=%d ew=%d dual=%d splits=%d epi=%s tin=%d tma_out=%d acc=%d group=1 mn3d=%d%d",
            bn, ctas, ew, dual ? 1 : 0, p.splits, fast_name(p.fast), p.tin, p.tma_out, accumulate, p.a3d, p.b3d);
@@ -1386,7 +1421,7 @@ extern "C" int k3m_gemm_grouped_bf16(const void* descs, int n, void* stream) {
   GroupArgs<8> g;
   g.n = n;
   for (int i = 0; i < n; ++i)
-    if (int rc = setup_problem(d[order[i]], bn, ctas, ew, splits[order[i]], &g.prob[i])) return rc;
+    if (int rc = setup_problem(d[order[i]], bn, ctas, ew, 1, splits[order[i]], &g.prob[i])) return rc;
   for (int i = n; i < 8; ++i) g.prob[i] = g.prob[0];
   snprintf(g_variant, sizeof(g_variant), "bn=%d ctas=%d ew=%d dual=0 splits=%d epi=%s tin=%d tma_out=%d acc=%d group=%d mn3d=%d%d",
            bn, ctas, ew, g.prob[0].p.splits, fast_name(g.prob[0].p.fast), g.prob[0].p.tin, g.prob[0].p.tma_out,

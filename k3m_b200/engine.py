@@ -24,7 +24,7 @@ import torch
 
 from .struct_plan import build_struct_plan
 
-ACT_NONE, ACT_GELU, ACT_DGELU, ACT_SIGMOID, ACT_TANH, ACT_DTANH = 0, 1, 2, 3, 4, 5
+ACT_NONE, ACT_GELU, ACT_DGELU, ACT_SIGMOID, ACT_TANH, ACT_DTANH, ACT_GELU_GRAD, ACT_MULAUX = 0, 1, 2, 3, 4, 5, 6, 7
 
 
 class _Seg(object):
@@ -69,6 +69,14 @@ class Engine(object):
         self._pend_w = self._pend_b = None
         self.defer_grads = os.environ.get("K3M_DEFER_GRADS", "1") != "0"
         self.ready_per_layer = os.environ.get("K3M_READY_PER_LAYER", "0") != "0"
+        # BertIntermediate (`:515-518`): the forward epilogue stores gelu'(pre) instead of the pre-activation — Phi(pre) is
+        # already in registers there, the derivative costs three more instructions — and the backward epilogue of the
+        # FFN-down dgrad is a plain multiply instead of ~18 instructions per element of erf arithmetic in the K = 768
+        # GEMMs whose tile time IS the epilogue (K3M_GELU_GRAD=0: pre-activation + ACT_DGELU as before)
+        if os.environ.get("K3M_GELU_GRAD", "1") != "0":
+            self.act_ffn_fwd, self.act_ffn_bwd = ACT_GELU_GRAD, ACT_MULAUX
+        else:
+            self.act_ffn_fwd, self.act_ffn_bwd = ACT_GELU, ACT_DGELU
         # per-layer parity taps (tests only; never set inside a captured step): when a dict, `tower_fwd` stores the
         # output of every BertLayer / BertImageLayer / BertConnectionLayer application under the key the reference's
         # module call would have: "<module name>#<call index>[/<output index>]" (tools/make_golden.py install_taps)
@@ -227,7 +235,7 @@ class Engine(object):
         ops = self.ops
         pres = [self.empty(a.shape[0], self.W(pi + ".dense.weight").shape[0]) for a, pi, _, _, _ in items]
         hs = self.gemms([dict(a=a, b=self.W(pi + ".dense.weight"), layout="nt", bias=self.W(pi + ".dense.bias"),
-                              act=ACT_GELU, aux_out=pre) for (a, pi, _, _, _), pre in zip(items, pres)])
+                              act=self.act_ffn_fwd, aux_out=pre) for (a, pi, _, _, _), pre in zip(items, pres)])
         sites = [self.site(it[3]) for it in items]
         zs = self.gemms([dict(a=h, b=self.W(po + ".dense.weight"), layout="nt", bias=self.W(po + ".dense.bias"),
                               drop=s, rng=self.rng, addend=a) for (a, _, po, _, _), h, s in zip(items, hs, sites)])
@@ -244,7 +252,7 @@ class Engine(object):
                             for dy, (a, pre, h, z, mean, rstd, s, pi, po) in items])
         self.wgrads([(lns[i][1], it[1][2], it[1][8] + ".dense.weight") for i, it in enumerate(items)])
         dpres = self.gemms([dict(a=lns[i][1], b=self.W(it[1][8] + ".dense.weight"), layout="nn", rng=self.rng,
-                                 act=ACT_DGELU, aux_in=it[1][1]) for i, it in enumerate(items)])
+                                 act=self.act_ffn_bwd, aux_in=it[1][1]) for i, it in enumerate(items)])
         self.bgrads([(dpres[i], it[1][7] + ".dense.bias") for i, it in enumerate(items)])
         self.wgrads([(dpres[i], it[1][0], it[1][7] + ".dense.weight") for i, it in enumerate(items)])
         return self.gemms([dict(a=dpres[i], b=self.W(it[1][7] + ".dense.weight"), layout="nn", rng=self.rng,
@@ -525,7 +533,15 @@ class Engine(object):
         dl = dlogits[:, :n_cols]
         self.bgrad(dl, p_dec_b)
         self.wgrad(dl, hn, p_dec_w)
-        dhn = self.dgrad(dl, p_dec_w)
+        if n_cols >= 8192:
+            # vocabulary decoder: [rows, 21128] x [21128, H] has 331 k-blocks but only 21 output tiles (labelled rows
+            # x H) — a bf16 output cannot be split along k, so it ran on 21 of 74 CTA pairs (170 us, 317 TF/s).
+            # Accumulating into a zeroed fp32 buffer lets the split-K planner fill the machine; one rounding at the end.
+            acc = self.zeros(dl.shape[0], self.W(p_dec_w).shape[1], torch.float32)
+            ops.gemm(dl, self.W(p_dec_w), "nn", out=acc, accumulate=True)
+            dhn = acc if self.adt == torch.float32 else ops.cast(acc, self.adt)
+        else:
+            dhn = self.dgrad(dl, p_dec_w)
         dh, _ = ops.ln_bwd(dhn, h, self.W(p + ".transform.LayerNorm.weight"), mean, rstd,
                            self.G(p + ".transform.LayerNorm.weight"),
                            self.G(p + ".transform.LayerNorm.bias"))

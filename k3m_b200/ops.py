@@ -7,7 +7,7 @@ import torch
 
 from . import _lib
 
-ACT_NONE, ACT_GELU, ACT_DGELU, ACT_SIGMOID, ACT_TANH, ACT_DTANH = 0, 1, 2, 3, 4, 5
+ACT_NONE, ACT_GELU, ACT_DGELU, ACT_SIGMOID, ACT_TANH, ACT_DTANH, ACT_GELU_GRAD, ACT_MULAUX = 0, 1, 2, 3, 4, 5, 6, 7
 _LAYOUT = {"nt": 0, "nn": 1, "tn": 2}
 _c = ctypes
 _vp, _i, _f, _u, _ll = _c.c_void_p, _c.c_int, _c.c_float, _c.c_uint, _c.c_longlong

@@ -13,7 +13,7 @@ import math
 
 import torch
 
-ACT_NONE, ACT_GELU, ACT_DGELU, ACT_SIGMOID, ACT_TANH, ACT_DTANH = 0, 1, 2, 3, 4, 5
+ACT_NONE, ACT_GELU, ACT_DGELU, ACT_SIGMOID, ACT_TANH, ACT_DTANH, ACT_GELU_GRAD, ACT_MULAUX = 0, 1, 2, 3, 4, 5, 6, 7
 
 _M0, _M1, _W0, _W1 = 0xD2511F53, 0xCD9E8D57, 0x9E3779B9, 0xBB67AE85
 _MASK32 = 0xFFFFFFFF
@@ -108,7 +108,8 @@ class RefOps(object):
     def gemm(self, a, b, layout, out=None, out_dtype=None, bias=None, act=ACT_NONE, aux_in=None,
              aux_out=None, addend=None, drop=None, rng=None, accumulate=False):
         """layout 'nt': a[M,K] b[N,K];  'nn': a[M,K] b[K,N];  'tn': a[K,M] b[K,N]  -> [M,N].
-        v = acc (+bias[n]); GELU: aux_out=v, v=gelu(v); DGELU: v*=gelu'(aux_in); SIGMOID/TANH;
+        v = acc (+bias[n]); GELU: aux_out=v, v=gelu(v); GELU_GRAD: aux_out=gelu'(v), v=gelu(v); DGELU: v*=gelu'(aux_in);
+        MULAUX: v*=aux_in; SIGMOID/TANH;
         DTANH: v *= 1-aux_in^2; then dropout; then += addend; then (accumulate ? out+=v : out=v)."""
         af, bf = a.float(), b.float()
         if layout == "nt":
@@ -125,6 +126,12 @@ class RefOps(object):
             if aux_out is not None:
                 aux_out.copy_(v)
             v = _gelu(v)
+        elif act == ACT_GELU_GRAD:
+            if aux_out is not None:
+                aux_out.copy_(_dgelu(v))
+            v = _gelu(v)
+        elif act == ACT_MULAUX:
+            v = v * aux_in.float()
         elif act == ACT_DGELU:
             v = v * _dgelu(aux_in.float())
         elif act == ACT_SIGMOID:

@@ -78,21 +78,21 @@ def test_gemm_plain(ops, ref, layout, M, N, K):
     close_bf16(got16, want, "gemm bf16 %s" % layout, atol=1e-3)
 
 
-@pytest.mark.parametrize("act", [0, 1, 3, 4])
+@pytest.mark.parametrize("act", [0, 1, 3, 4, 6])
 def test_gemm_epilogue_bias_act_addend(ops, ref, act):
     M, N, K = 300, 776, 264
     a, w = rnd(M, K), rnd(N, K, seed=1, scale=0.06)
     bias, add = rnd(N, seed=2), rnd(M, N, seed=3)
     aux_g = torch.zeros(M, N, dtype=BF, device=DEV)
     aux_r = torch.zeros(M, N, dtype=F32, device=DEV)
-    got = ops.gemm(a, w, "nt", bias=bias, act=act, aux_out=aux_g if act == 1 else None, addend=add)
-    want = ref.gemm(a, w, "nt", bias=bias, act=act, aux_out=aux_r if act == 1 else None, addend=add)
+    got = ops.gemm(a, w, "nt", bias=bias, act=act, aux_out=aux_g if act in (1, 6) else None, addend=add)
+    want = ref.gemm(a, w, "nt", bias=bias, act=act, aux_out=aux_r if act in (1, 6) else None, addend=add)
     close_bf16(got, want, "epilogue act=%d" % act, atol=2e-3)
-    if act == 1:
+    if act in (1, 6):          # 1: the pre-activation, 6 (ACT_GELU_GRAD): gelu'(pre-activation)
         close_bf16(aux_g, aux_r, "aux_out", atol=2e-3)
 
 
-@pytest.mark.parametrize("act", [2, 5])
+@pytest.mark.parametrize("act", [2, 5, 7])
 def test_gemm_epilogue_derivative(ops, ref, act):
     M, N, K = 260, 384, 200
     a, w = rnd(M, K), rnd(K, N, seed=1, scale=0.07)
@@ -137,11 +137,16 @@ BENCH_EPILOGUES = [
     ("attn_out_text", "nt", 9216, 768, 768, "bias_drop_add", ("ctas=2", "epi=F_ADD", "tin=2")),
     ("ffn_down_text", "nt", 9216, 768, 3072, "bias_drop_add", ("ctas=2", "epi=F_ADD", "tin=2")),
     ("ffn_up_text", "nt", 9216, 3072, 768, "bias_gelu", ("ctas=2", "epi=F_GELU")),
+    ("ffn_up_text_grad", "nt", 9216, 3072, 768, "bias_gelu_grad", ("ctas=2", "epi=F_GELU")),
+    ("ffn_up_image_grad", "nt", 4736, 1024, 1024, "bias_gelu_grad", ("ctas=2", "epi=F_GELU")),
     ("qkv_text", "nt", 9216, 2304, 768, "bias", ("ctas=2", "epi=F_PLAIN")),
     ("ffn_down_dgrad_text", "nn", 9216, 3072, 768, "dgelu", ("ctas=2", "epi=F_DGELU", "tin=1")),
+    ("ffn_down_dgrad_text_mulaux", "nn", 9216, 3072, 768, "mulaux", ("ctas=2", "epi=F_DGELU", "tin=1")),
     ("ffn_up_dgrad_text", "nn", 9216, 768, 3072, "add", ("ctas=2", "epi=F_ADD", "tin=2")),
     ("out_image", "nt", 4736, 1024, 1024, "bias_drop_add", ("ctas=2", "epi=F_ADD")),
     ("ffn_up_conn", "nt", 2304, 3072, 768, "bias_gelu", ("ctas=2", "epi=F_GELU")),
+    ("ffn_up_conn_grad", "nt", 2304, 3072, 768, "bias_gelu_grad", ("ctas=2", "epi=F_GELU")),
+    ("ffn_up_ragged_grad", "nt", 2300, 3048, 768, "bias_gelu_grad", ("ctas=2", "epi=F_GELU")),
     ("ffn_down_conn", "nt", 2304, 768, 3072, "bias_drop_add", ("epi=F_ADD",)),
     ("out_conn_image", "nt", 2368, 1024, 1024, "bias_drop_add", ("epi=F_ADD",)),
     ("dgrad_conn", "nn", 2304, 3072, 768, "dgelu", ("ctas=2", "epi=F_DGELU")),
@@ -165,16 +170,19 @@ def test_gemm_bench_shapes_fused_epilogues(ops, ref, name, layout, M, N, K, kind
         kw.update(addend=rnd(M, N, seed=3))
     if kind == "dgelu":
         kw.update(act=2, aux_in=rnd(M, N, seed=4, scale=1.5))
+    if kind == "mulaux":
+        kw.update(act=7, aux_in=rnd(M, N, seed=4, scale=0.6))
     aux_g = aux_r = None
-    if kind == "bias_gelu":
+    gelu_act = {"bias_gelu": 1, "bias_gelu_grad": 6}.get(kind)
+    if gelu_act:
         aux_g = torch.zeros(M, N, dtype=BF, device=DEV)
         aux_r = torch.zeros(M, N, dtype=F32, device=DEV)
-    got = ops.gemm(a, b, layout, act=1, aux_out=aux_g, **kw) if kind == "bias_gelu" else ops.gemm(a, b, layout, **kw)
+    got = ops.gemm(a, b, layout, act=gelu_act, aux_out=aux_g, **kw) if gelu_act else ops.gemm(a, b, layout, **kw)
     v = ops.gemm_last_variant()
     print("%s %s %dx%dx%d: %s" % (name, layout, M, N, K, v))
     for sub in variant:
         assert sub in v, (name, v, sub)
-    want = (ref.gemm(a, b, layout, act=1, aux_out=aux_r, out_dtype=F32, **kw) if kind == "bias_gelu"
+    want = (ref.gemm(a, b, layout, act=gelu_act, aux_out=aux_r, out_dtype=F32, **kw) if gelu_act
             else ref.gemm(a, b, layout, out_dtype=F32, **kw))
     close_bf16(got, want, name, atol=4e-3)
     if aux_g is not None:
@@ -206,7 +214,8 @@ def test_gemm_bench_shapes_weight_gradients(ops, ref, name, M, N, K):
 def _group_case(kind, M, N, K, seed):
     """one problem of a group with epilogue `kind`; returns (kwargs for ops.gemm / gemm_group, extra outputs)"""
     s = 1.0 / math.sqrt(K)
-    layout = {"bias": "nt", "bias_drop_add": "nt", "bias_gelu": "nt", "dgelu": "nn", "add": "nn", "acc": "tn"}[kind]
+    layout = {"bias": "nt", "bias_drop_add": "nt", "bias_gelu": "nt", "bias_gelu_grad": "nt", "dgelu": "nn", "mulaux": "nn",
+              "add": "nn", "acc": "tn"}[kind]
     if layout == "nt":
         a, b = rnd(M, K, seed=seed), rnd(N, K, seed=seed + 1, scale=s)
     elif layout == "nn":
@@ -222,8 +231,12 @@ def _group_case(kind, M, N, K, seed):
         kw.update(addend=rnd(M, N, seed=seed + 3))
     if kind == "dgelu":
         kw.update(act=2, aux_in=rnd(M, N, seed=seed + 4, scale=1.5))
+    if kind == "mulaux":
+        kw.update(act=7, aux_in=rnd(M, N, seed=seed + 4, scale=0.6))
     if kind == "bias_gelu":
         kw.update(act=1)
+    if kind == "bias_gelu_grad":
+        kw.update(act=6)
     return kw
 
 
@@ -237,12 +250,17 @@ GROUPS = {
                     ("bias_gelu", 2304, 3072, 768), ("bias_gelu", 2304, 3072, 768), ("bias_gelu", 2304, 3072, 768)],
     "conn_dgrad_mixed": [("dgelu", 2368, 1024, 1024), ("dgelu", 2304, 3072, 768), ("add", 2304, 768, 3072),
                          ("add", 2368, 1024, 3072)],
+    "conn_ffn_up_grad": [("bias_gelu_grad", 2368, 1024, 1024), ("bias_gelu_grad", 2304, 3072, 768), ("bias_gelu", 2368, 1024, 1024),
+                         ("bias_gelu_grad", 2304, 3072, 768), ("bias_gelu_grad", 2304, 3072, 768), ("bias_gelu", 2304, 3072, 768)],
+    "conn_dffn_mulaux": [("mulaux", 2368, 1024, 1024), ("mulaux", 2304, 3072, 768), ("dgelu", 2368, 1024, 1024),
+                         ("mulaux", 2304, 3072, 768), ("add", 2304, 768, 3072), ("mulaux", 2304, 3072, 768)],
     "conn_wgrad": [("acc", 1024, 1024, 2368), ("acc", 3072, 768, 2304), ("acc", 768, 3072, 2304), ("acc", 768, 768, 2304),
                    ("acc", 1024, 1024, 2368), ("acc", 768, 1024, 2304)],
     # a text and an image layer in lock-step
     "text_image": [("bias_drop_add", 9216, 768, 3072), ("bias_drop_add", 4736, 1024, 1024)],
     # small problems (tiny configs): 128 x 128 single-CTA tiles, ragged edges
     "small": [("bias_gelu", 100, 256, 128), ("bias_gelu", 48, 128, 256), ("bias_gelu", 300, 776, 264)],
+    "small_grad": [("bias_gelu_grad", 100, 256, 128), ("bias_gelu_grad", 48, 128, 256), ("bias_gelu_grad", 300, 776, 264)],
     "small_wgrad": [("acc", 256, 128, 100), ("acc", 128, 256, 48), ("acc", 384, 384, 300)],
     # nine problems: more than one launch's worth (8 per launch)
     "nine": [("bias", 256, 256, 128)] * 9,
@@ -259,7 +277,7 @@ def test_gemm_grouped_matches_single_problem_restatement(ops, ref, name):
         N = kw["b"].shape[0] if kw["layout"] == "nt" else kw["b"].shape[1]
         r = dict(kw)
         aux_g = aux_r = None
-        if kw.get("act") == 1:
+        if kw.get("act") in (1, 6):
             aux_g, aux_r = torch.zeros(M, N, dtype=BF, device=DEV), torch.zeros(M, N, dtype=F32, device=DEV)
             c["aux_out"], r["aux_out"] = aux_g, aux_r
         if kw["layout"] == "tn":
