@@ -52,11 +52,13 @@ FLOPS_PER_SAMPLE = WORKLOADS["base"]["flops_per_unit"]
 
 def ncu_gemm_traffic():
     """`roofline.traffic`: mean dram__bytes_read.sum + dram__bytes_write.sum per launch of the GEMM kernel, read
-    from the committed `ncu --set full` capture of THIS round's build (profiles/r02_ncu_gemm_full.csv, written by
-    tools/ncu_summary.py from the .ncu-rep).  None (unmeasured) when the file is absent."""
-    p = os.path.join(ROOT, "profiles", "r02_ncu_gemm_full.csv")
-    if not os.path.exists(p):
-        return None, "unmeasured: profiles/r02_ncu_gemm_full.csv absent"
+    from the committed `ncu --set full` capture of THIS round's build (profiles/r03_ncu_gemm_full.csv, written by
+    tools/ncu_full_summary.py from the .ncu-rep; the earlier r02 capture when that is absent).  None (unmeasured) when the file is absent."""
+    name = next((n for n in ("r03_ncu_gemm_full.csv", "r02_ncu_gemm_full.csv")
+                 if os.path.exists(os.path.join(ROOT, "profiles", n))), None)
+    if name is None:
+        return None, "unmeasured: profiles/r03_ncu_gemm_full.csv absent"
+    p = os.path.join(ROOT, "profiles", name)
     import csv
     tot, n = 0.0, 0
     for row in csv.DictReader(open(p)):
@@ -66,8 +68,8 @@ def ncu_gemm_traffic():
         except (KeyError, ValueError):
             continue
     if n == 0:
-        return None, "unmeasured: no launches in profiles/r02_ncu_gemm_full.csv"
-    return tot / n, "mean over the %d gemm_kernel launches in profiles/r02_ncu_gemm_full.csv (ncu --set full)" % n
+        return None, "unmeasured: no launches in profiles/%s" % name
+    return tot / n, "mean over the %d gemm_kernel launches in profiles/%s (ncu --set full)" % (n, name)
 
 
 def load_peaks():
