@@ -50,6 +50,20 @@ def input_spec(cfg, B, Lt, Lv1, Lpv, max_num_pv):
     )
 
 
+def _flat_views(spec, device):
+    """spec: ordered (name, shape, dtype) -> (flat uint8 buffer, {name: view}); every view starts 256-byte aligned, so
+    two buffers built from the same spec have the same layout and copy into each other as ONE memcpy."""
+    offs, off = [], 0
+    for _, shape, dtype in spec:
+        n = 1
+        for d_ in shape:
+            n *= int(d_)
+        offs.append((off, n * torch.empty((), dtype=dtype).element_size()))
+        off += (offs[-1][1] + 255) // 256 * 256
+    flat = torch.zeros(max(off, 256), dtype=torch.uint8, device=device)
+    return flat, {name: flat[o:o + nb].view(dtype).view(shape) for (name, shape, dtype), (o, nb) in zip(spec, offs)}
+
+
 class PretrainStep(object):
     KIND = "pretrain"       # parameter inventory / engine entry points (AlignmentStep: "alignment")
     HALVES = 1              # item groups that get their own `structure_aggregator` call
@@ -97,31 +111,35 @@ class PretrainStep(object):
         else:
             self.init_weights(init_seed)
         # static graph inputs
+        # Inputs, index plan and hyper-parameters are views into ONE flat buffer (`_flat_views`): a step's staged
+        # copy reaches the graph's static buffers as one device-to-device memcpy instead of ~25 small ones.
         self.spec = self._input_spec()
-        self.inputs = {k: torch.zeros(s, dtype=d, device=dev) for k, (s, d) in self.spec.items()}
         P_cap, T_cap, maxn = plan_capacity(self.n_items, max_num_pv, cfg.num_negative_pv)
         i32 = torch.int32
-        self.plan = dict(pair_item=torch.zeros(P_cap, dtype=i32, device=dev),
-                         pair_rows=torch.zeros(P_cap, 4, dtype=i32, device=dev),
-                         seg=torch.zeros(self.n_items, 2, dtype=i32, device=dev),
-                         terms=torch.zeros(T_cap, 4, dtype=i32, device=dev),
-                         n_terms=torch.zeros(1, dtype=i32, device=dev),
-                         fallback=torch.full((self.HALVES, 2), -1, dtype=i32, device=dev))
-        self.plan["seg"]._k3m_maxn = maxn
+        plan_spec = [("pair_item", (P_cap,), i32), ("pair_rows", (P_cap, 4), i32), ("seg", (self.n_items, 2), i32),
+                     ("terms", (T_cap, 4), i32), ("n_terms", (1,), i32), ("fallback", (self.HALVES, 2), i32)]
         # masked-LM head on the labelled rows only: static row / label lists of a fixed capacity (`build_mlm_plan`)
         self.mlm_cap = None
         if self.KIND == "pretrain" and mlm_cap_frac is not None:
             self.mlm_cap = mlm_capacity(batch_size * len_t, batch_size * len_pv, mlm_cap_frac)
             n = self.mlm_cap[0] + self.mlm_cap[1]
-            self.plan["mlm_rows"] = torch.full((n,), -1, dtype=i32, device=dev)
-            self.plan["mlm_labels"] = torch.full((n,), -1, dtype=torch.int64, device=dev)
+            plan_spec += [("mlm_rows", (n,), i32), ("mlm_labels", (n,), torch.int64)]
+        self._flat_spec = ([("in:" + k, tuple(s_), d) for k, (s_, d) in self.spec.items()] +
+                           [("plan:" + k, s_, d) for k, s_, d in plan_spec] + [("hyper", (2, 8), f32)])
+        self._static_flat, views = _flat_views(self._flat_spec, dev)
+        self.inputs = {k[3:]: v for k, v in views.items() if k.startswith("in:")}
+        self.plan = {k[5:]: v for k, v in views.items() if k.startswith("plan:")}
+        for k in ("fallback", "mlm_rows", "mlm_labels"):
+            if k in self.plan:
+                self.plan[k].fill_(-1)
+        self.plan["seg"]._k3m_maxn = maxn
         pin = (lambda t: t.pin_memory()) if self._cuda else (lambda t: t)
         self._plan_host = [{k: pin(torch.zeros(v.shape, dtype=v.dtype)) for k, v in self.plan.items()}
                            for _ in range(2)]
         if self.mlm_cap is not None:
             self.plan["mlm_cap_t"] = self.mlm_cap[0]
         # AdamW hyper-parameters live on the device (graph nodes stay valid); ring of pinned copies
-        self.hyper = torch.zeros(2, 8, dtype=f32, device=dev)
+        self.hyper = views["hyper"]
         self._hyper_host = [pin(torch.zeros(2, 8, dtype=f32)) for _ in range(2)]
         self._slot_events = [None, None]
         self._stage, self._copy_stream = None, None
@@ -535,10 +553,11 @@ class PretrainStep(object):
             # kernels), then a device-to-device hop into the graph's static input buffers on the main stream
             if self._stage is None:
                 self._copy_stream = torch.cuda.Stream(device=self.device)
-                mk = lambda t: torch.empty_like(t)          # noqa: E731
-                self._stage = [dict(inputs={k: mk(v) for k, v in self.inputs.items()},
-                                    plan={k: mk(v) for k, v in self.plan.items() if torch.is_tensor(v)}, hyper=mk(self.hyper))
-                               for _ in range(2)]
+                self._stage = []
+                for _ in range(2):
+                    flat, v = _flat_views(self._flat_spec, self.device)
+                    self._stage.append(dict(flat=flat, inputs={k[3:]: t for k, t in v.items() if k.startswith("in:")},
+                                            plan={k[5:]: t for k, t in v.items() if k.startswith("plan:")}, hyper=v["hyper"]))
             st = self._stage[slot]
             main = torch.cuda.current_stream()
             with torch.cuda.stream(self._copy_stream):
@@ -550,11 +569,7 @@ class PretrainStep(object):
                 landed = torch.cuda.Event()
                 landed.record(self._copy_stream)
             main.wait_event(landed)
-            for k in st["plan"]:
-                self.plan[k].copy_(st["plan"][k], non_blocking=True)
-            for k in self.inputs:
-                self.inputs[k].copy_(st["inputs"][k], non_blocking=True)
-            self.hyper.copy_(st["hyper"], non_blocking=True)
+            self._static_flat.copy_(st["flat"], non_blocking=True)      # inputs + plan + hyper: one memcpy
             ev = torch.cuda.Event()
             ev.record(main)                                 # slot's pinned + device staging free again
             self._slot_events[slot] = ev
