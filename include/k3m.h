@@ -33,8 +33,10 @@ extern "C" {
 #define K3M_ACT_SIGMOID 3
 #define K3M_ACT_TANH 4
 #define K3M_ACT_DTANH 5   /* out = v * (1 - aux_in^2)                                        */
-#define K3M_ACT_GELU_GRAD 6 /* out = gelu(v), aux_out = gelu'(v): BertIntermediate forward storing what its backward multiplies by */
-#define K3M_ACT_MULAUX 7  /* out = v * aux_in (backward of K3M_ACT_GELU_GRAD)                   */
+/* BertIntermediate (vilbert_k3m.py:515-518, gelu :119-125) with the derivative computed where Phi(v) already is:
+ * forward  out = gelu(v), aux_out = gelu'(v);  backward (autograd of :518 through the FFN-down dgrad)  out = v * aux_in */
+#define K3M_ACT_GELU_GRAD 6
+#define K3M_ACT_MULAUX 7
 
 /* GEMM operand layouts */
 #define K3M_GEMM_NT 0 /* A[M,K] , B[N,K]  : Y = X W^T    (nn.Linear forward)                   */
