@@ -360,6 +360,51 @@ __device__ __forceinline__ uint4 lds16(uint32_t saddr) {
   return u;
 }
 
+// Packed fp32 pairs (Blackwell FFMA2 / FMUL2 / FADD2: two IEEE-rounded fp32 operations per instruction, results equal
+// to the scalar fmaf / * / + bit for bit).  The epilogues are bound by instruction issue and dependent-issue latency
+// with only four epilogue warps per scheduler; the polynomial part of Phi and the bias / multiply steps halve.
+struct F2 { unsigned long long u; };
+__device__ __forceinline__ F2 f2(float lo, float hi) {
+  F2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r.u) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_get(F2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.u)); }
+__device__ __forceinline__ F2 f2_fma(F2 a, F2 b, F2 c) {
+  F2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.u) : "l"(a.u), "l"(b.u), "l"(c.u));
+  return r;
+}
+__device__ __forceinline__ F2 f2_mul(F2 a, F2 b) {
+  F2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u));
+  return r;
+}
+__device__ __forceinline__ F2 f2_add(F2 a, F2 b) {
+  F2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u));
+  return r;
+}
+// gauss_cdf (common.cuh) on a pair: same operations in the same order per element; `e` = exp(-x^2 / 2) of the pair
+__device__ __forceinline__ F2 gauss_cdf2(F2 x, F2& e) {
+  float x0, x1;
+  f2_get(x, x0, x1);
+  const F2 z = f2_mul(f2(fabsf(x0), fabsf(x1)), f2(0.70710678118654752f, 0.70710678118654752f));
+  float d0, d1;
+  f2_get(f2_fma(f2(0.3275911f, 0.3275911f), z, f2(1.0f, 1.0f)), d0, d1);
+  const F2 t = f2(rcp_approx(d0), rcp_approx(d1));
+  float q0, q1;
+  f2_get(f2_mul(f2_mul(x, x), f2(-0.72134752044448170f, -0.72134752044448170f)), q0, q1);
+  e = f2(ex2_approx(q0), ex2_approx(q1));
+  F2 p = f2_fma(f2(0.5f * 1.061405429f, 0.5f * 1.061405429f), t, f2(0.5f * -1.453152027f, 0.5f * -1.453152027f));
+  p = f2_fma(p, t, f2(0.5f * 1.421413741f, 0.5f * 1.421413741f));
+  p = f2_fma(p, t, f2(0.5f * -0.284496736f, 0.5f * -0.284496736f));
+  p = f2_fma(p, t, f2(0.5f * 0.254829592f, 0.5f * 0.254829592f));
+  float h0, h1;
+  f2_get(f2_mul(f2_mul(p, t), e), h0, h1);
+  return f2(x0 >= 0.0f ? 1.0f - h0 : h0, x1 >= 0.0f ? 1.0f - h1 : h1);
+}
+
 // The bias of a 32-column slab (four 16-byte loads) is requested BEFORE the TMEM read of the slab, so that the two
 // latencies overlap; loading it per 8-column group right where it is added put a global-load round trip in front of
 // every group (long-scoreboard stalls on the unpack instructions, profiles/r03a_gemm_gelu_hot.txt).
@@ -375,7 +420,17 @@ __device__ __forceinline__ void acc_bias(const uint32_t* r, const uint4& braw, f
   float t[8];
   unpack_bf16x8(braw, t);
 #pragma unroll
-  for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[j]) + t[j];
+  for (int j = 0; j < 8; j += 2)
+    f2_get(f2_add(f2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), f2(t[j], t[j + 1])), v[j], v[j + 1]);
+}
+// v[0..8) op= t[0..8) on packed pairs
+__device__ __forceinline__ void mul8(float v[8], const float t[8]) {
+#pragma unroll
+  for (int j = 0; j < 8; j += 2) f2_get(f2_mul(f2(v[j], v[j + 1]), f2(t[j], t[j + 1])), v[j], v[j + 1]);
+}
+__device__ __forceinline__ void add8(float v[8], const float t[8]) {
+#pragma unroll
+  for (int j = 0; j < 8; j += 2) f2_get(f2_add(f2(v[j], v[j + 1]), f2(t[j], t[j + 1])), v[j], v[j + 1]);
 }
 
 // one 32-row x CW-column piece of an output tile, by one epilogue warp (row = lane)
@@ -419,11 +474,13 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
         float v[8], a[8];
         acc_bias(r + g * 8, braw, v);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float e;
-          const float c = gauss_cdf(v[j], e);
-          a[j] = grad ? fmaf(v[j] * e, 0.3989422804014327f, c) : v[j];
-          v[j] *= c;
+        for (int j = 0; j < 8; j += 2) {
+          const F2 x = f2(v[j], v[j + 1]);
+          F2 e;
+          const F2 c = gauss_cdf2(x, e);
+          const F2 dg = f2_fma(f2_mul(x, e), f2(0.3989422804014327f, 0.3989422804014327f), c);
+          f2_get(grad ? dg : x, a[j], a[j + 1]);
+          f2_get(f2_mul(x, c), v[j], v[j + 1]);
         }
         const uint32_t off = swz((uint32_t)lane * 64u + (uint32_t)(g * 16), 3u);
         sts16(sbuf + off, pack_bf16x8(a));
@@ -473,8 +530,7 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
         float t[8];
         unpack_bf16x8(lds16(sbuf + off), t);
         if (p.act == ACT_MULAUX) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] *= t[j];
+          mul8(v, t);
         } else {
 #pragma unroll
           for (int j = 0; j < 8; ++j) v[j] *= dgelu_f(t[j]);
@@ -486,14 +542,15 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
         const unsigned long long idx = lin >> 3;      // == rng_words(p.drop.rng, p.drop.site, idx, w)
         philox4x32((uint32_t)idx, (uint32_t)(idx >> 32), p.drop.site, (uint32_t)step, (uint32_t)seed,
                    (uint32_t)(seed >> 32), w);
+        float dm[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] *= drop_mult(p.drop, w, j);
+        for (int j = 0; j < 8; ++j) dm[j] = drop_mult(p.drop, w, j);
+        mul8(v, dm);
       }
       if (MODE == F_ADD) {
         float t[8];
         unpack_bf16x8(lds16(sbuf + off), t);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] += t[j];
+        add8(v, t);
       }
       sts16(sbuf + off, pack_bf16x8(v));
     }
