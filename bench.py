@@ -199,7 +199,8 @@ def run_reference_arm(args):
 
 
 # ---- GPU arm ------------------------------------------------------------------------------------------
-HBM_KERNELS = ("k3m_ln_fwd", "k3m_ln_bwd", "k3m_colsum", "k3m_xent_fwd_bwd", "k3m_kl_fwd_bwd", "k3m_adamw", "k3m_adamw_bg",
+HBM_KERNELS = ("k3m_ln_fwd", "k3m_ln_fwd_grouped", "k3m_ln_bwd", "k3m_ln_bwd_grouped", "k3m_colsum", "k3m_colsum_grouped",
+               "k3m_xent_fwd_bwd", "k3m_kl_fwd_bwd", "k3m_adamw", "k3m_adamw_bg",
                "k3m_embed_fwd", "k3m_embed_bwd", "k3m_relu_cat3", "k3m_fuse_select_fwd", "k3m_fuse_select_bwd",
                "k3m_relu_bwd_split3", "k3m_axpy", "k3m_cast")
 
