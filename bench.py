@@ -357,7 +357,7 @@ def class_api_rate(dev, steps, warmup=4):
         loss = one(host[i % 4])
         if last is not None:
             float(last)                  # the previous step's loss: one device -> host read per step, one step late
-        last = loss
+        last = loss.detach()
     float(last)
     e1.record()
     torch.cuda.synchronize()
