@@ -872,7 +872,8 @@ extern "C" int k3m_ln_bwd_grouped(const void* descs, int n, void* stream) {
   // a third fewer instructions and no exposed row loads, but 109 registers (two CTAs per SM instead of three), three
   // block barriers per tile and a quarter of the phase-2 threads idle at H = 768 — measured EQUAL to the row-per-warp
   // form on the step (17.54 / 17.69 vs 17.59 / 17.64 ms, profiles/r03l_ln_bwd_tile_ab.txt; the GPU suite passes with
-  // either).  Kept selectable (K3M_LN_BWD_TILE=1) as the record of that experiment; off by default.
+  // either; forced to 80 registers / three CTAs per SM it is 0.3 ms SLOWER, profiles/r03m_ln_bwd_tile_ab.txt).  Kept
+  // selectable (K3M_LN_BWD_TILE=1) as the record of that experiment; off by default.
   static const int tile_mode = getenv("K3M_LN_BWD_TILE") ? atoi(getenv("K3M_LN_BWD_TILE")) : 0;
   static const int tile_ctas = getenv("K3M_LN_BWD_TILE_CTAS") ? atoi(getenv("K3M_LN_BWD_TILE_CTAS")) : 2;
   int hmin = hmax;
