@@ -193,6 +193,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t addr, uint32_t r[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void tmem_ld16(uint32_t addr, uint32_t r[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(addr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
 // shared-memory matrix descriptor (SWIZZLE_128B, descriptor version 1)
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   uint64_t d = 0;
@@ -328,8 +337,9 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const 
 //   F_ADD    out = acc (+ bias) (dropout) + addend (via TMA)     attention-out / FFN-down, dgrad + residual
 //   F_GELU   aux = acc + bias, out = gelu(aux)                   FFN-up
 //   F_DGELU  out = acc * gelu'(aux_in) (aux_in via TMA)          FFN-down dgrad
+//   F_ACC    out += acc (fp32, TMA bulk reduce-add)               weight gradients (split-K partial sums)
 // Preconditions (host): bf16 output through TMA, no accumulation, N % 8 == 0, 16-byte aligned bias.
-enum { F_NONE = 0, F_PLAIN = 1, F_ADD = 2, F_GELU = 3, F_DGELU = 4 };
+enum { F_NONE = 0, F_PLAIN = 1, F_ADD = 2, F_GELU = 3, F_DGELU = 4, F_ACC = 5 };
 
 __device__ __forceinline__ uint4 pack_bf16x8(const float v[8]) {
   uint4 u;
@@ -443,6 +453,33 @@ __device__ __forceinline__ void fast_tile(const GemmParams& p, const CUtensorMap
   uint8_t* buf = my_stage + (nstore % NBUF) * 4096;
   uint8_t* abuf = my_stage + ((nstore + 1) % NBUF) * 4096;
   const uint32_t sbuf = smem_u32(buf), sabuf = smem_u32(abuf);
+  if (MODE == F_ACC) {
+    // Weight-gradient partial sums: the accumulator leaves as fp32 through TMA bulk reduce-add, 16 columns (64-byte
+    // rows, SWIZZLE_64B boxes) at a time through the two 2 KB halves of the staging buffer — a half is rewritten
+    // only after the reduce issued two chunks earlier has read it (wait_group.read 1), so nothing waits mid-tile.
+    // The generic epilogue spent ~35 instructions per element deciding at run time what this path knows statically.
+#pragma unroll
+    for (int cc = 0; cc < CW; cc += 16) {
+      if (n0 + cc >= p.N) break;
+      const int h = (cc >> 4) & 1;
+      uint32_t r[16];
+      tmem_ld16(tbase + (uint32_t)cc, r);
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+      __syncwarp();
+      const uint32_t base = sbuf + (uint32_t)h * 2048u;
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        sts16(base + swz((uint32_t)lane * 64u + (uint32_t)(q * 16), 3u), make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]));
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) {
+        tma_reduce_add_2d(mc, buf + h * 2048, n0 + cc, row0);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    }
+    nstore += 1;
+    return;
+  }
   if (MODE == F_PLAIN || MODE == F_GELU) {        // (TMA-fed modes: the operand prefetch waited already)
     if (lane == 0) {
       if (MODE == F_GELU || NBUF == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -872,6 +909,7 @@ gemm_kernel(const __grid_constant__ GroupArgs<MAXP> g) {
             case F_PLAIN: fast_tile<CW, NBUF, F_PLAIN>(p, map_c, map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
             case F_ADD: fast_tile<CW, NBUF, F_ADD>(p, map_c, map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
             case F_GELU: fast_tile<CW, NBUF, F_GELU>(p, map_c, map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
+            case F_ACC: fast_tile<CW, NBUF, F_ACC>(p, map_c, map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
             default: fast_tile<CW, NBUF, F_DGELU>(p, map_c, map_aux, my_stage, nstore, tbase, row0, n0, lane); break;
           }
         } else {
@@ -1321,6 +1359,12 @@ int setup_problem(const Desc& d, int bn, int ctas, int ew, int nbuf, int splits,
       p.fast = F_DGELU;
     }
   }
+  static const int no_facc = getenv("K3M_GEMM_NO_FACC") ? atoi(getenv("K3M_GEMM_NO_FACC")) : 0;
+  if (!no_fast && !no_facc && p.tma_out && d.out_f32 && d.accumulate && d.act == ACT_NONE && d.bias == nullptr &&
+      d.addend == nullptr && d.aux_out == nullptr && p.drop.thresh == 0 && N % 4 == 0) {
+    p.fast = F_ACC;               // 16-column fp32 boxes (64-byte rows) for the half-buffer reduce-add epilogue
+    if (!get_map(d.out, N, M, d.ldc, 16, 32, &out->map_c, 4)) return K3M_ERR_CUDA;
+  }
   // F_GELU with ONE staging buffer per epilogue warp stores 32-column slabs from the two halves of that buffer
   // (fast_tile): output and saved-operand maps with 32 x 32 boxes (64-byte rows, SWIZZLE_64B)
   if (p.fast == F_GELU && nbuf == 1 && cw == 64) {
@@ -1331,7 +1375,7 @@ int setup_problem(const Desc& d, int bn, int ctas, int ew, int nbuf, int splits,
 }
 
 const char* fast_name(int f) {
-  static const char* names[] = {"generic", "F_PLAIN", "F_ADD", "F_GELU", "F_DGELU"};
+  static const char* names[] = {"generic", "F_PLAIN", "F_ADD", "F_GELU", "F_DGELU", "F_ACC"};
   return names[f];
 }
 
