@@ -229,7 +229,14 @@ class CudaOps(object):
         of a stage, a text and an image layer, a stage's weight gradients) then fill whole waves of CTA pairs
         together instead of each paying its own launch latency with half the SMs idle."""
         n = len(calls)
-        if n == 1 or not self.use_groups:
+
+        def f32_store(c):        # fp32 outputs that do not accumulate are not supported by the bf16 grouped entry point
+            if self.adt == torch.float32:      # (the fp32 check library stores fp32 everywhere and groups them fine)
+                return False
+            o = c.get("out")
+            dt = o.dtype if o is not None else (c.get("out_dtype") or self.adt)
+            return dt == torch.float32 and not (o is not None and c.get("accumulate", False))
+        if n == 1 or not self.use_groups or any(f32_store(c) for c in calls):
             return [self.gemm(**c) for c in calls]
         outs = []
         for i0 in range(0, n, 8):

@@ -305,6 +305,34 @@ def test_gemm_grouped_matches_single_problem_restatement(ops, ref, name):
             close_bf16(aux_g, aux_r, "%s[%d] aux_out" % (name, i), atol=4e-3)
 
 
+@pytest.mark.parametrize("shapes", [[(36, 384, 384), (40, 384, 384), (30, 768, 768)], [(300, 776, 264), (2304, 2304, 768)]],
+                         ids=["tiny", "mixed"])
+def test_gemm_grouped_fp32_outputs_and_in_place_addends(ops, ref, shapes):
+    """`gemm_group` with the epilogues the step itself only issues as single launches: fp32 STORE outputs with a bias
+    (the grouped entry point rejects those — a grouped fp32 store was found wrong on small problems — and the op table
+    issues them singly) and a residual addend that IS the output buffer (the fusion gates' input gradient)."""
+    calls, wants = [], []
+    for i, (M, N, K) in enumerate(shapes):
+        a, b, bias = rnd(M, K, seed=3 * i), rnd(N, K, seed=3 * i + 1, scale=1.0 / math.sqrt(K)), rnd(N, seed=3 * i + 2)
+        calls.append(dict(a=a, b=b, layout="nt", bias=bias, out_dtype=F32))
+        wants.append(ref.gemm(a, b, "nt", bias=bias, out_dtype=F32))
+    outs = ops.gemm_group(calls)
+    print("group fp32 out: %s" % ops.gemm_last_variant())
+    for i, (got, want) in enumerate(zip(outs, wants)):
+        assert got.dtype == F32
+        close(got, want, 2e-3, 2e-3, "fp32 out [%d]" % i)
+    calls, wants = [], []
+    for i, (M, N, K) in enumerate(shapes):
+        a, b = rnd(M, K, seed=30 + 3 * i), rnd(K, N, seed=31 + 3 * i, scale=1.0 / math.sqrt(K))
+        buf = rnd(M, N, seed=32 + 3 * i)
+        wants.append(ref.gemm(a, b, "nn", addend=buf.clone(), out_dtype=F32))
+        calls.append(dict(a=a, b=b, layout="nn", addend=buf, out=buf))
+    outs = ops.gemm_group(calls)
+    print("group in-place addend: %s" % ops.gemm_last_variant())
+    for i, (got, want) in enumerate(zip(outs, wants)):
+        close_bf16(got, want, "in-place addend [%d]" % i, atol=4e-3)
+
+
 def test_gemm_strided_views(ops, ref):
     # operands / outputs that are column slices of wider buffers (qkv, logits[:, :V])
     M, K, N = 192, 256, 200
