@@ -3,7 +3,8 @@
 `warmup_linear_factor` restates `pytorch_transformers==1.1.0` `WarmupLinearSchedule` (third-party,
 not vendored in the reference; call sites `pretrain.py:380-384,927-931`): a LambdaLR whose factor is
 `step / max(1, warmup)` during warm-up and `max(0, (T - step) / max(1, T - warmup))` afterwards.
-Parity for it is unpinned (the reference holds no test for it).
+The 1.1.0 source is absent here (the reference holds no test for it); the factor is held to the renamed successor
+`transformers.get_linear_schedule_with_warmup` in `tests/test_oracle.py`.
 
 `param_groups` reproduces the from-scratch grouping rule of `pretrain.py:835-851`.
 """

@@ -91,3 +91,23 @@ def test_warmup_linear_schedule():
     assert abs(warmup_linear_lambda(55, 10, 100) - 0.5) < 1e-12
     assert warmup_linear_lambda(100, 10, 100) == 0.0
     assert warmup_linear_lambda(150, 10, 100) == 0.0
+
+
+def test_warmup_linear_schedule_against_the_library_successor():
+    """`WarmupLinearSchedule` of pytorch_transformers 1.1.0 (`pretrain.py:380-384,927-931`) is not in this image; its
+    renamed successor in the same library line, `transformers.get_linear_schedule_with_warmup` (transformers 5.5 here),
+    is.  Both the oracle's and the product's factor are held to the successor's LambdaLR over whole runs — learning
+    rates of a real torch optimizer, step by step, incl. the degenerate warm-ups (0, 1, == total, > total).  This pins
+    the schedule to the published successor, not to the 1.1.0 source (DESIGN.md section 4 says which)."""
+    transformers = pytest.importorskip("transformers")
+    from k3m_b200.optim import warmup_linear_factor
+    for warm, total in [(0, 7), (1, 9), (10, 100), (37, 1000), (50, 50), (60, 50), (3, 4)]:
+        p = torch.nn.Parameter(torch.zeros(1))
+        opt = torch.optim.SGD([p], lr=1e-4)
+        sch = transformers.get_linear_schedule_with_warmup(opt, num_warmup_steps=warm, num_training_steps=total)
+        for step in range(total + 5):
+            want = sch.get_last_lr()[0]
+            assert want == 1e-4 * warmup_linear_lambda(step, warm, total), (warm, total, step)
+            assert want == 1e-4 * warmup_linear_factor(step, warm, total), (warm, total, step)
+            opt.step()
+            sch.step()
