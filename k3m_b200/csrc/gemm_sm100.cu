@@ -1475,7 +1475,9 @@ extern "C" int k3m_gemm_grouped_bf16(const void* descs, int n, void* stream) {
     K3M_REQUIRE(d[i].layout == d[0].layout, "gemm_grouped: every problem of a group must have the same layout");
     // fp32 outputs of a grouped launch must accumulate (weight gradients): a grouped fp32 STORE output was found wrong
     // on small problems (tests/test_kernels_gpu.py, round 2) and is not needed by the step — issue those singly
-    K3M_REQUIRE(!d[i].out_f32 || d[i].accumulate, "gemm_grouped: fp32 outputs must accumulate; use k3m_gemm_bf16 for problem %d", i);
+    // (K3M_GEMM_GROUPED_F32_STORE=1 lifts the check for tools/debug_group_f32.py, the reproducer of that defect)
+    static const int allow_f32_store = getenv("K3M_GEMM_GROUPED_F32_STORE") ? atoi(getenv("K3M_GEMM_GROUPED_F32_STORE")) : 0;
+    K3M_REQUIRE(allow_f32_store || !d[i].out_f32 || d[i].accumulate, "gemm_grouped: fp32 outputs must accumulate; use k3m_gemm_bf16 for problem %d", i);
   }
   // variant: CTA pairs (256 x 256 tile per pair) when every problem is at least one pair tile in both directions
   // and the group as a whole fills the pairs; else 128 x 128 single-CTA tiles

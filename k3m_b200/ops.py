@@ -2,6 +2,7 @@
 strides and the current CUDA stream to libk3m_sm100a.so, and returns torch tensors that own the
 outputs.  torch is used for memory and streams only — no torch arithmetic runs here."""
 import ctypes
+import os
 
 import torch
 
@@ -232,6 +233,8 @@ class CudaOps(object):
 
         def f32_store(c):        # fp32 outputs that do not accumulate are not supported by the bf16 grouped entry point
             if self.adt == torch.float32:      # (the fp32 check library stores fp32 everywhere and groups them fine)
+                return False
+            if os.environ.get("K3M_GEMM_GROUPED_F32_STORE", "0") == "1":      # tools/debug_group_f32.py only
                 return False
             o = c.get("out")
             dt = o.dtype if o is not None else (c.get("out_dtype") or self.adt)
