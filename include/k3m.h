@@ -64,8 +64,7 @@ int k3m_gemm_bf16(const void* a, int lda, const void* b, int ldb, int layout, in
  * walks the concatenated tile list (longest-k problems first), so the small M ~ 2304 problems of the three
  * connection layers of a stage (vilbert_k3m.py:1030-1111, called at :1686-1750 once per pass), a text and an
  * image layer, or a stage's weight gradients fill whole waves of CTA pairs together.  Each K3MGemmDesc holds
- * the arguments of k3m_gemm_bf16 (same meaning, same epilogues), except that an fp32 output must accumulate
- * (out_f32 && !accumulate is rejected: issue such problems through k3m_gemm_bf16).                         */
+ * the arguments of k3m_gemm_bf16 (same meaning, same epilogues).                                            */
 typedef struct K3MGemmDesc {
   const void* a; int lda; const void* b; int ldb; int layout; int M, N, K;
   void* out; int ldc; int out_f32; int accumulate; const void* bias; int act;

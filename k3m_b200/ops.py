@@ -223,7 +223,7 @@ class CudaOps(object):
                    r, s, p, self._st())
         return out
 
-    def gemm_group(self, calls):
+    def gemm_group(self, calls, group_f32_store=False):
         """Several independent GEMMs of ONE layout as one persistent launch (`k3m_gemm_grouped_bf16`): `calls` is a
         list of dicts with the keyword arguments of `gemm` (a, b, layout, out, out_dtype, bias, act, aux_in, aux_out,
         addend, drop, rng, accumulate).  Returns the list of outputs.  Small problems (the three connection layers
@@ -231,10 +231,9 @@ class CudaOps(object):
         together instead of each paying its own launch latency with half the SMs idle."""
         n = len(calls)
 
-        def f32_store(c):        # fp32 outputs that do not accumulate are not supported by the bf16 grouped entry point
-            if self.adt == torch.float32:      # (the fp32 check library stores fp32 everywhere and groups them fine)
-                return False
-            if os.environ.get("K3M_GEMM_GROUPED_F32_STORE", "0") == "1":      # tools/debug_group_f32.py only
+        def f32_store(c):        # fp32 outputs that do not accumulate: issued singly unless asked (`group_f32_store`) —
+            # the step's few such problems (fusion gates) measured no faster grouped (profiles/r03o_fuse_group_ab.txt)
+            if self.adt == torch.float32 or group_f32_store:
                 return False
             o = c.get("out")
             dt = o.dtype if o is not None else (c.get("out_dtype") or self.adt)

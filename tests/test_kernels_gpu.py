@@ -309,18 +309,36 @@ def test_gemm_grouped_matches_single_problem_restatement(ops, ref, name):
                          ids=["tiny", "mixed"])
 def test_gemm_grouped_fp32_outputs_and_in_place_addends(ops, ref, shapes):
     """`gemm_group` with the epilogues the step itself only issues as single launches: fp32 STORE outputs with a bias
-    (the grouped entry point rejects those — a grouped fp32 store was found wrong on small problems — and the op table
-    issues them singly) and a residual addend that IS the output buffer (the fusion gates' input gradient)."""
+    (the GENERIC epilogue; the op table issues them singly by default, `group_f32_store=True` sends them through
+    k3m_gemm_grouped_bf16) and a residual addend that IS the output buffer (the fusion gates' input gradient).
+    The grouped generic epilogue with a bias was wrong once in the 128 x 128 variant (bias elements 3, 5, 7 of every 8
+    read registers the load never wrote — `ld8_bits` in gemm_sm100.cu, tools/debug_group_f32.py); the grouped arm
+    below and the sigmoid / tanh groups are its regression test."""
     calls, wants = [], []
     for i, (M, N, K) in enumerate(shapes):
         a, b, bias = rnd(M, K, seed=3 * i), rnd(N, K, seed=3 * i + 1, scale=1.0 / math.sqrt(K)), rnd(N, seed=3 * i + 2)
         calls.append(dict(a=a, b=b, layout="nt", bias=bias, out_dtype=F32))
         wants.append(ref.gemm(a, b, "nt", bias=bias, out_dtype=F32))
-    outs = ops.gemm_group(calls)
-    print("group fp32 out: %s" % ops.gemm_last_variant())
-    for i, (got, want) in enumerate(zip(outs, wants)):
-        assert got.dtype == F32
-        close(got, want, 2e-3, 2e-3, "fp32 out [%d]" % i)
+    for grouped in (False, True):
+        outs = ops.gemm_group(calls, group_f32_store=grouped)
+        v = ops.gemm_last_variant()
+        print("group fp32 out (grouped launch: %s): %s" % (grouped, v))
+        assert ("group=%d" % len(shapes) in v) == grouped and "epi=generic" in v, v
+        for i, (got, want) in enumerate(zip(outs, wants)):
+            assert got.dtype == F32
+            close(got, want, 2e-3, 2e-3, "fp32 out [%d] grouped=%s" % (i, grouped))
+    # bf16 outputs through the generic epilogue of a grouped launch: bias + sigmoid / tanh (no specialised epilogue)
+    for act in (3, 4):
+        calls, wants = [], []
+        for i, (M, N, K) in enumerate(shapes):
+            a, b, bias = rnd(M, K, seed=50 + 3 * i), rnd(N, K, seed=51 + 3 * i, scale=1.0 / math.sqrt(K)), rnd(N, seed=52 + 3 * i)
+            calls.append(dict(a=a, b=b, layout="nt", bias=bias, act=act))
+            wants.append(ref.gemm(a, b, "nt", bias=bias, act=act, out_dtype=F32))
+        outs = ops.gemm_group(calls)
+        v = ops.gemm_last_variant()
+        assert "group=%d" % len(shapes) in v and "epi=generic" in v, v
+        for i, (got, want) in enumerate(zip(outs, wants)):
+            close_bf16(got, want, "generic act %d [%d]" % (act, i), atol=4e-3)
     calls, wants = [], []
     for i, (M, N, K) in enumerate(shapes):
         a, b = rnd(M, K, seed=30 + 3 * i), rnd(K, N, seed=31 + 3 * i, scale=1.0 / math.sqrt(K))

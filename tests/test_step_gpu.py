@@ -263,14 +263,21 @@ def test_checkpoint_resume_continues_the_run_on_gpu(tmp_path):
     c.step(batches[2])
     torch.cuda.synchronize()
     # fp32 reductions whose order is not fixed (split-K reduce-adds, embedding scatter-adds) keep two runs of
-    # the same step from being bit-identical, and Adam turns a last-bit change of a ~0 gradient into a change
-    # of up to lr: compare norms, and the losses (which see the restored dropout stream and weights)
-    for x, y, tol in ((c.p32, a.p32, 1e-5), (c.m, a.m, 1e-3), (c.v, a.v, 1e-3)):
+    # the same step from being bit-identical.  Usually the parameters of two runs then differ by ~1e-9 relative
+    # (tools/debug_resume.py: 13 fresh runs x 3 steps, <= 6e-8; Adam amplifies the order noise of gradients that are
+    # zero by construction: struc_w2.bias, key biases), but now and then one bf16 value of the backward chain rounds
+    # the other way and every gradient below it moves by ~1e-3 — the floor test_training_mode_is_deterministic_
+    # given_rng_state documents (5e-3 of the gradient norm) — which Adam turns into a few per cent of lr per element:
+    # this test saw 3.3e-4 of the parameter norm ONCE in ~10 validation runs (profiles/r03last_gpu_tests.log) against
+    # its former 1e-5 bound.  The bounds below admit that event and still separate the failures the test is about:
+    # a dropout / Gumbel stream that does not continue, or moments / step count that are not restored, move every
+    # element with a gradient by a sizeable fraction of lr (the last assertion prints and checks the second case).
+    for x, y, tol in ((c.p32, a.p32, 1.5e-3), (c.m, a.m, 1e-2), (c.v, a.v, 1e-2)):
         assert float((x - y).norm()) <= tol * float(y.norm())
     assert float((c.p32 - a.p32).abs().max()) <= 2.5e-3
     la, lc = a.read_losses(), c.read_losses()
     for k in la:
-        assert lc[k] == pytest.approx(la[k], rel=1e-4, abs=1e-6), k
+        assert lc[k] == pytest.approx(la[k], rel=5e-4, abs=1e-6), k
     # without the moments / step count the same third step lands elsewhere
     d = PretrainStep(cfg, 4, **kw)
     d.load_state_dict(b.state_dict())
@@ -278,4 +285,6 @@ def test_checkpoint_resume_continues_the_run_on_gpu(tmp_path):
     random.seed(2)
     d.step(batches[2])
     torch.cuda.synchronize()
-    assert float((d.p32 - a.p32).norm()) > 50 * float((c.p32 - a.p32).norm())
+    nd, nc, na = float((d.p32 - a.p32).norm()), float((c.p32 - a.p32).norm()), float(a.p32.norm())
+    print("resume: |c - a| = %.3e, |d - a| (moments lost) = %.3e, |a| = %.3e" % (nc, nd, na))
+    assert nd > 4 * nc and nd > 1e-4 * na

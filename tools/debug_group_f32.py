@@ -1,14 +1,15 @@
-"""Reproducer of the guarded defect of `k3m_gemm_grouped_bf16`: fp32 outputs that are STORED (not accumulated) by a
-grouped launch of small problems (128 x 128 single-CTA tiles, 16 epilogue warps) were found wrong by
-tests/test_kernels_gpu.py::test_gemm_grouped_fp32_outputs_and_in_place_addends; the entry point rejects them since.
-Run with K3M_GEMM_GROUPED_F32_STORE=1 (lifts the check); prints, per problem, how the result differs from the
-fp32 reference so that the failing piece (tile walk, staging layout, bulk store) can be told apart.
-Usage: K3M_GEMM_GROUPED_F32_STORE=1 python tools/debug_group_f32.py [case ...]"""
+"""Reproducer of a (fixed) defect of `k3m_gemm_grouped_bf16`: fp32 outputs STORED (not accumulated) by a grouped launch
+of small problems (128 x 128 single-CTA tiles, 16 epilogue warps) with a bias were wrong
+(tests/test_kernels_gpu.py::test_gemm_grouped_fp32_outputs_and_in_place_addends).  Prints, per problem, how the result
+differs from the fp32 reference.  What it showed (profiles/r03last_group_f32.txt): only WITH a bias, elements 3, 5, 7
+of every 8-column group, every row, garbage up to 1e38 — the generic epilogue's bias unpack (`ld8` through a punned
+pointer) compiled, in that one instantiation, to uniform-register code reading registers the load never wrote.
+Fixed by `ld8_bits` (gemm_sm100.cu); profiles/r03fix_group_f32.txt is this script on the fixed library.
+Usage: python tools/debug_group_f32.py [case ...]"""
 import math
 import os
 import sys
 
-os.environ.setdefault("K3M_GEMM_GROUPED_F32_STORE", "1")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 
@@ -61,7 +62,7 @@ def main():
             w = a.float() @ b.float().t()
             wants.append(w + bias.float() if with_bias else w)
         singles = [ops.gemm(**c) for c in calls]
-        outs = ops.gemm_group(calls)
+        outs = ops.gemm_group(calls, group_f32_store=True)
         torch.cuda.synchronize()
         print("%s: %s" % (name, ops.gemm_last_variant()))
         for i, (g, s, w) in enumerate(zip(outs, singles, wants)):
