@@ -24,6 +24,8 @@ def main():
               use_graph=os.environ.get("K3M_DEBUG_GRAPH", "1") != "0", len_t=12, len_v=9, len_pv=20, max_num_pv=4)
     batches = [synth_batch(cfg, 4, 12, 9, 20, max_num_pv=4, seed=60 + i) for i in range(3)]
     ref = None
+    detail_above = float(os.environ.get("K3M_DEBUG_DETAIL_ABOVE", "0"))     # per-tensor table only for larger differences
+    worst, quiet = [0.0, 0.0, 0.0], [0, 0, 0]
     for r in range(runs):
         s = PretrainStep(cfg, 4, **kw)
         snaps = []
@@ -52,6 +54,10 @@ def main():
                                  float(dm.max()), float(m0[off:off + num].abs().max()), n))
             rows.sort(reverse=True)
             tot = float((p - p0).norm()) / float(p0.norm())
+            worst[i] = max(worst[i], tot)
+            if tot < detail_above:
+                quiet[i] += 1
+                continue
             print("run %d step %d: rel param diff %.3e, %d tensors differ, loss diff %s; top by norm:" % (
                 r, i + 1, tot, len(rows), {k: "%.1e" % abs(lo[k] - lo0[k]) for k in lo if lo[k] != lo0[k]}))
             for dn, dx, cnt, num, dmx, mmax, n in rows[:10]:
@@ -60,6 +66,8 @@ def main():
             kb = sum(x[0] ** 2 for x in rows if ".key.bias" in x[6] or "key" in x[6] and "bias" in x[6]) ** 0.5
             print("    share of the difference in key biases: %.3f" % (kb / max(float((p - p0).norm()), 1e-30)))
         del s
+    print("%d runs: largest relative parameter difference to run 0 after step 1 / 2 / 3: %.3e / %.3e / %.3e; "
+          "run-steps below the detail threshold %.1e: %s" % (runs, worst[0], worst[1], worst[2], detail_above, quiet))
 
 
 if __name__ == "__main__":
