@@ -405,6 +405,7 @@ def run_gpu_arm(args):
     # warm-up through the public call (captures the graph on the first step)
     for i in range(max(3, args.warmup)):
         step.step(host[i % 4])
+        step.read_losses_lagged()          # the timed end-to-end loop's read path is warmed too (its pinned ring, events)
         note("warm-up step %d queued" % i)
     loss0 = step.read_losses()
     note("warm-up done %s" % loss0)

@@ -145,6 +145,12 @@ class PretrainStep(object):
         self._stage, self._copy_stream = None, None
         self.losses = torch.zeros(8, dtype=f32, device=dev)
         self.losses_host = pin(torch.zeros(8, dtype=f32))
+        # ring of `read_losses_lagged`: pinned here rather than on its first call (a page-locked allocation is a
+        # device-wide synchronisation point and does not belong inside a running training loop; measured: it was NOT
+        # what separates the end-to-end from the device-resident step time, profiles/r03end2_bench.json)
+        self._loss_ring = [pin(torch.zeros(8, dtype=f32)) for _ in range(2)]
+        self._loss_events = [None, None]
+        self._loss_reads = 0
         self.h2d_bytes = sum(int(np.prod(s)) * (8 if d == torch.int64 else 4) for s, d in self.spec.values())
         self.h2d_bytes += sum(v.numel() * v.element_size() for v in self.plan.values() if torch.is_tensor(v)) + self.hyper.numel() * 4
         self.d2h_bytes = self.losses.numel() * 4
@@ -593,11 +599,6 @@ class PretrainStep(object):
         PREVIOUS step's (None after the first step), waiting only for that older copy.  The host then
         prepares step i+1 (index plan, H2D) while the device runs step i — the reference's drivers block
         on five `.cpu()` calls per step instead (`pretrain.py:1071-1075`).  `read_losses()` drains."""
-        if not hasattr(self, "_loss_ring"):
-            pin = (lambda t: t.pin_memory()) if self._cuda else (lambda t: t)
-            self._loss_ring = [pin(torch.zeros(8, dtype=torch.float32)) for _ in range(2)]
-            self._loss_events = [None, None]
-            self._loss_reads = 0
         slot = self._loss_reads & 1
         prev = slot ^ 1
         had_prev = self._loss_reads > 0
