@@ -9,10 +9,12 @@ Every function cites the reference lines it follows.
 
 Pinning: the reference has no tests / golden vectors of its own for this path, so
 the oracle is pinned against the reference itself, imported unmodified in the build container
-(`oracle/ref_harness.py`): `tests/test_oracle_vs_reference.py` compares losses, c_initial /
-c_final and all 912 gradients on identical weights and inputs, and
-`tools/make_golden.py` writes reference outputs to `tests/golden/*.pt`, which
-`tests/test_oracle_golden.py` re-checks anywhere (including the GPU box).
+(`oracle/ref_harness.py`): `tests/test_oracle.py::test_oracle_matches_live_reference` compares
+losses, c_initial / c_final and the gradients on identical weights and inputs where `/root/reference`
+is mounted, and `tools/make_golden.py` writes reference outputs (losses, per-layer taps, gradient
+samples) to `tests/golden/*.pt`, which `tests/test_oracle.py::test_oracle_matches_golden` (and
+`tests/test_alignment_cpu.py::test_oracle_alignment_matches_reference` for the alignment model)
+re-check anywhere, including the GPU box.
 """
 import math
 import random
